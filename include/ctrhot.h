@@ -1,0 +1,221 @@
+/* libctrhot -- C-ABI of the B200-native CTR forward hot path.
+ *
+ * The reference (Hcyand/recommender_system) is pure Python on TensorFlow and has
+ * no FFI of its own; its only seam is the Keras object protocol
+ * (Layer.build/call, Model.call).  Each entry point below replaces the
+ * arithmetic of one such call() body; the citation names it.  Citations are
+ * relative to /root/reference/algorithm/deep_learning/ ("DL/").
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes; every function returns an int:
+ *    0 ok, <0 a ctrhot_status.  Nothing throws, nothing allocates
+ *    caller-visible memory: the caller owns every input/output/workspace buffer.
+ *  - All data pointers are DEVICE pointers unless the name starts with h_
+ *    (host).  Matrices are row-major with an explicit leading dimension (ld, in
+ *    elements).  Vectorised paths need 16-byte aligned bases and ld % 4 == 0;
+ *    otherwise a scalar path is taken (never an error).
+ *  - Launches are asynchronous on `stream` (a cudaStream_t passed as void*);
+ *    entry points are re-entrant and keep no mutable global state.
+ *  - Embedding tables of one layer live in one arena [sum(V_f), k] fp32;
+ *    row_off[f] is the first arena row of field f, row_off[F] the total
+ *    (int64, device).  Out-of-range ids write zeros and set *err_flag (device
+ *    int, may be NULL); ctrhot_check_flag() turns it into CTRHOT_EID.
+ *  - ids come either as int32 [B, ids_ld] (CTRHOT_IDS_I32) or as the
+ *    reference's float columns (CTRHOT_IDS_F32, truncated like keras Embedding's
+ *    int32 cast).
+ */
+#ifndef CTRHOT_H_
+#define CTRHOT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTRHOT_VERSION 100
+
+typedef enum {
+  CTRHOT_OK = 0,
+  CTRHOT_EARG = -1,        /* bad argument (null pointer, negative size, ...) */
+  CTRHOT_ESHAPE = -2,      /* shape not supported by any kernel variant */
+  CTRHOT_ECUDA = -3,       /* CUDA error; text via ctrhot_last_cuda_error() */
+  CTRHOT_EID = -4          /* an embedding id was out of range */
+} ctrhot_status;
+
+enum { CTRHOT_IDS_I32 = 0, CTRHOT_IDS_F32 = 1 };
+enum { CTRHOT_ACT_NONE = 0, CTRHOT_ACT_RELU = 1, CTRHOT_ACT_PRELU = 2, CTRHOT_ACT_DICE = 3,
+       CTRHOT_ACT_SIGMOID = 4, CTRHOT_ACT_TANH = 5 };
+
+int ctrhot_version(void);
+const char* ctrhot_status_str(int status);
+/* thread-local text of the last CUDA error seen by this host thread */
+const char* ctrhot_last_cuda_error(void);
+/* synchronises `stream`, reads *err_flag, clears it; CTRHOT_EID if it was set */
+int ctrhot_check_flag(int* err_flag, void* stream);
+
+/* ---- R1  EmbedLayer.call, DL/layer/core.py:273-280 (+ keras Embedding) --------
+ * out[b, D + f*k + c] = arena[row_off[f] + ids[b,f], c]; out[b, 0:D] = dense[b,:]
+ * (D = 0 / dense = NULL gives the plain EmbedLayer output [B, F*k]; D = 13
+ * gives the x = concat([dense, embed]) of DL/model/deepFM.py:26, dcn.py:27). */
+int ctrhot_gather_f32(const float* arena, const int64_t* row_off, int F, int k,
+                      const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
+                      const float* dense, int64_t dense_ld, int D,
+                      float* out, int64_t out_ld, int* err_flag, void* stream);
+
+/* ---- R2  WideLayer.call, DL/layer/interaction.py:24-26 -----------------------
+ * one-hot form: out[b] = w0 + sum_j dense[b,j]*w[dense_col[j]] + sum_f w[col_off[f]+ids[b,f]]
+ * (dense_col int32[D], col_off int64[F+1]; the reference's wide input repeats
+ * the dense columns, DL/model/wideDeep.py:23-27 -> pass D=26 dense entries). */
+int ctrhot_wide_onehot_f32(const float* dense, int64_t dense_ld, int D, const int32_t* dense_col,
+                           const void* ids, int ids_kind, int64_t ids_ld, int F,
+                           const int64_t* col_off, int64_t B,
+                           const float* w0, const float* w, float* out, void* stream);
+/* dense form: out[b] = w0 + x[b,:] @ w */
+int ctrhot_wide_dense_f32(const float* x, int64_t x_ld, int64_t n, int64_t B,
+                          const float* w0, const float* w, float* out, void* stream);
+
+/* ---- R3  FMLayer.call, DL/layer/interaction.py:106-114 -----------------------
+ * dense form over x[B,n] (DeepFM's FM term, DL/model/deepFM.py:28; also the
+ * reference FM model's dense one-hot matrix -- zeros are skipped):
+ *   out[b] = w0 + x@w1 + 0.5*sum_k[(x@v)_k^2 - (x^2 @ v^2)_k]          v:[n,kfm]
+ * apply_sigmoid != 0 adds FM.call's sigmoid (DL/model/fm.py:22). */
+int ctrhot_fm_dense_f32(const float* x, int64_t x_ld, int64_t n, int64_t B,
+                        const float* w0, const float* w1, const float* v, int kfm,
+                        float* out, int apply_sigmoid, void* stream);
+/* one-hot form = north_star's (sum v)^2 - sum v^2 over gathered rows */
+int ctrhot_fm_onehot_f32(const float* dense, int64_t dense_ld, int D, const int32_t* dense_col,
+                         const void* ids, int ids_kind, int64_t ids_ld, int F,
+                         const int64_t* col_off, int64_t B,
+                         const float* w0, const float* w1, const float* v, int kfm,
+                         float* out, int apply_sigmoid, void* stream);
+
+/* ---- R5  FFMLayer.call, DL/layer/interaction.py:141-163 ----------------------
+ * w:[n_feat], v:[n_feat, field_num, k]; features = D dense columns then the F
+ * one-hot blocks (col_off[f] = D + sum_{g<f} V_g, col_off[F] = n_feat).  Ids
+ * outside [0,V_f) contribute nothing (tf.one_hot semantics). */
+int ctrhot_ffm_onehot_f32(const float* dense, int64_t dense_ld, int D,
+                          const void* ids, int ids_kind, int64_t ids_ld, int F,
+                          const int64_t* col_off, int64_t B,
+                          const float* w0, const float* w, const float* v, int field_num, int k,
+                          float* out, int apply_sigmoid, void* stream);
+
+/* ---- R6/R7  InnerProductLayer / OuterProductLayer, interaction.py:166-215 ----
+ * e:[B,F,k] (ld = elements per sample), out[b,p] over row-major pairs i<j.
+ * outer: out[b,p] = sum_{a,c} e[b,j,a] * W[a,p,c] * e[b,i,c],  W:[k,P,k]. */
+int ctrhot_pnn_inner_f32(const float* e, int64_t e_ld, int F, int k, int64_t B,
+                         float* out, int64_t out_ld, void* stream);
+int ctrhot_pnn_outer_f32(const float* e, int64_t e_ld, int F, int k, int64_t B, const float* W,
+                         float* out, int64_t out_ld, void* stream);
+
+/* ---- R8  CrossLayer.call, DL/layer/interaction.py:75-83 ----------------------
+ * all L layers in one launch; w,b:[L,d].  out may alias x.
+ * If final_w != NULL also writes dot[b] = sum_j out[b,j]*final_w[j] (the cross
+ * half of DCN's last Dense, DL/model/dcn.py:32-33); out may then be NULL. */
+int ctrhot_cross_f32(const float* x, int64_t x_ld, int d, int64_t B, int L,
+                     const float* w, const float* b, float* out, int64_t out_ld,
+                     const float* final_w, float* dot, void* stream);
+
+/* ---- R4/R10  DNNLayer / Dense(+PReLU/Dice) towers, interaction.py:30-46 ------
+ * One descriptor per Dense layer.  y = act(x @ weight + bias).
+ *  weight  [in_dim, out_dim] row-major = the Keras `kernel`
+ *  act_param PRELU: alpha[alpha_rows, out_dim]; row = (global row % alpha_rows)
+ *            (alpha_rows = T for DIN's attention Dense, interaction.py:366; 1 otherwise)
+ *            DICE : [3, out_dim] = alphas, moving_mean, moving_var (eps in dice_eps)
+ * packed  NULL, or the buffer filled by ctrhot_mlp_pack() for the tensor-core path. */
+typedef struct {
+  const float* weight;
+  const float* bias;
+  const float* act_param;
+  const void* packed;
+  int32_t in_dim, out_dim, act, alpha_rows;
+  float dice_eps;
+  int32_t reserved;
+} ctrhot_dense_desc;
+
+/* exact fp32 CUDA-core path (FFMA, fp32 accumulate) */
+int ctrhot_mlp_f32(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_desc* h_layers,
+                   int n_layers, float* out, int64_t out_ld, void* workspace,
+                   int64_t workspace_bytes, void* stream);
+/* tcgen05/TMEM TF32 path (fp32 in HBM, TF32 multiply, fp32 accumulate) */
+int64_t ctrhot_mlp_pack_bytes(int in_dim, int out_dim);
+int ctrhot_mlp_pack(const float* weight, int in_dim, int out_dim, void* packed, void* stream);
+int ctrhot_mlp_tf32(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_desc* h_layers,
+                    int n_layers, float* out, int64_t out_ld, void* workspace,
+                    int64_t workspace_bytes, void* stream);
+int64_t ctrhot_mlp_workspace_bytes(int64_t M, const ctrhot_dense_desc* h_layers, int n_layers);
+
+/* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
+int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,
+                    const float* var, float eps, float* out, void* stream);
+
+/* ---- R9  DIN Attention.call, DL/layer/interaction.py:369-406 -----------------
+ * query [B,K]; key = value [B,T,K] (key_ld_b = elements per sample); mask [B,T] float (0 = padding);
+ * a layer with weight == NULL is an element-wise activation only (the 'dice' branch);
+ * 'prelu' branch: layers = Dense(4K->h1,PReLU[T,h1]), Dense(h1->h2,PReLU[T,h2]), ...
+ * then Dense(h_last->1); masked softmax with fill -2^32+1; out[B,K] = p @ value. */
+int ctrhot_din_attention_f32(const float* query, int64_t q_ld, const float* key, int64_t key_ld_b,
+                             const float* mask, int64_t B, int T, int K,
+                             const ctrhot_dense_desc* h_layers, int n_layers,
+                             const float* out_w, const float* out_b,
+                             float* out, int64_t out_ld, void* stream);
+/* fused: history/candidate gather + attention; keys never reach HBM.
+ * hist_ids [B,T] and cand_ids [B] index `table` [V,K]; mask = (hist id != 0)
+ * (DL/model/din.py:76-81).  item_out [B,K] receives the candidate embedding. */
+int ctrhot_din_attention_gather_f32(const float* table, int64_t V, int K,
+                                    const void* hist_ids, int ids_kind, int64_t hist_ld,
+                                    const void* cand_ids, int64_t cand_ld, int64_t B, int T,
+                                    const ctrhot_dense_desc* h_layers, int n_layers,
+                                    const float* out_w, const float* out_b,
+                                    float* att_out, int64_t att_ld, float* item_out, int64_t item_ld,
+                                    int* err_flag, void* stream);
+
+/* ---- R12/R14 fused model front ends ------------------------------------------
+ * gather -> x=[dense, embed] -> FM (DeepFM, DL/model/deepFM.py:24-28) or L cross
+ * layers (DCN, DL/model/dcn.py:25-29) in ONE kernel; the gathered rows are
+ * consumed from registers, x is written once for the tower (or not at all when
+ * x == NULL).  x uses the INTERNAL column order [embeddings F*k | dense D | zero
+ * pad to x_ld] so all stores are 128-bit; weights are permuted to that order by
+ * the pack helpers below (n = D + F*k reference columns, n_pad = n rounded up
+ * to 32):
+ *   ctrhot_fm_pack_planes : planes[kfm+2][n_pad] = v[:,c] | w1 | s_j=sum_c v[j,c]^2
+ *   ctrhot_permute_cols   : dst[rows][n_pad] from src[rows][n] (cross w/b, final w)
+ * fm_out / cross_dot are [B]; cross_out (optional) is [B, cross_ld] internal order. */
+int64_t ctrhot_fm_planes_bytes(int n, int kfm);
+int ctrhot_fm_pack_planes(const float* w1, const float* v, int n, int kfm, int D,
+                          float* planes, void* stream);
+int ctrhot_permute_cols(const float* src, int rows, int n, int D, float* dst, void* stream);
+int ctrhot_deepfm_front_f32(const float* arena, const int64_t* row_off, int F, int k,
+                            const void* ids, int ids_kind, int64_t ids_ld,
+                            const float* dense, int64_t dense_ld, int D, int64_t B,
+                            const float* w0, const float* planes, int kfm,
+                            float* x, int64_t x_ld, float* fm_out, int* err_flag, void* stream);
+int ctrhot_dcn_front_f32(const float* arena, const int64_t* row_off, int F, int k,
+                         const void* ids, int ids_kind, int64_t ids_ld,
+                         const float* dense, int64_t dense_ld, int D, int64_t B,
+                         int L, const float* cw, const float* cb, const float* final_w,
+                         float* x, int64_t x_ld, float* cross_out, int64_t cross_ld,
+                         float* cross_dot, int* err_flag, void* stream);
+/* out[b] = sigmoid(scale * (a[b] + (b_ ? b_[b] : 0) + (bias ? *bias : 0))) */
+int ctrhot_combine_sigmoid_f32(const float* a, const float* b_, const float* bias, float scale,
+                               int64_t B, float* out, void* stream);
+
+/* ---- 8(e) config 5: row-sharded tables, owner = id mod G, local row = id div G -
+ * route: bucket this rank's [B,F] ids by owner; send_ids/send_slot are laid out
+ * owner-major using counts/offsets computed by the same call (device int32[G]). */
+int ctrhot_shard_route_ids(const int32_t* ids, int64_t B, int F, int G,
+                           int32_t* send_local_row, int32_t* send_field, int32_t* send_slot,
+                           int32_t* counts, void* workspace, int64_t workspace_bytes, void* stream);
+int64_t ctrhot_shard_route_workspace_bytes(int64_t B, int F, int G);
+/* owner side: rows[n, k] = arena[row_off[field[n]] + local_row[n]] */
+int ctrhot_shard_gather_pack(const float* arena, const int64_t* row_off, int F, int k,
+                             const int32_t* local_row, const int32_t* field, int64_t n,
+                             float* rows, int* err_flag, void* stream);
+/* requester side: x[slot/F, D + (slot%F)*k + c] = rows[n, c] */
+int ctrhot_shard_unpack(const float* rows, const int32_t* slot, int64_t n, int F, int k, int D,
+                        float* x, int64_t x_ld, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTRHOT_H_ */

@@ -1,0 +1,384 @@
+"""CPU oracle for the CTR forward hot path -- TEST INFRASTRUCTURE ONLY.
+
+This module is the checker, never the product: only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import it.  Nothing under
+``recommender_system_b200/`` imports anything from ``oracle/``.
+
+PARITY UNPINNED.  The reference (Hcyand/recommender_system) delegates all of
+its arithmetic to TensorFlow/Keras (third party, not vendored, version
+unpinned; import style implies TF 2.6-2.11) and ships no tests, fixtures or
+golden vectors for this path.  TensorFlow is not installed here and cannot be,
+so this file is a *restatement*: each function follows the cited reference
+lines op for op, with the Keras defaults the reference leans on written out
+explicitly.  ``oracle/dump_tf.py`` lets a TF-equipped user emit the same
+vectors from the real reference to close the gap off-box.
+
+All citations are relative to /root/reference/algorithm/deep_learning/ ("DL/").
+
+Every function is dtype-parametric: call with float64 arrays for the O64
+tolerance judge, float32 arrays for O32 (the reference's own precision and op
+order).  Keras defaults restated here:
+
+* ``Embedding``: ids cast to int32 (truncation), then a row gather.
+* ``Dense``: ``x @ kernel + bias`` on the last axis, ``kernel`` is [in, out].
+* ``PReLU``: ``max(x,0) - alpha*max(-x,0)``, alpha shaped like the activation
+  input minus the batch axis.
+* ``BatchNormalization`` (inference): ``gamma*(x-mean)/sqrt(var+eps)+beta``,
+  eps 1e-3 by default; inside Dice eps=1e-9 and no gamma/beta.
+* ``Dropout``: identity at inference.  ``softmax``: last axis.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+MASK_FILL = float(-2 ** 32 + 1)  # DL/layer/interaction.py:399
+
+
+# --------------------------------------------------------------------------- helpers
+def sigmoid(x):
+    x = np.asarray(x)
+    out = np.empty_like(x)
+    pos = x >= 0
+    out[pos] = 1.0 / (1.0 + np.exp(-x[pos]))
+    ex = np.exp(x[~pos])
+    out[~pos] = ex / (1.0 + ex)
+    return out
+
+
+def softmax_last(x):
+    m = np.max(x, axis=-1, keepdims=True)
+    e = np.exp(x - m)
+    return e / np.sum(e, axis=-1, keepdims=True)
+
+
+def ids_to_int(ids):
+    """keras Embedding casts its input to int32 (truncation toward zero)."""
+    return np.asarray(ids).astype(np.int64)
+
+
+def activation(name, x):
+    if name is None or name == "linear":
+        return x
+    if name == "relu":
+        return np.maximum(x, 0)
+    if name == "sigmoid":
+        return sigmoid(x)
+    if name == "tanh":
+        return np.tanh(x)
+    raise ValueError("unknown activation %r" % (name,))
+
+
+def prelu(x, alpha):
+    """keras.layers.PReLU.call: relu(x) - alpha*relu(-x)."""
+    return np.maximum(x, 0) - alpha * np.maximum(-x, 0)
+
+
+def batchnorm_infer(x, mean, var, gamma=None, beta=None, eps=1e-3):
+    y = (x - mean) / np.sqrt(var + eps)
+    if gamma is not None:
+        y = y * gamma
+    if beta is not None:
+        y = y + beta
+    return y
+
+
+def pair_index(field_num):
+    """Row-major (i<j) pair order, DL/layer/interaction.py:174-177, 203-206."""
+    row, col = [], []
+    for i in range(field_num - 1):
+        for j in range(i + 1, field_num):
+            row.append(i)
+            col.append(j)
+    return np.asarray(row), np.asarray(col)
+
+
+# --------------------------------------------------------------------------- R1
+def embed_layer(sparse_inputs, tables, flatten=True):
+    """EmbedLayer.call, DL/layer/core.py:273-280.
+
+    26 separate gathers -> stack [F,B,k] -> transpose [B,F,k] -> reshape
+    [B,F*k].  Out-of-range ids raise IndexError (CPU TF raises
+    InvalidArgumentError).
+    """
+    ids = ids_to_int(sparse_inputs)
+    embs = []
+    for f, table in enumerate(tables):
+        col = ids[:, f]
+        if col.size and (col.min() < 0 or col.max() >= table.shape[0]):
+            raise IndexError("id out of range in field %d" % f)
+        embs.append(table[col])
+    emb = np.transpose(np.stack(embs, axis=0), (1, 0, 2))
+    if flatten:
+        emb = emb.reshape(emb.shape[0], emb.shape[1] * emb.shape[2])
+    return emb
+
+
+# --------------------------------------------------------------------------- R2
+def wide_layer(x, w0, w):
+    """WideLayer.call, DL/layer/interaction.py:24-26."""
+    return w0 + x @ w
+
+
+# --------------------------------------------------------------------------- R3
+def fm_layer(x, w0, w1, v):
+    """FMLayer.call, DL/layer/interaction.py:106-114."""
+    linear_part = x @ w1 + w0
+    inter_part1 = np.power(x @ v, 2)
+    inter_part2 = np.power(x, 2) @ np.power(v, 2)
+    inter_part = 0.5 * np.sum(inter_part1 - inter_part2, axis=-1, keepdims=True)
+    return linear_part + inter_part
+
+
+# --------------------------------------------------------------------------- R4
+def dnn_layer(x, hidden, out, act="relu"):
+    """DNNLayer.call, DL/layer/interaction.py:40-46.
+
+    ``hidden`` is a list of (kernel[in,out], bias[out]); ``out`` one such pair.
+    Dropout (:44) is the identity at inference.
+    """
+    for kernel, bias in hidden:
+        x = activation(act, x @ kernel + bias)
+    kernel, bias = out
+    return x @ kernel + bias
+
+
+# --------------------------------------------------------------------------- R8
+def cross_layer(x, ws, bs):
+    """CrossLayer.call, DL/layer/interaction.py:75-83.  ws/bs: lists of [d,1]."""
+    x0 = x[:, :, None]
+    x1 = x0
+    for w, b in zip(ws, bs):
+        x1_w = np.matmul(np.transpose(x1, (0, 2, 1)), w)        # [B,1,1]
+        x1 = np.matmul(x0, x1_w) + b + x1
+    return x1[:, :, 0]
+
+
+# --------------------------------------------------------------------------- R5
+def onehot_expand(inputs, vocab_sizes, n_dense=13, dtype=None):
+    """FFMLayer.call's one-hot construction, DL/layer/interaction.py:142-150.
+
+    tf.one_hot yields an all-zero row for an out-of-range index.
+    """
+    inputs = np.asarray(inputs)
+    dtype = dtype or inputs.dtype
+    dense = inputs[:, :n_dense].astype(dtype)
+    ids = ids_to_int(inputs[:, n_dense:])
+    cols = [dense]
+    for f, vsz in enumerate(vocab_sizes):
+        oh = np.zeros((inputs.shape[0], vsz), dtype=dtype)
+        c = ids[:, f]
+        ok = (c >= 0) & (c < vsz)
+        oh[np.nonzero(ok)[0], c[ok]] = 1
+        cols.append(oh)
+    return np.concatenate(cols, axis=1)
+
+
+def ffm_layer(inputs, vocab_sizes, w0, w, v, n_dense=13):
+    """FFMLayer.call, DL/layer/interaction.py:141-163 (dense one-hot form).
+
+    w:[n_feat,1], v:[n_feat, field_num, k].  NOT textbook FFM.
+    """
+    x = onehot_expand(inputs, vocab_sizes, n_dense, dtype=v.dtype)
+    linear_part = w0 + x @ w
+    field_f = np.tensordot(x, v, axes=1)                         # [B, field_num, k]
+    field_num = v.shape[1]
+    inter_part = np.zeros((x.shape[0], 1), dtype=v.dtype)
+    for i in range(field_num):
+        for j in range(i + 1, field_num):
+            inter_part = inter_part + np.sum(field_f[:, i] * field_f[:, j], axis=1, keepdims=True)
+    return linear_part + inter_part
+
+
+# --------------------------------------------------------------------------- R6 / R7
+def inner_product_layer(e):
+    """InnerProductLayer.call, DL/layer/interaction.py:170-183.  e:[B,F,k]."""
+    row, col = pair_index(e.shape[1])
+    et = np.transpose(e, (1, 0, 2))
+    p = np.transpose(et[row], (1, 0, 2))
+    q = np.transpose(et[col], (1, 0, 2))
+    return np.sum(p * q, axis=-1)
+
+
+def outer_product_layer(e, w):
+    """OuterProductLayer.call, DL/layer/interaction.py:201-215.  w:[k,P,k]."""
+    row, col = pair_index(e.shape[1])
+    et = np.transpose(e, (1, 0, 2))
+    p = np.transpose(et[row], (1, 0, 2))                         # [B,P,k]
+    q = np.transpose(et[col], (1, 0, 2))
+    p = p[:, None, :, :]                                         # [B,1,P,k]
+    tmp = p * w                                                  # [B,k,P,k]
+    tmp = np.sum(tmp, axis=-1)                                   # [B,k,P]
+    tmp = np.transpose(tmp, (0, 2, 1)) * q                       # [B,P,k]
+    return np.sum(tmp, axis=-1)
+
+
+# --------------------------------------------------------------------------- R10
+def dice(x, alphas, mean, var, eps=1e-9):
+    """Dice.call, DL/layer/interaction.py:422-425 (inference BN, no gamma/beta)."""
+    xn = batchnorm_infer(x, mean, var, eps=eps)
+    x_p = sigmoid(xn)
+    return alphas * (1.0 - x_p) * x + x_p * x
+
+
+# --------------------------------------------------------------------------- R9
+def din_attention(query, key, value, mask, dense, out, act="prelu", dice_params=None):
+    """DIN Attention.call, DL/layer/interaction.py:369-406.
+
+    ``act='prelu'``: ``dense`` is a list of (kernel[in,h], bias[h], alpha[T,h]).
+    ``act='dice'`` : no Dense projection at all; ``dice_params`` is a
+    list of (alphas[4K], mean[4K], var[4K]), applied on the 4K-wide concat.
+    ``out`` = (kernel[h_last,1], bias[1]).
+    """
+    T = key.shape[1]
+    q = np.tile(query[:, None, :], (1, T, 1))
+    emb = np.concatenate([q, key, q - key, q * key], axis=-1)    # [B,T,4K]
+    if act == "prelu":
+        for kernel, bias, alpha in dense:
+            emb = prelu(emb @ kernel + bias, alpha)
+    elif act == "dice":
+        for alphas, mean, var in dice_params:
+            emb = dice(emb, alphas, mean, var)
+    else:
+        raise ValueError(act)
+    kernel, bias = out
+    score = (emb @ kernel + bias)[..., 0]                        # [B,T]
+    padding = np.ones_like(score) * score.dtype.type(MASK_FILL)
+    score = np.where(mask == 0, padding, score)
+    score = softmax_last(score)
+    return np.matmul(score[:, None, :], value)[:, 0, :]
+
+
+# --------------------------------------------------------------------------- R11-R16 models
+def fm_model(x, w0, w1, v):
+    """FM.call, DL/model/fm.py:19-23."""
+    return sigmoid(fm_layer(x, w0, w1, v))
+
+
+def ffm_model(inputs, vocab_sizes, w0, w, v):
+    """FFM.call, DL/model/ffm.py:20-23."""
+    return sigmoid(ffm_layer(inputs, vocab_sizes, w0, w, v))
+
+
+def deepfm_model(inputs, tables, fm, dnn_hidden, dnn_out, act="relu", n_dense=13):
+    """DeepFM.call, DL/model/deepFM.py:23-31.  fm=(w0,w1,v) over d=n_dense+F*k."""
+    dense_inputs, sparse_inputs = inputs[:, :n_dense], inputs[:, n_dense:]
+    sparse_embed = embed_layer(sparse_inputs, tables)
+    x = np.concatenate([dense_inputs.astype(sparse_embed.dtype), sparse_embed], axis=-1)
+    fm_output = fm_layer(x, *fm)
+    dnn_output = dnn_layer(x, dnn_hidden, dnn_out, act)
+    return sigmoid(0.5 * (fm_output + dnn_output))
+
+
+def widedeep_model(inputs, tables, wide, dnn_hidden, dnn_out, act="relu", n_dense=13):
+    """WideDeep.call, DL/model/wideDeep.py:22-34.
+
+    inputs = [dense(13), ids(26), onehot(...)]; the deep side sees embeddings
+    only.  wide=(w0,w) with w over 13+len(onehot).
+    """
+    F = len(tables)
+    dense_inputs = inputs[:, :n_dense]
+    sparse_inputs = inputs[:, n_dense:n_dense + F]
+    onehot_inputs = inputs[:, n_dense + F:]
+    wide_input = np.concatenate([dense_inputs, onehot_inputs], axis=1)
+    wide_output = wide_layer(wide_input.astype(wide[1].dtype), *wide)
+    sparse_embed = embed_layer(sparse_inputs, tables)
+    deep_output = dnn_layer(sparse_embed, dnn_hidden, dnn_out, act)
+    return sigmoid(0.5 * (wide_output + deep_output))
+
+
+def dcn_model(inputs, tables, cross_ws, cross_bs, dnn_hidden, dnn_out, final, act="relu", n_dense=13):
+    """DCN.call, DL/model/dcn.py:24-34.  final=(kernel[d+od,1], bias[1])."""
+    dense_inputs, sparse_inputs = inputs[:, :n_dense], inputs[:, n_dense:]
+    sparse_embed = embed_layer(sparse_inputs, tables)
+    x = np.concatenate([dense_inputs.astype(sparse_embed.dtype), sparse_embed], axis=1)
+    cross_output = cross_layer(x, cross_ws, cross_bs)
+    dnn_output = dnn_layer(x, dnn_hidden, dnn_out, act)
+    x = np.concatenate([cross_output, dnn_output], axis=1)
+    kernel, bias = final
+    return sigmoid(x @ kernel + bias)
+
+
+def pnn_model(inputs, tables, mode, dnn_hidden, dnn_out, outer_w=None, act="relu", n_dense=13):
+    """PNN.call, DL/model/pnn.py:28-53 with the [B,F,k] view the product layers
+    are specified on.  No sigmoid (:52-53)."""
+    sparse_inputs = inputs[:, n_dense:]
+    z = embed_layer(sparse_inputs, tables, flatten=False)
+    embed = z.reshape(z.shape[0], z.shape[1] * z.shape[2])
+    if mode == "inner":
+        feats = [embed, inner_product_layer(z)]
+    elif mode == "outer":
+        feats = [embed, outer_product_layer(z, outer_w)]
+    elif mode == "both":
+        feats = [embed, inner_product_layer(z), outer_product_layer(z, outer_w)]
+    else:
+        raise ValueError("Please choice mode's value in 'inner', 'outer', 'both'.")
+    return dnn_layer(np.concatenate(feats, axis=1), dnn_hidden, dnn_out, act)
+
+
+def din_model(dense_inputs, other_ids, hist_ids, cand_ids,
+              other_tables, seq_tables, att_dense, att_out,
+              bn, tower, out, att_act="prelu", att_dice=None, dnn_act="prelu"):
+    """DIN.call, DL/model/din.py:56-95.
+
+    dense_inputs [B,nd]; other_ids [B,no]; hist_ids [B,T,nb]; cand_ids [B,nb];
+    seq_tables are shared by history and candidate (:76-79).
+    bn=(gamma,beta,mean,var) eps 1e-3 (:50,:89).
+    tower: list of (kernel,bias,alpha[u]) for 'prelu', or
+    (kernel,bias,(alphas,mean,var)) for Dice (:51).
+    """
+    dt = seq_tables[0].dtype
+    other_ids = ids_to_int(other_ids)
+    hist_ids_i = ids_to_int(hist_ids)
+    cand_ids = ids_to_int(cand_ids)
+    parts = [other_tables[i][other_ids[:, i]] for i in range(len(other_tables))]
+    parts.append(np.asarray(dense_inputs, dtype=dt))
+    other_feat = np.concatenate(parts, axis=-1)
+    seq_embed = np.concatenate([seq_tables[i][hist_ids_i[:, :, i]] for i in range(len(seq_tables))], axis=-1)
+    item_embed = np.concatenate([seq_tables[i][cand_ids[:, i]] for i in range(len(seq_tables))], axis=-1)
+    mask = (np.asarray(hist_ids)[:, :, 0] != 0).astype(dt)
+    att_emb = din_attention(item_embed, seq_embed, seq_embed, mask, att_dense, att_out, att_act, att_dice)
+    emb = np.concatenate([att_emb, item_embed, other_feat], axis=-1)
+    gamma, beta, mean, var = bn
+    emb = batchnorm_infer(emb, mean, var, gamma, beta, eps=1e-3)
+    for kernel, bias, a in tower:
+        h = emb @ kernel + bias
+        emb = prelu(h, a) if dnn_act == "prelu" else dice(h, *a)
+    kernel, bias = out
+    return sigmoid(emb @ kernel + bias)
+
+
+# --------------------------------------------------------------------------- sparse restatements
+# The B200 kernels never materialise the one-hot matrix.  These are the
+# gather-form equivalents, kept here so the tests can prove dense == sparse
+# on the oracle itself before any GPU is involved.
+def fm_onehot_sparse(dense_x, dense_cols, ids, offsets, w0, w1, v):
+    """FM over [dense, one-hot] as a gather.  Column of (field f, id i) is
+    offsets[f]+i; dense feature j sits at column dense_cols[j]."""
+    ids = ids_to_int(ids)
+    B = ids.shape[0]
+    cols = ids + np.asarray(offsets)[None, :]
+    lin = w0 + dense_x @ w1[dense_cols] + np.sum(w1[cols, 0], axis=1, keepdims=True)
+    s = dense_x @ v[dense_cols] + np.sum(v[cols], axis=1)                       # [B,k]
+    s2 = (dense_x ** 2) @ (v[dense_cols] ** 2) + np.sum(v[cols] ** 2, axis=1)
+    assert s.shape[0] == B
+    return lin + 0.5 * np.sum(s * s - s2, axis=-1, keepdims=True)
+
+
+def ffm_sparse(inputs, vocab_sizes, w0, w, v, n_dense=13):
+    """FFMLayer as gathers + the pair-sum identity
+    sum_{i<j}<a_i,a_j> = 0.5*(|sum a|^2 - sum |a|^2)."""
+    dense = np.asarray(inputs[:, :n_dense], dtype=v.dtype)
+    ids = ids_to_int(inputs[:, n_dense:])
+    offs = n_dense + np.concatenate([[0], np.cumsum(vocab_sizes)[:-1]])
+    lin = w0 + dense @ w[:n_dense]
+    field_f = np.tensordot(dense, v[:n_dense], axes=1)
+    for f, vsz in enumerate(vocab_sizes):
+        c = ids[:, f]
+        ok = ((c >= 0) & (c < vsz)).astype(v.dtype)
+        cc = np.clip(c, 0, vsz - 1) + offs[f]
+        lin = lin + ok[:, None] * w[cc]
+        field_f = field_f + ok[:, None, None] * v[cc]
+    tot = np.sum(field_f, axis=1)
+    inter = 0.5 * (np.sum(tot * tot, axis=1, keepdims=True) - np.sum(field_f * field_f, axis=(1, 2))[:, None])
+    return lin + inter

@@ -1,0 +1,175 @@
+// libctrhot: version / status / error plumbing and the config-5 shard helpers (K8).
+#include <cstdio>
+#include <cstring>
+#include "common.cuh"
+
+namespace ctrhot {
+
+static thread_local char g_err[512] = "";
+
+void set_cuda_error(cudaError_t e, const char* where) {
+  snprintf(g_err, sizeof(g_err), "%s: %s (%s)", where, cudaGetErrorString(e), cudaGetErrorName(e));
+}
+
+// ---------------------------------------------------------------- K8 shard route / pack / unpack
+// Row-sharded tables: owner(id) = id mod G, local row = id div G  (SURVEY 8(e)).
+// route: counting sort of the B*F (sample, field) slots by owner, stable inside an owner.
+__global__ void route_count_kernel(const int32_t* __restrict__ ids, int64_t n, int G,
+                                   int32_t* __restrict__ counts) {
+  extern __shared__ int32_t sc[];
+  for (int g = threadIdx.x; g < G; g += blockDim.x) sc[g] = 0;
+  __syncthreads();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t id = ids[i];
+    const int o = (int)(((id % G) + G) % G);
+    atomicAdd(&sc[o], 1);
+  }
+  __syncthreads();
+  for (int g = threadIdx.x; g < G; g += blockDim.x) if (sc[g]) atomicAdd(&counts[g], sc[g]);
+}
+
+__global__ void route_scan_kernel(const int32_t* __restrict__ counts, int G, int32_t* __restrict__ cursor) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    int32_t acc = 0;
+    for (int g = 0; g < G; ++g) { cursor[g] = acc; acc += counts[g]; }
+  }
+}
+
+__global__ void route_scatter_kernel(const int32_t* __restrict__ ids, int64_t n, int F, int G,
+                                     int32_t* __restrict__ cursor, int32_t* __restrict__ local_row,
+                                     int32_t* __restrict__ field, int32_t* __restrict__ slot) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t id = ids[i];
+    const int o = (int)(((id % G) + G) % G);
+    const int32_t pos = atomicAdd(&cursor[o], 1);
+    local_row[pos] = (id >= 0) ? id / G : -1;
+    field[pos] = (int32_t)(i % F);
+    slot[pos] = (int32_t)i;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+shard_gather_pack_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                         const int32_t* __restrict__ local_row, const int32_t* __restrict__ field, int64_t n,
+                         float* __restrict__ rows, int* __restrict__ err_flag) {
+  const int k4 = k >> 2;
+  const int64_t total = n * k4;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = t / k4;
+    const int c = (int)(t - r * k4);
+    const int f = field[r];
+    const int64_t lr = local_row[r];
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (f >= 0 && f < F && lr >= 0 && lr < row_off[f + 1] - row_off[f]) v = ldg_nc_f4(arena + (row_off[f] + lr) * k + c * 4);
+    else if (err_flag) *err_flag = 1;
+    stg_na_f4(rows + r * k + c * 4, v);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+shard_unpack_kernel(const float* __restrict__ rows, const int32_t* __restrict__ slot, int64_t n, int F, int k,
+                    int D, float* __restrict__ x, int64_t x_ld) {
+  const int k4 = k >> 2;
+  const int64_t total = n * k4;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = t / k4;
+    const int c = (int)(t - r * k4);
+    const int32_t s = slot[r];
+    const int64_t b = s / F;
+    const int f = s - (int)(b * F);
+    const float4 v = ldg_nc_f4(rows + r * k + c * 4);
+    float* dst = x + b * x_ld + D + (int64_t)f * k + c * 4;
+    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) *reinterpret_cast<float4*>(dst) = v;
+    else { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w; }
+  }
+}
+
+}  // namespace ctrhot
+
+using namespace ctrhot;
+
+extern "C" int ctrhot_version(void) { return CTRHOT_VERSION; }
+
+extern "C" const char* ctrhot_status_str(int status) {
+  switch (status) {
+    case CTRHOT_OK: return "ok";
+    case CTRHOT_EARG: return "bad argument";
+    case CTRHOT_ESHAPE: return "unsupported shape";
+    case CTRHOT_ECUDA: return "CUDA error";
+    case CTRHOT_EID: return "embedding id out of range";
+    default: return "unknown status";
+  }
+}
+
+extern "C" const char* ctrhot_last_cuda_error(void) { return g_err; }
+
+extern "C" int ctrhot_check_flag(int* err_flag, void* stream) {
+  if (!err_flag) return CTRHOT_EARG;
+  int h = 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CTRHOT_CUDA_OK(cudaMemcpyAsync(&h, err_flag, sizeof(int), cudaMemcpyDeviceToHost, st), "check_flag copy");
+  CTRHOT_CUDA_OK(cudaStreamSynchronize(st), "check_flag sync");
+  if (h != 0) {
+    CTRHOT_CUDA_OK(cudaMemsetAsync(err_flag, 0, sizeof(int), st), "check_flag clear");
+    return CTRHOT_EID;
+  }
+  return CTRHOT_OK;
+}
+
+extern "C" int64_t ctrhot_shard_route_workspace_bytes(int64_t B, int F, int G) {
+  if (B < 0 || F <= 0 || G <= 0) return CTRHOT_EARG;
+  return (int64_t)G * sizeof(int32_t) + 256;
+}
+
+extern "C" int ctrhot_shard_route_ids(const int32_t* ids, int64_t B, int F, int G,
+                                      int32_t* send_local_row, int32_t* send_field, int32_t* send_slot,
+                                      int32_t* counts, void* workspace, int64_t workspace_bytes, void* stream) {
+  if (!ids || !send_local_row || !send_field || !send_slot || !counts || !workspace) return CTRHOT_EARG;
+  if (B < 0 || F <= 0 || G <= 0 || G > 1024 || B * F > 2147483647LL) return CTRHOT_EARG;
+  if (workspace_bytes < ctrhot_shard_route_workspace_bytes(B, F, G)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int64_t n = B * F;
+  int32_t* cursor = static_cast<int32_t*>(workspace);
+  CTRHOT_CUDA_OK(cudaMemsetAsync(counts, 0, G * sizeof(int32_t), st), "route memset");
+  if (n > 0) {
+    int64_t g = (n + 255) / 256;
+    if (g > kNumSMs * 8) g = kNumSMs * 8;
+    route_count_kernel<<<(int)g, 256, G * sizeof(int32_t), st>>>(ids, n, G, counts);
+    CTRHOT_LAUNCH_OK("route_count");
+  }
+  route_scan_kernel<<<1, 32, 0, st>>>(counts, G, cursor);
+  CTRHOT_LAUNCH_OK("route_scan");
+  if (n > 0) {
+    int64_t g = (n + 255) / 256;
+    if (g > kNumSMs * 8) g = kNumSMs * 8;
+    route_scatter_kernel<<<(int)g, 256, 0, st>>>(ids, n, F, G, cursor, send_local_row, send_field, send_slot);
+    CTRHOT_LAUNCH_OK("route_scatter");
+  }
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_shard_gather_pack(const float* arena, const int64_t* row_off, int F, int k,
+                                        const int32_t* local_row, const int32_t* field, int64_t n,
+                                        float* rows, int* err_flag, void* stream) {
+  if (!arena || !row_off || !local_row || !field || !rows || F <= 0 || k <= 0 || n < 0) return CTRHOT_EARG;
+  if (k % 4 != 0 || !aligned16(arena) || !aligned16(rows)) return CTRHOT_ESHAPE;
+  if (n == 0) return CTRHOT_OK;
+  int64_t g = (n * (k / 4) + 255) / 256;
+  if (g > kNumSMs * 16) g = kNumSMs * 16;
+  shard_gather_pack_kernel<<<(int)g, 256, 0, static_cast<cudaStream_t>(stream)>>>(arena, row_off, F, k, local_row,
+                                                                               field, n, rows, err_flag);
+  CTRHOT_LAUNCH_OK("ctrhot_shard_gather_pack");
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_shard_unpack(const float* rows, const int32_t* slot, int64_t n, int F, int k, int D,
+                                   float* x, int64_t x_ld, void* stream) {
+  if (!rows || !slot || !x || F <= 0 || k <= 0 || n < 0 || D < 0 || x_ld < (int64_t)D + (int64_t)F * k) return CTRHOT_EARG;
+  if (k % 4 != 0 || !aligned16(rows)) return CTRHOT_ESHAPE;
+  if (n == 0) return CTRHOT_OK;
+  int64_t g = (n * (k / 4) + 255) / 256;
+  if (g > kNumSMs * 16) g = kNumSMs * 16;
+  shard_unpack_kernel<<<(int)g, 256, 0, static_cast<cudaStream_t>(stream)>>>(rows, slot, n, F, k, D, x, x_ld);
+  CTRHOT_LAUNCH_OK("ctrhot_shard_unpack");
+  return CTRHOT_OK;
+}

@@ -1,0 +1,67 @@
+// Shared device/host helpers for libctrhot (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "ctrhot.h"
+
+namespace ctrhot {
+
+constexpr int kWarp = 32;
+constexpr int kNumSMs = 148;   // B200
+
+// host: record + translate CUDA errors (thread-local text, no global mutable state shared across threads)
+void set_cuda_error(cudaError_t e, const char* where);
+#define CTRHOT_CUDA_OK(expr, where)                         \
+  do {                                                      \
+    cudaError_t _e = (expr);                                \
+    if (_e != cudaSuccess) {                                \
+      ::ctrhot::set_cuda_error(_e, where);                  \
+      return CTRHOT_ECUDA;                                  \
+    }                                                       \
+  } while (0)
+#define CTRHOT_LAUNCH_OK(where) CTRHOT_CUDA_OK(cudaGetLastError(), where)
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---------------------------------------------------------------- device
+__device__ __forceinline__ float4 ldg_nc_f4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float ldg_nc_f1(const float* p) {
+  float r;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg_na_f4(float* p, const float4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
+
+// ids arrive as int32 or as the reference's float columns (keras Embedding casts to int32)
+template <int KIND> struct IdLoad;
+template <> struct IdLoad<CTRHOT_IDS_I32> {
+  static __device__ __forceinline__ int64_t at(const void* p, int64_t i) {
+    return static_cast<int64_t>(__ldg(static_cast<const int32_t*>(p) + i));
+  }
+};
+template <> struct IdLoad<CTRHOT_IDS_F32> {
+  static __device__ __forceinline__ int64_t at(const void* p, int64_t i) {
+    return static_cast<int64_t>(__float2int_rz(__ldg(static_cast<const float*>(p) + i)));
+  }
+};
+
+}  // namespace ctrhot
