@@ -1,0 +1,286 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE metric: DeepFM forward samples/s at B=64K (config[1]: synthetic Criteo shape,
+13 dense + 26 sparse, emb dim 16, B=65536 per GPU), plus the gather/FM kernel's GB/s vs HBM peak.
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (CUDA, sm_100a)
+    python bench.py --impl reference ...                     # CPU arm: torch-CPU port of the reference ops
+
+One JSON line on stdout (rank 0).  N>1 is launched by torchrun, one rank per GPU; configs 2-4 shard by
+batch only (replicas, no data-path collective) -> "scaling": "weak".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ALGO_BYTES = {"deepfm": 26 * 4 + 13 * 4 + 26 * 64 + 4}        # SURVEY 8(d) cfg 2a: ids + dense + rows + output = 1824 B
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "tf": d["bf16_tflops"], "tf_sustained": d.get("bf16_tflops_sustained"),
+                "src": "measured"}
+    return {"hbm_gbs": 6650.0, "tf": 1590.0, "tf_sustained": 1400.0, "src": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            # NVML clocks-event-reason bits
+            names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+            while not self.stop_flag:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+                time.sleep(0.02)
+        except Exception as e:       # NVML missing: report that instead of inventing numbers
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def build_deepfm(device, vocab_name, k, precision):
+    from recommender_system_b200.model.criteo import DeepFM
+    from recommender_system_b200.utils import synth
+    from recommender_system_b200.layer import set_seed
+    set_seed(1)
+    vocab = synth.KAGGLE_VOCAB if vocab_name == "kaggle" else synth.SAMPLE_VOCAB
+    fc = synth.criteo_feature_columns(vocab, k)
+    m = DeepFM(fc, 10, 1e-4, 1e-4, [256, 128, 64], 1, "relu", embed_dim=k, precision=precision, check_ids=False,
+               device=device)
+    m.build(None)
+    return m, vocab
+
+
+def cpu_weights(m):
+    import torch
+    w = {n: t.detach().cpu() for n, t in m.named_weights().items() if "embeddings" not in n}
+    tables = [t.detach().cpu() for t in m.embed_layer.emb_layers]
+    fm = (w["FMLayer_1/w0"], w["FMLayer_1/w1"], w["FMLayer_1/v"])
+    hidden = [(w["DNNLayer_2/dense_%d/kernel" % i], w["DNNLayer_2/dense_%d/bias" % i]) for i in range(3)]
+    out = (w["DNNLayer_2/output/kernel"], w["DNNLayer_2/output/bias"])
+    return tables, fm, hidden, out
+
+
+def time_cpu(fn, inputs_list, budget_s=20.0, min_reps=2):
+    """median-free throughput: total samples / total time over >= min_reps passes within the budget."""
+    fn(inputs_list[0])                                    # warm-up
+    t0 = time.perf_counter()
+    n = reps = 0
+    while reps < min_reps or (time.perf_counter() - t0) < budget_s / 2:
+        x = inputs_list[reps % len(inputs_list)]
+        fn(x)
+        n += x.shape[0]
+        reps += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return n / dt, reps, dt
+
+
+def run_reference(args, rank, world):
+    """CPU arm: the torch-CPU port of the reference's op structure (oracle/cpu_ref_torch.py) on all host
+    threads, same config/metric; each step is a bounded sample of the B=65536 workload."""
+    if rank != 0:
+        return
+    import torch
+    from oracle import cpu_ref_torch as R
+    from recommender_system_b200.utils import synth
+    torch.set_num_threads(os.cpu_count() or 1)
+    k = args.embed_dim
+    vocab = synth.KAGGLE_VOCAB if args.vocab == "kaggle" else synth.SAMPLE_VOCAB
+    g = torch.Generator().manual_seed(1)
+    # host RAM bound: tables capped at 1M rows per field on the CPU arm (ids folded with %), stated in `sample`
+    cap = 1_000_000
+    vcpu = [min(v, cap) for v in vocab]
+    tables = [(torch.rand((v, k), generator=g) - 0.5) * 0.1 for v in vcpu]
+    d = 13 + 26 * k
+    fm = (torch.zeros(1), torch.randn((d, 1), generator=g) * 0.05, torch.randn((d, 10), generator=g) * 0.05)
+    dims = [d, 256, 128, 64]
+    hidden = [((torch.rand((dims[i], dims[i + 1]), generator=g) * 2 - 1) * (6.0 / (dims[i] + dims[i + 1])) ** 0.5,
+               torch.zeros(dims[i + 1])) for i in range(3)]
+    out = ((torch.rand((64, 1), generator=g) * 2 - 1) * (6.0 / 65) ** 0.5, torch.zeros(1))
+    Bs = args.cpu_batch
+    dense, ids = synth.criteo_batch(Bs, vocab, seed=1234)
+    ids = ids % np.array(vcpu, dtype=np.int64)[None, :]
+    x = torch.from_numpy(synth.criteo_matrix(dense, ids).astype(np.float32))
+    fn = lambda t: R.deepfm(t, tables, fm, hidden, out)
+    for _ in range(max(args.warmup, 1)):
+        fn(x)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        fn(x)
+    dt = time.perf_counter() - t0
+    val = Bs * args.steps / dt
+    sample = "B=%d rows per step of the B=65536 workload; tables capped at %d rows/field on the host" % (Bs, cap)
+    line = {"impl": "reference", "metric": "DeepFM forward samples/s", "value": val, "unit": "samples/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "deepfm_criteo_k%d_B65536" % k, "vocab": args.vocab, "ids": "uniform"},
+            "cpu_baseline": {"value": val, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": sample},
+            "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ctrhot", choices=["ctrhot", "reference"])
+    ap.add_argument("--batch", type=int, default=65536)
+    ap.add_argument("--embed-dim", type=int, default=16)
+    ap.add_argument("--vocab", default="kaggle", choices=["kaggle", "sample"])
+    ap.add_argument("--precision", default="tf32", choices=["tf32", "fp32"])
+    ap.add_argument("--cpu-batch", type=int, default=16384)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ctrhot" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from recommender_system_b200 import _lib
+    from recommender_system_b200.utils import synth
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: a CUDA device is required (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, k, K, W = args.batch, args.embed_dim, args.steps, args.warmup
+    model, vocab = build_deepfm(dev, args.vocab, k, args.precision)
+
+    # NB distinct input batches rotate through the timed loop; the tables (2.16 GB at kaggle/k=16) are >> L2
+    NB = 4
+    host = [synth.criteo_batch(B, vocab, seed=1234 + 97 * rank + i) for i in range(NB)]
+    dev_in = [(torch.from_numpy(d).to(dev), torch.from_numpy(i).to(dev)) for d, i in host]
+    pinned = [(torch.from_numpy(d).pin_memory(), torch.from_numpy(i).pin_memory()) for d, i in host]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing (value) with per-kernel events for the roofline
+    for i in range(W):
+        model(dev_in[i % NB])
+    model.events = []                                   # DeepFM.call records (front_start, front_end, tower_end) when set
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = _lib.LAUNCHES[0]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        out = model(dev_in[i % NB])
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = _lib.LAUNCHES[0] - l0
+    clocks = sampler.result()
+    evs = model.events
+    model.events = None
+    front_ms = float(np.mean([a.elapsed_time(b) for a, b, c in evs]))
+    tower_ms = float(np.mean([b.elapsed_time(c) for a, b, c in evs]))
+    model.check_ids()
+
+    # ---- end to end through the public API with HOST (pinned) buffers: H2D + forward + D2H every step
+    for i in range(2):
+        model(pinned[i % NB]).cpu()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        res = model(pinned[i % NB]).cpu()
+    torch.cuda.synchronize()
+    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    h2d = B * 13 * 4 + B * 26 * 4
+    d2h = B * 4
+
+    if rank == 0:
+        pk = peaks()
+        total = B * world * K
+        algo = ALGO_BYTES["deepfm"] if k == 16 else 26 * 4 + 13 * 4 + 26 * 4 * k + 4
+        d = 13 + 26 * k
+        flops = 2 * (d * 256 + 256 * 128 + 128 * 64 + 64)
+        front = {"kernel": "deepfm_front_kernel (gather+FM fused, writes x)", "bound": "hbm",
+                 "achieved": algo * B / (front_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s", "traffic": None,
+                 "ms": front_ms, "peak_src": pk["src"]}
+        front["frac"] = front["achieved"] / front["peak"]
+        tower = {"kernel": "dense_tc_kernel x3 (tcgen05 TF32 tower)", "bound": "tensor",
+                 "achieved": flops * B / (tower_ms * 1e-3) / 1e12, "peak": pk["tf"], "unit": "TFLOP/s", "traffic": None,
+                 "ms": tower_ms, "peak_src": pk["src"] + " bf16 dense (TF32 nominal peak is half)"}
+        tower["frac"] = tower["achieved"] / tower["peak"]
+        dom, other = (front, tower) if front_ms >= tower_ms else (tower, front)
+        line = {"metric": "DeepFM forward samples/s", "value": total / (ms * 1e-3), "unit": "samples/s",
+                "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32/tf32" if args.precision == "tf32" else "f32",
+                "data": "synthetic",
+                "config": {"workload": "deepfm_criteo_k%d_B%d" % (k, B), "batch_per_gpu": B, "vocab": args.vocab,
+                           "ids": "uniform", "tables_gb": sum(vocab) * k * 4 / 1e9, "parallelism": "dp%d" % world,
+                           "l2": "inputs rotate over %d batches; tables >> 126 MB L2" % NB},
+                "e2e": {"value": total / t_e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": d2h},
+                "gpu_launches": launches, "clocks": clocks, "roofline": dom, "roofline_other": other}
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import cpu_ref_torch as R
+            torch.set_num_threads(os.cpu_count() or 1)
+            tables, fm, hidden, outw = cpu_weights(model)
+            Bs = args.cpu_batch
+            xs = [torch.from_numpy(synth.criteo_matrix(d_[:Bs], i_[:Bs]).astype(np.float32)) for d_, i_ in host[:2]]
+            val, reps, dt = time_cpu(lambda t: R.deepfm(t, tables, fm, hidden, outw), xs)
+            ref = R.deepfm(xs[0], tables, fm, hidden, outw).numpy()
+            got = model(dev_in[0]).cpu().numpy()[:Bs]
+            line["cpu_baseline"] = {"value": val, "unit": "samples/s", "cores": torch.get_num_threads(),
+                                    "kind": "port",
+                                    "sample": "%d passes of B=%d rows of the same batches, same weights, %.1f s" % (reps, Bs, dt),
+                                    "max_abs_diff_vs_gpu": float(np.max(np.abs(ref - got)))}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -196,9 +196,11 @@ int ctrhot_dcn_front_f32(const float* arena, const int64_t* row_off, int F, int 
                          int L, const float* cw, const float* cb, const float* final_w,
                          float* x, int64_t x_ld, float* cross_out, int64_t cross_ld,
                          float* cross_dot, int* err_flag, void* stream);
-/* out[b] = sigmoid(scale * (a[b] + (b_ ? b_[b] : 0) + (bias ? *bias : 0))) */
-int ctrhot_combine_sigmoid_f32(const float* a, const float* b_, const float* bias, float scale,
-                               int64_t B, float* out, void* stream);
+/* out[b] = sigmoid(scale * (a[b] + (b_ ? b_[b] * (b_scale ? *b_scale : 1) : 0) + (bias ? *bias : 0)))
+ * -- DeepFM/WideDeep: scale 0.5 (deepFM.py:30, wideDeep.py:33); DCN: a = cross dot, b_ = tower
+ * output, b_scale = last weight of the final Dense, bias = its bias (dcn.py:32-33). */
+int ctrhot_combine_sigmoid_f32(const float* a, const float* b_, const float* b_scale, const float* bias,
+                               float scale, int64_t B, float* out, void* stream);
 
 /* ---- 8(e) config 5: row-sharded tables, owner = id mod G, local row = id div G -
  * route: bucket this rank's [B,F] ids by owner; send_ids/send_slot are laid out

@@ -105,9 +105,13 @@ def check(rc, what=""):
     raise ValueError("%s: %s" % (what, msg))
 
 
+LAUNCHES = [0]      # C-ABI compute calls issued by this process (each launches >= 1 kernel)
+
+
 def call(name, *args):
     lib = load()
     rc = getattr(lib, name)(*args)
+    LAUNCHES[0] += 1
     check(rc, name)
 
 

@@ -127,7 +127,8 @@ __device__ __forceinline__ void store_x(float* __restrict__ x, int64_t x_ld, int
       if (q < total) stg_na_f4(row + q * 4, xv[s][i]);
     }
     // dense tail + zero padding (x_ld - emb - D < 32 + D is required by the host wrapper)
-    for (int j = emb + lane; j < x_ld; j += 32) row[j] = (j - emb < D) ? __shfl_sync(0xffffffffu, xd[s], (j - emb) & 31) : 0.f;
+    // lane l < D holds dense[l] (xd is 0 for l >= D); everything past emb + 32 is padding
+    for (int j = emb + lane; j < x_ld; j += 32) row[j] = (j - emb == lane) ? xd[s] : 0.f;
   }
 }
 
@@ -360,12 +361,12 @@ __global__ void permute_cols_kernel(const float* __restrict__ src, int rows, int
 }
 
 __global__ void combine_sigmoid_kernel(const float* __restrict__ a, const float* __restrict__ b,
-                                       const float* __restrict__ bias, float scale, int64_t B,
-                                       float* __restrict__ out) {
+                                       const float* __restrict__ b_scale, const float* __restrict__ bias,
+                                       float scale, int64_t B, float* __restrict__ out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B) return;
   float t = a[i];
-  if (b) t += b[i];
+  if (b) t = fmaf(b[i], b_scale ? __ldg(b_scale) : 1.0f, t);
   if (bias) t += __ldg(bias);
   out[i] = 1.0f / (1.0f + expf(-scale * t));
 }
@@ -522,12 +523,13 @@ extern "C" int ctrhot_dcn_front_f32(const float* arena, const int64_t* row_off, 
   return CTRHOT_OK;
 }
 
-extern "C" int ctrhot_combine_sigmoid_f32(const float* a, const float* b_, const float* bias,
-                                          float scale, int64_t B, float* out, void* stream) {
+extern "C" int ctrhot_combine_sigmoid_f32(const float* a, const float* b_, const float* b_scale,
+                                          const float* bias, float scale, int64_t B, float* out,
+                                          void* stream) {
   if (!a || !out || B < 0) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
   combine_sigmoid_kernel<<<(unsigned)((B + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      a, b_, bias, scale, B, out);
+      a, b_, b_scale, bias, scale, B, out);
   CTRHOT_LAUNCH_OK("ctrhot_combine_sigmoid_f32");
   return CTRHOT_OK;
 }

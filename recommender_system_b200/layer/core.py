@@ -1,0 +1,169 @@
+"""Drop-in for the reference's ``layer/core.py`` hot-path class: ``EmbedLayer``
+(DL/layer/core.py:267-280), plus ``DenseStack``, the host-side driver of the Dense-tower kernels
+that DNNLayer / DIN / Attention share.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from .. import _lib
+from .base import (Layer, as_device_f32, ids_arg, init_glorot_uniform, init_uniform, init_zeros, ptr,
+                   require_cuda, stream_ptr)
+
+
+class EmbedLayer(Layer):
+    """``EmbedLayer(sparse_feature_columns, k=8)`` -- DL/layer/core.py:268.
+
+    The reference builds one keras ``Embedding(feat_onehot_dim, k)`` per field and ignores
+    ``feat['embed_dim']``; so does this.  All tables live in one arena
+    ``[sum(V_f), k]`` so a single kernel serves the 26 lookups; ``emb_layers[i]`` is a view of
+    table i.  ``call`` returns the flattened ``[B, F*k]`` of core.py:279 (``flatten=False`` gives
+    the ``[B, F, k]`` view the PNN product layers are specified on).
+    Out-of-range ids raise IndexError (CPU-TF behaviour); ``check_ids=False`` gives GPU-TF's
+    silent zero rows.
+    """
+
+    def __init__(self, sparse_feature_columns, k=8, flatten=True, check_ids=True, device=None, init="uniform"):
+        super().__init__(device)
+        self.k = int(k)
+        self.flatten = flatten
+        self.check = check_ids
+        self.vocab = [int(f["feat_onehot_dim"]) for f in sparse_feature_columns]
+        self.F = len(self.vocab)
+        off = np.concatenate([[0], np.cumsum(self.vocab)]).astype(np.int64)
+        self.row_off_host = off
+        self.row_off = torch.from_numpy(off).to(self.device)
+        total = int(off[-1])
+        if init == "uniform" and total * self.k > (1 << 24) and self.device.type == "cuda":
+            # large arenas: same U(-0.05, 0.05) law, generated on the device (no multi-GB host staging)
+            g = torch.Generator(device=self.device)
+            g.manual_seed(20240 + total)
+            self.arena = torch.empty((total, self.k), dtype=torch.float32, device=self.device)
+            self.arena.uniform_(-0.05, 0.05, generator=g)
+            self._weights["embeddings"] = self.arena
+        elif init == "uniform":
+            self.arena = self.add_weight("embeddings", (total, self.k), init_uniform)
+        else:                                   # caller fills the arena (e.g. hash-initialised shards)
+            self.arena = torch.empty((total, self.k), dtype=torch.float32, device=self.device)
+            self._weights["embeddings"] = self.arena
+        self.emb_layers = [self.arena[off[i]:off[i + 1]] for i in range(self.F)]
+        self.built = True
+
+    def set_tables(self, tables):
+        for dst, src in zip(self.emb_layers, tables):
+            dst.copy_(torch.as_tensor(np.asarray(src, dtype=np.float32)))
+        self._bump()
+
+    def gather(self, ids, dense=None, out=None, out_ld=None):
+        """x = [dense, embed(ids)] in the reference column order (dense may be None)."""
+        ids = ids if isinstance(ids, torch.Tensor) and ids.is_cuda else _ids_to_device(ids, self.device)
+        require_cuda(ids, "EmbedLayer")
+        ids, kind, ids_ld = ids_arg(ids)
+        B = ids.shape[0]
+        D = 0 if dense is None else dense.shape[1]
+        width = D + self.F * self.k
+        if out is None:
+            out_ld = width
+            out = torch.empty((B, width), dtype=torch.float32, device=self.device)
+        _lib.call("ctrhot_gather_f32", ptr(self.arena), ptr(self.row_off), self.F, self.k, ptr(ids), kind, ids_ld, B,
+                  ptr(dense), 0 if dense is None else dense.stride(0), D, ptr(out), out_ld, ptr(self.err_flag()),
+                  stream_ptr())
+        if self.check:
+            self.check_ids()
+        return out
+
+    def call(self, inputs, *args, **kwargs):
+        emb = self.gather(inputs)
+        if not self.flatten:
+            emb = emb.view(emb.shape[0], self.F, self.k)
+        return emb
+
+
+def _ids_to_device(ids, device):
+    if isinstance(ids, torch.Tensor):
+        t = ids
+    else:
+        a = np.asarray(ids)
+        if a.dtype == object:
+            a = a.astype(np.float32)
+        t = torch.from_numpy(np.ascontiguousarray(a))
+    if t.dtype in (torch.int64, torch.int16, torch.uint8, torch.int8):
+        t = t.to(torch.int32)
+    elif t.dtype in (torch.float64, torch.float16, torch.bfloat16):
+        t = t.to(torch.float32)
+    return t.to(device, non_blocking=True)
+
+
+class DenseStack:
+    """Host driver for a chain of Dense layers: descriptor array, packed weights, workspace.
+
+    ``layers``: list of dicts {kernel, bias, act, act_param, alpha_rows, dice_eps}.  ``precision`` is
+    'tf32' (tcgen05/TMEM path) or 'fp32' (CUDA-core path).
+    """
+
+    def __init__(self, precision="tf32"):
+        if precision not in ("tf32", "fp32"):
+            raise ValueError("precision must be 'tf32' or 'fp32'")
+        self.precision = precision
+        self.layers = []
+        self._packed = {}
+        self._ws = None
+        self._key = None
+
+    def set_layers(self, layers, version):
+        if self._key != version:
+            self.layers = layers
+            self._packed = {}
+            self._key = version
+
+    def descs(self):
+        n = len(self.layers)
+        arr = (_lib.DenseDesc * n)()
+        for i, L in enumerate(self.layers):
+            k = L["kernel"]
+            d = arr[i]
+            d.weight = ptr(k)
+            d.bias = ptr(L.get("bias"))
+            d.act_param = ptr(L.get("act_param"))
+            d.in_dim, d.out_dim = int(k.shape[0]), int(k.shape[1])
+            d.act = int(L.get("act", _lib.ACT_NONE))
+            d.alpha_rows = int(L.get("alpha_rows", 1))
+            d.dice_eps = float(L.get("dice_eps", 1e-9))
+            d.packed = 0
+            if self.precision == "tf32" and d.out_dim >= 8:
+                if i not in self._packed:
+                    nbytes = _lib.query("ctrhot_mlp_pack_bytes", d.in_dim, d.out_dim)
+                    buf = torch.empty(nbytes // 4, dtype=torch.float32, device=k.device)
+                    _lib.call("ctrhot_mlp_pack", ptr(k), d.in_dim, d.out_dim, ptr(buf), stream_ptr())
+                    self._packed[i] = buf
+                d.packed = ptr(self._packed[i])
+        return arr
+
+    def run(self, x, x_ld=None, out=None):
+        require_cuda(x, "DenseStack")
+        M = x.shape[0]
+        x_ld = x.stride(0) if x_ld is None else x_ld
+        arr = self.descs()
+        n = len(arr)
+        n_out = arr[n - 1].out_dim
+        if out is None:
+            out = torch.empty((M, n_out), dtype=torch.float32, device=x.device)
+        need = _lib.query("ctrhot_mlp_workspace_bytes", M, arr, n)
+        if self._ws is None or self._ws.numel() * 4 < need or self._ws.device != x.device:
+            self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=x.device)
+        fn = "ctrhot_mlp_tf32" if self.precision == "tf32" else "ctrhot_mlp_f32"
+        _lib.call(fn, ptr(x), x_ld, M, arr, n, ptr(out), out.stride(0), ptr(self._ws), self._ws.numel() * 4, stream_ptr())
+        fused_dot = (self.precision == "tf32" and n >= 2 and n_out == 1 and arr[n - 1].act == _lib.ACT_NONE
+                     and out.stride(0) == 1 and 8 <= arr[n - 2].out_dim <= 256)
+        _lib.LAUNCHES[0] += (n - 1 if fused_dot else n) - 1      # one kernel per layer; a trailing Dense(h->1) is fused
+        return out
+
+
+def dense_params(layer, name, in_dim, out_dim):
+    """keras Dense defaults: glorot_uniform kernel [in,out], zero bias."""
+    k = layer.add_weight(name + "/kernel", (in_dim, out_dim), init_glorot_uniform)
+    b = layer.add_weight(name + "/bias", (out_dim,), init_zeros)
+    return k, b

@@ -1,0 +1,352 @@
+"""Criteo-shaped models of the reference zoo on the fused B200 path:
+FM (DL/model/fm.py:14-23), FFM (ffm.py:14-23), DeepFM (deepFM.py:15-31), WideDeep
+(wideDeep.py:14-34), DCN (dcn.py:15-34), PNN (pnn.py:14-53).  Constructor signatures, weight names
+and ``call()`` layouts follow the reference; additive kwargs: ``embed_dim`` (the reference never
+passes EmbedLayer's k), ``precision`` ('tf32' tcgen05 tower | 'fp32'), ``device``.
+
+Inputs: the reference's single ``[B, 39]`` matrix (cols 0-12 dense floats, 13-38 label-encoded ids
+stored as floats) as numpy or torch; or the fast path ``(dense_f32 [B,13], ids_i32 [B,26])``.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .. import _lib
+from ..layer.base import Model, as_device_f32, ids_arg, ptr, require_cuda, stream_ptr
+from ..layer.core import EmbedLayer, _ids_to_device
+from ..layer.interaction import (CrossLayer, DNNLayer, FFMLayer, FMLayer, InnerProductLayer, OuterProductLayer,
+                                 WideLayer)
+
+N_DENSE = 13   # hard-coded in every reference call(): deepFM.py:24, dcn.py:25, wideDeep.py:23, pnn.py:29
+
+
+def split_inputs(inputs, device, n_dense=N_DENSE, n_sparse=None):
+    """-> (dense [B,D] fp32 view, ids [B,F] view (float or int32), rest or None), all on device."""
+    if isinstance(inputs, (tuple, list)) and len(inputs) == 2:
+        dense = as_device_f32(inputs[0], device)
+        ids = _ids_to_device(inputs[1], device)
+        return dense, ids, None
+    x = as_device_f32(inputs, device)
+    end = x.shape[1] if n_sparse is None else n_dense + n_sparse
+    rest = x[:, end:] if end < x.shape[1] else None
+    return x[:, :n_dense], x[:, n_dense:end], rest
+
+
+def _front_supported(k, kfm, F, D):
+    return k % 4 == 0 and F * (k // 4) <= 26 * 32 and D <= 32 and (kfm is None or kfm in (4, 8, 10, 16))
+
+
+def _pad32(n):
+    return (n + 31) // 32 * 32
+
+
+def _permute_rows(W, D):
+    """Reference column order [dense D | emb] -> internal [emb | dense D] (rows of a [n, *] weight)."""
+    return torch.cat([W[D:], W[:D]], dim=0).contiguous()
+
+
+class FM(Model):
+    """``sigmoid(FMLayer(k)(x))`` on the dense one-hot matrix -- DL/model/fm.py:14-23."""
+
+    def __init__(self, k, w_reg=1e-4, v_reg=1e-4, device=None):
+        super().__init__(device)
+        self.fm = self.track(FMLayer(k, w_reg, v_reg, device=self.device))
+
+    def build(self, input_shape):
+        if not self.fm.built:
+            self.fm.build(input_shape)
+            self.fm.built = True
+
+    def call(self, inputs, training=None, mask=None):
+        return self.fm(inputs, apply_sigmoid=True)
+
+    def call_sparse(self, dense, ids, onehot_offsets):
+        """Same result from (dense [B,13], ids [B,26]) + the one-hot column offset of each field."""
+        dense = as_device_f32(dense, self.device)
+        ids = _ids_to_device(ids, self.device)
+        dense_col = torch.arange(dense.shape[1], dtype=torch.int32, device=self.device)
+        col_off = torch.as_tensor(np.asarray(onehot_offsets, dtype=np.int64)).to(self.device)
+        return self.fm.call_onehot(dense, dense_col, ids, col_off, apply_sigmoid=True)
+
+
+class FFM(Model):
+    """``sigmoid(FFMLayer(feature_columns, k)(x))`` -- DL/model/ffm.py:14-23."""
+
+    def __init__(self, feature_columns, k, w_reg=1e-4, v_reg=1e-4, device=None):
+        super().__init__(device)
+        self.dense_feature_columns, self.sparse_feature_columns = feature_columns
+        self.ffm = self.track(FFMLayer(feature_columns, k, w_reg, v_reg, device=self.device))
+
+    def build(self, input_shape):
+        if not self.ffm.built:
+            self.ffm.build(input_shape)
+            self.ffm.built = True
+
+    def call(self, inputs, **kwargs):
+        return self.ffm(inputs, apply_sigmoid=True)
+
+
+class _EmbedTowerModel(Model):
+    """Shared plumbing: embedding arena + tower whose first kernel is permuted to the internal order."""
+
+    def _tower_layers(self, dnn, D):
+        key = (dnn._version, D)
+        if getattr(self, "_tl", None) is None or self._tl[0] != key:
+            ls = dnn.layer_dicts()
+            ls[0] = dict(ls[0], kernel=_permute_rows(ls[0]["kernel"], D))
+            self._tl = (key, ls)
+        return self._tl[1]
+
+    def _ensure_built(self, dnn, n):
+        if not dnn.built:
+            dnn.build((None, n))
+            dnn.built = True
+
+
+class DeepFM(_EmbedTowerModel):
+    """``sigmoid(0.5 * (FM(x) + DNN(x)))``, x = [dense, Embed(ids)] -- DL/model/deepFM.py:15-31.
+    The FM term is a dense FM over x with its own v:[d,k]."""
+
+    def __init__(self, feature_columns, k, w_reg, v_reg, hidden_units, output_dim, activation,
+                 embed_dim=8, precision="tf32", check_ids=True, device=None):
+        super().__init__(device)
+        self.dense_feature_columns, self.sparse_feature_columns = feature_columns
+        self.embed_layer = self.track(EmbedLayer(self.sparse_feature_columns, k=embed_dim, check_ids=False,
+                                                 device=self.device))
+        self.fm = self.track(FMLayer(k, w_reg, v_reg, device=self.device))
+        self.dnn = self.track(DNNLayer(hidden_units, output_dim, activation, precision=precision, device=self.device))
+        self.check = check_ids
+        self.fused = True
+        self.events = None          # bench hook: list receiving (front_start, front_end, tower_end) CUDA events
+        self.embed_layer._err_flag = self.err_flag()
+
+    def build(self, input_shape):
+        D = len(self.dense_feature_columns)
+        n = D + self.embed_layer.F * self.embed_layer.k
+        if not self.fm.built:
+            self.fm.build((None, n))
+            self.fm.built = True
+        self._ensure_built(self.dnn, n)
+
+    def call(self, inputs, training=None, mask=None):
+        E = self.embed_layer
+        D = len(self.dense_feature_columns)
+        dense, ids, _ = split_inputs(inputs, self.device, D)
+        require_cuda(dense, "DeepFM")
+        B = dense.shape[0]
+        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        if self.fused and self.dnn.output_dim == 1 and _front_supported(E.k, self.fm.k, E.F, D):
+            ids, kind, ids_ld = ids_arg(ids)
+            n = D + E.F * E.k
+            x_ld = _pad32(n)
+            x = torch.empty((B, x_ld), dtype=torch.float32, device=self.device)
+            fm_out = torch.empty((B,), dtype=torch.float32, device=self.device)
+            planes = self.fm.planes(D)
+            self.dnn.stack.set_layers(self._tower_layers(self.dnn, D), (self.dnn._version, D))
+            ev = None
+            if self.events is not None:
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                ev[0].record()
+            _lib.call("ctrhot_deepfm_front_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld,
+                      ptr(dense), dense.stride(0), D, B, ptr(self.fm.w0), ptr(planes), self.fm.k,
+                      ptr(x), x_ld, ptr(fm_out), ptr(self.err_flag()), stream_ptr())
+            if ev:
+                ev[1].record()
+            dnn_out = self.dnn.stack.run(x, x_ld)
+            if ev:
+                ev[2].record()
+                self.events.append(tuple(ev))
+        else:
+            x = E.gather(ids, dense)
+            fm_out = self.fm(x)
+            dnn_out = self.dnn(x)
+        _lib.call("ctrhot_combine_sigmoid_f32", ptr(fm_out), ptr(dnn_out), 0, 0, 0.5, B, ptr(out), stream_ptr())
+        if self.check:
+            self.check_ids()
+        return out
+
+
+class WideDeep(_EmbedTowerModel):
+    """``sigmoid(0.5 * (Wide([dense, onehot]) + DNN(Embed(ids))))`` -- DL/model/wideDeep.py:14-34.
+    The deep side sees embeddings only.  Matrix input: ``[B, 39 + n_onehot]``; fast path
+    ``(dense, ids)`` uses ``onehot_width`` (default: feat_onehot_dim) and never builds the one-hot."""
+
+    def __init__(self, feature_columns, hidden_units, output_dim, activation, embed_dim=8, precision="tf32",
+                 check_ids=True, onehot_width=None, device=None):
+        super().__init__(device)
+        self.dense_feature_columns, self.sparse_feature_columns = feature_columns
+        self.embed_layer = self.track(EmbedLayer(self.sparse_feature_columns, k=embed_dim, check_ids=False,
+                                                 device=self.device))
+        self.wide = self.track(WideLayer(device=self.device))
+        self.deep = self.track(DNNLayer(hidden_units, output_dim, activation, precision=precision, device=self.device))
+        self.check = check_ids
+        widths = onehot_width if onehot_width is not None else [f["feat_onehot_dim"] for f in self.sparse_feature_columns]
+        self.set_onehot_layout(widths)
+
+    def set_onehot_layout(self, widths):
+        D = len(self.dense_feature_columns)
+        self.onehot_width = [int(w) for w in widths]
+        # wide input = [dense(D), get_dummies block = dense(D) again + one-hot fields] (dataset.py:53-58)
+        off = 2 * D + np.concatenate([[0], np.cumsum(self.onehot_width)])
+        self.col_off = torch.from_numpy(off.astype(np.int64)).to(self.device)
+        self.dense_col = torch.arange(2 * D, dtype=torch.int32, device=self.device)
+        self.n_wide = int(off[-1])
+
+    def build(self, input_shape):
+        if not self.wide.built:
+            self.wide.build((None, self.n_wide))
+            self.wide.built = True
+        self._ensure_built(self.deep, self.embed_layer.F * self.embed_layer.k)
+
+    def call(self, inputs, training=None, mask=None):
+        E = self.embed_layer
+        D = len(self.dense_feature_columns)
+        dense, ids, onehot = split_inputs(inputs, self.device, D, E.F)
+        require_cuda(dense, "WideDeep")
+        B = dense.shape[0]
+        if onehot is not None:
+            wide_in = torch.cat([dense, onehot], dim=1)
+            if wide_in.shape[1] != self.wide.w.shape[0]:
+                raise ValueError("wide input has %d columns, weights expect %d" % (wide_in.shape[1], self.wide.w.shape[0]))
+            wide_out = self.wide(wide_in)
+        else:
+            dense2 = torch.cat([dense, dense], dim=1)
+            wide_out = self.wide.call_onehot(dense2, self.dense_col, ids, self.col_off)
+        emb = E.gather(ids)
+        deep_out = self.deep(emb)
+        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        _lib.call("ctrhot_combine_sigmoid_f32", ptr(wide_out), ptr(deep_out), 0, 0, 0.5, B, ptr(out), stream_ptr())
+        if self.check:
+            E.check_ids()
+        return out
+
+
+class DCN(_EmbedTowerModel):
+    """``sigmoid(Dense_1([Cross(x), DNN(x)]))`` -- DL/model/dcn.py:15-34; all cross layers fused with the gather."""
+
+    def __init__(self, feature_columns, hidden_units, output_dim, activation, layer_num, reg_w=1e-4, reg_b=1e-4,
+                 embed_dim=8, precision="tf32", check_ids=True, device=None):
+        super().__init__(device)
+        self.dense_feature_columns, self.sparse_feature_columns = feature_columns
+        self.embed_layer = self.track(EmbedLayer(self.sparse_feature_columns, k=embed_dim, check_ids=False,
+                                                 device=self.device))
+        self.dense_layer = self.track(DNNLayer(hidden_units, output_dim, activation, precision=precision,
+                                               device=self.device))
+        self.cross_layer = self.track(CrossLayer(layer_num, reg_w, reg_b, device=self.device))
+        self.check = check_ids
+        self.fused = True
+        self._packed = None
+        self.embed_layer._err_flag = self.err_flag()
+
+    def build(self, input_shape):
+        from ..layer.core import dense_params
+        D = len(self.dense_feature_columns)
+        n = D + self.embed_layer.F * self.embed_layer.k
+        if not self.cross_layer.built:
+            self.cross_layer.build((None, n))
+            self.cross_layer.built = True
+        self._ensure_built(self.dense_layer, n)
+        self.out_kernel, self.out_bias = dense_params(self, "output_layer", n + self.dense_layer.output_dim, 1)
+
+    def _packed_cross(self, D, n):
+        key = (self._version, self.cross_layer._version)
+        if self._packed is None or self._packed[0] != key:
+            n_pad = _pad32(n)
+            w, b = self.cross_layer.stacked()
+            L = max(self.cross_layer.layer_num, 1)
+            cw = torch.empty((L, n_pad), dtype=torch.float32, device=self.device)
+            cb = torch.empty((L, n_pad), dtype=torch.float32, device=self.device)
+            fw = torch.empty((1, n_pad), dtype=torch.float32, device=self.device)
+            _lib.call("ctrhot_permute_cols", ptr(w), L, n, D, ptr(cw), stream_ptr())
+            _lib.call("ctrhot_permute_cols", ptr(b), L, n, D, ptr(cb), stream_ptr())
+            fsrc = self.out_kernel[:n, 0].contiguous()
+            _lib.call("ctrhot_permute_cols", ptr(fsrc), 1, n, D, ptr(fw), stream_ptr())
+            self._packed = (key, cw, cb, fw)
+        return self._packed[1:]
+
+    def call(self, inputs, training=None, mask=None):
+        E = self.embed_layer
+        D = len(self.dense_feature_columns)
+        dense, ids, _ = split_inputs(inputs, self.device, D)
+        require_cuda(dense, "DCN")
+        B = dense.shape[0]
+        n = D + E.F * E.k
+        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        if self.fused and self.dense_layer.output_dim == 1 and _front_supported(E.k, None, E.F, D):
+            ids, kind, ids_ld = ids_arg(ids)
+            x_ld = _pad32(n)
+            cw, cb, fw = self._packed_cross(D, n)
+            x = torch.empty((B, x_ld), dtype=torch.float32, device=self.device)
+            cdot = torch.empty((B,), dtype=torch.float32, device=self.device)
+            _lib.call("ctrhot_dcn_front_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld,
+                      ptr(dense), dense.stride(0), D, B, self.cross_layer.layer_num, ptr(cw), ptr(cb), ptr(fw),
+                      ptr(x), x_ld, 0, 0, ptr(cdot), ptr(self.err_flag()), stream_ptr())
+            self.dense_layer.stack.set_layers(self._tower_layers(self.dense_layer, D), (self.dense_layer._version, D))
+            dnn_out = self.dense_layer.stack.run(x, x_ld)
+            _lib.call("ctrhot_combine_sigmoid_f32", ptr(cdot), ptr(dnn_out), ptr(self.out_kernel[n:]), ptr(self.out_bias),
+                      1.0, B, ptr(out), stream_ptr())
+        else:
+            x = E.gather(ids, dense)
+            cross = self.cross_layer(x)
+            dnn_out = self.dense_layer(x)
+            cat = torch.cat([cross, dnn_out], dim=1)
+            logit = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+            _lib.call("ctrhot_wide_dense_f32", ptr(cat), cat.stride(0), cat.shape[1], B, ptr(self.out_bias),
+                      ptr(self.out_kernel), ptr(logit), stream_ptr())
+            _lib.call("ctrhot_combine_sigmoid_f32", ptr(logit), 0, 0, 0, 1.0, B, ptr(out), stream_ptr())
+        if self.check:
+            self.check_ids()
+        return out
+
+
+class PNN(Model):
+    """``DNN([flat(E), inner(E) and/or outer(E)])``, no sigmoid -- DL/model/pnn.py:14-53.  The product
+    layers get the [B,F,k] view of the gathered buffer; the FGCNN branch is out of scope."""
+
+    def __init__(self, feature_columns, mode, hidden_units, output_dim, activation="relu", dropout=0.2,
+                 use_fgcnn=False, embed_dim=8, precision="tf32", check_ids=True, device=None):
+        super().__init__(device)
+        if mode not in ("inner", "outer", "both"):
+            raise ValueError("Please choice mode's value in 'inner', 'outer', 'both'.")
+        if use_fgcnn:
+            raise NotImplementedError("FGCNN branch (pnn.py:33-35) is outside the hot path (SURVEY 2.1 C8)")
+        self.mode = mode
+        self.dense_feature_columns, self.sparse_feature_columns = feature_columns
+        self.dnn_layer = self.track(DNNLayer(hidden_units, output_dim, activation, dropout, precision=precision,
+                                             device=self.device))
+        self.inner_product_layer = self.track(InnerProductLayer(device=self.device))
+        self.outer_product_layer = self.track(OuterProductLayer(device=self.device))
+        self.embed_layer = self.track(EmbedLayer(self.sparse_feature_columns, k=embed_dim, check_ids=check_ids,
+                                                 device=self.device))
+
+    def build(self, input_shape):
+        E = self.embed_layer
+        P = E.F * (E.F - 1) // 2
+        if not self.outer_product_layer.built:
+            self.outer_product_layer.build((None, E.F, E.k))
+            self.outer_product_layer.built = True
+        width = E.F * E.k + P * {"inner": 1, "outer": 1, "both": 2}[self.mode]
+        if not self.dnn_layer.built:
+            self.dnn_layer.build((None, width))
+            self.dnn_layer.built = True
+        self.width = width
+
+    def call(self, inputs, training=None, mask=None):
+        E = self.embed_layer
+        D = len(self.dense_feature_columns)
+        _dense, ids, _ = split_inputs(inputs, self.device, D)
+        B = ids.shape[0]
+        fk = E.F * E.k
+        P = E.F * (E.F - 1) // 2
+        ld = _pad32(self.width)
+        buf = torch.zeros((B, ld), dtype=torch.float32, device=self.device)
+        E.gather(ids, out=buf, out_ld=ld)
+        z = buf.as_strided((B, E.F, E.k), (ld, E.k, 1))
+        col = fk
+        if self.mode in ("inner", "both"):
+            self.inner_product_layer(z, out=buf[:, col:col + P])
+            col += P
+        if self.mode in ("outer", "both"):
+            self.outer_product_layer(z, out=buf[:, col:col + P])
+        return self.dnn_layer(buf[:, :self.width], x_ld=ld)

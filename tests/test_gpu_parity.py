@@ -1,0 +1,295 @@
+"""GPU parity (run with -m gpu on the B200): every CUDA path through the Python drop-ins / C-ABI
+against the float64 oracle on the frozen golden vectors.
+
+Tolerances (BASELINE north_star): gathered rows bit-exact; FM/FFM/PNN/DCN outputs <= 1e-5 relative
+in fp32; logits <= 2e-3 absolute where the towers / attention use TF32 tensor cores.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ctr_oracle as O
+from oracle import synth as S
+from recommender_system_b200 import _lib
+from recommender_system_b200.layer import (Attention, CrossLayer, Dice, DNNLayer, EmbedLayer, FFMLayer, FMLayer,
+                                           InnerProductLayer, OuterProductLayer, WideLayer)
+from recommender_system_b200.model.criteo import DCN, FFM, FM, PNN, DeepFM, WideDeep
+from recommender_system_b200.model.din import DIN
+from recommender_system_b200.utils import synth
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-5        # interaction layers, fp32
+LOGIT = 2e-3      # TF32 towers, absolute on logits (probabilities are tighter still)
+
+
+def npy(t):
+    return t.detach().cpu().numpy().astype(np.float64)
+
+
+def close_rel(got, want, rel=REL):
+    scale = np.maximum(np.abs(want), 1e-3 * np.max(np.abs(want)) + 1e-30)
+    err = np.max(np.abs(got - want) / scale)
+    assert err <= rel, "max rel err %.3g > %.3g" % (err, rel)
+
+
+def fc_from(vocab, k):
+    return synth.criteo_feature_columns([int(v) for v in vocab], k)
+
+
+def tables_of(a, prefix="table"):
+    return S._tables_of(a, prefix)
+
+
+def stack_weights(a, prefix):
+    out, i = [], 0
+    while "%s_k%d" % (prefix, i) in a:
+        out += [a["%s_k%d" % (prefix, i)], a["%s_b%d" % (prefix, i)]]
+        i += 1
+    return out
+
+
+# ------------------------------------------------------------------ layers
+@pytest.mark.parametrize("ids_as", ["float", "int32"])
+def test_embed_bit_exact(golden, lib, ids_as):
+    a, want = S.load_case(golden, "embed")
+    e = EmbedLayer(fc_from(a["vocab"], 8)[1], k=8)
+    e.set_tables(tables_of(a))
+    ids = a["ids"].astype(np.float32) if ids_as == "float" else a["ids"].astype(np.int32)
+    got = e(ids)
+    assert got.shape == (7, 26 * 8)
+    np.testing.assert_array_equal(got.cpu().numpy(), want.astype(np.float32))
+    got3 = EmbedLayer.call(e, ids).view(7, 26, 8)
+    np.testing.assert_array_equal(got3.cpu().numpy(), want.astype(np.float32).reshape(7, 26, 8))
+
+
+def test_embed_out_of_range(golden, lib):
+    a, _ = S.load_case(golden, "embed")
+    e = EmbedLayer(fc_from(a["vocab"], 8)[1], k=8)
+    ids = a["ids"].astype(np.int32).copy()
+    ids[2, 5] = int(a["vocab"][5])
+    with pytest.raises(IndexError):
+        e(ids)
+    e2 = EmbedLayer(fc_from(a["vocab"], 8)[1], k=8, check_ids=False)     # GPU-TF behaviour: silent zeros
+    out = e2(ids).cpu().numpy().reshape(7, 26, 8)
+    assert (out[2, 5] == 0).all() and (out[2, 4] != 0).any()
+
+
+def test_embed_odd_k_scalar_path(lib):
+    rng = np.random.default_rng(0)
+    vocab = [5, 9, 3]
+    e = EmbedLayer(fc_from(vocab, 6)[1], k=6)
+    ids = np.stack([rng.integers(0, v, 33) for v in vocab], 1).astype(np.int32)
+    want = O.embed_layer(ids, [t.cpu().numpy() for t in e.emb_layers])
+    np.testing.assert_array_equal(e(ids).cpu().numpy(), want)
+
+
+def test_wide(golden, lib):
+    a, want = S.load_case(golden, "wide")
+    L = WideLayer()
+    L.build((None, 40))
+    L.set_weights([a["w0"], a["w"]])
+    close_rel(npy(L(a["x"])), want)
+
+
+def test_fm_dense(golden, lib):
+    a, want = S.load_case(golden, "fm")
+    L = FMLayer(10)
+    L.build((None, a["x"].shape[1]))
+    L.set_weights([a["w0"], a["w1"], a["v"]])
+    close_rel(npy(L(a["x"])), want)
+
+
+def test_dnn_fp32_and_tf32(golden, lib):
+    a, want = S.load_case(golden, "dnn")
+    for prec, tol in (("fp32", 2e-5), ("tf32", LOGIT)):
+        L = DNNLayer([32, 16], 1, "relu", precision=prec)
+        L.build((None, a["x"].shape[1]))
+        L.set_weights(stack_weights(a, "dnn"))
+        got = npy(L(a["x"]))
+        assert np.max(np.abs(got - want)) <= tol, (prec, np.max(np.abs(got - want)))
+
+
+def test_cross(golden, lib):
+    a, want = S.load_case(golden, "cross")
+    L = CrossLayer(3)
+    L.build((None, a["x"].shape[1]))
+    L.set_weights([a["w0"], a["w1"], a["w2"], a["b0"], a["b1"], a["b2"]])
+    close_rel(npy(L(a["x"])), want)
+
+
+def test_ffm(golden, lib):
+    a, want = S.load_case(golden, "ffm")
+    L = FFMLayer(fc_from(a["vocab"], 4), 4)
+    L.build(None)
+    L.set_weights([a["w0"], a["w"], a["v"]])
+    close_rel(npy(L(a["inputs"])), want)
+
+
+def test_pnn_inner_outer(golden, lib):
+    a, want_i = S.load_case(golden, "inner")
+    _, want_o = S.load_case(golden, "outer")
+    close_rel(npy(InnerProductLayer()(a["e"])), want_i)
+    op = OuterProductLayer()
+    op.build(a["e"].shape)
+    op.set_weights([a["W"]])
+    close_rel(npy(op(a["e"])), want_o)
+
+
+def test_dice(golden, lib):
+    a, want = S.load_case(golden, "dice")
+    L = Dice()
+    L.build(a["x"].shape)
+    L.set_weights([a["alphas"], a["mean"], a["var"]])
+    close_rel(npy(L(a["x"])), want)
+
+
+def att_weights(a):
+    ws, i = [], 0
+    while "att_k%d" % i in a:
+        ws += [a["att_k%d" % i], a["att_b%d" % i], a["att_a%d" % i]]
+        i += 1
+    return ws + [a["att_ko"], a["att_bo"]]
+
+
+def test_attention_prelu(golden, lib):
+    a, want = S.load_case(golden, "att")
+    L = Attention((16, 8), "prelu")
+    L.build([a["query"].shape, a["key"].shape, a["key"].shape, a["mask"].shape])
+    L.set_weights(att_weights(a))
+    got = npy(L([a["query"], a["key"], a["key"], a["mask"]]))
+    close_rel(got, want, 2e-5)
+    # all-padding row 0 -> uniform average of the keys (interaction.py:399-404)
+    np.testing.assert_allclose(got[0], a["key"][0].mean(0), rtol=1e-5, atol=1e-6)
+
+
+def test_attention_dice(golden, lib):
+    a, want = S.load_case(golden, "att_dice")
+    L = Attention((16, 8), "dice")
+    L.build([a["query"].shape, a["key"].shape, a["key"].shape, a["mask"].shape])
+    w = {"out/kernel": a["att_ko"], "out/bias": a["att_bo"]}
+    for i in range(2):
+        w["Dice_%d/dice_alpha" % i] = a["dice_a%d" % i]
+        w["Dice_%d/bn/moving_mean" % i] = a["dice_m%d" % i]
+        w["Dice_%d/bn/moving_variance" % i] = a["dice_v%d" % i]
+    L.set_weights(w)
+    close_rel(npy(L([a["query"], a["key"], a["key"], a["mask"]])), want, 2e-5)
+
+
+# ------------------------------------------------------------------ models
+def set_embed(model, a):
+    model.embed_layer.set_tables(tables_of(a))
+
+
+@pytest.mark.parametrize("prec,fused", [("fp32", True), ("fp32", False), ("tf32", True)])
+def test_deepfm(golden, lib, prec, fused):
+    a, want = S.load_case(golden, "deepfm")
+    m = DeepFM(fc_from(a["vocab"], 8), 10, 1e-4, 1e-4, [32, 16, 8], 1, "relu", embed_dim=8, precision=prec)
+    m.fused = fused
+    m.build(None)
+    set_embed(m, a)
+    m.fm.set_weights([a["w0"], a["w1"], a["v"]])
+    m.dnn.set_weights(stack_weights(a, "dnn"))
+    got = npy(m(a["inputs"]))
+    tol = 2e-6 if prec == "fp32" else LOGIT / 4
+    assert np.max(np.abs(got - want)) <= tol, np.max(np.abs(got - want))
+    # fast path (dense f32, ids i32) gives the same bits as the [B,39] float matrix
+    got2 = npy(m((a["inputs"][:, :13].astype(np.float32), a["inputs"][:, 13:].astype(np.int32))))
+    np.testing.assert_array_equal(got, got2)
+
+
+def test_widedeep(golden, lib):
+    a, want = S.load_case(golden, "widedeep")
+    vocab = [int(v) for v in a["vocab"]]
+    m = WideDeep(fc_from(vocab, 8), [32, 16, 8], 1, "relu", embed_dim=8, precision="fp32")
+    m.build(None)
+    set_embed(m, a)
+    m.wide.set_weights([a["w0"], a["w"]])
+    m.deep.set_weights(stack_weights(a, "dnn"))
+    got = npy(m(a["inputs"]))                       # reference matrix form [dense, ids, onehot]
+    assert np.max(np.abs(got - want)) <= 2e-6
+    got2 = npy(m((a["inputs"][:, :13].astype(np.float32), a["inputs"][:, 13:39].astype(np.int32))))
+    assert np.max(np.abs(got2 - want)) <= 2e-6      # sparse form: no one-hot materialised
+
+
+@pytest.mark.parametrize("prec,fused", [("fp32", True), ("fp32", False), ("tf32", True)])
+def test_dcn(golden, lib, prec, fused):
+    a, want = S.load_case(golden, "dcn")
+    m = DCN(fc_from(a["vocab"], 8), [32, 16, 8], 1, "relu", 3, embed_dim=8, precision=prec)
+    m.fused = fused
+    m.build(None)
+    set_embed(m, a)
+    m.cross_layer.set_weights([a["cw0"], a["cw1"], a["cw2"], a["cb0"], a["cb1"], a["cb2"]])
+    m.dense_layer.set_weights(stack_weights(a, "dnn"))
+    m.set_weights({"output_layer/kernel": a["final_k"], "output_layer/bias": a["final_b"]})
+    got = npy(m(a["inputs"]))
+    tol = 2e-6 if prec == "fp32" else LOGIT / 4
+    assert np.max(np.abs(got - want)) <= tol, np.max(np.abs(got - want))
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_pnn(golden, lib, prec):
+    a, want = S.load_case(golden, "pnn")
+    m = PNN(fc_from(a["vocab"], 8), "both", [32, 16], 1, embed_dim=8, precision=prec)
+    m.build(None)
+    set_embed(m, a)
+    m.outer_product_layer.set_weights([a["W"]])
+    m.dnn_layer.set_weights(stack_weights(a, "dnn"))
+    got = npy(m(a["inputs"]))
+    tol = 2e-5 if prec == "fp32" else LOGIT
+    assert np.max(np.abs(got - want)) <= tol, np.max(np.abs(got - want))
+
+
+def din_from_case(a, prec):
+    fc = [[{"feat": "d0"}, {"feat": "d1"}],
+          [{"feat": "o0", "feat_onehot_dim": 11, "embed_dim": 8}, {"feat": "o1", "feat_onehot_dim": 7, "embed_dim": 8},
+           {"feat": "seq", "feat_onehot_dim": 40, "embed_dim": 8}]]
+    m = DIN(fc, ["seq"], att_hidden_units=(16, 8), dnn_hidden_units=(16, 8), precision=prec)
+    m.build(None)
+    m.att_layer.build_for(5, 8)
+    w = {"embed_sparse_0/embeddings": a["other_table0"], "embed_sparse_1/embeddings": a["other_table1"],
+         "embed_seq_0/embeddings": a["seq_table0"], "bn/gamma": a["bn_gamma"], "bn/beta": a["bn_beta"],
+         "bn/moving_mean": a["bn_mean"], "bn/moving_variance": a["bn_var"], "out/kernel": a["out_k"],
+         "out/bias": a["out_b"]}
+    for i in range(2):
+        w["dense_%d/kernel" % i] = a["tw_k%d" % i]
+        w["dense_%d/bias" % i] = a["tw_b%d" % i]
+        w["dense_%d/prelu_alpha" % i] = a["tw_a%d" % i]
+    m.set_weights(w)
+    m.att_layer.set_weights(att_weights(a))
+    inputs = {"d0": a["dense"][:, 0:1], "d1": a["dense"][:, 1:2], "o0": a["other_ids"][:, 0:1],
+              "o1": a["other_ids"][:, 1:2], "seq": a["hist_ids"][:, :, 0], "movie_id": a["cand_ids"]}
+    return m, inputs
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_din(golden, lib, prec):
+    a, want = S.load_case(golden, "din")
+    m, inputs = din_from_case(a, prec)
+    got = npy(m(inputs))
+    tol = 5e-6 if prec == "fp32" else LOGIT / 4
+    assert np.max(np.abs(got - want)) <= tol, np.max(np.abs(got - want))
+
+
+# ------------------------------------------------------------------ config 1: the reference's own data
+def test_fm_config1_on_reference_loader_output(criteo_cfg1, lib):
+    """FM k=8 on the bundled Criteo sample exactly as fm.py loads it (dense one-hot [2000, 43604]),
+    against the O64 oracle in the reference's dense form, and the gather form against both."""
+    z = criteo_cfg1
+    dense, ids = z["dense"], z["ids"]
+    n = int(z["onehot_cols"])
+    rng = np.random.default_rng(0)
+    w0, w1, v = np.zeros(1), S.f32(rng.normal(0, 0.05, (n, 1))), S.f32(rng.normal(0, 0.05, (n, 8)))
+    want = O.fm_onehot_sparse(dense.astype(np.float64), np.arange(13), ids, z["onehot_offsets"], w0, w1, v)
+    want = O.sigmoid(want)
+    X = np.zeros((dense.shape[0], n), np.float32)
+    X[:, :13] = dense
+    for f in range(26):
+        X[np.arange(X.shape[0]), z["onehot_offsets"][f] + ids[:, f]] = 1.0
+    m = FM(8)
+    m.build(X.shape)
+    m.fm.set_weights([w0, w1, v])
+    got_dense = npy(m(X))
+    got_sparse = npy(m.call_sparse(dense, ids, np.append(z["onehot_offsets"], n)))
+    close_rel(got_dense, want)
+    close_rel(got_sparse, want)

@@ -1,0 +1,98 @@
+"""CPU: the oracle against its frozen golden vectors and against algebraic identities
+(SURVEY 8(c)): one-hot == gather, pair-sum identity, Cross with w=0, Attention with W=0 -> masked
+mean, all-padding row -> uniform softmax."""
+import numpy as np
+import pytest
+
+from oracle import ctr_oracle as O
+from oracle import synth
+
+
+@pytest.mark.parametrize("name", list(synth.CASES))
+def test_oracle_matches_frozen_golden(golden, name):
+    arrays, expected = synth.load_case(golden, name)
+    got = synth.CASES[name][1](arrays)
+    np.testing.assert_allclose(got, expected, rtol=1e-12, atol=1e-12)
+
+
+@pytest.mark.parametrize("name", list(synth.CASES))
+def test_o32_close_to_o64(golden, name):
+    """O32 (fp32, reference op order) stays within the north_star tolerances of O64."""
+    arrays, expected = synth.load_case(golden, name)
+    a32 = {k: (v.astype(np.float32) if v.dtype == np.float64 else v) for k, v in arrays.items()}
+    got = synth.CASES[name][1](a32)
+    np.testing.assert_allclose(got, expected, rtol=2e-5, atol=2e-6)
+
+
+def test_fm_onehot_equals_gather_on_reference_data(criteo_cfg1):
+    """Config 1: FM on the reference loader's dense one-hot matrix == 39-row gather form."""
+    z = criteo_cfg1
+    dense, ids = z["dense"][:256].astype(np.float64), z["ids"][:256]
+    n = int(z["onehot_cols"])
+    rng = np.random.default_rng(0)
+    w0 = np.zeros(1)
+    w1 = rng.normal(0, 0.05, (n, 1))
+    v = rng.normal(0, 0.05, (n, 8))
+    X = np.zeros((dense.shape[0], n))
+    X[:, :13] = dense
+    for f in range(26):
+        X[np.arange(X.shape[0]), z["onehot_offsets"][f] + ids[:, f]] = 1.0
+    assert abs((X != 0).sum(1).mean() - 35) < 1.0
+    ref = O.fm_layer(X, w0, w1, v)
+    got = O.fm_onehot_sparse(dense, np.arange(13), ids, z["onehot_offsets"], w0, w1, v)
+    np.testing.assert_allclose(got, ref, rtol=1e-10, atol=1e-12)
+
+
+def test_ffm_sparse_identity(golden):
+    a, expected = synth.load_case(golden, "ffm")
+    got = O.ffm_sparse(a["inputs"], [int(x) for x in a["vocab"]], a["w0"], a["w"], a["v"])
+    np.testing.assert_allclose(got, expected, rtol=1e-10, atol=1e-12)
+
+
+def test_pair_sum_identity():
+    rng = np.random.default_rng(1)
+    e = rng.normal(size=(5, 26, 8))
+    inner = O.inner_product_layer(e).sum(axis=1)
+    tot = e.sum(axis=1)
+    np.testing.assert_allclose(inner, 0.5 * ((tot ** 2).sum(1) - (e ** 2).sum((1, 2))), rtol=1e-10)
+
+
+def test_cross_zero_w():
+    rng = np.random.default_rng(2)
+    x = rng.normal(size=(4, 20))
+    bs = [rng.normal(size=(20, 1)) for _ in range(3)]
+    out = O.cross_layer(x, [np.zeros((20, 1))] * 3, bs)
+    np.testing.assert_allclose(out, x + sum(b[:, 0] for b in bs), rtol=1e-12)
+
+
+def test_attention_zero_weights_is_masked_mean():
+    rng = np.random.default_rng(3)
+    B, T, K = 4, 6, 8
+    q, key = rng.normal(size=(B, K)), rng.normal(size=(B, T, K))
+    mask = (np.arange(T)[None, :] < np.array([0, 6, 3, 1])[:, None]).astype(float)
+    dense = [(np.zeros((4 * K, 5)), np.zeros(5), np.full((T, 5), 0.1))]
+    out = O.din_attention(q, key, key, mask, dense, (np.zeros((5, 1)), np.zeros(1)))
+    for b, n in enumerate([0, 6, 3, 1]):
+        want = key[b].mean(0) if n == 0 else key[b, :n].mean(0)   # all-padding row -> uniform 1/T (interaction.py:399-404)
+        np.testing.assert_allclose(out[b], want, rtol=1e-9, atol=1e-12)
+
+
+def test_outer_product_closed_form():
+    rng = np.random.default_rng(4)
+    e = rng.normal(size=(3, 5, 4))
+    W = rng.normal(size=(4, 10, 4))
+    out = O.outer_product_layer(e, W)
+    row, col = O.pair_index(5)
+    want = np.einsum("bpa,apc,bpc->bp", e[:, col], W, e[:, row])
+    np.testing.assert_allclose(out, want, rtol=1e-10)
+
+
+def test_embed_out_of_range_raises():
+    with pytest.raises(IndexError):
+        O.embed_layer(np.array([[3.0]]), [np.zeros((3, 2))])
+
+
+def test_embed_float_ids_truncate():
+    t = np.arange(10.0).reshape(5, 2)
+    out = O.embed_layer(np.array([[2.9]]), [t])
+    np.testing.assert_array_equal(out, t[2:3])
