@@ -145,6 +145,26 @@ int ctrhot_mlp_tf32(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_
                     int64_t workspace_bytes, void* stream);
 int64_t ctrhot_mlp_workspace_bytes(int64_t M, const ctrhot_dense_desc* h_layers, int n_layers);
 
+/* Whole tower in ONE persistent tcgen05 kernel: hidden activations stay in TMEM (layer l's epilogue
+ * writes layer l+1's A operand back with tcgen05.st), weights stream through the TMA engine.
+ * h_layers = 1..3 hidden Dense (out_dim 8..256, packed) + a final Dense(h -> 1, no activation).
+ *   out[m] = post(tower(x_m)),  post(y) = sigmoid?( scale * ( y * (y_scale?*y_scale:1) + (add_vec?add_vec[m]:0)
+ *                                                      + (add_bias?*add_bias:0) ) )
+ * (DeepFM: add_vec = FM term, scale 0.5, sigmoid -- deepFM.py:30; DCN: y_scale/add_vec/add_bias = the
+ * final Dense over [cross, dnn] -- dcn.py:32-33).  _gather: rows come straight from the embedding
+ * tables (x = [embeddings | dense] internal order never exists in HBM); first layer packed from the
+ * permuted kernel.  CTRHOT_ESHAPE when the shape does not fit (use ctrhot_mlp_tf32 then). */
+int ctrhot_tower_fused_tf32(const float* x, int64_t x_ld, int64_t M,
+                            const ctrhot_dense_desc* h_layers, int n_layers,
+                            const float* y_scale, const float* add_vec, const float* add_bias,
+                            float scale, int apply_sigmoid, float* out, void* stream);
+int ctrhot_tower_gather_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                             const void* ids, int ids_kind, int64_t ids_ld,
+                             const float* dense, int64_t dense_ld, int D, int64_t M,
+                             const ctrhot_dense_desc* h_layers, int n_layers,
+                             const float* y_scale, const float* add_vec, const float* add_bias,
+                             float scale, int apply_sigmoid, float* out, int* err_flag, void* stream);
+
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,
                     const float* var, float eps, float* out, void* stream);

@@ -158,14 +158,19 @@ __device__ __forceinline__ float warp_reduce_scatter(float (&v)[N], int lane) {
 // planes: [KFM+2][n_pad] in internal column order: plane c<KFM = v[:,c]; plane KFM = w1;
 // plane KFM+1 = s_j = sum_c v[j,c]^2   (so  sum_c (x^2 @ v^2)_c = x^2 . s, DL/layer/interaction.py:110-111).
 template <int IDKIND, int NQ, int S, int KFM>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (NQ * S <= 16) ? 2 : 1)
 deepfm_front_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k4,
                     const void* __restrict__ ids, int64_t ids_ld, const float* __restrict__ dense,
                     int64_t dense_ld, int D, int64_t B, const float* __restrict__ planes, int n_pad,
                     const float* __restrict__ w0, float* __restrict__ x, int64_t x_ld,
                     float* __restrict__ fm_out, int* __restrict__ err_flag) {
+  // The KFM+2 planes are processed in NG groups of GP <= 8 so that only S*GP accumulators are live
+  // (register budget <= 128 -> two CTAs per SM); each group ends in one 32-value warp reduce-scatter
+  // (value index = s*8 + c).
   constexpr int NP = KFM + 2;
-  constexpr int NPP = (NP <= 16) ? 16 : 32;       // slots per sample in the reduction
+  constexpr int NG = (NP + 7) / 8;
+  constexpr int GP = (NP + NG - 1) / NG;
+  static_assert(S * 8 <= 32, "S");
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -177,57 +182,62 @@ deepfm_front_kernel(const float* __restrict__ arena, const int64_t* __restrict__
     float xd[S];
     load_samples<IDKIND, NQ, S>(arena, row_off, F, k4, ids, ids_ld, dense, dense_ld, D, b0, B, lane,
                                 err_flag, xv, xd);
-    float acc[S][NP];
+    store_x<NQ, S>(x, x_ld, total, D, b0, B, lane, xv, xd);
+    float term = 0.f;
 #pragma unroll
-    for (int s = 0; s < S; ++s)
+    for (int g = 0; g < NG; ++g) {
+      float acc[S][GP];
 #pragma unroll
-      for (int c = 0; c < NP; ++c) acc[s][c] = 0.f;
+      for (int s = 0; s < S; ++s)
 #pragma unroll
-    for (int i = 0; i < NQ; ++i) {
-      const int q = lane + 32 * i;
-      if (q < total) {
+        for (int c = 0; c < GP; ++c) acc[s][c] = 0.f;
 #pragma unroll
-        for (int c = 0; c < NP; ++c) {
-          const float4 w = __ldg(reinterpret_cast<const float4*>(planes + (size_t)c * n_pad) + q);
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        if (q < total) {
 #pragma unroll
-          for (int s = 0; s < S; ++s) {
-            const float4 t = xv[s][i];
-            if (c == NP - 1)
-              acc[s][c] = fmaf(t.x * t.x, w.x, fmaf(t.y * t.y, w.y, fmaf(t.z * t.z, w.z, fmaf(t.w * t.w, w.w, acc[s][c]))));
-            else
-              acc[s][c] = fmaf(t.x, w.x, fmaf(t.y, w.y, fmaf(t.z, w.z, fmaf(t.w, w.w, acc[s][c]))));
+          for (int c = 0; c < GP; ++c) {
+            const int pl = g * GP + c;
+            if (pl < NP) {
+              const float4 w = __ldg(reinterpret_cast<const float4*>(planes + (size_t)pl * n_pad) + q);
+#pragma unroll
+              for (int s = 0; s < S; ++s) {
+                const float4 t = xv[s][i];
+                if (pl == NP - 1)
+                  acc[s][c] = fmaf(t.x * t.x, w.x, fmaf(t.y * t.y, w.y, fmaf(t.z * t.z, w.z, fmaf(t.w * t.w, w.w, acc[s][c]))));
+                else
+                  acc[s][c] = fmaf(t.x, w.x, fmaf(t.y, w.y, fmaf(t.z, w.z, fmaf(t.w, w.w, acc[s][c]))));
+              }
+            }
           }
         }
       }
-    }
-    if (lane < D) {
+      if (lane < D) {
 #pragma unroll
-      for (int c = 0; c < NP; ++c) {
-        const float w = __ldg(planes + (size_t)c * n_pad + emb + lane);
+        for (int c = 0; c < GP; ++c) {
+          const int pl = g * GP + c;
+          if (pl < NP) {
+            const float w = __ldg(planes + (size_t)pl * n_pad + emb + lane);
 #pragma unroll
-        for (int s = 0; s < S; ++s)
-          acc[s][c] = fmaf(c == NP - 1 ? xd[s] * xd[s] : xd[s], w, acc[s][c]);
+            for (int s = 0; s < S; ++s) acc[s][c] = fmaf(pl == NP - 1 ? xd[s] * xd[s] : xd[s], w, acc[s][c]);
+          }
+        }
       }
-    }
-    store_x<NQ, S>(x, x_ld, total, D, b0, B, lane, xv, xd);
-    // cross-lane reduction: value index = s*NPP + c, 32 values per reduce-scatter
-    constexpr int SPR = 32 / NPP;                  // samples per reduction
-#pragma unroll
-    for (int g = 0; g < S; g += SPR) {
       float vals[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        const int s = g + j / NPP, c = j % NPP;
-        vals[j] = (s < S && c < NP) ? acc[s < S ? s : 0][c < NP ? c : 0] : 0.f;
+        const int s = j >> 3, c = j & 7;
+        vals[j] = (s < S && c < GP && g * GP + c < NP) ? acc[s < S ? s : 0][c < GP ? c : 0] : 0.f;
       }
       const float tot = warp_reduce_scatter<32>(vals, lane);
-      const int c = lane % NPP;
-      float term = (c < KFM) ? 0.5f * tot * tot : (c == KFM ? tot : (c == KFM + 1 ? -0.5f * tot : 0.f));
-#pragma unroll
-      for (int o = NPP / 2; o >= 1; o >>= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
-      const int64_t b = b0 + g + lane / NPP;
-      if (c == 0 && (g + lane / NPP) < S && b < B) fm_out[b] = term + bias0;
+      const int pl = g * GP + (lane & 7);
+      if ((lane & 7) < GP) term += (pl < KFM) ? 0.5f * tot * tot : (pl == KFM ? tot : (pl == KFM + 1 ? -0.5f * tot : 0.f));
     }
+    term += __shfl_xor_sync(0xffffffffu, term, 4);
+    term += __shfl_xor_sync(0xffffffffu, term, 2);
+    term += __shfl_xor_sync(0xffffffffu, term, 1);
+    const int s = lane >> 3;
+    if ((lane & 7) == 0 && s < S && b0 + s < B) fm_out[b0 + s] = term + bias0;
   }
 }
 

@@ -177,8 +177,20 @@ class Layer:
             s._bump()
 
     # -- protocol
-    def build(self, input_shape):
-        pass
+    def __init_subclass__(cls, **kw):
+        """Like Keras, calling build() directly marks the layer built (so __call__ does not re-create weights)."""
+        super().__init_subclass__(**kw)
+        if "build" in cls.__dict__:
+            raw = cls.__dict__["build"]
+
+            def build(self, input_shape=None, _raw=raw):
+                _raw(self, input_shape)
+                self.built = True
+            build.__doc__ = raw.__doc__
+            cls.build = build
+
+    def build(self, input_shape=None):
+        self.built = True
 
     def call(self, inputs, *args, **kwargs):
         raise NotImplementedError

@@ -112,6 +112,7 @@ class DenseStack:
         self._packed = {}
         self._ws = None
         self._key = None
+        self.allow_fused = True
 
     def set_layers(self, layers, version):
         if self._key != version:
@@ -142,6 +143,43 @@ class DenseStack:
                 d.packed = ptr(self._packed[i])
         return arr
 
+    def fused_ok(self, arr=None):
+        """Shape fits the single persistent tcgen05 tower kernel (ctrhot_tower_fused_tf32 / _gather_tf32)."""
+        arr = arr if arr is not None else self.descs()
+        n = len(arr)
+        if self.precision != "tf32" or not (2 <= n <= 4) or not self.allow_fused:
+            return False
+        if arr[n - 1].out_dim != 1 or arr[n - 1].act != _lib.ACT_NONE:
+            return False
+        return all(8 <= arr[i].out_dim <= 256 for i in range(n - 1))
+
+    @staticmethod
+    def _post(post):
+        post = post or {}
+        return (ptr(post.get("y_scale")), ptr(post.get("add_vec")), ptr(post.get("add_bias")),
+                float(post.get("scale", 1.0)), int(bool(post.get("sigmoid", False))))
+
+    def run_fused(self, x, x_ld=None, post=None, out=None):
+        """Whole tower (+ optional post) in one kernel; x [M, >=K] fp32, 16-byte aligned rows."""
+        M = x.shape[0]
+        x_ld = x.stride(0) if x_ld is None else x_ld
+        arr = self.descs()
+        if out is None:
+            out = torch.empty((M, 1), dtype=torch.float32, device=x.device)
+        _lib.call("ctrhot_tower_fused_tf32", ptr(x), x_ld, M, arr, len(arr), *self._post(post), ptr(out), stream_ptr())
+        return out
+
+    def run_fused_gather(self, E, ids, kind, ids_ld, dense, B, post=None, err_flag=None, out=None):
+        """Tower fed straight from the embedding arena of EmbedLayer ``E`` (x never exists in HBM)."""
+        arr = self.descs()
+        D = 0 if dense is None else dense.shape[1]
+        if out is None:
+            out = torch.empty((B, 1), dtype=torch.float32, device=E.arena.device)
+        _lib.call("ctrhot_tower_gather_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld,
+                  ptr(dense), 0 if dense is None else dense.stride(0), D, B, arr, len(arr), *self._post(post),
+                  ptr(out), ptr(err_flag), stream_ptr())
+        return out
+
     def run(self, x, x_ld=None, out=None):
         require_cuda(x, "DenseStack")
         M = x.shape[0]
@@ -151,6 +189,8 @@ class DenseStack:
         n_out = arr[n - 1].out_dim
         if out is None:
             out = torch.empty((M, n_out), dtype=torch.float32, device=x.device)
+        if self.fused_ok(arr) and x_ld % 4 == 0 and x.data_ptr() % 16 == 0 and out.stride(0) == 1:
+            return self.run_fused(x, x_ld, None, out)
         need = _lib.query("ctrhot_mlp_workspace_bytes", M, arr, n)
         if self._ws is None or self._ws.numel() * 4 < need or self._ws.device != x.device:
             self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=x.device)

@@ -139,24 +139,39 @@ class DeepFM(_EmbedTowerModel):
         if self.fused and self.dnn.output_dim == 1 and _front_supported(E.k, self.fm.k, E.F, D):
             ids, kind, ids_ld = ids_arg(ids)
             n = D + E.F * E.k
-            x_ld = _pad32(n)
-            x = torch.empty((B, x_ld), dtype=torch.float32, device=self.device)
             fm_out = torch.empty((B,), dtype=torch.float32, device=self.device)
             planes = self.fm.planes(D)
-            self.dnn.stack.set_layers(self._tower_layers(self.dnn, D), (self.dnn._version, D))
+            stack = self.dnn.stack
+            stack.set_layers(self._tower_layers(self.dnn, D), (self.dnn._version, D))
+            one_kernel_tower = stack.fused_ok() and E.F <= 32
+            x, x_ld = None, 0
+            if not one_kernel_tower:
+                x_ld = _pad32(n)
+                x = torch.empty((B, x_ld), dtype=torch.float32, device=self.device)
             ev = None
             if self.events is not None:
                 ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
                 ev[0].record()
+            # K2: gather -> FM in registers (x is written only if the tower cannot gather for itself)
             _lib.call("ctrhot_deepfm_front_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld,
                       ptr(dense), dense.stride(0), D, B, ptr(self.fm.w0), ptr(planes), self.fm.k,
                       ptr(x), x_ld, ptr(fm_out), ptr(self.err_flag()), stream_ptr())
             if ev:
                 ev[1].record()
-            dnn_out = self.dnn.stack.run(x, x_ld)
+            if one_kernel_tower:
+                # K7f: gather -> 3 Dense layers -> Dense(1) -> sigmoid(0.5*(fm+dnn)), one persistent tcgen05 kernel
+                stack.run_fused_gather(E, ids, kind, ids_ld, dense, B,
+                                       {"add_vec": fm_out, "scale": 0.5, "sigmoid": True}, self.err_flag(), out)
+                dnn_out = None
+            else:
+                dnn_out = stack.run(x, x_ld)
             if ev:
                 ev[2].record()
                 self.events.append(tuple(ev))
+            if dnn_out is None:
+                if self.check:
+                    self.check_ids()
+                return out
         else:
             x = E.gather(ids, dense)
             fm_out = self.fm(x)
@@ -275,17 +290,27 @@ class DCN(_EmbedTowerModel):
         out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
         if self.fused and self.dense_layer.output_dim == 1 and _front_supported(E.k, None, E.F, D):
             ids, kind, ids_ld = ids_arg(ids)
-            x_ld = _pad32(n)
             cw, cb, fw = self._packed_cross(D, n)
-            x = torch.empty((B, x_ld), dtype=torch.float32, device=self.device)
+            stack = self.dense_layer.stack
+            stack.set_layers(self._tower_layers(self.dense_layer, D), (self.dense_layer._version, D))
+            one_kernel_tower = stack.fused_ok() and E.F <= 32
+            x, x_ld = None, 0
+            if not one_kernel_tower:
+                x_ld = _pad32(n)
+                x = torch.empty((B, x_ld), dtype=torch.float32, device=self.device)
             cdot = torch.empty((B,), dtype=torch.float32, device=self.device)
+            # K5: gather -> all L cross layers in registers -> dot with the cross half of the final Dense
             _lib.call("ctrhot_dcn_front_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld,
                       ptr(dense), dense.stride(0), D, B, self.cross_layer.layer_num, ptr(cw), ptr(cb), ptr(fw),
                       ptr(x), x_ld, 0, 0, ptr(cdot), ptr(self.err_flag()), stream_ptr())
-            self.dense_layer.stack.set_layers(self._tower_layers(self.dense_layer, D), (self.dense_layer._version, D))
-            dnn_out = self.dense_layer.stack.run(x, x_ld)
-            _lib.call("ctrhot_combine_sigmoid_f32", ptr(cdot), ptr(dnn_out), ptr(self.out_kernel[n:]), ptr(self.out_bias),
-                      1.0, B, ptr(out), stream_ptr())
+            if one_kernel_tower:
+                stack.run_fused_gather(E, ids, kind, ids_ld, dense, B,
+                                       {"y_scale": self.out_kernel[n:], "add_vec": cdot, "add_bias": self.out_bias,
+                                        "scale": 1.0, "sigmoid": True}, self.err_flag(), out)
+            else:
+                dnn_out = stack.run(x, x_ld)
+                _lib.call("ctrhot_combine_sigmoid_f32", ptr(cdot), ptr(dnn_out), ptr(self.out_kernel[n:]),
+                          ptr(self.out_bias), 1.0, B, ptr(out), stream_ptr())
         else:
             x = E.gather(ids, dense)
             cross = self.cross_layer(x)
