@@ -40,13 +40,20 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
-
-    def run(self):
-        try:
+        self.nv = self.h = None
+        try:                          # NVML is brought up BEFORE the timed region so the first sample lands inside it
             import pynvml as nv
             nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            self.nv, self.h = nv, nv.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        except Exception as e:
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def run(self):
+        if self.nv is None:
+            return
+        try:
+            nv, h = self.nv, self.h
             # NVML clocks-event-reason bits
             names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
             while not self.stop_flag:
@@ -58,7 +65,7 @@ class ClockSampler(threading.Thread):
                 for bit, nm in names.items():
                     if r & bit:
                         self.reasons.add(nm)
-                time.sleep(0.02)
+                time.sleep(0.002)
         except Exception as e:       # NVML missing: report that instead of inventing numbers
             self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
 
@@ -156,7 +163,7 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ctrhot", choices=["ctrhot", "reference"])
     ap.add_argument("--batch", type=int, default=65536)
