@@ -165,6 +165,33 @@ int ctrhot_tower_gather_tf32(const float* arena, const int64_t* row_off, int F, 
                              const float* y_scale, const float* add_vec, const float* add_bias,
                              float scale, int apply_sigmoid, float* out, int* err_flag, void* stream);
 
+/* ---- R12/R14 whole-model kernel: gather -> {FM | cross} -> tower -> sigmoid in ONE persistent launch ------
+ * (DeepFM.call, DL/model/deepFM.py:23-31; DCN.call, DL/model/dcn.py:24-34; EmbedLayer -> DNNLayer towers).
+ * Each embedding row is read from HBM once; x = [dense, embed] and the hidden activations never reach HBM.
+ * h_layers = 1..3 hidden Dense (out_dim 8..256, act none/relu/PReLU[out_dim]) + the final Dense(h -> 1).
+ *   h_layers[0].packed = ctrhot_fused_pack(W1 [n, n1], side [n, 16] or NULL): W1 (TF32) plus 16 "side" columns whose
+ *                        products x @ side are formed fp32-accurately on the tensor pipe (split-TF32, three MMAs);
+ *   h_layers[l>0].packed = ctrhot_mlp_pack.
+ * sq_w  [round32(n)] internal column order [embeddings | dense | 0] or NULL:  q = sum_j x_j^2 sq_w[j]   (fp32).
+ * mode 0 (tower):  out = y
+ * mode 1 (DeepFM): side[:, c < n_side] = v[:, c], side[:, n_side] = w1, sq_w[j] = sum_c v[j,c]^2, h_combine = {w0}:
+ *                  out = 0.5 * (w0 + S[n_side] + 0.5 * (sum_c S[c]^2 - q) + y)              (interaction.py:106-114)
+ * mode 2 (DCN):    side[:, l < n_side] = cross w_l, side[:, n_side] = final Dense kernel over the cross half,
+ *                  h_combine = {c_l . w_l (l < n_side), c_L . final_w, wy, bias} with c_l = sum_{i<l} b_i:
+ *                  a = 1; a += a * S[l] + h_combine[l];  out = a * S[L] + h_combine[L] + wy * y + bias
+ *                  (the L cross layers of interaction.py:75-83 collapse to these scalars because x_l = a_l x_0 + c_l)
+ * apply_sigmoid != 0 applies the model's final sigmoid.  h_combine is a HOST array (<= 24 floats).
+ * cluster: 0 = auto, else 1 | 2 | 4 CTAs share each weight chunk through TMA multicast.
+ * CTRHOT_ESHAPE when the tower does not fit (TMEM columns / shared memory / activation kind): use the layered path. */
+int64_t ctrhot_fused_pack_bytes(int n, int n1);
+int ctrhot_fused_pack(const float* W1, const float* side, int n, int n1, int D, void* packed, void* stream);
+int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                          const void* ids, int ids_kind, int64_t ids_ld,
+                          const float* dense, int64_t dense_ld, int D, int64_t M,
+                          const ctrhot_dense_desc* h_layers, int n_layers,
+                          const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                          int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
+
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,
                     const float* var, float eps, float* out, void* stream);

@@ -1,0 +1,693 @@
+// K-fused: the whole CTR forward for embedding + dense-interaction + tower models in ONE persistent kernel
+// (DeepFM, DL/model/deepFM.py:23-31; DCN, DL/model/dcn.py:24-34; plain EmbedLayer -> DNNLayer towers).
+//
+//   rows      x_m = [ Embed(ids_m) | dense_m ]            gathered ONCE from the tables, never written to HBM
+//   tower     y_m = w_out . act_L( ... act_1(x_m W_1 + b_1) ... ) + b_out        tcgen05 kind::tf32, fp32 accumulate
+//   side      S_m = x_m @ side[:, 0:16]                    fp32-accurate on the tensor pipe by a split-TF32 product:
+//                   x = x_hi + x_lo,  side = s_hi + s_lo,  S = x_hi s_hi + x_hi s_lo + x_lo s_hi   (error ~2^-21 |x||s|)
+//             q_m = sum_j x_mj^2 sq_w[j]                   CUDA cores (fp32)
+//   combine   DeepFM: sigmoid(0.5 * (w0 + S[kfm] + 0.5 * (sum_c S[c]^2 - q) + y))     (FMLayer, interaction.py:106-114)
+//             DCN   : the L cross layers collapse to scalars: x_l = a_l x_0 + c_l with a_0 = 1, c_l = sum_{i<l} b_i,
+//                     d_l = a_l (x_0 . w_l) + c_l . w_l,  a_{l+1} = a_l + d_l     (CrossLayer, interaction.py:75-83)
+//                     so side = [w_0 .. w_{L-1}, final_w] and  out = sigmoid(a_L S[L] + c_L.final_w + wy * y + bias)
+//
+// One CTA per SM (persistent over 128-row tiles), 18 warps:
+//   warps 0-7   epilogue: tcgen05.ld the accumulator -> bias + activation -> TF32 -> tcgen05.st back IN PLACE as the next
+//               layer's A operand (hidden activations never leave TMEM); the last layer's epilogue does the final
+//               Dense(h -> 1) dot, the combine and writes 4 bytes per row.  Warp w owns TMEM lanes 32*(w%4).., column half w/4.
+//   warps 8-11  gather: 16-byte cp.async (LDGSTS) straight from the embedding rows into the 128B-swizzled K-major A stage.
+//   warps 12-15 splitter: one thread per tile row; reads its row of the stage, writes x_lo = x - trunc_tf32(x) into the
+//               "lo" tile and accumulates q_m.
+//   warp 16     TMEM owner + MMA issuer (one lane).  Per 32-column K chunk: D1 += x_hi W1 (N = N1), DS += x_hi [s_hi | s_lo]
+//               (N = 32), DS[0:16] += x_lo s_hi (N = 16); layers >= 2 read A from TMEM (TS form).
+//   warp 17     W producer: one cp.async.bulk (TMA engine) per K chunk of the pre-swizzled weights, multicast to the
+//               CLUSTER so one L2 read feeds C SMs.
+// TMEM columns: D1/H1 at 0, DS (32) next, D2/H2, D3.  HBM traffic = ids + dense + each needed row once + 4 B out.
+#include "common.cuh"
+#include "tc05.cuh"
+#include "mlp.cuh"
+
+namespace ctrhot {
+using namespace tc;
+
+constexpr int FU_BM = 128;
+constexpr int FU_NA = 3;                    // A ring: raw (16 KB) + lo (16 KB) per stage
+constexpr int FU_NB = 3;                    // W ring
+constexpr int FU_PA = 2;                    // cp.async groups in flight per gather thread (<= FU_NA - 1)
+constexpr int FU_TILE_BYTES = FU_BM * 128;  // 16 KB
+constexpr int FU_A_STAGE = 2 * FU_TILE_BYTES;
+constexpr int FU_MAXL = 3;
+constexpr int FU_THREADS = 18 * 32;
+constexpr int FU_SIDE = 16;                 // side columns
+constexpr int FU_NCB = 24;                  // combine constants
+
+enum { FU_MODE_TOWER = 0, FU_MODE_DEEPFM = 1, FU_MODE_DCN = 2 };
+
+struct FuLayer {
+  const float* Wp; const float* bias; const float* alpha;   // alpha: PReLU [N] or NULL
+  int N, KC, BN, KP, col, act;                              // KP = N rounded up to 32 (= K extent of the next layer)
+};
+
+struct FuParams {
+  const float* arena; const int64_t* row_off; int F; int k4; const void* ids; int ids_kind; int64_t ids_ld;
+  const float* dense; int64_t dense_ld; int D; int emb;
+  int64_t M; int n_tiles; int n_super;
+  FuLayer L[FU_MAXL];
+  const float* w_out; const float* b_out;
+  const float* sq_w;                                       // [KC1*32] internal order or NULL
+  int mode; int n_side; float cb[FU_NCB];
+  int apply_sigmoid;
+  int ds_col;                                              // TMEM column of the side accumulator
+  float* out; int* err_flag;
+  uint32_t b_stage_bytes;
+};
+
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+      "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      :: "r"(taddr),
+         "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+         "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+         "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+         "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15])),
+         "r"(__float_as_uint(v[16])), "r"(__float_as_uint(v[17])), "r"(__float_as_uint(v[18])), "r"(__float_as_uint(v[19])),
+         "r"(__float_as_uint(v[20])), "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
+         "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])), "r"(__float_as_uint(v[27])),
+         "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])), "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+      : "memory");
+}
+
+// arrive on the same mbarrier offset in every CTA of `mask` when the issuing thread's prior MMAs complete
+__device__ __forceinline__ void mma_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               :: "r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_mc(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar, uint16_t mask) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+               :: "r"(dst_smem), "l"(src), "r"(bytes), "r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ uint32_t cluster_id_x() {
+  uint32_t r; asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctaid_x() {
+  uint32_t r; asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const float4& v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
+constexpr int FU_NR = 4;                    // raw-row ring (gather depth)
+constexpr int FU_NLO = 2;                   // lo-tile ring
+constexpr int FU_PG = 3;                    // cp.async groups in flight per gather thread (<= FU_NR - 1)
+
+// float-region layout (shared by host sizing and device carving); all offsets in floats, 16-byte aligned
+struct FuSmemMap {
+  int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, total;
+};
+__host__ __device__ inline FuSmemMap fu_smem_map(int F, int KC1, const int* KP, int nl) {
+  FuSmemMap m;
+  int o = 0;
+  m.rowoff = o; o += ((F + 1) * 2 + 3) / 4 * 4;
+  m.sq = o; o += KC1 * 32;
+  for (int l = 0; l < FU_MAXL; ++l) {
+    m.bias[l] = o; if (l < nl) o += KP[l];
+    m.alpha[l] = o; if (l < nl) o += KP[l];
+  }
+  m.wout = o; o += KP[nl - 1];
+  m.q = o; o += 2 * FU_BM;
+  m.part = o; o += 2 * FU_BM;
+  m.total = o;
+  return m;
+}
+
+__device__ __forceinline__ float fu_act(float t, float a) { return fmaxf(t, 0.f) + a * fminf(t, 0.f); }
+
+// one 32-column chunk of a hidden layer's epilogue: acc -> act(acc + b) -> tf32 -> back to TMEM in place
+__device__ __forceinline__ void fu_hidden_chunk(uint32_t taddr, const float* sb, const float* sa, int c0, int N) {
+  float acc[32];
+  tmem_ld32(taddr, acc);
+  if (c0 + 32 <= N) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
+      const float4 a = *reinterpret_cast<const float4*>(sa + c0 + j);
+      acc[j + 0] = to_tf32_rna(fu_act(acc[j + 0] + b.x, a.x));
+      acc[j + 1] = to_tf32_rna(fu_act(acc[j + 1] + b.y, a.y));
+      acc[j + 2] = to_tf32_rna(fu_act(acc[j + 2] + b.z, a.z));
+      acc[j + 3] = to_tf32_rna(fu_act(acc[j + 3] + b.w, a.w));
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      acc[j] = (c0 + j < N) ? to_tf32_rna(fu_act(acc[j] + sb[c0 + j], sa[c0 + j])) : 0.f;
+  }
+  tmem_st32(taddr, acc);
+}
+
+// one 32-column chunk of the LAST hidden layer: returns sum_n act(acc + b)[n] * w_out[n]
+__device__ __forceinline__ float fu_last_chunk(uint32_t taddr, const float* sb, const float* sa, const float* sw,
+                                               int c0, int N) {
+  float acc[32];
+  tmem_ld32(taddr, acc);
+  float d0 = 0.f, d1 = 0.f;
+  if (c0 + 32 <= N) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
+      const float4 a = *reinterpret_cast<const float4*>(sa + c0 + j);
+      const float4 w = *reinterpret_cast<const float4*>(sw + c0 + j);
+      d0 = fmaf(fu_act(acc[j + 0] + b.x, a.x), w.x, d0);
+      d1 = fmaf(fu_act(acc[j + 1] + b.y, a.y), w.y, d1);
+      d0 = fmaf(fu_act(acc[j + 2] + b.z, a.z), w.z, d0);
+      d1 = fmaf(fu_act(acc[j + 3] + b.w, a.w), w.w, d1);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (c0 + j < N) d0 = fmaf(fu_act(acc[j] + sb[c0 + j], sa[c0 + j]), sw[c0 + j], d0);
+  }
+  return d0 + d1;
+}
+
+#ifndef FU_MASK_HI
+#define FU_MASK_HI 1      // splitter rewrites the raw tile with trunc_tf32(x): the split is exact whatever the MMA's own rounding
+#endif
+
+template <int NL, int C>
+__global__ void __launch_bounds__(FU_THREADS, 1)
+ctr_fused_kernel(const __grid_constant__ FuParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t base = (raw_addr + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - raw_addr);
+  const uint32_t r_base = base;                                         // FU_NR raw tiles
+  const uint32_t lo_base = r_base + FU_NR * FU_TILE_BYTES;              // FU_NLO lo tiles
+  const uint32_t b_base = lo_base + FU_NLO * FU_TILE_BYTES;             // FU_NB weight stages
+  const uint32_t f_base = b_base + FU_NB * p.b_stage_bytes;             // float region
+  int KP[FU_MAXL];
+#pragma unroll
+  for (int l = 0; l < FU_MAXL; ++l) KP[l] = (l < NL) ? p.L[l].KP : 0;
+  const int KC1 = p.L[0].KC;
+  const FuSmemMap mp = fu_smem_map(p.F, KC1, KP, NL);
+  float* fptr = reinterpret_cast<float*>(base_ptr + (f_base - base));
+  const uint32_t bars = f_base + (uint32_t)mp.total * 4u;
+  // barrier map
+  auto full_raw = [&](int s) { return bars + 8u * s; };
+  auto empty_raw = [&](int s) { return bars + 8u * (FU_NR + s); };
+  auto full_lo = [&](int s) { return bars + 8u * (2 * FU_NR + s); };
+  auto empty_lo = [&](int s) { return bars + 8u * (2 * FU_NR + FU_NLO + s); };
+  auto full_b = [&](int s) { return bars + 8u * (2 * FU_NR + 2 * FU_NLO + s); };
+  auto empty_b = [&](int s) { return bars + 8u * (2 * FU_NR + 2 * FU_NLO + FU_NB + s); };
+  const uint32_t misc = bars + 8u * (2 * FU_NR + 2 * FU_NLO + 2 * FU_NB);
+  auto d_full = [&](int l) { return misc + 8u * l; };
+  auto h_ready = [&](int l) { return misc + 8u * (FU_MAXL + l); };
+  const uint32_t last_free = misc + 8u * (2 * FU_MAXL);
+  const uint32_t slot_addr = last_free + 8u;
+  volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (slot_addr - base));
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t crank = (C > 1) ? cluster_ctarank() : 0u;
+  const uint32_t cid = (C > 1) ? cluster_id_x() : blockIdx.x;
+  const uint32_t ncl = (C > 1) ? cluster_nctaid_x() : gridDim.x;
+  const uint16_t cmask = (uint16_t)((1u << C) - 1u);
+
+  if (tid == 0) {
+    for (int s = 0; s < FU_NR; ++s) { mbar_init(full_raw(s), 128); mbar_init(empty_raw(s), 1); }
+    for (int s = 0; s < FU_NLO; ++s) { mbar_init(full_lo(s), 128); mbar_init(empty_lo(s), 1); }
+    for (int s = 0; s < FU_NB; ++s) { mbar_init(full_b(s), 1); mbar_init(empty_b(s), C); }
+    for (int l = 0; l < FU_MAXL; ++l) { mbar_init(d_full(l), 1); mbar_init(h_ready(l), 256); }
+    mbar_init(last_free, 256);
+    mbar_fence_init();
+  }
+  // stage the small per-column vectors
+  {
+    int64_t* s_ro = reinterpret_cast<int64_t*>(fptr + mp.rowoff);
+    for (int i = tid; i <= p.F; i += FU_THREADS) s_ro[i] = p.row_off[i];
+    for (int i = tid; i < KC1 * 32; i += FU_THREADS) fptr[mp.sq + i] = p.sq_w ? __ldg(p.sq_w + i) : 0.f;
+#pragma unroll
+    for (int l = 0; l < NL; ++l) {
+      const FuLayer& L = p.L[l];
+      for (int i = tid; i < L.KP; i += FU_THREADS) {
+        fptr[mp.bias[l] + i] = (i < L.N && L.bias) ? __ldg(L.bias + i) : 0.f;
+        float a = 0.f;
+        if (i < L.N) a = (L.act == CTRHOT_ACT_NONE) ? 1.f : (L.act == CTRHOT_ACT_PRELU ? __ldg(L.alpha + i) : 0.f);
+        fptr[mp.alpha[l] + i] = a;
+      }
+    }
+    const FuLayer& LL = p.L[NL - 1];
+    for (int i = tid; i < LL.KP; i += FU_THREADS) fptr[mp.wout + i] = (i < LL.N) ? __ldg(p.w_out + i) : 0.f;
+  }
+  if (warp == 16) { tmem_alloc(slot_addr, 512u); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  if (C > 1) cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *slot_ptr;
+  const int n_my = ((int)cid < p.n_super) ? (p.n_super - (int)cid + (int)ncl - 1) / (int)ncl : 0;
+
+  if (warp >= 8 && warp < 12) {
+    // ================================================================ gather (cp.async)
+    const int tg = tid - 256;
+    const int c = tg & 7;                    // 16-byte piece of the 128-byte stage row: the same for all of this thread's copies
+    const int rsub = tg >> 3;                // rows rsub + 16 i
+    const int64_t* s_ro = reinterpret_cast<const int64_t*>(fptr + mp.rowoff);
+    constexpr int32_t NOROW = INT32_MIN;
+    auto ids_for = [&](int64_t row0, int kc, int32_t (&reg)[8]) {
+      const int col = kc * 32 + c * 4;
+      if (col >= p.emb) return;
+      const int f = (col >> 2) / p.k4;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int64_t gm = row0 + rsub + 16 * i;
+        int32_t v = NOROW;
+        if (gm < p.M) {
+          v = (p.ids_kind == CTRHOT_IDS_I32)
+                  ? __ldg(static_cast<const int32_t*>(p.ids) + gm * p.ids_ld + f)
+                  : __float2int_rz(__ldg(static_cast<const float*>(p.ids) + gm * p.ids_ld + f));
+          if (v == NOROW) v = -1;
+        }
+        reg[i] = v;
+      }
+    };
+    int32_t idc[8], idn[8];
+    uint32_t it = 0, signalled = 0;
+    if (n_my > 0) ids_for(((int64_t)cid * C + crank) * FU_BM, 0, idc);
+    for (int lt = 0; lt < n_my; ++lt) {
+      const int64_t row0 = (((int64_t)cid + (int64_t)lt * ncl) * C + crank) * FU_BM;
+      const int64_t row0n = (((int64_t)cid + (int64_t)(lt + 1) * ncl) * C + crank) * FU_BM;
+      for (int kc = 0; kc < KC1; ++kc, ++it) {
+        if (kc + 1 < KC1) ids_for(row0, kc + 1, idn);
+        else if (lt + 1 < n_my) ids_for(row0n, 0, idn);
+        const int s = it % FU_NR;
+        mbar_wait(empty_raw(s), ((it / FU_NR) & 1u) ^ 1u);
+        const uint32_t stage = r_base + s * FU_TILE_BYTES;
+        const int col = kc * 32 + c * 4;
+        if (col < p.emb) {
+          const int q = col >> 2;
+          const int f = q / p.k4, part = q - f * p.k4;
+          const int64_t r0 = s_ro[f], nrow = s_ro[f + 1] - r0;
+          const float* fbase = p.arena + (r0 * p.k4 + part) * 4;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int smp = rsub + 16 * i;
+            const int32_t id = idc[i];
+            const bool ok = id >= 0 && id < nrow;
+            if (!ok && id != NOROW && p.err_flag) *p.err_flag = 1;
+            cp_async16(stage + sw128_offset((uint32_t)smp, (uint32_t)c),
+                       ok ? (const void*)(fbase + (int64_t)id * (p.k4 * 4)) : (const void*)p.arena, ok ? 16u : 0u);
+          }
+        } else {                                       // dense tail [emb, emb + D) then zero padding
+          const int j = col - p.emb;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int smp = rsub + 16 * i;
+            const int64_t gm = row0 + smp;
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gm < p.M && j < p.D) {
+              const float* src = p.dense + gm * p.dense_ld;
+              t.x = __ldg(src + j);
+              if (j + 1 < p.D) t.y = __ldg(src + j + 1);
+              if (j + 2 < p.D) t.z = __ldg(src + j + 2);
+              if (j + 3 < p.D) t.w = __ldg(src + j + 3);
+            }
+            sts128(stage + sw128_offset((uint32_t)smp, (uint32_t)c), t);
+          }
+        }
+        cp_async_commit();
+        if (it + 1 - signalled >= (uint32_t)FU_PG) {
+          cp_async_wait<FU_PG - 1>();
+          fence_proxy_async_smem();
+          mbar_arrive(full_raw(signalled % FU_NR));
+          ++signalled;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) idc[i] = idn[i];
+      }
+    }
+    cp_async_wait<0>();
+    fence_proxy_async_smem();
+    while (signalled < it) { mbar_arrive(full_raw(signalled % FU_NR)); ++signalled; }
+  } else if (warp >= 12 && warp < 16) {
+    // ================================================================ splitter: x_lo tile + q = sum x^2 sq_w
+    const int row = tid - 384;
+    uint32_t it = 0;
+    for (int lt = 0; lt < n_my; ++lt) {
+      float q = 0.f;
+      for (int kc = 0; kc < KC1; ++kc, ++it) {
+        const int sr = it % FU_NR, sl = it % FU_NLO;
+        mbar_wait(full_raw(sr), (it / FU_NR) & 1u);
+        mbar_wait(empty_lo(sl), ((it / FU_NLO) & 1u) ^ 1u);
+        const uint32_t raw = r_base + sr * FU_TILE_BYTES, lo = lo_base + sl * FU_TILE_BYTES;
+        const float* sq = fptr + mp.sq + kc * 32;
+#pragma unroll
+        for (int cc = 0; cc < 8; ++cc) {
+          const uint32_t off = sw128_offset((uint32_t)row, (uint32_t)cc);
+          const float4 x = lds128(raw + off);
+          const float4 w = *reinterpret_cast<const float4*>(sq + cc * 4);
+          float4 hi, l;
+          hi.x = trunc_tf32(x.x); hi.y = trunc_tf32(x.y); hi.z = trunc_tf32(x.z); hi.w = trunc_tf32(x.w);
+          l.x = x.x - hi.x; l.y = x.y - hi.y; l.z = x.z - hi.z; l.w = x.w - hi.w;
+          q = fmaf(x.x * x.x, w.x, q); q = fmaf(x.y * x.y, w.y, q);
+          q = fmaf(x.z * x.z, w.z, q); q = fmaf(x.w * x.w, w.w, q);
+          sts128(lo + off, l);
+          if (FU_MASK_HI) sts128(raw + off, hi);
+        }
+        if (kc == KC1 - 1) fptr[mp.q + (lt & 1) * FU_BM + row] = q;
+        fence_proxy_async_smem();
+        mbar_arrive(full_lo(sl));
+      }
+    }
+  } else if (warp == 16) {
+    // ================================================================ MMA issuer
+    if (lane == 0) {
+      uint32_t ia = 0, ib = 0;
+      uint32_t hcount[FU_MAXL] = {0, 0, 0};
+      const uint32_t ds_t = tmem_base + (uint32_t)p.ds_col;
+      for (int lt = 0; lt < n_my; ++lt) {
+        {
+          const FuLayer& L = p.L[0];
+          const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BN);
+          const uint32_t idesc32 = make_idesc_tf32(FU_BM, 32u), idesc16 = make_idesc_tf32(FU_BM, 16u);
+          const uint32_t d_t = tmem_base + (uint32_t)L.col;
+          if (NL == 1 && lt > 0) { mbar_wait(last_free, (uint32_t)(lt - 1) & 1u); tc_fence_after(); }
+          for (int kc = 0; kc < L.KC; ++kc, ++ia, ++ib) {
+            const int sr = ia % FU_NR, sl = ia % FU_NLO, sb = ib % FU_NB;
+            mbar_wait(full_b(sb), (ib / FU_NB) & 1u);
+            if (!FU_MASK_HI) mbar_wait(full_raw(sr), (ia / FU_NR) & 1u);
+            else mbar_wait(full_lo(sl), (ia / FU_NLO) & 1u);
+            tc_fence_after();
+            const uint64_t da = make_desc_sw128(r_base + sr * FU_TILE_BYTES);
+            const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
+            const uint64_t ds = make_desc_sw128(b_base + sb * p.b_stage_bytes + (uint32_t)L.BN * 128u);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              mma_tf32_ss(d_t, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
+              mma_tf32_ss(ds_t, da + (uint64_t)(2 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
+            }
+            if (!FU_MASK_HI) { mbar_wait(full_lo(sl), (ia / FU_NLO) & 1u); tc_fence_after(); }
+            const uint64_t dl = make_desc_sw128(lo_base + sl * FU_TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              mma_tf32_ss(ds_t, dl + (uint64_t)(2 * k), ds + (uint64_t)(2 * k), idesc16, 1u);
+            mma_commit(empty_raw(sr));
+            mma_commit(empty_lo(sl));
+            if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
+          }
+          mma_commit(d_full(0));
+        }
+#pragma unroll
+        for (int l = 1; l < NL; ++l) {
+          const FuLayer& L = p.L[l];
+          const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BN);
+          const uint32_t d_t = tmem_base + (uint32_t)L.col;
+          const uint32_t a_t = tmem_base + (uint32_t)p.L[l - 1].col;
+          mbar_wait(h_ready(l - 1), hcount[l - 1] & 1u); ++hcount[l - 1];
+          if (l == NL - 1 && lt > 0) mbar_wait(last_free, (uint32_t)(lt - 1) & 1u);
+          tc_fence_after();
+          for (int kc = 0; kc < L.KC; ++kc, ++ib) {
+            const int sb = ib % FU_NB;
+            mbar_wait(full_b(sb), (ib / FU_NB) & 1u);
+            tc_fence_after();
+            const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              mma_tf32_ts(d_t, a_t + (uint32_t)(kc * 32 + k * 8), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
+            if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
+          }
+          mma_commit(d_full(l));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 17) {
+    // ================================================================ W producer (bulk async copies, cluster multicast)
+    if (lane == 0) {
+      uint32_t ib = 0;
+      for (int lt = 0; lt < n_my; ++lt) {
+#pragma unroll
+        for (int l = 0; l < NL; ++l) {
+          const FuLayer& L = p.L[l];
+          const uint32_t bytes = (uint32_t)(L.BN + (l == 0 ? 2 * FU_SIDE : 0)) * 128u;
+          const uint32_t piece = bytes / C;
+          for (int kc = 0; kc < L.KC; ++kc, ++ib) {
+            const int sb = ib % FU_NB;
+            mbar_wait(empty_b(sb), ((ib / FU_NB) & 1u) ^ 1u);
+            mbar_arrive_expect_tx(full_b(sb), bytes);
+            const uint8_t* src = reinterpret_cast<const uint8_t*>(L.Wp) + (size_t)kc * bytes + (size_t)crank * piece;
+            const uint32_t dst = b_base + sb * p.b_stage_bytes + crank * piece;
+            if (C > 1) bulk_g2s_mc(dst, src, piece, full_b(sb), cmask);
+            else bulk_g2s(dst, src, bytes, full_b(sb));
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ================================================================ epilogue (warps 0-7)
+    const int q4 = warp & 3, half = warp >> 2;
+    const int row = q4 * 32 + lane;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
+    uint32_t dcount[FU_MAXL] = {0, 0, 0};
+    for (int lt = 0; lt < n_my; ++lt) {
+      const int64_t gm = (((int64_t)cid + (int64_t)lt * ncl) * C + crank) * FU_BM + row;
+      float side = 0.f;
+#pragma unroll
+      for (int l = 0; l < NL; ++l) {
+        const FuLayer& L = p.L[l];
+        mbar_wait(d_full(l), dcount[l] & 1u); ++dcount[l];
+        tc_fence_after();
+        if (l == 0 && half == 0 && p.mode != FU_MODE_TOWER) {
+          float S[32];
+          tmem_ld32(t_lane + (uint32_t)p.ds_col, S);
+#pragma unroll
+          for (int j = 0; j < FU_SIDE; ++j) S[j] += S[FU_SIDE + j];
+          if (p.mode == FU_MODE_DEEPFM) {
+            float sq = 0.f, lin = 0.f;
+#pragma unroll
+            for (int j = 0; j < FU_SIDE; ++j) {
+              if (j < p.n_side) sq = fmaf(S[j], S[j], sq);
+              else if (j == p.n_side) lin = S[j];
+            }
+            side = p.cb[0] + lin + 0.5f * (sq - fptr[mp.q + (lt & 1) * FU_BM + row]);
+          } else {
+            float a = 1.f, fin = 0.f;
+#pragma unroll
+            for (int j = 0; j < FU_SIDE; ++j) {
+              if (j < p.n_side) a += fmaf(a, S[j], p.cb[j]);
+              else if (j == p.n_side) fin = S[j];
+            }
+            side = fmaf(a, fin, p.cb[p.n_side]);
+          }
+        }
+        const float* sb = fptr + mp.bias[l];
+        const float* sa = fptr + mp.alpha[l];
+        if (l < NL - 1) {
+          for (int c0 = half * 32; c0 < L.KP; c0 += 64)
+            fu_hidden_chunk(t_lane + (uint32_t)(L.col + c0), sb, sa, c0, L.N);
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(h_ready(l));
+        } else {
+          float dot = 0.f;
+          for (int c0 = half * 32; c0 < L.KP; c0 += 64)
+            dot += fu_last_chunk(t_lane + (uint32_t)(L.col + c0), sb, sa, fptr + mp.wout, c0, L.N);
+          tc_fence_before();
+          mbar_arrive(last_free);
+          float* part = fptr + mp.part + (lt & 1) * FU_BM;
+          if (half == 1) part[row] = dot;
+          named_bar_sync(1 + q4, 64);
+          if (half == 0 && gm < p.M) {
+            const float y = dot + part[row] + (p.b_out ? __ldg(p.b_out) : 0.f);
+            float r;
+            if (p.mode == FU_MODE_DEEPFM) r = 0.5f * (side + y);
+            else if (p.mode == FU_MODE_DCN) r = side + fmaf(y, p.cb[p.n_side + 1], p.cb[p.n_side + 2]);
+            else r = y;
+            p.out[gm] = p.apply_sigmoid ? 1.0f / (1.0f + __expf(-r)) : r;
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (C > 1) cluster_sync_all();
+  if (warp == 16) { tc_fence_after(); tmem_dealloc(tmem_base, 512u); }
+}
+
+// ---------------------------------------------------------------- first-layer pack: [KC1][(BN1 + 32) rows][32 cols]
+// rows [0, BN1)        = W1[:, n]          (tf32, round to nearest)
+// rows [BN1, BN1+16)   = trunc_tf32(side[:, c])             "s_hi"
+// rows [BN1+16, BN1+32)= side[:, c] - s_hi                  "s_lo"   (the MMA keeps its leading 11 bits)
+// Columns are the INTERNAL order [embeddings | dense D | zero pad]; W1 / side arrive in the reference order
+// [dense D | embeddings] (deepFM.py:26, dcn.py:27).  Each 32-column chunk is stored 128B-swizzled, K-major.
+__global__ void fused_pack_kernel(const float* __restrict__ W1, const float* __restrict__ side, int n, int N1, int D,
+                                  int KC1, int BN1, float* __restrict__ Wp) {
+  const int rows = BN1 + 2 * FU_SIDE;
+  const int64_t total = (int64_t)KC1 * rows * 32;
+  const int emb = n - D;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int kk = (int)(i % 32);
+    const int r = (int)((i / 32) % rows);
+    const int kc = (int)(i / ((int64_t)32 * rows));
+    const int j = kc * 32 + kk;                                  // internal column
+    float v = 0.f;
+    if (j < n) {
+      const int jr = (j < emb) ? (D + j) : (j - emb);            // reference column
+      if (r < BN1) {
+        if (r < N1) v = to_tf32_rna(W1[(size_t)jr * N1 + r]);
+      } else if (side != nullptr) {
+        const int c = (r - BN1) % FU_SIDE;
+        const float s = side[(size_t)jr * FU_SIDE + c];
+        const float hi = __uint_as_float(__float_as_uint(s) & 0xFFFFE000u);
+        v = (r - BN1 < FU_SIDE) ? hi : (s - hi);
+      }
+    }
+    Wp[(size_t)kc * rows * 32 + (sw128_offset((uint32_t)r, (uint32_t)(kk >> 2)) >> 2) + (kk & 3)] = v;
+  }
+}
+
+}  // namespace ctrhot
+
+using namespace ctrhot;
+
+static inline int fu_round(int v, int m) { return (v + m - 1) / m * m; }
+
+extern "C" int64_t ctrhot_fused_pack_bytes(int n, int n1) {
+  if (n <= 0 || n1 <= 0 || n1 > 256) return CTRHOT_EARG;
+  const int KC1 = (n + 31) / 32, BN1 = fu_round(n1, 16);
+  return (int64_t)KC1 * (BN1 + 2 * FU_SIDE) * 32 * sizeof(float);
+}
+
+extern "C" int ctrhot_fused_pack(const float* W1, const float* side, int n, int n1, int D, void* packed, void* stream) {
+  if (!W1 || !packed || n <= 0 || n1 <= 0 || n1 > 256 || D < 0 || D > n || !aligned16(packed)) return CTRHOT_EARG;
+  const int KC1 = (n + 31) / 32, BN1 = fu_round(n1, 16);
+  const int64_t total = (int64_t)KC1 * (BN1 + 2 * FU_SIDE) * 32;
+  int64_t grid = (total + 255) / 256;
+  if (grid > kNumSMs * 16) grid = kNumSMs * 16;
+  fused_pack_kernel<<<(int)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(W1, side, n, n1, D, KC1, BN1,
+                                                                             static_cast<float*>(packed));
+  CTRHOT_LAUNCH_OK("ctrhot_fused_pack");
+  return CTRHOT_OK;
+}
+
+namespace {
+template <int NL, int C>
+int fu_launch(const FuParams& p0, size_t smem, cudaStream_t st) {
+  FuParams p = p0;
+  auto kern = ctr_fused_kernel<NL, C>;
+  CTRHOT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "ctr_fused attr");
+  p.n_super = (p.n_tiles + C - 1) / C;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(FU_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int max_clusters = kNumSMs / C;
+  if (C > 1) {
+    cfg.gridDim = dim3(kNumSMs / C * C);
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0) max_clusters = n;
+    else (void)cudaGetLastError();
+  }
+  const int n_clusters = p.n_super < max_clusters ? p.n_super : max_clusters;
+  cfg.gridDim = dim3(n_clusters * C);
+  CTRHOT_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, p), "ctrhot_ctr_fused_tf32 launch");
+  return CTRHOT_OK;
+}
+
+template <int C>
+int fu_launch_nl(const FuParams& p, int nl, size_t smem, cudaStream_t st) {
+  switch (nl) {
+    case 1: return fu_launch<1, C>(p, smem, st);
+    case 2: return fu_launch<2, C>(p, smem, st);
+    default: return fu_launch<3, C>(p, smem, st);
+  }
+}
+}  // namespace
+
+extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                     const void* ids, int ids_kind, int64_t ids_ld,
+                                     const float* dense, int64_t dense_ld, int D, int64_t M,
+                                     const ctrhot_dense_desc* h_layers, int n_layers,
+                                     const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                                     int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  if (!arena || !row_off || !ids || !out || !h_layers || F <= 0 || k <= 0 || M < 0 || D < 0) return CTRHOT_EARG;
+  if (D > 0 && !dense) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (mode < FU_MODE_TOWER || mode > FU_MODE_DCN || n_side < 0 || n_side >= FU_SIDE) return CTRHOT_EARG;
+  if (n_combine < 0 || n_combine > FU_NCB || (n_combine > 0 && !h_combine)) return CTRHOT_EARG;
+  if (mode == FU_MODE_DEEPFM && n_combine < 1) return CTRHOT_EARG;
+  if (mode == FU_MODE_DCN && n_combine < n_side + 3) return CTRHOT_EARG;
+  if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4) return CTRHOT_EARG;
+  if (k % 4 != 0 || !aligned16(arena) || F > 63) return CTRHOT_ESHAPE;
+  if (n_layers < 2 || n_layers > FU_MAXL + 1) return CTRHOT_ESHAPE;
+  const ctrhot_dense_desc& o = h_layers[n_layers - 1];
+  if (o.out_dim != 1 || o.act != CTRHOT_ACT_NONE || !o.weight) return CTRHOT_ESHAPE;
+  FuParams p{};
+  const int nl = n_layers - 1;
+  const int n = D + F * k;
+  int KP[FU_MAXL] = {0, 0, 0};
+  int col = 0;
+  uint32_t bmax = 0;
+  for (int l = 0; l < nl; ++l) {
+    const ctrhot_dense_desc& d = h_layers[l];
+    if (!d.weight || !d.packed || !aligned16(d.packed) || d.in_dim <= 0 || d.out_dim <= 0) return CTRHOT_EARG;
+    if (d.out_dim > 256 || d.out_dim < 8) return CTRHOT_ESHAPE;
+    if (l == 0 ? d.in_dim != n : d.in_dim != h_layers[l - 1].out_dim) return CTRHOT_EARG;
+    if (d.act == CTRHOT_ACT_PRELU) {
+      if (!d.act_param) return CTRHOT_EARG;
+      if (d.alpha_rows > 1) return CTRHOT_ESHAPE;
+    } else if (d.act != CTRHOT_ACT_NONE && d.act != CTRHOT_ACT_RELU) {
+      return CTRHOT_ESHAPE;
+    }
+    FuLayer& L = p.L[l];
+    L.Wp = static_cast<const float*>(d.packed); L.bias = d.bias; L.alpha = d.act_param; L.act = d.act;
+    L.N = d.out_dim; L.KC = (d.in_dim + 31) / 32; L.BN = fu_round(d.out_dim, 16); L.KP = fu_round(d.out_dim, 32);
+    L.col = col;
+    col += L.KP;
+    if (l == 0) { p.ds_col = col; col += 2 * FU_SIDE; }
+    KP[l] = L.KP;
+    const uint32_t b = (uint32_t)(L.BN + (l == 0 ? 2 * FU_SIDE : 0)) * 128u;
+    if (b > bmax) bmax = b;
+  }
+  if (col > 512) return CTRHOT_ESHAPE;
+  if (o.in_dim != h_layers[nl - 1].out_dim) return CTRHOT_EARG;
+  if (M == 0) return CTRHOT_OK;
+  p.arena = arena; p.row_off = row_off; p.F = F; p.k4 = k / 4; p.ids = ids; p.ids_kind = ids_kind; p.ids_ld = ids_ld;
+  p.dense = dense; p.dense_ld = dense_ld; p.D = D; p.emb = F * k;
+  p.M = M; p.n_tiles = (int)((M + FU_BM - 1) / FU_BM);
+  p.w_out = o.weight; p.b_out = o.bias; p.sq_w = sq_w;
+  p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid;
+  for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
+  p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
+  const FuSmemMap mp = fu_smem_map(F, p.L[0].KC, KP, nl);
+  const size_t n_bars = 2 * FU_NR + 2 * FU_NLO + 2 * FU_NB + 2 * FU_MAXL + 1;
+  const size_t smem = 1024 + (size_t)(FU_NR + FU_NLO) * FU_TILE_BYTES + (size_t)FU_NB * bmax + (size_t)mp.total * 4 +
+                      8 * n_bars + 16;
+  if (smem > 227 * 1024) return CTRHOT_ESHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int C = cluster;
+  if (C == 0) C = (p.n_tiles >= 4 * 32) ? 4 : (p.n_tiles >= 2 ? 2 : 1);
+  // every multicast piece must stay 16-byte granular (it is: rows * 128 / C)
+  if (C == 4) return fu_launch_nl<4>(p, nl, smem, st);
+  if (C == 2) return fu_launch_nl<2>(p, nl, smem, st);
+  return fu_launch_nl<1>(p, nl, smem, st);
+}

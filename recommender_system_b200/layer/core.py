@@ -180,6 +180,49 @@ class DenseStack:
                   ptr(out), ptr(err_flag), stream_ptr())
         return out
 
+    # -- whole-model kernel (ctrhot_ctr_fused_tf32): gather -> side products -> tower -> combine, one launch
+    def ctr_fused_ok(self, F, k, arr=None):
+        arr = arr if arr is not None else self.descs()
+        n = len(arr)
+        if self.precision != "tf32" or not (2 <= n <= 4) or not self.allow_fused or k % 4 != 0 or F > 63:
+            return False
+        if arr[n - 1].out_dim != 1 or arr[n - 1].act != _lib.ACT_NONE:
+            return False
+        cols = 32                                            # side accumulator
+        for i in range(n - 1):
+            d = arr[i]
+            if not (8 <= d.out_dim <= 256):
+                return False
+            if d.act == _lib.ACT_PRELU:
+                if d.alpha_rows > 1:
+                    return False
+            elif d.act not in (_lib.ACT_NONE, _lib.ACT_RELU):
+                return False
+            cols += (d.out_dim + 31) // 32 * 32
+        return cols <= 512
+
+    def run_ctr_fused(self, E, ids, kind, ids_ld, dense, B, first_kernel_ref, side=None, sq_w=None, mode=0, n_side=0,
+                      combine=(), sigmoid=False, err_flag=None, out=None, cluster=0, side_key=None):
+        """``first_kernel_ref``: layer-0 kernel [n, n1] in the REFERENCE column order [dense | embeddings];
+        ``side`` [n, 16] (reference order) / ``sq_w`` / ``combine`` as described in include/ctrhot.h."""
+        arr = self.descs()
+        n, n1 = int(first_kernel_ref.shape[0]), int(first_kernel_ref.shape[1])
+        D = 0 if dense is None else dense.shape[1]
+        key = ("fused", side_key)
+        if key not in self._packed:
+            nbytes = _lib.query("ctrhot_fused_pack_bytes", n, n1)
+            buf = torch.empty(nbytes // 4, dtype=torch.float32, device=first_kernel_ref.device)
+            _lib.call("ctrhot_fused_pack", ptr(first_kernel_ref.contiguous()), ptr(side), n, n1, D, ptr(buf), stream_ptr())
+            self._packed[key] = buf
+        arr[0].packed = ptr(self._packed[key])
+        if out is None:
+            out = torch.empty((B, 1), dtype=torch.float32, device=E.arena.device)
+        cb = (ctypes.c_float * max(len(combine), 1))(*[float(c) for c in combine])
+        _lib.call("ctrhot_ctr_fused_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld,
+                  ptr(dense), 0 if dense is None else dense.stride(0), D, B, arr, len(arr), ptr(sq_w), int(mode),
+                  int(n_side), cb, len(combine), int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag), stream_ptr())
+        return out
+
     def run(self, x, x_ld=None, out=None):
         require_cuda(x, "DenseStack")
         M = x.shape[0]

@@ -118,8 +118,25 @@ class DeepFM(_EmbedTowerModel):
         self.dnn = self.track(DNNLayer(hidden_units, output_dim, activation, precision=precision, device=self.device))
         self.check = check_ids
         self.fused = True
+        self.whole = True           # one persistent kernel for the whole forward (ctrhot_ctr_fused_tf32) when it fits
+        self.cluster = 0            # CTAs sharing each weight chunk by TMA multicast (0 = auto)
         self.events = None          # bench hook: list receiving (front_start, front_end, tower_end) CUDA events
+        self._side = None
         self.embed_layer._err_flag = self.err_flag()
+
+    def _fm_side(self, D):
+        """FM weights as the whole-model kernel wants them: side [n,16] = [v | w1 | 0], sq_w[j] = sum_c v[j,c]^2
+        (internal column order), combine = {w0}  (FMLayer.call, DL/layer/interaction.py:106-114)."""
+        key = (self.fm._version, D)
+        if self._side is None or self._side[0] != key:
+            n, k = self.fm.v.shape
+            side = torch.zeros((n, 16), dtype=torch.float32, device=self.device)
+            side[:, :k] = self.fm.v
+            side[:, k] = self.fm.w1[:, 0]
+            n_pad = _pad32(n)
+            sq_w = self.fm.planes(D)[(k + 1) * n_pad:(k + 2) * n_pad]
+            self._side = (key, side, sq_w, [float(self.fm.w0.item())])
+        return self._side[1:]
 
     def build(self, input_shape):
         D = len(self.dense_feature_columns)
@@ -136,6 +153,26 @@ class DeepFM(_EmbedTowerModel):
         require_cuda(dense, "DeepFM")
         B = dense.shape[0]
         out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        if self.fused and self.whole and self.dnn.output_dim == 1 and self.fm.k < 16:
+            stack = self.dnn.stack
+            stack.set_layers(self._tower_layers(self.dnn, D), (self.dnn._version, D))
+            if stack.ctr_fused_ok(E.F, E.k):
+                # K-fused: gather -> FM (split-TF32 side columns + x^2 term) -> tower -> sigmoid(0.5*(fm+dnn)), ONE launch
+                side, sq_w, cb = self._fm_side(D)
+                ids, kind, ids_ld = ids_arg(ids)
+                ev = None
+                if self.events is not None:
+                    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+                    ev[0].record()
+                stack.run_ctr_fused(E, ids, kind, ids_ld, dense, B, self.dnn.hidden[0][0], side, sq_w, mode=1,
+                                    n_side=self.fm.k, combine=cb, sigmoid=True, err_flag=self.err_flag(), out=out,
+                                    cluster=self.cluster, side_key=("fm", self.fm._version))
+                if ev:
+                    ev[1].record()
+                    self.events.append(tuple(ev))
+                if self.check:
+                    self.check_ids()
+                return out
         if self.fused and self.dnn.output_dim == 1 and _front_supported(E.k, self.fm.k, E.F, D):
             ids, kind, ids_ld = ids_arg(ids)
             n = D + E.F * E.k
@@ -251,7 +288,10 @@ class DCN(_EmbedTowerModel):
         self.cross_layer = self.track(CrossLayer(layer_num, reg_w, reg_b, device=self.device))
         self.check = check_ids
         self.fused = True
+        self.whole = True
+        self.cluster = 0
         self._packed = None
+        self._side = None
         self.embed_layer._err_flag = self.err_flag()
 
     def build(self, input_shape):
@@ -263,6 +303,27 @@ class DCN(_EmbedTowerModel):
             self.cross_layer.built = True
         self._ensure_built(self.dense_layer, n)
         self.out_kernel, self.out_bias = dense_params(self, "output_layer", n + self.dense_layer.output_dim, 1)
+
+    def _cross_side(self, n):
+        """Cross layers as scalars for the whole-model kernel (include/ctrhot.h, mode 2): x_l = a_l x_0 + c_l, so
+        side = [w_0 .. w_{L-1} | final_w], combine = {c_l . w_l, c_L . final_w, wy, bias}, c_l = sum_{i<l} b_i."""
+        key = (self._version, self.cross_layer._version)
+        if self._side is None or self._side[0] != key:
+            L = self.cross_layer.layer_num
+            w, b = self.cross_layer.stacked()
+            fw = self.out_kernel[:n, 0]
+            side = torch.zeros((n, 16), dtype=torch.float32, device=self.device)
+            cb = []
+            c = torch.zeros(n, dtype=torch.float64, device=self.device)
+            for l in range(L):
+                side[:, l] = w[l]
+                cb.append(float((c * w[l].double()).sum().item()))
+                c = c + b[l].double()
+            side[:, L] = fw
+            cb.append(float((c * fw.double()).sum().item()))
+            cb += [float(self.out_kernel[n, 0].item()), float(self.out_bias[0].item())]
+            self._side = (key, side, cb)
+        return self._side[1:]
 
     def _packed_cross(self, D, n):
         key = (self._version, self.cross_layer._version)
@@ -288,6 +349,19 @@ class DCN(_EmbedTowerModel):
         B = dense.shape[0]
         n = D + E.F * E.k
         out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        if self.fused and self.whole and self.dense_layer.output_dim == 1 and self.cross_layer.layer_num < 16:
+            stack = self.dense_layer.stack
+            stack.set_layers(self._tower_layers(self.dense_layer, D), (self.dense_layer._version, D))
+            if stack.ctr_fused_ok(E.F, E.k):
+                side, cb = self._cross_side(n)
+                ids, kind, ids_ld = ids_arg(ids)
+                stack.run_ctr_fused(E, ids, kind, ids_ld, dense, B, self.dense_layer.hidden[0][0], side, None, mode=2,
+                                    n_side=self.cross_layer.layer_num, combine=cb, sigmoid=True,
+                                    err_flag=self.err_flag(), out=out, cluster=self.cluster,
+                                    side_key=("dcn", self._version, self.cross_layer._version))
+                if self.check:
+                    self.check_ids()
+                return out
         if self.fused and self.dense_layer.output_dim == 1 and _front_supported(E.k, None, E.F, D):
             ids, kind, ids_ld = ids_arg(ids)
             cw, cb, fw = self._packed_cross(D, n)
