@@ -13,7 +13,8 @@ import re
 PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 HEADER = os.path.join(ROOT, "include", "ctrhot.h")
-LIB_PATH = os.path.join(PKG, "libctrhot.so")
+# CTRHOT_LIB: developer knob for tuning builds (profiles/build_variants.py); still the same C-ABI, still CUDA only
+LIB_PATH = os.environ.get("CTRHOT_LIB") or os.path.join(PKG, "libctrhot.so")
 
 OK, EARG, ESHAPE, ECUDA, EID = 0, -1, -2, -3, -4
 IDS_I32, IDS_F32 = 0, 1

@@ -31,11 +31,11 @@ namespace ctrhot {
 using namespace tc;
 
 constexpr int FU_BM = 128;
-constexpr int FU_NA = 3;                    // A ring: raw (16 KB) + lo (16 KB) per stage
-constexpr int FU_NB = 3;                    // W ring
-constexpr int FU_PA = 2;                    // cp.async groups in flight per gather thread (<= FU_NA - 1)
+#ifndef FU_NB_
+#define FU_NB_ 3
+#endif
+constexpr int FU_NB = FU_NB_;               // W ring
 constexpr int FU_TILE_BYTES = FU_BM * 128;  // 16 KB
-constexpr int FU_A_STAGE = 2 * FU_TILE_BYTES;
 constexpr int FU_MAXL = 3;
 constexpr int FU_THREADS = 18 * 32;
 constexpr int FU_SIDE = 16;                 // side columns
@@ -110,9 +110,15 @@ __device__ __forceinline__ void sts128(uint32_t addr, const float4& v) {
 }
 __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
-constexpr int FU_NR = 4;                    // raw-row ring (gather depth)
-constexpr int FU_NLO = 2;                   // lo-tile ring
-constexpr int FU_PG = 3;                    // cp.async groups in flight per gather thread (<= FU_NR - 1)
+#ifndef FU_NR_
+#define FU_NR_ 4
+#endif
+#ifndef FU_NLO_
+#define FU_NLO_ 2
+#endif
+constexpr int FU_NR = FU_NR_;               // raw-row ring (gather depth)
+constexpr int FU_NLO = FU_NLO_;             // lo-tile ring
+constexpr int FU_PF = 3;                    // chunks by which the id loads run ahead of the row copies
 
 // float-region layout (shared by host sizing and device carving); all offsets in floats, 16-byte aligned
 struct FuSmemMap {
@@ -260,87 +266,79 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   const int n_my = ((int)cid < p.n_super) ? (p.n_super - (int)cid + (int)ncl - 1) / (int)ncl : 0;
 
   if (warp >= 8 && warp < 12) {
-    // ================================================================ gather (cp.async)
+    // ================================================================ gather (cp.async, completion tracked by mbarrier)
+    // Thread (c, rsub) owns 16-byte piece c of stage rows rsub + 16 i.  The ids of a chunk are fetched FU_PF chunks ahead
+    // of the copies that need them (their latency is a DRAM round trip); the copies themselves are never waited for by
+    // this thread: cp.async.mbarrier.arrive.noinc hands their completion to full_raw, so FU_NR chunks stay in flight.
     const int tg = tid - 256;
-    const int c = tg & 7;                    // 16-byte piece of the 128-byte stage row: the same for all of this thread's copies
-    const int rsub = tg >> 3;                // rows rsub + 16 i
+    const int c = tg & 7;
+    const int rsub = tg >> 3;
     const int64_t* s_ro = reinterpret_cast<const int64_t*>(fptr + mp.rowoff);
-    constexpr int32_t NOROW = INT32_MIN;
-    auto ids_for = [&](int64_t row0, int kc, int32_t (&reg)[8]) {
+    const int total_chunks = n_my * KC1;
+    auto tile_row0 = [&](int lt) { return (((int64_t)cid + (int64_t)lt * ncl) * C + crank) * FU_BM; };
+    auto fetch = [&](int g, int32_t (&reg)[8]) {
+      if (g >= total_chunks) return;
+      const int lt = g / KC1, kc = g - lt * KC1;
       const int col = kc * 32 + c * 4;
       if (col >= p.emb) return;
       const int f = (col >> 2) / p.k4;
+      const int64_t row0 = tile_row0(lt);
+      const int32_t* src = static_cast<const int32_t*>(p.ids) + f;         // int32 or float bits (converted at use)
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        const int64_t gm = row0 + rsub + 16 * i;
-        int32_t v = NOROW;
-        if (gm < p.M) {
-          v = (p.ids_kind == CTRHOT_IDS_I32)
-                  ? __ldg(static_cast<const int32_t*>(p.ids) + gm * p.ids_ld + f)
-                  : __float2int_rz(__ldg(static_cast<const float*>(p.ids) + gm * p.ids_ld + f));
-          if (v == NOROW) v = -1;
-        }
-        reg[i] = v;
+        int64_t gm = row0 + rsub + 16 * i;
+        if (gm >= p.M) gm = p.M - 1;                                       // value unused: the copy is zero-filled
+        reg[i] = __ldg(src + gm * p.ids_ld);
       }
     };
-    int32_t idc[8], idn[8];
-    uint32_t it = 0, signalled = 0;
-    if (n_my > 0) ids_for(((int64_t)cid * C + crank) * FU_BM, 0, idc);
-    for (int lt = 0; lt < n_my; ++lt) {
-      const int64_t row0 = (((int64_t)cid + (int64_t)lt * ncl) * C + crank) * FU_BM;
-      const int64_t row0n = (((int64_t)cid + (int64_t)(lt + 1) * ncl) * C + crank) * FU_BM;
-      for (int kc = 0; kc < KC1; ++kc, ++it) {
-        if (kc + 1 < KC1) ids_for(row0, kc + 1, idn);
-        else if (lt + 1 < n_my) ids_for(row0n, 0, idn);
-        const int s = it % FU_NR;
-        mbar_wait(empty_raw(s), ((it / FU_NR) & 1u) ^ 1u);
-        const uint32_t stage = r_base + s * FU_TILE_BYTES;
-        const int col = kc * 32 + c * 4;
-        if (col < p.emb) {
-          const int q = col >> 2;
-          const int f = q / p.k4, part = q - f * p.k4;
-          const int64_t r0 = s_ro[f], nrow = s_ro[f + 1] - r0;
-          const float* fbase = p.arena + (r0 * p.k4 + part) * 4;
+    auto issue = [&](int g, const int32_t (&reg)[8]) {
+      const int lt = g / KC1, kc = g - lt * KC1;
+      const int s = g % FU_NR;
+      const int64_t row0 = tile_row0(lt);
+      mbar_wait(empty_raw(s), (((uint32_t)g / FU_NR) & 1u) ^ 1u);
+      const uint32_t stage = r_base + s * FU_TILE_BYTES;
+      const int col = kc * 32 + c * 4;
+      if (col < p.emb) {
+        const int q = col >> 2;
+        const int f = q / p.k4, part = q - f * p.k4;
+        const int64_t r0 = s_ro[f], nrow = s_ro[f + 1] - r0;
+        const float* fbase = p.arena + (r0 * p.k4 + part) * 4;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int smp = rsub + 16 * i;
-            const int32_t id = idc[i];
-            const bool ok = id >= 0 && id < nrow;
-            if (!ok && id != NOROW && p.err_flag) *p.err_flag = 1;
-            cp_async16(stage + sw128_offset((uint32_t)smp, (uint32_t)c),
-                       ok ? (const void*)(fbase + (int64_t)id * (p.k4 * 4)) : (const void*)p.arena, ok ? 16u : 0u);
-          }
-        } else {                                       // dense tail [emb, emb + D) then zero padding
-          const int j = col - p.emb;
+        for (int i = 0; i < 8; ++i) {
+          const int smp = rsub + 16 * i;
+          const int32_t id = (p.ids_kind == CTRHOT_IDS_I32) ? reg[i] : __float2int_rz(__int_as_float(reg[i]));
+          const bool live = row0 + smp < p.M;
+          const bool ok = live && id >= 0 && id < nrow;
+          if (live && !ok && p.err_flag) *p.err_flag = 1;
+          cp_async16(stage + sw128_offset((uint32_t)smp, (uint32_t)c),
+                     ok ? (const void*)(fbase + (int64_t)id * (p.k4 * 4)) : (const void*)p.arena, ok ? 16u : 0u);
+        }
+      } else {                                         // dense tail [emb, emb + D) then zero padding: 4-byte copies
+        const int j = col - p.emb;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int smp = rsub + 16 * i;
-            const int64_t gm = row0 + smp;
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (gm < p.M && j < p.D) {
-              const float* src = p.dense + gm * p.dense_ld;
-              t.x = __ldg(src + j);
-              if (j + 1 < p.D) t.y = __ldg(src + j + 1);
-              if (j + 2 < p.D) t.z = __ldg(src + j + 2);
-              if (j + 3 < p.D) t.w = __ldg(src + j + 3);
-            }
-            sts128(stage + sw128_offset((uint32_t)smp, (uint32_t)c), t);
+        for (int i = 0; i < 8; ++i) {
+          const int smp = rsub + 16 * i;
+          const int64_t gm = row0 + smp;
+          const bool live = gm < p.M;
+          const float* src = p.dense + (live ? gm : 0) * p.dense_ld + j;
+          const uint32_t dst = stage + sw128_offset((uint32_t)smp, (uint32_t)c);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const bool ok = live && (j + e < p.D);
+            cp_async4(dst + 4u * e, ok ? (const void*)(src + e) : (const void*)p.arena, ok ? 4u : 0u);
           }
         }
-        cp_async_commit();
-        if (it + 1 - signalled >= (uint32_t)FU_PG) {
-          cp_async_wait<FU_PG - 1>();
-          fence_proxy_async_smem();
-          mbar_arrive(full_raw(signalled % FU_NR));
-          ++signalled;
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) idc[i] = idn[i];
       }
+      cp_async_mbar_arrive_noinc(full_raw(s));
+    };
+    static_assert(FU_PF == 3, "the loop below is unrolled for three id registers sets");
+    int32_t ra[8], rb[8], rc[8];
+    fetch(0, ra); fetch(1, rb); fetch(2, rc);
+    for (int g = 0; g < total_chunks; g += FU_PF) {
+      issue(g, ra); fetch(g + FU_PF, ra);
+      if (g + 1 < total_chunks) { issue(g + 1, rb); fetch(g + 1 + FU_PF, rb); }
+      if (g + 2 < total_chunks) { issue(g + 2, rc); fetch(g + 2 + FU_PF, rc); }
     }
-    cp_async_wait<0>();
-    fence_proxy_async_smem();
-    while (signalled < it) { mbar_arrive(full_raw(signalled % FU_NR)); ++signalled; }
   } else if (warp >= 12 && warp < 16) {
     // ================================================================ splitter: x_lo tile + q = sum x^2 sq_w
     const int row = tid - 384;
