@@ -22,7 +22,7 @@ def main(specs):
     others = [os.path.join(B.OBJ, s[:-3] + ".o") for s in B._sources() if s != "fused.cu"]
     for spec in specs:
         tag = spec.replace("=", "").replace(",", "_")
-        defs = ["-DFU_%s_=%s" % tuple(kv.split("=")) for kv in spec.split(",")]
+        defs = [("-DFU_TRACE" if kv == "TRACE=1" else "-DFU_%s_=%s" % tuple(kv.split("="))) for kv in spec.split(",")]
         obj = os.path.join(OUT, "fused_%s.o" % tag)
         lib = os.path.join(OUT, "libctrhot_%s.so" % tag)
         subprocess.check_call([B.NVCC] + B.FLAGS + defs + ["-c", os.path.join(B.CSRC, "fused.cu"), "-o", obj])

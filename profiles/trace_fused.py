@@ -1,0 +1,37 @@
+"""Where does the MMA thread of the whole-model kernel wait?  Needs a TRACE=1 tuning build:
+
+    python profiles/build_variants.py TRACE=1
+    CTRHOT_LIB=recommender_system_b200/build/variants/libctrhot_TRACE1.so python profiles/trace_fused.py [cluster]
+"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+from recommender_system_b200 import _lib  # noqa: E402
+from recommender_system_b200.utils import synth  # noqa: E402
+
+dev = torch.device("cuda", 0)
+model, vocab = bench.build_deepfm(dev, "kaggle", 16, "tf32")
+model.cluster = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+B = 65536
+ins = [tuple(torch.from_numpy(a).to(dev) for a in synth.criteo_batch(B, vocab, seed=5 + i)) for i in range(3)]
+for i in range(3):
+    model(ins[i])
+torch.cuda.synchronize()
+lib = _lib.load()
+buf = (ctypes.c_ulonglong * (256 * 8))()
+assert lib.ctrhot_debug_fused_trace(buf) == 0
+t = np.frombuffer(buf, dtype=np.uint64).reshape(256, 8).astype(np.float64)
+t = t[t[:, 7] > 0]
+names = ["W(L1)", "raw", "lo", "h_ready", "last_free", "W(L2+)", "tiles", "total"]
+print("CTAs", len(t))
+for lab, sel in (("all CTAs mean", t.mean(0)), ("CTAs with most tiles, mean", t[t[:, 6] == t[:, 6].max()].mean(0))):
+    print(lab)
+    for n, v in zip(names, sel):
+        print("   %-10s %10.0f %s" % (n, v, "" if n == "tiles" else "cyc (%.1f%% of total)" % (100 * v / sel[7])))

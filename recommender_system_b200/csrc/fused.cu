@@ -15,14 +15,19 @@
 //   warps 0-7   epilogue: tcgen05.ld the accumulator -> bias + activation -> TF32 -> tcgen05.st back IN PLACE as the next
 //               layer's A operand (hidden activations never leave TMEM); the last layer's epilogue does the final
 //               Dense(h -> 1) dot, the combine and writes 4 bytes per row.  Warp w owns TMEM lanes 32*(w%4).., column half w/4.
-//   warps 8-11  gather: 16-byte cp.async (LDGSTS) straight from the embedding rows into the 128B-swizzled K-major A stage.
-//   warps 12-15 splitter: one thread per tile row; reads its row of the stage, writes x_lo = x - trunc_tf32(x) into the
-//               "lo" tile and accumulates q_m.
-//   warp 16     TMEM owner + MMA issuer (one lane).  Per 32-column K chunk: D1 += x_hi W1 (N = N1), DS += x_hi [s_hi | s_lo]
-//               (N = 32), DS[0:16] += x_lo s_hi (N = 16); layers >= 2 read A from TMEM (TS form).
+//   warps 8-11  gather: 16-byte cp.async (LDGSTS) straight from the embedding rows into a smem ring of [128 x 32] chunks;
+//               completion is tracked by mbarrier (cp.async.mbarrier.arrive.noinc), ids are fetched 3 chunks ahead.
+//   warps 12-15 stager: one thread per tile row = per TMEM lane.  Reads its 32 floats of the chunk from smem and writes
+//               x and x_lo = x - trunc_tf32(x) into a TMEM ring with tcgen05.st; accumulates q_m.  The first layer's A
+//               operand therefore comes from TMEM: shared memory carries each gathered byte once in and once out, which
+//               matters because a TF32 SS-mode MMA at M=128 would spend the whole smem bandwidth (128 B/clk) on operands.
+//   warp 16     TMEM owner + MMA issuer (one lane).  Per 32-column K chunk: D1 += x W1 (N = N1), DS += x [s_hi | s_lo]
+//               (N = 32), DS[0:16] += x_lo s_hi (N = 16) -- the tensor pipe drops the low 13 mantissa bits of x itself, i.e.
+//               it multiplies by trunc_tf32(x); every layer reads A from TMEM (TS form).
 //   warp 17     W producer: one cp.async.bulk (TMA engine) per K chunk of the pre-swizzled weights, multicast to the
 //               CLUSTER so one L2 read feeds C SMs.
-// TMEM columns: D1/H1 at 0, DS (32) next, D2/H2, D3.  HBM traffic = ids + dense + each needed row once + 4 B out.
+// TMEM columns: D1/H1 at 0, DS (32) next, then a region shared in time by the A ring (2..4 slots of x|x_lo, live during
+// layer 1) and D2/H2, D3 (live afterwards).  HBM traffic = ids + dense + each needed row once + 4 B out.
 #include "common.cuh"
 #include "tc05.cuh"
 #include "mlp.cuh"
@@ -32,9 +37,10 @@ using namespace tc;
 
 constexpr int FU_BM = 128;
 #ifndef FU_NB_
-#define FU_NB_ 3
+#define FU_NB_ 4
 #endif
-constexpr int FU_NB = FU_NB_;               // W ring
+constexpr int FU_NB = FU_NB_;               // W ring, at most (the host takes one stage off when shared memory is short)
+constexpr int FU_NAS = 4;                   // A slots in TMEM, at most (64 columns each: x | x_lo)
 constexpr int FU_TILE_BYTES = FU_BM * 128;  // 16 KB
 constexpr int FU_MAXL = 3;
 constexpr int FU_THREADS = 18 * 32;
@@ -58,6 +64,8 @@ struct FuParams {
   int mode; int n_side; float cb[FU_NCB];
   int apply_sigmoid;
   int ds_col;                                              // TMEM column of the side accumulator
+  int a_col, n_as;                                         // TMEM A ring: first column, slots (64 columns each)
+  int nb;                                                  // W ring stages in use (<= FU_NB)
   float* out; int* err_flag;
   uint32_t b_stage_bytes;
 };
@@ -113,11 +121,7 @@ __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__
 #ifndef FU_NR_
 #define FU_NR_ 4
 #endif
-#ifndef FU_NLO_
-#define FU_NLO_ 2
-#endif
 constexpr int FU_NR = FU_NR_;               // raw-row ring (gather depth)
-constexpr int FU_NLO = FU_NLO_;             // lo-tile ring
 constexpr int FU_PF = 3;                    // chunks by which the id loads run ahead of the row copies
 
 // float-region layout (shared by host sizing and device carving); all offsets in floats, 16-byte aligned
@@ -127,7 +131,7 @@ struct FuSmemMap {
 __host__ __device__ inline FuSmemMap fu_smem_map(int F, int KC1, const int* KP, int nl) {
   FuSmemMap m;
   int o = 0;
-  m.rowoff = o; o += ((F + 1) * 2 + 3) / 4 * 4;
+  m.rowoff = o; o += (F * 3 + 3) / 4 * 4;          // per field: table base address (8 B) x F, then row count (4 B) x F
   m.sq = o; o += KC1 * 32;
   for (int l = 0; l < FU_MAXL; ++l) {
     m.bias[l] = o; if (l < nl) o += KP[l];
@@ -189,8 +193,15 @@ __device__ __forceinline__ float fu_last_chunk(uint32_t taddr, const float* sb, 
   return d0 + d1;
 }
 
-#ifndef FU_MASK_HI
-#define FU_MASK_HI 1      // splitter rewrites the raw tile with trunc_tf32(x): the split is exact whatever the MMA's own rounding
+#ifndef FU_EXP_
+#define FU_EXP_ 0         // tuning builds only: bit 0 drops the N=32 side MMA, bit 1 the N=16 one (results are then wrong)
+#endif
+#ifdef FU_TRACE
+// tuning builds only (profiles/build_variants.py TRACE=1): cycles the MMA thread of every CTA spent waiting, per cause
+__device__ unsigned long long fu_trace[256][8];
+#define FU_TWAIT(slot, stmt) do { const long long t0_ = clock64(); stmt; tw[slot] += clock64() - t0_; } while (0)
+#else
+#define FU_TWAIT(slot, stmt) do { stmt; } while (0)
 #endif
 
 template <int NL, int C>
@@ -200,10 +211,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t base = (raw_addr + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - raw_addr);
-  const uint32_t r_base = base;                                         // FU_NR raw tiles
-  const uint32_t lo_base = r_base + FU_NR * FU_TILE_BYTES;              // FU_NLO lo tiles
-  const uint32_t b_base = lo_base + FU_NLO * FU_TILE_BYTES;             // FU_NB weight stages
-  const uint32_t f_base = b_base + FU_NB * p.b_stage_bytes;             // float region
+  const uint32_t r_base = base;                                         // FU_NR raw chunks
+  const uint32_t b_base = r_base + FU_NR * FU_TILE_BYTES;               // p.nb weight stages
+  const uint32_t f_base = b_base + (uint32_t)p.nb * p.b_stage_bytes;    // float region
   int KP[FU_MAXL];
 #pragma unroll
   for (int l = 0; l < FU_MAXL; ++l) KP[l] = (l < NL) ? p.L[l].KP : 0;
@@ -214,11 +224,11 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   // barrier map
   auto full_raw = [&](int s) { return bars + 8u * s; };
   auto empty_raw = [&](int s) { return bars + 8u * (FU_NR + s); };
-  auto full_lo = [&](int s) { return bars + 8u * (2 * FU_NR + s); };
-  auto empty_lo = [&](int s) { return bars + 8u * (2 * FU_NR + FU_NLO + s); };
-  auto full_b = [&](int s) { return bars + 8u * (2 * FU_NR + 2 * FU_NLO + s); };
-  auto empty_b = [&](int s) { return bars + 8u * (2 * FU_NR + 2 * FU_NLO + FU_NB + s); };
-  const uint32_t misc = bars + 8u * (2 * FU_NR + 2 * FU_NLO + 2 * FU_NB);
+  auto a_full = [&](int s) { return bars + 8u * (2 * FU_NR + s); };
+  auto a_free = [&](int s) { return bars + 8u * (2 * FU_NR + FU_NAS + s); };
+  auto full_b = [&](int s) { return bars + 8u * (2 * FU_NR + 2 * FU_NAS + s); };
+  auto empty_b = [&](int s) { return bars + 8u * (2 * FU_NR + 2 * FU_NAS + FU_NB + s); };
+  const uint32_t misc = bars + 8u * (2 * FU_NR + 2 * FU_NAS + 2 * FU_NB);
   auto d_full = [&](int l) { return misc + 8u * l; };
   auto h_ready = [&](int l) { return misc + 8u * (FU_MAXL + l); };
   const uint32_t last_free = misc + 8u * (2 * FU_MAXL);
@@ -232,8 +242,8 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   const uint16_t cmask = (uint16_t)((1u << C) - 1u);
 
   if (tid == 0) {
-    for (int s = 0; s < FU_NR; ++s) { mbar_init(full_raw(s), 128); mbar_init(empty_raw(s), 1); }
-    for (int s = 0; s < FU_NLO; ++s) { mbar_init(full_lo(s), 128); mbar_init(empty_lo(s), 1); }
+    for (int s = 0; s < FU_NR; ++s) { mbar_init(full_raw(s), 128); mbar_init(empty_raw(s), 128); }
+    for (int s = 0; s < FU_NAS; ++s) { mbar_init(a_full(s), 128); mbar_init(a_free(s), 1); }
     for (int s = 0; s < FU_NB; ++s) { mbar_init(full_b(s), 1); mbar_init(empty_b(s), C); }
     for (int l = 0; l < FU_MAXL; ++l) { mbar_init(d_full(l), 1); mbar_init(h_ready(l), 256); }
     mbar_init(last_free, 256);
@@ -241,8 +251,13 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   }
   // stage the small per-column vectors
   {
-    int64_t* s_ro = reinterpret_cast<int64_t*>(fptr + mp.rowoff);
-    for (int i = tid; i <= p.F; i += FU_THREADS) s_ro[i] = p.row_off[i];
+    const float** s_fb = reinterpret_cast<const float**>(fptr + mp.rowoff);
+    uint32_t* s_fn = reinterpret_cast<uint32_t*>(fptr + mp.rowoff + 2 * p.F);
+    for (int i = tid; i < p.F; i += FU_THREADS) {
+      const int64_t r0 = p.row_off[i], nr = p.row_off[i + 1] - r0;
+      s_fb[i] = p.arena + r0 * (int64_t)(p.k4 * 4);
+      s_fn[i] = nr < 0 ? 0u : (nr > 0x7FFFFFFF ? 0x7FFFFFFFu : (uint32_t)nr);   // ids are int32: larger tables cannot be addressed anyway
+    }
     for (int i = tid; i < KC1 * 32; i += FU_THREADS) fptr[mp.sq + i] = p.sq_w ? __ldg(p.sq_w + i) : 0.f;
 #pragma unroll
     for (int l = 0; l < NL; ++l) {
@@ -270,140 +285,173 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     // Thread (c, rsub) owns 16-byte piece c of stage rows rsub + 16 i.  The ids of a chunk are fetched FU_PF chunks ahead
     // of the copies that need them (their latency is a DRAM round trip); the copies themselves are never waited for by
     // this thread: cp.async.mbarrier.arrive.noinc hands their completion to full_raw, so FU_NR chunks stay in flight.
+    // Two cursors (fetch, issue) walk the same (tile, chunk) sequence; (f, part) advance incrementally -- no divisions.
     const int tg = tid - 256;
     const int c = tg & 7;
     const int rsub = tg >> 3;
-    const int64_t* s_ro = reinterpret_cast<const int64_t*>(fptr + mp.rowoff);
+    const float* const* s_fb = reinterpret_cast<const float* const*>(fptr + mp.rowoff);
+    const uint32_t* s_fn = reinterpret_cast<const uint32_t*>(fptr + mp.rowoff + 2 * p.F);
     const int total_chunks = n_my * KC1;
-    auto tile_row0 = [&](int lt) { return (((int64_t)cid + (int64_t)lt * ncl) * C + crank) * FU_BM; };
-    auto fetch = [&](int g, int32_t (&reg)[8]) {
-      if (g >= total_chunks) return;
-      const int lt = g / KC1, kc = g - lt * KC1;
-      const int col = kc * 32 + c * 4;
-      if (col >= p.emb) return;
-      const int f = (col >> 2) / p.k4;
-      const int64_t row0 = tile_row0(lt);
-      const int32_t* src = static_cast<const int32_t*>(p.ids) + f;         // int32 or float bits (converted at use)
+    const int k4 = p.k4;
+    const int f0 = c / k4, part0 = c - f0 * k4;
+    const uint32_t rowbytes = (uint32_t)k4 * 16u;
+    const uint32_t dst0 = r_base + (uint32_t)rsub * 128u + (uint32_t)((c ^ (rsub & 7)) << 4);   // rows rsub + 16 i: + 2048 i
+    const int64_t tile_stride = (int64_t)ncl * C * FU_BM;
+    const int64_t first_row0 = ((int64_t)cid * C + crank) * FU_BM;
+    struct Cur { int kc, f, part; int64_t row0; };
+    auto advance = [&](Cur& u) {
+      ++u.kc; u.part += 8;
+      while (u.part >= k4) { u.part -= k4; ++u.f; }
+      if (u.kc == KC1) { u.kc = 0; u.f = f0; u.part = part0; u.row0 += tile_stride; }
+    };
+    Cur cf{0, f0, part0, first_row0}, ci = cf;
+    int n_fetched = 0;
+    auto fetch = [&](int32_t (&reg)[8]) {
+      if (n_fetched >= total_chunks) return;
+      ++n_fetched;
+      if (cf.f < p.F) {
+        const int32_t* src = static_cast<const int32_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + cf.f;   // int32 or float bits
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        int64_t gm = row0 + rsub + 16 * i;
-        if (gm >= p.M) gm = p.M - 1;                                       // value unused: the copy is zero-filled
-        reg[i] = __ldg(src + gm * p.ids_ld);
+        for (int i = 0; i < 8; ++i)                        // rows past M read id 0: a valid row, never consumed
+          reg[i] = (cf.row0 + rsub + 16 * i < p.M) ? __ldg(src + (int64_t)(16 * i) * p.ids_ld) : 0;
       }
+      advance(cf);
     };
     auto issue = [&](int g, const int32_t (&reg)[8]) {
-      const int lt = g / KC1, kc = g - lt * KC1;
       const int s = g % FU_NR;
-      const int64_t row0 = tile_row0(lt);
       mbar_wait(empty_raw(s), (((uint32_t)g / FU_NR) & 1u) ^ 1u);
-      const uint32_t stage = r_base + s * FU_TILE_BYTES;
-      const int col = kc * 32 + c * 4;
-      if (col < p.emb) {
-        const int q = col >> 2;
-        const int f = q / p.k4, part = q - f * p.k4;
-        const int64_t r0 = s_ro[f], nrow = s_ro[f + 1] - r0;
-        const float* fbase = p.arena + (r0 * p.k4 + part) * 4;
+      const uint32_t dst = dst0 + (uint32_t)s * FU_TILE_BYTES;
+      if (ci.f < p.F) {
+        const char* fb = reinterpret_cast<const char*>(s_fb[ci.f]) + ci.part * 16;
+        const uint32_t nrow = s_fn[ci.f];
+        bool bad = false;
+        if (p.ids_kind == CTRHOT_IDS_I32) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int smp = rsub + 16 * i;
-          const int32_t id = (p.ids_kind == CTRHOT_IDS_I32) ? reg[i] : __float2int_rz(__int_as_float(reg[i]));
-          const bool live = row0 + smp < p.M;
-          const bool ok = live && id >= 0 && id < nrow;
-          if (live && !ok && p.err_flag) *p.err_flag = 1;
-          cp_async16(stage + sw128_offset((uint32_t)smp, (uint32_t)c),
-                     ok ? (const void*)(fbase + (int64_t)id * (p.k4 * 4)) : (const void*)p.arena, ok ? 16u : 0u);
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t id = (uint32_t)reg[i];
+            const bool ok = id < nrow;
+            bad |= !ok;
+            cp_async16(dst + 2048u * i, ok ? (const void*)(fb + (uint64_t)id * rowbytes) : (const void*)p.arena, ok ? 16u : 0u);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t id = (uint32_t)__float2int_rz(__int_as_float(reg[i]));
+            const bool ok = id < nrow;
+            bad |= !ok;
+            cp_async16(dst + 2048u * i, ok ? (const void*)(fb + (uint64_t)id * rowbytes) : (const void*)p.arena, ok ? 16u : 0u);
+          }
         }
+        if (bad && p.err_flag) *p.err_flag = 1;
       } else {                                         // dense tail [emb, emb + D) then zero padding: 4-byte copies
-        const int j = col - p.emb;
+        const int j = ((ci.f - p.F) * k4 + ci.part) * 4;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const int smp = rsub + 16 * i;
-          const int64_t gm = row0 + smp;
+          const int64_t gm = ci.row0 + rsub + 16 * i;
           const bool live = gm < p.M;
           const float* src = p.dense + (live ? gm : 0) * p.dense_ld + j;
-          const uint32_t dst = stage + sw128_offset((uint32_t)smp, (uint32_t)c);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const bool ok = live && (j + e < p.D);
-            cp_async4(dst + 4u * e, ok ? (const void*)(src + e) : (const void*)p.arena, ok ? 4u : 0u);
+            cp_async4(dst + 2048u * i + 4u * e, ok ? (const void*)(src + e) : (const void*)p.arena, ok ? 4u : 0u);
           }
         }
       }
       cp_async_mbar_arrive_noinc(full_raw(s));
+      advance(ci);
     };
-    static_assert(FU_PF == 3, "the loop below is unrolled for three id registers sets");
+    static_assert(FU_PF == 3, "the loop below is unrolled for three id register sets");
     int32_t ra[8], rb[8], rc[8];
-    fetch(0, ra); fetch(1, rb); fetch(2, rc);
+    fetch(ra); fetch(rb); fetch(rc);
     for (int g = 0; g < total_chunks; g += FU_PF) {
-      issue(g, ra); fetch(g + FU_PF, ra);
-      if (g + 1 < total_chunks) { issue(g + 1, rb); fetch(g + 1 + FU_PF, rb); }
-      if (g + 2 < total_chunks) { issue(g + 2, rc); fetch(g + 2 + FU_PF, rc); }
+      issue(g, ra); fetch(ra);
+      if (g + 1 < total_chunks) { issue(g + 1, rb); fetch(rb); }
+      if (g + 2 < total_chunks) { issue(g + 2, rc); fetch(rc); }
     }
   } else if (warp >= 12 && warp < 16) {
-    // ================================================================ splitter: x_lo tile + q = sum x^2 sq_w
-    const int row = tid - 384;
-    uint32_t it = 0;
+    // ================================================================ stager: smem chunk -> TMEM A ring (x | x_lo), q = sum x^2 sq_w
+    const int row = tid - 384;                          // = TMEM lane; warps 12..15 own lane quarters 0..3
+    const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)p.a_col;
+    const uint32_t src0 = r_base + (uint32_t)row * 128u;
+    const uint32_t rx = (uint32_t)(row & 7);
+    const int n_as = p.n_as;
+    uint32_t it = 0, sa = 0, pa = 0;                    // A slot and its phase
     for (int lt = 0; lt < n_my; ++lt) {
       float q = 0.f;
       for (int kc = 0; kc < KC1; ++kc, ++it) {
-        const int sr = it % FU_NR, sl = it % FU_NLO;
+        const int sr = it % FU_NR;
         mbar_wait(full_raw(sr), (it / FU_NR) & 1u);
-        mbar_wait(empty_lo(sl), ((it / FU_NLO) & 1u) ^ 1u);
-        const uint32_t raw = r_base + sr * FU_TILE_BYTES, lo = lo_base + sl * FU_TILE_BYTES;
+        const uint32_t raw = src0 + sr * FU_TILE_BYTES;
         const float* sq = fptr + mp.sq + kc * 32;
+        float x[32], lo[32];
 #pragma unroll
         for (int cc = 0; cc < 8; ++cc) {
-          const uint32_t off = sw128_offset((uint32_t)row, (uint32_t)cc);
-          const float4 x = lds128(raw + off);
-          const float4 w = *reinterpret_cast<const float4*>(sq + cc * 4);
-          float4 hi, l;
-          hi.x = trunc_tf32(x.x); hi.y = trunc_tf32(x.y); hi.z = trunc_tf32(x.z); hi.w = trunc_tf32(x.w);
-          l.x = x.x - hi.x; l.y = x.y - hi.y; l.z = x.z - hi.z; l.w = x.w - hi.w;
-          q = fmaf(x.x * x.x, w.x, q); q = fmaf(x.y * x.y, w.y, q);
-          q = fmaf(x.z * x.z, w.z, q); q = fmaf(x.w * x.w, w.w, q);
-          sts128(lo + off, l);
-          if (FU_MASK_HI) sts128(raw + off, hi);
+          const float4 v = lds128(raw + (((uint32_t)cc ^ rx) << 4));
+          x[4 * cc + 0] = v.x; x[4 * cc + 1] = v.y; x[4 * cc + 2] = v.z; x[4 * cc + 3] = v.w;
         }
-        if (kc == KC1 - 1) fptr[mp.q + (lt & 1) * FU_BM + row] = q;
-        fence_proxy_async_smem();
-        mbar_arrive(full_lo(sl));
+#pragma unroll
+        for (int cc = 0; cc < 8; ++cc) {
+          const float4 w = *reinterpret_cast<const float4*>(sq + cc * 4);
+          q = fmaf(x[4 * cc + 0] * x[4 * cc + 0], w.x, q); q = fmaf(x[4 * cc + 1] * x[4 * cc + 1], w.y, q);
+          q = fmaf(x[4 * cc + 2] * x[4 * cc + 2], w.z, q); q = fmaf(x[4 * cc + 3] * x[4 * cc + 3], w.w, q);
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) lo[j] = x[j] - trunc_tf32(x[j]);
+        mbar_arrive(empty_raw(sr));                     // the chunk is in registers: the gather may refill the stage
+        // the A ring shares its TMEM columns with the later layers' accumulators: wait until the previous tile is done with them
+        if (kc == 0 && lt > 0) mbar_wait(last_free, (uint32_t)(lt - 1) & 1u);
+        mbar_wait(a_free(sa), pa ^ 1u);
+        tc_fence_after();
+        tmem_st32(t_lane + sa * 64u, x);
+        tmem_st32(t_lane + sa * 64u + 32u, lo);
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(a_full(sa));
+        if (++sa == (uint32_t)n_as) { sa = 0; pa ^= 1u; }
       }
+      fptr[mp.q + (lt & 1) * FU_BM + row] = q;
     }
   } else if (warp == 16) {
     // ================================================================ MMA issuer
     if (lane == 0) {
-      uint32_t ia = 0, ib = 0;
+#ifdef FU_TRACE
+      long long tw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      const long long t_begin = clock64();
+#endif
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0;     // A slot / W stage and their phases
       uint32_t hcount[FU_MAXL] = {0, 0, 0};
       const uint32_t ds_t = tmem_base + (uint32_t)p.ds_col;
+      const uint32_t a_t0 = tmem_base + (uint32_t)p.a_col;
       for (int lt = 0; lt < n_my; ++lt) {
         {
           const FuLayer& L = p.L[0];
           const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BN);
           const uint32_t idesc32 = make_idesc_tf32(FU_BM, 32u), idesc16 = make_idesc_tf32(FU_BM, 16u);
           const uint32_t d_t = tmem_base + (uint32_t)L.col;
-          if (NL == 1 && lt > 0) { mbar_wait(last_free, (uint32_t)(lt - 1) & 1u); tc_fence_after(); }
-          for (int kc = 0; kc < L.KC; ++kc, ++ia, ++ib) {
-            const int sr = ia % FU_NR, sl = ia % FU_NLO, sb = ib % FU_NB;
-            mbar_wait(full_b(sb), (ib / FU_NB) & 1u);
-            if (!FU_MASK_HI) mbar_wait(full_raw(sr), (ia / FU_NR) & 1u);
-            else mbar_wait(full_lo(sl), (ia / FU_NLO) & 1u);
+          if (NL == 1 && lt > 0) { FU_TWAIT(4, mbar_wait(last_free, (uint32_t)(lt - 1) & 1u)); tc_fence_after(); }
+          for (int kc = 0; kc < L.KC; ++kc) {
+            FU_TWAIT(0, mbar_wait(full_b(sb), pb));
+            FU_TWAIT(1, mbar_wait(a_full(sa), pa));
             tc_fence_after();
-            const uint64_t da = make_desc_sw128(r_base + sr * FU_TILE_BYTES);
+            const uint32_t a_hi = a_t0 + sa * 64u, a_lo = a_hi + 32u;
             const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
             const uint64_t ds = make_desc_sw128(b_base + sb * p.b_stage_bytes + (uint32_t)L.BN * 128u);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              mma_tf32_ss(d_t, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
-              mma_tf32_ss(ds_t, da + (uint64_t)(2 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
+              mma_tf32_ts(d_t, a_hi + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
+#if !(FU_EXP_ & 1)
+              mma_tf32_ts(ds_t, a_hi + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
+#endif
             }
-            if (!FU_MASK_HI) { mbar_wait(full_lo(sl), (ia / FU_NLO) & 1u); tc_fence_after(); }
-            const uint64_t dl = make_desc_sw128(lo_base + sl * FU_TILE_BYTES);
+#if !(FU_EXP_ & 2)
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              mma_tf32_ss(ds_t, dl + (uint64_t)(2 * k), ds + (uint64_t)(2 * k), idesc16, 1u);
-            mma_commit(empty_raw(sr));
-            mma_commit(empty_lo(sl));
+              mma_tf32_ts(ds_t, a_lo + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc16, 1u);
+#endif
+            mma_commit(a_free(sa));
             if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
+            if (++sa == (uint32_t)p.n_as) { sa = 0; pa ^= 1u; }
+            if (++sb == (uint32_t)p.nb) { sb = 0; pb ^= 1u; }
           }
           mma_commit(d_full(0));
         }
@@ -413,42 +461,47 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BN);
           const uint32_t d_t = tmem_base + (uint32_t)L.col;
           const uint32_t a_t = tmem_base + (uint32_t)p.L[l - 1].col;
-          mbar_wait(h_ready(l - 1), hcount[l - 1] & 1u); ++hcount[l - 1];
-          if (l == NL - 1 && lt > 0) mbar_wait(last_free, (uint32_t)(lt - 1) & 1u);
+          FU_TWAIT(3, mbar_wait(h_ready(l - 1), hcount[l - 1] & 1u)); ++hcount[l - 1];
+          if (l == NL - 1 && lt > 0) FU_TWAIT(4, mbar_wait(last_free, (uint32_t)(lt - 1) & 1u));
           tc_fence_after();
-          for (int kc = 0; kc < L.KC; ++kc, ++ib) {
-            const int sb = ib % FU_NB;
-            mbar_wait(full_b(sb), (ib / FU_NB) & 1u);
+          for (int kc = 0; kc < L.KC; ++kc) {
+            FU_TWAIT(5, mbar_wait(full_b(sb), pb));
             tc_fence_after();
             const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
               mma_tf32_ts(d_t, a_t + (uint32_t)(kc * 32 + k * 8), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
             if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
+            if (++sb == (uint32_t)p.nb) { sb = 0; pb ^= 1u; }
           }
           mma_commit(d_full(l));
         }
       }
+#ifdef FU_TRACE
+      tw[7] = clock64() - t_begin;
+      tw[6] = n_my;
+      if (blockIdx.x < 256) for (int i = 0; i < 8; ++i) fu_trace[blockIdx.x][i] = (unsigned long long)tw[i];
+#endif
     }
     __syncwarp();
   } else if (warp == 17) {
     // ================================================================ W producer (bulk async copies, cluster multicast)
     if (lane == 0) {
-      uint32_t ib = 0;
+      uint32_t sb = 0, pb = 0;
       for (int lt = 0; lt < n_my; ++lt) {
 #pragma unroll
         for (int l = 0; l < NL; ++l) {
           const FuLayer& L = p.L[l];
           const uint32_t bytes = (uint32_t)(L.BN + (l == 0 ? 2 * FU_SIDE : 0)) * 128u;
           const uint32_t piece = bytes / C;
-          for (int kc = 0; kc < L.KC; ++kc, ++ib) {
-            const int sb = ib % FU_NB;
-            mbar_wait(empty_b(sb), ((ib / FU_NB) & 1u) ^ 1u);
+          for (int kc = 0; kc < L.KC; ++kc) {
+            mbar_wait(empty_b(sb), pb ^ 1u);
             mbar_arrive_expect_tx(full_b(sb), bytes);
             const uint8_t* src = reinterpret_cast<const uint8_t*>(L.Wp) + (size_t)kc * bytes + (size_t)crank * piece;
             const uint32_t dst = b_base + sb * p.b_stage_bytes + crank * piece;
             if (C > 1) bulk_g2s_mc(dst, src, piece, full_b(sb), cmask);
             else bulk_g2s(dst, src, bytes, full_b(sb));
+            if (++sb == (uint32_t)p.nb) { sb = 0; pb ^= 1u; }
           }
         }
       }
@@ -582,6 +635,12 @@ extern "C" int ctrhot_fused_pack(const float* W1, const float* side, int n, int 
   return CTRHOT_OK;
 }
 
+#ifdef FU_TRACE
+extern "C" int ctrhot_debug_fused_trace(unsigned long long* h_out) {
+  return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
+}
+#endif
+
 namespace {
 template <int NL, int C>
 int fu_launch(const FuParams& p0, size_t smem, cudaStream_t st) {
@@ -661,12 +720,14 @@ extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off,
     L.N = d.out_dim; L.KC = (d.in_dim + 31) / 32; L.BN = fu_round(d.out_dim, 16); L.KP = fu_round(d.out_dim, 32);
     L.col = col;
     col += L.KP;
-    if (l == 0) { p.ds_col = col; col += 2 * FU_SIDE; }
+    if (l == 0) { p.ds_col = col; col += 2 * FU_SIDE; p.a_col = col; }
     KP[l] = L.KP;
     const uint32_t b = (uint32_t)(L.BN + (l == 0 ? 2 * FU_SIDE : 0)) * 128u;
     if (b > bmax) bmax = b;
   }
   if (col > 512) return CTRHOT_ESHAPE;
+  p.n_as = (512 - p.a_col) / 64 < FU_NAS ? (512 - p.a_col) / 64 : FU_NAS;
+  if (p.n_as < 2) return CTRHOT_ESHAPE;
   if (o.in_dim != h_layers[nl - 1].out_dim) return CTRHOT_EARG;
   if (M == 0) return CTRHOT_OK;
   p.arena = arena; p.row_off = row_off; p.F = F; p.k4 = k / 4; p.ids = ids; p.ids_kind = ids_kind; p.ids_ld = ids_ld;
@@ -677,10 +738,13 @@ extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off,
   for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
   const FuSmemMap mp = fu_smem_map(F, p.L[0].KC, KP, nl);
-  const size_t n_bars = 2 * FU_NR + 2 * FU_NLO + 2 * FU_NB + 2 * FU_MAXL + 1;
-  const size_t smem = 1024 + (size_t)(FU_NR + FU_NLO) * FU_TILE_BYTES + (size_t)FU_NB * bmax + (size_t)mp.total * 4 +
-                      8 * n_bars + 16;
-  if (smem > 227 * 1024) return CTRHOT_ESHAPE;
+  const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1;
+  size_t smem = 0;
+  for (p.nb = FU_NB; p.nb >= 2; --p.nb) {
+    smem = 1024 + (size_t)FU_NR * FU_TILE_BYTES + (size_t)p.nb * bmax + (size_t)mp.total * 4 + 8 * n_bars + 16;
+    if (smem <= 227 * 1024) break;
+  }
+  if (p.nb < 2) return CTRHOT_ESHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int C = cluster;
   if (C == 0) C = (p.n_tiles >= 4 * 32) ? 4 : (p.n_tiles >= 2 ? 2 : 1);
