@@ -217,6 +217,23 @@ int ctrhot_din_attention_gather_f32(const float* table, int64_t V, int K,
                                     float* att_out, int64_t att_ld, float* item_out, int64_t item_ld,
                                     int* err_flag, void* stream);
 
+/* tcgen05 version of the fused gather + attention unit ('prelu' / relu branch with exactly two hidden Dense layers,
+ * K in {8,16,32,64}, T <= 128, h1 <= 96, h2 <= 64; CTRHOT_ESHAPE otherwise -> use the _f32 entry point).
+ * TF32 multiply, fp32 accumulate; the first layer is evaluated as q (W1a + W1c) + k (W1b - W1c) + (q*k) W1d.
+ * packed = ctrhot_din_pack(h_layers[2], out_w, out_b): weights in the kernel's shared-memory layout (re-pack when they
+ * change).  workspace: ctrhot_din_tc_workspace_bytes(B, h1) bytes, 16-byte aligned.  item_out is REQUIRED (it carries the
+ * candidate rows between the two launches) and item_ld % 4 == 0. */
+int64_t ctrhot_din_pack_bytes(int T, int K, int h1, int h2);
+int ctrhot_din_pack(const ctrhot_dense_desc* h_layers, int n_layers, const float* out_w, const float* out_b,
+                    int T, int K, void* packed, void* stream);
+int64_t ctrhot_din_tc_workspace_bytes(int64_t B, int h1);
+int ctrhot_din_attention_gather_tf32(const float* table, int64_t V, int K,
+                                     const void* hist_ids, int ids_kind, int64_t hist_ld,
+                                     const void* cand_ids, int64_t cand_ld, int64_t B, int T,
+                                     const void* packed, int h1, int h2,
+                                     float* att_out, int64_t att_ld, float* item_out, int64_t item_ld,
+                                     void* workspace, int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R12/R14 fused model front ends ------------------------------------------
  * gather -> x=[dense, embed] -> FM (DeepFM, DL/model/deepFM.py:24-28) or L cross
  * layers (DCN, DL/model/dcn.py:25-29) in ONE kernel; the gathered rows are

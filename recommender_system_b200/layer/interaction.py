@@ -263,13 +263,15 @@ class Attention(Layer):
     PReLU) layers whose alpha is [T,h] (Keras builds PReLU over input_shape[1:]); 'dice': Dice
     layers only, no Dense projection, then Dense(1)."""
 
-    def __init__(self, hidden_units, activation="prelu", device=None):
+    def __init__(self, hidden_units, activation="prelu", device=None, precision="tf32"):
         super().__init__(device)
         self.hidden_units = list(hidden_units)
         if activation not in ("prelu", "dice"):
             raise ValueError("activation must be 'prelu' or 'dice'")
         self.activation = activation
+        self.precision = precision          # 'tf32': tcgen05 unit (csrc/din_tc.cu) when the shape fits; 'fp32': CUDA cores
         self._descs = None
+        self._tc = None
 
     def build(self, input_shape):
         q_shape, k_shape = input_shape[0], input_shape[1]
@@ -344,6 +346,22 @@ class Attention(Layer):
         arr, _keep = self.descs()
         att = _out(B, self.device, K)
         item = _out(B, self.device, K)
+        if self.precision == "tf32" and self.activation == "prelu" and len(self.layers) == 2:
+            h1, h2 = self.hidden_units
+            nbytes = _lib.load().ctrhot_din_pack_bytes(T, K, h1, h2)
+            if nbytes > 0:
+                if self._tc is None or self._tc[0] != self._version:
+                    blob = torch.empty(nbytes // 4, dtype=torch.float32, device=self.device)
+                    _lib.call("ctrhot_din_pack", arr, len(arr), ptr(self.out_kernel), ptr(self.out_bias), T, K, ptr(blob),
+                              stream_ptr())
+                    self._tc = (self._version, blob)
+                ws = torch.empty(_lib.query("ctrhot_din_tc_workspace_bytes", B, h1) // 4 + 4, dtype=torch.float32,
+                                 device=self.device)
+                _lib.call("ctrhot_din_attention_gather_tf32", ptr(table), V, K, ptr(hist_ids), kind, hist_ld,
+                          ptr(cand_ids), cand_ld, B, T, ptr(self._tc[1]), h1, h2, ptr(att), att.stride(0), ptr(item),
+                          item.stride(0), ptr(ws), ws.numel() * 4, ptr(check_flag), stream_ptr())
+                _lib.LAUNCHES[0] += 1                       # prep + main kernel
+                return att, item
         _lib.call("ctrhot_din_attention_gather_f32", ptr(table), V, K, ptr(hist_ids), kind, hist_ld, ptr(cand_ids),
                   cand_ld, B, T, arr, len(arr), ptr(self.out_kernel), ptr(self.out_bias), ptr(att), att.stride(0),
                   ptr(item), item.stride(0), ptr(check_flag), stream_ptr())

@@ -38,7 +38,7 @@ class DIN(Model):
         self.embed_seq_layers = [self.add_weight("embed_seq_%d/embeddings" % i,
                                                  (f["feat_onehot_dim"], f["embed_dim"]), init_uniform)
                                  for i, f in enumerate(self.behavior)]
-        self.att_layer = self.track(Attention(att_hidden_units, att_attention, device=self.device))
+        self.att_layer = self.track(Attention(att_hidden_units, att_attention, device=self.device, precision=precision))
         self.dnn_hidden_units = list(dnn_hidden_units)
         self.dnn_activation = dnn_activation
         self.dnn_dropout = dnn_dropout
