@@ -10,15 +10,16 @@
 // [K] x [K,h1] product per SAMPLE (done by din_prep_kernel with the candidate gather, fp32), so the per-(sample, t) GEMM
 // has K-extent 2K instead of 4K.  This changes rounding only (SURVEY 8(d) cfg 4 allows it).
 //
-// One persistent CTA per SM, one 128-row MMA tile per SAMPLE (rows t >= T are zero), 13 warps:
+// One persistent CTA per SM, one 128-row MMA tile per SAMPLE (rows t >= T are zero), 17 warps:
 //   warps 4-7   gather: 16-byte cp.async of the T history rows (+ q and u = q Wq + b1 of this sample) into a 3-stage smem
 //               ring; history ids prefetched one sample ahead; completion by mbarrier.
 //   warps 8-11  stager: thread t reads key row t from smem and writes [k_t | q * k_t] into the TMEM A slot (tcgen05.st).
 //   warp 12     MMA issuer: D1 = A W' (TS form, B resident in smem), D2 = H1 W2; two TMEM slots so that the epilogue of
 //               sample s overlaps the MMAs of s+1:   L1(s), L2(s-1), L1(s+1), L2(s), ...
-//   warps 0-3   epilogue: thread t owns TMEM lane t.  ep1: D1 + u -> PReLU -> TF32 back in place (A of layer 2);
-//               ep2: D2 + b2 -> PReLU -> . w3 -> mask -> softmax over the CTA's 128 lanes -> out = p @ keys (keys re-read
-//               from the smem stage) -> 4K bytes per sample to HBM.
+//   warps 0-3   epilogue 1: thread t owns TMEM lane t.  D1 + u -> PReLU -> TF32 back in place (A of layer 2).
+//   warps 13-16 epilogue 2: D2 + b2 -> PReLU -> . w3 -> mask -> softmax over the CTA's 128 lanes -> out = p @ keys (keys
+//               re-read from the smem stage) -> 4K bytes per sample to HBM.  Two warp groups so that the two epilogues
+//               of consecutive samples run concurrently.
 // All weights (W', W2, alpha1, alpha2, ...) stay resident in shared memory for the whole launch.
 // HBM traffic per sample = (T + 1) ids + (T + 1) rows + u + out; tensor work = 2 T (2K h1 + h1 h2) flop.
 #include "common.cuh"
@@ -29,7 +30,7 @@ using namespace tc;
 
 constexpr int DT_BM = 128;
 constexpr int DT_NRAW = 3;
-constexpr int DT_THREADS = 13 * 32;
+constexpr int DT_THREADS = 17 * 32;
 constexpr int DT_HDR_BYTES = 2048;            // per stage: ids[128] int32 | q[<=64] | u[<=96]
 constexpr int DT_HDR_Q = 512, DT_HDR_U = 1024;
 
@@ -162,6 +163,15 @@ __device__ __forceinline__ float4 dt_lds128(uint32_t addr) {
   asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
   return r;
 }
+__device__ __forceinline__ void dt_ld16_nowait(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void dt_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float dt_prelu(float v, float a) { return fmaxf(v, 0.f) + a * fminf(v, 0.f); }
 
 struct DinParams {
@@ -255,43 +265,51 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
 
   if (warp >= 4 && warp < 8) {
     // ================================================================ gather
+    // TPR threads share a key row, each copying PT consecutive 16-byte pieces of it; a thread serves NP rows per sample
+    // (K = 64: 4 threads x 4 pieces, 4 rows each).  History ids are fetched two samples ahead of the copies.
     const int tg = tid - 128;
     const int PPR = K / 4;                                   // 16-byte pieces per key row (2, 4, 8 or 16)
-    const int c = tg % PPR, rsub = tg / PPR, rpp = DT_BM / PPR;  // this thread: piece c of rows rsub + rpp * i, i < PPR
+    const int TPR = PPR >= 4 ? PPR / 4 : 1, PT = PPR / TPR;  // threads per row, pieces per thread
+    const int RPP = DT_BM / TPR, NP = TPR;                   // rows per pass, passes
+    const int q = tg % TPR, rsub = tg / TPR;
     const uint32_t rowbytes = (uint32_t)K * 4u;
-    auto fetch = [&](int64_t i, int32_t (&reg)[16]) {
+    auto fetch = [&](int64_t i, int32_t (&reg)[4]) {
       if (i >= n_my) return;
       const int64_t b = blockIdx.x + i * gridDim.x;
       const int32_t* src = static_cast<const int32_t*>(p.hist_ids) + b * p.hist_ld;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int r = rsub + rpp * j;
-        reg[j] = (j < PPR && r < T) ? __ldg(src + r) : 0;
+      for (int j = 0; j < 4; ++j) {
+        const int r = rsub + RPP * j;
+        reg[j] = (j < NP && r < T) ? __ldg(src + r) : 0;
       }
     };
-    auto issue = [&](int64_t i, const int32_t (&reg)[16]) {
+    auto issue = [&](int64_t i, const int32_t (&reg)[4]) {
       const int st = (int)(i % nraw);
       const int64_t b = blockIdx.x + i * gridDim.x;
       mbar_wait(raw_free(st), (uint32_t)((i / nraw) & 1) ^ 1u);
       const uint32_t stage = base + mp.stage0 + (uint32_t)st * mp.stage_bytes;
       const uint32_t hdr = stage + (uint32_t)s.nchK * DT_BM * 128u;
-      const uint32_t chunk = (uint32_t)(c >> 3) * (DT_BM * 128u), pc = (uint32_t)(c & 7);
+      int32_t* ids_s = reinterpret_cast<int32_t*>(bp + (hdr - base));
       bool bad = false;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        if (j < PPR) {
-          const int r = rsub + rpp * j;
+      for (int j = 0; j < 4; ++j) {
+        if (j < NP) {
+          const int r = rsub + RPP * j;
           const int64_t id = (IDKIND == CTRHOT_IDS_I32) ? (int64_t)reg[j] : (int64_t)__float2int_rz(__int_as_float(reg[j]));
           const bool live = r < T;
           const bool ok = live && id >= 0 && id < p.V;
           bad |= live && !ok;
-          cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
-                     ok ? (const void*)(reinterpret_cast<const char*>(p.table) + (uint64_t)id * rowbytes + (uint32_t)c * 16u)
-                        : (const void*)p.table, ok ? 16u : 0u);
-          if (c == 0) {
-            int32_t* ids_s = reinterpret_cast<int32_t*>(bp + (hdr - base));
-            ids_s[r] = live ? (int32_t)id : 0;
+          const char* src = reinterpret_cast<const char*>(p.table) + (ok ? (uint64_t)id * rowbytes : 0ull);
+          const uint32_t dst = stage + (uint32_t)r * 128u;
+          const uint32_t rx = (uint32_t)(r & 7);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            if (e < PT) {
+              const uint32_t c = (uint32_t)(q * PT + e);             // piece of the row: chunk c / 8, slot (c % 8) ^ rx
+              cp_async16(dst + (c >> 3) * (DT_BM * 128u) + (((c & 7u) ^ rx) << 4), src + c * 16u, ok ? 16u : 0u);
+            }
           }
+          if (q == 0) ids_s[r] = live ? (int32_t)id : 0;
         }
       }
       if (bad && p.err_flag) *p.err_flag = 1;
@@ -300,12 +318,12 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       cp_async_mbar_arrive_noinc(full_raw(st));
       mbar_arrive(full_raw(st));                             // releases the ids written with plain stores
     };
-    int32_t ra[16], rb[16];
-    fetch(0, ra);
-    for (int64_t i = 0; i < n_my; i += 2) {
-      fetch(i + 1, rb);
-      issue(i, ra);
-      if (i + 1 < n_my) { fetch(i + 2, ra); issue(i + 1, rb); }
+    int32_t ra[4], rb[4], rc[4];
+    fetch(0, ra); fetch(1, rb);
+    for (int64_t i = 0; i < n_my; i += 3) {
+      fetch(i + 2, rc); issue(i, ra);
+      if (i + 1 < n_my) { fetch(i + 3, ra); issue(i + 1, rb); }
+      if (i + 2 < n_my) { fetch(i + 4, rb); issue(i + 2, rc); }
     }
   } else if (warp >= 8 && warp < 12) {
     // ================================================================ stager: keys -> TMEM A slot [k | q * k]
@@ -370,38 +388,60 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       if (n_my > 0) layer2(n_my - 1);
     }
     __syncwarp();
-  } else {
-    // ================================================================ epilogue (warps 0-3): thread t = TMEM lane t
+  } else if (warp < 4) {
+    // ================================================================ epilogue 1 (warps 0-3): thread t = TMEM lane t
     const int t = tid;
     const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
     const float* al1 = reinterpret_cast<const float*>(bp + mp.al1) + (size_t)(t < T ? t : 0) * s.S1;
-    const float* al2 = reinterpret_cast<const float*>(bp + mp.al2) + (size_t)(t < T ? t : 0) * s.S2;
-    auto ep1 = [&](int64_t i) {
+    const bool exact = (s.h1 == s.N1p);
+    auto chunk = [&](uint32_t (&r)[16], int n0, const float* u, uint32_t d_t) {
+      float acc[16];
+#pragma unroll
+      for (int j = 0; j < 16; j += 4) {
+        const float4 uu = *reinterpret_cast<const float4*>(u + n0 + j);
+        const float4 aa = *reinterpret_cast<const float4*>(al1 + n0 + j);
+        acc[j + 0] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 0]) + uu.x, aa.x));
+        acc[j + 1] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 1]) + uu.y, aa.y));
+        acc[j + 2] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 2]) + uu.z, aa.z));
+        acc[j + 3] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 3]) + uu.w, aa.w));
+      }
+      if (!exact) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) if (n0 + j >= s.h1) acc[j] = 0.f;
+      }
+      tmem_st16(d_t + (uint32_t)n0, acc);
+    };
+    for (int64_t i = 0; i < n_my; ++i) {
       const int st = (int)(i % nraw), slot = (int)(i & 1);
       const float* u = reinterpret_cast<const float*>(bp + mp.stage0 + (uint32_t)st * mp.stage_bytes +
                                                       (uint32_t)s.nchK * DT_BM * 128u + DT_HDR_U);
       mbar_wait(d1_full(slot), (uint32_t)((i >> 1) & 1));
       tc_fence_after();
       const uint32_t d_t = t_lane + (uint32_t)(slot * s.slot_cols + s.c_d1);
-      for (int n0 = 0; n0 < s.N1p; n0 += 16) {
-        float acc[16];
-        tmem_ld16(d_t + (uint32_t)n0, acc);
-#pragma unroll
-        for (int j = 0; j < 16; j += 4) {
-          const float4 uu = *reinterpret_cast<const float4*>(u + n0 + j);
-          const float4 aa = *reinterpret_cast<const float4*>(al1 + n0 + j);
-          acc[j + 0] = (n0 + j + 0 < s.h1) ? to_tf32_rna(dt_prelu(acc[j + 0] + uu.x, aa.x)) : 0.f;
-          acc[j + 1] = (n0 + j + 1 < s.h1) ? to_tf32_rna(dt_prelu(acc[j + 1] + uu.y, aa.y)) : 0.f;
-          acc[j + 2] = (n0 + j + 2 < s.h1) ? to_tf32_rna(dt_prelu(acc[j + 2] + uu.z, aa.z)) : 0.f;
-          acc[j + 3] = (n0 + j + 3 < s.h1) ? to_tf32_rna(dt_prelu(acc[j + 3] + uu.w, aa.w)) : 0.f;
-        }
-        tmem_st16(d_t + (uint32_t)n0, acc);
+      uint32_t r0[16], r1[16];                              // two chunks in flight: load n+1 while n is processed
+      dt_ld16_nowait(d_t, r0);
+      dt_ld_wait();
+      for (int n0 = 0; n0 < s.N1p; n0 += 32) {
+        if (n0 + 16 < s.N1p) dt_ld16_nowait(d_t + (uint32_t)(n0 + 16), r1);
+        chunk(r0, n0, u, d_t);
+        dt_ld_wait();
+        if (n0 + 32 < s.N1p) dt_ld16_nowait(d_t + (uint32_t)(n0 + 32), r0);
+        if (n0 + 16 < s.N1p) chunk(r1, n0 + 16, u, d_t);
+        dt_ld_wait();
       }
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(h1_ready(slot));
-    };
-    auto ep2 = [&](int64_t i) {
+    }
+  } else {
+    // ================================================================ epilogue 2 (warps 13-16): scores, softmax, weighted sum
+    const int q4 = warp & 3;
+    const int t = q4 * 32 + lane;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
+    const float* al2 = reinterpret_cast<const float*>(bp + mp.al2) + (size_t)(t < T ? t : 0) * s.S2;
+    const int G = DT_BM / K, c = t % K, g = t / K;
+    const uint32_t pc = (uint32_t)((c & 31) >> 2), ce = (uint32_t)(c & 3);
+    for (int64_t i = 0; i < n_my; ++i) {
       const int st = (int)(i % nraw), slot = (int)(i & 1);
       const int64_t b = blockIdx.x + i * gridDim.x;
       const uint32_t stage_off = mp.stage0 + (uint32_t)st * mp.stage_bytes;
@@ -433,28 +473,32 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       float m = sc;
 #pragma unroll
       for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-      if (lane == 0) s_red[warp] = m;
+      if (lane == 0) s_red[q4] = m;
       named_bar_sync(1, 128);
       m = fmaxf(fmaxf(s_red[0], s_red[1]), fmaxf(s_red[2], s_red[3]));
       const float e = live ? __expf(sc - m) : 0.f;
       float sum = e;
 #pragma unroll
       for (int o = 16; o >= 1; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-      if (lane == 0) s_red[4 + warp] = sum;
+      if (lane == 0) s_red[4 + q4] = sum;
       named_bar_sync(1, 128);
       sum = (s_red[4] + s_red[5]) + (s_red[6] + s_red[7]);
       s_P[t] = e / sum;
       named_bar_sync(1, 128);
       // out[c] = sum_t p_t k[t][c]: thread = (column c, group g of rows t = g, g + G, ...)
-      const int G = DT_BM / K, c = t % K, g = t / K;
       const uint8_t* kt = bp + stage_off + (uint32_t)(c >> 5) * (DT_BM * 128u);
-      const uint32_t pc = (uint32_t)((c & 31) >> 2), ce = (uint32_t)(c & 3);
-      float acc = 0.f;
-      for (int r = g; r < T; r += G) {
-        const float kv = *reinterpret_cast<const float*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4) + ce * 4u);
-        acc = fmaf(s_P[r], kv, acc);
+      float acc0 = 0.f, acc1 = 0.f;
+      int r = g;
+#pragma unroll 4
+      for (; r + G < T; r += 2 * G) {
+        const float k0 = *reinterpret_cast<const float*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4) + ce * 4u);
+        const float k1 = *reinterpret_cast<const float*>(kt + (uint32_t)(r + G) * 128u + ((pc ^ (uint32_t)((r + G) & 7)) << 4) + ce * 4u);
+        acc0 = fmaf(s_P[r], k0, acc0);
+        acc1 = fmaf(s_P[r + G], k1, acc1);
       }
-      s_part[t] = acc;
+      if (r < T)
+        acc0 = fmaf(s_P[r], *reinterpret_cast<const float*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4) + ce * 4u), acc0);
+      s_part[t] = acc0 + acc1;
       named_bar_sync(1, 128);
       if (t < K) {
         float o = 0.f;
@@ -462,12 +506,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
         p.out[b * p.out_ld + t] = o;
       }
       mbar_arrive(raw_free(st));
-    };
-    for (int64_t i = 0; i < n_my; ++i) {
-      ep1(i);
-      if (i > 0) ep2(i - 1);
     }
-    if (n_my > 0) ep2(n_my - 1);
   }
   tc_fence_before();
   __syncthreads();
