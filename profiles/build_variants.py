@@ -19,13 +19,18 @@ OUT = os.path.join(B.OBJ, "variants")
 def main(specs):
     os.makedirs(OUT, exist_ok=True)
     B.build_lib(verbose=False)
-    others = [os.path.join(B.OBJ, s[:-3] + ".o") for s in B._sources() if s != "fused.cu"]
+    src_name = "fused.cu"
+    if specs and specs[0].startswith("src="):
+        src_name, specs = specs[0][4:], specs[1:]
+    others = [os.path.join(B.OBJ, s[:-3] + ".o") for s in B._sources() if s != src_name]
     for spec in specs:
         tag = spec.replace("=", "").replace(",", "_")
-        defs = [("-DFU_TRACE" if kv == "TRACE=1" else "-DFU_%s_=%s" % tuple(kv.split("="))) for kv in spec.split(",")]
-        obj = os.path.join(OUT, "fused_%s.o" % tag)
+        defs = [(("-DFU_TRACE" if src_name == "fused.cu" else "-DDT_TRACE") if kv == "TRACE=1" else "-DDT_FIXED_ORDER" if kv == "FIXED=1" else "-DDT_OLD_WSUM" if kv == "OLDW=1" else "-DDT_LATE_ARRIVE" if kv == "LATE=1" else "-DDT_OLD_STAGER" if kv == "OLDS=1"
+                 else "-DFU_%s_=%s" % tuple(kv.split("="))) for kv in spec.split(",")]
+        obj = os.path.join(OUT, "%s_%s.o" % (src_name[:-3], tag))
+        tag = src_name[:-3] + "_" + tag if src_name != "fused.cu" else tag
         lib = os.path.join(OUT, "libctrhot_%s.so" % tag)
-        subprocess.check_call([B.NVCC] + B.FLAGS + defs + ["-c", os.path.join(B.CSRC, "fused.cu"), "-o", obj])
+        subprocess.check_call([B.NVCC] + B.FLAGS + defs + ["-c", os.path.join(B.CSRC, src_name), "-o", obj])
         subprocess.check_call([B.NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib, obj] + others)
         print(lib)
 

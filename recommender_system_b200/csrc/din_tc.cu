@@ -199,12 +199,20 @@ __host__ __device__ inline DinSmem din_smem(const DinShape& s, int nraw) {
   m.stage0 = o; o += (uint32_t)nraw * m.stage_bytes;
   m.al1 = o; o += (uint32_t)s.T * s.S1 * 4u;
   m.al2 = o; o += (uint32_t)s.T * s.S2 * 4u;
-  m.small = o; o += (uint32_t)(2 * s.N2p + 4 + DT_BM + 16 + DT_BM) * 4u;     // b2 | w3 | b3 | P[128] | red[16] | part[128]
+  m.small = o; o += (uint32_t)(2 * s.N2p + 4 + DT_BM + 16 + 4 * DT_BM) * 4u; // b2 | w3 | b3 | P[128] | red[16] | part[512]
   o = (o + 15u) & ~15u;
   m.bars = o; o += 8u * (2 * DT_NRAW + 12) + 16u;
   m.total = o;
   return m;
 }
+
+#ifdef DT_TRACE
+// tuning builds only: clock64 of pipeline events of CTA 0, [event][sample]
+__device__ long long dt_trace[8][128];
+#define DT_MARK(ev, i) do { if (blockIdx.x == 0 && (i) < 128 && (threadIdx.x & 31) == 0) dt_trace[ev][i] = clock64(); } while (0)
+#else
+#define DT_MARK(ev, i) do { } while (0)
+#endif
 
 template <int IDKIND>
 __global__ void __launch_bounds__(DT_THREADS, 1)
@@ -265,65 +273,54 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
 
   if (warp >= 4 && warp < 8) {
     // ================================================================ gather
-    // TPR threads share a key row, each copying PT consecutive 16-byte pieces of it; a thread serves NP rows per sample
-    // (K = 64: 4 threads x 4 pieces, 4 rows each).  History ids are fetched two samples ahead of the copies.
+    // Thread tg fetches the history id of row tg (two samples ahead), the 128 ids go through the stage header (the mask
+    // needs them there anyway); then PPR adjacent threads copy one key row together (coalesced 16-byte pieces).
     const int tg = tid - 128;
     const int PPR = K / 4;                                   // 16-byte pieces per key row (2, 4, 8 or 16)
-    const int TPR = PPR >= 4 ? PPR / 4 : 1, PT = PPR / TPR;  // threads per row, pieces per thread
-    const int RPP = DT_BM / TPR, NP = TPR;                   // rows per pass, passes
-    const int q = tg % TPR, rsub = tg / TPR;
+    const int c = tg % PPR, rsub = tg / PPR, rpp = DT_BM / PPR;  // this thread: piece c of rows rsub + rpp * j, j < PPR
     const uint32_t rowbytes = (uint32_t)K * 4u;
-    auto fetch = [&](int64_t i, int32_t (&reg)[4]) {
-      if (i >= n_my) return;
+    const uint32_t chunk = (uint32_t)(c >> 3) * (DT_BM * 128u), pc = (uint32_t)(c & 7);
+    auto fetch = [&](int64_t i) -> int32_t {
+      if (i >= n_my || tg >= T) return 0;
       const int64_t b = blockIdx.x + i * gridDim.x;
-      const int32_t* src = static_cast<const int32_t*>(p.hist_ids) + b * p.hist_ld;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int r = rsub + RPP * j;
-        reg[j] = (j < NP && r < T) ? __ldg(src + r) : 0;
-      }
+      return __ldg(static_cast<const int32_t*>(p.hist_ids) + b * p.hist_ld + tg);
     };
-    auto issue = [&](int64_t i, const int32_t (&reg)[4]) {
+    auto issue = [&](int64_t i, int32_t raw_id) {
       const int st = (int)(i % nraw);
       const int64_t b = blockIdx.x + i * gridDim.x;
       mbar_wait(raw_free(st), (uint32_t)((i / nraw) & 1) ^ 1u);
       const uint32_t stage = base + mp.stage0 + (uint32_t)st * mp.stage_bytes;
       const uint32_t hdr = stage + (uint32_t)s.nchK * DT_BM * 128u;
       int32_t* ids_s = reinterpret_cast<int32_t*>(bp + (hdr - base));
-      bool bad = false;
+      {
+        const int32_t id = (IDKIND == CTRHOT_IDS_I32) ? raw_id : __float2int_rz(__int_as_float(raw_id));
+        const bool ok = tg >= T || (id >= 0 && (int64_t)id < p.V);
+        if (!ok && p.err_flag) *p.err_flag = 1;
+        ids_s[tg] = (tg < T) ? (ok ? id : -1) : 0;           // -1: out of range -> zero row, not masked
+      }
+      named_bar_sync(2, 128);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (j < NP) {
-          const int r = rsub + RPP * j;
-          const int64_t id = (IDKIND == CTRHOT_IDS_I32) ? (int64_t)reg[j] : (int64_t)__float2int_rz(__int_as_float(reg[j]));
-          const bool live = r < T;
-          const bool ok = live && id >= 0 && id < p.V;
-          bad |= live && !ok;
-          const char* src = reinterpret_cast<const char*>(p.table) + (ok ? (uint64_t)id * rowbytes : 0ull);
-          const uint32_t dst = stage + (uint32_t)r * 128u;
-          const uint32_t rx = (uint32_t)(r & 7);
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            if (e < PT) {
-              const uint32_t c = (uint32_t)(q * PT + e);             // piece of the row: chunk c / 8, slot (c % 8) ^ rx
-              cp_async16(dst + (c >> 3) * (DT_BM * 128u) + (((c & 7u) ^ rx) << 4), src + c * 16u, ok ? 16u : 0u);
-            }
-          }
-          if (q == 0) ids_s[r] = live ? (int32_t)id : 0;
+      for (int j = 0; j < 16; ++j) {
+        if (j < PPR) {
+          const int r = rsub + rpp * j;
+          const int32_t id = ids_s[r];
+          const bool ok = r < T && id >= 0;
+          cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
+                     reinterpret_cast<const char*>(p.table) + (ok ? (uint64_t)(uint32_t)id * rowbytes : 0ull) + (uint32_t)c * 16u,
+                     ok ? 16u : 0u);
         }
       }
-      if (bad && p.err_flag) *p.err_flag = 1;
       if (tg < PPR) cp_async16(hdr + DT_HDR_Q + tg * 16u, p.item + b * p.item_ld + tg * 4, 16u);
       else if (tg < PPR + s.N1p / 4) cp_async16(hdr + DT_HDR_U + (tg - PPR) * 16u, p.U + b * s.N1p + (tg - PPR) * 4, 16u);
       cp_async_mbar_arrive_noinc(full_raw(st));
       mbar_arrive(full_raw(st));                             // releases the ids written with plain stores
+      if (tg == 0) DT_MARK(0, i);
     };
-    int32_t ra[4], rb[4], rc[4];
-    fetch(0, ra); fetch(1, rb);
+    int32_t ra = fetch(0), rb = fetch(1), rc;
     for (int64_t i = 0; i < n_my; i += 3) {
-      fetch(i + 2, rc); issue(i, ra);
-      if (i + 1 < n_my) { fetch(i + 3, ra); issue(i + 1, rb); }
-      if (i + 2 < n_my) { fetch(i + 4, rb); issue(i + 2, rc); }
+      rc = fetch(i + 2); issue(i, ra);
+      if (i + 1 < n_my) { ra = fetch(i + 3); issue(i + 1, rb); }
+      if (i + 2 < n_my) { rb = fetch(i + 4); issue(i + 2, rc); }
     }
   } else if (warp >= 8 && warp < 12) {
     // ================================================================ stager: keys -> TMEM A slot [k | q * k]
@@ -335,10 +332,13 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       const uint32_t stage = base + mp.stage0 + (uint32_t)st * mp.stage_bytes;
       const uint32_t hq = stage + (uint32_t)s.nchK * DT_BM * 128u + DT_HDR_Q;
       mbar_wait(full_raw(st), (uint32_t)((i / nraw) & 1));
+      if (t == 0) DT_MARK(1, i);
       mbar_wait(a_free(slot), (uint32_t)((i >> 1) & 1) ^ 1u);
       tc_fence_after();
       const uint32_t a_t = t_lane + (uint32_t)(slot * s.slot_cols + s.c_a);
-      for (int g = 0; g < K / 8; ++g) {
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        if (g >= K / 8) break;
         const uint32_t row = stage + (uint32_t)(g >> 2) * (DT_BM * 128u) + (uint32_t)t * 128u;
         const uint32_t p0 = (uint32_t)((2 * g) & 7), p1 = p0 + 1;
         const float4 k0 = dt_lds128(row + ((p0 ^ rx) << 4)), k1 = dt_lds128(row + ((p1 ^ rx) << 4));
@@ -351,6 +351,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(a_full(slot));
+      if (t == 0) DT_MARK(2, i);
     }
   } else if (warp == 12) {
     // ================================================================ MMA issuer: L1(i), L2(i-1), L1(i+1), ...
@@ -359,9 +360,6 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       const uint32_t wa = base + mp.wa, w2 = base + mp.w2;
       auto layer2 = [&](int64_t i) {
         const int slot = (int)(i & 1);
-        const uint32_t ph = (uint32_t)((i >> 1) & 1);
-        mbar_wait(h1_ready(slot), ph);
-        mbar_wait(d2_free(slot), ph ^ 1u);
         tc_fence_after();
         const uint32_t a_t = tmem_base + (uint32_t)(slot * s.slot_cols + s.c_d1);
         const uint32_t d_t = tmem_base + (uint32_t)(slot * s.slot_cols + s.c_d2);
@@ -371,9 +369,8 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
         }
         mma_commit(d2_full(slot));
       };
-      for (int64_t i = 0; i < n_my; ++i) {
+      auto layer1 = [&](int64_t i) {
         const int slot = (int)(i & 1);
-        mbar_wait(a_full(slot), (uint32_t)((i >> 1) & 1));
         tc_fence_after();
         const uint32_t a_t = tmem_base + (uint32_t)(slot * s.slot_cols + s.c_a);
         const uint32_t d_t = tmem_base + (uint32_t)(slot * s.slot_cols + s.c_d1);
@@ -383,9 +380,20 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
         }
         mma_commit(a_free(slot));
         mma_commit(d1_full(slot));
-        if (i > 0) layer2(i - 1);
+      };
+      // Whatever is ready goes first, finishing samples before starting new ones: L2(i2) needs H1(i2) and a free D2 slot;
+      // L1(i1) needs A(i1) and must not overwrite H1(i1 - 2) before L2(i1 - 2) was issued (two TMEM slots).
+      int64_t i1 = 0, i2 = 0;
+      while (i2 < n_my) {
+        if (i2 < i1) {
+          const int slot = (int)(i2 & 1);
+          const uint32_t ph = (uint32_t)((i2 >> 1) & 1);
+          if (mbar_try_wait(h1_ready(slot), ph) && mbar_try_wait(d2_free(slot), ph ^ 1u)) { layer2(i2); ++i2; continue; }
+        }
+        if (i1 < n_my && i1 - i2 < 2) {
+          if (mbar_try_wait(a_full((int)(i1 & 1)), (uint32_t)((i1 >> 1) & 1))) { layer1(i1); ++i1; }
+        }
       }
-      if (n_my > 0) layer2(n_my - 1);
     }
     __syncwarp();
   } else if (warp < 4) {
@@ -416,6 +424,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       const float* u = reinterpret_cast<const float*>(bp + mp.stage0 + (uint32_t)st * mp.stage_bytes +
                                                       (uint32_t)s.nchK * DT_BM * 128u + DT_HDR_U);
       mbar_wait(d1_full(slot), (uint32_t)((i >> 1) & 1));
+      if (t == 0) DT_MARK(3, i);
       tc_fence_after();
       const uint32_t d_t = t_lane + (uint32_t)(slot * s.slot_cols + s.c_d1);
       uint32_t r0[16], r1[16];                              // two chunks in flight: load n+1 while n is processed
@@ -432,6 +441,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(h1_ready(slot));
+      if (t == 0) DT_MARK(4, i);
     }
   } else {
     // ================================================================ epilogue 2 (warps 13-16): scores, softmax, weighted sum
@@ -439,14 +449,14 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
     const int t = q4 * 32 + lane;
     const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
     const float* al2 = reinterpret_cast<const float*>(bp + mp.al2) + (size_t)(t < T ? t : 0) * s.S2;
-    const int G = DT_BM / K, c = t % K, g = t / K;
-    const uint32_t pc = (uint32_t)((c & 31) >> 2), ce = (uint32_t)(c & 3);
+    const int NQ = K / 4, G = DT_BM / NQ, cq = t % NQ, g = t / NQ;   // column quads, row groups
     for (int64_t i = 0; i < n_my; ++i) {
       const int st = (int)(i % nraw), slot = (int)(i & 1);
       const int64_t b = blockIdx.x + i * gridDim.x;
       const uint32_t stage_off = mp.stage0 + (uint32_t)st * mp.stage_bytes;
       const int32_t* ids_s = reinterpret_cast<const int32_t*>(bp + stage_off + (uint32_t)s.nchK * DT_BM * 128u);
       mbar_wait(d2_full(slot), (uint32_t)((i >> 1) & 1));
+      if (lane == 0 && q4 == 0) DT_MARK(5, i);
       tc_fence_after();
       const uint32_t d_t = t_lane + (uint32_t)(slot * s.slot_cols + s.c_d2);
       float sc = s_b3[0];
@@ -485,27 +495,34 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       sum = (s_red[4] + s_red[5]) + (s_red[6] + s_red[7]);
       s_P[t] = e / sum;
       named_bar_sync(1, 128);
-      // out[c] = sum_t p_t k[t][c]: thread = (column c, group g of rows t = g, g + G, ...)
-      const uint8_t* kt = bp + stage_off + (uint32_t)(c >> 5) * (DT_BM * 128u);
-      float acc0 = 0.f, acc1 = 0.f;
-      int r = g;
-#pragma unroll 4
-      for (; r + G < T; r += 2 * G) {
-        const float k0 = *reinterpret_cast<const float*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4) + ce * 4u);
-        const float k1 = *reinterpret_cast<const float*>(kt + (uint32_t)(r + G) * 128u + ((pc ^ (uint32_t)((r + G) & 7)) << 4) + ce * 4u);
-        acc0 = fmaf(s_P[r], k0, acc0);
-        acc1 = fmaf(s_P[r + G], k1, acc1);
+      // out[c] = sum_t p_t k[t][c]: thread = (four columns 4 cq .., group g of rows t = g, g + G, ...)
+      {
+        const uint8_t* kt = bp + stage_off + (uint32_t)(cq >> 3) * (DT_BM * 128u);
+        const uint32_t pq = (uint32_t)(cq & 7);
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+        int r = g;
+        for (; r + G < T; r += 2 * G) {
+          const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pq ^ (uint32_t)(r & 7)) << 4));
+          const float4 k1 = *reinterpret_cast<const float4*>(kt + (uint32_t)(r + G) * 128u + ((pq ^ (uint32_t)((r + G) & 7)) << 4));
+          const float p0 = s_P[r], p1 = s_P[r + G];
+          a0.x = fmaf(p0, k0.x, a0.x); a0.y = fmaf(p0, k0.y, a0.y); a0.z = fmaf(p0, k0.z, a0.z); a0.w = fmaf(p0, k0.w, a0.w);
+          a1.x = fmaf(p1, k1.x, a1.x); a1.y = fmaf(p1, k1.y, a1.y); a1.z = fmaf(p1, k1.z, a1.z); a1.w = fmaf(p1, k1.w, a1.w);
+        }
+        if (r < T) {
+          const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pq ^ (uint32_t)(r & 7)) << 4));
+          const float p0 = s_P[r];
+          a0.x = fmaf(p0, k0.x, a0.x); a0.y = fmaf(p0, k0.y, a0.y); a0.z = fmaf(p0, k0.z, a0.z); a0.w = fmaf(p0, k0.w, a0.w);
+        }
+        *reinterpret_cast<float4*>(s_part + (size_t)g * K + 4 * cq) = make_float4(a0.x + a1.x, a0.y + a1.y, a0.z + a1.z, a0.w + a1.w);
       }
-      if (r < T)
-        acc0 = fmaf(s_P[r], *reinterpret_cast<const float*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4) + ce * 4u), acc0);
-      s_part[t] = acc0 + acc1;
       named_bar_sync(1, 128);
+      mbar_arrive(raw_free(st));                             // keys no longer needed: the gather may refill the stage
       if (t < K) {
         float o = 0.f;
         for (int gg = 0; gg < G; ++gg) o += s_part[gg * K + t];
         p.out[b * p.out_ld + t] = o;
       }
-      mbar_arrive(raw_free(st));
+      if (lane == 0 && q4 == 0) DT_MARK(6, i);
     }
   }
   tc_fence_before();
@@ -606,3 +623,9 @@ extern "C" int ctrhot_din_attention_gather_tf32(const float* table, int64_t V, i
   CTRHOT_LAUNCH_OK("ctrhot_din_attention_gather_tf32");
   return CTRHOT_OK;
 }
+
+#ifdef DT_TRACE
+extern "C" int ctrhot_debug_din_trace(long long* h_out) {
+  return cudaMemcpyFromSymbol(h_out, ctrhot::dt_trace, sizeof(long long) * 8 * 128) == cudaSuccess ? 0 : -3;
+}
+#endif
