@@ -99,6 +99,67 @@ def cpu_weights(m):
     return tables, fm, hidden, out
 
 
+def secondary(dev, rank):
+    """The other half of BASELINE.json's metric, on one GPU, device-resident inputs, CUDA events:
+    DIN forward samples/s (config 4: B=16384, T=100, emb 64, attention 80-40, tcgen05 unit) and the standalone
+    embedding gather's GB/s against the measured HBM peak (64-byte rows, kaggle vocabulary; rows read + rows written)."""
+    import torch
+    from recommender_system_b200 import _lib
+    from recommender_system_b200.layer import set_seed
+    from recommender_system_b200.layer.core import EmbedLayer
+    from recommender_system_b200.model.din import DIN
+    from recommender_system_b200.utils import synth
+    pk = peaks()
+
+    def timeit(fn, steps, warm):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    out = {}
+    set_seed(1)
+    Bd, T, v_item = 16384, 100, 10_000_000
+    m = DIN(synth.din_feature_columns(v_item=v_item), ["movies_seq"], (80, 40), (256, 128, 64), "prelu", "prelu", 0.0,
+            precision="tf32", check_ids=False, device=dev)
+    ins = []
+    for i in range(3):
+        d = synth.din_batch(Bd, T, v_item=v_item, seed=11 + i)
+        ins.append({k: torch.from_numpy(v).to(dev) for k, v in d.items()})
+    m(ins[0])
+    it = [0]
+
+    def run_din():
+        m(ins[it[0] % 3]); it[0] += 1
+    l0 = _lib.LAUNCHES[0]
+    ms = timeit(run_din, 20, 3)
+    algo = 26528                                              # SURVEY 8(d) cfg 4: ids + 102 rows of 256 B + output
+    out["din_cfg4"] = {"metric": "DIN forward samples/s", "value": Bd / ms * 1e3, "ms_per_step": ms, "batch": Bd,
+                       "workload": "din_amazon_T100_k64_att80-40_B16384, item vocab 10M (HBM-resident)",
+                       "launches_per_step": (_lib.LAUNCHES[0] - l0) / 23.0,
+                       "hbm_frac": algo * Bd / ms / 1e6 / pk["hbm_gbs"],
+                       "tensor_TFLOPs": 4.95e6 * Bd / ms / 1e9}
+    del m, ins
+    set_seed(1)
+    B, k = 65536, 16
+    E = EmbedLayer(synth.criteo_feature_columns(synth.KAGGLE_VOCAB, k)[1], k=k, check_ids=False, device=dev)
+    idb = [torch.from_numpy(synth.criteo_batch(B, synth.KAGGLE_VOCAB, seed=7 + i)[1]).to(dev) for i in range(4)]
+
+    def run_gather():
+        E(idb[it[0] % 4]); it[0] += 1
+    ms = timeit(run_gather, 30, 5)
+    gbs = (26 * 4 + 2 * 26 * 4 * k) * B / ms / 1e6
+    out["gather_k16"] = {"metric": "EmbedLayer gather GB/s (ids + rows read + rows written)", "value": gbs, "ms": ms,
+                         "hbm_frac": gbs / pk["hbm_gbs"], "rows": "64 B, uniform ids over 33.8 M rows (2.16 GB)"}
+    return out
+
+
 def time_cpu(fn, inputs_list, budget_s=20.0, min_reps=2):
     """median-free throughput: total samples / total time over >= min_reps passes within the budget."""
     fn(inputs_list[0])                                    # warm-up
@@ -172,6 +233,7 @@ def main():
     ap.add_argument("--precision", default="tf32", choices=["tf32", "fp32"])
     ap.add_argument("--cpu-batch", type=int, default=16384)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the DIN / gather lines under \"also\"")
     ap.add_argument("--cluster", type=int, default=0, help="CTAs sharing each weight chunk by TMA multicast (0 = auto)")
     ap.add_argument("--two-kernel", action="store_true", help="front (gather+FM) + tower kernels instead of the fused one")
     args = ap.parse_args()
@@ -242,17 +304,25 @@ def main():
         tower_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
     model.check_ids()
 
-    # ---- end to end through the public API with HOST (pinned) buffers: H2D + forward + D2H every step
-    for i in range(2):
-        model(pinned[i % NB]).cpu()
+    # ---- end to end through the public API with HOST (pinned) buffers: every step copies its own inputs host->device and
+    # its probabilities device->host; HostPipeline keeps three batches in flight so the copies overlap the kernel
+    from recommender_system_b200.utils.pipeline import HostPipeline
+    pipe = HostPipeline(model, B, depth=3)
+    for i in range(3):
+        pipe.result(pipe.submit(*pinned[i % NB]))
     barrier()
     t0 = time.perf_counter()
+    tickets, checksum = [], 0.0
     for i in range(K):
-        res = model(pinned[i % NB]).cpu()
+        tickets.append(pipe.submit(*pinned[i % NB]))
+        if i >= 2:
+            checksum += float(pipe.result(tickets[i - 2])[0, 0])     # the step's result is read on the host
+    for r in pipe.drain():
+        checksum += float(r[0, 0])
     torch.cuda.synchronize()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
-    h2d = B * 13 * 4 + B * 26 * 4
-    d2h = B * 4
+    h2d, d2h = pipe.h2d_bytes, pipe.d2h_bytes
+    also = secondary(dev, rank) if (world == 1 and not args.no_secondary) else None
 
     if rank == 0:
         pk = peaks()
@@ -267,7 +337,7 @@ def main():
                   "bound": "hbm", "achieved": algo * B / (whole_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
                   "traffic": None, "ms": whole_ms, "peak_src": pk["src"]}
             hb["frac"] = hb["achieved"] / hb["peak"]
-            fm_flops = 2 * d * 48                        # side columns: three N<=32 MMAs per K step
+            fm_flops = 2 * d * 21                        # FM = 2 * 429 * 21 (the split-TF32 extras are not counted)
             tn = {"kernel": hb["kernel"], "bound": "tensor", "achieved": (flops + fm_flops) * B / (whole_ms * 1e-3) / 1e12,
                   "peak": tf32_peak, "unit": "TFLOP/s", "traffic": None, "ms": whole_ms,
                   "peak_src": pk["src"] + " bf16 dense / 2 (TF32 runs at half the bf16 rate)"}
@@ -293,6 +363,8 @@ def main():
                 "e2e": {"value": total / t_e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h},
                 "gpu_launches": launches, "clocks": clocks, "roofline": dom, "roofline_other": other}
+        if also:
+            line["also"] = also
         if world == 1 and not args.no_cpu_baseline:
             from oracle import cpu_ref_torch as R
             torch.set_num_threads(os.cpu_count() or 1)

@@ -121,33 +121,52 @@ __global__ void din_pack_kernel(const float* __restrict__ W1, const float* __res
   }
 }
 
-// ---------------------------------------------------------------- prep: candidate gather + u = q Wq + b1, one warp per sample
+// ---------------------------------------------------------------- prep: candidate gather + u = q Wq + b1
+// One CTA = DP_S samples: the candidate rows are gathered (coalesced, and written to item_out), kept in shared memory,
+// then thread (column n, sample group) forms u[s][n] for its samples with one Wq load per (c, n) shared by all of them.
+constexpr int DP_S = 32;          // samples per CTA
+constexpr int DP_T = 256;
 template <int IDKIND>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(DP_T)
 din_prep_kernel(const float* __restrict__ table, int64_t V, int K, const void* __restrict__ cand_ids, int64_t cand_ld,
                 int64_t B, const float* __restrict__ Wq, const float* __restrict__ b1, int N1p,
                 float* __restrict__ item_out, int64_t item_ld, float* __restrict__ U, int* __restrict__ err_flag) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
-  for (int64_t b = warp; b < B; b += nwarps) {
-    const int64_t id = IdLoad<IDKIND>::at(cand_ids, b * cand_ld);
-    const bool ok = id >= 0 && id < V;
-    if (!ok && err_flag && lane == 0) *err_flag = 1;
-    float q0 = 0.f, q1 = 0.f;                                     // lane holds q[lane], q[lane + 32]
-    if (ok && lane < K) q0 = ldg_nc_f1(table + id * K + lane);
-    if (ok && lane + 32 < K) q1 = ldg_nc_f1(table + id * K + lane + 32);
-    if (lane < K) item_out[b * item_ld + lane] = q0;
-    if (lane + 32 < K) item_out[b * item_ld + lane + 32] = q1;
-    for (int n0 = 0; n0 < N1p; n0 += 32) {
-      const int n = n0 + lane;
-      float acc = (n < N1p) ? __ldg(b1 + n) : 0.f;
-      for (int c = 0; c < K; ++c) {
-        const float qc = __shfl_sync(0xffffffffu, c < 32 ? q0 : q1, c & 31);
-        if (n < N1p) acc = fmaf(qc, __ldg(Wq + (size_t)c * N1p + n), acc);
-      }
-      if (n < N1p) U[b * N1p + n] = acc;
+  __shared__ float sq[DP_S][64 + 1];
+  const int tid = threadIdx.x;
+  const int64_t b0 = (int64_t)blockIdx.x * DP_S;
+  for (int e = tid; e < DP_S * K; e += DP_T) {
+    const int s = e / K, c = e - s * K;
+    const int64_t b = b0 + s;
+    float v = 0.f;
+    if (b < B) {
+      const int64_t id = IdLoad<IDKIND>::at(cand_ids, b * cand_ld);
+      const bool ok = id >= 0 && id < V;
+      if (!ok && err_flag && c == 0) *err_flag = 1;
+      if (ok) v = ldg_nc_f1(table + id * K + c);
+      item_out[b * item_ld + c] = v;
     }
+    sq[s][c] = v;
+  }
+  __syncthreads();
+  const int groups = DP_T / N1p;                      // column n = tid % N1p, sample group = tid / N1p
+  const int n = tid % N1p, g = tid / N1p;
+  if (g >= groups) return;
+  constexpr int MAXS = 16;
+  const int per = (DP_S + groups - 1) / groups;       // samples per group (<= MAXS for N1p <= 96 -> groups >= 2)
+  float acc[MAXS];
+  const float bias = __ldg(b1 + n);
+#pragma unroll
+  for (int i = 0; i < MAXS; ++i) acc[i] = bias;
+  for (int c = 0; c < K; ++c) {
+    const float w = __ldg(Wq + (size_t)c * N1p + n);
+#pragma unroll
+    for (int i = 0; i < MAXS; ++i)
+      if (i < per) acc[i] = fmaf(sq[(g * per + i) % DP_S][c], w, acc[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < MAXS; ++i) {
+    const int s = g * per + i;
+    if (i < per && s < DP_S && b0 + s < B) U[(b0 + s) * N1p + n] = acc[i];
   }
 }
 
@@ -591,8 +610,7 @@ extern "C" int ctrhot_din_attention_gather_tf32(const float* table, int64_t V, i
   const float* P = static_cast<const float*>(packed);
   float* U = static_cast<float*>(workspace);
   {
-    int64_t grid = (B + 7) / 8;
-    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    const int64_t grid = (B + DP_S - 1) / DP_S;
     if (ids_kind == CTRHOT_IDS_I32)
       din_prep_kernel<CTRHOT_IDS_I32><<<(int)grid, 256, 0, st>>>(table, V, K, cand_ids, cand_ld, B, P + s.o_wq, P + s.o_b1, s.N1p,
                                                               item_out, item_ld, U, err_flag);

@@ -223,7 +223,9 @@ class DenseStack:
                   int(n_side), cb, len(combine), int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag), stream_ptr())
         return out
 
-    def run(self, x, x_ld=None, out=None):
+    def run(self, x, x_ld=None, out=None, final_sigmoid=False):
+        """``final_sigmoid``: sigmoid on the (activation-free) last layer's output -- inside the single-kernel tower when
+        the shape fits it, otherwise as one more elementwise pass."""
         require_cuda(x, "DenseStack")
         M = x.shape[0]
         x_ld = x.stride(0) if x_ld is None else x_ld
@@ -233,7 +235,7 @@ class DenseStack:
         if out is None:
             out = torch.empty((M, n_out), dtype=torch.float32, device=x.device)
         if self.fused_ok(arr) and x_ld % 4 == 0 and x.data_ptr() % 16 == 0 and out.stride(0) == 1:
-            return self.run_fused(x, x_ld, None, out)
+            return self.run_fused(x, x_ld, {"sigmoid": True} if final_sigmoid else None, out)
         need = _lib.query("ctrhot_mlp_workspace_bytes", M, arr, n)
         if self._ws is None or self._ws.numel() * 4 < need or self._ws.device != x.device:
             self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=x.device)
@@ -242,6 +244,8 @@ class DenseStack:
         fused_dot = (self.precision == "tf32" and n >= 2 and n_out == 1 and arr[n - 1].act == _lib.ACT_NONE
                      and out.stride(0) == 1 and 8 <= arr[n - 2].out_dim <= 256)
         _lib.LAUNCHES[0] += (n - 1 if fused_dot else n) - 1      # one kernel per layer; a trailing Dense(h->1) is fused
+        if final_sigmoid:
+            torch.sigmoid_(out)
         return out
 
 

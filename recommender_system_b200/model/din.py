@@ -84,7 +84,8 @@ class DIN(Model):
                 else:
                     layers.append({"kernel": k, "bias": b, "act": _lib.ACT_DICE, "act_param": torch.stack(a).contiguous(),
                                    "dice_eps": 1e-9})
-            layers.append({"kernel": self.out_kernel, "bias": self.out_bias, "act": _lib.ACT_SIGMOID})
+            # final Dense(1, sigmoid) (din.py:54): the sigmoid rides in the tower kernel's post stage
+            layers.append({"kernel": self.out_kernel, "bias": self.out_bias, "act": _lib.ACT_NONE})
             self._folded = (self._version, layers)
         return self._folded[1]
 
@@ -109,7 +110,8 @@ class DIN(Model):
         require_cuda(cand, "DIN")
         B = cand.shape[0]
         flag = self.err_flag()
-        emb = torch.empty((B, self.dcat), dtype=torch.float32, device=dev)
+        ld = (self.dcat + 3) // 4 * 4                           # 16-byte aligned rows for the tower kernel
+        emb = torch.empty((B, ld), dtype=torch.float32, device=dev)[:, :self.dcat]
         K = self.K
         if self.behavior_num == 1:
             att, item = self.att_layer.call_gather(self.embed_seq_layers[0], hist[0], cand[:, 0:1], flag)
@@ -146,7 +148,7 @@ class DIN(Model):
                                for f in self.dense_feature_columns], dim=-1)
             emb[:, col:col + self.dense_num] = dense
         self.stack.set_layers(self._tower_layers(), self._version)
-        out = self.stack.run(emb)
+        out = self.stack.run(emb, final_sigmoid=True)
         if self.check:
             self.check_ids()
         return out
