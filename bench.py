@@ -160,6 +160,87 @@ def secondary(dev, rank):
     return out
 
 
+def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, k=128, B=262144):
+    """BASELINE.json configs[4]: DeepFM over 26 tables x 10M rows x emb 128 (133 GB) row-sharded over `world` GPUs, global
+    B = 262144 (strong scaling: B/world samples per rank), device-resident inputs, CUDA events, max over ranks.  Both
+    exchanges are measured: "a2a" (route + NCCL all-to-all pair + pack/unpack kernels) and "peer" (one gather kernel
+    reading the owners' HBM over NVLink).  Roofline per SURVEY 8(d): 13472 B/sample against HBM at G=1; at G>=2 the
+    13312*(G-1)/G B/sample that cross NVLink against 900 GB/s per-GPU ingress."""
+    import torch
+    import torch.distributed as dist
+    from recommender_system_b200.layer import set_seed
+    from recommender_system_b200.model.sharded import ShardedDeepFM
+    pk = peaks()
+    vocab = [rows_per_table] * 26
+    Bl = B // world
+    rng = np.random.default_rng(77 + rank)
+    ins = []
+    for i in range(2):
+        dense = torch.from_numpy(rng.random((Bl, 13), dtype=np.float32)).to(dev)
+        ids = torch.from_numpy(rng.integers(0, rows_per_table, (Bl, 26), dtype=np.int32)).to(dev)
+        ins.append((dense, ids))
+    out = {"workload": "deepfm_sharded_26x%dx%d_B%d" % (rows_per_table, k, B), "batch_global": B, "batch_per_gpu": Bl,
+           "tables_gb_total": 26 * rows_per_table * k * 4 / 1e9, "scaling": "strong", "n_gpus": world}
+
+    def timed(fn, n, w):
+        for _ in range(w):
+            fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / n], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for mode in ("fused", "peer", "a2a"):
+        set_seed(1)
+        m = ShardedDeepFM(vocab, k, fm_k=10, hidden_units=(256, 128, 64), device=dev, rank=rank, world=world, exchange=mode)
+        m.build()
+        m.embed.init_hash(1234)
+        it = [0]
+
+        def step():
+            m(ins[it[0] % 2]); it[0] += 1
+        ms = timed(step, steps, warm)
+        m.embed.check_ids()
+        r = {"value": B / ms * 1e3, "unit": "samples/s", "ms_per_step": ms}
+        if mode != "fused":                                   # the lookup alone (x written to HBM), for the gather roofline
+            x = torch.empty((Bl, m.x_ld), dtype=torch.float32, device=dev)
+
+            def look():
+                m.embed.lookup_into(ins[it[0] % 2][1], x, m.D, dense=ins[it[0] % 2][0]); it[0] += 1
+            lms = timed(look, steps, warm)
+            r["lookup_ms"] = lms
+            r["lookup_gbs_per_gpu"] = (104 + 52 + 2 * 26 * 4 * k) * Bl / lms / 1e6
+            r["lookup_frac_of_bound"] = ((104 + 52 + 2 * 26 * 4 * k) * Bl / lms / 1e6 / pk["hbm_gbs"] if world == 1 else
+                                         26 * 4 * k * (world - 1) / world * Bl / lms / 1e6 / 900.0)
+            del x
+        if world == 1:
+            r["roofline"] = {"bound": "hbm", "achieved": 13472 * Bl / ms / 1e6, "peak": pk["hbm_gbs"], "unit": "GB/s"}
+        else:
+            r["roofline"] = {"bound": "nvlink", "achieved": 26 * 4 * k * (world - 1) / world * Bl / ms / 1e6, "peak": 900.0,
+                             "unit": "GB/s ingress per GPU (nominal NVLink 5)"}
+        r["roofline"]["frac"] = r["roofline"]["achieved"] / r["roofline"]["peak"]
+        if mode == "fused":
+            tf = (2 * 3341 * 21 + 2 * (3341 * 256 + 256 * 128 + 128 * 64 + 64)) * Bl / ms / 1e9
+            r["tensor"] = {"achieved": tf, "peak": pk["tf"] / 2.0, "unit": "TFLOP/s (TF32 = measured bf16 / 2)",
+                           "frac": tf / (pk["tf"] / 2.0)}
+        out[mode] = r
+        m.embed.close()
+        del m
+        torch.cuda.empty_cache()
+    return out
+
+
 def time_cpu(fn, inputs_list, budget_s=20.0, min_reps=2):
     """median-free throughput: total samples / total time over >= min_reps passes within the budget."""
     fn(inputs_list[0])                                    # warm-up
@@ -234,6 +315,8 @@ def main():
     ap.add_argument("--cpu-batch", type=int, default=16384)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the DIN / gather lines under \"also\"")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the row-sharded config-5 measurement under \"also\"")
+    ap.add_argument("--sharded-rows", type=int, default=10_000_000, help="rows per table of the config-5 measurement")
     ap.add_argument("--cluster", type=int, default=0, help="CTAs sharing each weight chunk by TMA multicast (0 = auto)")
     ap.add_argument("--two-kernel", action="store_true", help="front (gather+FM) + tower kernels instead of the fused one")
     args = ap.parse_args()
@@ -378,6 +461,15 @@ def main():
                                     "kind": "port",
                                     "sample": "%d passes of B=%d rows of the same batches, same weights, %.1f s" % (reps, Bs, dt),
                                     "max_abs_diff_vs_gpu": float(np.max(np.abs(ref - got)))}
+    # ---- BASELINE.json configs[4] (row-sharded, all ranks take part), after everything of the main workload is released
+    sh = None
+    if not args.no_sharded:
+        del model, dev_in, pipe, out
+        torch.cuda.empty_cache()
+        sh = sharded_cfg5(dev, rank, world, rows_per_table=args.sharded_rows)
+    if rank == 0:
+        if sh:
+            line.setdefault("also", {})["sharded_cfg5"] = sh
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

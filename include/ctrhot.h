@@ -191,6 +191,17 @@ int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int
                           const ctrhot_dense_desc* h_layers, int n_layers,
                           const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                           int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
+/* The same kernel over ROW-SHARDED tables (8(e), config 5): arenas = HOST array of G device pointers (arena of owner g;
+ * this rank's own at index `rank`, the peers' mapped by ctrhot_peer_open), row_off = device int64 [G, F+1], ids = GLOBAL
+ * row numbers: row id of field f is read at arenas[id mod G] + (row_off[id mod G][f] + id div G) * k -- the gather warps
+ * pull remote rows over NVLink/NVSwitch with the same 16-byte async copies, under the tensor work of earlier tiles.
+ * No all-to-all, no x in HBM.  G <= 16. */
+int ctrhot_ctr_fused_sharded_tf32(const void* const* arenas, const int64_t* row_off, int G, int rank, int F, int k,
+                                  const void* ids, int ids_kind, int64_t ids_ld,
+                                  const float* dense, int64_t dense_ld, int D, int64_t M,
+                                  const ctrhot_dense_desc* h_layers, int n_layers,
+                                  const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                                  int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
 
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,
@@ -280,6 +291,29 @@ int ctrhot_shard_gather_pack(const float* arena, const int64_t* row_off, int F, 
 /* requester side: x[slot/F, D + (slot%F)*k + c] = rows[n, c] */
 int ctrhot_shard_unpack(const float* rows, const int32_t* slot, int64_t n, int F, int k, int D,
                         float* x, int64_t x_ld, void* stream);
+
+/* synthetic config-5 tables: arena[row_off[f] + lr, c] = hash(seed, f, lr * G + rank, c) in U(-0.05, 0.05); every rank
+ * can regenerate any global row for checking (SURVEY 8(d) cfg 5).  total_rows = row_off[F] (host copy of it). */
+int ctrhot_shard_init_hash_f32(float* arena, const int64_t* row_off, int64_t total_rows, int F, int k,
+                               int G, int rank, uint64_t seed, void* stream);
+
+/* ---- 8(e) config 5 over NVSwitch peer memory: the requester gathers straight out of the owners' HBM (P2P loads over
+ * NVLink), fusing route + all-to-all(ids) + gather_pack + all-to-all(rows) + unpack into ONE kernel (csrc/peer.cu).
+ * ctrhot_peer_alloc cudaMalloc's an arena whose base a CUDA IPC handle names; every rank exports its handle
+ * (ctrhot_peer_handle_bytes() opaque bytes, exchanged once by the host over torch.distributed at load time -- not on the
+ * data path) and opens its peers'.  arenas = HOST array of G device pointers (own arena at index rank), row_off = device
+ * int64 [G, F+1] (rank g's per-field first rows), ids [B, F] int32 global row numbers.  Writes
+ * x[b, D + f*k + c] = arena_{id mod G}[row_off[id mod G][f] + id div G, c]; with dense != NULL also x[b, 0:D] = dense[b, :]
+ * and zeroes columns [D + F*k, x_ld).  Ids outside their table raise *err_flag (row reads as zeros). */
+int ctrhot_peer_handle_bytes(void);
+int ctrhot_peer_alloc(int64_t bytes, void** ptr);
+int ctrhot_peer_free(void* ptr);
+int ctrhot_peer_export(void* ptr, void* handle_out);
+int ctrhot_peer_open(const void* handle, void** ptr);
+int ctrhot_peer_close(void* ptr);
+int ctrhot_shard_lookup_peer_f32(const void* const* arenas, const int64_t* row_off, int F, int k, int G,
+                                 const int32_t* ids, int64_t B, int D, const float* dense, int64_t dense_ld,
+                                 float* x, int64_t x_ld, int* err_flag, void* stream);
 
 #ifdef __cplusplus
 }

@@ -361,3 +361,18 @@ def load_case(npz, name):
     pre = name + "/"
     a = {k[len(pre):]: npz[k] for k in npz.files if k.startswith(pre) and k != pre + "expected"}
     return a, npz[pre + "expected"]
+
+
+def hash_table_value(seed, f, grow, col):
+    """NumPy twin of csrc/api.cu::shard_hash_value (synthetic config-5 tables, SURVEY 8(d)): U(-0.05, 0.05) float32 from a
+    counter-based hash of (field, global row, column).  Arguments broadcast."""
+    M = np.uint64(0xFFFFFFFFFFFFFFFF)
+    with np.errstate(over="ignore"):
+        z = (np.uint64(seed) + np.uint64(0x9E3779B97F4A7C15) * (np.asarray(f, dtype=np.uint64) + np.uint64(1))
+             + np.uint64(0xBF58476D1CE4E5B9) * np.asarray(grow, dtype=np.uint64)
+             + np.uint64(0x94D049BB133111EB) * (np.asarray(col, dtype=np.uint64) + np.uint64(1))) & M
+        z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & M
+        z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & M
+        z = z ^ (z >> np.uint64(31))
+    u = (z >> np.uint64(40)).astype(np.float32) * np.float32(1.0 / 16777216.0)
+    return ((u - np.float32(0.5)) * np.float32(0.1)).astype(np.float32)

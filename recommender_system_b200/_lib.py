@@ -31,7 +31,7 @@ class DenseDesc(ctypes.Structure):
                 ("reserved", ctypes.c_int32)]
 
 
-_SCALARS = {"int": ctypes.c_int, "int32_t": ctypes.c_int32, "int64_t": ctypes.c_int64, "float": ctypes.c_float}
+_SCALARS = {"uint64_t": ctypes.c_uint64, "int": ctypes.c_int, "int32_t": ctypes.c_int32, "int64_t": ctypes.c_int64, "float": ctypes.c_float}
 
 
 def _ctype(decl):

@@ -79,14 +79,53 @@ shard_unpack_kernel(const float* __restrict__ rows, const int32_t* __restrict__ 
     const int f = s - (int)(b * F);
     const float4 v = ldg_nc_f4(rows + r * k + c * 4);
     float* dst = x + b * x_ld + D + (int64_t)f * k + c * 4;
-    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) *reinterpret_cast<float4*>(dst) = v;
+    // (the aligned store is inline asm on purpose: a float4 cast here lets the compiler assume alignment and turn the
+    //  scalar branch into a 128-bit store too -- found by tests/test_gpu_sharded.py with D = 13)
+    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) stg_na_f4(dst, v);
     else { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w; }
+  }
+}
+
+// Synthetic tables for config 5: value(f, global row, col) = U(-0.05, 0.05) from a counter-based hash, so any
+// rank can regenerate any row without a 133-GB host copy (oracle/synth.py::hash_table_value is the same function in NumPy).
+__host__ __device__ inline float shard_hash_value(uint64_t seed, int f, int64_t grow, int col) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * ((uint64_t)f + 1u) + 0xBF58476D1CE4E5B9ull * (uint64_t)grow +
+               0x94D049BB133111EBull * ((uint64_t)col + 1u);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  const float u = (float)(uint32_t)(z >> 40) * (1.0f / 16777216.0f);      // 24 bits -> [0, 1)
+  return (u - 0.5f) * 0.1f;
+}
+
+__global__ void __launch_bounds__(256)
+shard_init_hash_kernel(float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k, int G, int rank,
+                       uint64_t seed) {
+  const int64_t total = row_off[F] * k;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t ar = t / k;
+    const int c = (int)(t - ar * k);
+    int f = 0;
+    while (f + 1 < F && row_off[f + 1] <= ar) ++f;
+    const int64_t lr = ar - row_off[f];
+    arena[t] = shard_hash_value(seed, f, lr * G + rank, c);
   }
 }
 
 }  // namespace ctrhot
 
 using namespace ctrhot;
+
+extern "C" int ctrhot_shard_init_hash_f32(float* arena, const int64_t* row_off, int64_t total_rows, int F, int k,
+                                          int G, int rank, uint64_t seed, void* stream) {
+  if (!arena || !row_off || F <= 0 || k <= 0 || G <= 0 || rank < 0 || rank >= G || total_rows < 0) return CTRHOT_EARG;
+  if (total_rows == 0) return CTRHOT_OK;
+  int64_t g = (total_rows * k + 255) / 256;
+  if (g > kNumSMs * 32) g = kNumSMs * 32;
+  shard_init_hash_kernel<<<(int)g, 256, 0, static_cast<cudaStream_t>(stream)>>>(arena, row_off, F, k, G, rank, seed);
+  CTRHOT_LAUNCH_OK("ctrhot_shard_init_hash_f32");
+  return CTRHOT_OK;
+}
 
 extern "C" int ctrhot_version(void) { return CTRHOT_VERSION; }
 

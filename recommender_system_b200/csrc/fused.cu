@@ -54,8 +54,11 @@ struct FuLayer {
   int N, KC, BN, KP, col, act;                              // KP = N rounded up to 32 (= K extent of the next layer)
 };
 
+constexpr int FU_MAXG = 16;
 struct FuParams {
   const float* arena; const int64_t* row_off; int F; int k4; const void* ids; int ids_kind; int64_t ids_ld;
+  int G; const float* peer[FU_MAXG];                       // row-sharded tables (cfg 5): owner = id mod G, arenas mapped over NVLink;
+                                                           // row_off is then [G, F+1].  G = 1: peer[0] = arena
   const float* dense; int64_t dense_ld; int D; int emb;
   int64_t M; int n_tiles; int n_super;
   FuLayer L[FU_MAXL];
@@ -128,7 +131,7 @@ constexpr int FU_PF = 3;                    // chunks by which the id loads run 
 struct FuSmemMap {
   int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, total;
 };
-__host__ __device__ inline FuSmemMap fu_smem_map(int F, int KC1, const int* KP, int nl) {
+__host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries */, int KC1, const int* KP, int nl) {
   FuSmemMap m;
   int o = 0;
   m.rowoff = o; o += (F * 3 + 3) / 4 * 4;          // per field: table base address (8 B) x F, then row count (4 B) x F
@@ -218,7 +221,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
   for (int l = 0; l < FU_MAXL; ++l) KP[l] = (l < NL) ? p.L[l].KP : 0;
   const int KC1 = p.L[0].KC;
-  const FuSmemMap mp = fu_smem_map(p.F, KC1, KP, NL);
+  const FuSmemMap mp = fu_smem_map(p.F * p.G, KC1, KP, NL);
   float* fptr = reinterpret_cast<float*>(base_ptr + (f_base - base));
   const uint32_t bars = f_base + (uint32_t)mp.total * 4u;
   // barrier map
@@ -252,10 +255,11 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   // stage the small per-column vectors
   {
     const float** s_fb = reinterpret_cast<const float**>(fptr + mp.rowoff);
-    uint32_t* s_fn = reinterpret_cast<uint32_t*>(fptr + mp.rowoff + 2 * p.F);
-    for (int i = tid; i < p.F; i += FU_THREADS) {
-      const int64_t r0 = p.row_off[i], nr = p.row_off[i + 1] - r0;
-      s_fb[i] = p.arena + r0 * (int64_t)(p.k4 * 4);
+    uint32_t* s_fn = reinterpret_cast<uint32_t*>(fptr + mp.rowoff + 2 * p.F * p.G);
+    for (int i = tid; i < p.F * p.G; i += FU_THREADS) {       // entry (owner o, field f) at o * F + f
+      const int o = i / p.F, f = i - o * p.F;
+      const int64_t r0 = p.row_off[o * (p.F + 1) + f], nr = p.row_off[o * (p.F + 1) + f + 1] - r0;
+      s_fb[i] = p.peer[o] + r0 * (int64_t)(p.k4 * 4);
       s_fn[i] = nr < 0 ? 0u : (nr > 0x7FFFFFFF ? 0x7FFFFFFFu : (uint32_t)nr);   // ids are int32: larger tables cannot be addressed anyway
     }
     for (int i = tid; i < KC1 * 32; i += FU_THREADS) fptr[mp.sq + i] = p.sq_w ? __ldg(p.sq_w + i) : 0.f;
@@ -290,7 +294,8 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     const int c = tg & 7;
     const int rsub = tg >> 3;
     const float* const* s_fb = reinterpret_cast<const float* const*>(fptr + mp.rowoff);
-    const uint32_t* s_fn = reinterpret_cast<const uint32_t*>(fptr + mp.rowoff + 2 * p.F);
+    const uint32_t* s_fn = reinterpret_cast<const uint32_t*>(fptr + mp.rowoff + 2 * p.F * p.G);
+    const uint32_t G = (uint32_t)p.G;
     const int total_chunks = n_my * KC1;
     const int k4 = p.k4;
     const int f0 = c / k4, part0 = c - f0 * k4;
@@ -325,7 +330,21 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         const char* fb = reinterpret_cast<const char*>(s_fb[ci.f]) + ci.part * 16;
         const uint32_t nrow = s_fn[ci.f];
         bool bad = false;
-        if (p.ids_kind == CTRHOT_IDS_I32) {
+        if (G > 1) {
+          // row-sharded: the row lives in arena (id mod G) at local row (id div G); that arena may be a peer's HBM mapped
+          // over NVLink -- the same 16-byte LDGSTS, only the latency differs (the raw ring keeps FU_NR chunks in flight)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t id = (p.ids_kind == CTRHOT_IDS_I32) ? (uint32_t)reg[i]
+                                                               : (uint32_t)__float2int_rz(__int_as_float(reg[i]));
+            const uint32_t lr = id / G, o = id - lr * G;
+            const int e = (int)o * p.F + ci.f;
+            const bool ok = (int32_t)id >= 0 && lr < s_fn[e];
+            bad |= !ok;
+            const char* src = reinterpret_cast<const char*>(s_fb[e]) + ci.part * 16 + (uint64_t)lr * rowbytes;
+            cp_async16(dst + 2048u * i, ok ? (const void*)src : (const void*)p.arena, ok ? 16u : 0u);
+          }
+        } else if (p.ids_kind == CTRHOT_IDS_I32) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const uint32_t id = (uint32_t)reg[i];
@@ -678,14 +697,19 @@ int fu_launch_nl(const FuParams& p, int nl, size_t smem, cudaStream_t st) {
     default: return fu_launch<3, C>(p, smem, st);
   }
 }
-}  // namespace
 
-extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
-                                     const void* ids, int ids_kind, int64_t ids_ld,
-                                     const float* dense, int64_t dense_ld, int D, int64_t M,
-                                     const ctrhot_dense_desc* h_layers, int n_layers,
-                                     const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
-                                     int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+// peers[0..G): arena of owner g (this rank's own at its index; the others mapped through ctrhot_peer_open); G = 1 is the
+// unsharded case.  row_off is [G, F+1].
+int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off, int F, int k,
+             const void* ids, int ids_kind, int64_t ids_ld,
+             const float* dense, int64_t dense_ld, int D, int64_t M,
+             const ctrhot_dense_desc* h_layers, int n_layers,
+             const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+             int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  if (!peers || G < 1 || G > FU_MAXG || rank < 0 || rank >= G) return CTRHOT_EARG;
+  for (int g = 0; g < G; ++g) if (!peers[g] || !aligned16(peers[g])) return CTRHOT_EARG;
+  if ((int64_t)F * G > 4096) return CTRHOT_ESHAPE;
+  const float* arena = peers[rank];
   if (!arena || !row_off || !ids || !out || !h_layers || F <= 0 || k <= 0 || M < 0 || D < 0) return CTRHOT_EARG;
   if (D > 0 && !dense) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
@@ -730,6 +754,8 @@ extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off,
   if (p.n_as < 2) return CTRHOT_ESHAPE;
   if (o.in_dim != h_layers[nl - 1].out_dim) return CTRHOT_EARG;
   if (M == 0) return CTRHOT_OK;
+  p.G = G;
+  for (int g = 0; g < FU_MAXG; ++g) p.peer[g] = g < G ? peers[g] : nullptr;
   p.arena = arena; p.row_off = row_off; p.F = F; p.k4 = k / 4; p.ids = ids; p.ids_kind = ids_kind; p.ids_ld = ids_ld;
   p.dense = dense; p.dense_ld = dense_ld; p.D = D; p.emb = F * k;
   p.M = M; p.n_tiles = (int)((M + FU_BM - 1) / FU_BM);
@@ -737,7 +763,7 @@ extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off,
   p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid;
   for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
-  const FuSmemMap mp = fu_smem_map(F, p.L[0].KC, KP, nl);
+  const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl);
   const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1;
   size_t smem = 0;
   for (p.nb = FU_NB; p.nb >= 2; --p.nb) {
@@ -752,4 +778,30 @@ extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off,
   if (C == 4) return fu_launch_nl<4>(p, nl, smem, st);
   if (C == 2) return fu_launch_nl<2>(p, nl, smem, st);
   return fu_launch_nl<1>(p, nl, smem, st);
+}
+}  // namespace
+
+extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                     const void* ids, int ids_kind, int64_t ids_ld,
+                                     const float* dense, int64_t dense_ld, int D, int64_t M,
+                                     const ctrhot_dense_desc* h_layers, int n_layers,
+                                     const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                                     int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  if (!arena) return CTRHOT_EARG;
+  return fu_entry(&arena, 1, 0, row_off, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w, mode,
+                  n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag, stream);
+}
+
+extern "C" int ctrhot_ctr_fused_sharded_tf32(const void* const* arenas, const int64_t* row_off, int G, int rank, int F, int k,
+                                             const void* ids, int ids_kind, int64_t ids_ld,
+                                             const float* dense, int64_t dense_ld, int D, int64_t M,
+                                             const ctrhot_dense_desc* h_layers, int n_layers,
+                                             const float* sq_w, int mode, int n_side, const float* h_combine,
+                                             int n_combine, int apply_sigmoid, int cluster, float* out, int* err_flag,
+                                             void* stream) {
+  if (!arenas || G < 1 || G > FU_MAXG) return CTRHOT_EARG;
+  const float* peers[FU_MAXG];
+  for (int g = 0; g < G; ++g) peers[g] = static_cast<const float*>(arenas[g]);
+  return fu_entry(peers, G, rank, row_off, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w,
+                  mode, n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag, stream);
 }

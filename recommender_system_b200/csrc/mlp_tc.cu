@@ -156,7 +156,7 @@ dense_tc_kernel(const TcParams p) {
           if (((p.y_ld & 3) == 0) && n0 + 16 <= p.y_ld && ((reinterpret_cast<uintptr_t>(p.Y) & 15) == 0)) {
 #pragma unroll
             for (int j = 0; j < 16; j += 4)
-              if (n0 + j < p.y_ld) *reinterpret_cast<float4*>(dst + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+              if (n0 + j < p.y_ld) stg_na_f4(dst + j, make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]));   // asm: no alignment inference
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j) if (n0 + j < p.N) dst[j] = acc[j];

@@ -218,9 +218,14 @@ class DenseStack:
         if out is None:
             out = torch.empty((B, 1), dtype=torch.float32, device=E.arena.device)
         cb = (ctypes.c_float * max(len(combine), 1))(*[float(c) for c in combine])
-        _lib.call("ctrhot_ctr_fused_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld,
-                  ptr(dense), 0 if dense is None else dense.stride(0), D, B, arr, len(arr), ptr(sq_w), int(mode),
-                  int(n_side), cb, len(combine), int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag), stream_ptr())
+        tail = (ptr(ids), kind, ids_ld, ptr(dense), 0 if dense is None else dense.stride(0), D, B, arr, len(arr), ptr(sq_w),
+                int(mode), int(n_side), cb, len(combine), int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag),
+                stream_ptr())
+        if getattr(E, "peers", None) is not None:
+            # row-sharded tables (model/sharded.py): the gather warps read the owners' arenas over NVLink
+            _lib.call("ctrhot_ctr_fused_sharded_tf32", E.peers, ptr(E.row_off_all), E.G, E.rank, E.F, E.k, *tail)
+        else:
+            _lib.call("ctrhot_ctr_fused_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, *tail)
         return out
 
     def run(self, x, x_ld=None, out=None, final_sigmoid=False):
