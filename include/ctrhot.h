@@ -311,6 +311,7 @@ int ctrhot_peer_free(void* ptr);
 int ctrhot_peer_export(void* ptr, void* handle_out);
 int ctrhot_peer_open(const void* handle, void** ptr);
 int ctrhot_peer_close(void* ptr);
+int ctrhot_peer_enable(int peer_device);   /* single process, several GPUs: cudaDeviceEnablePeerAccess for the current device */
 int ctrhot_shard_lookup_peer_f32(const void* const* arenas, const int64_t* row_off, int F, int k, int G,
                                  const int32_t* ids, int64_t B, int D, const float* dense, int64_t dense_ld,
                                  float* x, int64_t x_ld, int* err_flag, void* stream);

@@ -137,6 +137,14 @@ extern "C" int ctrhot_peer_open(const void* handle, void** ptr) {
   return CTRHOT_OK;
 }
 
+extern "C" int ctrhot_peer_enable(int peer_device) {
+  // one process driving several GPUs: let kernels on the current device dereference peer_device's allocations
+  const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { (void)cudaGetLastError(); return CTRHOT_OK; }
+  CTRHOT_CUDA_OK(e, "ctrhot_peer_enable");
+  return CTRHOT_OK;
+}
+
 extern "C" int ctrhot_peer_close(void* ptr) {
   if (ptr) CTRHOT_CUDA_OK(cudaIpcCloseMemHandle(ptr), "ctrhot_peer_close");
   return CTRHOT_OK;

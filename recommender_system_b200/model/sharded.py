@@ -80,7 +80,8 @@ class _PeerArena:
 
 class ShardedEmbedding:
     """Local shard of F tables of ``vocab[f]`` global rows each, width k, on ``device``; rank/world from the process group.
-    ``peer=True`` allocates the arena so that it can be mapped by the other ranks (``connect`` / ``connect_local``)."""
+    ``peer=True`` allocates the arena so that it can be mapped by the other ranks (``connect`` / ``connect_local``):
+    torch symmetric memory when world > 1 (``peer="ipc"``: a cudaMalloc block shared through CUDA IPC handles instead)."""
 
     def __init__(self, vocab, k, device, rank=0, world=1, group=None, peer=False):
         self.vocab, self.k, self.F = [int(v) for v in vocab], int(k), len(vocab)
@@ -93,7 +94,16 @@ class ShardedEmbedding:
         self.row_off = self.row_off_all[rank].contiguous()
         self.total_rows = int(sum(local))
         self._block = None
-        if peer and self.total_rows > 0:
+        self._symm = None
+        if peer and world > 1 and peer != "ipc":
+            # torch symmetric memory = cuMem (VMM) allocations mapped into every rank with 2 MB pages.  Measured on 2 B200s
+            # (profiles/p2p_probe_mp.py): random 512-B rows out of a 26 GB peer shard read at 634 GB/s through this mapping
+            # but at 100 GB/s through a cudaIpcOpenMemHandle mapping (small pages: TLB-bound), so IPC is opt-in only.
+            import torch.distributed._symmetric_memory as symm
+            rows = int(offs[:, -1].max())                                      # symmetric: same size on every rank
+            self._symm = symm.empty((max(rows, 1), k), dtype=torch.float32, device=device)
+            self.arena = self._symm[:self.total_rows]
+        elif peer == "ipc" and self.total_rows > 0:
             with torch.cuda.device(device):
                 self._block = _PeerArena(self.total_rows, k)
             self.arena = torch.as_tensor(self._block, device=device)
@@ -110,6 +120,14 @@ class ShardedEmbedding:
         lib = _lib.load()
         if self.G == 1:
             return self.connect_local([self])
+        if self._symm is not None:
+            import torch.distributed._symmetric_memory as symm
+            torch.cuda.synchronize(self.device)
+            hdl = symm.rendezvous(self._symm, self.group if self.group is not None else dist.group.WORLD)
+            self._hdl = hdl
+            self.peers = (ctypes.c_void_p * self.G)(*[int(p) for p in hdl.buffer_ptrs])
+            dist.barrier(group=self.group)
+            return
         if self._block is None:
             raise _lib.CtrhotError("ShardedEmbedding.connect: build with peer=True")
         nb = lib.ctrhot_peer_handle_bytes()
@@ -148,9 +166,13 @@ class ShardedEmbedding:
             lib.ctrhot_peer_close(ctypes.c_void_p(p))
         self._opened = []
         self.peers = None
-        if had_peers and dist.is_initialized():
+        if (had_peers or self._symm is not None) and dist.is_initialized():
             torch.cuda.synchronize(self.device)
             dist.barrier(group=self.group)
+        if self._symm is not None:
+            self.arena = None
+            self._hdl = None
+            self._symm = None
         if self._block is not None:
             torch.cuda.synchronize(self.device)
             self.arena = None
@@ -216,10 +238,12 @@ class ShardedEmbedding:
 class ShardedDeepFM(Model):
     """DeepFM over row-sharded tables: ``call((dense [B_l,13], ids [B_l,26]))`` on every rank with ITS samples returns
     their probabilities [B_l,1].  Dense-side weights (FM, tower) are replicated: build them with the same seed on all ranks
-    (or broadcast once at load time -- not on the data path)."""
+    (or broadcast once at load time -- not on the data path).  ``arena``: how a peer-readable shard is allocated -- "auto"
+    (symmetric memory when world > 1), "ipc" (cudaMalloc + CUDA IPC) or "torch" (ordinary allocation: all shards in one
+    process, wired with ``embed.connect_local``)."""
 
     def __init__(self, vocab, k, fm_k=10, hidden_units=(256, 128, 64), activation="relu", n_dense=13, precision="tf32",
-                 device=None, rank=None, world=None, group=None, exchange="a2a"):
+                 device=None, rank=None, world=None, group=None, exchange="a2a", arena="auto"):
         super().__init__(device)
         if exchange not in ("a2a", "peer", "fused"):
             raise ValueError("exchange must be 'a2a' (NCCL all-to-all pair), 'peer' (one gather kernel with P2P loads over "
@@ -231,7 +255,7 @@ class ShardedDeepFM(Model):
             world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.D, self.k, self.F = n_dense, k, len(vocab)
         self.n = n_dense + self.F * k
-        self.embed = ShardedEmbedding(vocab, k, self.device, rank, world, group, peer=(exchange != "a2a"))
+        self.embed = ShardedEmbedding(vocab, k, self.device, rank, world, group, peer=(False if exchange == "a2a" else {"auto": True, "torch": False, "ipc": "ipc"}[arena]))
         self.fm = self.track(FMLayer(fm_k, device=self.device))
         self.dnn = self.track(DNNLayer(list(hidden_units), 1, activation, precision=precision, device=self.device))
         self.x_ld = (self.n + 3) // 4 * 4

@@ -100,7 +100,7 @@ def test_peer_lookup_virtual_ranks(lib, G, k, D, pad):
     vocab, Bl = [7, 1, 4000, 130, 2, 999], 301
     F = len(vocab)
     tables = hash_tables(vocab, k, 21)
-    embeds = [ShardedEmbedding(vocab, k, dev, r, G, peer=(r % 2 == 0)) for r in range(G)]
+    embeds = [ShardedEmbedding(vocab, k, dev, r, G, peer=("ipc" if r % 2 == 0 else False)) for r in range(G)]
     for E in embeds:
         E.init_hash(21)
         E.connect_local(embeds)
@@ -125,7 +125,7 @@ def test_peer_lookup_virtual_ranks(lib, G, k, D, pad):
 def test_peer_lookup_flags_bad_ids(lib):
     dev = torch.device("cuda", 0)
     vocab, k = [10, 20], 8
-    E = ShardedEmbedding(vocab, k, dev, 0, 1, peer=True)
+    E = ShardedEmbedding(vocab, k, dev, 0, 1, peer="ipc")
     E.init_hash(1)
     E.connect_local([E])
     x = torch.empty((2, 16), dtype=torch.float32, device=dev)
@@ -166,7 +166,7 @@ def test_sharded_deepfm_fused_virtual_ranks(lib, G, k, B):
     models = []
     for r in range(G):
         set_seed(4)
-        m = ShardedDeepFM(vocab, k, fm_k=10, hidden_units=(64, 32), device=dev, rank=r, world=G, exchange="fused")
+        m = ShardedDeepFM(vocab, k, fm_k=10, hidden_units=(64, 32), device=dev, rank=r, world=G, exchange="fused", arena="torch")
         m.build()
         m.embed.init_hash(5)
         models.append(m)
@@ -197,7 +197,7 @@ def test_sharded_fused_flags_bad_ids(lib):
     dev = torch.device("cuda", 0)
     vocab, k = [10, 20, 30, 40], 16
     set_seed(1)
-    ms = [ShardedDeepFM(vocab, k, fm_k=4, hidden_units=(32, 16), n_dense=2, device=dev, rank=r, world=2, exchange="fused")
+    ms = [ShardedDeepFM(vocab, k, fm_k=4, hidden_units=(32, 16), n_dense=2, device=dev, rank=r, world=2, exchange="fused", arena="torch")
           for r in range(2)]
     for m in ms:
         m.build(); m.embed.init_hash(1)
