@@ -46,6 +46,13 @@ class ClockSampler(threading.Thread):
             nv.nvmlInit()
             self.nv, self.h = nv, nv.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            # the first call of each query can take seconds on a fresh box and holds a driver lock that kernel launches
+            # also need (seen once: 4 s per step with 5 timed steps) -- pay for it here, outside the timed region
+            nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+            try:
+                nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:
+                nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
         except Exception as e:
             self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
 
@@ -65,7 +72,7 @@ class ClockSampler(threading.Thread):
                 for bit, nm in names.items():
                     if r & bit:
                         self.reasons.add(nm)
-                time.sleep(0.002)
+                time.sleep(0.01)
         except Exception as e:       # NVML missing: report that instead of inventing numbers
             self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
 
@@ -222,13 +229,13 @@ def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, 
             r["lookup_ms"] = lms
             r["lookup_gbs_per_gpu"] = (104 + 52 + 2 * 26 * 4 * k) * Bl / lms / 1e6
             r["lookup_frac_of_bound"] = ((104 + 52 + 2 * 26 * 4 * k) * Bl / lms / 1e6 / pk["hbm_gbs"] if world == 1 else
-                                         26 * 4 * k * (world - 1) / world * Bl / lms / 1e6 / 900.0)
+                                         26 * 4 * k * (world - 1) / world * Bl / lms / 1e6 / 770.0)
             del x
         if world == 1:
             r["roofline"] = {"bound": "hbm", "achieved": 13472 * Bl / ms / 1e6, "peak": pk["hbm_gbs"], "unit": "GB/s"}
         else:
-            r["roofline"] = {"bound": "nvlink", "achieved": 26 * 4 * k * (world - 1) / world * Bl / ms / 1e6, "peak": 900.0,
-                             "unit": "GB/s ingress per GPU (nominal NVLink 5)"}
+            r["roofline"] = {"bound": "nvlink", "achieved": 26 * 4 * k * (world - 1) / world * Bl / ms / 1e6, "peak": 770.0,
+                             "unit": "GB/s ingress per GPU (measured peer copy, B200_PROFILING.md; nominal 900)"}
         r["roofline"]["frac"] = r["roofline"]["achieved"] / r["roofline"]["peak"]
         if mode == "fused":
             tf = (2 * 3341 * 21 + 2 * (3341 * 256 + 256 * 128 + 128 * 64 + 64)) * Bl / ms / 1e9
@@ -236,6 +243,7 @@ def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, 
                            "frac": tf / (pk["tf"] / 2.0)}
         out[mode] = r
         m.embed.close()
+        step = look = None                                    # the closures hold the model (and its 133 GB arena at G = 1)
         del m
         torch.cuda.empty_cache()
     return out

@@ -87,6 +87,245 @@ fm_dense_kernel(const float* __restrict__ x, int64_t x_ld, int64_t n, int64_t B,
   }
 }
 
+// Same layer for WIDE inputs (config 5: x [B, 3341] dense; config 1: x [B, 43604] one-hot).  A CTA owns 32 samples, a warp
+// FOUR of them, so every v row is used 32 times per staging and 4 times per register load.  v / w1 are staged per tile of
+// 256 columns into shared memory TRANSPOSED ([factor][column]: lanes read consecutive words, no bank conflicts -- reading
+// v[j, c] straight from global costs one L1 wavefront per lane because rows are kfm*4 bytes apart).  Per 32 columns:
+//   all four rows zero  -> skip (one-hot inputs are mostly this);
+//   <= 4 live columns   -> the sparse walk of fm_dense_kernel (lane c = factor c), for the four samples at once;
+//   otherwise           -> dense: lane l owns column j0 + l, accumulates s[i][c] += x_i v[j,c] in registers (reduced
+//                          across lanes once at the end) and t_i += x_i^2 * sum_c v[j,c]^2.
+// HBM: x is read once (coalesced 128-B rows).
+constexpr int FMW_TJ = 256;
+template <int KF>
+__global__ void __launch_bounds__(256)
+fm_dense_wide_kernel(const float* __restrict__ x, int64_t x_ld, int64_t n, int64_t B,
+                     const float* __restrict__ w0, const float* __restrict__ w1,
+                     const float* __restrict__ v, int kfm, float* __restrict__ out, int apply_sigmoid) {
+  __shared__ float vs[(KF + 1) * FMW_TJ];                     // planes 0..kfm-1 = v[:, c], plane kfm = w1
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const int64_t ngroups = (B + 3) >> 2;
+  const int64_t nblocks = (ngroups + 7) >> 3;
+  for (int64_t gb = blockIdx.x; gb < nblocks; gb += gridDim.x) {
+    const int64_t g = gb * 8 + wic;
+    const bool live_w = g < ngroups;
+    const int64_t b0 = g << 2;
+    const float* row[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) row[i] = x + ((live_w && b0 + i < B) ? b0 + i : B - 1) * x_ld;
+    float s[4][KF], lin[4], t[4], sps[4], spt[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      lin[i] = t[i] = sps[i] = spt[i] = 0.f;
+#pragma unroll
+      for (int c = 0; c < KF; ++c) s[i][c] = 0.f;
+    }
+    for (int64_t jt = 0; jt < n; jt += FMW_TJ) {
+      const int tj = (int)((n - jt < FMW_TJ) ? n - jt : FMW_TJ);
+      __syncthreads();                                         // the previous tile is no longer being read
+      for (int idx = threadIdx.x; idx < tj * kfm; idx += 256) {
+        const int jl = idx / kfm, c = idx - jl * kfm;
+        vs[c * FMW_TJ + jl] = __ldg(v + jt * kfm + idx);
+      }
+      for (int jl = threadIdx.x; jl < tj; jl += 256) vs[kfm * FMW_TJ + jl] = __ldg(w1 + jt + jl);
+      __syncthreads();
+      if (!live_w) continue;
+      for (int jq = 0; jq < tj; jq += 128) {
+        // 16 row loads in flight per lane (4 groups of 32 columns x 4 samples) before any of them is consumed: the
+        // kernel is a stream over x, and 2 CTAs x 256 threads x 64 B is what covers the HBM latency
+        float xq[4][4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int jl = jq + 32 * u + lane;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) xq[u][i] = (jl < tj) ? ldg_nc_f1(row[i] + jt + jl) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int jg = jq + 32 * u;
+          const int jl = jg + lane;
+          const float (&xv)[4] = xq[u];
+          unsigned m = __ballot_sync(0xffffffffu, (xv[0] != 0.f) | (xv[1] != 0.f) | (xv[2] != 0.f) | (xv[3] != 0.f));
+          if (m == 0) {
+          } else if (__popc(m) <= 4) {
+            while (m) {
+              const int src = __ffs(m) - 1;
+              m &= m - 1;
+              const float wv = (lane <= kfm) ? vs[lane * FMW_TJ + jg + src] : 0.f;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float xs = __shfl_sync(0xffffffffu, xv[i], src);
+                sps[i] = fmaf(xs, wv, sps[i]);
+                spt[i] = fmaf(xs * xs, wv * wv, spt[i]);      // only lanes < kfm use it
+              }
+            }
+          } else if (jl < tj) {
+            const float wl = vs[kfm * FMW_TJ + jl];
+            float q = 0.f;
+#pragma unroll
+            for (int c = 0; c < KF; ++c) {
+              if (c < kfm) {
+                const float vv = vs[c * FMW_TJ + jl];
+                q = fmaf(vv, vv, q);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) s[i][c] = fmaf(xv[i], vv, s[i][c]);
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              lin[i] = fmaf(xv[i], wl, lin[i]);
+              t[i] = fmaf(xv[i] * xv[i], q, t[i]);
+            }
+          }
+        }
+      }
+    }
+    if (!live_w) continue;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float inter = 0.f;
+#pragma unroll
+      for (int c = 0; c < KF; ++c) {
+        if (c < kfm) {
+          const float tot = warp_sum(s[i][c]) + __shfl_sync(0xffffffffu, sps[i], c);
+          inter = fmaf(tot, tot, inter);
+        }
+      }
+      const float tt = warp_sum(t[i] + (lane < kfm ? spt[i] : 0.f));
+      const float ll = warp_sum(lin[i] + (lane == kfm ? sps[i] : 0.f));
+      if (lane == 0 && b0 + i < B) {
+        const float r = __ldg(w0) + ll + 0.5f * (inter - tt);
+        out[b0 + i] = apply_sigmoid ? 1.0f / (1.0f + expf(-r)) : r;
+      }
+    }
+  }
+}
+
+// The same kernel for 16-byte aligned rows (x_ld % 4 == 0): lane l owns the FOUR consecutive columns 4l..4l+3 of a block
+// of 128, so one warp instruction reads 512 contiguous bytes of a row (four full DRAM sectors runs instead of 128-byte
+// pieces of four different DRAM pages -- measured 2.7 ms -> see DESIGN.md for x [262144, 3341]) and one LDS.128 fetches
+// v[4l..4l+3, c].  skip / sparse / dense is decided per block of 128 columns.
+template <int KF>
+__global__ void __launch_bounds__(256)
+fm_dense_wide_v4_kernel(const float* __restrict__ x, int64_t x_ld, int64_t n, int64_t B,
+                        const float* __restrict__ w0, const float* __restrict__ w1,
+                        const float* __restrict__ v, int kfm, float* __restrict__ out, int apply_sigmoid) {
+  __shared__ __align__(16) float vs[(KF + 1) * FMW_TJ];       // planes 0..kfm-1 = v[:, c], plane kfm = w1; zero past n
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const int64_t ngroups = (B + 3) >> 2;
+  const int64_t nblocks = (ngroups + 7) >> 3;
+  for (int64_t gb = blockIdx.x; gb < nblocks; gb += gridDim.x) {
+    const int64_t g = gb * 8 + wic;
+    const bool live_w = g < ngroups;
+    const int64_t b0 = g << 2;
+    const float* row[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) row[i] = x + ((live_w && b0 + i < B) ? b0 + i : B - 1) * x_ld;
+    float s[4][KF], lin[4], t[4], sps[4], spt[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      lin[i] = t[i] = sps[i] = spt[i] = 0.f;
+#pragma unroll
+      for (int c = 0; c < KF; ++c) s[i][c] = 0.f;
+    }
+    for (int64_t jt = 0; jt < n; jt += FMW_TJ) {
+      const int tj = (int)((n - jt < FMW_TJ) ? n - jt : FMW_TJ);
+      __syncthreads();                                         // the previous tile is no longer being read
+      for (int idx = threadIdx.x; idx < FMW_TJ * kfm; idx += 256) {
+        const int jl = idx / kfm, c = idx - jl * kfm;
+        vs[c * FMW_TJ + jl] = (jl < tj) ? __ldg(v + jt * kfm + idx) : 0.f;
+      }
+      vs[kfm * FMW_TJ + threadIdx.x] = ((int)threadIdx.x < tj) ? __ldg(w1 + jt + threadIdx.x) : 0.f;
+      __syncthreads();
+      if (!live_w) continue;
+      float4 xq[2][4];                                          // both 128-column blocks of the tile are fetched up front
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int jl = 128 * h + 4 * lane;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          // x_ld % 4 == 0 and the columns [n, x_ld) of a row are readable, so a float4 straddling n stays inside the row;
+          // its columns >= n meet zeros in vs
+          xq[h][i] = (jl < tj) ? ldg_nc_f4(row[i] + jt + jl) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int jl = 128 * h + 4 * lane;
+        float xa[4][4];                                         // [sample][column of mine]
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { xa[i][0] = xq[h][i].x; xa[i][1] = xq[h][i].y; xa[i][2] = xq[h][i].z; xa[i][3] = xq[h][i].w; }
+        if (jl < tj && jt + jl + 4 > n) {                       // the straddling float4: drop what lies past n
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (jt + jl + e >= n) { xa[0][e] = xa[1][e] = xa[2][e] = xa[3][e] = 0.f; }
+        }
+        unsigned nz = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          nz |= ((xa[0][e] != 0.f) | (xa[1][e] != 0.f) | (xa[2][e] != 0.f) | (xa[3][e] != 0.f)) ? (1u << e) : 0u;
+        unsigned m = __ballot_sync(0xffffffffu, nz != 0u);
+        if (m == 0) {
+        } else if (__popc(m) <= 4) {
+          while (m) {
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const unsigned snz = __shfl_sync(0xffffffffu, nz, src);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (!(snz & (1u << e))) continue;                 // warp-uniform
+              const float wv = (lane <= kfm) ? vs[lane * FMW_TJ + 128 * h + 4 * src + e] : 0.f;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float xs = __shfl_sync(0xffffffffu, xa[i][e], src);
+                sps[i] = fmaf(xs, wv, sps[i]);
+                spt[i] = fmaf(xs * xs, wv * wv, spt[i]);      // only lanes < kfm use it
+              }
+            }
+          }
+        } else if (jl < tj) {
+          const float4 wl = *reinterpret_cast<const float4*>(&vs[kfm * FMW_TJ + jl]);
+          float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int c = 0; c < KF; ++c) {
+            if (c < kfm) {
+              const float4 vv = *reinterpret_cast<const float4*>(&vs[c * FMW_TJ + jl]);
+              q.x = fmaf(vv.x, vv.x, q.x); q.y = fmaf(vv.y, vv.y, q.y); q.z = fmaf(vv.z, vv.z, q.z); q.w = fmaf(vv.w, vv.w, q.w);
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                s[i][c] = fmaf(xa[i][3], vv.w, fmaf(xa[i][2], vv.z, fmaf(xa[i][1], vv.y, fmaf(xa[i][0], vv.x, s[i][c]))));
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            lin[i] = fmaf(xa[i][3], wl.w, fmaf(xa[i][2], wl.z, fmaf(xa[i][1], wl.y, fmaf(xa[i][0], wl.x, lin[i]))));
+            t[i] = fmaf(xa[i][3] * xa[i][3], q.w, fmaf(xa[i][2] * xa[i][2], q.z,
+                   fmaf(xa[i][1] * xa[i][1], q.y, fmaf(xa[i][0] * xa[i][0], q.x, t[i]))));
+          }
+        }
+      }
+    }
+    if (!live_w) continue;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float inter = 0.f;
+#pragma unroll
+      for (int c = 0; c < KF; ++c) {
+        if (c < kfm) {
+          const float tot = warp_sum(s[i][c]) + __shfl_sync(0xffffffffu, sps[i], c);
+          inter = fmaf(tot, tot, inter);
+        }
+      }
+      const float tt = warp_sum(t[i] + (lane < kfm ? spt[i] : 0.f));
+      const float ll = warp_sum(lin[i] + (lane == kfm ? sps[i] : 0.f));
+      if (lane == 0 && b0 + i < B) {
+        const float r = __ldg(w0) + ll + 0.5f * (inter - tt);
+        out[b0 + i] = apply_sigmoid ? 1.0f / (1.0f + expf(-r)) : r;
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------- R3 FMLayer, one-hot as gather
 template <int IDKIND>
 __global__ void __launch_bounds__(256)
@@ -376,8 +615,20 @@ extern "C" int ctrhot_fm_dense_f32(const float* x, int64_t x_ld, int64_t n, int6
   if (kfm > 0 && !v) return CTRHOT_EARG;
   if (kfm > 31) return CTRHOT_ESHAPE;
   if (B == 0) return CTRHOT_OK;
-  fm_dense_kernel<<<warp_grid(B, 8), 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out,
-                                                          apply_sigmoid);
+  if (n >= 128 && kfm >= 1 && kfm <= 16) {                    // wide rows: four samples per warp, dense / sparse per 32 columns
+    int64_t nb = ((B + 3) / 4 + 7) / 8;
+    const int grid = (int)(nb < (int64_t)kNumSMs * 8 ? nb : (int64_t)kNumSMs * 8);
+    const bool v4 = (x_ld % 4 == 0) && aligned16(x);
+    if (v4 && kfm <= 8) fm_dense_wide_v4_kernel<8><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+    else if (v4 && kfm <= 12) fm_dense_wide_v4_kernel<12><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+    else if (v4) fm_dense_wide_v4_kernel<16><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+    else if (kfm <= 4) fm_dense_wide_kernel<4><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+    else if (kfm <= 8) fm_dense_wide_kernel<8><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+    else if (kfm <= 12) fm_dense_wide_kernel<12><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+    else fm_dense_wide_kernel<16><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+  } else {
+    fm_dense_kernel<<<warp_grid(B, 8), 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
+  }
   CTRHOT_LAUNCH_OK("ctrhot_fm_dense_f32");
   return CTRHOT_OK;
 }

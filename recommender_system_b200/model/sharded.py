@@ -175,9 +175,9 @@ class ShardedEmbedding:
             self._symm = None
         if self._block is not None:
             torch.cuda.synchronize(self.device)
-            self.arena = None
             self._block.free()
             self._block = None
+        self.arena = None                                                      # an ordinary torch arena is released too
 
     def init_hash(self, seed=1234):
         """value(f, global row, col) from the counter-based hash: any rank can regenerate any row (oracle.synth.hash_table_value)."""

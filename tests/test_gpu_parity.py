@@ -102,6 +102,28 @@ def test_fm_dense(golden, lib):
     close_rel(npy(L(a["x"])), want)
 
 
+@pytest.mark.parametrize("n,kfm,B,density", [(3341, 10, 1001, 1.0), (3341, 10, 3, 1.0), (5000, 8, 259, 0.005),
+                                              (700, 16, 130, 0.3), (129, 1, 64, 1.0), (131, 20, 33, 1.0),
+                                              (5001, 8, 259, 0.005), (701, 16, 130, 0.3), (1021, 12, 77, 0.02)])
+def test_fm_dense_wide_rows(lib, n, kfm, B, density):
+    """FMLayer on wide x (config 5: n = 3341 dense; config 1: one-hot): the four-samples-per-warp kernel with its dense /
+    sparse / skip paths per 32 columns (kfm = 20 stays on the one-sample kernel), 1e-5 relative to the float64 oracle."""
+    rng = np.random.default_rng(n + kfm)
+    x = S.f32(rng.uniform(-0.5, 1.0, (B, n)))
+    if density < 1.0:
+        x = x * (rng.random((B, n)) < density)
+        x[:, :13] = rng.random((B, 13))                     # a dense head like [dense | one-hot]
+    x = S.f32(x)
+    w0, w1, v = S.f32(rng.normal(0, 1, (1,))), S.f32(rng.normal(0, 0.05, (n, 1))), S.f32(rng.normal(0, 0.05, (n, kfm)))
+    want = O.fm_layer(x.astype(np.float64), w0.astype(np.float64), w1.astype(np.float64), v.astype(np.float64))
+    L = FMLayer(kfm)
+    L.build((None, n))
+    L.set_weights([w0, w1, v])
+    xd = torch.zeros((B, n + 3), dtype=torch.float32, device="cuda")      # a row stride that is not the width
+    xd[:, :n] = torch.from_numpy(x)
+    close_rel(npy(L(xd[:, :n])), want)
+
+
 def test_dnn_fp32_and_tf32(golden, lib):
     a, want = S.load_case(golden, "dnn")
     for prec, tol in (("fp32", 2e-5), ("tf32", LOGIT)):
