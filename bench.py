@@ -167,7 +167,8 @@ def secondary(dev, rank):
     return out
 
 
-def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, k=128, B=262144):
+def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, k=128, B=262144,
+                 modes=("fused", "peer", "a2a")):
     """BASELINE.json configs[4]: DeepFM over 26 tables x 10M rows x emb 128 (133 GB) row-sharded over `world` GPUs, global
     B = 262144 (strong scaling: B/world samples per rank), device-resident inputs, CUDA events, max over ranks.  Both
     exchanges are measured: "a2a" (route + NCCL all-to-all pair + pack/unpack kernels) and "peer" (one gather kernel
@@ -208,10 +209,11 @@ def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, 
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    for mode in ("fused", "peer", "a2a"):
+    for mode in modes:
         set_seed(1)
         m = ShardedDeepFM(vocab, k, fm_k=10, hidden_units=(256, 128, 64), device=dev, rank=rank, world=world, exchange=mode)
         m.build()
+        m.cluster = int(os.environ.get("CTRHOT_CFG5_CLUSTER", "0"))      # tuning knob for profiles/; 0 = the library's choice
         m.embed.init_hash(1234)
         it = [0]
 

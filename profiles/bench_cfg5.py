@@ -1,6 +1,6 @@
 """Only the row-sharded config-5 measurement of bench.py (all three exchanges), 1 process or under torchrun:
 
-    python profiles/bench_cfg5.py [rows_per_table]
+    python profiles/bench_cfg5.py [rows_per_table [modes, e.g. fused,peer]]      (CTRHOT_CFG5_CLUSTER=1|2|4 for the fused kernel)
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 profiles/bench_cfg5.py
 """
 import json
@@ -19,7 +19,8 @@ dev = torch.device("cuda", local)
 if world > 1:
     dist.init_process_group("nccl", device_id=dev)
 rows = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
-r = bench.sharded_cfg5(dev, rank, world, rows_per_table=rows)
+modes = tuple(sys.argv[2].split(",")) if len(sys.argv) > 2 else ("fused", "peer", "a2a")
+r = bench.sharded_cfg5(dev, rank, world, rows_per_table=rows, modes=modes)
 if rank == 0:
     print(json.dumps(r), flush=True)
 if world > 1:
