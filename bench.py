@@ -429,10 +429,13 @@ def main():
             hb = {"kernel": "ctr_fused_kernel (gather + split-TF32 FM + TMEM-chained TF32 tower + sigmoid)",
                   "bound": "hbm", "achieved": algo * B / (whole_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
                   "traffic": None, "ms": whole_ms, "peak_src": pk["src"]}
+            if k == 16 and B == 65536 and args.vocab == "kaggle":
+                # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r01d_ncu_summary.md (ncu --set full)
+                hb["traffic"] = 73_980_672
             hb["frac"] = hb["achieved"] / hb["peak"]
             fm_flops = 2 * d * 21                        # FM = 2 * 429 * 21 (the split-TF32 extras are not counted)
             tn = {"kernel": hb["kernel"], "bound": "tensor", "achieved": (flops + fm_flops) * B / (whole_ms * 1e-3) / 1e12,
-                  "peak": tf32_peak, "unit": "TFLOP/s", "traffic": None, "ms": whole_ms,
+                  "peak": tf32_peak, "unit": "TFLOP/s", "traffic": hb["traffic"], "ms": whole_ms,
                   "peak_src": pk["src"] + " bf16 dense / 2 (TF32 runs at half the bf16 rate)"}
             tn["frac"] = tn["achieved"] / tn["peak"]
             front, tower = hb, tn
@@ -476,7 +479,10 @@ def main():
     if not args.no_sharded:
         del model, dev_in, pipe, out
         torch.cuda.empty_cache()
-        sh = sharded_cfg5(dev, rank, world, rows_per_table=args.sharded_rows)
+        try:
+            sh = sharded_cfg5(dev, rank, world, rows_per_table=args.sharded_rows)
+        except Exception as e:                                # the main line must still be printed
+            sh = {"error": "%s: %s" % (type(e).__name__, str(e)[:300])}
     if rank == 0:
         if sh:
             line.setdefault("also", {})["sharded_cfg5"] = sh

@@ -661,11 +661,43 @@ extern "C" int ctrhot_debug_fused_trace(unsigned long long* h_out) {
 #endif
 
 namespace {
+// Resident clusters of C CTAs for this kernel variant (a cluster must fit inside one GPC: 33 clusters of 4 = 132 CTAs,
+// 74 of 2 = 148 on B200).  The occupancy query costs host time, so it is made once per (variant, smem size).
+template <int NL, int C>
+int fu_max_clusters(size_t smem) {
+  static size_t cached_smem = ~(size_t)0;
+  static int cached_n = 0;
+  if (cached_smem == smem && cached_n > 0) return cached_n;
+  auto kern = ctr_fused_kernel<NL, C>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return kNumSMs / C;
+  }
+  int n = kNumSMs / C;
+  if (C > 1) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(FU_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.gridDim = dim3(kNumSMs / C * C);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int q = 0;
+    if (cudaOccupancyMaxActiveClusters(&q, kern, &cfg) == cudaSuccess && q > 0) n = q;
+    else (void)cudaGetLastError();
+  }
+  cached_smem = smem;
+  cached_n = n;
+  return n;
+}
+
 template <int NL, int C>
 int fu_launch(const FuParams& p0, size_t smem, cudaStream_t st) {
   FuParams p = p0;
   auto kern = ctr_fused_kernel<NL, C>;
-  CTRHOT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "ctr_fused attr");
+  const int max_clusters = fu_max_clusters<NL, C>(smem);      // also sets the dynamic shared memory attribute
   p.n_super = (p.n_tiles + C - 1) / C;
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(FU_THREADS);
@@ -676,17 +708,19 @@ int fu_launch(const FuParams& p0, size_t smem, cudaStream_t st) {
   attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  int max_clusters = kNumSMs / C;
-  if (C > 1) {
-    cfg.gridDim = dim3(kNumSMs / C * C);
-    int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0) max_clusters = n;
-    else (void)cudaGetLastError();
-  }
   const int n_clusters = p.n_super < max_clusters ? p.n_super : max_clusters;
   cfg.gridDim = dim3(n_clusters * C);
   CTRHOT_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, p), "ctrhot_ctr_fused_tf32 launch");
   return CTRHOT_OK;
+}
+
+template <int C>
+int fu_max_clusters_nl(int nl, size_t smem) {
+  switch (nl) {
+    case 1: return fu_max_clusters<1, C>(smem);
+    case 2: return fu_max_clusters<2, C>(smem);
+    default: return fu_max_clusters<3, C>(smem);
+  }
 }
 
 template <int C>
@@ -773,7 +807,17 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   if (p.nb < 2) return CTRHOT_ESHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int C = cluster;
-  if (C == 0) C = (p.n_tiles >= 4 * 32) ? 4 : (p.n_tiles >= 2 ? 2 : 1);
+  if (C == 0) {
+    // larger clusters share each weight chunk among more CTAs (less L2 traffic) but leave SMs idle when a GPC's SM count
+    // is not a multiple of the cluster size: take 4 unless 2 saves a whole wave of tiles
+    if (p.n_tiles < 2) C = 1;
+    else if (p.n_tiles < 4 * 32) C = 2;
+    else {
+      const int n4 = fu_max_clusters_nl<4>(nl, smem), n2 = fu_max_clusters_nl<2>(nl, smem);
+      const int w4 = ((p.n_tiles + 3) / 4 + n4 - 1) / n4, w2 = ((p.n_tiles + 1) / 2 + n2 - 1) / n2;
+      C = (w4 <= w2) ? 4 : 2;
+    }
+  }
   // every multicast piece must stay 16-byte granular (it is: rows * 128 / C)
   if (C == 4) return fu_launch_nl<4>(p, nl, smem, st);
   if (C == 2) return fu_launch_nl<2>(p, nl, smem, st);

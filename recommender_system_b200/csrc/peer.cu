@@ -169,7 +169,7 @@ extern "C" int ctrhot_shard_lookup_peer_f32(const void* const* arenas, const int
   int64_t grid = (thr + 255) / 256;
   const int64_t cap = (int64_t)kNumSMs * 8 * 4;               // 8 CTAs of 256 threads per SM, 4 waves
   if (grid > cap) grid = cap;
-  shard_lookup_peer_kernel<4><<<(int)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  shard_lookup_peer_kernel<2><<<(int)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       pa, row_off, F, k, G, ids, n_slots, D, dense, dense_ld, x, x_ld, tl, err_flag);
   CTRHOT_LAUNCH_OK("ctrhot_shard_lookup_peer_f32");
   return CTRHOT_OK;
