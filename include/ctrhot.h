@@ -203,6 +203,14 @@ int ctrhot_ctr_fused_sharded_tf32(const void* const* arenas, const int64_t* row_
                                   const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                                   int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
 
+/* DNNLayer.call (DL/layer/interaction.py:40-46) on a matrix x [M, K] (row stride x_ld, x_ld % 4 == 0, x 16-byte aligned)
+ * that already lives in HBM, by the same persistent kernel: out[m] = (sigmoid of) Dense(h->1)(tower(x[m, :])).
+ * h_layers as for ctrhot_ctr_fused_tf32 with h_layers[0].packed = ctrhot_fused_pack(W1r, NULL, K, n1, K % 4) where
+ * W1r = rows [K - K % 4, K) of W1 followed by rows [0, K - K % 4)  (the kernel reads the 16-byte pieces first). */
+int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M,
+                           const ctrhot_dense_desc* h_layers, int n_layers, int apply_sigmoid, int cluster,
+                           float* out, void* stream);
+
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,
                     const float* var, float eps, float* out, void* stream);

@@ -57,6 +57,8 @@ struct FuLayer {
 constexpr int FU_MAXG = 16;
 struct FuParams {
   const float* arena; const int64_t* row_off; int F; int k4; const void* ids; int ids_kind; int64_t ids_ld;
+  int row_stride4;                                         // 16-byte units between consecutive table rows (= k4 for a table;
+                                                           // = x_ld / 4 when the 'table' is an activation matrix, rows mode)
   int G; const float* peer[FU_MAXG];                       // row-sharded tables (cfg 5): owner = id mod G, arenas mapped over NVLink;
                                                            // row_off is then [G, F+1].  G = 1: peer[0] = arena
   const float* dense; int64_t dense_ld; int D; int emb;
@@ -258,8 +260,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     uint32_t* s_fn = reinterpret_cast<uint32_t*>(fptr + mp.rowoff + 2 * p.F * p.G);
     for (int i = tid; i < p.F * p.G; i += FU_THREADS) {       // entry (owner o, field f) at o * F + f
       const int o = i / p.F, f = i - o * p.F;
-      const int64_t r0 = p.row_off[o * (p.F + 1) + f], nr = p.row_off[o * (p.F + 1) + f + 1] - r0;
-      s_fb[i] = p.peer[o] + r0 * (int64_t)(p.k4 * 4);
+      const int64_t r0 = p.row_off ? p.row_off[o * (p.F + 1) + f] : 0;      // rows mode: one 'field', M rows, no offsets
+      const int64_t nr = p.row_off ? p.row_off[o * (p.F + 1) + f + 1] - r0 : p.M;
+      s_fb[i] = p.peer[o] + r0 * (int64_t)(p.row_stride4 * 4);
       s_fn[i] = nr < 0 ? 0u : (nr > 0x7FFFFFFF ? 0x7FFFFFFFu : (uint32_t)nr);   // ids are int32: larger tables cannot be addressed anyway
     }
     for (int i = tid; i < KC1 * 32; i += FU_THREADS) fptr[mp.sq + i] = p.sq_w ? __ldg(p.sq_w + i) : 0.f;
@@ -299,7 +302,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     const int total_chunks = n_my * KC1;
     const int k4 = p.k4;
     const int f0 = c / k4, part0 = c - f0 * k4;
-    const uint32_t rowbytes = (uint32_t)k4 * 16u;
+    const uint32_t rowbytes = (uint32_t)p.row_stride4 * 16u;
     const uint32_t dst0 = r_base + (uint32_t)rsub * 128u + (uint32_t)((c ^ (rsub & 7)) << 4);   // rows rsub + 16 i: + 2048 i
     const int64_t tile_stride = (int64_t)ncl * C * FU_BM;
     const int64_t first_row0 = ((int64_t)cid * C + crank) * FU_BM;
@@ -315,10 +318,15 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       if (n_fetched >= total_chunks) return;
       ++n_fetched;
       if (cf.f < p.F) {
-        const int32_t* src = static_cast<const int32_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + cf.f;   // int32 or float bits
+        if (p.ids == nullptr) {                            // rows mode: row m of the tile IS row m of the matrix
 #pragma unroll
-        for (int i = 0; i < 8; ++i)                        // rows past M read id 0: a valid row, never consumed
-          reg[i] = (cf.row0 + rsub + 16 * i < p.M) ? __ldg(src + (int64_t)(16 * i) * p.ids_ld) : 0;
+          for (int i = 0; i < 8; ++i) reg[i] = (cf.row0 + rsub + 16 * i < p.M) ? (int32_t)(cf.row0 + rsub + 16 * i) : 0;
+        } else {
+          const int32_t* src = static_cast<const int32_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + cf.f;   // int32 or float bits
+#pragma unroll
+          for (int i = 0; i < 8; ++i)                      // rows past M read id 0: a valid row, never consumed
+            reg[i] = (cf.row0 + rsub + 16 * i < p.M) ? __ldg(src + (int64_t)(16 * i) * p.ids_ld) : 0;
+        }
       }
       advance(cf);
     };
@@ -734,7 +742,7 @@ int fu_launch_nl(const FuParams& p, int nl, size_t smem, cudaStream_t st) {
 
 // peers[0..G): arena of owner g (this rank's own at its index; the others mapped through ctrhot_peer_open); G = 1 is the
 // unsharded case.  row_off is [G, F+1].
-int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off, int F, int k,
+int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off, int row_stride, int F, int k,
              const void* ids, int ids_kind, int64_t ids_ld,
              const float* dense, int64_t dense_ld, int D, int64_t M,
              const ctrhot_dense_desc* h_layers, int n_layers,
@@ -744,7 +752,10 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   for (int g = 0; g < G; ++g) if (!peers[g] || !aligned16(peers[g])) return CTRHOT_EARG;
   if ((int64_t)F * G > 4096) return CTRHOT_ESHAPE;
   const float* arena = peers[rank];
-  if (!arena || !row_off || !ids || !out || !h_layers || F <= 0 || k <= 0 || M < 0 || D < 0) return CTRHOT_EARG;
+  const bool rows_mode = (row_off == nullptr && ids == nullptr);       // ctrhot_tower_rows_tf32: the table is x itself
+  if (!arena || !out || !h_layers || F <= 0 || k <= 0 || M < 0 || D < 0) return CTRHOT_EARG;
+  if (!rows_mode && (!row_off || !ids)) return CTRHOT_EARG;
+  if (rows_mode && (F != 1 || G != 1 || M > 0x7FFFFFFF || row_stride < k || row_stride % 4 != 0)) return CTRHOT_EARG;
   if (D > 0 && !dense) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
   if (mode < FU_MODE_TOWER || mode > FU_MODE_DCN || n_side < 0 || n_side >= FU_SIDE) return CTRHOT_EARG;
@@ -790,6 +801,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   if (M == 0) return CTRHOT_OK;
   p.G = G;
   for (int g = 0; g < FU_MAXG; ++g) p.peer[g] = g < G ? peers[g] : nullptr;
+  p.row_stride4 = rows_mode ? row_stride / 4 : k / 4;
   p.arena = arena; p.row_off = row_off; p.F = F; p.k4 = k / 4; p.ids = ids; p.ids_kind = ids_kind; p.ids_ld = ids_ld;
   p.dense = dense; p.dense_ld = dense_ld; p.D = D; p.emb = F * k;
   p.M = M; p.n_tiles = (int)((M + FU_BM - 1) / FU_BM);
@@ -832,7 +844,7 @@ extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off,
                                      const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                                      int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
   if (!arena) return CTRHOT_EARG;
-  return fu_entry(&arena, 1, 0, row_off, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w, mode,
+  return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w, mode,
                   n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag, stream);
 }
 
@@ -846,6 +858,19 @@ extern "C" int ctrhot_ctr_fused_sharded_tf32(const void* const* arenas, const in
   if (!arenas || G < 1 || G > FU_MAXG) return CTRHOT_EARG;
   const float* peers[FU_MAXG];
   for (int g = 0; g < G; ++g) peers[g] = static_cast<const float*>(arenas[g]);
-  return fu_entry(peers, G, rank, row_off, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w,
+  return fu_entry(peers, G, rank, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w,
                   mode, n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag, stream);
+}
+
+// DNNLayer.call (DL/layer/interaction.py:40-46) on an activation matrix that already lives in HBM: the same persistent
+// kernel with the matrix as its one 'table' (row m of a tile = row m of x, no ids, no offsets).  The first K - K % 4
+// columns are fetched as 16-byte pieces, the K % 4 tail through the dense path (4-byte copies, zero-filled), so neither
+// the padding of a row nor whatever lies behind column K is ever multiplied.
+extern "C" int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M,
+                                      const ctrhot_dense_desc* h_layers, int n_layers, int apply_sigmoid, int cluster,
+                                      float* out, void* stream) {
+  if (!x || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
+  const int r = K % 4, k = K - r;
+  return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, h_layers,
+                  n_layers, nullptr, FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, nullptr, stream);
 }

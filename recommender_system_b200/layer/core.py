@@ -169,6 +169,24 @@ class DenseStack:
         _lib.call("ctrhot_tower_fused_tf32", ptr(x), x_ld, M, arr, len(arr), *self._post(post), ptr(out), stream_ptr())
         return out
 
+    def run_rows(self, x, x_ld, sigmoid, out):
+        """Tower over a matrix in HBM through the persistent whole-model kernel (no ids: row m of x feeds row m)."""
+        arr = self.descs()
+        K, n1 = arr[0].in_dim, arr[0].out_dim
+        r = K % 4
+        key = ("rows", r)
+        if key not in self._packed:
+            W1 = self.layers[0]["kernel"]
+            W1r = torch.cat([W1[K - r:], W1[:K - r]], dim=0).contiguous() if r else W1.contiguous()
+            nbytes = _lib.query("ctrhot_fused_pack_bytes", K, n1)
+            buf = torch.empty(nbytes // 4, dtype=torch.float32, device=W1.device)
+            _lib.call("ctrhot_fused_pack", ptr(W1r), None, K, n1, r, ptr(buf), stream_ptr())
+            self._packed[key] = buf
+        arr[0].packed = ptr(self._packed[key])
+        _lib.call("ctrhot_tower_rows_tf32", ptr(x), x_ld, K, x.shape[0], arr, len(arr), int(bool(sigmoid)), 0, ptr(out),
+                  stream_ptr())
+        return out
+
     def run_fused_gather(self, E, ids, kind, ids_ld, dense, B, post=None, err_flag=None, out=None):
         """Tower fed straight from the embedding arena of EmbedLayer ``E`` (x never exists in HBM)."""
         arr = self.descs()
@@ -239,7 +257,12 @@ class DenseStack:
         n_out = arr[n - 1].out_dim
         if out is None:
             out = torch.empty((M, n_out), dtype=torch.float32, device=x.device)
-        if self.fused_ok(arr) and x_ld % 4 == 0 and x.data_ptr() % 16 == 0 and out.stride(0) == 1:
+        aligned = x_ld % 4 == 0 and x.data_ptr() % 16 == 0 and out.stride(0) == 1
+        K = arr[0].in_dim
+        if aligned and M >= 128 and K >= 4 and self.ctr_fused_ok(1, 4, arr):
+            # the whole-model kernel with x as its one 'table' (ctrhot_tower_rows_tf32): warp-specialised, TMEM-chained
+            return self.run_rows(x, x_ld, final_sigmoid, out)
+        if self.fused_ok(arr) and aligned:
             return self.run_fused(x, x_ld, {"sigmoid": True} if final_sigmoid else None, out)
         need = _lib.query("ctrhot_mlp_workspace_bytes", M, arr, n)
         if self._ws is None or self._ws.numel() * 4 < need or self._ws.device != x.device:

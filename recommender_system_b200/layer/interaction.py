@@ -335,8 +335,9 @@ class Attention(Layer):
                   arr, len(arr), ptr(self.out_kernel), ptr(self.out_bias), ptr(out), out.stride(0), stream_ptr())
         return out
 
-    def call_gather(self, table, hist_ids, cand_ids, check_flag=None):
-        """Fused history/candidate gather + attention: keys never reach HBM.  -> (att [B,K], item [B,K])."""
+    def call_gather(self, table, hist_ids, cand_ids, check_flag=None, out=None):
+        """Fused history/candidate gather + attention: keys never reach HBM.  -> (att [B,K], item [B,K]);
+        ``out=(att, item)``: write into these (row-strided) views instead, e.g. columns of the tower's input matrix."""
         hist_ids, kind, hist_ld = ids_arg(hist_ids)
         cand_ids, kind2, cand_ld = ids_arg(cand_ids)
         if kind2 != kind:
@@ -344,8 +345,7 @@ class Attention(Layer):
         B, T = hist_ids.shape
         V, K = table.shape
         arr, _keep = self.descs()
-        att = _out(B, self.device, K)
-        item = _out(B, self.device, K)
+        att, item = out if out is not None else (_out(B, self.device, K), _out(B, self.device, K))
         if self.precision == "tf32" and self.activation == "prelu" and len(self.layers) == 2:
             h1, h2 = self.hidden_units
             nbytes = _lib.load().ctrhot_din_pack_bytes(T, K, h1, h2)

@@ -113,7 +113,11 @@ class DIN(Model):
         ld = (self.dcat + 3) // 4 * 4                           # 16-byte aligned rows for the tower kernel
         emb = torch.empty((B, ld), dtype=torch.float32, device=dev)[:, :self.dcat]
         K = self.K
-        if self.behavior_num == 1:
+        direct = self.behavior_num == 1 and K % 4 == 0
+        if direct:
+            # the attention kernel writes [att | item] straight into the tower's input matrix (din.py:84-90's concat)
+            self.att_layer.call_gather(self.embed_seq_layers[0], hist[0], cand[:, 0:1], flag, out=(emb[:, :K], emb[:, K:2 * K]))
+        elif self.behavior_num == 1:
             att, item = self.att_layer.call_gather(self.embed_seq_layers[0], hist[0], cand[:, 0:1], flag)
         else:
             keys, items = [], []
@@ -129,8 +133,9 @@ class DIN(Model):
             item = torch.cat(items, dim=-1)
             m = (hist[0] != 0).to(torch.float32)
             att = self.att_layer([item, key, key, m])
-        emb[:, :K] = att
-        emb[:, K:2 * K] = item
+        if not direct:
+            emb[:, :K] = att
+            emb[:, K:2 * K] = item
         col = 2 * K
         for i, (f, tab) in enumerate(zip(self.other_sparse, self.embed_sparse_layers)):
             ids = _ids_to_device(self._col(inputs, f["feat"]), dev)
