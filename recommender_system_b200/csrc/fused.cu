@@ -455,6 +455,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BN);
           const uint32_t idesc32 = make_idesc_tf32(FU_BM, 32u), idesc16 = make_idesc_tf32(FU_BM, 16u);
           const uint32_t d_t = tmem_base + (uint32_t)L.col;
+          const bool side_on = (p.mode != FU_MODE_TOWER);      // a plain tower has no side products: skip their MMAs
           if (NL == 1 && lt > 0) { FU_TWAIT(4, mbar_wait(last_free, (uint32_t)(lt - 1) & 1u)); tc_fence_after(); }
           for (int kc = 0; kc < L.KC; ++kc) {
             FU_TWAIT(0, mbar_wait(full_b(sb), pb));
@@ -466,15 +467,15 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               mma_tf32_ts(d_t, a_hi + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
-#if !(FU_EXP_ & 1)
-              mma_tf32_ts(ds_t, a_hi + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
-#endif
+              // (folding the side columns into the main MMA as two N = 144 halves was measured SLOWER, 88.9 -> 92.5 us:
+              //  an MMA wider than 128 columns costs the full 138 cycles; kept in git history only)
+              if (side_on) mma_tf32_ts(ds_t, a_hi + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
             }
-#if !(FU_EXP_ & 2)
+            if (side_on) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              mma_tf32_ts(ds_t, a_lo + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc16, 1u);
-#endif
+              for (int k = 0; k < 4; ++k)
+                mma_tf32_ts(ds_t, a_lo + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc16, 1u);
+            }
             mma_commit(a_free(sa));
             if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
             if (++sa == (uint32_t)p.n_as) { sa = 0; pa ^= 1u; }
