@@ -203,6 +203,16 @@ int ctrhot_ctr_fused_sharded_tf32(const void* const* arenas, const int64_t* row_
                                   const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                                   int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
 
+/* WideDeep.call (DL/model/wideDeep.py:24-34): out[m] = (sigmoid of) scale * (add_vec[m] + DNN([Embed(ids), dense])[m]) --
+ * the deep tower fed straight from the embedding arena by the persistent kernel; add_vec (device [M], may be NULL) is the
+ * wide logit from ctrhot_wide_onehot_f32.  h_layers[0].packed = ctrhot_fused_pack(W1, NULL, n, n1, D). */
+int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                          const void* ids, int ids_kind, int64_t ids_ld,
+                          const float* dense, int64_t dense_ld, int D, int64_t M,
+                          const ctrhot_dense_desc* h_layers, int n_layers,
+                          const float* add_vec, float scale, int apply_sigmoid, int cluster,
+                          float* out, int* err_flag, void* stream);
+
 /* DNNLayer.call (DL/layer/interaction.py:40-46) on a matrix x [M, K] (row stride x_ld, x_ld % 4 == 0, x 16-byte aligned)
  * that already lives in HBM, by the same persistent kernel: out[m] = (sigmoid of) Dense(h->1)(tower(x[m, :])).
  * h_layers as for ctrhot_ctr_fused_tf32 with h_layers[0].packed = ctrhot_fused_pack(W1r, NULL, K, n1, K % 4) where

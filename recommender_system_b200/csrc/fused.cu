@@ -71,6 +71,7 @@ struct FuParams {
   int ds_col;                                              // TMEM column of the side accumulator
   int a_col, n_as;                                         // TMEM A ring: first column, slots (64 columns each)
   int nb;                                                  // W ring stages in use (<= FU_NB)
+  const float* add_vec; float out_scale;                   // tower mode: out = out_scale * (y + add_vec[m])   (WideDeep)
   float* out; int* err_flag;
   uint32_t b_stage_bytes;
 };
@@ -594,7 +595,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             float r;
             if (p.mode == FU_MODE_DEEPFM) r = 0.5f * (side + y);
             else if (p.mode == FU_MODE_DCN) r = side + fmaf(y, p.cb[p.n_side + 1], p.cb[p.n_side + 2]);
-            else r = y;
+            else r = p.out_scale * (y + (p.add_vec ? __ldg(p.add_vec + gm) : 0.f));
             p.out[gm] = p.apply_sigmoid ? 1.0f / (1.0f + __expf(-r)) : r;
           }
         }
@@ -748,7 +749,8 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
              const float* dense, int64_t dense_ld, int D, int64_t M,
              const ctrhot_dense_desc* h_layers, int n_layers,
              const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
-             int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+             int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream,
+             const float* add_vec = nullptr, float out_scale = 1.f) {
   if (!peers || G < 1 || G > FU_MAXG || rank < 0 || rank >= G) return CTRHOT_EARG;
   for (int g = 0; g < G; ++g) if (!peers[g] || !aligned16(peers[g])) return CTRHOT_EARG;
   if ((int64_t)F * G > 4096) return CTRHOT_ESHAPE;
@@ -810,6 +812,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid;
   for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
+  p.add_vec = add_vec; p.out_scale = out_scale;
   const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl);
   const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1;
   size_t smem = 0;
@@ -874,4 +877,17 @@ extern "C" int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64
   const int r = K % 4, k = K - r;
   return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, h_layers,
                   n_layers, nullptr, FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, nullptr, stream);
+}
+
+// WideDeep.call (DL/model/wideDeep.py:24-34): out = sigmoid(scale * (add_vec[m] + DNN(Embed(ids))[m])) with the deep tower
+// fed straight from the embedding arena by the persistent kernel (no side products: main MMAs only).
+extern "C" int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                     const void* ids, int ids_kind, int64_t ids_ld,
+                                     const float* dense, int64_t dense_ld, int D, int64_t M,
+                                     const ctrhot_dense_desc* h_layers, int n_layers,
+                                     const float* add_vec, float scale, int apply_sigmoid, int cluster,
+                                     float* out, int* err_flag, void* stream) {
+  if (!arena) return CTRHOT_EARG;
+  return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, nullptr,
+                  FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, err_flag, stream, add_vec, scale);
 }

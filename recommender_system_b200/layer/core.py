@@ -187,6 +187,26 @@ class DenseStack:
                   stream_ptr())
         return out
 
+    def run_ctr_tower(self, E, ids, kind, ids_ld, dense, B, first_kernel_ref, add_vec=None, scale=1.0, sigmoid=False,
+                      err_flag=None, out=None, cluster=0):
+        """Tower fed from EmbedLayer ``E`` by the whole-model kernel; out = (sigmoid of) scale * (add_vec + y)."""
+        arr = self.descs()
+        n, n1 = int(first_kernel_ref.shape[0]), int(first_kernel_ref.shape[1])
+        D = 0 if dense is None else dense.shape[1]
+        key = ("fused", None)
+        if key not in self._packed:
+            nbytes = _lib.query("ctrhot_fused_pack_bytes", n, n1)
+            buf = torch.empty(nbytes // 4, dtype=torch.float32, device=first_kernel_ref.device)
+            _lib.call("ctrhot_fused_pack", ptr(first_kernel_ref.contiguous()), None, n, n1, D, ptr(buf), stream_ptr())
+            self._packed[key] = buf
+        arr[0].packed = ptr(self._packed[key])
+        if out is None:
+            out = torch.empty((B, 1), dtype=torch.float32, device=E.arena.device)
+        _lib.call("ctrhot_ctr_tower_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(dense),
+                  0 if dense is None else dense.stride(0), D, B, arr, len(arr), ptr(add_vec), float(scale),
+                  int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag), stream_ptr())
+        return out
+
     def run_fused_gather(self, E, ids, kind, ids_ld, dense, B, post=None, err_flag=None, out=None):
         """Tower fed straight from the embedding arena of EmbedLayer ``E`` (x never exists in HBM)."""
         arr = self.descs()

@@ -265,9 +265,19 @@ class WideDeep(_EmbedTowerModel):
         else:
             dense2 = torch.cat([dense, dense], dim=1)
             wide_out = self.wide.call_onehot(dense2, self.dense_col, ids, self.col_off)
+        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        stack = self.deep.stack
+        stack.set_layers(self.deep.layer_dicts(), self.deep._version)
+        if self.deep.output_dim == 1 and stack.ctr_fused_ok(E.F, E.k):
+            # deep tower fed from the arena by the persistent kernel, wide logit added in its epilogue: two launches in all
+            ids2, kind, ids_ld = ids_arg(ids)
+            stack.run_ctr_tower(E, ids2, kind, ids_ld, None, B, self.deep.hidden[0][0], add_vec=wide_out, scale=0.5,
+                                sigmoid=True, err_flag=E.err_flag(), out=out)
+            if self.check:
+                E.check_ids()
+            return out
         emb = E.gather(ids)
         deep_out = self.deep(emb)
-        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
         _lib.call("ctrhot_combine_sigmoid_f32", ptr(wide_out), ptr(deep_out), 0, 0, 0.5, B, ptr(out), stream_ptr())
         if self.check:
             E.check_ids()
