@@ -23,38 +23,59 @@ gather_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_o
   const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
   constexpr int U = 4;
   if (VEC) {
+    // Work items = (sample, pass of 32*U chunks).  The ids of item i+1 are loaded BEFORE the row loads of item i are
+    // issued, so a warp pays one DRAM round trip per item (rows), not two (ids, then rows).
     const int k4 = k >> 2;
     const int total = F * k4;
-    for (int64_t b = warp; b < B; b += nwarps) {
-      for (int j = lane; j < D; j += 32) out[b * out_ld + j] = __ldg(dense + b * dense_ld + j);
-      float* orow = out + b * out_ld + D;
-      for (int q0 = 0; q0 < total; q0 += 32 * U) {
-        float4 buf[U];
+    const int span = 32 * U;
+    auto load_ids = [&](int64_t b, int q0, int64_t (&id)[U]) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int q = q0 + u * 32 + lane;
-          buf[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (q < total) {
-            const int f = q / k4, c = q - f * k4;
-            const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
-            const int64_t r0 = row_off[f], r1 = row_off[f + 1];
-            if (id >= 0 && id < r1 - r0) buf[u] = ldg_nc_f4(arena + (r0 + id) * k + c * 4);
-            else if (err_flag) *err_flag = 1;
-          }
+      for (int u = 0; u < U; ++u) {
+        const int q = q0 + u * 32 + lane;
+        id[u] = -1;
+        if (q < total && b < B) id[u] = IdLoad<IDKIND>::at(ids, b * ids_ld + q / k4);
+      }
+    };
+    int64_t b = warp;
+    int q0 = 0;
+    int64_t idc[U], idn[U];
+    load_ids(b, q0, idc);
+    while (b < B) {
+      int64_t bn = b;
+      int qn = q0 + span;
+      if (qn >= total) { qn = 0; bn = b + nwarps; }
+      load_ids(bn, qn, idn);
+      float4 buf[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int q = q0 + u * 32 + lane;
+        buf[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (q < total) {
+          const int f = q / k4, c = q - f * k4;
+          const int64_t r0 = __ldg(row_off + f), r1 = __ldg(row_off + f + 1);
+          if (idc[u] >= 0 && idc[u] < r1 - r0) buf[u] = ldg_nc_f4(arena + (r0 + idc[u]) * k + c * 4);
+          else if (err_flag) *err_flag = 1;
         }
+      }
+      if (q0 == 0)
+        for (int j = lane; j < D; j += 32) out[b * out_ld + j] = __ldg(dense + b * dense_ld + j);
+      float* orow = out + b * out_ld + D;
+      const bool al = (reinterpret_cast<uintptr_t>(orow) & 15) == 0;
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int q = q0 + u * 32 + lane;
-          if (q < total) {
-            if (((reinterpret_cast<uintptr_t>(orow) & 15) == 0)) {
-              stg_na_f4(orow + q * 4, buf[u]);
-            } else {
-              orow[q * 4 + 0] = buf[u].x; orow[q * 4 + 1] = buf[u].y;
-              orow[q * 4 + 2] = buf[u].z; orow[q * 4 + 3] = buf[u].w;
-            }
+      for (int u = 0; u < U; ++u) {
+        const int q = q0 + u * 32 + lane;
+        if (q < total) {
+          if (al) {
+            stg_na_f4(orow + q * 4, buf[u]);
+          } else {
+            orow[q * 4 + 0] = buf[u].x; orow[q * 4 + 1] = buf[u].y;
+            orow[q * 4 + 2] = buf[u].z; orow[q * 4 + 3] = buf[u].w;
           }
         }
       }
+#pragma unroll
+      for (int u = 0; u < U; ++u) idc[u] = idn[u];
+      b = bn; q0 = qn;
     }
   } else {
     const int total = F * k;

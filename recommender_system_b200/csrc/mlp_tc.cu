@@ -1,16 +1,10 @@
 // K7: Dense tower on the 5th-gen tensor cores.  y = act(x @ W + b), TF32 multiply / fp32 accumulate.
 //
-// One CTA = one 128-row x BN-column output tile (BN <= 256, fp32 accumulator = BN TMEM columns).
-//   warps 0-3  A producers: 128-bit global loads of the x tile -> round-to-nearest TF32 -> st.shared in the
-//              128-byte-swizzled K-major layout the UMMA descriptor expects; afterwards the epilogue
-//              (tcgen05.ld of their own 32 TMEM lanes -> bias + activation -> store, or the fused
-//              final Dense(h->1) dot).
-//   warp 4     owns TMEM (tcgen05.alloc/dealloc); lane 0 issues tcgen05.mma.kind::tf32 (M=128,N=BN,K=8)
-//              four per 32-column K chunk and tcgen05.commit's the stage back to the producers.
-//   warp 5     lane 0 streams the pre-packed, pre-swizzled W chunk (BN x 128 B, one contiguous
-//              block) with a single cp.async.bulk per stage (TMA engine, mbarrier complete_tx).
-// Two CTAs are resident per SM (<= 100 KB smem, <= 256 TMEM columns each) so one CTA's epilogue
-// overlaps the other's main loop.  Tensor-bound roofline: 2*M*K*N flop per layer.
+// A layer is a persistent kernel (one CTA per SM over 128-row tiles, column tiles of BN <= 256 accumulated in two
+// alternating 256-column TMEM buffers); see dense_tc_kernel below.  The chain of layers goes through HBM (fp32), a
+// trailing Dense(N -> 1) is folded into the previous layer's epilogue.  Used for every tower shape the single-kernel
+// towers (tower_fused.cu, fused.cu) do not take, e.g. DCN's 400-wide tower (cfg 3).
+// Roofline per layer: tensor 2*M*K*N flop at the TF32 rate, HBM 4*M*(K + N) bytes.
 #include "common.cuh"
 #include "epilogue.cuh"
 #include "mlp.cuh"
@@ -29,7 +23,7 @@ struct TcParams {
   const float* Wp; const float* bias; Epilogue ep;
   float* Y; int64_t y_ld;
   const float* dot_w; const float* dot_b; float* y_dot;   // fused Dense(N -> 1) (N fits one tile)
-  int KC, BN, stages, tmem_cols;
+  int KC, BN, stages, tmem_cols, n_tiles;
 };
 
 TcGeom tc_geom(int K, int N) {
@@ -59,8 +53,63 @@ __global__ void mlp_pack_kernel(const float* __restrict__ W, int K, int N, int K
   }
 }
 
+// ---------------------------------------------------------------- persistent layer kernel
+// One CTA per SM walks 128-row tiles; per row tile it runs the layer's n_tiles column tiles back to back (the second
+// pass over the x rows hits L2), each into one of TWO TMEM accumulator buffers so that the epilogue of one step runs
+// under the MMAs of the next.  14 warps:
+//   warps 0-3   epilogue: tcgen05.ld of their own 32 TMEM lanes -> bias + activation -> 128 B per row and chunk to HBM,
+//               or the fused trailing Dense(N -> 1) dot (accumulated in registers across the column tiles).
+//   warps 4-11  A producers: coalesced 128-bit loads of x (4 rows per warp instruction) held in registers TC_PF chunks
+//               ahead of their use -> round-to-nearest TF32 -> st.shared in the 128-byte-swizzled K-major layout.
+//   warp 12     lane 0 issues tcgen05.mma.kind::tf32 (M=128, N=BN, K=8), four per 32-column chunk.
+//   warp 13     lane 0 streams the pre-swizzled W chunk (BN x 128 B) with one cp.async.bulk per stage.
+constexpr int TC_THREADS = 14 * 32;
+constexpr int TC_PF = 4;                     // chunks of x in registers ahead of the smem ring
+constexpr int TC_ACC_COLS = 256;             // columns per accumulator buffer
+
+constexpr int TC_MAXN = 1024;                // widest layer the persistent kernel stages vectors for (n_tiles * BN)
+
+// bias + activation (+ the trailing-dot partial sum) on W columns held by one thread; padding columns come out as 0
+template <int W>
+__device__ __forceinline__ void tc_epi_chunk(float (&acc)[W], const float* sb, const float* sa, const float* sd, float& dot) {
+  float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < W; j += 4) {
+    const float4 b = *reinterpret_cast<const float4*>(sb + j);
+    const float4 a = *reinterpret_cast<const float4*>(sa + j);
+    const float4 w = *reinterpret_cast<const float4*>(sd + j);
+    float t;
+    t = acc[j + 0] + b.x; t = fmaxf(t, 0.f) + a.x * fminf(t, 0.f); acc[j + 0] = t; d0 = fmaf(t, w.x, d0);
+    t = acc[j + 1] + b.y; t = fmaxf(t, 0.f) + a.y * fminf(t, 0.f); acc[j + 1] = t; d1 = fmaf(t, w.y, d1);
+    t = acc[j + 2] + b.z; t = fmaxf(t, 0.f) + a.z * fminf(t, 0.f); acc[j + 2] = t; d0 = fmaf(t, w.z, d0);
+    t = acc[j + 3] + b.w; t = fmaxf(t, 0.f) + a.w * fminf(t, 0.f); acc[j + 3] = t; d1 = fmaf(t, w.w, d1);
+  }
+  dot += d0 + d1;
+}
+
+// W consecutive columns [n0, n0 + W) of one output row
+template <int W>
+__device__ __forceinline__ void tc_store_chunk(const float (&acc)[W], float* row, int n0, int N, int64_t y_ld, bool vec) {
+  float* dst = row + n0;
+  if (vec && n0 + W <= y_ld) {
+#pragma unroll
+    for (int j = 0; j < W; j += 4)
+      stg_na_f4(dst + j, make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]));   // asm: no alignment inference
+  } else {
+#pragma unroll
+    for (int j = 0; j < W; ++j) if (n0 + j < N) dst[j] = acc[j];
+  }
+}
+
+struct TcCursor {
+  int lt, nt, kc;
+  __device__ __forceinline__ void advance(int KC, int n_tiles) {
+    if (++kc == KC) { kc = 0; if (++nt == n_tiles) { nt = 0; ++lt; } }
+  }
+};
+
 template <bool VEC>
-__global__ void __launch_bounds__(192, 2)
+__global__ void __launch_bounds__(TC_THREADS, 1)
 dense_tc_kernel(const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
@@ -68,40 +117,62 @@ dense_tc_kernel(const TcParams p) {
   uint8_t* base_ptr = smem_raw + (base - raw_addr);
   const uint32_t b_bytes = (uint32_t)p.BN * 128u;
   const uint32_t stage_bytes = TC_A_BYTES + b_bytes;
-  const uint32_t bars = base + p.stages * stage_bytes;          // full[S], empty[S], accum, tmem slot
+  const uint32_t bars = base + p.stages * stage_bytes;          // full[S], empty[S], acc_full[2], acc_free[2], tmem slot
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (p.stages + s); };
-  const uint32_t accum_bar = bars + 8u * (2 * p.stages);
-  const uint32_t slot_addr = accum_bar + 8u;
+  auto acc_full = [&](int b) { return bars + 8u * (2 * p.stages + b); };
+  auto acc_free = [&](int b) { return bars + 8u * (2 * p.stages + 2 + b); };
+  const uint32_t slot_addr = bars + 8u * (2 * p.stages + 4);
   volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (slot_addr - base));
+  // per-column vectors of the layer, zero-padded to n_tiles * BN: bias | slope of the negative side | trailing-dot weights
+  float* s_vec = reinterpret_cast<float*>(base_ptr + (bars + 256u - base));
+  const int NP = p.n_tiles * p.BN;
+  float* s_bias = s_vec;
+  float* s_alpha = s_vec + TC_MAXN;
+  float* s_dot = s_vec + 2 * TC_MAXN;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // none / relu / PReLU with one alpha row: act(t) = max(t, 0) + a * min(t, 0) with a = 1 / 0 / alpha[n]
+  const bool fast_act = p.ep.act == CTRHOT_ACT_NONE || p.ep.act == CTRHOT_ACT_RELU ||
+                        (p.ep.act == CTRHOT_ACT_PRELU && p.ep.alpha_rows == 1);
+  for (int i = tid; i < NP; i += TC_THREADS) {
+    s_bias[i] = (i < p.N && p.bias) ? __ldg(p.bias + i) : 0.f;
+    float a = 0.f;
+    if (i < p.N) a = (p.ep.act == CTRHOT_ACT_NONE) ? 1.f : (p.ep.act == CTRHOT_ACT_PRELU && fast_act ? __ldg(p.ep.p + i) : 0.f);
+    s_alpha[i] = a;
+    s_dot[i] = (i < p.N && p.dot_w) ? __ldg(p.dot_w + i) : 0.f;
+  }
   if (tid == 0) {
-    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 4 + 1); mbar_init(empty_bar(s), 1); }
-    mbar_init(accum_bar, 1);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 8 + 1); mbar_init(empty_bar(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(acc_full(b), 1); mbar_init(acc_free(b), 4); }
     mbar_fence_init();
   }
-  if (warp == 4) { tmem_alloc(slot_addr, (uint32_t)p.tmem_cols); tmem_relinquish(); }
+  if (warp == 12) { tmem_alloc(slot_addr, 512u); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *slot_ptr;
 
-  const int64_t m0 = (int64_t)blockIdx.y * TC_BM;
-  const int nt = blockIdx.x;
+  const int n_row_tiles = (int)((p.M + TC_BM - 1) / TC_BM);
+  const int n_my = ((int)blockIdx.x < n_row_tiles) ? (n_row_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int KC = p.KC, NT = p.n_tiles;
+  const int total_chunks = n_my * NT * KC;
 
-  if (warp < 4) {
-    // ------------------------------------------------ A producer
-    const int c = tid & 7;                       // 16-byte chunk within the 128-byte row
-    const int r0 = tid >> 3;                     // 0..15
-    for (int kc = 0; kc < p.KC; ++kc) {
-      const int s = kc % p.stages;
-      const uint32_t ph = (uint32_t)(kc / p.stages) & 1u;
-      float4 v[8];
-      const int col = kc * TC_BK + c * 4;
+  if (warp >= 4 && warp < 12) {
+    // ------------------------------------------------ A producers (256 threads: piece c of rows r0 + 32 i)
+    const int t = tid - 128;
+    const int c = t & 7;
+    const int r0 = t >> 3;                      // 0..31
+    TcCursor cf{0, 0, 0}, cp{0, 0, 0};
+    int n_fetched = 0;
+    auto fetch = [&](float4 (&v)[4]) {
+      if (n_fetched >= total_chunks) return;
+      ++n_fetched;
+      const int64_t m0 = ((int64_t)blockIdx.x + (int64_t)cf.lt * gridDim.x) * TC_BM;
+      const int col = cf.kc * TC_BK + c * 4;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int64_t gm = m0 + r0 + 16 * i;
+      for (int i = 0; i < 4; ++i) {
+        const int64_t gm = m0 + r0 + 32 * i;
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (gm < p.M) {
           const float* src = p.X + gm * p.x_ld + col;
@@ -115,93 +186,136 @@ dense_tc_kernel(const TcParams p) {
           }
         }
       }
-      mbar_wait(empty_bar(s), ph ^ 1u);
+      cf.advance(KC, NT);
+    };
+    auto put = [&](int g, const float4 (&v)[4]) {
+      const int s = g % p.stages;
+      mbar_wait(empty_bar(s), (((uint32_t)(g / p.stages)) & 1u) ^ 1u);
       uint8_t* a_tile = base_ptr + (size_t)s * stage_bytes;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint32_t row = (uint32_t)(r0 + 16 * i);
-        float4 t = v[i];
-        t.x = to_tf32_rna(t.x); t.y = to_tf32_rna(t.y); t.z = to_tf32_rna(t.z); t.w = to_tf32_rna(t.w);
-        *reinterpret_cast<float4*>(a_tile + sw128_offset(row, (uint32_t)c)) = t;
+      for (int i = 0; i < 4; ++i) {
+        float4 q = v[i];
+        q.x = to_tf32_rna(q.x); q.y = to_tf32_rna(q.y); q.z = to_tf32_rna(q.z); q.w = to_tf32_rna(q.w);
+        *reinterpret_cast<float4*>(a_tile + sw128_offset((uint32_t)(r0 + 32 * i), (uint32_t)c)) = q;
       }
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(full_bar(s));
+    };
+    static_assert(TC_PF == 4, "the loop below is unrolled for four register sets");
+    float4 va[4], vb[4], vc[4], vd[4];
+    fetch(va); fetch(vb); fetch(vc); fetch(vd);
+    for (int g = 0; g < total_chunks; g += TC_PF) {
+      put(g, va); fetch(va);
+      if (g + 1 < total_chunks) { put(g + 1, vb); fetch(vb); }
+      if (g + 2 < total_chunks) { put(g + 2, vc); fetch(vc); }
+      if (g + 3 < total_chunks) { put(g + 3, vd); fetch(vd); }
     }
-    // ------------------------------------------------ epilogue
-    mbar_wait(accum_bar, 0);
-    tc_fence_after();
-    const int row = warp * 32 + lane;
-    const int64_t gm = m0 + row;
-    const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
-    float dot = 0.f;
-    for (int c0 = 0; c0 < p.BN; c0 += 16) {
-      float acc[16];
-      tmem_ld16(t_lane + (uint32_t)c0, acc);
-      const int n0 = nt * p.BN + c0;
-      if (gm < p.M) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int n = n0 + j;
-          float t = 0.f;
-          if (n < p.N) {
-            t = acc[j] + (p.bias ? __ldg(p.bias + n) : 0.f);
-            t = p.ep.apply(t, gm, n, p.N);
-            if (p.dot_w) dot = fmaf(t, __ldg(p.dot_w + n), dot);
-          }
-          acc[j] = t;
-        }
-        if (p.Y) {
-          float* dst = p.Y + gm * p.y_ld + n0;
-          if (((p.y_ld & 3) == 0) && n0 + 16 <= p.y_ld && ((reinterpret_cast<uintptr_t>(p.Y) & 15) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 16; j += 4)
-              if (n0 + j < p.y_ld) stg_na_f4(dst + j, make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]));   // asm: no alignment inference
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) if (n0 + j < p.N) dst[j] = acc[j];
-          }
-        }
-      }
-    }
-    if (p.dot_w && gm < p.M) p.y_dot[gm] = dot + (p.dot_b ? __ldg(p.dot_b) : 0.f);
-    tc_fence_before();
-  } else if (warp == 4) {
+    (void)cp;
+  } else if (warp == 12) {
     // ------------------------------------------------ MMA issuer
     if (lane == 0) {
       const uint32_t idesc = make_idesc_tf32(TC_BM, (uint32_t)p.BN);
-      for (int kc = 0; kc < p.KC; ++kc) {
-        const int s = kc % p.stages;
-        const uint32_t ph = (uint32_t)(kc / p.stages) & 1u;
-        mbar_wait(full_bar(s), ph);
-        tc_fence_after();
-        const uint32_t a_addr = base + s * stage_bytes;
-        const uint64_t da = make_desc_sw128(a_addr);
-        const uint64_t db = make_desc_sw128(a_addr + TC_A_BYTES);
+      int g = 0;
+      uint32_t step = 0;
+      for (int lt = 0; lt < n_my; ++lt) {
+        for (int nt = 0; nt < NT; ++nt, ++step) {
+          const uint32_t buf = step & 1u;
+          mbar_wait(acc_free(buf), ((step >> 1) & 1u) ^ 1u);          // the epilogue has drained this buffer
+          tc_fence_after();
+          const uint32_t d_t = tmem_base + buf * TC_ACC_COLS;
+          for (int kc = 0; kc < KC; ++kc, ++g) {
+            const int s = g % p.stages;
+            mbar_wait(full_bar(s), ((uint32_t)(g / p.stages)) & 1u);
+            tc_fence_after();
+            const uint32_t a_addr = base + s * stage_bytes;
+            const uint64_t da = make_desc_sw128(a_addr);
+            const uint64_t db = make_desc_sw128(a_addr + TC_A_BYTES);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)       // 4 x (K=8 tf32 = 32 bytes) per 128-byte swizzle row
-          mma_tf32_ss(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
-        mma_commit(empty_bar(s));
+            for (int k = 0; k < 4; ++k)       // 4 x (K=8 tf32 = 32 bytes) per 128-byte swizzle row
+              mma_tf32_ss(d_t, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
+            mma_commit(empty_bar(s));
+          }
+          mma_commit(acc_full(buf));
+        }
       }
-      mma_commit(accum_bar);
+    }
+    __syncwarp();
+  } else if (warp == 13) {
+    // ------------------------------------------------ W producer (bulk async copy)
+    if (lane == 0) {
+      int g = 0;
+      for (int lt = 0; lt < n_my; ++lt) {
+        for (int nt = 0; nt < NT; ++nt) {
+          const float* wsrc = p.Wp + (size_t)nt * KC * p.BN * TC_BK;
+          for (int kc = 0; kc < KC; ++kc, ++g) {
+            const int s = g % p.stages;
+            mbar_wait(empty_bar(s), (((uint32_t)(g / p.stages)) & 1u) ^ 1u);
+            mbar_arrive_expect_tx(full_bar(s), b_bytes);
+            bulk_g2s(base + s * stage_bytes + TC_A_BYTES, wsrc + (size_t)kc * p.BN * TC_BK, b_bytes, full_bar(s));
+          }
+        }
+      }
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------ W producer (bulk async copy)
-    if (lane == 0) {
-      const float* wsrc = p.Wp + (size_t)nt * p.KC * p.BN * TC_BK;
-      for (int kc = 0; kc < p.KC; ++kc) {
-        const int s = kc % p.stages;
-        const uint32_t ph = (uint32_t)(kc / p.stages) & 1u;
-        mbar_wait(empty_bar(s), ph ^ 1u);
-        mbar_arrive_expect_tx(full_bar(s), b_bytes);
-        bulk_g2s(base + s * stage_bytes + TC_A_BYTES, wsrc + (size_t)kc * p.BN * TC_BK, b_bytes, full_bar(s));
+    // ------------------------------------------------ epilogue (warps 0-3 = TMEM lane quarters 0-3)
+    const int row = warp * 32 + lane;
+    const bool y_vec = p.Y && ((p.y_ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.Y) & 15) == 0);
+    uint32_t step = 0;
+    for (int lt = 0; lt < n_my; ++lt) {
+      const int64_t gm = ((int64_t)blockIdx.x + (int64_t)lt * gridDim.x) * TC_BM + row;
+      float dot = 0.f;
+      for (int nt = 0; nt < NT; ++nt, ++step) {
+        const uint32_t buf = step & 1u;
+        mbar_wait(acc_full(buf), (step >> 1) & 1u);
+        tc_fence_after();
+        const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16) + buf * TC_ACC_COLS;
+        if (fast_act) {
+          for (int c0 = 0; c0 < p.BN; c0 += 32) {
+            const int n0 = nt * p.BN + c0;
+            if (c0 + 32 <= p.BN) {
+              float acc[32];
+              tmem_ld32(t_lane + (uint32_t)c0, acc);
+              tc_epi_chunk<32>(acc, s_bias + n0, s_alpha + n0, s_dot + n0, dot);
+              if (gm < p.M && p.Y) tc_store_chunk<32>(acc, p.Y + gm * p.y_ld, n0, p.N, p.y_ld, y_vec);
+            } else {
+              float acc[16];
+              tmem_ld16(t_lane + (uint32_t)c0, acc);
+              tc_epi_chunk<16>(acc, s_bias + n0, s_alpha + n0, s_dot + n0, dot);
+              if (gm < p.M && p.Y) tc_store_chunk<16>(acc, p.Y + gm * p.y_ld, n0, p.N, p.y_ld, y_vec);
+            }
+          }
+        } else {
+          for (int c0 = 0; c0 < p.BN; c0 += 16) {
+            float acc[16];
+            tmem_ld16(t_lane + (uint32_t)c0, acc);
+            const int n0 = nt * p.BN + c0;
+            if (gm < p.M) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const int n = n0 + j;
+                float v = 0.f;
+                if (n < p.N) {
+                  v = p.ep.apply(acc[j] + s_bias[n], gm, n, p.N);
+                  dot = fmaf(v, s_dot[n], dot);
+                }
+                acc[j] = v;
+              }
+              if (p.Y) tc_store_chunk<16>(acc, p.Y + gm * p.y_ld, n0, p.N, p.y_ld, y_vec);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free(buf));
       }
+      if (p.dot_w && gm < p.M) p.y_dot[gm] = dot + (p.dot_b ? __ldg(p.dot_b) : 0.f);
     }
-    __syncwarp();
   }
+  tc_fence_before();
   __syncthreads();
-  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols); }
+  if (warp == 12) { tc_fence_after(); tmem_dealloc(tmem_base, 512u); }
 }
 
 int launch_dense_tc(const float* X, int64_t x_ld, int64_t M, const ctrhot_dense_desc& d, float* Y, int64_t y_ld,
@@ -211,13 +325,21 @@ int launch_dense_tc(const float* X, int64_t x_ld, int64_t M, const ctrhot_dense_
   p.X = X; p.x_ld = x_ld; p.M = M; p.K = d.in_dim; p.N = d.out_dim;
   p.Wp = static_cast<const float*>(d.packed); p.bias = d.bias; p.ep = Epilogue::from(d);
   p.Y = Y; p.y_ld = y_ld; p.dot_w = dot_w; p.dot_b = dot_b; p.y_dot = y_dot;
-  p.KC = g.KC; p.BN = g.BN; p.stages = g.stages; p.tmem_cols = g.tmem_cols;
-  const size_t smem = (size_t)g.stages * (TC_A_BYTES + g.BN * 128) + 1024 + 128;
+  p.KC = g.KC; p.BN = g.BN; p.n_tiles = g.n_tiles; p.tmem_cols = 512;
+  const size_t stage = (size_t)TC_A_BYTES + (size_t)g.BN * 128;
+  if (g.n_tiles * g.BN > TC_MAXN) return CTRHOT_ESHAPE;
+  const size_t tail = 1024 + 256 + 3 * TC_MAXN * sizeof(float);      // alignment slack, barriers, per-column vectors
+  int stages = (int)((227 * 1024 - tail) / stage);
+  if (stages > 6) stages = 6;
+  if (stages < 2) return CTRHOT_ESHAPE;
+  p.stages = stages;
+  const size_t smem = (size_t)stages * stage + tail;
   const bool vec = (x_ld % 4 == 0) && aligned16(X);
   auto kern = vec ? dense_tc_kernel<true> : dense_tc_kernel<false>;
   CTRHOT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "mlp_tc attr");
-  dim3 grid(g.n_tiles, (unsigned)((M + TC_BM - 1) / TC_BM));
-  kern<<<grid, 192, smem, st>>>(p);
+  const int64_t row_tiles = (M + TC_BM - 1) / TC_BM;
+  const int grid = (int)(row_tiles < kNumSMs ? row_tiles : kNumSMs);
+  kern<<<grid, TC_THREADS, smem, st>>>(p);
   CTRHOT_LAUNCH_OK("ctrhot_mlp_tf32");
   return CTRHOT_OK;
 }
@@ -274,8 +396,7 @@ extern "C" int ctrhot_mlp_tf32(const float* x, int64_t x_ld, int64_t M, const ct
     const bool last = (l == n_layers - 1);
     // fuse a trailing Dense(h -> 1, no activation) into this layer's epilogue
     const bool fuse_next = (l == n_layers - 2) && h_layers[l + 1].out_dim == 1 &&
-                           h_layers[l + 1].act == CTRHOT_ACT_NONE && d.out_dim >= 8 &&
-                           tc_geom(d.in_dim, d.out_dim).n_tiles == 1 && out_ld == 1;
+                           h_layers[l + 1].act == CTRHOT_ACT_NONE && d.out_dim >= 8 && out_ld == 1;
     float* y = last ? out : buf[l & 1];
     const int64_t y_ld = last ? out_ld : mx;
     int rc;

@@ -161,6 +161,31 @@ def test_tower_tf32_fused_vs_layered_vs_oracle(lib, M, hidden):
     assert np.max(np.abs(outs["fused"] - outs["layered"])) <= 1e-3
 
 
+@pytest.mark.parametrize("M", [1, 300, 4099, 128 * 148 * 2 + 77])
+@pytest.mark.parametrize("hidden,out_dim", [([400, 400, 400], 1), ([300], 1), ([264, 40], 5), ([24], 3)])
+def test_tower_tf32_wide_layers(lib, M, hidden, out_dim):
+    """The persistent per-layer tcgen05 kernel (mlp_tc.cu): layers wider than one 256-column tile (DCN cfg 3's 400-wide
+    tower), several column tiles per row tile, more row tiles than SMs, a trailing Dense(N -> 1) folded into the last
+    hidden layer, and a plain [M, out_dim] store whose row stride is not a multiple of 16 bytes."""
+    rng = np.random.default_rng(M % 1000 + len(hidden) + out_dim)
+    K = 221
+    x = S.f32(rng.uniform(-0.5, 1.0, (M, K)))
+    dims = [K] + hidden + [out_dim]
+    ws = []
+    for i in range(len(dims) - 1):
+        lim = np.sqrt(6.0 / (dims[i] + dims[i + 1]))
+        ws += [S.f32(rng.uniform(-lim, lim, (dims[i], dims[i + 1]))), S.f32(rng.normal(0, 0.1, (dims[i + 1],)))]
+    pairs = [(ws[2 * i], ws[2 * i + 1]) for i in range(len(dims) - 1)]
+    want = O.dnn_layer(x, pairs[:-1], pairs[-1], "relu")
+    L = DNNLayer(hidden, out_dim, "relu", precision="tf32")
+    L.build((None, K))
+    L.set_weights(ws)
+    L.stack.allow_fused = False
+    got = npy(L(x))
+    assert got.shape == want.shape
+    assert np.max(np.abs(got - want)) <= LOGIT, np.max(np.abs(got - want))
+
+
 def test_cross(golden, lib):
     a, want = S.load_case(golden, "cross")
     L = CrossLayer(3)
