@@ -164,6 +164,29 @@ def secondary(dev, rank):
     gbs = (26 * 4 + 2 * 26 * 4 * k) * B / ms / 1e6
     out["gather_k16"] = {"metric": "EmbedLayer gather GB/s (ids + rows read + rows written)", "value": gbs, "ms": ms,
                          "hbm_frac": gbs / pk["hbm_gbs"], "rows": "64 B, uniform ids over 33.8 M rows (2.16 GB)"}
+    del E, idb
+    # configs[2] (DCN, L=3 cross layers + 400-400-400 tower) and configs[1]'s Wide&Deep, same inputs as the main workload
+    from recommender_system_b200.model.criteo import DCN, WideDeep
+    fc = synth.criteo_feature_columns(synth.KAGGLE_VOCAB, k)
+    cins = [tuple(torch.from_numpy(a).to(dev) for a in synth.criteo_batch(B, synth.KAGGLE_VOCAB, seed=3 + i)) for i in range(4)]
+    for name, make, flops, algo in (
+            ("dcn_cfg3", lambda: DCN(fc, [400, 400, 400], 1, "relu", 3, embed_dim=k, precision="tf32", check_ids=False,
+                                     device=dev), 2 * (429 * 400 + 2 * 400 * 400 + 400) + 15 * 429 + 860, 1824),
+            ("widedeep_cfg2b", lambda: WideDeep(fc, [256, 128, 64], 1, "relu", embed_dim=k, precision="tf32",
+                                                check_ids=False, device=dev), 2 * (416 * 256 + 256 * 128 + 128 * 64 + 64), 1928)):
+        set_seed(1)
+        mm = make()
+        mm.build(None)
+
+        def run_model():
+            mm(cins[it[0] % 4]); it[0] += 1
+        l0 = _lib.LAUNCHES[0]
+        ms = timeit(run_model, 50, 10)
+        out[name] = {"metric": "forward samples/s", "value": B / ms * 1e3, "ms_per_step": ms, "batch": B,
+                     "launches_per_step": (_lib.LAUNCHES[0] - l0) / 60.0,
+                     "tensor_TFLOPs": flops * B / ms / 1e9, "tensor_frac": flops * B / ms / 1e9 / (pk["tf"] / 2),
+                     "hbm_frac": algo * B / ms / 1e6 / pk["hbm_gbs"]}
+        del mm
     return out
 
 

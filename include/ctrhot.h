@@ -144,6 +144,9 @@ int ctrhot_mlp_tf32(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_
                     int n_layers, float* out, int64_t out_ld, void* workspace,
                     int64_t workspace_bytes, void* stream);
 int64_t ctrhot_mlp_workspace_bytes(int64_t M, const ctrhot_dense_desc* h_layers, int n_layers);
+/* tuning hook: d_counters = device buffer of 148 * 4 uint64 that the following ctrhot_mlp_tf32 launches fill per CTA with
+ * {cycles the MMA thread waited for an operand stage, for a free accumulator, its total cycles, steps}; NULL = off */
+int ctrhot_debug_tc_trace(uint64_t* d_counters);
 
 /* Whole tower in ONE persistent tcgen05 kernel: hidden activations stay in TMEM (layer l's epilogue
  * writes layer l+1's A operand back with tcgen05.st), weights stream through the TMA engine.
@@ -220,6 +223,13 @@ int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off, int F, int
 int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M,
                            const ctrhot_dense_desc* h_layers, int n_layers, int apply_sigmoid, int cluster,
                            float* out, void* stream);
+/* One Dense layer (8 <= out_dim <= 416, act none/relu/PReLU[out_dim], packed by ctrhot_fused_pack(W, NULL, K, out_dim,
+ * K % 4, ..) from W with its last K % 4 rows moved to the front) over x [M, x_ld >= K] in HBM through the same persistent
+ * kernel (two MMA column halves when out_dim > 256): h[m, 0:out_dim] = tf32(act(x_m W + b)), h[m, out_dim:h_ld) = 0.
+ * Chains layers too wide for TMEM through HBM (DCN cfg 3's 400-wide tower, DL/model/dcn.py:45); the last hidden layer
+ * and the final Dense(h -> 1) then go through ctrhot_tower_rows_tf32 (one hidden layer may be up to 416 wide there). */
+int ctrhot_dense_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M, const ctrhot_dense_desc* layer,
+                           float* h, int64_t h_ld, int cluster, void* stream);
 
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,

@@ -69,7 +69,7 @@ int main() {
   cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const int iters = 2000;
   const char* names[4] = {"tf32 SS", "tf32 TS", "bf16 SS", "bf16 TS"};
-  for (int M : {128, 64}) for (int alt : {1, 2, 4}) for (int mode : {0, 1, 2, 3}) for (int N : {16, 32, 64, 128, 256}) {
+  for (int M : {128, 64}) for (int alt : {1, 2, 4}) for (int mode : {0, 1, 2, 3}) for (int N : {16, 32, 64, 128, 208, 256}) {
     if (alt * 64 > 256 && N > 64) continue;
     if (alt > 1 && N > 64) continue;
     if (M == 64 && alt > 1) continue;

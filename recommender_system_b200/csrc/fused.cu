@@ -46,12 +46,15 @@ constexpr int FU_MAXL = 3;
 constexpr int FU_THREADS = 18 * 32;
 constexpr int FU_SIDE = 16;                 // side columns
 constexpr int FU_NCB = 24;                  // combine constants
+constexpr int FU_MAXN1 = 416;               // widest single layer (two MMA column halves, 416 TMEM columns + a 96-column A ring)
 
 enum { FU_MODE_TOWER = 0, FU_MODE_DEEPFM = 1, FU_MODE_DCN = 2 };
 
 struct FuLayer {
   const float* Wp; const float* bias; const float* alpha;   // alpha: PReLU [N] or NULL
   int N, KC, BN, KP, col, act;                              // KP = N rounded up to 32 (= K extent of the next layer)
+  int BNa;                                                  // columns of the first MMA per K step (= BN unless BN > 256:
+                                                            // a wide single layer is issued as two column halves)
 };
 
 constexpr int FU_MAXG = 16;
@@ -69,7 +72,11 @@ struct FuParams {
   int mode; int n_side; float cb[FU_NCB];
   int apply_sigmoid;
   int ds_col;                                              // TMEM column of the side accumulator
-  int a_col, n_as;                                         // TMEM A ring: first column, slots (64 columns each)
+  int a_col, n_as, a_w;                                    // TMEM A ring: first column, slots, columns per slot (x | x_lo = 64
+                                                           // with side products, x = 32 without)
+  int nr;                                                  // raw-row ring stages in use (<= FU_NR)
+  int side_rows;                                           // rows of [s_hi | s_lo] behind W1 in every first-layer chunk (32 or 0)
+  float* h_out; int64_t h_ld;                              // single hidden layer: act(x W + b), TF32-rounded, to HBM (no final dot)
   int nb;                                                  // W ring stages in use (<= FU_NB)
   const float* add_vec; float out_scale;                   // tower mode: out = out_scale * (y + add_vec[m])   (WideDeep)
   float* out; int* err_flag;
@@ -205,6 +212,10 @@ __device__ __forceinline__ float fu_last_chunk(uint32_t taddr, const float* sb, 
 #ifdef FU_TRACE
 // tuning builds only (profiles/build_variants.py TRACE=1): cycles the MMA thread of every CTA spent waiting, per cause
 __device__ unsigned long long fu_trace[256][8];
+__device__ unsigned long long fu_times[256][4];     // globaltimer ns: CTA entry, MMA loop begin, MMA loop end, CTA exit
+__device__ __forceinline__ unsigned long long fu_now() {
+  unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t;
+}
 #define FU_TWAIT(slot, stmt) do { const long long t0_ = clock64(); stmt; tw[slot] += clock64() - t0_; } while (0)
 #else
 #define FU_TWAIT(slot, stmt) do { stmt; } while (0)
@@ -214,11 +225,14 @@ template <int NL, int C>
 __global__ void __launch_bounds__(FU_THREADS, 1)
 ctr_fused_kernel(const __grid_constant__ FuParams p) {
   extern __shared__ uint8_t smem_raw[];
+#ifdef FU_TRACE
+  if (threadIdx.x == 0 && blockIdx.x < 256) fu_times[blockIdx.x][0] = fu_now();
+#endif
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t base = (raw_addr + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - raw_addr);
   const uint32_t r_base = base;                                         // FU_NR raw chunks
-  const uint32_t b_base = r_base + FU_NR * FU_TILE_BYTES;               // p.nb weight stages
+  const uint32_t b_base = r_base + (uint32_t)p.nr * FU_TILE_BYTES;      // p.nb weight stages
   const uint32_t f_base = b_base + (uint32_t)p.nb * p.b_stage_bytes;    // float region
   int KP[FU_MAXL];
 #pragma unroll
@@ -278,7 +292,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       }
     }
     const FuLayer& LL = p.L[NL - 1];
-    for (int i = tid; i < LL.KP; i += FU_THREADS) fptr[mp.wout + i] = (i < LL.N) ? __ldg(p.w_out + i) : 0.f;
+    for (int i = tid; i < LL.KP; i += FU_THREADS) fptr[mp.wout + i] = (i < LL.N && p.w_out) ? __ldg(p.w_out + i) : 0.f;
   }
   if (warp == 16) { tmem_alloc(slot_addr, 512u); tmem_relinquish(); }
   tc_fence_before();
@@ -331,9 +345,11 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       }
       advance(cf);
     };
+    int rs = 0; uint32_t rph = 0;                        // raw stage of the next issue and its phase
     auto issue = [&](int g, const int32_t (&reg)[8]) {
-      const int s = g % FU_NR;
-      mbar_wait(empty_raw(s), (((uint32_t)g / FU_NR) & 1u) ^ 1u);
+      const int s = rs;
+      mbar_wait(empty_raw(s), rph ^ 1u);
+      if (++rs == p.nr) { rs = 0; rph ^= 1u; }
       const uint32_t dst = dst0 + (uint32_t)s * FU_TILE_BYTES;
       if (ci.f < p.F) {
         const char* fb = reinterpret_cast<const char*>(s_fb[ci.f]) + ci.part * 16;
@@ -403,12 +419,13 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     const uint32_t src0 = r_base + (uint32_t)row * 128u;
     const uint32_t rx = (uint32_t)(row & 7);
     const int n_as = p.n_as;
-    uint32_t it = 0, sa = 0, pa = 0;                    // A slot and its phase
+    uint32_t sa = 0, pa = 0;                            // A slot and its phase
+    int sr = 0; uint32_t pr = 0;                        // raw stage and its phase
+    const bool with_lo = (p.a_w == 64);
     for (int lt = 0; lt < n_my; ++lt) {
       float q = 0.f;
-      for (int kc = 0; kc < KC1; ++kc, ++it) {
-        const int sr = it % FU_NR;
-        mbar_wait(full_raw(sr), (it / FU_NR) & 1u);
+      for (int kc = 0; kc < KC1; ++kc) {
+        mbar_wait(full_raw(sr), pr);
         const uint32_t raw = src0 + sr * FU_TILE_BYTES;
         const float* sq = fptr + mp.sq + kc * 32;
         float x[32], lo[32];
@@ -426,12 +443,13 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) lo[j] = x[j] - trunc_tf32(x[j]);
         mbar_arrive(empty_raw(sr));                     // the chunk is in registers: the gather may refill the stage
+        if (++sr == p.nr) { sr = 0; pr ^= 1u; }
         // the A ring shares its TMEM columns with the later layers' accumulators: wait until the previous tile is done with them
-        if (kc == 0 && lt > 0) mbar_wait(last_free, (uint32_t)(lt - 1) & 1u);
+        if (NL > 1 && kc == 0 && lt > 0) mbar_wait(last_free, (uint32_t)(lt - 1) & 1u);
         mbar_wait(a_free(sa), pa ^ 1u);
         tc_fence_after();
-        tmem_st32(t_lane + sa * 64u, x);
-        tmem_st32(t_lane + sa * 64u + 32u, lo);
+        tmem_st32(t_lane + sa * (uint32_t)p.a_w, x);
+        if (with_lo) tmem_st32(t_lane + sa * 64u + 32u, lo);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(a_full(sa));
@@ -445,6 +463,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #ifdef FU_TRACE
       long long tw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       const long long t_begin = clock64();
+      if (blockIdx.x < 256) fu_times[blockIdx.x][1] = fu_now();
 #endif
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0;     // A slot / W stage and their phases
       uint32_t hcount[FU_MAXL] = {0, 0, 0};
@@ -453,7 +472,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       for (int lt = 0; lt < n_my; ++lt) {
         {
           const FuLayer& L = p.L[0];
-          const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BN);
+          const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BNa);
+          const uint32_t idesc_b = make_idesc_tf32(FU_BM, (uint32_t)(L.BN - L.BNa));      // second column half (wide layer)
+          const bool two = L.BN > L.BNa;
           const uint32_t idesc32 = make_idesc_tf32(FU_BM, 32u), idesc16 = make_idesc_tf32(FU_BM, 16u);
           const uint32_t d_t = tmem_base + (uint32_t)L.col;
           const bool side_on = (p.mode != FU_MODE_TOWER);      // a plain tower has no side products: skip their MMAs
@@ -462,12 +483,15 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             FU_TWAIT(0, mbar_wait(full_b(sb), pb));
             FU_TWAIT(1, mbar_wait(a_full(sa), pa));
             tc_fence_after();
-            const uint32_t a_hi = a_t0 + sa * 64u, a_lo = a_hi + 32u;
+            const uint32_t a_hi = a_t0 + sa * (uint32_t)p.a_w, a_lo = a_hi + 32u;
             const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
+            const uint64_t db2 = make_desc_sw128(b_base + sb * p.b_stage_bytes + (uint32_t)L.BNa * 128u);
             const uint64_t ds = make_desc_sw128(b_base + sb * p.b_stage_bytes + (uint32_t)L.BN * 128u);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               mma_tf32_ts(d_t, a_hi + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
+              if (two) mma_tf32_ts(d_t + (uint32_t)L.BNa, a_hi + (uint32_t)(8 * k), db2 + (uint64_t)(2 * k), idesc_b,
+                                   (uint32_t)((kc | k) != 0));
               // (folding the side columns into the main MMA as two N = 144 halves was measured SLOWER, 88.9 -> 92.5 us:
               //  an MMA wider than 128 columns costs the full 138 cycles; kept in git history only)
               if (side_on) mma_tf32_ts(ds_t, a_hi + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
@@ -509,6 +533,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #ifdef FU_TRACE
       tw[7] = clock64() - t_begin;
       tw[6] = n_my;
+      if (blockIdx.x < 256) fu_times[blockIdx.x][2] = fu_now();
       if (blockIdx.x < 256) for (int i = 0; i < 8; ++i) fu_trace[blockIdx.x][i] = (unsigned long long)tw[i];
 #endif
     }
@@ -521,12 +546,13 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
         for (int l = 0; l < NL; ++l) {
           const FuLayer& L = p.L[l];
-          const uint32_t bytes = (uint32_t)(L.BN + (l == 0 ? 2 * FU_SIDE : 0)) * 128u;
+          const uint32_t bytes = (uint32_t)(L.BN + (l == 0 ? p.side_rows : 0)) * 128u;
+          const size_t stride = (size_t)(L.BN + (l == 0 ? 2 * FU_SIDE : 0)) * 128u;      // the pack always carries the side rows
           const uint32_t piece = bytes / C;
           for (int kc = 0; kc < L.KC; ++kc) {
             mbar_wait(empty_b(sb), pb ^ 1u);
             mbar_arrive_expect_tx(full_b(sb), bytes);
-            const uint8_t* src = reinterpret_cast<const uint8_t*>(L.Wp) + (size_t)kc * bytes + (size_t)crank * piece;
+            const uint8_t* src = reinterpret_cast<const uint8_t*>(L.Wp) + (size_t)kc * stride + (size_t)crank * piece;
             const uint32_t dst = b_base + sb * p.b_stage_bytes + crank * piece;
             if (C > 1) bulk_g2s_mc(dst, src, piece, full_b(sb), cmask);
             else bulk_g2s(dst, src, bytes, full_b(sb));
@@ -581,6 +607,26 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           tmem_st_wait();
           tc_fence_before();
           mbar_arrive(h_ready(l));
+        } else if (p.h_out) {
+          // single wide layer: the activations go to HBM (TF32-rounded, so the next layer's MMA reads them exactly)
+          for (int c0 = half * 32; c0 < L.KP; c0 += 64) {
+            float acc[32];
+            tmem_ld32(t_lane + (uint32_t)(L.col + c0), acc);
+            if (gm < p.M) {
+              float* dst = p.h_out + gm * p.h_ld + c0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
+                const float4 a = *reinterpret_cast<const float4*>(sa + c0 + j);
+                float4 o;
+                o.x = to_tf32_rna(fu_act(acc[j + 0] + b.x, a.x)); o.y = to_tf32_rna(fu_act(acc[j + 1] + b.y, a.y));
+                o.z = to_tf32_rna(fu_act(acc[j + 2] + b.z, a.z)); o.w = to_tf32_rna(fu_act(acc[j + 3] + b.w, a.w));
+                if (c0 + j < p.h_ld) stg_na_f4(dst + j, o);       // columns in [N, h_ld) are written as zeros
+              }
+            }
+          }
+          tc_fence_before();
+          mbar_arrive(last_free);
         } else {
           float dot = 0.f;
           for (int c0 = half * 32; c0 < L.KP; c0 += 64)
@@ -606,6 +652,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   __syncthreads();
   if (C > 1) cluster_sync_all();
   if (warp == 16) { tc_fence_after(); tmem_dealloc(tmem_base, 512u); }
+#ifdef FU_TRACE
+  if (threadIdx.x == 0 && blockIdx.x < 256) fu_times[blockIdx.x][3] = fu_now();
+#endif
 }
 
 // ---------------------------------------------------------------- first-layer pack: [KC1][(BN1 + 32) rows][32 cols]
@@ -647,13 +696,13 @@ using namespace ctrhot;
 static inline int fu_round(int v, int m) { return (v + m - 1) / m * m; }
 
 extern "C" int64_t ctrhot_fused_pack_bytes(int n, int n1) {
-  if (n <= 0 || n1 <= 0 || n1 > 256) return CTRHOT_EARG;
+  if (n <= 0 || n1 <= 0 || n1 > FU_MAXN1) return CTRHOT_EARG;
   const int KC1 = (n + 31) / 32, BN1 = fu_round(n1, 16);
   return (int64_t)KC1 * (BN1 + 2 * FU_SIDE) * 32 * sizeof(float);
 }
 
 extern "C" int ctrhot_fused_pack(const float* W1, const float* side, int n, int n1, int D, void* packed, void* stream) {
-  if (!W1 || !packed || n <= 0 || n1 <= 0 || n1 > 256 || D < 0 || D > n || !aligned16(packed)) return CTRHOT_EARG;
+  if (!W1 || !packed || n <= 0 || n1 <= 0 || n1 > FU_MAXN1 || D < 0 || D > n || !aligned16(packed)) return CTRHOT_EARG;
   const int KC1 = (n + 31) / 32, BN1 = fu_round(n1, 16);
   const int64_t total = (int64_t)KC1 * (BN1 + 2 * FU_SIDE) * 32;
   int64_t grid = (total + 255) / 256;
@@ -667,6 +716,9 @@ extern "C" int ctrhot_fused_pack(const float* W1, const float* side, int n, int 
 #ifdef FU_TRACE
 extern "C" int ctrhot_debug_fused_trace(unsigned long long* h_out) {
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
+}
+extern "C" int ctrhot_debug_fused_times(unsigned long long* h_out) {
+  return cudaMemcpyFromSymbol(h_out, ctrhot::fu_times, sizeof(unsigned long long) * 256 * 4) == cudaSuccess ? 0 : -3;
 }
 #endif
 
@@ -750,13 +802,13 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
              const ctrhot_dense_desc* h_layers, int n_layers,
              const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
              int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream,
-             const float* add_vec = nullptr, float out_scale = 1.f) {
+             const float* add_vec = nullptr, float out_scale = 1.f, float* h_out = nullptr, int64_t h_ld = 0) {
   if (!peers || G < 1 || G > FU_MAXG || rank < 0 || rank >= G) return CTRHOT_EARG;
   for (int g = 0; g < G; ++g) if (!peers[g] || !aligned16(peers[g])) return CTRHOT_EARG;
   if ((int64_t)F * G > 4096) return CTRHOT_ESHAPE;
   const float* arena = peers[rank];
   const bool rows_mode = (row_off == nullptr && ids == nullptr);       // ctrhot_tower_rows_tf32: the table is x itself
-  if (!arena || !out || !h_layers || F <= 0 || k <= 0 || M < 0 || D < 0) return CTRHOT_EARG;
+  if (!arena || (!out && !h_out) || !h_layers || F <= 0 || k <= 0 || M < 0 || D < 0) return CTRHOT_EARG;
   if (!rows_mode && (!row_off || !ids)) return CTRHOT_EARG;
   if (rows_mode && (F != 1 || G != 1 || M > 0x7FFFFFFF || row_stride < k || row_stride % 4 != 0)) return CTRHOT_EARG;
   if (D > 0 && !dense) return CTRHOT_EARG;
@@ -767,11 +819,13 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   if (mode == FU_MODE_DCN && n_combine < n_side + 3) return CTRHOT_EARG;
   if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4) return CTRHOT_EARG;
   if (k % 4 != 0 || !aligned16(arena) || F > 63) return CTRHOT_ESHAPE;
-  if (n_layers < 2 || n_layers > FU_MAXL + 1) return CTRHOT_ESHAPE;
+  // h_out: ONE hidden layer whose activations go to HBM (no final Dense); otherwise hidden layers + the final Dense(h -> 1)
+  if (h_out ? (n_layers != 1 || mode != FU_MODE_TOWER) : (n_layers < 2 || n_layers > FU_MAXL + 1)) return CTRHOT_ESHAPE;
   const ctrhot_dense_desc& o = h_layers[n_layers - 1];
-  if (o.out_dim != 1 || o.act != CTRHOT_ACT_NONE || !o.weight) return CTRHOT_ESHAPE;
+  if (!h_out && (o.out_dim != 1 || o.act != CTRHOT_ACT_NONE || !o.weight)) return CTRHOT_ESHAPE;
   FuParams p{};
-  const int nl = n_layers - 1;
+  const int nl = h_out ? 1 : n_layers - 1;
+  const bool side_on = (mode != FU_MODE_TOWER);
   const int n = D + F * k;
   int KP[FU_MAXL] = {0, 0, 0};
   int col = 0;
@@ -779,7 +833,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   for (int l = 0; l < nl; ++l) {
     const ctrhot_dense_desc& d = h_layers[l];
     if (!d.weight || !d.packed || !aligned16(d.packed) || d.in_dim <= 0 || d.out_dim <= 0) return CTRHOT_EARG;
-    if (d.out_dim > 256 || d.out_dim < 8) return CTRHOT_ESHAPE;
+    if (d.out_dim > (nl == 1 ? FU_MAXN1 : 256) || d.out_dim < 8) return CTRHOT_ESHAPE;
     if (l == 0 ? d.in_dim != n : d.in_dim != h_layers[l - 1].out_dim) return CTRHOT_EARG;
     if (d.act == CTRHOT_ACT_PRELU) {
       if (!d.act_param) return CTRHOT_EARG;
@@ -790,17 +844,24 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
     FuLayer& L = p.L[l];
     L.Wp = static_cast<const float*>(d.packed); L.bias = d.bias; L.alpha = d.act_param; L.act = d.act;
     L.N = d.out_dim; L.KC = (d.in_dim + 31) / 32; L.BN = fu_round(d.out_dim, 16); L.KP = fu_round(d.out_dim, 32);
+    L.BNa = L.BN <= 256 ? L.BN : fu_round(L.BN / 2, 16);
     L.col = col;
     col += L.KP;
-    if (l == 0) { p.ds_col = col; col += 2 * FU_SIDE; p.a_col = col; }
+    if (l == 0) {
+      if (side_on) { p.ds_col = col; col += 2 * FU_SIDE; }
+      p.a_col = col;
+    }
     KP[l] = L.KP;
-    const uint32_t b = (uint32_t)(L.BN + (l == 0 ? 2 * FU_SIDE : 0)) * 128u;
+    const uint32_t b = (uint32_t)(L.BN + (l == 0 && side_on ? 2 * FU_SIDE : 0)) * 128u;
     if (b > bmax) bmax = b;
   }
   if (col > 512) return CTRHOT_ESHAPE;
-  p.n_as = (512 - p.a_col) / 64 < FU_NAS ? (512 - p.a_col) / 64 : FU_NAS;
+  p.a_w = side_on ? 64 : 32;
+  p.side_rows = side_on ? 2 * FU_SIDE : 0;
+  p.n_as = (512 - p.a_col) / p.a_w < FU_NAS ? (512 - p.a_col) / p.a_w : FU_NAS;
   if (p.n_as < 2) return CTRHOT_ESHAPE;
-  if (o.in_dim != h_layers[nl - 1].out_dim) return CTRHOT_EARG;
+  if (!h_out && o.in_dim != h_layers[nl - 1].out_dim) return CTRHOT_EARG;
+  if (h_out && (h_ld < h_layers[0].out_dim || h_ld % 4 != 0 || !aligned16(h_out))) return CTRHOT_EARG;
   if (M == 0) return CTRHOT_OK;
   p.G = G;
   for (int g = 0; g < FU_MAXG; ++g) p.peer[g] = g < G ? peers[g] : nullptr;
@@ -808,7 +869,8 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   p.arena = arena; p.row_off = row_off; p.F = F; p.k4 = k / 4; p.ids = ids; p.ids_kind = ids_kind; p.ids_ld = ids_ld;
   p.dense = dense; p.dense_ld = dense_ld; p.D = D; p.emb = F * k;
   p.M = M; p.n_tiles = (int)((M + FU_BM - 1) / FU_BM);
-  p.w_out = o.weight; p.b_out = o.bias; p.sq_w = sq_w;
+  p.w_out = h_out ? nullptr : o.weight; p.b_out = h_out ? nullptr : o.bias; p.sq_w = sq_w;
+  p.h_out = h_out; p.h_ld = h_ld;
   p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid;
   for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
@@ -816,11 +878,18 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl);
   const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1;
   size_t smem = 0;
-  for (p.nb = FU_NB; p.nb >= 2; --p.nb) {
-    smem = 1024 + (size_t)FU_NR * FU_TILE_BYTES + (size_t)p.nb * bmax + (size_t)mp.total * 4 + 8 * n_bars + 16;
-    if (smem <= 227 * 1024) break;
+  bool fits = false;
+  // deepest rings that fit: weight stages first (each is a round trip to L2), then raw-row stages
+  for (p.nb = FU_NB; p.nb >= 2 && !fits; --p.nb) {
+    for (p.nr = FU_NR; p.nr >= (p.nb >= 3 ? 3 : 2) && !fits; --p.nr) {
+      smem = 1024 + (size_t)FU_NR * FU_TILE_BYTES + (size_t)p.nb * bmax + (size_t)mp.total * 4 + 8 * n_bars + 16
+             - (size_t)(FU_NR - p.nr) * FU_TILE_BYTES;
+      fits = smem <= 227 * 1024;
+      if (fits) break;
+    }
+    if (fits) break;
   }
-  if (p.nb < 2) return CTRHOT_ESHAPE;
+  if (!fits) return CTRHOT_ESHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int C = cluster;
   if (C == 0) {
@@ -877,6 +946,17 @@ extern "C" int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64
   const int r = K % 4, k = K - r;
   return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, h_layers,
                   n_layers, nullptr, FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, nullptr, stream);
+}
+
+// One Dense layer of up to 416 units over a matrix in HBM, activations written back to HBM: the building block of towers
+// too wide to be chained through TMEM (DCN cfg 3: 429 -> 400 -> 400 -> 400 -> 1 runs as store, store, then
+// ctrhot_tower_rows_tf32 with the last hidden layer + the final Dense).  h[m, 0:N] = tf32(act(x_m W + b)), h[m, N:h_ld) = 0.
+extern "C" int ctrhot_dense_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M, const ctrhot_dense_desc* layer,
+                                      float* h, int64_t h_ld, int cluster, void* stream) {
+  if (!x || !layer || !h || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
+  const int r = K % 4, k = K - r;
+  return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, layer, 1,
+                  nullptr, FU_MODE_TOWER, 0, nullptr, 0, 0, cluster, nullptr, nullptr, stream, nullptr, 1.f, h, h_ld);
 }
 
 // WideDeep.call (DL/model/wideDeep.py:24-34): out = sigmoid(scale * (add_vec[m] + DNN(Embed(ids))[m])) with the deep tower

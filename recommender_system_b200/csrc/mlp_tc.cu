@@ -24,6 +24,7 @@ struct TcParams {
   float* Y; int64_t y_ld;
   const float* dot_w; const float* dot_b; float* y_dot;   // fused Dense(N -> 1) (N fits one tile)
   int KC, BN, stages, tmem_cols, n_tiles;
+  unsigned long long* trace;     // tuning only: [grid][4] cycles the MMA thread waited for {x/W stage, free accumulator}, total, steps
 };
 
 TcGeom tc_geom(int K, int N) {
@@ -198,7 +199,9 @@ dense_tc_kernel(const TcParams p) {
         q.x = to_tf32_rna(q.x); q.y = to_tf32_rna(q.y); q.z = to_tf32_rna(q.z); q.w = to_tf32_rna(q.w);
         *reinterpret_cast<float4*>(a_tile + sw128_offset((uint32_t)(r0 + 32 * i), (uint32_t)c)) = q;
       }
-      fence_proxy_async_smem();
+      // No proxy fence here: a thread with loads in flight would sit in it until they land (the fence drains the
+      // thread's outstanding memory operations), serialising the prefetch.  The MMA thread fences after its wait on
+      // full_bar instead -- the fence only has to lie on the causality path between these stores and the MMA's reads.
       __syncwarp();
       if (lane == 0) mbar_arrive(full_bar(s));
     };
@@ -218,15 +221,28 @@ dense_tc_kernel(const TcParams p) {
       const uint32_t idesc = make_idesc_tf32(TC_BM, (uint32_t)p.BN);
       int g = 0;
       uint32_t step = 0;
+      long long tw_full = 0, tw_acc = 0;
+      const long long t_begin = p.trace ? clock64() : 0;
       for (int lt = 0; lt < n_my; ++lt) {
         for (int nt = 0; nt < NT; ++nt, ++step) {
           const uint32_t buf = step & 1u;
+          if (p.trace) {
+            const long long t0 = clock64();
+            mbar_wait(acc_free(buf), ((step >> 1) & 1u) ^ 1u);
+            tw_acc += clock64() - t0;
+          }
           mbar_wait(acc_free(buf), ((step >> 1) & 1u) ^ 1u);          // the epilogue has drained this buffer
           tc_fence_after();
           const uint32_t d_t = tmem_base + buf * TC_ACC_COLS;
           for (int kc = 0; kc < KC; ++kc, ++g) {
             const int s = g % p.stages;
+            if (p.trace) {
+              const long long t0 = clock64();
+              mbar_wait(full_bar(s), ((uint32_t)(g / p.stages)) & 1u);
+              tw_full += clock64() - t0;
+            }
             mbar_wait(full_bar(s), ((uint32_t)(g / p.stages)) & 1u);
+            fence_proxy_async_smem();             // generic-proxy stores of the A producers -> async-proxy reads of the MMA
             tc_fence_after();
             const uint32_t a_addr = base + s * stage_bytes;
             const uint64_t da = make_desc_sw128(a_addr);
@@ -238,6 +254,11 @@ dense_tc_kernel(const TcParams p) {
           }
           mma_commit(acc_full(buf));
         }
+      }
+      if (p.trace) {
+        unsigned long long* t = p.trace + 4 * blockIdx.x;
+        t[0] = (unsigned long long)tw_full; t[1] = (unsigned long long)tw_acc;
+        t[2] = (unsigned long long)(clock64() - t_begin); t[3] = step;
       }
     }
     __syncwarp();
@@ -318,6 +339,8 @@ dense_tc_kernel(const TcParams p) {
   if (warp == 12) { tc_fence_after(); tmem_dealloc(tmem_base, 512u); }
 }
 
+static unsigned long long* g_tc_trace = nullptr;   // tuning only (ctrhot_debug_tc_trace)
+
 int launch_dense_tc(const float* X, int64_t x_ld, int64_t M, const ctrhot_dense_desc& d, float* Y, int64_t y_ld,
                     const float* dot_w, const float* dot_b, float* y_dot, cudaStream_t st) {
   const TcGeom g = tc_geom(d.in_dim, d.out_dim);
@@ -325,7 +348,7 @@ int launch_dense_tc(const float* X, int64_t x_ld, int64_t M, const ctrhot_dense_
   p.X = X; p.x_ld = x_ld; p.M = M; p.K = d.in_dim; p.N = d.out_dim;
   p.Wp = static_cast<const float*>(d.packed); p.bias = d.bias; p.ep = Epilogue::from(d);
   p.Y = Y; p.y_ld = y_ld; p.dot_w = dot_w; p.dot_b = dot_b; p.y_dot = y_dot;
-  p.KC = g.KC; p.BN = g.BN; p.n_tiles = g.n_tiles; p.tmem_cols = 512;
+  p.KC = g.KC; p.BN = g.BN; p.n_tiles = g.n_tiles; p.tmem_cols = 512; p.trace = g_tc_trace;
   const size_t stage = (size_t)TC_A_BYTES + (size_t)g.BN * 128;
   if (g.n_tiles * g.BN > TC_MAXN) return CTRHOT_ESHAPE;
   const size_t tail = 1024 + 256 + 3 * TC_MAXN * sizeof(float);      // alignment slack, barriers, per-column vectors
@@ -347,6 +370,12 @@ int launch_dense_tc(const float* X, int64_t x_ld, int64_t M, const ctrhot_dense_
 }  // namespace ctrhot
 
 using namespace ctrhot;
+
+// tuning only: device buffer of kNumSMs * 4 counters filled by the next per-layer launches (NULL switches it off)
+extern "C" int ctrhot_debug_tc_trace(uint64_t* d_buf) {
+  ctrhot::g_tc_trace = reinterpret_cast<unsigned long long*>(d_buf);
+  return CTRHOT_OK;
+}
 
 extern "C" int64_t ctrhot_mlp_pack_bytes(int in_dim, int out_dim) {
   if (in_dim <= 0 || out_dim <= 0) return CTRHOT_EARG;

@@ -187,6 +187,61 @@ class DenseStack:
                   stream_ptr())
         return out
 
+    def _rows_pack(self, l, K, n1):
+        """Layer ``l`` packed for the persistent kernel in rows mode (last K % 4 rows of W first)."""
+        r = K % 4
+        key = ("rows", l, r)
+        if key not in self._packed:
+            W = self.layers[l]["kernel"]
+            Wr = torch.cat([W[K - r:], W[:K - r]], dim=0).contiguous() if r else W.contiguous()
+            nbytes = _lib.query("ctrhot_fused_pack_bytes", K, n1)
+            buf = torch.empty(nbytes // 4, dtype=torch.float32, device=W.device)
+            _lib.call("ctrhot_fused_pack", ptr(Wr), None, K, n1, r, ptr(buf), stream_ptr())
+            self._packed[key] = buf
+        return self._packed[key]
+
+    def wide_rows_ok(self, arr=None):
+        """Tower too wide to chain through TMEM but every hidden layer fits one persistent launch (<= 416 units):
+        ctrhot_dense_rows_tf32 per hidden layer, the last one + the final Dense(h -> 1) by ctrhot_tower_rows_tf32."""
+        arr = arr if arr is not None else self.descs()
+        n = len(arr)
+        if self.precision != "tf32" or n < 2 or not self.allow_fused:
+            return False
+        if arr[n - 1].out_dim != 1 or arr[n - 1].act != _lib.ACT_NONE:
+            return False
+        for i in range(n - 1):
+            d = arr[i]
+            if not (8 <= d.out_dim <= 416) or d.in_dim < 4:
+                return False
+            if d.act == _lib.ACT_PRELU:
+                if d.alpha_rows > 1:
+                    return False
+            elif d.act not in (_lib.ACT_NONE, _lib.ACT_RELU):
+                return False
+        return True
+
+    def run_rows_wide(self, x, x_ld, sigmoid, out):
+        arr = self.descs()
+        n = len(arr)
+        M = x.shape[0]
+        mx = max((arr[i].out_dim + 31) // 32 * 32 for i in range(n - 1))
+        if n > 2 and (self._ws is None or self._ws.numel() < 2 * M * mx or self._ws.device != x.device):
+            self._ws = torch.empty(2 * M * mx, dtype=torch.float32, device=x.device)
+        cur, cur_ld = x, x_ld
+        for l in range(n - 1):
+            K, n1 = arr[l].in_dim, arr[l].out_dim
+            arr[l].packed = ptr(self._rows_pack(l, K, n1))
+            if l < n - 2:
+                h_ld = (n1 + 31) // 32 * 32
+                h = self._ws[(l & 1) * M * mx:(l & 1) * M * mx + M * h_ld].view(M, h_ld)
+                _lib.call("ctrhot_dense_rows_tf32", ptr(cur), cur_ld, K, M, ctypes.pointer(arr[l]), ptr(h), h_ld, 0,
+                          stream_ptr())
+                cur, cur_ld = h, h_ld
+            else:
+                _lib.call("ctrhot_tower_rows_tf32", ptr(cur), cur_ld, K, M, ctypes.pointer(arr[l]), 2, int(bool(sigmoid)), 0,
+                          ptr(out), stream_ptr())
+        return out
+
     def run_ctr_tower(self, E, ids, kind, ids_ld, dense, B, first_kernel_ref, add_vec=None, scale=1.0, sigmoid=False,
                       err_flag=None, out=None, cluster=0):
         """Tower fed from EmbedLayer ``E`` by the whole-model kernel; out = (sigmoid of) scale * (add_vec + y)."""
@@ -284,6 +339,8 @@ class DenseStack:
             return self.run_rows(x, x_ld, final_sigmoid, out)
         if self.fused_ok(arr) and aligned:
             return self.run_fused(x, x_ld, {"sigmoid": True} if final_sigmoid else None, out)
+        if aligned and K >= 4 and self.wide_rows_ok(arr):
+            return self.run_rows_wide(x, x_ld, final_sigmoid, out)
         need = _lib.query("ctrhot_mlp_workspace_bytes", M, arr, n)
         if self._ws is None or self._ws.numel() * 4 < need or self._ws.device != x.device:
             self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=x.device)

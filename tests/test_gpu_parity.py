@@ -162,9 +162,11 @@ def test_tower_tf32_fused_vs_layered_vs_oracle(lib, M, hidden):
 
 
 @pytest.mark.parametrize("M", [1, 300, 4099, 128 * 148 * 2 + 77])
-@pytest.mark.parametrize("hidden,out_dim", [([400, 400, 400], 1), ([300], 1), ([264, 40], 5), ([24], 3)])
-def test_tower_tf32_wide_layers(lib, M, hidden, out_dim):
-    """The persistent per-layer tcgen05 kernel (mlp_tc.cu): layers wider than one 256-column tile (DCN cfg 3's 400-wide
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("hidden,out_dim", [([400, 400, 400], 1), ([300], 1), ([264, 40], 5), ([24], 3), ([416, 72], 1)])
+def test_tower_tf32_wide_layers(lib, M, hidden, out_dim, fused):
+    """fused=True: hidden layers of up to 416 units one persistent launch each through HBM (ctrhot_dense_rows_tf32 +
+    ctrhot_tower_rows_tf32, fused.cu).  fused=False: the persistent per-layer tcgen05 kernel (mlp_tc.cu): layers wider than one 256-column tile (DCN cfg 3's 400-wide
     tower), several column tiles per row tile, more row tiles than SMs, a trailing Dense(N -> 1) folded into the last
     hidden layer, and a plain [M, out_dim] store whose row stride is not a multiple of 16 bytes."""
     rng = np.random.default_rng(M % 1000 + len(hidden) + out_dim)
@@ -180,7 +182,7 @@ def test_tower_tf32_wide_layers(lib, M, hidden, out_dim):
     L = DNNLayer(hidden, out_dim, "relu", precision="tf32")
     L.build((None, K))
     L.set_weights(ws)
-    L.stack.allow_fused = False
+    L.stack.allow_fused = fused
     got = npy(L(x))
     assert got.shape == want.shape
     assert np.max(np.abs(got - want)) <= LOGIT, np.max(np.abs(got - want))
