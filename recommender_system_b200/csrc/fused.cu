@@ -159,35 +159,60 @@ __host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries
 
 __device__ __forceinline__ float fu_act(float t, float a) { return fmaxf(t, 0.f) + a * fminf(t, 0.f); }
 
+// round-to-nearest (ties away) TF32 of a finite value by integer arithmetic on its bit pattern: two full-rate ALU ops
+// instead of the NaN-preserving sequence cvt.rna.tf32.f32 compiles to (the epilogues below are issue-bound)
+__device__ __forceinline__ float tf32_rna_fast(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
+}
+
 // one 32-column chunk of a hidden layer's epilogue: acc -> act(acc + b) -> tf32 -> back to TMEM in place
-__device__ __forceinline__ void fu_hidden_chunk(uint32_t taddr, const float* sb, const float* sa, int c0, int N) {
+__device__ __forceinline__ void fu_hidden_chunk(uint32_t taddr, const float* sb, const float* sa, int c0, int N, bool relu) {
   float acc[32];
   tmem_ld32(taddr, acc);
-  if (c0 + 32 <= N) {
+  if (relu && c0 + 32 <= N) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
+      acc[j + 0] = tf32_rna_fast(fmaxf(acc[j + 0] + b.x, 0.f));
+      acc[j + 1] = tf32_rna_fast(fmaxf(acc[j + 1] + b.y, 0.f));
+      acc[j + 2] = tf32_rna_fast(fmaxf(acc[j + 2] + b.z, 0.f));
+      acc[j + 3] = tf32_rna_fast(fmaxf(acc[j + 3] + b.w, 0.f));
+    }
+  } else if (c0 + 32 <= N) {
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
       const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
       const float4 a = *reinterpret_cast<const float4*>(sa + c0 + j);
-      acc[j + 0] = to_tf32_rna(fu_act(acc[j + 0] + b.x, a.x));
-      acc[j + 1] = to_tf32_rna(fu_act(acc[j + 1] + b.y, a.y));
-      acc[j + 2] = to_tf32_rna(fu_act(acc[j + 2] + b.z, a.z));
-      acc[j + 3] = to_tf32_rna(fu_act(acc[j + 3] + b.w, a.w));
+      acc[j + 0] = tf32_rna_fast(fu_act(acc[j + 0] + b.x, a.x));
+      acc[j + 1] = tf32_rna_fast(fu_act(acc[j + 1] + b.y, a.y));
+      acc[j + 2] = tf32_rna_fast(fu_act(acc[j + 2] + b.z, a.z));
+      acc[j + 3] = tf32_rna_fast(fu_act(acc[j + 3] + b.w, a.w));
     }
   } else {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      acc[j] = (c0 + j < N) ? to_tf32_rna(fu_act(acc[j] + sb[c0 + j], sa[c0 + j])) : 0.f;
+      acc[j] = (c0 + j < N) ? tf32_rna_fast(fu_act(acc[j] + sb[c0 + j], sa[c0 + j])) : 0.f;
   }
   tmem_st32(taddr, acc);
 }
 
 // one 32-column chunk of the LAST hidden layer: returns sum_n act(acc + b)[n] * w_out[n]
 __device__ __forceinline__ float fu_last_chunk(uint32_t taddr, const float* sb, const float* sa, const float* sw,
-                                               int c0, int N) {
+                                               int c0, int N, bool relu) {
   float acc[32];
   tmem_ld32(taddr, acc);
   float d0 = 0.f, d1 = 0.f;
-  if (c0 + 32 <= N) {
+  if (relu && c0 + 32 <= N) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
+      const float4 w = *reinterpret_cast<const float4*>(sw + c0 + j);
+      d0 = fmaf(fmaxf(acc[j + 0] + b.x, 0.f), w.x, d0);
+      d1 = fmaf(fmaxf(acc[j + 1] + b.y, 0.f), w.y, d1);
+      d0 = fmaf(fmaxf(acc[j + 2] + b.z, 0.f), w.z, d0);
+      d1 = fmaf(fmaxf(acc[j + 3] + b.w, 0.f), w.w, d1);
+    }
+  } else if (c0 + 32 <= N) {
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
       const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
@@ -434,14 +459,18 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           const float4 v = lds128(raw + (((uint32_t)cc ^ rx) << 4));
           x[4 * cc + 0] = v.x; x[4 * cc + 1] = v.y; x[4 * cc + 2] = v.z; x[4 * cc + 3] = v.w;
         }
+        if (p.sq_w) {                                   // FM's sum x^2 (sum_c v^2) term
 #pragma unroll
-        for (int cc = 0; cc < 8; ++cc) {
-          const float4 w = *reinterpret_cast<const float4*>(sq + cc * 4);
-          q = fmaf(x[4 * cc + 0] * x[4 * cc + 0], w.x, q); q = fmaf(x[4 * cc + 1] * x[4 * cc + 1], w.y, q);
-          q = fmaf(x[4 * cc + 2] * x[4 * cc + 2], w.z, q); q = fmaf(x[4 * cc + 3] * x[4 * cc + 3], w.w, q);
+          for (int cc = 0; cc < 8; ++cc) {
+            const float4 w = *reinterpret_cast<const float4*>(sq + cc * 4);
+            q = fmaf(x[4 * cc + 0] * x[4 * cc + 0], w.x, q); q = fmaf(x[4 * cc + 1] * x[4 * cc + 1], w.y, q);
+            q = fmaf(x[4 * cc + 2] * x[4 * cc + 2], w.z, q); q = fmaf(x[4 * cc + 3] * x[4 * cc + 3], w.w, q);
+          }
         }
+        if (with_lo) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) lo[j] = x[j] - trunc_tf32(x[j]);
+          for (int j = 0; j < 32; ++j) lo[j] = x[j] - trunc_tf32(x[j]);
+        }
         mbar_arrive(empty_raw(sr));                     // the chunk is in registers: the gather may refill the stage
         if (++sr == p.nr) { sr = 0; pr ^= 1u; }
         // the A ring shares its TMEM columns with the later layers' accumulators: wait until the previous tile is done with them
@@ -603,7 +632,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         const float* sa = fptr + mp.alpha[l];
         if (l < NL - 1) {
           for (int c0 = half * 32; c0 < L.KP; c0 += 64)
-            fu_hidden_chunk(t_lane + (uint32_t)(L.col + c0), sb, sa, c0, L.N);
+            fu_hidden_chunk(t_lane + (uint32_t)(L.col + c0), sb, sa, c0, L.N, L.act == CTRHOT_ACT_RELU);
           tmem_st_wait();
           tc_fence_before();
           mbar_arrive(h_ready(l));
@@ -619,8 +648,8 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
                 const float4 b = *reinterpret_cast<const float4*>(sb + c0 + j);
                 const float4 a = *reinterpret_cast<const float4*>(sa + c0 + j);
                 float4 o;
-                o.x = to_tf32_rna(fu_act(acc[j + 0] + b.x, a.x)); o.y = to_tf32_rna(fu_act(acc[j + 1] + b.y, a.y));
-                o.z = to_tf32_rna(fu_act(acc[j + 2] + b.z, a.z)); o.w = to_tf32_rna(fu_act(acc[j + 3] + b.w, a.w));
+                o.x = tf32_rna_fast(fu_act(acc[j + 0] + b.x, a.x)); o.y = tf32_rna_fast(fu_act(acc[j + 1] + b.y, a.y));
+                o.z = tf32_rna_fast(fu_act(acc[j + 2] + b.z, a.z)); o.w = tf32_rna_fast(fu_act(acc[j + 3] + b.w, a.w));
                 if (c0 + j < p.h_ld) stg_na_f4(dst + j, o);       // columns in [N, h_ld) are written as zeros
               }
             }
@@ -630,7 +659,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         } else {
           float dot = 0.f;
           for (int c0 = half * 32; c0 < L.KP; c0 += 64)
-            dot += fu_last_chunk(t_lane + (uint32_t)(L.col + c0), sb, sa, fptr + mp.wout, c0, L.N);
+            dot += fu_last_chunk(t_lane + (uint32_t)(L.col + c0), sb, sa, fptr + mp.wout, c0, L.N, L.act == CTRHOT_ACT_RELU);
           tc_fence_before();
           mbar_arrive(last_free);
           float* part = fptr + mp.part + (lt & 1) * FU_BM;
