@@ -230,6 +230,25 @@ int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M,
  * and the final Dense(h -> 1) then go through ctrhot_tower_rows_tf32 (one hidden layer may be up to 416 wide there). */
 int ctrhot_dense_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M, const ctrhot_dense_desc* layer,
                            float* h, int64_t h_ld, int cluster, void* stream);
+/* ctrhot_tower_rows_tf32 with an affine post:
+ *   out[m] = (sigmoid of) y_scale * Dense(h->1)(tower(x[m, :])) + add_scale * add_vec[m] + add_const     (add_vec may be NULL) */
+int ctrhot_tower_rows_post_tf32(const float* x, int64_t x_ld, int K, int64_t M,
+                                const ctrhot_dense_desc* h_layers, int n_layers,
+                                const float* add_vec, float y_scale, float add_scale, float add_const,
+                                int apply_sigmoid, int cluster, float* out, void* stream);
+/* DCN.call (DL/model/dcn.py:24-34) with a tower too wide to chain through TMEM (cfg 3: 400-400-400), FIRST launch:
+ * gather -> { the L <= 3 cross layers collapsed to scalars (see mode 2 of ctrhot_ctr_fused_tf32), exact fp32 on the CUDA
+ * cores | first Dense layer (out_dim <= 416) on the tensor pipe }.  h[m, :] = tf32(act(x_m W1 + b1)) and
+ * side[m] = a_L (x_m . final_w) + c_L . final_w reach HBM; x = [dense | embed] never does.
+ * layer->packed = ctrhot_fused_pack(W1, NULL, n, out_dim, D); cc_w = device [round32(n), 4], INTERNAL column order
+ * [embeddings | dense | 0], columns {w_0 .. w_{L-1}, final_w}; h_combine as for mode 2.  The remaining layers run as
+ * ctrhot_dense_rows_tf32 and ctrhot_tower_rows_post_tf32(add_vec = side, y_scale = wy, add_scale = 1, add_const = bias). */
+int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                const void* ids, int ids_kind, int64_t ids_ld,
+                                const float* dense, int64_t dense_ld, int D, int64_t M,
+                                const ctrhot_dense_desc* layer, const float* cc_w, int n_side,
+                                const float* h_combine, int n_combine, float* h, int64_t h_ld, float* side_out,
+                                int cluster, int* err_flag, void* stream);
 
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,

@@ -78,7 +78,10 @@ struct FuParams {
   int side_rows;                                           // rows of [s_hi | s_lo] behind W1 in every first-layer chunk (32 or 0)
   float* h_out; int64_t h_ld;                              // single hidden layer: act(x W + b), TF32-rounded, to HBM (no final dot)
   int nb;                                                  // W ring stages in use (<= FU_NB)
-  const float* add_vec; float out_scale;                   // tower mode: out = out_scale * (y + add_vec[m])   (WideDeep)
+  const float* add_vec; float out_scale, add_scale, add_const;   // tower mode: out = out_scale * y + add_scale * add_vec[m] + add_const
+  const float* cc_w; int cc_n;                             // DCN with few cross layers: side products on the CUDA cores (stager),
+                                                           // cc_w [KC1*32][4] internal column order, cc_n = n_side + 1 <= 4
+  float* side_out;                                         // store mode: the cross term of every row (fed to the last launch)
   float* out; int* err_flag;
   uint32_t b_stage_bytes;
 };
@@ -139,9 +142,10 @@ constexpr int FU_PF = 3;                    // chunks by which the id loads run 
 
 // float-region layout (shared by host sizing and device carving); all offsets in floats, 16-byte aligned
 struct FuSmemMap {
-  int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, total;
+  int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, ccw, total;
 };
-__host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries */, int KC1, const int* KP, int nl) {
+__host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries */, int KC1, const int* KP, int nl,
+                                                 bool cc = false) {
   FuSmemMap m;
   int o = 0;
   m.rowoff = o; o += (F * 3 + 3) / 4 * 4;          // per field: table base address (8 B) x F, then row count (4 B) x F
@@ -153,6 +157,7 @@ __host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries
   m.wout = o; o += KP[nl - 1];
   m.q = o; o += 2 * FU_BM;
   m.part = o; o += 2 * FU_BM;
+  m.ccw = o; if (cc) o += KC1 * 32 * 4;
   m.total = o;
   return m;
 }
@@ -263,7 +268,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
   for (int l = 0; l < FU_MAXL; ++l) KP[l] = (l < NL) ? p.L[l].KP : 0;
   const int KC1 = p.L[0].KC;
-  const FuSmemMap mp = fu_smem_map(p.F * p.G, KC1, KP, NL);
+  const FuSmemMap mp = fu_smem_map(p.F * p.G, KC1, KP, NL, p.cc_n > 0);
   float* fptr = reinterpret_cast<float*>(base_ptr + (f_base - base));
   const uint32_t bars = f_base + (uint32_t)mp.total * 4u;
   // barrier map
@@ -306,6 +311,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       s_fn[i] = nr < 0 ? 0u : (nr > 0x7FFFFFFF ? 0x7FFFFFFFu : (uint32_t)nr);   // ids are int32: larger tables cannot be addressed anyway
     }
     for (int i = tid; i < KC1 * 32; i += FU_THREADS) fptr[mp.sq + i] = p.sq_w ? __ldg(p.sq_w + i) : 0.f;
+    if (p.cc_n > 0) for (int i = tid; i < KC1 * 32 * 4; i += FU_THREADS) fptr[mp.ccw + i] = __ldg(p.cc_w + i);
 #pragma unroll
     for (int l = 0; l < NL; ++l) {
       const FuLayer& L = p.L[l];
@@ -449,6 +455,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     const bool with_lo = (p.a_w == 64);
     for (int lt = 0; lt < n_my; ++lt) {
       float q = 0.f;
+      float S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f;     // CUDA-core side products (DCN: x . w_l and x . final_w)
       for (int kc = 0; kc < KC1; ++kc) {
         mbar_wait(full_raw(sr), pr);
         const uint32_t raw = src0 + sr * FU_TILE_BYTES;
@@ -471,6 +478,29 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) lo[j] = x[j] - trunc_tf32(x[j]);
         }
+        if (p.cc_n > 0) {                               // exact fp32: the weights are read as warp-wide broadcasts
+          const float4* cw = reinterpret_cast<const float4*>(fptr + mp.ccw) + kc * 32;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float4 w = cw[j];
+            S0 = fmaf(x[j], w.x, S0); S1 = fmaf(x[j], w.y, S1); S2 = fmaf(x[j], w.z, S2); S3 = fmaf(x[j], w.w, S3);
+          }
+        }
+        if (kc == KC1 - 1) {
+          // per-row scalar for the epilogue, published before the arrive that lets the last MMAs of the tile go
+          float v = q;
+          if (p.cc_n > 0) {
+            const float S[4] = {S0, S1, S2, S3};
+            float a = 1.f, fin = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (j < p.n_side) a += fmaf(a, S[j], p.cb[j]);
+              else if (j == p.n_side) fin = S[j];
+            }
+            v = fmaf(a, fin, p.cb[p.n_side]);
+          }
+          fptr[mp.q + (lt & 1) * FU_BM + row] = v;
+        }
         mbar_arrive(empty_raw(sr));                     // the chunk is in registers: the gather may refill the stage
         if (++sr == p.nr) { sr = 0; pr ^= 1u; }
         // the A ring shares its TMEM columns with the later layers' accumulators: wait until the previous tile is done with them
@@ -484,7 +514,6 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         mbar_arrive(a_full(sa));
         if (++sa == (uint32_t)n_as) { sa = 0; pa ^= 1u; }
       }
-      fptr[mp.q + (lt & 1) * FU_BM + row] = q;
     }
   } else if (warp == 16) {
     // ================================================================ MMA issuer
@@ -506,7 +535,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           const bool two = L.BN > L.BNa;
           const uint32_t idesc32 = make_idesc_tf32(FU_BM, 32u), idesc16 = make_idesc_tf32(FU_BM, 16u);
           const uint32_t d_t = tmem_base + (uint32_t)L.col;
-          const bool side_on = (p.mode != FU_MODE_TOWER);      // a plain tower has no side products: skip their MMAs
+          const bool side_on = (p.side_rows > 0);              // tensor-pipe side products (none for a plain tower / CUDA-core sides)
           if (NL == 1 && lt > 0) { FU_TWAIT(4, mbar_wait(last_free, (uint32_t)(lt - 1) & 1u)); tc_fence_after(); }
           for (int kc = 0; kc < L.KC; ++kc) {
             FU_TWAIT(0, mbar_wait(full_b(sb), pb));
@@ -605,7 +634,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         const FuLayer& L = p.L[l];
         mbar_wait(d_full(l), dcount[l] & 1u); ++dcount[l];
         tc_fence_after();
-        if (l == 0 && half == 0 && p.mode != FU_MODE_TOWER) {
+        if (l == 0 && half == 0 && p.cc_n > 0) {
+          side = fptr[mp.q + (lt & 1) * FU_BM + row];
+          if (p.side_out && gm < p.M) p.side_out[gm] = side;
+        } else if (l == 0 && half == 0 && p.mode != FU_MODE_TOWER) {
           float S[32];
           tmem_ld32(t_lane + (uint32_t)p.ds_col, S);
 #pragma unroll
@@ -670,7 +702,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             float r;
             if (p.mode == FU_MODE_DEEPFM) r = 0.5f * (side + y);
             else if (p.mode == FU_MODE_DCN) r = side + fmaf(y, p.cb[p.n_side + 1], p.cb[p.n_side + 2]);
-            else r = p.out_scale * (y + (p.add_vec ? __ldg(p.add_vec + gm) : 0.f));
+            else r = fmaf(p.out_scale, y, fmaf(p.add_scale, p.add_vec ? __ldg(p.add_vec + gm) : 0.f, p.add_const));
             p.out[gm] = p.apply_sigmoid ? 1.0f / (1.0f + __expf(-r)) : r;
           }
         }
@@ -823,6 +855,12 @@ int fu_launch_nl(const FuParams& p, int nl, size_t smem, cudaStream_t st) {
   }
 }
 
+struct FuExtra {
+  const float* add_vec = nullptr; float out_scale = 1.f, add_scale = 1.f, add_const = 0.f;   // tower-mode post
+  float* h_out = nullptr; int64_t h_ld = 0;                                                  // store mode
+  const float* cc_w = nullptr; float* side_out = nullptr;                                    // CUDA-core side products (DCN)
+};
+
 // peers[0..G): arena of owner g (this rank's own at its index; the others mapped through ctrhot_peer_open); G = 1 is the
 // unsharded case.  row_off is [G, F+1].
 int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off, int row_stride, int F, int k,
@@ -830,8 +868,9 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
              const float* dense, int64_t dense_ld, int D, int64_t M,
              const ctrhot_dense_desc* h_layers, int n_layers,
              const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
-             int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream,
-             const float* add_vec = nullptr, float out_scale = 1.f, float* h_out = nullptr, int64_t h_ld = 0) {
+             int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream, const FuExtra& ex = FuExtra()) {
+  float* const h_out = ex.h_out;
+  const int64_t h_ld = ex.h_ld;
   if (!peers || G < 1 || G > FU_MAXG || rank < 0 || rank >= G) return CTRHOT_EARG;
   for (int g = 0; g < G; ++g) if (!peers[g] || !aligned16(peers[g])) return CTRHOT_EARG;
   if ((int64_t)F * G > 4096) return CTRHOT_ESHAPE;
@@ -849,12 +888,14 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4) return CTRHOT_EARG;
   if (k % 4 != 0 || !aligned16(arena) || F > 63) return CTRHOT_ESHAPE;
   // h_out: ONE hidden layer whose activations go to HBM (no final Dense); otherwise hidden layers + the final Dense(h -> 1)
-  if (h_out ? (n_layers != 1 || mode != FU_MODE_TOWER) : (n_layers < 2 || n_layers > FU_MAXL + 1)) return CTRHOT_ESHAPE;
+  if (h_out ? (n_layers != 1 || mode == FU_MODE_DEEPFM) : (n_layers < 2 || n_layers > FU_MAXL + 1)) return CTRHOT_ESHAPE;
+  if (ex.cc_w && (mode != FU_MODE_DCN || n_side + 1 > 4)) return CTRHOT_ESHAPE;
+  if (h_out && mode == FU_MODE_DCN && !ex.cc_w) return CTRHOT_ESHAPE;
   const ctrhot_dense_desc& o = h_layers[n_layers - 1];
   if (!h_out && (o.out_dim != 1 || o.act != CTRHOT_ACT_NONE || !o.weight)) return CTRHOT_ESHAPE;
   FuParams p{};
   const int nl = h_out ? 1 : n_layers - 1;
-  const bool side_on = (mode != FU_MODE_TOWER);
+  const bool side_on = (mode != FU_MODE_TOWER) && !ex.cc_w;      // side products on the tensor pipe
   const int n = D + F * k;
   int KP[FU_MAXL] = {0, 0, 0};
   int col = 0;
@@ -903,8 +944,9 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid;
   for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
-  p.add_vec = add_vec; p.out_scale = out_scale;
-  const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl);
+  p.add_vec = ex.add_vec; p.out_scale = ex.out_scale; p.add_scale = ex.add_scale; p.add_const = ex.add_const;
+  p.cc_w = ex.cc_w; p.cc_n = ex.cc_w ? n_side + 1 : 0; p.side_out = ex.side_out;
+  const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl, p.cc_n > 0);
   const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1;
   size_t smem = 0;
   bool fits = false;
@@ -984,8 +1026,10 @@ extern "C" int ctrhot_dense_rows_tf32(const float* x, int64_t x_ld, int K, int64
                                       float* h, int64_t h_ld, int cluster, void* stream) {
   if (!x || !layer || !h || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
   const int r = K % 4, k = K - r;
+  FuExtra ex;
+  ex.h_out = h; ex.h_ld = h_ld;
   return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, layer, 1,
-                  nullptr, FU_MODE_TOWER, 0, nullptr, 0, 0, cluster, nullptr, nullptr, stream, nullptr, 1.f, h, h_ld);
+                  nullptr, FU_MODE_TOWER, 0, nullptr, 0, 0, cluster, nullptr, nullptr, stream, ex);
 }
 
 // WideDeep.call (DL/model/wideDeep.py:24-34): out = sigmoid(scale * (add_vec[m] + DNN(Embed(ids))[m])) with the deep tower
@@ -997,6 +1041,37 @@ extern "C" int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off,
                                      const float* add_vec, float scale, int apply_sigmoid, int cluster,
                                      float* out, int* err_flag, void* stream) {
   if (!arena) return CTRHOT_EARG;
+  FuExtra ex;
+  ex.add_vec = add_vec; ex.out_scale = scale; ex.add_scale = scale;
   return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, nullptr,
-                  FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, err_flag, stream, add_vec, scale);
+                  FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, err_flag, stream, ex);
+}
+
+// DCN whose tower is too wide for TMEM chaining (cfg 3: 400-400-400), first launch: gather -> { L cross layers as scalars on
+// the CUDA cores (exact fp32, in the stager threads) | first Dense layer on the tensor pipe }; h1 and the per-row cross term
+// side[m] = a_L (x . final_w) + c_L . final_w go to HBM, x = [dense | embed] does not.  n_side = L <= 3.
+extern "C" int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                           const void* ids, int ids_kind, int64_t ids_ld,
+                                           const float* dense, int64_t dense_ld, int D, int64_t M,
+                                           const ctrhot_dense_desc* layer, const float* cc_w, int n_side,
+                                           const float* h_combine, int n_combine, float* h, int64_t h_ld, float* side_out,
+                                           int cluster, int* err_flag, void* stream) {
+  if (!arena || !cc_w || !side_out || !h) return CTRHOT_EARG;
+  FuExtra ex;
+  ex.h_out = h; ex.h_ld = h_ld; ex.cc_w = cc_w; ex.side_out = side_out;
+  return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, layer, 1, nullptr,
+                  FU_MODE_DCN, n_side, h_combine, n_combine, 0, cluster, nullptr, err_flag, stream, ex);
+}
+
+// ctrhot_tower_rows_tf32 with an affine post: out[m] = (sigmoid of) y_scale * tower(x_m) + add_scale * add_vec[m] + add_const
+extern "C" int ctrhot_tower_rows_post_tf32(const float* x, int64_t x_ld, int K, int64_t M,
+                                           const ctrhot_dense_desc* h_layers, int n_layers,
+                                           const float* add_vec, float y_scale, float add_scale, float add_const,
+                                           int apply_sigmoid, int cluster, float* out, void* stream) {
+  if (!x || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
+  const int r = K % 4, k = K - r;
+  FuExtra ex;
+  ex.add_vec = add_vec; ex.out_scale = y_scale; ex.add_scale = add_scale; ex.add_const = add_const;
+  return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, h_layers,
+                  n_layers, nullptr, FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, nullptr, stream, ex);
 }

@@ -242,6 +242,47 @@ class DenseStack:
                           ptr(out), stream_ptr())
         return out
 
+    def run_dcn_wide(self, E, ids, kind, ids_ld, dense, B, first_kernel_ref, cc_w, n_side, combine, wy, bias, err_flag, out,
+                     cluster=0):
+        """DCN with a wide tower (hidden layers of up to 416 units): ctrhot_dcn_first_layer_tf32 (gather + cross scalars +
+        first layer), ctrhot_dense_rows_tf32 per middle layer, ctrhot_tower_rows_post_tf32 (last hidden + final Dense +
+        sigmoid(side + wy * y + bias)).  Neither x nor the cross output exist in HBM."""
+        arr = self.descs()
+        n = len(arr)
+        D = dense.shape[1]
+        n_in, n1 = int(first_kernel_ref.shape[0]), int(first_kernel_ref.shape[1])
+        key = ("fused", None)
+        if key not in self._packed:
+            nbytes = _lib.query("ctrhot_fused_pack_bytes", n_in, n1)
+            buf = torch.empty(nbytes // 4, dtype=torch.float32, device=first_kernel_ref.device)
+            _lib.call("ctrhot_fused_pack", ptr(first_kernel_ref.contiguous()), None, n_in, n1, D, ptr(buf), stream_ptr())
+            self._packed[key] = buf
+        mx = max((arr[i].out_dim + 31) // 32 * 32 for i in range(n - 1))
+        if self._ws is None or self._ws.numel() < 2 * B * mx + B or self._ws.device != dense.device:
+            self._ws = torch.empty(2 * B * mx + B, dtype=torch.float32, device=dense.device)
+        side = self._ws[2 * B * mx:2 * B * mx + B]
+        cb = (ctypes.c_float * len(combine))(*[float(c) for c in combine])
+        h_ld = (n1 + 31) // 32 * 32
+        h = self._ws[:B * h_ld].view(B, h_ld)
+        arr[0].packed = ptr(self._packed[key])
+        _lib.call("ctrhot_dcn_first_layer_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(dense),
+                  dense.stride(0), D, B, ctypes.pointer(arr[0]), ptr(cc_w), int(n_side), cb, len(combine), ptr(h), h_ld,
+                  ptr(side), int(cluster), ptr(err_flag), stream_ptr())
+        cur, cur_ld = h, h_ld
+        for l in range(1, n - 1):
+            K, nl = arr[l].in_dim, arr[l].out_dim
+            arr[l].packed = ptr(self._rows_pack(l, K, nl))
+            if l < n - 2:
+                h_ld = (nl + 31) // 32 * 32
+                h = self._ws[(l & 1) * B * mx:(l & 1) * B * mx + B * h_ld].view(B, h_ld)
+                _lib.call("ctrhot_dense_rows_tf32", ptr(cur), cur_ld, K, B, ctypes.pointer(arr[l]), ptr(h), h_ld, 0,
+                          stream_ptr())
+                cur, cur_ld = h, h_ld
+            else:
+                _lib.call("ctrhot_tower_rows_post_tf32", ptr(cur), cur_ld, K, B, ctypes.pointer(arr[l]), 2, ptr(side),
+                          float(wy), 1.0, float(bias), 1, 0, ptr(out), stream_ptr())
+        return out
+
     def run_ctr_tower(self, E, ids, kind, ids_ld, dense, B, first_kernel_ref, add_vec=None, scale=1.0, sigmoid=False,
                       err_flag=None, out=None, cluster=0):
         """Tower fed from EmbedLayer ``E`` by the whole-model kernel; out = (sigmoid of) scale * (add_vec + y)."""

@@ -335,6 +335,16 @@ class DCN(_EmbedTowerModel):
             self._side = (key, side, cb)
         return self._side[1:]
 
+    def _cc_side(self, side, D, n):
+        """[round32(n), 4] copy of the first four side columns in the kernels' internal column order [embeddings | dense | 0]."""
+        key = (self._version, self.cross_layer._version)
+        if getattr(self, "_cc", None) is None or self._cc[0] != key:
+            cc = torch.zeros((_pad32(n), 4), dtype=torch.float32, device=self.device)
+            cc[:n - D] = side[D:n, :4]
+            cc[n - D:n] = side[:D, :4]
+            self._cc = (key, cc)
+        return self._cc[1]
+
     def _packed_cross(self, D, n):
         key = (self._version, self.cross_layer._version)
         if self._packed is None or self._packed[0] != key:
@@ -369,6 +379,21 @@ class DCN(_EmbedTowerModel):
                                     n_side=self.cross_layer.layer_num, combine=cb, sigmoid=True,
                                     err_flag=self.err_flag(), out=out, cluster=self.cluster,
                                     side_key=("dcn", self._version, self.cross_layer._version))
+                if self.check:
+                    self.check_ids()
+                return out
+        if (self.fused and self.whole and self.dense_layer.output_dim == 1 and self.cross_layer.layer_num <= 3
+                and len(self.dense_layer.hidden) >= 2 and E.k % 4 == 0 and E.F <= 63):
+            stack = self.dense_layer.stack
+            stack.set_layers(self._tower_layers(self.dense_layer, D), (self.dense_layer._version, D))
+            if stack.wide_rows_ok():
+                # tower too wide to chain through TMEM (cfg 3): gather + cross scalars + first layer in one launch, then one
+                # launch per remaining hidden layer; h1, h2 and the per-row cross term are the only intermediates in HBM
+                side, cb = self._cross_side(n)
+                cc_w = self._cc_side(side, D, n)
+                ids, kind, ids_ld = ids_arg(ids)
+                stack.run_dcn_wide(E, ids, kind, ids_ld, dense, B, self.dense_layer.hidden[0][0], cc_w,
+                                   self.cross_layer.layer_num, cb, cb[-2], cb[-1], self.err_flag(), out, cluster=self.cluster)
                 if self.check:
                     self.check_ids()
                 return out

@@ -139,8 +139,11 @@ def dcn_case(B, k, L, hidden, seed):
     return m, dense, ids, want
 
 
-@pytest.mark.parametrize("B,k,L,hidden", [(900, 16, 3, [256, 128, 64]), (130, 8, 6, [64, 32]), (2000, 16, 1, [128])])
+@pytest.mark.parametrize("B,k,L,hidden", [(900, 16, 3, [256, 128, 64]), (130, 8, 6, [64, 32]), (2000, 16, 1, [128]),
+                                          (1500, 16, 3, [400, 400, 400]), (129, 8, 2, [300, 72]), (20000, 16, 1, [416, 264, 40])])
 def test_dcn_whole_kernel(lib, B, k, L, hidden):
+    """The last three cases have towers too wide to chain through TMEM (cfg 3's 400-400-400 among them): the cross layers
+    run as exact fp32 scalars on the CUDA cores of the first launch, the layers go through HBM one launch each."""
     m, dense, ids, want = dcn_case(B, k, L, hidden, seed=B + L)
     got = npy(m((dense, ids)))
     logit_close(got, want)
