@@ -192,6 +192,8 @@ __device__ __forceinline__ void dt_ld16_nowait(uint32_t taddr, uint32_t (&r)[16]
 }
 __device__ __forceinline__ void dt_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float dt_prelu(float v, float a) { return fmaxf(v, 0.f) + a * fminf(v, 0.f); }
+// round-to-nearest (ties away) TF32 of a finite value: two integer ops instead of cvt.rna's NaN-preserving sequence
+__device__ __forceinline__ float dt_tf32_fast(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u); }
 
 struct DinParams {
   const float* table; int64_t V;
@@ -427,10 +429,10 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       for (int j = 0; j < 16; j += 4) {
         const float4 uu = *reinterpret_cast<const float4*>(u + n0 + j);
         const float4 aa = *reinterpret_cast<const float4*>(al1 + n0 + j);
-        acc[j + 0] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 0]) + uu.x, aa.x));
-        acc[j + 1] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 1]) + uu.y, aa.y));
-        acc[j + 2] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 2]) + uu.z, aa.z));
-        acc[j + 3] = to_tf32_rna(dt_prelu(__uint_as_float(r[j + 3]) + uu.w, aa.w));
+        acc[j + 0] = dt_tf32_fast(dt_prelu(__uint_as_float(r[j + 0]) + uu.x, aa.x));
+        acc[j + 1] = dt_tf32_fast(dt_prelu(__uint_as_float(r[j + 1]) + uu.y, aa.y));
+        acc[j + 2] = dt_tf32_fast(dt_prelu(__uint_as_float(r[j + 2]) + uu.z, aa.z));
+        acc[j + 3] = dt_tf32_fast(dt_prelu(__uint_as_float(r[j + 3]) + uu.w, aa.w));
       }
       if (!exact) {
 #pragma unroll

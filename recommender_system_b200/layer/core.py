@@ -388,7 +388,7 @@ class DenseStack:
         fn = "ctrhot_mlp_tf32" if self.precision == "tf32" else "ctrhot_mlp_f32"
         _lib.call(fn, ptr(x), x_ld, M, arr, n, ptr(out), out.stride(0), ptr(self._ws), self._ws.numel() * 4, stream_ptr())
         fused_dot = (self.precision == "tf32" and n >= 2 and n_out == 1 and arr[n - 1].act == _lib.ACT_NONE
-                     and out.stride(0) == 1 and 8 <= arr[n - 2].out_dim <= 256)
+                     and out.stride(0) == 1 and arr[n - 2].out_dim >= 8)
         _lib.LAUNCHES[0] += (n - 1 if fused_dot else n) - 1      # one kernel per layer; a trailing Dense(h->1) is fused
         if final_sigmoid:
             torch.sigmoid_(out)
