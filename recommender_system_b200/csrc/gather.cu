@@ -94,6 +94,84 @@ gather_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_o
   }
 }
 
+// ------------------------------------------------------------------ gather, F*k/4 <= 128 chunks per sample (k = 16: 104)
+// The ncu capture of gather_kernel at k = 16 (profiles/r01e_ncu_summary.md) showed DRAM at 29 % and the issue slots at 54 %:
+// the per-chunk index arithmetic (q / k4, 64-bit offsets, two row_off loads, range test) is what the warps spend their
+// time on.  With at most 4 chunks per lane all of that is a per-LANE constant: it is hoisted out of the sample loop, which
+// is left with 4 id loads (one sample ahead), 4 row loads and 4 stores per lane.
+#ifndef FU_GSMINB_
+#define FU_GSMINB_ 4          // resident CTAs per SM the register budget is cut for (tuning builds: profiles/build_variants.py)
+#endif
+template <int IDKIND>
+__global__ void __launch_bounds__(256, FU_GSMINB_)
+gather_small_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                    const void* __restrict__ ids, int64_t ids_ld, int64_t B,
+                    const float* __restrict__ dense, int64_t dense_ld, int D,
+                    float* __restrict__ out, int64_t out_ld, int* __restrict__ err_flag) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  constexpr int U = 4;
+  const int k4 = k >> 2, total = F * k4;
+  const float* base[U];
+  uint32_t nrow[U];
+  int fld[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int q = u * 32 + lane;
+    const bool act = q < total;
+    const int f = act ? q / k4 : 0, c = q - f * k4;
+    const int64_t r0 = row_off[f], nr = row_off[f + 1] - r0;
+    base[u] = arena + r0 * k + c * 4;
+    nrow[u] = !act ? 0u : (nr > 0x7FFFFFFF ? 0x7FFFFFFFu : (nr < 0 ? 0u : (uint32_t)nr));   // ids are int32
+    fld[u] = f;
+  }
+  const bool al = ((reinterpret_cast<uintptr_t>(out + D) & 15) == 0) && ((out_ld & 3) == 0);
+  auto load_ids = [&](int64_t b, uint32_t (&id)[U]) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      id[u] = 0xFFFFFFFFu;
+      if (b < B && u * 32 + lane < total) {
+        if (IDKIND == CTRHOT_IDS_I32) id[u] = (uint32_t)__ldg(static_cast<const int32_t*>(ids) + b * ids_ld + fld[u]);
+        else id[u] = (uint32_t)__float2int_rz(__ldg(static_cast<const float*>(ids) + b * ids_ld + fld[u]));
+      }
+    }
+  };
+  uint32_t idc[U], idn[U];
+  int64_t b = warp;
+  load_ids(b, idc);
+  bool bad = false;
+  while (b < B) {
+    const int64_t bn = b + nwarps;
+    load_ids(bn, idn);
+    float4 buf[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      buf[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (idc[u] < nrow[u]) buf[u] = ldg_nc_f4(base[u] + (uint64_t)idc[u] * (uint32_t)k);
+      else if (u * 32 + lane < total) bad = true;
+    }
+    for (int j = lane; j < D; j += 32) out[b * out_ld + j] = __ldg(dense + b * dense_ld + j);
+    float* orow = out + b * out_ld + D;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int q = u * 32 + lane;
+      if (q < total) {
+        if (al) {
+          stg_na_f4(orow + q * 4, buf[u]);
+        } else {
+          orow[q * 4 + 0] = buf[u].x; orow[q * 4 + 1] = buf[u].y;
+          orow[q * 4 + 2] = buf[u].z; orow[q * 4 + 3] = buf[u].w;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) idc[u] = idn[u];
+    b = bn;
+  }
+  if (bad && err_flag) *err_flag = 1;
+}
+
 // ------------------------------------------------------------------ shared front-end loader
 // Loads S samples' rows into registers: xv[s][i] = chunk q = lane + 32 i, xd[s] = dense[lane].
 template <int IDKIND, int NQ, int S>
@@ -429,6 +507,16 @@ extern "C" int ctrhot_gather_f32(const float* arena, const int64_t* row_off, int
 #define LAUNCH(KIND, VEC)                                                                         \
   gather_kernel<KIND, VEC><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, dense,     \
                                                  dense_ld, D, out, out_ld, err_flag)
+  if (vec && F * (k / 4) <= 128) {
+    if (ids_kind == CTRHOT_IDS_I32)
+      gather_small_kernel<CTRHOT_IDS_I32><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, dense, dense_ld, D, out,
+                                                                out_ld, err_flag);
+    else
+      gather_small_kernel<CTRHOT_IDS_F32><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, dense, dense_ld, D, out,
+                                                                out_ld, err_flag);
+    CTRHOT_LAUNCH_OK("ctrhot_gather_f32");
+    return CTRHOT_OK;
+  }
   if (ids_kind == CTRHOT_IDS_I32) { if (vec) LAUNCH(CTRHOT_IDS_I32, true); else LAUNCH(CTRHOT_IDS_I32, false); }
   else                            { if (vec) LAUNCH(CTRHOT_IDS_F32, true); else LAUNCH(CTRHOT_IDS_F32, false); }
 #undef LAUNCH
