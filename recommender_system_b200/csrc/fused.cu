@@ -669,11 +669,39 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           tc_fence_before();
           mbar_arrive(h_ready(l));
         } else if (p.h_out) {
+          const bool h_vec8 = ((reinterpret_cast<uintptr_t>(p.h_out) & 31) == 0) && ((p.h_ld & 7) == 0);
           // single wide layer: the activations go to HBM (TF32-rounded, so the next layer's MMA reads them exactly)
           for (int c0 = half * 32; c0 < L.KP; c0 += 64) {
             float acc[32];
             tmem_ld32(t_lane + (uint32_t)(L.col + c0), acc);
-            if (gm < p.M) {
+            if (gm < p.M && h_vec8) {
+              // 32 bytes per store: every instruction fills whole sectors (half as many LSU transactions as 16-byte stores;
+              // this epilogue holds up the next tile's MMAs, the accumulator is single-buffered at this width)
+              float* dst = p.h_out + gm * p.h_ld + c0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                float o[8];
+                const float4 b0 = *reinterpret_cast<const float4*>(sb + c0 + j), b1 = *reinterpret_cast<const float4*>(sb + c0 + j + 4);
+                if (L.act == CTRHOT_ACT_RELU) {
+                  o[0] = fmaxf(acc[j + 0] + b0.x, 0.f); o[1] = fmaxf(acc[j + 1] + b0.y, 0.f);
+                  o[2] = fmaxf(acc[j + 2] + b0.z, 0.f); o[3] = fmaxf(acc[j + 3] + b0.w, 0.f);
+                  o[4] = fmaxf(acc[j + 4] + b1.x, 0.f); o[5] = fmaxf(acc[j + 5] + b1.y, 0.f);
+                  o[6] = fmaxf(acc[j + 6] + b1.z, 0.f); o[7] = fmaxf(acc[j + 7] + b1.w, 0.f);
+                } else {
+                  const float4 a0 = *reinterpret_cast<const float4*>(sa + c0 + j), a1 = *reinterpret_cast<const float4*>(sa + c0 + j + 4);
+                  o[0] = fu_act(acc[j + 0] + b0.x, a0.x); o[1] = fu_act(acc[j + 1] + b0.y, a0.y);
+                  o[2] = fu_act(acc[j + 2] + b0.z, a0.z); o[3] = fu_act(acc[j + 3] + b0.w, a0.w);
+                  o[4] = fu_act(acc[j + 4] + b1.x, a1.x); o[5] = fu_act(acc[j + 5] + b1.y, a1.y);
+                  o[6] = fu_act(acc[j + 6] + b1.z, a1.z); o[7] = fu_act(acc[j + 7] + b1.w, a1.w);
+                }
+#pragma unroll
+                for (int e = 0; e < 8; ++e) o[e] = tf32_rna_fast(o[e]);
+                if (c0 + j < p.h_ld)
+                  asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                               :: "l"(dst + j), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]),
+                                  "f"(o[7]) : "memory");
+              }
+            } else if (gm < p.M) {
               float* dst = p.h_out + gm * p.h_ld + c0;
 #pragma unroll
               for (int j = 0; j < 32; j += 4) {
