@@ -35,6 +35,44 @@ wide_onehot_kernel(const float* __restrict__ dense, int64_t dense_ld, int D,
                    int64_t ids_ld, int F, const int64_t* __restrict__ col_off, int64_t B,
                    const float* __restrict__ w0, const float* __restrict__ w, float* __restrict__ out) {
   WARP_IDS();
+  // S samples per warp pass: all S * ceil(F/32) id loads are issued before the first dependent weight load, so a warp pays
+  // two DRAM round trips per S samples instead of per sample (the kernel is latency-bound: 4 bytes per (sample, field))
+  constexpr int S = 4;
+  if (F <= 32) {
+    const bool actf = lane < F;
+    const int64_t c0 = actf ? col_off[lane] : 0, nc = actf ? col_off[lane + 1] - c0 : 0;
+    const float wd = (lane < D) ? __ldg(w + __ldg(dense_col + lane)) : 0.f;
+    const float bias = __ldg(w0);
+    for (int64_t b0 = warp * S; b0 < B; b0 += nwarps * S) {
+      int64_t id[S];
+      float xd[S], acc[S];
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        const int64_t b = b0 + s;
+        id[s] = (actf && b < B) ? IdLoad<IDKIND>::at(ids, b * ids_ld + lane) : -1;
+        xd[s] = (lane < D && b < B) ? __ldg(dense + b * dense_ld + lane) : 0.f;
+      }
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        acc[s] = xd[s] * wd;
+        if (id[s] >= 0 && id[s] < nc) acc[s] += ldg_nc_f1(w + c0 + id[s]);
+      }
+      for (int j = 32 + lane; j < D; j += 32) {                  // more than 32 dense columns: rare
+#pragma unroll
+        for (int s = 0; s < S; ++s)
+          if (b0 + s < B) acc[s] = fmaf(__ldg(dense + (b0 + s) * dense_ld + j), __ldg(w + __ldg(dense_col + j)), acc[s]);
+      }
+#pragma unroll
+      for (int s = 0; s < S; ++s) acc[s] = warp_sum(acc[s]);
+      if (lane < S && b0 + lane < B) {
+        float v = acc[0];
+#pragma unroll
+        for (int s = 1; s < S; ++s) if (lane == s) v = acc[s];
+        out[b0 + lane] = v + bias;
+      }
+    }
+    return;
+  }
   for (int64_t b = warp; b < B; b += nwarps) {
     float acc = 0.f;
     for (int j = lane; j < D; j += 32)

@@ -141,7 +141,12 @@ class DIN(Model):
             ids = _ids_to_device(self._col(inputs, f["feat"]), dev)
             ids = ids.reshape(B, -1)[:, :1]
             e = tab.shape[1]
-            row_off = torch.tensor([0, tab.shape[0]], dtype=torch.int64, device=dev)
+            if not hasattr(self, "_row_offs"):
+                self._row_offs = {}
+            cached = self._row_offs.get(i)                 # built once: torch.tensor(..., device=) is a blocking copy
+            if cached is None or cached[0] != tab.shape[0]:
+                cached = self._row_offs[i] = (tab.shape[0], torch.tensor([0, tab.shape[0]], dtype=torch.int64, device=dev))
+            row_off = cached[1]
             from ..layer.base import ids_arg
             ids2, kind, ld = ids_arg(ids)
             view = emb[:, col:col + e]
