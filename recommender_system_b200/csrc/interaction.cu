@@ -514,6 +514,50 @@ pnn_inner_kernel(const float* __restrict__ e, int64_t e_ld, int F, int k, int64_
   }
 }
 
+// ---------------------------------------------------------------- R6 InnerProductLayer, warp = sample, lane = field
+// Lane i < F holds row e_i in registers (one coalesced 128-bit-per-piece read of the sample).  Round d = 1 .. F/2: every lane
+// fetches row (i + d) mod F from its owner by warp shuffles and forms one dot product, so each unordered pair is computed
+// once and the work is balanced ((F-1)/2 rounds for all lanes, plus half a round when F is even).  The 325 results are put
+// in pair order in a per-warp smem row and written as consecutive floats.  No smem traffic for the operands at all.
+// (Measured before: thread per (sample, pair) with scalar smem reads = 0.07 of HBM; a lane-per-sample tile variant was
+// latency-bound at one warp per scheduler and slower still.)
+template <int K>
+__global__ void __launch_bounds__(256)
+pnn_inner_rot_kernel(const float* __restrict__ e, int64_t e_ld, int F, int64_t B, float* __restrict__ out, int64_t out_ld) {
+  extern __shared__ float sm[];
+  WARP_IDS();
+  constexpr int K4 = K / 4;
+  const int P = F * (F - 1) / 2;
+  float* st = sm + (size_t)(threadIdx.x >> 5) * P;
+  const int full = (F - 1) / 2;                       // rounds in which every lane owns a pair
+  const bool half = (F & 1) == 0;                     // F even: round F/2 pairs lane i < F/2 with i + F/2
+  const bool act = lane < F;
+  for (int64_t b = warp; b < B; b += nwarps) {
+    float a[K];
+#pragma unroll
+    for (int c = 0; c < K4; ++c) {
+      const float4 v = act ? ldg_nc_f4(e + b * e_ld + (lane * K4 + c) * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      a[4 * c] = v.x; a[4 * c + 1] = v.y; a[4 * c + 2] = v.z; a[4 * c + 3] = v.w;
+    }
+    __syncwarp();                                     // the previous sample's results have left st
+    for (int d = 1; d <= full + (half ? 1 : 0); ++d) {
+      int j = lane + d;
+      if (j >= F) j -= F;
+      const int src = act ? j : lane;
+      float dot = 0.f;
+#pragma unroll
+      for (int c = 0; c < K; ++c) dot = fmaf(a[c], __shfl_sync(0xffffffffu, a[c], src), dot);
+      const bool mine = act && (d <= full || lane < F / 2);
+      if (mine) {
+        const int lo = lane < j ? lane : j, hi = lane < j ? j : lane;
+        st[lo * (2 * F - lo - 1) / 2 + hi - lo - 1] = dot;
+      }
+    }
+    __syncwarp();
+    for (int p = lane; p < P; p += 32) out[b * out_ld + p] = st[p];
+  }
+}
+
 // ---------------------------------------------------------------- R7 OuterProductLayer
 // out[b,p] = sum_a q[a] * (sum_c W[a,p,c] p_[c]),  p_=e_i, q=e_j.  CTA = (pair chunk, sample tile):
 // W[:,p,:] for PC pairs staged in smem once and reused by TS samples.
@@ -562,6 +606,140 @@ pnn_outer_kernel(const float* __restrict__ e, int64_t e_ld, int F, int k, int64_
   }
 }
 
+// ---------------------------------------------------------------- R8 CrossLayer, rows of up to 32 * 4 * NQ floats in registers
+// One warp per sample, S samples per pass: lane l holds the 16-byte pieces l, l + 32, ... of x_0 and x_l; the L weight and
+// bias vectors sit in smem (zero-padded to a multiple of 4, so the padding of the last piece contributes nothing).
+// HBM-bound: one read of x, one write of the output (or 4 bytes when only the dot with final_w is wanted).
+template <int NQ, int S>
+__global__ void __launch_bounds__(256)
+cross_reg_kernel(const float* __restrict__ x, int64_t x_ld, int d, int64_t B, int L,
+                 const float* __restrict__ w, const float* __restrict__ bia, float* __restrict__ out,
+                 int64_t out_ld, const float* __restrict__ final_w, float* __restrict__ dot_out) {
+  extern __shared__ float sm[];
+  WARP_IDS();
+  const int d4 = (d + 3) / 4, dp = d4 * 4;
+  float* s_w = sm;                       // [L][dp]
+  float* s_b = sm + (size_t)L * dp;      // [L][dp]
+  float* s_f = s_b + (size_t)L * dp;     // [dp]
+  for (int i = threadIdx.x; i < L * dp; i += blockDim.x) {
+    const int l = i / dp, j = i - l * dp;
+    s_w[i] = j < d ? __ldg(w + (size_t)l * d + j) : 0.f;
+    s_b[i] = j < d ? __ldg(bia + (size_t)l * d + j) : 0.f;
+  }
+  for (int j = threadIdx.x; j < dp; j += blockDim.x) s_f[j] = (final_w && j < d) ? __ldg(final_w + j) : 0.f;
+  __syncthreads();
+  const bool out_vec = out && ((out_ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  for (int64_t b0 = warp * S; b0 < B; b0 += nwarps * S) {
+    float4 x0[S][NQ], xl[S][NQ];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (q < d4 && b0 + s < B) {
+          v = ldg_nc_f4(x + (b0 + s) * x_ld + 4 * q);
+          if (4 * q + 3 >= d) {                        // last piece: whatever lies behind column d is not part of x
+            if (4 * q + 1 >= d) v.y = 0.f;
+            if (4 * q + 2 >= d) v.z = 0.f;
+            v.w = 0.f;
+          }
+        }
+        x0[s][i] = v; xl[s][i] = v;
+      }
+    }
+    for (int l = 0; l < L; ++l) {
+      const float4* wl = reinterpret_cast<const float4*>(s_w + (size_t)l * dp);
+      const float4* bl = reinterpret_cast<const float4*>(s_b + (size_t)l * dp);
+      float dot[S];
+#pragma unroll
+      for (int s = 0; s < S; ++s) dot[s] = 0.f;
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        if (q < d4) {
+          const float4 ww = wl[q];
+#pragma unroll
+          for (int s = 0; s < S; ++s)
+            dot[s] = fmaf(xl[s][i].x, ww.x, fmaf(xl[s][i].y, ww.y, fmaf(xl[s][i].z, ww.z, fmaf(xl[s][i].w, ww.w, dot[s]))));
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < S; ++s) dot[s] = warp_sum(dot[s]);
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        if (q < d4) {
+          const float4 bb = bl[q];
+#pragma unroll
+          for (int s = 0; s < S; ++s) {
+            xl[s][i].x = fmaf(x0[s][i].x, dot[s], bb.x) + xl[s][i].x;
+            xl[s][i].y = fmaf(x0[s][i].y, dot[s], bb.y) + xl[s][i].y;
+            xl[s][i].z = fmaf(x0[s][i].z, dot[s], bb.z) + xl[s][i].z;
+            xl[s][i].w = fmaf(x0[s][i].w, dot[s], bb.w) + xl[s][i].w;
+          }
+        }
+      }
+    }
+    if (out) {
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        if (b0 + s >= B) continue;
+        float* row = out + (b0 + s) * out_ld;
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) {
+          const int q = lane + 32 * i;
+          if (q >= d4) continue;
+          if (out_vec && 4 * q + 3 < d) stg_na_f4(row + 4 * q, xl[s][i]);
+        }
+        if (!out_vec || (d & 3)) {
+          // rows that are not 16-byte aligned (out_ld = d = 429): the 128 floats a pass holds are redistributed by
+          // shuffles so that every store instruction writes 32 CONSECUTIVE floats (4 sectors instead of 16 per instruction)
+#pragma unroll
+          for (int i = 0; i < NQ; ++i) {
+            if (32 * i * 4 >= d) continue;                                  // warp-uniform
+            const bool whole = out_vec && (128 * i + 127 < d);              // this pass was stored as whole float4 above
+            if (whole) continue;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int src = 8 * e + (lane >> 2);
+              const float vx = __shfl_sync(0xffffffffu, xl[s][i].x, src), vy = __shfl_sync(0xffffffffu, xl[s][i].y, src);
+              const float vz = __shfl_sync(0xffffffffu, xl[s][i].z, src), vw = __shfl_sync(0xffffffffu, xl[s][i].w, src);
+              const int c = lane & 3;
+              const float v = c == 0 ? vx : (c == 1 ? vy : (c == 2 ? vz : vw));
+              const int col = 128 * i + 32 * e + lane;
+              // with aligned rows only the tail piece (4 q + 3 >= d) is still to be written
+              const bool todo = out_vec ? ((col | 3) >= d) : true;
+              if (col < d && todo) row[col] = v;
+            }
+          }
+        }
+      }
+    }
+    if (final_w) {
+      const float4* fw = reinterpret_cast<const float4*>(s_f);
+      float dot[S];
+#pragma unroll
+      for (int s = 0; s < S; ++s) dot[s] = 0.f;
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        if (q < d4) {
+          const float4 ww = fw[q];
+#pragma unroll
+          for (int s = 0; s < S; ++s)
+            dot[s] = fmaf(xl[s][i].x, ww.x, fmaf(xl[s][i].y, ww.y, fmaf(xl[s][i].z, ww.z, fmaf(xl[s][i].w, ww.w, dot[s]))));
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        dot[s] = warp_sum(dot[s]);
+        if (lane == 0 && b0 + s < B) dot_out[b0 + s] = dot[s];
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------- R8 CrossLayer (x already in HBM)
 // One warp per sample, x0 / x_l held in a per-warp smem slab (any d); all L layers in one launch.
 __global__ void __launch_bounds__(128)
@@ -592,6 +770,36 @@ cross_kernel(const float* __restrict__ x, int64_t x_ld, int d, int64_t B, int L,
       if (lane == 0) dot_out[b] = s;
     }
     __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------- R10 Dice (elementwise), 128-bit path
+// Per-column constants (alpha, mean, 1/sqrt(var + eps)) staged in smem once per CTA; the column of a thread's float4 is
+// advanced incrementally (no 64-bit modulo per element, which was most of the old kernel's instruction count).
+__global__ void __launch_bounds__(256)
+dice_vec_kernel(const float* __restrict__ x, int64_t total4, int h4, const float* __restrict__ alphas,
+                const float* __restrict__ mean, const float* __restrict__ var, float eps, float* __restrict__ out) {
+  extern __shared__ float sm[];
+  const int h = h4 * 4;
+  float* s_a = sm; float* s_m = sm + h; float* s_r = sm + 2 * h;
+  for (int c = threadIdx.x; c < h; c += blockDim.x) {
+    s_a[c] = __ldg(alphas + c); s_m[c] = __ldg(mean + c); s_r[c] = 1.0f / sqrtf(__ldg(var + c) + eps);
+  }
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int c4 = (int)(i % h4);
+  const int step = (int)(stride % h4);
+  auto one = [&](float t, int c) {
+    const float p = 1.0f / (1.0f + expf(-(t - s_m[c]) * s_r[c]));
+    return s_a[c] * (1.0f - p) * t + p * t;
+  };
+  for (; i < total4; i += stride) {
+    const float4 v = ldg_nc_f4(x + i * 4);
+    const int c = c4 * 4;
+    stg_na_f4(out + i * 4, make_float4(one(v.x, c), one(v.y, c + 1), one(v.z, c + 2), one(v.w, c + 3)));
+    c4 += step;
+    if (c4 >= h4) c4 -= h4;
   }
 }
 
@@ -719,6 +927,13 @@ extern "C" int ctrhot_pnn_inner_f32(const float* e, int64_t e_ld, int F, int k, 
   const int P = F * (F - 1) / 2;
   if (!e || !out || F < 2 || k <= 0 || B < 0 || e_ld < (int64_t)F * k || out_ld < P) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
+  if ((k == 16 || k == 8) && F <= 32 && e_ld % 4 == 0 && aligned16(e)) {
+    const size_t sm2 = (size_t)8 * P * sizeof(float);
+    if (k == 16) pnn_inner_rot_kernel<16><<<warp_grid(B, 8), 256, sm2, ST(stream)>>>(e, e_ld, F, B, out, out_ld);
+    else pnn_inner_rot_kernel<8><<<warp_grid(B, 8), 256, sm2, ST(stream)>>>(e, e_ld, F, B, out, out_ld);
+    CTRHOT_LAUNCH_OK("ctrhot_pnn_inner_f32");
+    return CTRHOT_OK;
+  }
   const size_t smem = (size_t)8 * (F * k + 1) * sizeof(float) + (size_t)2 * P * sizeof(int);
   if (smem > 200 * 1024) return CTRHOT_ESHAPE;
   CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_inner_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -760,6 +975,26 @@ extern "C" int ctrhot_cross_f32(const float* x, int64_t x_ld, int d, int64_t B, 
   if (!out && !final_w) return CTRHOT_EARG;
   if ((out && out_ld < d) || (final_w && !dot)) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
+  if (x_ld % 4 == 0 && aligned16(x) && d <= 1024 && L <= 16) {
+    // rows fit the registers of a warp: register-resident kernel, 128-bit accesses
+    const int d4 = (d + 3) / 4;
+    const size_t sm2 = (size_t)(2 * L + 1) * d4 * 4 * sizeof(float);
+    const int nq = (d4 + 31) / 32;
+#define CROSS_LAUNCH(NQ, S)                                                                                         \
+    do {                                                                                                              \
+      CTRHOT_CUDA_OK(cudaFuncSetAttribute(cross_reg_kernel<NQ, S>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
+                                          (int)sm2), "cross attr");                                                  \
+      cross_reg_kernel<NQ, S><<<warp_grid(B, 8 * S), 256, sm2, ST(stream)>>>(x, x_ld, d, B, L, w, b, out, out_ld,     \
+                                                                            final_w, dot);                           \
+    } while (0)
+    if (nq <= 1) CROSS_LAUNCH(1, 4);
+    else if (nq <= 2) CROSS_LAUNCH(2, 4);
+    else if (nq <= 4) CROSS_LAUNCH(4, 1);
+    else CROSS_LAUNCH(8, 1);
+#undef CROSS_LAUNCH
+    CTRHOT_LAUNCH_OK("ctrhot_cross_f32");
+    return CTRHOT_OK;
+  }
   const size_t smem = (size_t)4 * 2 * d * sizeof(float);
   if (smem > 220 * 1024) return CTRHOT_ESHAPE;
   CTRHOT_CUDA_OK(cudaFuncSetAttribute(cross_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -774,6 +1009,14 @@ extern "C" int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float*
   if (!x || !alphas || !mean || !var || !out || rows < 0 || h <= 0) return CTRHOT_EARG;
   const int64_t total = rows * h;
   if (total == 0) return CTRHOT_OK;
+  if (h % 4 == 0 && h <= 4096 && aligned16(x) && aligned16(out)) {
+    const int64_t total4 = total / 4;
+    int64_t g4 = (total4 + 255) / 256;
+    if (g4 > kNumSMs * 8) g4 = kNumSMs * 8;
+    dice_vec_kernel<<<(int)g4, 256, (size_t)3 * h * sizeof(float), ST(stream)>>>(x, total4, h / 4, alphas, mean, var, eps, out);
+    CTRHOT_LAUNCH_OK("ctrhot_dice_f32");
+    return CTRHOT_OK;
+  }
   int64_t g = (total + 255) / 256;
   if (g > kNumSMs * 16) g = kNumSMs * 16;
   dice_kernel<<<(int)g, 256, 0, ST(stream)>>>(x, total, h, alphas, mean, var, eps, out);

@@ -214,6 +214,51 @@ def test_pnn_inner_outer(golden, lib):
     close_rel(npy(op(a["e"])), want_o)
 
 
+@pytest.mark.parametrize("B,F,k", [(1, 26, 16), (1000, 26, 16), (4099, 26, 8), (77, 5, 16), (333, 2, 8), (100, 33, 8), (64, 7, 4)])
+def test_pnn_products_shapes(lib, B, F, k):
+    """InnerProductLayer / OuterProductLayer on ragged batches, odd and minimal field counts (the lane-per-sample kernels
+    take k in {8, 16}, F <= 33; everything else goes through the generic kernels) against the float64 oracle, <= 1e-5."""
+    rng = np.random.default_rng(B + F + k)
+    e = S.f32(rng.uniform(-0.5, 0.5, (B, F, k)))
+    close_rel(npy(InnerProductLayer()(e)), O.inner_product_layer(e.astype(np.float64)))
+    P = F * (F - 1) // 2
+    W = S.f32(rng.normal(0, 0.05, (k, P, k)))
+    op = OuterProductLayer()
+    op.build(e.shape)
+    op.set_weights([W])
+    close_rel(npy(op(e)), O.outer_product_layer(e.astype(np.float64), W.astype(np.float64)))
+
+
+@pytest.mark.parametrize("B,d,L", [(1, 429, 3), (515, 429, 3), (300, 221, 6), (64, 1024, 2), (100, 7, 1), (50, 1500, 2)])
+def test_cross_shapes(lib, B, d, L):
+    """CrossLayer on row widths that are not multiples of 4 (output rows unaligned), the register-resident kernel's
+    widest case (d = 1024) and the generic kernel beyond it."""
+    rng = np.random.default_rng(B + d)
+    x = S.f32(rng.uniform(-1, 1, (B, d)))
+    ws = [S.f32(rng.normal(0, 0.05, (d, 1))) for _ in range(L)]
+    bs = [S.f32(rng.normal(0, 0.05, (d, 1))) for _ in range(L)]
+    Lr = CrossLayer(L)
+    Lr.build((None, d))
+    Lr.set_weights(ws + bs)
+    want = O.cross_layer(x.astype(np.float64), [w.astype(np.float64) for w in ws], [b.astype(np.float64) for b in bs])
+    close_rel(npy(Lr(x)), want)
+    xp = torch.zeros((B, (d + 3) // 4 * 4 + 4), dtype=torch.float32, device="cuda")      # padded rows: 128-bit loads
+    xp[:, :d] = torch.from_numpy(x)
+    xp[:, d:] = 7.0                                                                       # must not leak into the result
+    close_rel(npy(Lr(xp[:, :d])), want)
+
+
+@pytest.mark.parametrize("rows,h", [(1, 256), (1000, 64), (333, 40), (50, 7)])
+def test_dice_shapes(lib, rows, h):
+    rng = np.random.default_rng(rows + h)
+    x = S.f32(rng.normal(0, 2, (rows, h)))
+    a, m, v = S.f32(rng.uniform(0, 0.3, h)), S.f32(rng.normal(0, 0.5, h)), S.f32(rng.uniform(0.5, 1.5, h))
+    L = Dice()
+    L.build(x.shape)
+    L.set_weights([a, m, v])
+    close_rel(npy(L(x)), O.dice(x.astype(np.float64), a.astype(np.float64), m.astype(np.float64), v.astype(np.float64)))
+
+
 def test_dice(golden, lib):
     a, want = S.load_case(golden, "dice")
     L = Dice()
