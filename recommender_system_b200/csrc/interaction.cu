@@ -606,6 +606,110 @@ pnn_outer_kernel(const float* __restrict__ e, int64_t e_ld, int F, int k, int64_
   }
 }
 
+// ---------------------------------------------------------------- R7 OuterProductLayer, lane = sample
+// out[b,p] = sum_a q[a] * (sum_c W[a,p,c] p_[c]) is 272 FMA per (sample, pair): compute-bound (88 K FMA per sample at F = 26,
+// k = 16; 156 us at the fp32 peak for B = 65 536).  A warp owns 32 samples: their rows sit in a smem tile whose row stride is
+// an odd number of 16-byte chunks (lane s reads ITS sample conflict-free), p_ = e_i and q = e_j are held in registers, and
+// W[:, p, :] of a chunk of PC pairs is staged in smem once per CTA pass and read as warp-wide BROADCASTS, one LDS.128 per 4
+// FMA, 16 independent accumulation chains per pair.  (The old kernel read W and both rows by scalar LDS per FMA: 4.2 ms.)
+template <int K>
+__global__ void __launch_bounds__(128)
+pnn_outer_ls_kernel(const float* __restrict__ e, int64_t e_ld, int F, int64_t B, const float* __restrict__ W,
+                    float* __restrict__ out, int64_t out_ld, int ES, int warps, int PC) {
+  extern __shared__ float sm[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  constexpr int K4 = K / 4, KK = K * K;
+  const int P = F * (F - 1) / 2;
+  const int fk4 = F * K4;
+  float* sW = sm;                                            // [PC][K][K]
+  float* tile = sm + (size_t)PC * KK + (size_t)wid * 32 * ES;
+  const float* my = tile + (size_t)lane * ES;
+  const int64_t n_tiles = (B + 31) / 32;
+  const int64_t n_groups = (n_tiles + warps - 1) / warps;
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int64_t t = g * warps + wid;
+    const bool live = (wid < warps) && (t < n_tiles);
+    const int64_t b0 = t * 32;
+    // W chunk of PC = 2048 / K^2 pairs = 16 floats per thread, fetched into registers one chunk AHEAD of its use: the L2
+    // round trip of chunk n+1 runs under the FMAs of chunk n (it was 38 % of the stall samples when loaded in place)
+    float wr[16];
+    auto wload = [&](int p0) {
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        const int idx = (int)threadIdx.x + 128 * u;
+        const int pp = idx / KK, r = idx - pp * KK;
+        const int a = r / K, c = r - a * K;
+        wr[u] = (p0 + pp < P) ? __ldg(W + ((size_t)a * P + (p0 + pp)) * K + c) : 0.f;
+      }
+    };
+    wload(0);
+    if (live) {
+      for (int s2 = 0; s2 < 32; s2 += 2) {                   // two samples' loads in flight per pass
+        const int64_t ba = b0 + s2, bb = ba + 1;
+        for (int c = lane; c < fk4; c += 32) {
+          const float4 va = (ba < B) ? ldg_nc_f4(e + ba * e_ld + 4 * c) : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float4 vb = (bb < B) ? ldg_nc_f4(e + bb * e_ld + 4 * c) : make_float4(0.f, 0.f, 0.f, 0.f);
+          *reinterpret_cast<float4*>(tile + (size_t)s2 * ES + 4 * c) = va;
+          *reinterpret_cast<float4*>(tile + (size_t)(s2 + 1) * ES + 4 * c) = vb;
+        }
+      }
+    }
+    const int64_t b = b0 + lane;
+    int i = 0, j = 1;                                        // pair p = (i, j), row-major over i < j
+    for (int p0 = 0; p0 < P; p0 += PC) {
+      const int np = min(PC, P - p0);
+      __syncthreads();                                       // the previous chunk of W has been used by every warp
+#pragma unroll
+      for (int u = 0; u < 16; ++u) sW[(int)threadIdx.x + 128 * u] = wr[u];
+      __syncthreads();
+      if (p0 + PC < P) wload(p0 + PC);
+      if (!live) {                                           // keep (i, j) in step; nothing to compute
+        continue;
+      }
+      float pi[K];
+      int i_loaded = -1;
+      for (int pp = 0; pp < np; ++pp) {
+        if (i != i_loaded) {
+#pragma unroll
+          for (int c = 0; c < K4; ++c) {
+            const float4 v = *reinterpret_cast<const float4*>(my + (i * K4 + c) * 4);
+            pi[4 * c] = v.x; pi[4 * c + 1] = v.y; pi[4 * c + 2] = v.z; pi[4 * c + 3] = v.w;
+          }
+          i_loaded = i;
+        }
+        float qj[K];
+#pragma unroll
+        for (int c = 0; c < K4; ++c) {
+          const float4 v = *reinterpret_cast<const float4*>(my + (j * K4 + c) * 4);
+          qj[4 * c] = v.x; qj[4 * c + 1] = v.y; qj[4 * c + 2] = v.z; qj[4 * c + 3] = v.w;
+        }
+        const float4* w = reinterpret_cast<const float4*>(sW + (size_t)pp * KK);
+        // K independent chains t2[a] (c outermost): the dependent-FMA latency is hidden inside one warp, which matters at one
+        // warp per scheduler (a 54 KB tile per warp); summation order per chain is still c = 0 .. K-1
+        float t2[K];
+#pragma unroll
+        for (int a = 0; a < K; ++a) t2[a] = 0.f;
+#pragma unroll
+        for (int c = 0; c < K4; ++c) {
+#pragma unroll
+          for (int a = 0; a < K; ++a) {
+            const float4 ww = w[a * K4 + c];
+            t2[a] = fmaf(ww.x, pi[4 * c], t2[a]); t2[a] = fmaf(ww.y, pi[4 * c + 1], t2[a]);
+            t2[a] = fmaf(ww.z, pi[4 * c + 2], t2[a]); t2[a] = fmaf(ww.w, pi[4 * c + 3], t2[a]);
+          }
+        }
+        float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+        for (int a = 0; a < K; a += 2) { acc0 = fmaf(t2[a], qj[a], acc0); acc1 = fmaf(t2[a + 1], qj[a + 1], acc1); }
+        const float acc = acc0 + acc1;
+        if (b < B) out[b * out_ld + p0 + pp] = acc;
+        if (++j == F) { ++i; j = i + 1; }
+      }
+    }
+    __syncthreads();                                         // tiles are rewritten by the next group
+  }
+}
+
 // ---------------------------------------------------------------- R8 CrossLayer, rows of up to 32 * 4 * NQ floats in registers
 // One warp per sample, S samples per pass: lane l holds the 16-byte pieces l, l + 32, ... of x_0 and x_l; the L weight and
 // bias vectors sit in smem (zero-padded to a multiple of 4, so the padding of the last piece contributes nothing).
@@ -693,26 +797,18 @@ cross_reg_kernel(const float* __restrict__ x, int64_t x_ld, int d, int64_t B, in
           if (out_vec && 4 * q + 3 < d) stg_na_f4(row + 4 * q, xl[s][i]);
         }
         if (!out_vec || (d & 3)) {
-          // rows that are not 16-byte aligned (out_ld = d = 429): the 128 floats a pass holds are redistributed by
-          // shuffles so that every store instruction writes 32 CONSECUTIVE floats (4 sectors instead of 16 per instruction)
+          // rows that are not 16-byte aligned (out_ld = d = 429): the row goes through a per-warp smem slab so that every
+          // store instruction writes 32 CONSECUTIVE floats (4 sectors per instruction instead of 16; shuffles were slower)
+          float* slab = s_f + dp + (size_t)(threadIdx.x >> 5) * dp;
+          __syncwarp();
 #pragma unroll
           for (int i = 0; i < NQ; ++i) {
-            if (32 * i * 4 >= d) continue;                                  // warp-uniform
-            const bool whole = out_vec && (128 * i + 127 < d);              // this pass was stored as whole float4 above
-            if (whole) continue;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int src = 8 * e + (lane >> 2);
-              const float vx = __shfl_sync(0xffffffffu, xl[s][i].x, src), vy = __shfl_sync(0xffffffffu, xl[s][i].y, src);
-              const float vz = __shfl_sync(0xffffffffu, xl[s][i].z, src), vw = __shfl_sync(0xffffffffu, xl[s][i].w, src);
-              const int c = lane & 3;
-              const float v = c == 0 ? vx : (c == 1 ? vy : (c == 2 ? vz : vw));
-              const int col = 128 * i + 32 * e + lane;
-              // with aligned rows only the tail piece (4 q + 3 >= d) is still to be written
-              const bool todo = out_vec ? ((col | 3) >= d) : true;
-              if (col < d && todo) row[col] = v;
-            }
+            const int q = lane + 32 * i;
+            if (q < d4) *reinterpret_cast<float4*>(slab + 4 * q) = xl[s][i];
           }
+          __syncwarp();
+          // with aligned rows only the tail piece (4 q + 3 >= d) is still to be written
+          for (int col = out_vec ? (d & ~3) + lane : lane; col < d; col += 32) row[col] = slab[col];
         }
       }
     }
@@ -950,6 +1046,34 @@ extern "C" int ctrhot_pnn_outer_f32(const float* e, int64_t e_ld, int F, int k, 
   const int P = F * (F - 1) / 2;
   if (!e || !W || !out || F < 2 || k <= 0 || B < 0 || e_ld < (int64_t)F * k || out_ld < P) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
+  if ((k == 16 || k == 8) && e_ld % 4 == 0 && aligned16(e)) {
+    const int ES = ((F * k / 4) | 1) * 4;                                  // odd number of 16-byte chunks per tile row
+    const size_t tile_bytes = (size_t)32 * ES * sizeof(float);
+    int warps = 0, pc = 0;
+    for (int cand : {2048 / (k * k)}) {                                    // pairs of W per smem chunk (16 floats per thread)
+      const size_t wb = (size_t)cand * k * k * sizeof(float);
+      if (wb + tile_bytes > 220 * 1024) continue;
+      int wq = (int)((220 * 1024 - wb) / tile_bytes);
+      if (wq > 4) wq = 4;
+      if (wq > warps) { warps = wq; pc = cand; }
+    }
+    if (warps >= 1) {
+      const size_t sm2 = (size_t)pc * k * k * sizeof(float) + tile_bytes * warps;
+      const int64_t n_groups = ((B + 31) / 32 + warps - 1) / warps;
+      const int g2 = (int)(n_groups < kNumSMs ? n_groups : kNumSMs);
+      if (k == 16) {
+        CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_outer_ls_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2),
+                       "pnn_outer attr");
+        pnn_outer_ls_kernel<16><<<g2, 128, sm2, ST(stream)>>>(e, e_ld, F, B, W, out, out_ld, ES, warps, pc);
+      } else {
+        CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_outer_ls_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2),
+                       "pnn_outer attr");
+        pnn_outer_ls_kernel<8><<<g2, 128, sm2, ST(stream)>>>(e, e_ld, F, B, W, out, out_ld, ES, warps, pc);
+      }
+      CTRHOT_LAUNCH_OK("ctrhot_pnn_outer_f32");
+      return CTRHOT_OK;
+    }
+  }
   const int TS = 32;
   int PC = (int)((160 * 1024 / sizeof(float) - (size_t)TS * (F * k + 1)) / (k * k + 1));
   if (PC < 1) return CTRHOT_ESHAPE;
@@ -978,7 +1102,7 @@ extern "C" int ctrhot_cross_f32(const float* x, int64_t x_ld, int d, int64_t B, 
   if (x_ld % 4 == 0 && aligned16(x) && d <= 1024 && L <= 16) {
     // rows fit the registers of a warp: register-resident kernel, 128-bit accesses
     const int d4 = (d + 3) / 4;
-    const size_t sm2 = (size_t)(2 * L + 1) * d4 * 4 * sizeof(float);
+    const size_t sm2 = (size_t)(2 * L + 1 + 8) * d4 * 4 * sizeof(float);      // weights, biases, final_w, 8 per-warp slabs
     const int nq = (d4 + 31) / 32;
 #define CROSS_LAUNCH(NQ, S)                                                                                         \
     do {                                                                                                              \
