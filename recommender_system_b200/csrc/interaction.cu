@@ -2,6 +2,7 @@
 // the reference's FFM, PNN inner / outer product, DCN cross.  One warp per sample unless noted.
 // All are HBM/L2-bound integer+fp32 work; no tensor cores (interaction outputs must stay
 // within 1e-5 relative of the fp32 reference, which TF32 cannot give).
+#include <algorithm>
 #include "common.cuh"
 
 namespace ctrhot {
@@ -475,6 +476,113 @@ ffm_kernel(const float* __restrict__ dense, int64_t dense_ld, int D, const void*
     if (lane == 0) {
       const float r = lin + __ldg(w0) + 0.5f * (tsq - sq);
       out[b] = apply_sigmoid ? 1.0f / (1.0f + expf(-r)) : r;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- R3 FMLayer, dense x of up to 1024 columns in registers
+// One warp per S samples: lane l holds the 16-byte pieces l, l + 32, ... of each row.  v is staged transposed in smem as
+// sv[c][piece] = (v[4q][c] .. v[4q+3][c]) so that consecutive lanes read consecutive 16-byte words; two more planes carry w1
+// and sum_c v[j][c]^2.  Per element: KF + 2 FMA; the KF + 2 partial sums of a sample are reduced by shuffles.
+// out = w0 + x.w1 + 0.5 * (sum_c (x.v_c)^2 - sum_j x_j^2 sum_c v_jc^2)         (FMLayer.call, interaction.py:106-114)
+template <int KF, int NQ, int S>
+__global__ void __launch_bounds__(256)
+fm_dense_reg_kernel(const float* __restrict__ x, int64_t x_ld, int n, int64_t B, const float* __restrict__ w0,
+                    const float* __restrict__ w1, const float* __restrict__ v, int kfm, float* __restrict__ out,
+                    int apply_sigmoid) {
+  extern __shared__ float sm[];
+  WARP_IDS();
+  const int n4 = (n + 3) / 4;
+  float4* sv = reinterpret_cast<float4*>(sm);                 // [KF + 2][n4]
+  for (int i = threadIdx.x; i < (KF + 2) * n4; i += blockDim.x) {
+    const int c = i / n4, q = i - c * n4;
+    float r[4];
+#pragma unroll
+    for (int e2 = 0; e2 < 4; ++e2) {
+      const int j = 4 * q + e2;
+      float t = 0.f;
+      if (j < n) {
+        if (c < kfm) t = __ldg(v + (size_t)j * kfm + c);
+        else if (c == KF) t = __ldg(w1 + j);
+        else if (c == KF + 1) { for (int cc = 0; cc < kfm; ++cc) { const float u = __ldg(v + (size_t)j * kfm + cc); t = fmaf(u, u, t); } }
+      }
+      r[e2] = t;
+    }
+    sv[i] = make_float4(r[0], r[1], r[2], r[3]);
+  }
+  __syncthreads();
+  const float bias = __ldg(w0);
+  for (int64_t b0 = warp * S; b0 < B; b0 += nwarps * S) {
+    float4 xv[S][NQ];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (q < n4 && b0 + s < B) {
+          t = ldg_nc_f4(x + (b0 + s) * x_ld + 4 * q);
+          if (4 * q + 3 >= n) {                          // last piece: columns past n are not part of x
+            if (4 * q + 1 >= n) t.y = 0.f;
+            if (4 * q + 2 >= n) t.z = 0.f;
+            t.w = 0.f;
+          }
+        }
+        xv[s][i] = t;
+      }
+    }
+    float acc[S][KF + 2];
+#pragma unroll
+    for (int s = 0; s < S; ++s)
+#pragma unroll
+      for (int c = 0; c < KF + 2; ++c) acc[s][c] = 0.f;
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) {
+      const int q = lane + 32 * i;
+      if (q < n4) {
+#pragma unroll
+        for (int c = 0; c < KF + 1; ++c) {
+          const float4 w = sv[c * n4 + q];
+#pragma unroll
+          for (int s = 0; s < S; ++s)
+            acc[s][c] = fmaf(xv[s][i].x, w.x, fmaf(xv[s][i].y, w.y, fmaf(xv[s][i].z, w.z, fmaf(xv[s][i].w, w.w, acc[s][c]))));
+        }
+        const float4 w = sv[(KF + 1) * n4 + q];
+#pragma unroll
+        for (int s = 0; s < S; ++s)
+          acc[s][KF + 1] = fmaf(xv[s][i].x * xv[s][i].x, w.x, fmaf(xv[s][i].y * xv[s][i].y, w.y,
+                           fmaf(xv[s][i].z * xv[s][i].z, w.z, fmaf(xv[s][i].w * xv[s][i].w, w.w, acc[s][KF + 1]))));
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      // reduce-scatter of the KF + 2 partial sums (padded to 16): 31 shuffles instead of 5 per value, then one more
+      // warp sum of the per-factor terms (shuffles, not FMAs, are what this kernel issues most of)
+      float r16[16];
+#pragma unroll
+      for (int c = 0; c < 16; ++c) r16[c] = c < KF + 2 ? acc[s][c] : 0.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) r16[c] += __shfl_xor_sync(0xffffffffu, r16[c], 16);
+#pragma unroll
+      for (int o = 8; o >= 1; o >>= 1) {
+        const bool up = (lane & o) != 0;
+#pragma unroll
+        for (int c = 0; c < o; ++c) {
+          const float send = up ? r16[c] : r16[c + o];
+          const float keep = up ? r16[c + o] : r16[c];
+          r16[c] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+      }
+      const float t = r16[0];                              // lane l: total of value l % 16
+      float term = 0.f;
+      if (lane < KF) term = 0.5f * t * t;
+      else if (lane == KF) term = t;
+      else if (lane == KF + 1) term = -0.5f * t;
+      term = warp_sum(term);
+      if (lane == 0 && b0 + s < B) {
+        const float r = bias + term;
+        out[b0 + s] = apply_sigmoid ? 1.0f / (1.0f + expf(-r)) : r;
+      }
     }
   }
 }
@@ -957,6 +1065,23 @@ extern "C" int ctrhot_fm_dense_f32(const float* x, int64_t x_ld, int64_t n, int6
   if (kfm > 0 && !v) return CTRHOT_EARG;
   if (kfm > 31) return CTRHOT_ESHAPE;
   if (B == 0) return CTRHOT_OK;
+  if (n <= 512 && kfm >= 1 && kfm <= 12 && x_ld % 4 == 0 && aligned16(x)) {
+    // rows fit the registers of a warp (DeepFM's x = [dense | embed], n = 429): register-resident kernel
+    const int n4 = (int)((n + 3) / 4), nq = (n4 + 31) / 32;
+    const size_t sm2 = (size_t)(12 + 2) * n4 * sizeof(float4);
+#define FM_LAUNCH(KF, NQ, S)                                                                                          \
+    fm_dense_reg_kernel<KF, NQ, S><<<fm_grid, 256, (size_t)(KF + 2) * n4 * sizeof(float4), ST(stream)>>>(             \
+        x, x_ld, (int)n, B, w0, w1, v, kfm, out, apply_sigmoid)
+    (void)sm2;
+    // persistent: the weight planes are staged once per CTA, so no more CTAs than stay resident (2 per SM at 91 registers)
+    const int fm_grid = (int)std::min<int64_t>((B + 15) / 16, (int64_t)kNumSMs * 2);
+    if (kfm <= 4) { if (nq <= 1) FM_LAUNCH(4, 1, 4); else if (nq <= 2) FM_LAUNCH(4, 2, 2); else FM_LAUNCH(4, 4, 2); }
+    else if (kfm <= 8) { if (nq <= 1) FM_LAUNCH(8, 1, 4); else if (nq <= 2) FM_LAUNCH(8, 2, 2); else FM_LAUNCH(8, 4, 2); }
+    else { if (nq <= 1) FM_LAUNCH(12, 1, 4); else if (nq <= 2) FM_LAUNCH(12, 2, 2); else FM_LAUNCH(12, 4, 2); }
+#undef FM_LAUNCH
+    CTRHOT_LAUNCH_OK("ctrhot_fm_dense_f32");
+    return CTRHOT_OK;
+  }
   if (n >= 128 && kfm >= 1 && kfm <= 16) {                    // wide rows: four samples per warp, dense / sparse per 32 columns
     int64_t nb = ((B + 3) / 4 + 7) / 8;
     const int grid = (int)(nb < (int64_t)kNumSMs * 8 ? nb : (int64_t)kNumSMs * 8);
