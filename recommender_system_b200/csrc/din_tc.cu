@@ -29,9 +29,9 @@ namespace ctrhot {
 using namespace tc;
 
 constexpr int DT_BM = 128;
-constexpr int DT_NRAW = 3;
+constexpr int DT_NRAW = 4;
 constexpr int DT_THREADS = 17 * 32;
-constexpr int DT_HDR_BYTES = 2048;            // per stage: ids[128] int32 | q[<=64] | u[<=96]
+constexpr int DT_HDR_BYTES = 1536;            // per stage: ids[128] int32 | q[<=64] | u[<=96]  (1024 + 96 * 4 <= 1536)
 constexpr int DT_HDR_Q = 512, DT_HDR_U = 1024;
 
 struct DinShape {
@@ -39,6 +39,7 @@ struct DinShape {
   int N1p, N2p;            // out dims rounded up to 16 (MMA N)
   int AK;                  // 2K: K-extent of layer 1
   int nchK, nchA, nch2;    // 32-column chunks: key tile, W', W2
+  int SR;                  // key rows a stage holds: T rounded up to 8 (rows T..127 of the MMA tile are zeros made by the stager)
   int S1, S2;              // padded alpha row strides (floats): conflict-free one-row-per-thread reads
   // packed blob offsets (floats)
   int o_wq, o_b1, o_wa, o_w2, o_al1, o_al2, o_b2, o_w3, o_b3, total;
@@ -53,6 +54,7 @@ __host__ __device__ inline bool din_shape(int T, int K, int h1, int h2, DinShape
   if (!(K == 8 || K == 16 || K == 32 || K == 64)) return false;
   if (h1 < 8 || h1 > 96 || h2 < 1 || h2 > 64) return false;
   s.T = T; s.K = K; s.h1 = h1; s.h2 = h2;
+  s.SR = dt_round(T, 8);
   s.N1p = dt_round(h1, 16); s.N2p = dt_round(h2, 16);
   s.AK = 2 * K;
   s.nchK = (K + 31) / 32; s.nchA = (s.AK + 31) / 32; s.nch2 = (s.N1p + 31) / 32;
@@ -216,7 +218,7 @@ __host__ __device__ inline DinSmem din_smem(const DinShape& s, int nraw) {
   m.wa = o; o += (uint32_t)s.nchA * s.N1p * 128u;
   m.w2 = o; o += (uint32_t)s.nch2 * s.N2p * 128u;
   o = (o + 1023u) & ~1023u;
-  m.stage_bytes = (uint32_t)s.nchK * DT_BM * 128u + DT_HDR_BYTES;
+  m.stage_bytes = (uint32_t)s.nchK * (uint32_t)s.SR * 128u + DT_HDR_BYTES;
   m.stage0 = o; o += (uint32_t)nraw * m.stage_bytes;
   m.al1 = o; o += (uint32_t)s.T * s.S1 * 4u;
   m.al2 = o; o += (uint32_t)s.T * s.S2 * 4u;
@@ -300,7 +302,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
     const int PPR = K / 4;                                   // 16-byte pieces per key row (2, 4, 8 or 16)
     const int c = tg % PPR, rsub = tg / PPR, rpp = DT_BM / PPR;  // this thread: piece c of rows rsub + rpp * j, j < PPR
     const uint32_t rowbytes = (uint32_t)K * 4u;
-    const uint32_t chunk = (uint32_t)(c >> 3) * (DT_BM * 128u), pc = (uint32_t)(c & 7);
+    const uint32_t chunk = (uint32_t)(c >> 3) * ((uint32_t)s.SR * 128u), pc = (uint32_t)(c & 7);
     auto fetch = [&](int64_t i) -> int32_t {
       if (i >= n_my || tg >= T) return 0;
       const int64_t b = blockIdx.x + i * gridDim.x;
@@ -311,7 +313,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       const int64_t b = blockIdx.x + i * gridDim.x;
       mbar_wait(raw_free(st), (uint32_t)((i / nraw) & 1) ^ 1u);
       const uint32_t stage = base + mp.stage0 + (uint32_t)st * mp.stage_bytes;
-      const uint32_t hdr = stage + (uint32_t)s.nchK * DT_BM * 128u;
+      const uint32_t hdr = stage + (uint32_t)s.nchK * (uint32_t)s.SR * 128u;
       int32_t* ids_s = reinterpret_cast<int32_t*>(bp + (hdr - base));
       {
         const int32_t id = (IDKIND == CTRHOT_IDS_I32) ? raw_id : __float2int_rz(__int_as_float(raw_id));
@@ -322,8 +324,8 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       named_bar_sync(2, 128);
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
-        if (j < PPR) {
-          const int r = rsub + rpp * j;
+        const int r = rsub + rpp * j;
+        if (j < PPR && r < s.SR) {                       // rows >= SR are not stored: the stager writes zeros for them
           const int32_t id = ids_s[r];
           const bool ok = r < T && id >= 0;
           cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
@@ -351,7 +353,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
     for (int64_t i = 0; i < n_my; ++i) {
       const int st = (int)(i % nraw), slot = (int)(i & 1);
       const uint32_t stage = base + mp.stage0 + (uint32_t)st * mp.stage_bytes;
-      const uint32_t hq = stage + (uint32_t)s.nchK * DT_BM * 128u + DT_HDR_Q;
+      const uint32_t hq = stage + (uint32_t)s.nchK * (uint32_t)s.SR * 128u + DT_HDR_Q;
       mbar_wait(full_raw(st), (uint32_t)((i / nraw) & 1));
       if (t == 0) DT_MARK(1, i);
       mbar_wait(a_free(slot), (uint32_t)((i >> 1) & 1) ^ 1u);
@@ -360,9 +362,10 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
         if (g >= K / 8) break;
-        const uint32_t row = stage + (uint32_t)(g >> 2) * (DT_BM * 128u) + (uint32_t)t * 128u;
+        const uint32_t row = stage + (uint32_t)(g >> 2) * ((uint32_t)s.SR * 128u) + (uint32_t)(t < s.SR ? t : 0) * 128u;
         const uint32_t p0 = (uint32_t)((2 * g) & 7), p1 = p0 + 1;
-        const float4 k0 = dt_lds128(row + ((p0 ^ rx) << 4)), k1 = dt_lds128(row + ((p1 ^ rx) << 4));
+        float4 k0 = dt_lds128(row + ((p0 ^ rx) << 4)), k1 = dt_lds128(row + ((p1 ^ rx) << 4));
+        if (t >= s.SR) { k0 = make_float4(0.f, 0.f, 0.f, 0.f); k1 = k0; }
         const float4 q0 = dt_lds128(hq + (uint32_t)g * 32u), q1 = dt_lds128(hq + (uint32_t)g * 32u + 16u);
         const float kv[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
         const float qk[8] = {k0.x * q0.x, k0.y * q0.y, k0.z * q0.z, k0.w * q0.w, k1.x * q1.x, k1.y * q1.y, k1.z * q1.z, k1.w * q1.w};
@@ -443,7 +446,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
     for (int64_t i = 0; i < n_my; ++i) {
       const int st = (int)(i % nraw), slot = (int)(i & 1);
       const float* u = reinterpret_cast<const float*>(bp + mp.stage0 + (uint32_t)st * mp.stage_bytes +
-                                                      (uint32_t)s.nchK * DT_BM * 128u + DT_HDR_U);
+                                                      (uint32_t)s.nchK * (uint32_t)s.SR * 128u + DT_HDR_U);
       mbar_wait(d1_full(slot), (uint32_t)((i >> 1) & 1));
       if (t == 0) DT_MARK(3, i);
       tc_fence_after();
@@ -475,7 +478,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       const int st = (int)(i % nraw), slot = (int)(i & 1);
       const int64_t b = blockIdx.x + i * gridDim.x;
       const uint32_t stage_off = mp.stage0 + (uint32_t)st * mp.stage_bytes;
-      const int32_t* ids_s = reinterpret_cast<const int32_t*>(bp + stage_off + (uint32_t)s.nchK * DT_BM * 128u);
+      const int32_t* ids_s = reinterpret_cast<const int32_t*>(bp + stage_off + (uint32_t)s.nchK * (uint32_t)s.SR * 128u);
       mbar_wait(d2_full(slot), (uint32_t)((i >> 1) & 1));
       if (lane == 0 && q4 == 0) DT_MARK(5, i);
       tc_fence_after();
@@ -518,7 +521,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       named_bar_sync(1, 128);
       // out[c] = sum_t p_t k[t][c]: thread = (four columns 4 cq .., group g of rows t = g, g + G, ...)
       {
-        const uint8_t* kt = bp + stage_off + (uint32_t)(cq >> 3) * (DT_BM * 128u);
+        const uint8_t* kt = bp + stage_off + (uint32_t)(cq >> 3) * ((uint32_t)s.SR * 128u);
         const uint32_t pq = (uint32_t)(cq & 7);
         float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
         int r = g;
