@@ -396,7 +396,14 @@ def main():
     # ---- device-resident timing (value) with per-kernel events for the roofline
     for i in range(W):
         model(dev_in[i % NB])
+    # per-kernel CUDA events for the roofline line: a separate, untimed pass (two event records per step cost host time
+    # that the timed loop below should not carry -- the launch path is within ~10 us of the kernel's own duration)
     model.events = []                                   # DeepFM.call records (front_start, front_end, tower_end) when set
+    for i in range(min(K, 50)):
+        model(dev_in[i % NB])
+    torch.cuda.synchronize()
+    evs = model.events
+    model.events = None
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
@@ -410,11 +417,12 @@ def main():
     ms = max_over_ranks(e0.elapsed_time(e1))
     launches = _lib.LAUNCHES[0] - l0
     clocks = sampler.result()
-    evs = model.events
-    model.events = None
     whole = len(evs[0]) == 2                            # one persistent kernel did the whole forward
     if whole:
         whole_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+        # the step IS this one kernel: an event pair around a single launch also times the launch gap, so the kernel's
+        # duration is bounded above by the back-to-back step time of the timed loop
+        whole_ms = min(whole_ms, ms / K)
     else:
         front_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
         tower_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))

@@ -119,8 +119,19 @@ class DenseStack:
             self.layers = layers
             self._packed = {}
             self._key = version
+            self._descs_tmpl = None
 
     def descs(self):
+        """Fresh descriptor array (callers overwrite ``packed`` of layer 0); built once per weight version and copied after
+        that -- filling the ctypes structs was a third of the host time of a forward call."""
+        tmpl = getattr(self, "_descs_tmpl", None)
+        if tmpl is not None and tmpl[0] is self.layers:
+            return type(tmpl[1]).from_buffer_copy(tmpl[1])
+        arr = self._build_descs()
+        self._descs_tmpl = (self.layers, arr)
+        return type(arr).from_buffer_copy(arr)
+
+    def _build_descs(self):
         n = len(self.layers)
         arr = (_lib.DenseDesc * n)()
         for i, L in enumerate(self.layers):
