@@ -216,6 +216,17 @@ int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off, int F, int
                           const float* add_vec, float scale, int apply_sigmoid, int cluster,
                           float* out, int* err_flag, void* stream);
 
+/* WideDeep.call in ONE launch: as ctrhot_ctr_tower_tf32 (no dense columns in the deep input), with the wide logit
+ * w0 + sum_j dense[m, j] dw[j] + sum_f w[wide_off[f] + ids[m, f]] formed inside the kernel: the gather warps fetch the 4-byte
+ * weights next to the embedding rows, the stager threads add them up per row; out = (sigmoid of) scale * (tower + wide).
+ * wide_off: device int64 [F]; h_dw: HOST float [wide_D <= 16]; k a power of two >= 8. */
+int ctrhot_widedeep_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                               const void* ids, int ids_kind, int64_t ids_ld, int64_t M,
+                               const ctrhot_dense_desc* h_layers, int n_layers,
+                               const float* wide_w, const int64_t* wide_off, const float* wide_dense,
+                               int64_t wide_dense_ld, int wide_D, const float* h_dw, float w0, float scale,
+                               int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
+
 /* DNNLayer.call (DL/layer/interaction.py:40-46) on a matrix x [M, K] (row stride x_ld, x_ld % 4 == 0, x 16-byte aligned)
  * that already lives in HBM, by the same persistent kernel: out[m] = (sigmoid of) Dense(h->1)(tower(x[m, :])).
  * h_layers as for ctrhot_ctr_fused_tf32 with h_layers[0].packed = ctrhot_fused_pack(W1r, NULL, K, n1, K % 4) where

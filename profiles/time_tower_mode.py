@@ -18,6 +18,7 @@ ins = [tuple(torch.from_numpy(a).to(dev) for a in synth.criteo_batch(B, vocab, s
 set_seed(1)
 wd = WideDeep(synth.criteo_feature_columns(vocab, k), [256, 128, 64], 1, "relu", embed_dim=k, check_ids=False, device=dev)
 wd.build(None)
+wd.one_launch = False          # this script times the bare tower launch (and must run on A/B builds without the fused entry)
 wd(ins[0])
 E = wd.embed_layer
 stack = wd.deep.stack

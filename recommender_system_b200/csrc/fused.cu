@@ -82,6 +82,10 @@ struct FuParams {
   const float* cc_w; int cc_n;                             // DCN with few cross layers: side products on the CUDA cores (stager),
                                                            // cc_w [KC1*32][4] internal column order, cc_n = n_side + 1 <= 4
   float* side_out;                                         // store mode: the cross term of every row (fed to the last launch)
+  // Wide&Deep: the wide logit w0 + sum_j dense_j wd_j + sum_f w[wide_off[f] + id_f] formed inside this kernel: the gather warps
+  // fetch the 4-byte weights next to the rows (a 2 KB tail of every raw stage), the stager threads add them up per row
+  const float* wide_w; const int64_t* wide_off; const float* wide_dense; int64_t wide_dense_ld; int wide_D; float wide_dw[16];
+  uint32_t raw_stride;                                     // bytes per raw stage (16 KB, + 2 KB with the wide tail)
   float* out; int* err_flag;
   uint32_t b_stage_bytes;
 };
@@ -142,10 +146,10 @@ constexpr int FU_PF = 3;                    // chunks by which the id loads run 
 
 // float-region layout (shared by host sizing and device carving); all offsets in floats, 16-byte aligned
 struct FuSmemMap {
-  int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, ccw, total;
+  int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, ccw, wb, total;
 };
 __host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries */, int KC1, const int* KP, int nl,
-                                                 bool cc = false) {
+                                                 bool cc = false, bool wide = false) {
   FuSmemMap m;
   int o = 0;
   m.rowoff = o; o += (F * 3 + 3) / 4 * 4;          // per field: table base address (8 B) x F, then row count (4 B) x F
@@ -158,6 +162,7 @@ __host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries
   m.q = o; o += 2 * FU_BM;
   m.part = o; o += 2 * FU_BM;
   m.ccw = o; if (cc) o += KC1 * 32 * 4;
+  m.wb = o; if (wide) o += (2 * F + 3) / 4 * 4;     // per field: address of its block of the wide weight vector
   m.total = o;
   return m;
 }
@@ -251,10 +256,11 @@ __device__ __forceinline__ unsigned long long fu_now() {
 #define FU_TWAIT(slot, stmt) do { stmt; } while (0)
 #endif
 
-template <int NL, int C>
+template <int NL, int C, bool WIDE>
 __global__ void __launch_bounds__(FU_THREADS, 1)
 ctr_fused_kernel(const __grid_constant__ FuParams p) {
   extern __shared__ uint8_t smem_raw[];
+  constexpr uint32_t RAW_STRIDE = FU_TILE_BYTES + (WIDE ? 2048u : 0u);   // raw stage: 128 x 128 B of rows (+ the wide tail)
 #ifdef FU_TRACE
   if (threadIdx.x == 0 && blockIdx.x < 256) fu_times[blockIdx.x][0] = fu_now();
 #endif
@@ -262,13 +268,13 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   const uint32_t base = (raw_addr + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - raw_addr);
   const uint32_t r_base = base;                                         // FU_NR raw chunks
-  const uint32_t b_base = r_base + (uint32_t)p.nr * FU_TILE_BYTES;      // p.nb weight stages
+  const uint32_t b_base = r_base + (uint32_t)p.nr * RAW_STRIDE;       // p.nb weight stages
   const uint32_t f_base = b_base + (uint32_t)p.nb * p.b_stage_bytes;    // float region
   int KP[FU_MAXL];
 #pragma unroll
   for (int l = 0; l < FU_MAXL; ++l) KP[l] = (l < NL) ? p.L[l].KP : 0;
   const int KC1 = p.L[0].KC;
-  const FuSmemMap mp = fu_smem_map(p.F * p.G, KC1, KP, NL, p.cc_n > 0);
+  const FuSmemMap mp = fu_smem_map(p.F * p.G, KC1, KP, NL, p.cc_n > 0, WIDE);
   float* fptr = reinterpret_cast<float*>(base_ptr + (f_base - base));
   const uint32_t bars = f_base + (uint32_t)mp.total * 4u;
   // barrier map
@@ -312,6 +318,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     }
     for (int i = tid; i < KC1 * 32; i += FU_THREADS) fptr[mp.sq + i] = p.sq_w ? __ldg(p.sq_w + i) : 0.f;
     if (p.cc_n > 0) for (int i = tid; i < KC1 * 32 * 4; i += FU_THREADS) fptr[mp.ccw + i] = __ldg(p.cc_w + i);
+    if (WIDE) {
+      const float** s_wb = reinterpret_cast<const float**>(fptr + mp.wb);
+      for (int i = tid; i < p.F; i += FU_THREADS) s_wb[i] = p.wide_w + p.wide_off[i];
+    }
 #pragma unroll
     for (int l = 0; l < NL; ++l) {
       const FuLayer& L = p.L[l];
@@ -377,11 +387,21 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       advance(cf);
     };
     int rs = 0; uint32_t rph = 0;                        // raw stage of the next issue and its phase
+    constexpr bool wide_on = WIDE;
     auto issue = [&](int g, const int32_t (&reg)[8]) {
       const int s = rs;
       mbar_wait(empty_raw(s), rph ^ 1u);
       if (++rs == p.nr) { rs = 0; rph ^= 1u; }
-      const uint32_t dst = dst0 + (uint32_t)s * FU_TILE_BYTES;
+      const uint32_t dst = dst0 + (uint32_t)s * RAW_STRIDE;
+      // wide tail of the stage: [128 rows][4 slots] floats; this thread owns a slot when its piece is the first of a field
+      bool wide_here = false;
+      uint32_t wdst = 0;
+      const float* wbase = nullptr;
+      if (wide_on && ci.f < p.F && ci.part == 0) {
+        wide_here = true;
+        wdst = r_base + (uint32_t)s * RAW_STRIDE + FU_TILE_BYTES + (uint32_t)rsub * 16u + (k4 < 8 ? (uint32_t)(c / k4) * 4u : 0u);
+        wbase = reinterpret_cast<const float* const*>(fptr + mp.wb)[ci.f];
+      }
       if (ci.f < p.F) {
         const char* fb = reinterpret_cast<const char*>(s_fb[ci.f]) + ci.part * 16;
         const uint32_t nrow = s_fn[ci.f];
@@ -407,6 +427,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             const bool ok = id < nrow;
             bad |= !ok;
             cp_async16(dst + 2048u * i, ok ? (const void*)(fb + (uint64_t)id * rowbytes) : (const void*)p.arena, ok ? 16u : 0u);
+            if (wide_here) cp_async4(wdst + 256u * i, ok ? (const void*)(wbase + id) : (const void*)p.arena, ok ? 4u : 0u);
           }
         } else {
 #pragma unroll
@@ -415,6 +436,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             const bool ok = id < nrow;
             bad |= !ok;
             cp_async16(dst + 2048u * i, ok ? (const void*)(fb + (uint64_t)id * rowbytes) : (const void*)p.arena, ok ? 16u : 0u);
+            if (wide_here) cp_async4(wdst + 256u * i, ok ? (const void*)(wbase + id) : (const void*)p.arena, ok ? 4u : 0u);
           }
         }
         if (bad && p.err_flag) *p.err_flag = 1;
@@ -456,9 +478,18 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     for (int lt = 0; lt < n_my; ++lt) {
       float q = 0.f;
       float S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f;     // CUDA-core side products (DCN: x . w_l and x . final_w)
+      float wsum = 0.f;                                 // Wide&Deep: wide logit of this row (without w0)
+      if (WIDE && p.wide_D > 0) {
+        const int64_t gm = (((int64_t)cid + (int64_t)lt * ncl) * C + crank) * FU_BM + row;
+        if (gm < p.M) {
+          const float* dr = p.wide_dense + gm * p.wide_dense_ld;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) if (j < p.wide_D) wsum = fmaf(__ldg(dr + j), p.wide_dw[j], wsum);
+        }
+      }
       for (int kc = 0; kc < KC1; ++kc) {
         mbar_wait(full_raw(sr), pr);
-        const uint32_t raw = src0 + sr * FU_TILE_BYTES;
+        const uint32_t raw = src0 + sr * RAW_STRIDE;
         const float* sq = fptr + mp.sq + kc * 32;
         float x[32], lo[32];
 #pragma unroll
@@ -478,6 +509,21 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) lo[j] = x[j] - trunc_tf32(x[j]);
         }
+        if (WIDE) {
+          // the fields whose first piece lies in this chunk left their wide weight in the stage tail, in field order
+          const float4 wv = lds128(r_base + sr * RAW_STRIDE + FU_TILE_BYTES + (uint32_t)row * 16u);
+          const int k4 = p.k4;
+          const int piece0 = kc * 8;
+          if (k4 >= 8) {
+            if ((piece0 & (k4 - 1)) == 0 && piece0 < p.F * k4) wsum += wv.x;
+          } else {
+            const int nf = 8 / k4, f0 = piece0 / k4;
+            if (f0 < p.F) wsum += wv.x;
+            if (nf > 1 && f0 + 1 < p.F) wsum += wv.y;
+            if (nf > 2 && f0 + 2 < p.F) wsum += wv.z;
+            if (nf > 2 && f0 + 3 < p.F) wsum += wv.w;
+          }
+        }
         if (p.cc_n > 0) {                               // exact fp32: the weights are read as warp-wide broadcasts
           const float4* cw = reinterpret_cast<const float4*>(fptr + mp.ccw) + kc * 32;
 #pragma unroll
@@ -488,7 +534,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         }
         if (kc == KC1 - 1) {
           // per-row scalar for the epilogue, published before the arrive that lets the last MMAs of the tile go
-          float v = q;
+          float v = WIDE ? wsum : q;
           if (p.cc_n > 0) {
             const float S[4] = {S0, S1, S2, S3};
             float a = 1.f, fin = 0.f;
@@ -730,6 +776,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             float r;
             if (p.mode == FU_MODE_DEEPFM) r = 0.5f * (side + y);
             else if (p.mode == FU_MODE_DCN) r = side + fmaf(y, p.cb[p.n_side + 1], p.cb[p.n_side + 2]);
+            else if (WIDE) r = fmaf(p.out_scale, y, fmaf(p.add_scale, fptr[mp.q + (lt & 1) * FU_BM + row], p.add_const));
             else r = fmaf(p.out_scale, y, fmaf(p.add_scale, p.add_vec ? __ldg(p.add_vec + gm) : 0.f, p.add_const));
             p.out[gm] = p.apply_sigmoid ? 1.0f / (1.0f + __expf(-r)) : r;
           }
@@ -814,12 +861,12 @@ extern "C" int ctrhot_debug_fused_times(unsigned long long* h_out) {
 namespace {
 // Resident clusters of C CTAs for this kernel variant (a cluster must fit inside one GPC: 33 clusters of 4 = 132 CTAs,
 // 74 of 2 = 148 on B200).  The occupancy query costs host time, so it is made once per (variant, smem size).
-template <int NL, int C>
+template <int NL, int C, bool WIDE>
 int fu_max_clusters(size_t smem) {
   static size_t cached_smem = ~(size_t)0;
   static int cached_n = 0;
   if (cached_smem == smem && cached_n > 0) return cached_n;
-  auto kern = ctr_fused_kernel<NL, C>;
+  auto kern = ctr_fused_kernel<NL, C, WIDE>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
     (void)cudaGetLastError();
     return kNumSMs / C;
@@ -844,11 +891,11 @@ int fu_max_clusters(size_t smem) {
   return n;
 }
 
-template <int NL, int C>
+template <int NL, int C, bool WIDE>
 int fu_launch(const FuParams& p0, size_t smem, cudaStream_t st) {
   FuParams p = p0;
-  auto kern = ctr_fused_kernel<NL, C>;
-  const int max_clusters = fu_max_clusters<NL, C>(smem);      // also sets the dynamic shared memory attribute
+  auto kern = ctr_fused_kernel<NL, C, WIDE>;
+  const int max_clusters = fu_max_clusters<NL, C, WIDE>(smem);      // also sets the dynamic shared memory attribute
   p.n_super = (p.n_tiles + C - 1) / C;
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(FU_THREADS);
@@ -866,20 +913,20 @@ int fu_launch(const FuParams& p0, size_t smem, cudaStream_t st) {
 }
 
 template <int C>
-int fu_max_clusters_nl(int nl, size_t smem) {
+int fu_max_clusters_nl(int nl, size_t smem, bool wide) {
   switch (nl) {
-    case 1: return fu_max_clusters<1, C>(smem);
-    case 2: return fu_max_clusters<2, C>(smem);
-    default: return fu_max_clusters<3, C>(smem);
+    case 1: return wide ? fu_max_clusters<1, C, true>(smem) : fu_max_clusters<1, C, false>(smem);
+    case 2: return wide ? fu_max_clusters<2, C, true>(smem) : fu_max_clusters<2, C, false>(smem);
+    default: return wide ? fu_max_clusters<3, C, true>(smem) : fu_max_clusters<3, C, false>(smem);
   }
 }
 
 template <int C>
-int fu_launch_nl(const FuParams& p, int nl, size_t smem, cudaStream_t st) {
+int fu_launch_nl(const FuParams& p, int nl, size_t smem, cudaStream_t st, bool wide) {
   switch (nl) {
-    case 1: return fu_launch<1, C>(p, smem, st);
-    case 2: return fu_launch<2, C>(p, smem, st);
-    default: return fu_launch<3, C>(p, smem, st);
+    case 1: return wide ? fu_launch<1, C, true>(p, smem, st) : fu_launch<1, C, false>(p, smem, st);
+    case 2: return wide ? fu_launch<2, C, true>(p, smem, st) : fu_launch<2, C, false>(p, smem, st);
+    default: return wide ? fu_launch<3, C, true>(p, smem, st) : fu_launch<3, C, false>(p, smem, st);
   }
 }
 
@@ -887,6 +934,8 @@ struct FuExtra {
   const float* add_vec = nullptr; float out_scale = 1.f, add_scale = 1.f, add_const = 0.f;   // tower-mode post
   float* h_out = nullptr; int64_t h_ld = 0;                                                  // store mode
   const float* cc_w = nullptr; float* side_out = nullptr;                                    // CUDA-core side products (DCN)
+  const float* wide_w = nullptr; const int64_t* wide_off = nullptr; const float* wide_dense = nullptr;   // Wide&Deep wide term
+  int64_t wide_dense_ld = 0; int wide_D = 0; const float* wide_dw = nullptr;
 };
 
 // peers[0..G): arena of owner g (this rank's own at its index; the others mapped through ctrhot_peer_open); G = 1 is the
@@ -974,15 +1023,24 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
   p.add_vec = ex.add_vec; p.out_scale = ex.out_scale; p.add_scale = ex.add_scale; p.add_const = ex.add_const;
   p.cc_w = ex.cc_w; p.cc_n = ex.cc_w ? n_side + 1 : 0; p.side_out = ex.side_out;
-  const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl, p.cc_n > 0);
+  if (ex.wide_w) {
+    // the stage tail holds at most four fields per 32-column chunk and assumes fields start on piece boundaries
+    if (mode != FU_MODE_TOWER || G != 1 || rows_mode || !ex.wide_off || ex.wide_D < 0 || ex.wide_D > 16 ||
+        (ex.wide_D > 0 && (!ex.wide_dense || !ex.wide_dw)) || (k & (k - 1)) != 0 || k < 8) return CTRHOT_ESHAPE;
+    p.wide_w = ex.wide_w; p.wide_off = ex.wide_off; p.wide_dense = ex.wide_dense; p.wide_dense_ld = ex.wide_dense_ld;
+    p.wide_D = ex.wide_D;
+    for (int j = 0; j < 16; ++j) p.wide_dw[j] = j < ex.wide_D ? ex.wide_dw[j] : 0.f;
+  }
+  const bool wide = (ex.wide_w != nullptr);
+  p.raw_stride = FU_TILE_BYTES + (wide ? 2048u : 0u);
+  const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl, p.cc_n > 0, p.wide_w != nullptr);
   const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1;
   size_t smem = 0;
   bool fits = false;
   // deepest rings that fit: weight stages first (each is a round trip to L2), then raw-row stages
   for (p.nb = FU_NB; p.nb >= 2 && !fits; --p.nb) {
     for (p.nr = FU_NR; p.nr >= (p.nb >= 3 ? 3 : 2) && !fits; --p.nr) {
-      smem = 1024 + (size_t)FU_NR * FU_TILE_BYTES + (size_t)p.nb * bmax + (size_t)mp.total * 4 + 8 * n_bars + 16
-             - (size_t)(FU_NR - p.nr) * FU_TILE_BYTES;
+      smem = 1024 + (size_t)p.nr * p.raw_stride + (size_t)p.nb * bmax + (size_t)mp.total * 4 + 8 * n_bars + 16;
       fits = smem <= 227 * 1024;
       if (fits) break;
     }
@@ -997,15 +1055,15 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
     if (p.n_tiles < 2) C = 1;
     else if (p.n_tiles < 4 * 32) C = 2;
     else {
-      const int n4 = fu_max_clusters_nl<4>(nl, smem), n2 = fu_max_clusters_nl<2>(nl, smem);
+      const int n4 = fu_max_clusters_nl<4>(nl, smem, wide), n2 = fu_max_clusters_nl<2>(nl, smem, wide);
       const int w4 = ((p.n_tiles + 3) / 4 + n4 - 1) / n4, w2 = ((p.n_tiles + 1) / 2 + n2 - 1) / n2;
       C = (w4 <= w2) ? 4 : 2;
     }
   }
   // every multicast piece must stay 16-byte granular (it is: rows * 128 / C)
-  if (C == 4) return fu_launch_nl<4>(p, nl, smem, st);
-  if (C == 2) return fu_launch_nl<2>(p, nl, smem, st);
-  return fu_launch_nl<1>(p, nl, smem, st);
+  if (C == 4) return fu_launch_nl<4>(p, nl, smem, st, wide);
+  if (C == 2) return fu_launch_nl<2>(p, nl, smem, st, wide);
+  return fu_launch_nl<1>(p, nl, smem, st, wide);
 }
 }  // namespace
 
@@ -1072,6 +1130,27 @@ extern "C" int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off,
   FuExtra ex;
   ex.add_vec = add_vec; ex.out_scale = scale; ex.add_scale = scale;
   return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, nullptr,
+                  FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, err_flag, stream, ex);
+}
+
+// WideDeep.call (DL/model/wideDeep.py:22-34) in ONE launch: the deep tower fed from the embedding arena as in
+// ctrhot_ctr_tower_tf32, and the wide logit formed inside the same kernel -- the gather warps fetch w[wide_off[f] + id_f] next to
+// the embedding rows (the ids are in their registers anyway), the stager threads add them and the dense term per row:
+//   out[m] = (sigmoid of) scale * (tower(m) + w0 + sum_j dense[m, j] dw[j] + sum_f w[wide_off[f] + ids[m, f]])
+// wide_off: DEVICE int64 [F]; dw: HOST float [wide_D <= 16] (the reference's wide input carries the dense block twice: pass the sum
+// of the two weight blocks).  k must be a power of two >= 8.
+extern "C" int ctrhot_widedeep_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                          const void* ids, int ids_kind, int64_t ids_ld, int64_t M,
+                                          const ctrhot_dense_desc* h_layers, int n_layers,
+                                          const float* wide_w, const int64_t* wide_off, const float* wide_dense,
+                                          int64_t wide_dense_ld, int wide_D, const float* h_dw, float w0, float scale,
+                                          int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  if (!arena || !wide_w || !wide_off) return CTRHOT_EARG;
+  FuExtra ex;
+  ex.out_scale = scale; ex.add_scale = scale; ex.add_const = scale * w0;
+  ex.wide_w = wide_w; ex.wide_off = wide_off; ex.wide_dense = wide_dense; ex.wide_dense_ld = wide_dense_ld;
+  ex.wide_D = wide_D; ex.wide_dw = h_dw;
+  return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, nullptr, 0, 0, M, h_layers, n_layers, nullptr,
                   FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, err_flag, stream, ex);
 }
 

@@ -314,6 +314,23 @@ class DenseStack:
                   int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag), stream_ptr())
         return out
 
+    def run_widedeep(self, E, ids, kind, ids_ld, B, first_kernel_ref, wide_w, wide_off, dense, D, h_dw, w0, scale, err_flag,
+                     out, cluster=0):
+        """Wide&Deep in one launch: deep tower from the arena + the wide logit formed in the same kernel."""
+        arr = self.descs()
+        n, n1 = int(first_kernel_ref.shape[0]), int(first_kernel_ref.shape[1])
+        key = ("fused", None)
+        if key not in self._packed:
+            nbytes = _lib.query("ctrhot_fused_pack_bytes", n, n1)
+            buf = torch.empty(nbytes // 4, dtype=torch.float32, device=first_kernel_ref.device)
+            _lib.call("ctrhot_fused_pack", ptr(first_kernel_ref.contiguous()), None, n, n1, 0, ptr(buf), stream_ptr())
+            self._packed[key] = buf
+        arr[0].packed = ptr(self._packed[key])
+        _lib.call("ctrhot_widedeep_fused_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, B, arr, len(arr),
+                  ptr(wide_w), ptr(wide_off), ptr(dense), dense.stride(0), int(D), h_dw, float(w0), float(scale), 1,
+                  int(cluster), ptr(out), ptr(err_flag), stream_ptr())
+        return out
+
     def run_fused_gather(self, E, ids, kind, ids_ld, dense, B, post=None, err_flag=None, out=None):
         """Tower fed straight from the embedding arena of EmbedLayer ``E`` (x never exists in HBM)."""
         arr = self.descs()

@@ -37,13 +37,14 @@ class WideLayer(Layer):
                   ptr(out), stream_ptr())
         return out
 
-    def call_onehot(self, dense, dense_col, ids, col_off):
-        """Same result without materialising the one-hot block: w0 + sum dense_j w[dense_col_j] + sum_f w[col_off_f+id_f]."""
+    def call_onehot(self, dense, dense_col, ids, col_off, w=None):
+        """Same result without materialising the one-hot block: w0 + sum dense_j w[dense_col_j] + sum_f w[col_off_f+id_f].
+        ``w``: a weight vector of the same layout to use instead of ``self.w`` (WideDeep folds its duplicated dense block)."""
         ids, kind, ids_ld = ids_arg(ids)
         B = ids.shape[0]
         out = _out(B, self.device)
         _lib.call("ctrhot_wide_onehot_f32", ptr(dense), dense.stride(0), dense.shape[1], ptr(dense_col), ptr(ids), kind,
-                  ids_ld, ids.shape[1], ptr(col_off), B, ptr(self.w0), ptr(self.w), ptr(out), stream_ptr())
+                  ids_ld, ids.shape[1], ptr(col_off), B, ptr(self.w0), ptr(self.w if w is None else w), ptr(out), stream_ptr())
         return out
 
 

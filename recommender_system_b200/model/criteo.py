@@ -9,6 +9,8 @@ stored as floats) as numpy or torch; or the fast path ``(dense_f32 [B,13], ids_i
 """
 from __future__ import annotations
 
+import ctypes
+
 import numpy as np
 import torch
 
@@ -257,14 +259,39 @@ class WideDeep(_EmbedTowerModel):
         dense, ids, onehot = split_inputs(inputs, self.device, D, E.F)
         require_cuda(dense, "WideDeep")
         B = dense.shape[0]
+        stack = self.deep.stack
+        stack.set_layers(self.deep.layer_dicts(), self.deep._version)
+        if (onehot is None and getattr(self, "one_launch", True) and self.deep.output_dim == 1 and D <= 16 and E.k >= 8
+                and (E.k & (E.k - 1)) == 0 and stack.ctr_fused_ok(E.F, E.k)):
+            # ONE launch: the wide logit is formed inside the persistent kernel (ctrhot_widedeep_fused_tf32)
+            wkey = self.wide._version
+            if getattr(self, "_wide_host", None) is None or self._wide_host[0] != wkey:
+                w = self.wide.w.reshape(-1)
+                dw = (w[:D] + w[D:2 * D]).cpu().tolist()       # the dense block appears twice in the wide input
+                self._wide_host = (wkey, (ctypes.c_float * max(D, 1))(*dw), float(self.wide.w0.item()), w.contiguous())
+            _, dw, w0, wflat = self._wide_host
+            out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+            ids2, kind, ids_ld = ids_arg(ids)
+            stack.run_widedeep(E, ids2, kind, ids_ld, B, self.deep.hidden[0][0], wflat, self.col_off, dense, D, dw, w0, 0.5,
+                               E.err_flag(), out)
+            if self.check:
+                E.check_ids()
+            return out
         if onehot is not None:
             wide_in = torch.cat([dense, onehot], dim=1)
             if wide_in.shape[1] != self.wide.w.shape[0]:
                 raise ValueError("wide input has %d columns, weights expect %d" % (wide_in.shape[1], self.wide.w.shape[0]))
             wide_out = self.wide(wide_in)
         else:
-            dense2 = torch.cat([dense, dense], dim=1)
-            wide_out = self.wide.call_onehot(dense2, self.dense_col, ids, self.col_off)
+            # the wide input carries the dense block twice (dataset.py:53-58): x_j w_j + x_j w_{D+j} = x_j (w_j + w_{D+j}), so
+            # the two weight blocks are summed once per weight version instead of concatenating [dense, dense] per call
+            wkey = self.wide._version
+            if getattr(self, "_wide_folded", None) is None or self._wide_folded[0] != wkey:
+                w2 = self.wide.w.clone()
+                w2[:D] += w2[D:2 * D]
+                w2[D:2 * D] = 0
+                self._wide_folded = (wkey, w2)
+            wide_out = self.wide.call_onehot(dense, self.dense_col[:D], ids, self.col_off, w=self._wide_folded[1])
         out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
         stack = self.deep.stack
         stack.set_layers(self.deep.layer_dicts(), self.deep._version)

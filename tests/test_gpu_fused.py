@@ -12,7 +12,7 @@ import torch
 
 from oracle import ctr_oracle as O
 from oracle import synth as S
-from recommender_system_b200.model.criteo import DCN, DeepFM
+from recommender_system_b200.model.criteo import DCN, DeepFM, WideDeep
 from recommender_system_b200.utils import synth
 
 pytestmark = pytest.mark.gpu
@@ -150,6 +150,49 @@ def test_dcn_whole_kernel(lib, B, k, L, hidden):
     m.whole = False
     got2 = npy(m((dense, ids)))
     logit_close(got2, want)
+
+
+@pytest.mark.parametrize("B,k,hidden", [(900, 16, [256, 128, 64]), (129, 8, [64, 32]), (3000, 32, [128]), (65, 64, [40, 24])])
+def test_widedeep_one_launch(lib, B, k, hidden):
+    """Wide&Deep with the wide logit formed inside the persistent kernel (ctrhot_widedeep_fused_tf32: 4-byte weights fetched by
+    the gather warps next to the embedding rows) against the float64 oracle in its sparse form, and against the two-launch path."""
+    rng = np.random.default_rng(B + k)
+    vocab = small_vocab(rng)
+    D, F = 13, 26
+    m = WideDeep(synth.criteo_feature_columns(vocab, k), hidden, 1, "relu", embed_dim=k, precision="tf32")
+    m.build(None)
+    tables = [S.f32(rng.uniform(-0.5, 0.5, (v, k))) for v in vocab]
+    m.embed_layer.set_tables(tables)
+    n_wide = 2 * D + sum(vocab)
+    w0, w = S.f32(rng.normal(0, 0.1, (1,))), S.f32(rng.normal(0, 0.3, (n_wide, 1)))
+    m.wide.set_weights([w0, w])
+    ws = []
+    dims = [F * k] + list(hidden) + [1]
+    for i in range(len(dims) - 1):
+        lim = np.sqrt(6.0 / (dims[i] + dims[i + 1]))
+        ws += [S.f32(rng.uniform(-lim, lim, (dims[i], dims[i + 1]))), S.f32(rng.normal(0, 0.1, (dims[i + 1],)))]
+    m.deep.set_weights(ws)
+    dense, ids = synth.criteo_batch(B, vocab, seed=B)
+    off = 2 * D + np.concatenate([[0], np.cumsum(vocab)])
+    w64 = w[:, 0].astype(np.float64)
+    wide = w0.astype(np.float64)[0] + dense.astype(np.float64) @ (w64[:D] + w64[D:2 * D])
+    for f in range(F):
+        wide = wide + w64[off[f] + ids[:, f]]
+    pairs = [(ws[2 * i].astype(np.float64), ws[2 * i + 1].astype(np.float64)) for i in range(len(ws) // 2)]
+    emb = O.embed_layer(ids, [t.astype(np.float64) for t in tables])
+    deep = O.dnn_layer(emb, pairs[:-1], pairs[-1], "relu")[:, 0]
+    want = O.sigmoid(0.5 * (wide + deep))
+    got = npy(m((dense, ids)))[:, 0]
+    logit_close(got, want)
+    m.one_launch = False
+    got2 = npy(m((dense, ids)))[:, 0]
+    logit_close(got2, want)
+    # an id past its field's vocabulary is reported, as on the two-launch path
+    bad = ids.copy()
+    bad[B // 2, 5] = vocab[5]
+    m.one_launch = True
+    with pytest.raises(IndexError):
+        m((dense, bad))
 
 
 def test_whole_kernel_out_of_range_id(lib):
