@@ -63,6 +63,15 @@ int ctrhot_gather_f32(const float* arena, const int64_t* row_off, int F, int k,
                       const float* dense, int64_t dense_ld, int D,
                       float* out, int64_t out_ld, int* err_flag, void* stream);
 
+/* ---- 8(f) next: NFM bi-interaction, NFM.call DL/model/nfm.py:24-30 (with the [B, F, k] view of the embeddings the model
+ * means: SURVEY N2) ------------------------------------------------------------------------------------------------------
+ * out[b, 0:D] = dense[b, :],  out[b, D:D+k] = 0.5 * ((sum_f e_f)^2 - sum_f e_f^2),  out[b, D+k:out_ld) = 0  -- gather and
+ * pooling in registers, the F rows never reach HBM.  k a multiple of 4 with k/4 a power of two, k <= 128. */
+int ctrhot_nfm_bi_f32(const float* arena, const int64_t* row_off, int F, int k,
+                      const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
+                      const float* dense, int64_t dense_ld, int D,
+                      float* out, int64_t out_ld, int* err_flag, void* stream);
+
 /* ---- R2  WideLayer.call, DL/layer/interaction.py:24-26 -----------------------
  * one-hot form: out[b] = w0 + sum_j dense[b,j]*w[dense_col[j]] + sum_f w[col_off[f]+ids[b,f]]
  * (dense_col int32[D], col_off int64[F+1]; the reference's wide input repeats

@@ -299,6 +299,24 @@ def dcn_model(inputs, tables, cross_ws, cross_bs, dnn_hidden, dnn_out, final, ac
     return sigmoid(x @ kernel + bias)
 
 
+def bi_interaction(emb):
+    """NFM's Bi-Interaction pooling, DL/model/nfm.py:28: 0.5 * ((sum_f e_f)^2 - sum_f e_f^2) over the field axis of [B,F,k]."""
+    return 0.5 * (np.sum(emb, axis=1) ** 2 - np.sum(emb ** 2, axis=1))
+
+
+def nfm_model(inputs, tables, bn, dnn_hidden, dnn_out, final, act="relu", n_dense=13):
+    """NFM.call, DL/model/nfm.py:24-34.  The reference pools ``emb`` over ``axis=1`` of what its own
+    comment calls ``[None, 26, embed_dim]``; its EmbedLayer returns the flattened [B, F*k] (core.py:279), so the model as
+    written does not run -- this follows the comment: the [B, F, k] view.
+    bn = (mean, var, gamma, beta) of keras BatchNormalization (eps 1e-3); final = (kernel [out_dim,1], bias [1])."""
+    dense_inputs, sparse_inputs = inputs[:, :n_dense], inputs[:, n_dense:n_dense + len(tables)]
+    emb = embed_layer(sparse_inputs, tables, flatten=False)
+    x = np.concatenate([dense_inputs, bi_interaction(emb)], axis=-1)
+    x = batchnorm_infer(x, bn[0], bn[1], bn[2], bn[3], eps=1e-3)
+    y = dnn_layer(x, dnn_hidden, dnn_out, act)
+    return sigmoid(y @ final[0] + final[1])
+
+
 def pnn_model(inputs, tables, mode, dnn_hidden, dnn_out, outer_w=None, act="relu", n_dense=13):
     """PNN.call, DL/model/pnn.py:28-53 with the [B,F,k] view the product layers
     are specified on.  No sigmoid (:52-53)."""

@@ -6,7 +6,7 @@ import numpy as np
 import torch
 from recommender_system_b200 import _lib
 from recommender_system_b200.layer import set_seed
-from recommender_system_b200.model.criteo import DCN, PNN, WideDeep
+from recommender_system_b200.model.criteo import DCN, NFM, PNN, WideDeep
 from recommender_system_b200.utils import synth
 
 dev = torch.device("cuda", 0)
@@ -50,3 +50,10 @@ m = DCN(fc, [256, 128, 64], 1, "relu", 3, embed_dim=k, check_ids=False, device=d
 ms, l = t(lambda i: m(ins[i % 3]))
 line("DCN (L=3, tower 256-128-64: whole-model kernel)", ms, l, 2 * (429 * 256 + 256 * 128 + 128 * 64 + 64) + 6 * 429)
 del m
+del m
+set_seed(1)
+fc8 = synth.criteo_feature_columns(vocab, 8)
+m = NFM(fc8, [256, 128, 64], 1, "relu", embed_dim=8, check_ids=False, device=dev)
+m.build(None)
+ms, l = t(lambda i: m(ins[i % 3]))
+line("NFM (k=8, Bi-Interaction + tower 256-128-64; SURVEY 8(f) rank 1)", ms, l, 2 * (21 * 256 + 256 * 128 + 128 * 64 + 64) + 26 * 8 * 3)

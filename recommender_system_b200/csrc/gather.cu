@@ -172,6 +172,65 @@ gather_small_kernel(const float* __restrict__ arena, const int64_t* __restrict__
   if (bad && err_flag) *err_flag = 1;
 }
 
+// ------------------------------------------------------------------ NFM bi-interaction
+// NFM.call, DL/model/nfm.py:24-30:  bi = 0.5 * ((sum_f e_f)^2 - sum_f e_f^2)  over the F gathered rows, x = [dense | bi].
+// One warp per sample; lane l takes the 16-byte pieces l, l + 32, ... of the sample's F*k/4 pieces.  k/4 divides 32, so all
+// pieces of a lane belong to the same 4 columns: the lane keeps sum and sum of squares of those columns in registers, lanes
+// with equal l mod k/4 are combined by xor-shuffles, and lanes 0 .. k/4-1 write the k results.  The rows never reach HBM.
+template <int IDKIND>
+__global__ void __launch_bounds__(256)
+nfm_bi_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+              const void* __restrict__ ids, int64_t ids_ld, int64_t B,
+              const float* __restrict__ dense, int64_t dense_ld, int D,
+              float* __restrict__ out, int64_t out_ld, int* __restrict__ err_flag) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const int k4 = k >> 2, total = F * k4;
+  const int sh = 31 - __clz(k4);                       // k4 = 1 << sh
+  const int c = lane & (k4 - 1);
+  constexpr int U = 4;
+  bool bad = false;
+  for (int64_t b = warp; b < B; b += nwarps) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f), ss = s;
+    for (int q0 = 0; q0 < total; q0 += 32 * U) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int q = q0 + 32 * u + lane;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (q < total) {
+          const int f = q >> sh;
+          const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+          const int64_t r0 = __ldg(row_off + f), r1 = __ldg(row_off + f + 1);
+          if (id >= 0 && id < r1 - r0) v[u] = ldg_nc_f4(arena + (r0 + id) * k + c * 4);
+          else bad = true;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {                    // fixed order: the sum over fields is deterministic
+        s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w;
+        ss.x = fmaf(v[u].x, v[u].x, ss.x); ss.y = fmaf(v[u].y, v[u].y, ss.y);
+        ss.z = fmaf(v[u].z, v[u].z, ss.z); ss.w = fmaf(v[u].w, v[u].w, ss.w);
+      }
+    }
+    for (int o = 16; o >= k4; o >>= 1) {
+      s.x += __shfl_xor_sync(0xffffffffu, s.x, o); s.y += __shfl_xor_sync(0xffffffffu, s.y, o);
+      s.z += __shfl_xor_sync(0xffffffffu, s.z, o); s.w += __shfl_xor_sync(0xffffffffu, s.w, o);
+      ss.x += __shfl_xor_sync(0xffffffffu, ss.x, o); ss.y += __shfl_xor_sync(0xffffffffu, ss.y, o);
+      ss.z += __shfl_xor_sync(0xffffffffu, ss.z, o); ss.w += __shfl_xor_sync(0xffffffffu, ss.w, o);
+    }
+    float* row = out + b * out_ld;
+    for (int j = lane; j < D; j += 32) row[j] = __ldg(dense + b * dense_ld + j);
+    if (lane < k4) {
+      row[D + 4 * lane + 0] = 0.5f * (s.x * s.x - ss.x); row[D + 4 * lane + 1] = 0.5f * (s.y * s.y - ss.y);
+      row[D + 4 * lane + 2] = 0.5f * (s.z * s.z - ss.z); row[D + 4 * lane + 3] = 0.5f * (s.w * s.w - ss.w);
+    }
+    for (int j = D + k + lane; j < out_ld; j += 32) row[j] = 0.f;         // padding of the row (the tower reads 16-byte pieces)
+  }
+  if (bad && err_flag) *err_flag = 1;
+}
+
 // ------------------------------------------------------------------ shared front-end loader
 // Loads S samples' rows into registers: xv[s][i] = chunk q = lane + 32 i, xd[s] = dense[lane].
 template <int IDKIND, int NQ, int S>
@@ -521,6 +580,28 @@ extern "C" int ctrhot_gather_f32(const float* arena, const int64_t* row_off, int
   else                            { if (vec) LAUNCH(CTRHOT_IDS_F32, true); else LAUNCH(CTRHOT_IDS_F32, false); }
 #undef LAUNCH
   CTRHOT_LAUNCH_OK("ctrhot_gather_f32");
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_nfm_bi_f32(const float* arena, const int64_t* row_off, int F, int k,
+                                 const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
+                                 const float* dense, int64_t dense_ld, int D,
+                                 float* out, int64_t out_ld, int* err_flag, void* stream) {
+  if (!arena || !row_off || !ids || !out || F <= 0 || k <= 0 || B < 0 || D < 0) return CTRHOT_EARG;
+  if (D > 0 && !dense) return CTRHOT_EARG;
+  if (out_ld < (int64_t)D + k) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (k % 4 != 0 || ((k / 4) & (k / 4 - 1)) != 0 || k > 128 || !aligned16(arena)) return CTRHOT_ESHAPE;
+  if (B == 0) return CTRHOT_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = grid_for(B, 8);
+  if (ids_kind == CTRHOT_IDS_I32)
+    nfm_bi_kernel<CTRHOT_IDS_I32><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, dense, dense_ld, D, out, out_ld,
+                                                        err_flag);
+  else
+    nfm_bi_kernel<CTRHOT_IDS_F32><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, dense, dense_ld, D, out, out_ld,
+                                                        err_flag);
+  CTRHOT_LAUNCH_OK("ctrhot_nfm_bi_f32");
   return CTRHOT_OK;
 }
 

@@ -461,6 +461,73 @@ class DCN(_EmbedTowerModel):
         return out
 
 
+class NFM(_EmbedTowerModel):
+    """``sigmoid(Dense_1(DNN(BN([dense, BiInteraction(Embed(ids))]))))`` -- DL/model/nfm.py:15-34.
+    Bi-Interaction = 0.5 * ((sum_f e_f)^2 - sum_f e_f^2) over the [B, F, k] view of the embeddings (the view the reference's
+    own comment names; its EmbedLayer flattens).  Two launches: gather + pooling in registers
+    (ctrhot_nfm_bi_f32, the F rows never reach HBM), then the tower with the inference BatchNormalization folded into its
+    first layer and the final Dense(1) + sigmoid in its epilogue."""
+
+    def __init__(self, feature_columns, hidden_units, output_dim, activation="relu", dropout=0, embed_dim=8,
+                 precision="tf32", check_ids=True, device=None):
+        super().__init__(device)
+        self.dense_feature_columns, self.sparse_feature_columns = feature_columns
+        self.emb_layers = self.track(EmbedLayer(self.sparse_feature_columns, k=embed_dim, check_ids=False,
+                                                device=self.device))
+        self.dnn_layers = self.track(DNNLayer(hidden_units, output_dim, activation, dropout, precision=precision,
+                                              device=self.device))
+        self.check = check_ids
+        self._folded = None
+        self.emb_layers._err_flag = self.err_flag()
+
+    def build(self, input_shape):
+        from ..layer.base import init_ones, init_zeros
+        from ..layer.core import dense_params
+        n = len(self.dense_feature_columns) + self.emb_layers.k
+        self.bn_gamma = self.add_weight("bn/gamma", (n,), init_ones)
+        self.bn_beta = self.add_weight("bn/beta", (n,), init_zeros)
+        self.bn_mean = self.add_weight("bn/moving_mean", (n,), init_zeros)
+        self.bn_var = self.add_weight("bn/moving_variance", (n,), init_ones)
+        self._ensure_built(self.dnn_layers, n)
+        self.out_kernel, self.out_bias = dense_params(self, "output_layer", self.dnn_layers.output_dim, 1)
+
+    def _tower(self):
+        """BN (inference, eps 1e-3) folded into the first Dense; DNN's activation-free output layer and the model's final
+        Dense(1) are two linear maps in a row and are multiplied out: one [h_last, 1] layer."""
+        key = (self._version, self.dnn_layers._version)
+        if self._folded is None or self._folded[0] != key:
+            s = (self.bn_gamma / torch.sqrt(self.bn_var + 1e-3)).double()
+            t = self.bn_beta.double() - self.bn_mean.double() * s
+            ls = [dict(l) for l in self.dnn_layers.layer_dicts()]
+            k0 = ls[0]["kernel"].double()
+            ls[0]["bias"] = (ls[0]["bias"].double() + t @ k0).float().contiguous()
+            ls[0]["kernel"] = (s[:, None] * k0).float().contiguous()
+            wo, bo = ls[-1]["kernel"].double(), ls[-1]["bias"].double()
+            fk, fb = self.out_kernel.double(), self.out_bias.double()
+            ls[-1] = dict(ls[-1], kernel=(wo @ fk).float().contiguous(), bias=(bo @ fk + fb).float().contiguous())
+            self._folded = (key, ls)
+        return self._folded[1]
+
+    def call(self, inputs, training=None, mask=None):
+        E = self.emb_layers
+        D = len(self.dense_feature_columns)
+        dense, ids, _ = split_inputs(inputs, self.device, D)
+        require_cuda(dense, "NFM")
+        B = dense.shape[0]
+        n = D + E.k
+        x_ld = (n + 3) // 4 * 4
+        x = torch.empty((B, x_ld), dtype=torch.float32, device=self.device)
+        ids, kind, ids_ld = ids_arg(ids)
+        _lib.call("ctrhot_nfm_bi_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, B, ptr(dense),
+                  dense.stride(0), D, ptr(x), x_ld, ptr(self.err_flag()), stream_ptr())
+        stack = self.dnn_layers.stack
+        stack.set_layers(self._tower(), (self._version, self.dnn_layers._version, "nfm"))
+        out = stack.run(x[:, :n], x_ld, final_sigmoid=True)
+        if self.check:
+            self.check_ids()
+        return out
+
+
 class PNN(Model):
     """``DNN([flat(E), inner(E) and/or outer(E)])``, no sigmoid -- DL/model/pnn.py:14-53.  The product
     layers get the [B,F,k] view of the gathered buffer; the FGCNN branch is out of scope."""

@@ -12,7 +12,7 @@ import torch
 
 from oracle import ctr_oracle as O
 from oracle import synth as S
-from recommender_system_b200.model.criteo import DCN, DeepFM, WideDeep
+from recommender_system_b200.model.criteo import DCN, NFM, DeepFM, WideDeep
 from recommender_system_b200.utils import synth
 
 pytestmark = pytest.mark.gpu
@@ -191,6 +191,50 @@ def test_widedeep_one_launch(lib, B, k, hidden):
     bad = ids.copy()
     bad[B // 2, 5] = vocab[5]
     m.one_launch = True
+    with pytest.raises(IndexError):
+        m((dense, bad))
+
+
+@pytest.mark.parametrize("B,k,hidden,out_dim,prec", [(700, 8, [256, 128, 64], 1, "tf32"), (129, 16, [64, 32], 1, "tf32"),
+                                                     (1, 8, [32], 1, "fp32"), (333, 32, [40, 24], 3, "fp32"),
+                                                     (65536, 8, [256, 128, 64], 1, "tf32")])
+def test_nfm(lib, B, k, hidden, out_dim, prec):
+    """NFM: Bi-Interaction pooled in registers by the gather kernel, BatchNormalization folded into the
+    tower's first layer, DNN output layer and final Dense(1) multiplied out -- against the float64 oracle of nfm.py:24-34."""
+    rng = np.random.default_rng(B + k)
+    vocab = small_vocab(rng)
+    D, F = 13, 26
+    m = NFM(synth.criteo_feature_columns(vocab, k), hidden, out_dim, "relu", embed_dim=k, precision=prec)
+    m.build(None)
+    tables = [S.f32(rng.uniform(-0.5, 0.5, (v, k))) for v in vocab]
+    m.emb_layers.set_tables(tables)
+    n = D + k
+    bn = [S.f32(rng.normal(0, 0.2, n)), S.f32(rng.uniform(0.5, 1.5, n)), S.f32(rng.uniform(0.8, 1.2, n)), S.f32(rng.normal(0, 0.1, n))]
+    ws = []
+    dims = [n] + list(hidden) + [out_dim]
+    for i in range(len(dims) - 1):
+        lim = np.sqrt(6.0 / (dims[i] + dims[i + 1]))
+        ws += [S.f32(rng.uniform(-lim, lim, (dims[i], dims[i + 1]))), S.f32(rng.normal(0, 0.1, (dims[i + 1],)))]
+    m.dnn_layers.set_weights(ws)
+    fk, fb = S.f32(rng.normal(0, 0.5, (out_dim, 1))), S.f32(rng.normal(0, 0.1, (1,)))
+    m.set_weights({"bn/moving_mean": bn[0], "bn/moving_variance": bn[1], "bn/gamma": bn[2], "bn/beta": bn[3],
+                   "output_layer/kernel": fk, "output_layer/bias": fb})
+    dense, ids = synth.criteo_batch(B, vocab, seed=B)
+    if B > 4096:                                            # full size: oracle on a strided subset
+        sub = np.arange(0, B, 131)
+    else:
+        sub = np.arange(B)
+    pairs = [(ws[2 * i].astype(np.float64), ws[2 * i + 1].astype(np.float64)) for i in range(len(ws) // 2)]
+    want = O.nfm_model(synth.criteo_matrix(dense[sub], ids[sub]).astype(np.float64), [t.astype(np.float64) for t in tables],
+                       [b.astype(np.float64) for b in bn], pairs[:-1], pairs[-1],
+                       (fk.astype(np.float64), fb.astype(np.float64)))[:, 0]
+    got = npy(m((dense, ids)))[:, 0][sub]
+    if prec == "fp32":
+        assert np.max(np.abs(got - want)) <= 5e-6, np.max(np.abs(got - want))
+    else:
+        logit_close(got, want)
+    bad = ids.copy()
+    bad[B // 2, 7] = vocab[7]
     with pytest.raises(IndexError):
         m((dense, bad))
 

@@ -96,3 +96,15 @@ def test_embed_float_ids_truncate():
     t = np.arange(10.0).reshape(5, 2)
     out = O.embed_layer(np.array([[2.9]]), [t])
     np.testing.assert_array_equal(out, t[2:3])
+
+
+def test_bi_interaction_is_the_sum_of_pairwise_products():
+    """NFM's pooling (nfm.py:28) equals sum_{i<j} e_i * e_j elementwise -- the identity the kernel's sum / sum-of-squares
+    form relies on."""
+    rng = np.random.default_rng(0)
+    e = rng.normal(size=(5, 7, 4))
+    want = np.zeros((5, 4))
+    for i in range(7):
+        for j in range(i + 1, 7):
+            want += e[:, i] * e[:, j]
+    np.testing.assert_allclose(O.bi_interaction(e), want, rtol=1e-12, atol=1e-12)
