@@ -71,6 +71,15 @@ int ctrhot_nfm_bi_f32(const float* arena, const int64_t* row_off, int F, int k,
                       const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
                       const float* dense, int64_t dense_ld, int D,
                       float* out, int64_t out_ld, int* err_flag, void* stream);
+/* AFMLayer.call, DL/layer/interaction.py:322-351 (+ InteractionLayer :281-297, AttentionLayer :300-319), and AFM.call,
+ * DL/model/afm.py: out[b] = sigmoid^n_sigmoid(pool_p(e_i * e_j) . out_w + out_b) without building the [B, P, k] pair tensor.
+ * mode 0 'avg' (mean over the P pairs), 1 'att' (the reference's softmax runs over a size-1 axis: every weight is 1, the
+ * pooling is the SUM over pairs), 2 'max'.  out_w: device [k] (16-byte aligned), out_b: device [1]; n_sigmoid 1 for the layer,
+ * 2 for the model (it applies sigmoid again).  k as for ctrhot_nfm_bi_f32. */
+int ctrhot_afm_pool_f32(const float* arena, const int64_t* row_off, int F, int k,
+                        const void* ids, int ids_kind, int64_t ids_ld, int64_t B, int mode,
+                        const float* out_w, const float* out_b, int n_sigmoid, float* out, int* err_flag,
+                        void* stream);
 
 /* ---- R2  WideLayer.call, DL/layer/interaction.py:24-26 -----------------------
  * one-hot form: out[b] = w0 + sum_j dense[b,j]*w[dense_col[j]] + sum_f w[col_off[f]+ids[b,f]]

@@ -317,6 +317,32 @@ def nfm_model(inputs, tables, bn, dnn_hidden, dnn_out, final, act="relu", n_dens
     return sigmoid(y @ final[0] + final[1])
 
 
+def afm_layer(inputs, tables, mode, att_w=None, att_h=None, out=None, n_dense=13):
+    """AFMLayer.call, DL/layer/interaction.py:337-351, literally: InteractionLayer (:291-297) builds every e_i * e_j, i < j;
+    'avg' / 'max' pool over the pairs; 'att' runs AttentionLayer (:313-319): Dense(P, relu) and Dense(1) on the pairs, then
+    ``tf.nn.softmax`` over the LAST axis of the [B, P, 1] scores -- a size-1 axis, so every attention weight is exactly 1 and the
+    result is the sum over pairs.  att_w = (kernel [k,P], bias [P]), att_h = (kernel [P,1], bias [1]), out = (kernel [k,1], bias [1])."""
+    sparse_inputs = inputs[:, n_dense:n_dense + len(tables)]
+    e = embed_layer(sparse_inputs, tables, flatten=False)
+    F = e.shape[1]
+    pairs = np.stack([e[:, i] * e[:, j] for i in range(F) for j in range(i + 1, F)], axis=1)      # [B, P, k]
+    if mode == "avg":
+        x = pairs.mean(axis=1)
+    elif mode == "max":
+        x = pairs.max(axis=1)
+    else:
+        h = np.maximum(pairs @ att_w[0] + att_w[1], 0.0)                                         # [B, P, P]
+        sc = h @ att_h[0] + att_h[1]                                                              # [B, P, 1]
+        a = softmax_last(sc)                                                                      # over the size-1 axis
+        x = (np.transpose(a, (0, 2, 1)) @ pairs)[:, 0, :]
+    return sigmoid(x @ out[0] + out[1])
+
+
+def afm_model(inputs, tables, mode, att_w=None, att_h=None, out=None, n_dense=13):
+    """AFM.call, DL/model/afm.py: sigmoid of the layer's (already sigmoid) output."""
+    return sigmoid(afm_layer(inputs, tables, mode, att_w, att_h, out, n_dense))
+
+
 def pnn_model(inputs, tables, mode, dnn_hidden, dnn_out, outer_w=None, act="relu", n_dense=13):
     """PNN.call, DL/model/pnn.py:28-53 with the [B,F,k] view the product layers
     are specified on.  No sigmoid (:52-53)."""

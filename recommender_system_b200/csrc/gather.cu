@@ -231,6 +231,98 @@ nfm_bi_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_o
   if (bad && err_flag) *err_flag = 1;
 }
 
+// ------------------------------------------------------------------ AFM pooling over the pairwise products
+// AFMLayer.call, DL/layer/interaction.py:337-351: embed -> InteractionLayer (all e_i * e_j, i < j: [B, P, k]) -> pooling over the
+// P pairs -> Dense(1) -> sigmoid; AFM.call (DL/model/afm.py) applies a second sigmoid.  None of the [B, P, k] tensor is built:
+//   avg  mean over pairs                = (0.5 ((sum e)^2 - sum e^2)) / P
+//   att  AttentionLayer (:300-319) takes softmax over the LAST axis of a [B, P, 1] tensor, i.e. every weight is exactly 1:
+//        its output is the plain sum over pairs = 0.5 ((sum e)^2 - sum e^2), whatever its two Dense layers hold
+//   max  max over pairs of x_i x_j per column = max(product of the two largest, product of the two smallest values)
+// Same warp-per-sample gather as nfm_bi_kernel; the k pooled values meet out_w in registers, 4 bytes per sample leave.
+template <int IDKIND>
+__global__ void __launch_bounds__(256)
+afm_pool_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                const void* __restrict__ ids, int64_t ids_ld, int64_t B, int mode,
+                const float* __restrict__ out_w, const float* __restrict__ out_b, int n_sigmoid,
+                float* __restrict__ out, int* __restrict__ err_flag) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const int k4 = k >> 2, total = F * k4;
+  const int sh = 31 - __clz(k4);
+  const int c = lane & (k4 - 1);
+  const float inv_pairs = 2.0f / ((float)F * (float)(F - 1));
+  const float4 w = (lane < k4) ? __ldg(reinterpret_cast<const float4*>(out_w) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float bias = __ldg(out_b);
+  constexpr int U = 4;
+  const float INF = __int_as_float(0x7f800000);
+  bool bad = false;
+  for (int64_t b = warp; b < B; b += nwarps) {
+    float s[4] = {0.f, 0.f, 0.f, 0.f}, ss[4] = {0.f, 0.f, 0.f, 0.f};
+    float a1[4], a2[4], b1[4], b2[4];                  // two largest / two smallest values per column (mode max)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { a1[e] = -INF; a2[e] = -INF; b1[e] = INF; b2[e] = INF; }
+    for (int q0 = 0; q0 < total; q0 += 32 * U) {
+      float4 v[U];
+      bool have[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int q = q0 + 32 * u + lane;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        have[u] = q < total;
+        if (have[u]) {
+          const int f = q >> sh;
+          const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+          const int64_t r0 = __ldg(row_off + f), r1 = __ldg(row_off + f + 1);
+          if (id >= 0 && id < r1 - r0) v[u] = ldg_nc_f4(arena + (r0 + id) * k + c * 4);
+          else bad = true;                              // the row counts as zeros, like the gather's
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!have[u]) continue;
+        const float x[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          s[e] += x[e];
+          ss[e] = fmaf(x[e], x[e], ss[e]);
+          a2[e] = fmaxf(a2[e], fminf(a1[e], x[e])); a1[e] = fmaxf(a1[e], x[e]);
+          b2[e] = fminf(b2[e], fmaxf(b1[e], x[e])); b1[e] = fminf(b1[e], x[e]);
+        }
+      }
+    }
+    for (int o = 16; o >= k4; o >>= 1) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        s[e] += __shfl_xor_sync(0xffffffffu, s[e], o);
+        ss[e] += __shfl_xor_sync(0xffffffffu, ss[e], o);
+        const float oa1 = __shfl_xor_sync(0xffffffffu, a1[e], o), oa2 = __shfl_xor_sync(0xffffffffu, a2[e], o);
+        const float ob1 = __shfl_xor_sync(0xffffffffu, b1[e], o), ob2 = __shfl_xor_sync(0xffffffffu, b2[e], o);
+        a2[e] = fmaxf(fminf(a1[e], oa1), fmaxf(a2[e], oa2)); a1[e] = fmaxf(a1[e], oa1);
+        b2[e] = fminf(fmaxf(b1[e], ob1), fminf(b2[e], ob2)); b1[e] = fminf(b1[e], ob1);
+      }
+    }
+    float dot = 0.f;
+    if (lane < k4) {
+      const float ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float pooled;
+        if (mode == 2) pooled = fmaxf(a1[e] * a2[e], b1[e] * b2[e]);
+        else pooled = 0.5f * (s[e] * s[e] - ss[e]) * (mode == 0 ? inv_pairs : 1.0f);
+        dot = fmaf(pooled, ww[e], dot);
+      }
+    }
+    dot = warp_sum(dot);
+    if (lane == 0) {
+      float r = dot + bias;
+      for (int i = 0; i < n_sigmoid; ++i) r = 1.0f / (1.0f + expf(-r));
+      out[b] = r;
+    }
+  }
+  if (bad && err_flag) *err_flag = 1;
+}
+
 // ------------------------------------------------------------------ shared front-end loader
 // Loads S samples' rows into registers: xv[s][i] = chunk q = lane + 32 i, xd[s] = dense[lane].
 template <int IDKIND, int NQ, int S>
@@ -602,6 +694,27 @@ extern "C" int ctrhot_nfm_bi_f32(const float* arena, const int64_t* row_off, int
     nfm_bi_kernel<CTRHOT_IDS_F32><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, dense, dense_ld, D, out, out_ld,
                                                         err_flag);
   CTRHOT_LAUNCH_OK("ctrhot_nfm_bi_f32");
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_afm_pool_f32(const float* arena, const int64_t* row_off, int F, int k,
+                                   const void* ids, int ids_kind, int64_t ids_ld, int64_t B, int mode,
+                                   const float* out_w, const float* out_b, int n_sigmoid, float* out, int* err_flag,
+                                   void* stream) {
+  if (!arena || !row_off || !ids || !out || !out_w || !out_b || F < 2 || k <= 0 || B < 0) return CTRHOT_EARG;
+  if (mode < 0 || mode > 2 || n_sigmoid < 0 || n_sigmoid > 2) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (k % 4 != 0 || ((k / 4) & (k / 4 - 1)) != 0 || k > 128 || !aligned16(arena) || !aligned16(out_w)) return CTRHOT_ESHAPE;
+  if (B == 0) return CTRHOT_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = grid_for(B, 8);
+  if (ids_kind == CTRHOT_IDS_I32)
+    afm_pool_kernel<CTRHOT_IDS_I32><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, mode, out_w, out_b, n_sigmoid, out,
+                                                          err_flag);
+  else
+    afm_pool_kernel<CTRHOT_IDS_F32><<<grid, 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, mode, out_w, out_b, n_sigmoid, out,
+                                                          err_flag);
+  CTRHOT_LAUNCH_OK("ctrhot_afm_pool_f32");
   return CTRHOT_OK;
 }
 

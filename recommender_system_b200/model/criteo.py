@@ -528,6 +528,58 @@ class NFM(_EmbedTowerModel):
         return out
 
 
+class AFMLayer(Model):
+    """``AFMLayer(feature_columns, mode)`` -- DL/layer/interaction.py:322-351 with its InteractionLayer / AttentionLayer
+    (:281-319): sigmoid(Dense_1(pool over all e_i * e_j)), mode in 'avg' | 'max' | 'att'.  One launch (ctrhot_afm_pool_f32):
+    the [B, P, k] pair tensor is never built.  In 'att' mode the reference's softmax runs over a size-1 axis, so the attention
+    weights are all 1 and its two Dense layers (kept here as weights, for checkpoints) do not reach the output."""
+
+    def __init__(self, feature_columns, mode, n_sigmoid=1, check_ids=True, device=None):
+        super().__init__(device)
+        if mode not in ("avg", "max", "att"):
+            raise ValueError("mode must be 'avg', 'max' or 'att'")
+        self.dense_feature_columns, self.sparse_feature_columns = feature_columns
+        self.mode = mode
+        ks = {int(f.get("embed_dim", 8)) for f in self.sparse_feature_columns}
+        if len(ks) != 1:
+            raise ValueError("AFMLayer: all sparse features must share one embed_dim")
+        self.embed_layer = self.track(EmbedLayer(self.sparse_feature_columns, k=ks.pop(), check_ids=False, device=self.device))
+        self.n_sigmoid = n_sigmoid
+        self.check = check_ids
+        self.embed_layer._err_flag = self.err_flag()
+
+    def build(self, input_shape):
+        from ..layer.core import dense_params
+        F, k = self.embed_layer.F, self.embed_layer.k
+        P = F * (F - 1) // 2
+        if self.mode == "att":
+            self.att_w = dense_params(self, "attention_w", k, P)
+            self.att_h = dense_params(self, "attention_h", P, 1)
+        self.out_kernel, self.out_bias = dense_params(self, "output_layer", k, 1)
+
+    def call(self, inputs, training=None, mask=None):
+        E = self.embed_layer
+        D = len(self.dense_feature_columns)
+        _, ids, _ = split_inputs(inputs, self.device, D)
+        require_cuda(ids, "AFMLayer")
+        B = ids.shape[0]
+        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        ids, kind, ids_ld = ids_arg(ids)
+        _lib.call("ctrhot_afm_pool_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, B,
+                  {"avg": 0, "att": 1, "max": 2}[self.mode], ptr(self.out_kernel), ptr(self.out_bias), int(self.n_sigmoid),
+                  ptr(out), ptr(self.err_flag()), stream_ptr())
+        if self.check:
+            self.check_ids()
+        return out
+
+
+class AFM(AFMLayer):
+    """``AFM(feature_columns, mode)`` -- DL/model/afm.py: sigmoid(AFMLayer(x)), i.e. the sigmoid is applied twice."""
+
+    def __init__(self, feature_columns, mode, check_ids=True, device=None):
+        super().__init__(feature_columns, mode, n_sigmoid=2, check_ids=check_ids, device=device)
+
+
 class PNN(Model):
     """``DNN([flat(E), inner(E) and/or outer(E)])``, no sigmoid -- DL/model/pnn.py:14-53.  The product
     layers get the [B,F,k] view of the gathered buffer; the FGCNN branch is out of scope."""

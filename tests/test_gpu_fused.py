@@ -12,7 +12,7 @@ import torch
 
 from oracle import ctr_oracle as O
 from oracle import synth as S
-from recommender_system_b200.model.criteo import DCN, NFM, DeepFM, WideDeep
+from recommender_system_b200.model.criteo import AFM, DCN, NFM, AFMLayer, DeepFM, WideDeep
 from recommender_system_b200.utils import synth
 
 pytestmark = pytest.mark.gpu
@@ -235,6 +235,43 @@ def test_nfm(lib, B, k, hidden, out_dim, prec):
         logit_close(got, want)
     bad = ids.copy()
     bad[B // 2, 7] = vocab[7]
+    with pytest.raises(IndexError):
+        m((dense, bad))
+
+
+@pytest.mark.parametrize("mode", ["avg", "max", "att"])
+@pytest.mark.parametrize("B,F,k", [(1, 26, 8), (515, 26, 8), (300, 26, 16), (64, 2, 8), (100, 5, 32), (65536, 26, 8)])
+def test_afm(lib, mode, B, F, k):
+    """AFMLayer / AFM against the literal float64 restatement (all P pair products built, pooled,
+    attention included -- whose softmax over a size-1 axis makes every weight 1), <= 1e-5 relative on the logit."""
+    rng = np.random.default_rng(B + F + k)
+    vocab = small_vocab(rng, F)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": v, "embed_dim": k} for i, v in enumerate(vocab)]]
+    tables = [S.f32(rng.uniform(-1.0, 1.0, (v, k))) for v in vocab]
+    P = F * (F - 1) // 2
+    att_w = (S.f32(rng.normal(0, 0.3, (k, P))), S.f32(rng.normal(0, 0.1, (P,))))
+    att_h = (S.f32(rng.normal(0, 0.3, (P, 1))), S.f32(rng.normal(0, 0.1, (1,))))
+    out = (S.f32(rng.normal(0, 0.5, (k, 1))), S.f32(rng.normal(0, 0.1, (1,))))
+    dense = S.f32(rng.uniform(0, 1, (B, 13)))
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1).astype(np.int32)
+    sub = np.arange(0, B, 257) if B > 4096 else np.arange(B)
+    x64 = np.concatenate([dense[sub], ids[sub]], axis=1).astype(np.float64)
+    f64 = lambda t: tuple(a.astype(np.float64) for a in t)                                    # noqa: E731
+    for cls, ref in ((AFMLayer, O.afm_layer), (AFM, O.afm_model)):
+        m = cls(fc, mode)
+        m.build(None)
+        m.embed_layer.set_tables(tables)
+        w = {"output_layer/kernel": out[0], "output_layer/bias": out[1]}
+        if mode == "att":
+            w.update({"attention_w/kernel": att_w[0], "attention_w/bias": att_w[1],
+                      "attention_h/kernel": att_h[0], "attention_h/bias": att_h[1]})
+        m.set_weights(w)
+        want = ref(x64, [t.astype(np.float64) for t in tables], mode, f64(att_w), f64(att_h), f64(out))[:, 0]
+        got = npy(m((dense, ids)))[:, 0][sub]
+        assert np.max(np.abs(got - want)) <= 1e-5 * np.maximum(np.abs(want), 0.25).max(), (cls.__name__, np.max(np.abs(got - want)))
+    bad = ids.copy()
+    bad[B // 2, F - 1] = vocab[F - 1]
     with pytest.raises(IndexError):
         m((dense, bad))
 
