@@ -165,6 +165,43 @@ def secondary(dev, rank):
     out["gather_k16"] = {"metric": "EmbedLayer gather GB/s (ids + rows read + rows written)", "value": gbs, "ms": ms,
                          "hbm_frac": gbs / pk["hbm_gbs"], "rows": "64 B, uniform ids over 33.8 M rows (2.16 GB)"}
     del E, idb
+    # configs[0]: FM (k=8) on the bundled Criteo sample as the reference's fm.py loads it ([rows, 43 604] dense one-hot; the
+    # loader's output is the committed fixture tests/golden/criteo_cfg1.npz): the reference's dense form and the gather form on
+    # the GPU, beside the reference-form CPU pass (three GEMMs over the one-hot matrix, oracle/cpu_ref_torch.py)
+    fx = os.path.join(ROOT, "tests", "golden", "criteo_cfg1.npz")
+    if os.path.exists(fx):
+        from oracle import cpu_ref_torch as CR
+        from recommender_system_b200.model.criteo import FM
+        z = np.load(fx)
+        dn, idn, n1 = z["dense"], z["ids"], int(z["onehot_cols"])
+        rows = dn.shape[0]
+        X = np.zeros((rows, n1), np.float32)
+        X[:, :13] = dn
+        for f in range(26):
+            X[np.arange(rows), z["onehot_offsets"][f] + idn[:, f]] = 1.0
+        set_seed(0)
+        fm = FM(8, device=dev)
+        fm.build(X.shape)
+        Xd = torch.from_numpy(X).to(dev)
+        dd, idd = torch.from_numpy(dn.astype(np.float32)).to(dev), torch.from_numpy(idn.astype(np.int32)).to(dev)
+        offs = np.append(z["onehot_offsets"], n1)
+        fm(Xd); fm.call_sparse(dd, idd, offs)
+        ms_d = timeit(lambda: fm(Xd), 20, 3)
+        ms_s = timeit(lambda: fm.call_sparse(dd, idd, offs), 50, 5)
+        w0c, w1c, vc = [t.detach().cpu() for t in (fm.fm.w0, fm.fm.w1, fm.fm.v)]
+        Xc = torch.from_numpy(X)
+        torch.set_num_threads(os.cpu_count() or 1)
+        CR.fm_layer(Xc, w0c, w1c, vc)
+        t0 = time.perf_counter()
+        reps = 0
+        while time.perf_counter() - t0 < 2.0:
+            torch.sigmoid(CR.fm_layer(Xc, w0c, w1c, vc)); reps += 1
+        cpu_s = rows * reps / (time.perf_counter() - t0)
+        out["fm_cfg1"] = {"metric": "FM (k=8) forward samples/s on the bundled Criteo sample", "rows": rows, "onehot_cols": n1,
+                          "gpu_dense_form": rows / ms_d * 1e3, "gpu_gather_form": rows / ms_s * 1e3,
+                          "cpu_reference_form": cpu_s, "cpu_cores": os.cpu_count(),
+                          "note": "%d rows are a latency-sized batch: one launch each" % rows}
+        del fm, Xd
     # configs[2] (DCN, L=3 cross layers + 400-400-400 tower) and configs[1]'s Wide&Deep, same inputs as the main workload
     from recommender_system_b200.model.criteo import DCN, WideDeep
     fc = synth.criteo_feature_columns(synth.KAGGLE_VOCAB, k)
