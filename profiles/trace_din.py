@@ -40,3 +40,14 @@ for e in range(1, 7):
 print("stage spacing: mean cycles between consecutive events")
 for e in range(1, 7):
     print("  %-18s -> %-18s %7.0f" % (names[e - 1], names[e], np.mean(t[e, 10:n] - t[e - 1, 10:n])))
+# whole-launch time against (samples per CTA) x (period of CTA 0): how far the other CTAs / the start-up are from CTA 0's steady state
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(20):
+    L.call_gather(table, hist, cand, None)
+e1.record(); torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / 20
+per = (t[6, n] - t[6, 10]) / (n - 10)
+n_my = (B + 147) // 148
+print("call_gather (prep + attention kernels): %.1f us; %d samples per CTA x %.0f cycles = %.1f us at 1.965 GHz; CTA 0 first gather -> last sample done: %.0f cycles"
+      % (ms * 1e3, n_my, per, n_my * per / 1965.0, t[6, min(n_my, 128) - 1] - t[0, 0]))
