@@ -222,7 +222,7 @@ __host__ __device__ inline DinSmem din_smem(const DinShape& s, int nraw) {
   m.stage0 = o; o += (uint32_t)nraw * m.stage_bytes;
   m.al1 = o; o += (uint32_t)s.T * s.S1 * 4u;
   m.al2 = o; o += (uint32_t)s.T * s.S2 * 4u;
-  m.small = o; o += (uint32_t)(2 * s.N2p + 4 + DT_BM + 16 + 4 * DT_BM) * 4u; // b2 | w3 | b3 | P[128] | red[16] | part[512]
+  m.small = o; o += (uint32_t)(2 * s.N2p + 4 + DT_BM + 16 + 4 * DT_BM + 64) * 4u; // b2 | w3 | b3 | P[128] | red[16] | part[512] | row0[64]
   o = (o + 15u) & ~15u;
   m.bars = o; o += 8u * (2 * DT_NRAW + 12) + 16u;
   m.total = o;
@@ -264,6 +264,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
   float* f_small = reinterpret_cast<float*>(bp + mp.small);
   float* s_b2 = f_small; float* s_w3 = s_b2 + s.N2p; float* s_b3 = s_w3 + s.N2p;
   float* s_P = s_b3 + 4; float* s_red = s_P + DT_BM; float* s_part = s_red + 16;
+  float* s_row0 = s_part + 4 * DT_BM;            // table row 0: the key of every padding position (history id 0)
 
   if (tid == 0) {
     for (int i = 0; i < DT_NRAW; ++i) { mbar_init(full_raw(i), 256); mbar_init(raw_free(i), 128); }
@@ -284,6 +285,7 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
     float* a2 = reinterpret_cast<float*>(bp + mp.al2);
     for (int i = tid; i < s.T * s.S2; i += DT_THREADS) a2[i] = __ldg(p.packed + s.o_al2 + i);
     for (int i = tid; i < 2 * s.N2p + 4; i += DT_THREADS) f_small[i] = __ldg(p.packed + s.o_b2 + i);
+    for (int i = tid; i < s.K; i += DT_THREADS) s_row0[i] = (p.V > 0) ? __ldg(p.table + i) : 0.f;
   }
   fence_proxy_async_smem();
   if (warp == 12) { tmem_alloc(slot_addr, 512u); tmem_relinquish(); }
@@ -327,7 +329,10 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
         const int r = rsub + rpp * j;
         if (j < PPR && r < s.SR) {                       // rows >= SR are not stored: the stager writes zeros for them
           const int32_t id = ids_s[r];
-          const bool ok = r < T && id >= 0;
+          // id 0 = padding (masked: softmax weight exactly 0 unless the WHOLE history is padding): its key is table row 0,
+          // which epilogue 2 adds from smem in that one case -- not fetching it halves the gather of a half-padded batch and
+          // removes 16384 x ~50 reads of one 256-byte line (all served by a single L2 slice)
+          const bool ok = r < T && id > 0;
           cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
                      reinterpret_cast<const char*>(p.table) + (ok ? (uint64_t)(uint32_t)id * rowbytes : 0ull) + (uint32_t)c * 16u,
                      ok ? 16u : 0u);
@@ -544,6 +549,8 @@ din_tc_kernel(const __grid_constant__ DinParams p) {
       if (t < K) {
         float o = 0.f;
         for (int gg = 0; gg < G; ++gg) o += s_part[gg * K + t];
+        // every position masked: the softmax is uniform over T copies of table row 0 (whose rows were not fetched)
+        if (m == -4294967295.0f) o += s_row0[t];
         p.out[b * p.out_ld + t] = o;
       }
       if (lane == 0 && q4 == 0) DT_MARK(6, i);
