@@ -136,18 +136,39 @@ din_prep_kernel(const float* __restrict__ table, int64_t V, int K, const void* _
   __shared__ float sq[DP_S][64 + 1];
   const int tid = threadIdx.x;
   const int64_t b0 = (int64_t)blockIdx.x * DP_S;
-  for (int e = tid; e < DP_S * K; e += DP_T) {
-    const int s = e / K, c = e - s * K;
-    const int64_t b = b0 + s;
-    float v = 0.f;
-    if (b < B) {
-      const int64_t id = IdLoad<IDKIND>::at(cand_ids, b * cand_ld);
-      const bool ok = id >= 0 && id < V;
-      if (!ok && err_flag && c == 0) *err_flag = 1;
-      if (ok) v = ldg_nc_f1(table + id * K + c);
-      item_out[b * item_ld + c] = v;
+  // two batches of independent loads (all ids of this thread's elements, then all rows) instead of an id -> row round trip
+  // per element: the loop was 2 x DRAM latency x 8 iterations long
+  constexpr int PE = 8;                               // elements per thread and pass
+  for (int e0 = 0; e0 < DP_S * K; e0 += DP_T * PE) {
+    int64_t id[PE];
+    float v[PE];
+#pragma unroll
+    for (int i = 0; i < PE; ++i) {
+      const int e = e0 + tid + DP_T * i;
+      const int s = e / K;
+      id[i] = -1;
+      if (e < DP_S * K && b0 + s < B) id[i] = IdLoad<IDKIND>::at(cand_ids, (b0 + s) * cand_ld);
     }
-    sq[s][c] = v;
+#pragma unroll
+    for (int i = 0; i < PE; ++i) {
+      const int e = e0 + tid + DP_T * i;
+      const int s = e / K, c = e - s * K;
+      v[i] = 0.f;
+      if (e < DP_S * K && b0 + s < B) {
+        const bool ok = id[i] >= 0 && id[i] < V;
+        if (!ok && err_flag && c == 0) *err_flag = 1;
+        if (ok) v[i] = ldg_nc_f1(table + id[i] * K + c);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < PE; ++i) {
+      const int e = e0 + tid + DP_T * i;
+      const int s = e / K, c = e - s * K;
+      if (e < DP_S * K) {
+        if (b0 + s < B) item_out[(b0 + s) * item_ld + c] = v[i];
+        sq[s][c] = v[i];
+      }
+    }
   }
   __syncthreads();
   const int groups = DP_T / N1p;                      // column n = tid % N1p, sample group = tid / N1p
@@ -159,11 +180,16 @@ din_prep_kernel(const float* __restrict__ table, int64_t V, int K, const void* _
   const float bias = __ldg(b1 + n);
 #pragma unroll
   for (int i = 0; i < MAXS; ++i) acc[i] = bias;
-  for (int c = 0; c < K; ++c) {
-    const float w = __ldg(Wq + (size_t)c * N1p + n);
+  for (int c0 = 0; c0 < K; c0 += 4) {                  // K is 8, 16, 32 or 64: four weight loads in flight
+    float w[4];
 #pragma unroll
-    for (int i = 0; i < MAXS; ++i)
-      if (i < per) acc[i] = fmaf(sq[(g * per + i) % DP_S][c], w, acc[i]);
+    for (int u = 0; u < 4; ++u) w[u] = __ldg(Wq + (size_t)(c0 + u) * N1p + n);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int i = 0; i < MAXS; ++i)
+        if (i < per) acc[i] = fmaf(sq[(g * per + i) % DP_S][c0 + u], w[u], acc[i]);
+    }
   }
 #pragma unroll
   for (int i = 0; i < MAXS; ++i) {
