@@ -289,6 +289,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
   auto h_ready = [&](int l) { return misc + 8u * (FU_MAXL + l); };
   const uint32_t last_free = misc + 8u * (2 * FU_MAXL);
   const uint32_t slot_addr = last_free + 8u;
+  // hidden activations are handed to the next layer per 32-column chunk: its MMAs over chunk kc start when the four epilogue
+  // warps owning that chunk are done, while the other chunks of the same epilogue are still being converted
+  auto h_chunk = [&](int l, int c) { return slot_addr + 8u + 8u * (uint32_t)(l * 8 + c); };
   volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(base_ptr + (slot_addr - base));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -302,6 +305,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     for (int s = 0; s < FU_NAS; ++s) { mbar_init(a_full(s), 128); mbar_init(a_free(s), 1); }
     for (int s = 0; s < FU_NB; ++s) { mbar_init(full_b(s), 1); mbar_init(empty_b(s), C); }
     for (int l = 0; l < FU_MAXL; ++l) { mbar_init(d_full(l), 1); mbar_init(h_ready(l), 256); }
+    for (int l = 0; l < FU_MAXL; ++l) for (int c = 0; c < 8; ++c) mbar_init(h_chunk(l, c), 128);
     mbar_init(last_free, 256);
     mbar_fence_init();
   }
@@ -618,10 +622,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           const uint32_t idesc = make_idesc_tf32(FU_BM, (uint32_t)L.BN);
           const uint32_t d_t = tmem_base + (uint32_t)L.col;
           const uint32_t a_t = tmem_base + (uint32_t)p.L[l - 1].col;
-          FU_TWAIT(3, mbar_wait(h_ready(l - 1), hcount[l - 1] & 1u)); ++hcount[l - 1];
+          const uint32_t hph = hcount[l - 1] & 1u; ++hcount[l - 1];
           if (l == NL - 1 && lt > 0) FU_TWAIT(4, mbar_wait(last_free, (uint32_t)(lt - 1) & 1u));
-          tc_fence_after();
           for (int kc = 0; kc < L.KC; ++kc) {
+            FU_TWAIT(3, mbar_wait(h_chunk(l - 1, kc), hph));       // columns [32 kc, 32 kc + 32) of the previous layer are in TMEM
             FU_TWAIT(5, mbar_wait(full_b(sb), pb));
             tc_fence_after();
             const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
@@ -709,11 +713,12 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         const float* sb = fptr + mp.bias[l];
         const float* sa = fptr + mp.alpha[l];
         if (l < NL - 1) {
-          for (int c0 = half * 32; c0 < L.KP; c0 += 64)
+          for (int c0 = half * 32; c0 < L.KP; c0 += 64) {
             fu_hidden_chunk(t_lane + (uint32_t)(L.col + c0), sb, sa, c0, L.N, L.act == CTRHOT_ACT_RELU);
-          tmem_st_wait();
-          tc_fence_before();
-          mbar_arrive(h_ready(l));
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(h_chunk(l, c0 >> 5));
+          }
         } else if (p.h_out) {
           const bool h_vec8 = ((reinterpret_cast<uintptr_t>(p.h_out) & 31) == 0) && ((p.h_ld & 7) == 0);
           // single wide layer: the activations go to HBM (TF32-rounded, so the next layer's MMA reads them exactly)
@@ -1034,7 +1039,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   const bool wide = (ex.wide_w != nullptr);
   p.raw_stride = FU_TILE_BYTES + (wide ? 2048u : 0u);
   const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl, p.cc_n > 0, p.wide_w != nullptr);
-  const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1;
+  const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1 + 1 + 8 * FU_MAXL;   // + TMEM slot word, h_chunk
   size_t smem = 0;
   bool fits = false;
   // deepest rings that fit: weight stages first (each is a round trip to L2), then raw-row stages
