@@ -498,8 +498,8 @@ def main():
                   "bound": "hbm", "achieved": algo * B / (whole_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
                   "traffic": None, "ms": whole_ms, "peak_src": pk["src"]}
             if k == 16 and B == 65536 and args.vocab == "kaggle":
-                # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r01e_ncu_summary.md (ncu --set full)
-                hb["traffic"] = 75_985_664
+                # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r01f_raw_cfg2_ctr_fused.csv (ncu --set full)
+                hb["traffic"] = 74_196_992
             hb["frac"] = hb["achieved"] / hb["peak"]
             fm_flops = 2 * d * 21                        # FM = 2 * 429 * 21 (the split-TF32 extras are not counted)
             tn = {"kernel": hb["kernel"], "bound": "tensor", "achieved": (flops + fm_flops) * B / (whole_ms * 1e-3) / 1e12,
