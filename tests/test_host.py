@@ -11,7 +11,9 @@ from recommender_system_b200.layer import (Attention, CrossLayer, Dice, DNNLayer
                                            InnerProductLayer, OuterProductLayer, WideLayer)
 from recommender_system_b200.model.dcn import DCN
 from recommender_system_b200.model.deepFM import DeepFM
+from recommender_system_b200.model.afm import AFM, AFMLayer
 from recommender_system_b200.model.din import DIN
+from recommender_system_b200.model.nfm import NFM
 from recommender_system_b200.model.ffm import FFM
 from recommender_system_b200.model.fm import FM
 from recommender_system_b200.model.pnn import PNN
@@ -44,6 +46,9 @@ def test_constructor_signatures_start_like_the_reference():
                                          "dropout", "use_fgcnn"]
     assert _params(DIN.__init__)[:7] == ["feature_columns", "behavior_feature_list", "att_hidden_units",
                                          "dnn_hidden_units", "att_attention", "dnn_activation", "dnn_dropout"]
+    assert _params(NFM.__init__)[:5] == ["feature_columns", "hidden_units", "output_dim", "activation", "dropout"]  # nfm.py:16
+    assert _params(AFMLayer.__init__)[:2] == ["feature_columns", "mode"]                            # interaction.py:323
+    assert _params(AFM.__init__)[:2] == ["feature_columns", "mode"]                                 # afm.py
 
 
 def test_weight_names_and_shapes_follow_add_weight():
