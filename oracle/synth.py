@@ -327,6 +327,45 @@ def run_din(a):
                        (a["out_k"], a["out_b"]))
 
 
+def make_nfm(rng, k=8):
+    vocab = _vocab(rng)
+    n = D + k
+    a = {"inputs": _criteo_inputs(rng, vocab), "vocab": vocab.astype(np.int64),
+         "bn_mean": f32(rng.normal(0, 0.1, (n,))), "bn_var": f32(rng.uniform(0.5, 1.5, (n,))),
+         "bn_gamma": f32(rng.uniform(0.5, 1.5, (n,))), "bn_beta": f32(rng.normal(0, 0.1, (n,)))}
+    for i, t in enumerate(_tables(rng, vocab, k)):
+        a["table%d" % i] = t
+    _dense_stack(rng, [n, 32, 16, 3], "dnn", a)
+    a["final_k"] = f32(rng.uniform(-0.5, 0.5, (3, 1)))
+    a["final_b"] = f32(rng.normal(0, 0.1, (1,)))
+    return a
+
+
+def run_nfm(a):
+    hidden, out = _get_stack(a, "dnn")
+    return O.nfm_model(a["inputs"], _tables_of(a), (a["bn_mean"], a["bn_var"], a["bn_gamma"], a["bn_beta"]),
+                       hidden, out, (a["final_k"], a["final_b"]))
+
+
+def make_afm(rng, k=8):
+    vocab = _vocab(rng)
+    P = F * (F - 1) // 2
+    a = {"inputs": _criteo_inputs(rng, vocab), "vocab": vocab.astype(np.int64),
+         "att_wk": f32(rng.uniform(-0.3, 0.3, (k, P))), "att_wb": f32(rng.normal(0, 0.1, (P,))),
+         "att_hk": f32(rng.uniform(-0.3, 0.3, (P, 1))), "att_hb": f32(rng.normal(0, 0.1, (1,))),
+         "out_k": f32(rng.uniform(-0.5, 0.5, (k, 1))), "out_b": f32(rng.normal(0, 0.1, (1,)))}
+    for i, t in enumerate(_tables(rng, vocab, k)):
+        a["table%d" % i] = f32(t * 10.0)          # pair products of 0.05-scale rows would all be ~1e-3
+    return a
+
+
+def _run_afm(mode):
+    def run(a):
+        return O.afm_model(a["inputs"], _tables_of(a), mode, (a["att_wk"], a["att_wb"]), (a["att_hk"], a["att_hb"]),
+                           (a["out_k"], a["out_b"]))
+    return run
+
+
 CASES = {
     "embed": (make_embed, run_embed),
     "wide": (make_wide, run_wide),
@@ -344,6 +383,10 @@ CASES = {
     "dcn": (make_dcn, run_dcn),
     "pnn": (make_pnn, run_pnn),
     "din": (make_din, run_din),
+    "nfm": (make_nfm, run_nfm),
+    "afm_avg": (make_afm, _run_afm("avg")),
+    "afm_max": (make_afm, _run_afm("max")),
+    "afm_att": (make_afm, _run_afm("att")),
 }
 
 

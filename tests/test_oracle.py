@@ -1,5 +1,6 @@
-"""CPU: the oracle against its frozen golden vectors and against algebraic identities
-(SURVEY 8(c)): one-hot == gather, pair-sum identity, Cross with w=0, Attention with W=0 -> masked
+"""CPU: the oracle against the REFERENCE'S OWN outputs (tests/golden/ref_layers.npz: the reference's unmodified
+layer / model files executed under tests/golden/tf_shim by make_ref_golden.py), against its frozen vectors, and against
+algebraic identities: one-hot == gather, pair-sum identity, Cross with w=0, Attention with W=0 -> masked
 mean, all-padding row -> uniform softmax."""
 import numpy as np
 import pytest
@@ -9,16 +10,46 @@ from oracle import synth
 
 
 @pytest.mark.parametrize("name", list(synth.CASES))
-def test_oracle_matches_frozen_golden(golden, name):
-    arrays, expected = synth.load_case(golden, name)
+def test_oracle_matches_the_reference(golden_oracle, ref_golden, name):
+    """THE PIN: float64 oracle == the reference's own call() output on the same inputs and weights, <= 1e-12."""
+    arrays, _ = synth.load_case(golden_oracle, name)
+    got = synth.CASES[name][1](arrays)
+    want = ref_golden[name + "/expected"]
+    assert got.shape == want.shape
+    np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-12)
+
+
+@pytest.mark.parametrize("name", list(synth.CASES))
+def test_o32_matches_the_reference_in_float32(golden_oracle, ref_golden, name):
+    """The oracle run in float32 against the reference run in float32 (its own precision): same op order, so the two agree
+    to a few float32 roundings."""
+    arrays, _ = synth.load_case(golden_oracle, name)
+    a32 = {k: (v.astype(np.float32) if v.dtype == np.float64 else v) for k, v in arrays.items()}
+    got = synth.CASES[name][1](a32)
+    want = ref_golden[name + "/expected_f32"]
+    np.testing.assert_allclose(got, want, rtol=2e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("name,fn", [("fm", lambda a: O.fm_model(a["x"], a["w0"], a["w1"], a["v"])),
+                                     ("ffm", lambda a: O.ffm_model(a["inputs"], [int(v) for v in a["vocab"]], a["w0"],
+                                                                   a["w"], a["v"]))])
+def test_sigmoid_model_wrappers_match_the_reference(golden_oracle, ref_golden, name, fn):
+    """R11: FM.call (model/fm.py:19-23) and FFM.call (model/ffm.py:20-23)."""
+    arrays, _ = synth.load_case(golden_oracle, name)
+    np.testing.assert_allclose(fn(arrays), ref_golden[name + "_model/expected"], rtol=1e-12, atol=1e-12)
+
+
+@pytest.mark.parametrize("name", list(synth.CASES))
+def test_oracle_matches_frozen_golden(golden_oracle, name):
+    arrays, expected = synth.load_case(golden_oracle, name)
     got = synth.CASES[name][1](arrays)
     np.testing.assert_allclose(got, expected, rtol=1e-12, atol=1e-12)
 
 
 @pytest.mark.parametrize("name", list(synth.CASES))
-def test_o32_close_to_o64(golden, name):
+def test_o32_close_to_o64(golden_oracle, name):
     """O32 (fp32, reference op order) stays within the north_star tolerances of O64."""
-    arrays, expected = synth.load_case(golden, name)
+    arrays, expected = synth.load_case(golden_oracle, name)
     a32 = {k: (v.astype(np.float32) if v.dtype == np.float64 else v) for k, v in arrays.items()}
     got = synth.CASES[name][1](a32)
     np.testing.assert_allclose(got, expected, rtol=2e-5, atol=2e-6)
