@@ -35,3 +35,21 @@ for lab, sel in (("all CTAs mean", t.mean(0)), ("CTAs with most tiles, mean", t[
     print(lab)
     for n, v in zip(names, sel):
         print("   %-10s %10.0f %s" % (n, v, "" if n == "tiles" else "cyc (%.1f%% of total)" % (100 * v / sel[7])))
+
+buf2 = (ctypes.c_ulonglong * (256 * 8))()
+if hasattr(lib, "ctrhot_debug_fused_trace2") and lib.ctrhot_debug_fused_trace2(buf2) == 0:
+    t2 = np.frombuffer(buf2, dtype=np.uint64).reshape(256, 8).astype(np.float64)
+    t2 = t2[t2[:, 3] > 0]
+    n2 = ["stager: wait full_raw", "stager: wait a_free", "stager: wait last_free", "stager total", "gather: wait empty_raw",
+          "gather total", "epilogue: wait d_full", "epilogue total"]
+    m = t2.mean(0)
+    for i, n in enumerate(n2):
+        tot = m[3] if i < 4 else m[5] if i < 6 else m[7]
+        print("   %-24s %10.0f cyc (%.1f%% of its role)" % (n, m[i], 100 * m[i] / tot))
+tb = (ctypes.c_ulonglong * (256 * 4))()
+if lib.ctrhot_debug_fused_times(tb) == 0:
+    tt = np.frombuffer(tb, dtype=np.uint64).reshape(256, 4).astype(np.float64)
+    tt = tt[tt[:, 3] > 0]
+    print("CTA entry -> MMA loop begin %.1f us, MMA loop %.1f us, loop end -> exit %.1f us; first entry -> last exit %.1f us" % (
+        (tt[:, 1] - tt[:, 0]).mean() / 1e3, (tt[:, 2] - tt[:, 1]).mean() / 1e3, (tt[:, 3] - tt[:, 2]).mean() / 1e3,
+        (tt[:, 3].max() - tt[:, 0].min()) / 1e3))

@@ -248,12 +248,17 @@ __device__ __forceinline__ float fu_last_chunk(uint32_t taddr, const float* sb, 
 // tuning builds only (profiles/build_variants.py TRACE=1): cycles the MMA thread of every CTA spent waiting, per cause
 __device__ unsigned long long fu_trace[256][8];
 __device__ unsigned long long fu_times[256][4];     // globaltimer ns: CTA entry, MMA loop begin, MMA loop end, CTA exit
+// cycles other roles waited: [0] stager on full_raw, [1] stager on a_free, [2] stager on last_free, [3] stager total,
+// [4] gather on empty_raw, [5] gather total, [6] epilogue (warp 0) on d_full, [7] epilogue total
+__device__ unsigned long long fu_trace2[256][8];
+#define FU_T2(var, stmt) do { const long long t0_ = clock64(); stmt; var += clock64() - t0_; } while (0)
 __device__ __forceinline__ unsigned long long fu_now() {
   unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t;
 }
 #define FU_TWAIT(slot, stmt) do { const long long t0_ = clock64(); stmt; tw[slot] += clock64() - t0_; } while (0)
 #else
 #define FU_TWAIT(slot, stmt) do { stmt; } while (0)
+#define FU_T2(var, stmt) do { stmt; } while (0)
 #endif
 
 template <int NL, int C, bool WIDE>
@@ -392,9 +397,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     };
     int rs = 0; uint32_t rph = 0;                        // raw stage of the next issue and its phase
     constexpr bool wide_on = WIDE;
+    long long t2_wait = 0; (void)t2_wait;
     auto issue = [&](int g, const int32_t (&reg)[8]) {
       const int s = rs;
-      mbar_wait(empty_raw(s), rph ^ 1u);
+      FU_T2(t2_wait, mbar_wait(empty_raw(s), rph ^ 1u));
       if (++rs == p.nr) { rs = 0; rph ^= 1u; }
       const uint32_t dst = dst0 + (uint32_t)s * RAW_STRIDE;
       // wide tail of the stage: [128 rows][4 slots] floats; this thread owns a slot when its piece is the first of a field
@@ -462,6 +468,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       advance(ci);
     };
     static_assert(FU_PF == 3, "the loop below is unrolled for three id register sets");
+#ifdef FU_TRACE
+    const long long t2_begin = clock64();
+#endif
     int32_t ra[8], rb[8], rc[8];
     fetch(ra); fetch(rb); fetch(rc);
     for (int g = 0; g < total_chunks; g += FU_PF) {
@@ -469,6 +478,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       if (g + 1 < total_chunks) { issue(g + 1, rb); fetch(rb); }
       if (g + 2 < total_chunks) { issue(g + 2, rc); fetch(rc); }
     }
+#ifdef FU_TRACE
+    if (tg == 0 && blockIdx.x < 256) { fu_trace2[blockIdx.x][4] = t2_wait; fu_trace2[blockIdx.x][5] = clock64() - t2_begin; }
+#endif
   } else if (warp >= 12 && warp < 16) {
     // ================================================================ stager: smem chunk -> TMEM A ring (x | x_lo), q = sum x^2 sq_w
     const int row = tid - 384;                          // = TMEM lane; warps 12..15 own lane quarters 0..3
@@ -479,6 +491,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     uint32_t sa = 0, pa = 0;                            // A slot and its phase
     int sr = 0; uint32_t pr = 0;                        // raw stage and its phase
     const bool with_lo = (p.a_w == 64);
+    long long s2_raw = 0, s2_af = 0, s2_lf = 0; (void)s2_raw; (void)s2_af; (void)s2_lf;
+#ifdef FU_TRACE
+    const long long s2_begin = clock64();
+#endif
     for (int lt = 0; lt < n_my; ++lt) {
       float q = 0.f;
       float S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f;     // CUDA-core side products (DCN: x . w_l and x . final_w)
@@ -492,7 +508,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         }
       }
       for (int kc = 0; kc < KC1; ++kc) {
-        mbar_wait(full_raw(sr), pr);
+        FU_T2(s2_raw, mbar_wait(full_raw(sr), pr));
         const uint32_t raw = src0 + sr * RAW_STRIDE;
         const float* sq = fptr + mp.sq + kc * 32;
         float x[32], lo[32];
@@ -554,8 +570,8 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         mbar_arrive(empty_raw(sr));                     // the chunk is in registers: the gather may refill the stage
         if (++sr == p.nr) { sr = 0; pr ^= 1u; }
         // the A ring shares its TMEM columns with the later layers' accumulators: wait until the previous tile is done with them
-        if (NL > 1 && kc == 0 && lt > 0) mbar_wait(last_free, (uint32_t)(lt - 1) & 1u);
-        mbar_wait(a_free(sa), pa ^ 1u);
+        if (NL > 1 && kc == 0 && lt > 0) FU_T2(s2_lf, mbar_wait(last_free, (uint32_t)(lt - 1) & 1u));
+        FU_T2(s2_af, mbar_wait(a_free(sa), pa ^ 1u));
         tc_fence_after();
         tmem_st32(t_lane + sa * (uint32_t)p.a_w, x);
         if (with_lo) tmem_st32(t_lane + sa * 64u + 32u, lo);
@@ -565,13 +581,19 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         if (++sa == (uint32_t)n_as) { sa = 0; pa ^= 1u; }
       }
     }
+#ifdef FU_TRACE
+    if (row == 0 && blockIdx.x < 256) {
+      fu_trace2[blockIdx.x][0] = s2_raw; fu_trace2[blockIdx.x][1] = s2_af; fu_trace2[blockIdx.x][2] = s2_lf;
+      fu_trace2[blockIdx.x][3] = clock64() - s2_begin;
+    }
+#endif
   } else if (warp == 16) {
-    // ================================================================ MMA issuer
-    if (lane == 0) {
+    // ================================================================ MMA issuer: the warp stays converged, one elected lane issues
+    {
 #ifdef FU_TRACE
       long long tw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       const long long t_begin = clock64();
-      if (blockIdx.x < 256) fu_times[blockIdx.x][1] = fu_now();
+      if (lane == 0 && blockIdx.x < 256) fu_times[blockIdx.x][1] = fu_now();
 #endif
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0;     // A slot / W stage and their phases
       uint32_t hcount[FU_MAXL] = {0, 0, 0};
@@ -595,6 +617,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
             const uint64_t db2 = make_desc_sw128(b_base + sb * p.b_stage_bytes + (uint32_t)L.BNa * 128u);
             const uint64_t ds = make_desc_sw128(b_base + sb * p.b_stage_bytes + (uint32_t)L.BN * 128u);
+            if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               mma_tf32_ts(d_t, a_hi + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
@@ -611,10 +634,13 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             }
             mma_commit(a_free(sa));
             if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
+            }
+            __syncwarp();
             if (++sa == (uint32_t)p.n_as) { sa = 0; pa ^= 1u; }
             if (++sb == (uint32_t)p.nb) { sb = 0; pb ^= 1u; }
           }
-          mma_commit(d_full(0));
+          if (elect_one()) mma_commit(d_full(0));
+          __syncwarp();
         }
 #pragma unroll
         for (int l = 1; l < NL; ++l) {
@@ -629,26 +655,31 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             FU_TWAIT(5, mbar_wait(full_b(sb), pb));
             tc_fence_after();
             const uint64_t db = make_desc_sw128(b_base + sb * p.b_stage_bytes);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              mma_tf32_ts(d_t, a_t + (uint32_t)(kc * 32 + k * 8), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
-            if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
+              for (int k = 0; k < 4; ++k)
+                mma_tf32_ts(d_t, a_t + (uint32_t)(kc * 32 + k * 8), db + (uint64_t)(2 * k), idesc, (uint32_t)((kc | k) != 0));
+              if (C > 1) mma_commit_mc(empty_b(sb), cmask); else mma_commit(empty_b(sb));
+            }
+            __syncwarp();
             if (++sb == (uint32_t)p.nb) { sb = 0; pb ^= 1u; }
           }
-          mma_commit(d_full(l));
+          if (elect_one()) mma_commit(d_full(l));
+          __syncwarp();
         }
       }
 #ifdef FU_TRACE
       tw[7] = clock64() - t_begin;
       tw[6] = n_my;
-      if (blockIdx.x < 256) fu_times[blockIdx.x][2] = fu_now();
-      if (blockIdx.x < 256) for (int i = 0; i < 8; ++i) fu_trace[blockIdx.x][i] = (unsigned long long)tw[i];
+      if (lane == 0 && blockIdx.x < 256) fu_times[blockIdx.x][2] = fu_now();
+      if (lane == 0 && blockIdx.x < 256) for (int i = 0; i < 8; ++i) fu_trace[blockIdx.x][i] = (unsigned long long)tw[i];
 #endif
     }
     __syncwarp();
   } else if (warp == 17) {
     // ================================================================ W producer (bulk async copies, cluster multicast)
-    if (lane == 0) {
+    // (converged warp, one elected lane issues: a bulk copy under a divergent `lane == 0` branch compiles to a waterfall loop)
+    {
       uint32_t sb = 0, pb = 0;
       for (int lt = 0; lt < n_my; ++lt) {
 #pragma unroll
@@ -659,11 +690,14 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           const uint32_t piece = bytes / C;
           for (int kc = 0; kc < L.KC; ++kc) {
             mbar_wait(empty_b(sb), pb ^ 1u);
-            mbar_arrive_expect_tx(full_b(sb), bytes);
             const uint8_t* src = reinterpret_cast<const uint8_t*>(L.Wp) + (size_t)kc * stride + (size_t)crank * piece;
             const uint32_t dst = b_base + sb * p.b_stage_bytes + crank * piece;
-            if (C > 1) bulk_g2s_mc(dst, src, piece, full_b(sb), cmask);
-            else bulk_g2s(dst, src, bytes, full_b(sb));
+            if (elect_one()) {
+              mbar_arrive_expect_tx(full_b(sb), bytes);
+              if (C > 1) bulk_g2s_mc(dst, src, piece, full_b(sb), cmask);
+              else bulk_g2s(dst, src, bytes, full_b(sb));
+            }
+            __syncwarp();
             if (++sb == (uint32_t)p.nb) { sb = 0; pb ^= 1u; }
           }
         }
@@ -676,13 +710,17 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     const int row = q4 * 32 + lane;
     const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
     uint32_t dcount[FU_MAXL] = {0, 0, 0};
+    long long e2_wait = 0; (void)e2_wait;
+#ifdef FU_TRACE
+    const long long e2_begin = clock64();
+#endif
     for (int lt = 0; lt < n_my; ++lt) {
       const int64_t gm = (((int64_t)cid + (int64_t)lt * ncl) * C + crank) * FU_BM + row;
       float side = 0.f;
 #pragma unroll
       for (int l = 0; l < NL; ++l) {
         const FuLayer& L = p.L[l];
-        mbar_wait(d_full(l), dcount[l] & 1u); ++dcount[l];
+        FU_T2(e2_wait, mbar_wait(d_full(l), dcount[l] & 1u)); ++dcount[l];
         tc_fence_after();
         if (l == 0 && half == 0 && p.cc_n > 0) {
           side = fptr[mp.q + (lt & 1) * FU_BM + row];
@@ -788,6 +826,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         }
       }
     }
+#ifdef FU_TRACE
+    if (tid == 0 && blockIdx.x < 256) { fu_trace2[blockIdx.x][6] = e2_wait; fu_trace2[blockIdx.x][7] = clock64() - e2_begin; }
+#endif
   }
   tc_fence_before();
   __syncthreads();
@@ -857,6 +898,9 @@ extern "C" int ctrhot_fused_pack(const float* W1, const float* side, int n, int 
 #ifdef FU_TRACE
 extern "C" int ctrhot_debug_fused_trace(unsigned long long* h_out) {
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
+}
+extern "C" int ctrhot_debug_fused_trace2(unsigned long long* h_out) {
+  return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace2, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
 }
 extern "C" int ctrhot_debug_fused_times(unsigned long long* h_out) {
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_times, sizeof(unsigned long long) * 256 * 4) == cudaSuccess ? 0 : -3;

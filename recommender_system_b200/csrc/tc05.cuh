@@ -60,6 +60,17 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+// One lane of a CONVERGED warp (elect.sync).  tcgen05.mma / commit take their operands from uniform registers: issued under
+// this predicate by a warp that runs the issue loop with all 32 lanes, each compiles to ONE UTCHMMA.  Issued from a divergent
+// `if (lane == 0)` branch the compiler cannot prove uniformity and wraps every instruction in an ELECT / BRA.U.ANY waterfall
+// loop (twice when the accumulate flag is a run-time predicate): measured 118 -> 72 cycles per narrow MMA
+// (profiles/micro/mma_pair.cu).  The same lane is elected every time, so commits track the MMAs issued before them.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xFFFFFFFF;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // D[tmem] (+)= A[smem] * B[smem]^T, TF32 inputs, fp32 accumulate; one thread issues for the CTA
 __device__ __forceinline__ void mma_tf32_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                             uint32_t accumulate) {
