@@ -155,6 +155,19 @@ typedef struct {
 int ctrhot_mlp_f32(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_desc* h_layers,
                    int n_layers, float* out, int64_t out_ld, void* workspace,
                    int64_t workspace_bytes, void* stream);
+/* ctrhot_mlp_f32 without any allocation, by the caller or by the library.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arithmetic, same kernels and same results as ctrhot_mlp_f32; the hidden
+ * activations ping-pong through a file-scope device array of CTRHOT_MLP_STATIC_SCRATCH_BYTES (16 MiB) that every GPU which
+ * loads the library holds until exit.  Needs 2 * M * round32(widest hidden layer) * 4 bytes of it: more returns
+ * CTRHOT_ESHAPE with the sizes in ctrhot_last_cuda_error() (e.g. 8 192 rows at 256 hidden units fit exactly).  Calls no
+ * cudaMalloc / cudaFree / allocating library routine; the first call on each device resolves the array's device address
+ * (cudaGetSymbolAddress) -- make that call outside a graph capture.  ALL CALLS SHARE THE ONE ARRAY PER DEVICE: calls that
+ * can overlap on the GPU (different streams, no ordering between them) race on it -- serialise them.  Nothing in the array
+ * needs clearing between calls: every element is written by layer l before layer l + 1 reads it. */
+#define CTRHOT_MLP_STATIC_SCRATCH_BYTES (16 << 20)
+int ctrhot_mlp_f32_static(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_desc* h_layers,
+                          int n_layers, float* out, int64_t out_ld, void* stream);
 /* tcgen05/TMEM TF32 path (fp32 in HBM, TF32 multiply, fp32 accumulate) */
 int64_t ctrhot_mlp_pack_bytes(int in_dim, int out_dim);
 int ctrhot_mlp_pack(const float* weight, int in_dim, int out_dim, void* packed, void* stream);

@@ -11,6 +11,9 @@ void set_cuda_error(cudaError_t e, const char* where) {
   snprintf(g_err, sizeof(g_err), "%s: %s (%s)", where, cudaGetErrorString(e), cudaGetErrorName(e));
 }
 
+// same thread-local text, for a refusal that is not a CUDA error (read back through ctrhot_last_cuda_error())
+void set_error_text(const char* text) { snprintf(g_err, sizeof(g_err), "%s", text); }
+
 // ---------------------------------------------------------------- K8 shard route / pack / unpack
 // Row-sharded tables: owner(id) = id mod G, local row = id div G  (SURVEY 8(e)).
 // route: counting sort of the B*F (sample, field) slots by owner, stable inside an owner.

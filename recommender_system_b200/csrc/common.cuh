@@ -11,6 +11,7 @@ constexpr int kNumSMs = 148;   // B200
 
 // host: record + translate CUDA errors (thread-local text, no global mutable state shared across threads)
 void set_cuda_error(cudaError_t e, const char* where);
+void set_error_text(const char* text);
 #define CTRHOT_CUDA_OK(expr, where)                         \
   do {                                                      \
     cudaError_t _e = (expr);                                \
