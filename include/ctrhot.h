@@ -250,7 +250,9 @@ int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off, int F, int
 /* WideDeep.call in ONE launch: as ctrhot_ctr_tower_tf32 (no dense columns in the deep input), with the wide logit
  * w0 + sum_j dense[m, j] dw[j] + sum_f w[wide_off[f] + ids[m, f]] formed inside the kernel: the gather warps fetch the 4-byte
  * weights next to the embedding rows, the stager threads add them up per row; out = (sigmoid of) scale * (tower + wide).
- * wide_off: device int64 [F]; h_dw: HOST float [wide_D <= 16]; k a power of two >= 8. */
+ * wide_off: device int64 [F + 1] -- field f's one-hot block is [wide_off[f], wide_off[f+1]); an id at or beyond that width
+ * contributes 0 (a get_dummies column that does not exist, dataset.py:53-58), exactly as ctrhot_wide_onehot_f32 does;
+ * h_dw: HOST float [wide_D <= 16]; k a power of two >= 8. */
 int ctrhot_widedeep_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
                                const void* ids, int ids_kind, int64_t ids_ld, int64_t M,
                                const ctrhot_dense_desc* h_layers, int n_layers,

@@ -162,7 +162,8 @@ __host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries
   m.q = o; o += 2 * FU_BM;
   m.part = o; o += 2 * FU_BM;
   m.ccw = o; if (cc) o += KC1 * 32 * 4;
-  m.wb = o; if (wide) o += (2 * F + 3) / 4 * 4;     // per field: address of its block of the wide weight vector
+  m.wb = o; if (wide) o += (3 * F + 3) / 4 * 4;     // per field: address of its block of the wide weight vector (8 B) x F,
+                                                    // then its one-hot width (4 B) x F
   m.total = o;
   return m;
 }
@@ -329,7 +330,14 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     if (p.cc_n > 0) for (int i = tid; i < KC1 * 32 * 4; i += FU_THREADS) fptr[mp.ccw + i] = __ldg(p.cc_w + i);
     if (WIDE) {
       const float** s_wb = reinterpret_cast<const float**>(fptr + mp.wb);
-      for (int i = tid; i < p.F; i += FU_THREADS) s_wb[i] = p.wide_w + p.wide_off[i];
+      uint32_t* s_ww = reinterpret_cast<uint32_t*>(fptr + mp.wb + 2 * p.F);
+      for (int i = tid; i < p.F; i += FU_THREADS) {
+        s_wb[i] = p.wide_w + p.wide_off[i];
+        // the one-hot block of a field may be narrower than its embedding table (get_dummies keeps only the labels it saw,
+        // dataset.py:53-58): an id in [width, vocab) has no column, i.e. contributes 0 -- as wide_onehot_kernel does
+        const int64_t wd = p.wide_off[i + 1] - p.wide_off[i];
+        s_ww[i] = wd < 0 ? 0u : (wd > 0x7FFFFFFF ? 0x7FFFFFFFu : (uint32_t)wd);
+      }
     }
 #pragma unroll
     for (int l = 0; l < NL; ++l) {
@@ -407,8 +415,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       bool wide_here = false;
       uint32_t wdst = 0;
       const float* wbase = nullptr;
+      uint32_t wwidth = 0;
       if (wide_on && ci.f < p.F && ci.part == 0) {
         wide_here = true;
+        wwidth = reinterpret_cast<const uint32_t*>(fptr + mp.wb + 2 * p.F)[ci.f];
         wdst = r_base + (uint32_t)s * RAW_STRIDE + FU_TILE_BYTES + (uint32_t)rsub * 16u + (k4 < 8 ? (uint32_t)(c / k4) * 4u : 0u);
         wbase = reinterpret_cast<const float* const*>(fptr + mp.wb)[ci.f];
       }
@@ -437,7 +447,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             const bool ok = id < nrow;
             bad |= !ok;
             cp_async16(dst + 2048u * i, ok ? (const void*)(fb + (uint64_t)id * rowbytes) : (const void*)p.arena, ok ? 16u : 0u);
-            if (wide_here) cp_async4(wdst + 256u * i, ok ? (const void*)(wbase + id) : (const void*)p.arena, ok ? 4u : 0u);
+            if (wide_here) {
+              const bool wok = ok && id < wwidth;
+              cp_async4(wdst + 256u * i, wok ? (const void*)(wbase + id) : (const void*)p.arena, wok ? 4u : 0u);
+            }
           }
         } else {
 #pragma unroll
@@ -446,7 +459,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             const bool ok = id < nrow;
             bad |= !ok;
             cp_async16(dst + 2048u * i, ok ? (const void*)(fb + (uint64_t)id * rowbytes) : (const void*)p.arena, ok ? 16u : 0u);
-            if (wide_here) cp_async4(wdst + 256u * i, ok ? (const void*)(wbase + id) : (const void*)p.arena, ok ? 4u : 0u);
+            if (wide_here) {
+              const bool wok = ok && id < wwidth;
+              cp_async4(wdst + 256u * i, wok ? (const void*)(wbase + id) : (const void*)p.arena, wok ? 4u : 0u);
+            }
           }
         }
         if (bad && p.err_flag) *p.err_flag = 1;
@@ -1186,7 +1202,8 @@ extern "C" int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off,
 // ctrhot_ctr_tower_tf32, and the wide logit formed inside the same kernel -- the gather warps fetch w[wide_off[f] + id_f] next to
 // the embedding rows (the ids are in their registers anyway), the stager threads add them and the dense term per row:
 //   out[m] = (sigmoid of) scale * (tower(m) + w0 + sum_j dense[m, j] dw[j] + sum_f w[wide_off[f] + ids[m, f]])
-// wide_off: DEVICE int64 [F]; dw: HOST float [wide_D <= 16] (the reference's wide input carries the dense block twice: pass the sum
+// wide_off: DEVICE int64 [F + 1] (field f's one-hot block is [wide_off[f], wide_off[f+1]); an id at or beyond its width adds 0,
+// like a get_dummies column that does not exist); dw: HOST float [wide_D <= 16] (the reference's wide input carries the dense block twice: pass the sum
 // of the two weight blocks).  k must be a power of two >= 8.
 extern "C" int ctrhot_widedeep_fused_tf32(const float* arena, const int64_t* row_off, int F, int k,
                                           const void* ids, int ids_kind, int64_t ids_ld, int64_t M,

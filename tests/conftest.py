@@ -8,6 +8,16 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+PARITY_LOG = []       # filled by tests/test_gpu_parity.py::close_rel: norm-wise (asserted) and element-wise relative errors
+
+
+def pytest_sessionfinish(session, exitstatus):
+    if PARITY_LOG and os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+        import json
+        with open(os.path.join(ROOT, "gpurun_out", "parity_relative_errors.json"), "w") as f:
+            json.dump(PARITY_LOG, f, indent=1)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 

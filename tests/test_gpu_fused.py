@@ -295,3 +295,44 @@ def test_whole_kernel_full_size_properties(lib):
     sub = np.arange(0, 65536, 97)
     want = deepfm_oracle(m, dense[sub], ids[sub], ws)[:, 0]
     logit_close(got[sub], want)
+
+
+def test_widedeep_onehot_narrower_than_vocab(lib):
+    """WideDeep built with onehot_width[f] < feat_onehot_dim[f] (get_dummies keeps only the labels it saw,
+    dataset.py:53-58).  An id in [width, vocab) has an embedding row but no one-hot column: it must add 0 to the wide logit on
+    BOTH paths (the one-launch kernel used to add the next field's weight, and read past the end of w for the last field)."""
+    rng = np.random.default_rng(77)
+    B, k, D, F, hidden = 700, 16, 13, 26, [64, 32]
+    vocab = small_vocab(rng)
+    widths = [max(1, v - int(rng.integers(0, 3))) for v in vocab]
+    widths[F - 1] = max(1, vocab[F - 1] - 2)                       # the last field: the old code read beyond the weight vector
+    m = WideDeep(synth.criteo_feature_columns(vocab, k), hidden, 1, "relu", embed_dim=k, precision="tf32", onehot_width=widths)
+    m.build(None)
+    tables = [S.f32(rng.uniform(-0.5, 0.5, (v, k))) for v in vocab]
+    m.embed_layer.set_tables(tables)
+    n_wide = 2 * D + sum(widths)
+    w0, w = S.f32(rng.normal(0, 0.1, (1,))), S.f32(rng.normal(0, 1.0, (n_wide, 1)))
+    m.wide.set_weights([w0, w])
+    ws = []
+    dims = [F * k] + hidden + [1]
+    for i in range(len(dims) - 1):
+        lim = np.sqrt(6.0 / (dims[i] + dims[i + 1]))
+        ws += [S.f32(rng.uniform(-lim, lim, (dims[i], dims[i + 1]))), S.f32(rng.normal(0, 0.1, (dims[i + 1],)))]
+    m.deep.set_weights(ws)
+    dense, ids = synth.criteo_batch(B, vocab, seed=78)
+    for f in range(F):                                             # make sure every field has ids in [width, vocab)
+        if widths[f] < vocab[f]:
+            ids[f::F, f][: 8] = vocab[f] - 1
+    assert any((ids[:, f] >= widths[f]).any() for f in range(F))
+    off = 2 * D + np.concatenate([[0], np.cumsum(widths)])
+    w64_ = w[:, 0].astype(np.float64)
+    wide = w0.astype(np.float64)[0] + dense.astype(np.float64) @ (w64_[:D] + w64_[D:2 * D])
+    for f in range(F):
+        inside = ids[:, f] < widths[f]
+        wide = wide + np.where(inside, w64_[off[f] + np.minimum(ids[:, f], widths[f] - 1)], 0.0)
+    pairs = [(ws[2 * i].astype(np.float64), ws[2 * i + 1].astype(np.float64)) for i in range(len(ws) // 2)]
+    deep = O.dnn_layer(O.embed_layer(ids, [t.astype(np.float64) for t in tables]), pairs[:-1], pairs[-1], "relu")[:, 0]
+    want = O.sigmoid(0.5 * (wide + deep))
+    for one in (True, False):
+        m.one_launch = one
+        logit_close(npy(m((dense, ids)))[:, 0], want)

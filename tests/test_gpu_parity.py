@@ -29,10 +29,19 @@ def npy(t):
 
 def close_rel(got, want, rel=REL):
     # relative to each element, floored at the RMS of the output: fp32 round-off scales with the operands of
-    # a dot product (whose size the output's RMS tracks), not with a result that happens to cancel to ~0
+    # a dot product (whose size the output's RMS tracks), not with a result that happens to cancel to ~0.
+    # This NORM-WISE figure is what is asserted; the plain element-wise one is recorded beside it (conftest.PARITY_LOG ->
+    # gpurun_out/parity_relative_errors.json) so the relaxation of north_star's "1e-5 relative" stays visible.
+    import os
+    from conftest import PARITY_LOG
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
     scale = np.maximum(np.abs(want), np.sqrt(np.mean(np.square(want))) + 1e-30)
     err = np.max(np.abs(got - want) / scale)
-    assert err <= rel, "max rel err %.3g > %.3g" % (err, rel)
+    nz = np.abs(want) > 0
+    elementwise = float(np.max(np.abs(got - want)[nz] / np.abs(want)[nz])) if nz.any() else 0.0
+    PARITY_LOG.append({"test": os.environ.get("PYTEST_CURRENT_TEST", "?").split(" ")[0], "n": int(want.size),
+                       "normwise_rel_err": float(err), "elementwise_rel_err": elementwise, "bound": float(rel)})
+    assert err <= rel, "max rel err %.3g > %.3g (element-wise %.3g)" % (err, rel, elementwise)
 
 
 def fc_from(vocab, k):
