@@ -43,7 +43,7 @@ typedef enum {
   CTRHOT_EID = -4          /* an embedding id was out of range */
 } ctrhot_status;
 
-enum { CTRHOT_IDS_I32 = 0, CTRHOT_IDS_F32 = 1 };
+enum { CTRHOT_IDS_I32 = 0, CTRHOT_IDS_F32 = 1, CTRHOT_IDS_PACKED = 2 /* transport records, see ctrhot_rows_* */ };
 enum { CTRHOT_ACT_NONE = 0, CTRHOT_ACT_RELU = 1, CTRHOT_ACT_PRELU = 2, CTRHOT_ACT_DICE = 3,
        CTRHOT_ACT_SIGMOID = 4, CTRHOT_ACT_TANH = 5 };
 
@@ -225,6 +225,30 @@ int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int
                           const ctrhot_dense_desc* h_layers, int n_layers,
                           const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                           int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
+/* ---- transport records: the copy on the left of the path (the reference passes one float64 [B, 39]
+ * matrix, DL/utils/dataset.py:61, DL/model/deepFM.py:24 -- 312 B per sample; the int32 fast path above takes 156 B) --------
+ *   record = [ dense: D x float32 (bit-exact) | id_f in width[f] little-endian bytes, f = 0..F-1 | zero pad to 4 bytes ]
+ *   width[f] = 1 / 2 / 3 / 4 bytes for feat_onehot_dim <= 2^8 / 2^16 / 2^24 / 2^31      (104 B on Criteo-Kaggle cardinalities)
+ * ctrhot_rows_layout   : HOST.  h_vocab [F] -> h_desc [F] = (byte offset in the record) | width << 16; returns the record
+ *                        size in bytes (> 0, a multiple of 4) or a negative status.  Dense block at byte 0.
+ * ctrhot_rows_pack_host: HOST, no GPU work.  (dense [B, D], ids int32 [B, F]) -> records, n_threads host threads (<= 0: all).
+ *                        CTRHOT_EID if an id does not fit its width (that id is stored as 0, never truncated silently).
+ * ctrhot_rows_unpack   : DEVICE records -> dense float32 [M, dense_ld], ids int32 [M, ids_ld]; desc = DEVICE int32 [F].
+ *                        The generic way into every (dense, ids) entry point: one extra launch.
+ * ctrhot_ctr_fused_packed_tf32: ctrhot_ctr_fused_tf32 reading the records directly -- its gather warps decode the ids,
+ *                        the dense columns are read in place: ONE host-to-device copy per batch, no unpack pass.
+ *                        records 16-byte aligned, rec_bytes % 4 == 0, pack_desc = DEVICE int32 [F]. */
+int ctrhot_rows_layout(const int64_t* h_vocab, int F, int D, int32_t* h_desc);
+int ctrhot_rows_pack_host(const float* h_dense, int64_t dense_ld, const int32_t* h_ids, int64_t ids_ld, int64_t B,
+                          const int32_t* h_desc, int F, int D, int64_t rec_bytes, void* h_records, int n_threads);
+int ctrhot_rows_unpack(const void* records, int64_t rec_bytes, const int32_t* desc, int F, int dense_off, int D,
+                       int64_t M, float* dense, int64_t dense_ld, int32_t* ids, int64_t ids_ld, void* stream);
+int ctrhot_ctr_fused_packed_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                 const void* records, int64_t rec_bytes, const int32_t* pack_desc,
+                                 int dense_off, int D, int64_t M,
+                                 const ctrhot_dense_desc* h_layers, int n_layers,
+                                 const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                                 int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
 /* The same kernel over ROW-SHARDED tables (8(e), config 5): arenas = HOST array of G device pointers (arena of owner g;
  * this rank's own at index `rank`, the peers' mapped by ctrhot_peer_open), row_off = device int64 [G, F+1], ids = GLOBAL
  * row numbers: row id of field f is read at arenas[id mod G] + (row_off[id mod G][f] + id div G) * k -- the gather warps

@@ -64,6 +64,8 @@ struct FuParams {
                                                            // = x_ld / 4 when the 'table' is an activation matrix, rows mode)
   int G; const float* peer[FU_MAXG];                       // row-sharded tables (cfg 5): owner = id mod G, arenas mapped over NVLink;
                                                            // row_off is then [G, F+1].  G = 1: peer[0] = arena
+  const int32_t* pack_desc;                                // CTRHOT_IDS_PACKED: per field (byte offset in the record) | (width in bytes) << 16;
+                                                           // ids = first record, ids_ld = record bytes (a multiple of 4)
   const float* dense; int64_t dense_ld; int D; int emb;
   int64_t M; int n_tiles; int n_super;
   FuLayer L[FU_MAXL];
@@ -146,10 +148,10 @@ constexpr int FU_PF = 3;                    // chunks by which the id loads run 
 
 // float-region layout (shared by host sizing and device carving); all offsets in floats, 16-byte aligned
 struct FuSmemMap {
-  int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, ccw, wb, total;
+  int rowoff, sq, bias[FU_MAXL], alpha[FU_MAXL], wout, q, part, ccw, wb, pk, total;
 };
 __host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries */, int KC1, const int* KP, int nl,
-                                                 bool cc = false, bool wide = false) {
+                                                 bool cc = false, bool wide = false, bool packed = false) {
   FuSmemMap m;
   int o = 0;
   m.rowoff = o; o += (F * 3 + 3) / 4 * 4;          // per field: table base address (8 B) x F, then row count (4 B) x F
@@ -164,6 +166,7 @@ __host__ __device__ inline FuSmemMap fu_smem_map(int F /* (owner, field) entries
   m.ccw = o; if (cc) o += KC1 * 32 * 4;
   m.wb = o; if (wide) o += (3 * F + 3) / 4 * 4;     // per field: address of its block of the wide weight vector (8 B) x F,
                                                     // then its one-hot width (4 B) x F
+  m.pk = o; if (packed) o += (F + 3) / 4 * 4;       // per field: packed-id descriptor
   m.total = o;
   return m;
 }
@@ -280,7 +283,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #pragma unroll
   for (int l = 0; l < FU_MAXL; ++l) KP[l] = (l < NL) ? p.L[l].KP : 0;
   const int KC1 = p.L[0].KC;
-  const FuSmemMap mp = fu_smem_map(p.F * p.G, KC1, KP, NL, p.cc_n > 0, WIDE);
+  const FuSmemMap mp = fu_smem_map(p.F * p.G, KC1, KP, NL, p.cc_n > 0, WIDE, p.pack_desc != nullptr);
   float* fptr = reinterpret_cast<float*>(base_ptr + (f_base - base));
   const uint32_t bars = f_base + (uint32_t)mp.total * 4u;
   // barrier map
@@ -328,6 +331,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     }
     for (int i = tid; i < KC1 * 32; i += FU_THREADS) fptr[mp.sq + i] = p.sq_w ? __ldg(p.sq_w + i) : 0.f;
     if (p.cc_n > 0) for (int i = tid; i < KC1 * 32 * 4; i += FU_THREADS) fptr[mp.ccw + i] = __ldg(p.cc_w + i);
+    if (p.pack_desc) {
+      int32_t* s_pk = reinterpret_cast<int32_t*>(fptr + mp.pk);
+      for (int i = tid; i < p.F; i += FU_THREADS) s_pk[i] = __ldg(p.pack_desc + i);
+    }
     if (WIDE) {
       const float** s_wb = reinterpret_cast<const float**>(fptr + mp.wb);
       uint32_t* s_ww = reinterpret_cast<uint32_t*>(fptr + mp.wb + 2 * p.F);
@@ -394,6 +401,25 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         if (p.ids == nullptr) {                            // rows mode: row m of the tile IS row m of the matrix
 #pragma unroll
           for (int i = 0; i < 8; ++i) reg[i] = (cf.row0 + rsub + 16 * i < p.M) ? (int32_t)(cf.row0 + rsub + 16 * i) : 0;
+        } else if (p.ids_kind == CTRHOT_IDS_PACKED) {
+          // compact transport records: field f is `w` little-endian bytes at byte `off` of each record (any alignment).
+          // Two aligned 32-bit loads + a funnel shift; neighbouring fields share the words, so these hit L1.
+          const uint32_t d = (uint32_t)reinterpret_cast<const int32_t*>(fptr + mp.pk)[cf.f];
+          const uint32_t w8 = (d >> 16) * 8u;
+          const uint32_t mask = w8 >= 32u ? 0xFFFFFFFFu : ((1u << w8) - 1u);
+          const uint8_t* rec = static_cast<const uint8_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + (d & 0xFFFFu);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            reg[i] = 0;
+            if (cf.row0 + rsub + 16 * i < p.M) {
+              const uintptr_t a = reinterpret_cast<uintptr_t>(rec + (int64_t)(16 * i) * p.ids_ld);
+              const uint32_t* al = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+              const uint32_t sh = (uint32_t)(a & 3u) * 8u;
+              const uint32_t lo = __ldg(al);
+              const uint32_t hi = (sh + w8 > 32u) ? __ldg(al + 1) : 0u;    // never beyond the record: it ends on a word
+              reg[i] = (int32_t)(__funnelshift_r(lo, hi, sh) & mask);
+            }
+          }
         } else {
           const int32_t* src = static_cast<const int32_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + cf.f;   // int32 or float bits
 #pragma unroll
@@ -431,7 +457,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           // over NVLink -- the same 16-byte LDGSTS, only the latency differs (the raw ring keeps FU_NR chunks in flight)
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const uint32_t id = (p.ids_kind == CTRHOT_IDS_I32) ? (uint32_t)reg[i]
+            const uint32_t id = (p.ids_kind != CTRHOT_IDS_F32) ? (uint32_t)reg[i]
                                                                : (uint32_t)__float2int_rz(__int_as_float(reg[i]));
             const uint32_t lr = id / G, o = id - lr * G;
             const int e = (int)o * p.F + ci.f;
@@ -440,7 +466,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
             const char* src = reinterpret_cast<const char*>(s_fb[e]) + ci.part * 16 + (uint64_t)lr * rowbytes;
             cp_async16(dst + 2048u * i, ok ? (const void*)src : (const void*)p.arena, ok ? 16u : 0u);
           }
-        } else if (p.ids_kind == CTRHOT_IDS_I32) {
+        } else if (p.ids_kind != CTRHOT_IDS_F32) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const uint32_t id = (uint32_t)reg[i];
@@ -1001,6 +1027,7 @@ struct FuExtra {
   const float* cc_w = nullptr; float* side_out = nullptr;                                    // CUDA-core side products (DCN)
   const float* wide_w = nullptr; const int64_t* wide_off = nullptr; const float* wide_dense = nullptr;   // Wide&Deep wide term
   int64_t wide_dense_ld = 0; int wide_D = 0; const float* wide_dw = nullptr;
+  const int32_t* pack_desc = nullptr;                                                        // CTRHOT_IDS_PACKED
 };
 
 // peers[0..G): arena of owner g (this rank's own at its index; the others mapped through ctrhot_peer_open); G = 1 is the
@@ -1022,7 +1049,11 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   if (!rows_mode && (!row_off || !ids)) return CTRHOT_EARG;
   if (rows_mode && (F != 1 || G != 1 || M > 0x7FFFFFFF || row_stride < k || row_stride % 4 != 0)) return CTRHOT_EARG;
   if (D > 0 && !dense) return CTRHOT_EARG;
-  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (ids_kind == CTRHOT_IDS_PACKED) {
+    if (!ex.pack_desc || rows_mode || ids_ld <= 0 || ids_ld % 4 != 0 || (reinterpret_cast<uintptr_t>(ids) & 3u)) return CTRHOT_EARG;
+  } else if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) {
+    return CTRHOT_EARG;
+  }
   if (mode < FU_MODE_TOWER || mode > FU_MODE_DCN || n_side < 0 || n_side >= FU_SIDE) return CTRHOT_EARG;
   if (n_combine < 0 || n_combine > FU_NCB || (n_combine > 0 && !h_combine)) return CTRHOT_EARG;
   if (mode == FU_MODE_DEEPFM && n_combine < 1) return CTRHOT_EARG;
@@ -1088,6 +1119,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
   p.add_vec = ex.add_vec; p.out_scale = ex.out_scale; p.add_scale = ex.add_scale; p.add_const = ex.add_const;
   p.cc_w = ex.cc_w; p.cc_n = ex.cc_w ? n_side + 1 : 0; p.side_out = ex.side_out;
+  p.pack_desc = (ids_kind == CTRHOT_IDS_PACKED) ? ex.pack_desc : nullptr;
   if (ex.wide_w) {
     // the stage tail holds at most four fields per 32-column chunk and assumes fields start on piece boundaries
     if (mode != FU_MODE_TOWER || G != 1 || rows_mode || !ex.wide_off || ex.wide_D < 0 || ex.wide_D > 16 ||
@@ -1098,7 +1130,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   }
   const bool wide = (ex.wide_w != nullptr);
   p.raw_stride = FU_TILE_BYTES + (wide ? 2048u : 0u);
-  const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl, p.cc_n > 0, p.wide_w != nullptr);
+  const FuSmemMap mp = fu_smem_map(F * G, p.L[0].KC, KP, nl, p.cc_n > 0, p.wide_w != nullptr, p.pack_desc != nullptr);
   const size_t n_bars = 2 * FU_NR + 2 * FU_NAS + 2 * FU_NB + 2 * FU_MAXL + 1 + 1 + 8 * FU_MAXL;   // + TMEM slot word, h_chunk
   size_t smem = 0;
   bool fits = false;
@@ -1155,6 +1187,25 @@ extern "C" int ctrhot_ctr_fused_sharded_tf32(const void* const* arenas, const in
   for (int g = 0; g < G; ++g) peers[g] = static_cast<const float*>(arenas[g]);
   return fu_entry(peers, G, rank, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w,
                   mode, n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag, stream);
+}
+
+// ctrhot_ctr_fused_tf32 fed from compact transport records (csrc/transport.cu): record r = [ ... dense D floats at byte
+// dense_off ... | ids at their per-field byte widths ... ], rec_bytes a multiple of 4.  The gather warps decode the ids
+// themselves, the dense columns are read in place: one host-to-device copy per batch, no unpack pass, no int32 id matrix.
+extern "C" int ctrhot_ctr_fused_packed_tf32(const float* arena, const int64_t* row_off, int F, int k,
+                                            const void* records, int64_t rec_bytes, const int32_t* pack_desc,
+                                            int dense_off, int D, int64_t M,
+                                            const ctrhot_dense_desc* h_layers, int n_layers,
+                                            const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                                            int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  if (!arena || !records || !pack_desc || rec_bytes <= 0 || rec_bytes % 4 != 0 || dense_off < 0 || dense_off % 4 != 0 ||
+      (int64_t)dense_off + 4 * (int64_t)D > rec_bytes || !aligned16(records)) return CTRHOT_EARG;
+  FuExtra ex;
+  ex.pack_desc = pack_desc;
+  const float* dense = reinterpret_cast<const float*>(static_cast<const char*>(records) + dense_off);
+  return fu_entry(&arena, 1, 0, row_off, 0, F, k, records, CTRHOT_IDS_PACKED, rec_bytes, D > 0 ? dense : nullptr, rec_bytes / 4,
+                  D, M, h_layers, n_layers, sq_w, mode, n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag,
+                  stream, ex);
 }
 
 // DNNLayer.call (DL/layer/interaction.py:40-46) on an activation matrix that already lives in HBM: the same persistent

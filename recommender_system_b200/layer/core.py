@@ -364,12 +364,12 @@ class DenseStack:
         return cols <= 512
 
     def run_ctr_fused(self, E, ids, kind, ids_ld, dense, B, first_kernel_ref, side=None, sq_w=None, mode=0, n_side=0,
-                      combine=(), sigmoid=False, err_flag=None, out=None, cluster=0, side_key=None):
+                      combine=(), sigmoid=False, err_flag=None, out=None, cluster=0, side_key=None, records=None, n_dense=None):
         """``first_kernel_ref``: layer-0 kernel [n, n1] in the REFERENCE column order [dense | embeddings];
         ``side`` [n, 16] (reference order) / ``sq_w`` / ``combine`` as described in include/ctrhot.h."""
         arr = self.descs()
         n, n1 = int(first_kernel_ref.shape[0]), int(first_kernel_ref.shape[1])
-        D = 0 if dense is None else dense.shape[1]
+        D = (0 if dense is None else dense.shape[1]) if records is None else int(n_dense)
         key = ("fused", side_key)
         if key not in self._packed:
             nbytes = _lib.query("ctrhot_fused_pack_bytes", n, n1)
@@ -380,6 +380,13 @@ class DenseStack:
         if out is None:
             out = torch.empty((B, 1), dtype=torch.float32, device=E.arena.device)
         cb = (ctypes.c_float * max(len(combine), 1))(*[float(c) for c in combine])
+        if records is not None:
+            # compact transport records (utils/transport.py): ids decoded by the gather warps, dense read in place
+            lay, rec = records.layout, records.records
+            _lib.call("ctrhot_ctr_fused_packed_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(rec), rec.stride(0),
+                      ptr(lay.desc(rec.device)), lay.dense_off, D, B, arr, len(arr), ptr(sq_w), int(mode), int(n_side), cb,
+                      len(combine), int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag), stream_ptr())
+            return out
         tail = (ptr(ids), kind, ids_ld, ptr(dense), 0 if dense is None else dense.stride(0), D, B, arr, len(arr), ptr(sq_w),
                 int(mode), int(n_side), cb, len(combine), int(bool(sigmoid)), int(cluster), ptr(out), ptr(err_flag),
                 stream_ptr())

@@ -20,11 +20,16 @@ from ..layer.core import EmbedLayer, _ids_to_device
 from ..layer.interaction import (CrossLayer, DNNLayer, FFMLayer, FMLayer, InnerProductLayer, OuterProductLayer,
                                  WideLayer)
 
+from ..utils.transport import PackedRows  # noqa: E402
+
 N_DENSE = 13   # hard-coded in every reference call(): deepFM.py:24, dcn.py:25, wideDeep.py:23, pnn.py:29
 
 
 def split_inputs(inputs, device, n_dense=N_DENSE, n_sparse=None):
     """-> (dense [B,D] fp32 view, ids [B,F] view (float or int32), rest or None), all on device."""
+    if isinstance(inputs, PackedRows):                     # transport records: one unpack launch (utils/transport.py)
+        dense, ids = inputs.layout.unpack(inputs.records)
+        return dense, ids, None
     if isinstance(inputs, (tuple, list)) and len(inputs) == 2:
         dense = as_device_f32(inputs[0], device)
         ids = _ids_to_device(inputs[1], device)
@@ -151,24 +156,36 @@ class DeepFM(_EmbedTowerModel):
     def call(self, inputs, training=None, mask=None):
         E = self.embed_layer
         D = len(self.dense_feature_columns)
-        dense, ids, _ = split_inputs(inputs, self.device, D)
-        require_cuda(dense, "DeepFM")
-        B = dense.shape[0]
-        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        records, fits = None, False
         if self.fused and self.whole and self.dnn.output_dim == 1 and self.fm.k < 16:
             stack = self.dnn.stack
             stack.set_layers(self._tower_layers(self.dnn, D), (self.dnn._version, D))
-            if stack.ctr_fused_ok(E.F, E.k):
+            fits = stack.ctr_fused_ok(E.F, E.k)
+        if isinstance(inputs, PackedRows) and fits and inputs.layout.D == D and inputs.layout.F == E.F:
+            # transport records go straight into the whole-model kernel: its gather warps decode the ids
+            records = inputs
+            require_cuda(records.records, "DeepFM")
+            dense, ids, B = records.records, None, records.records.shape[0]
+        else:
+            dense, ids, _ = split_inputs(inputs, self.device, D)
+            require_cuda(dense, "DeepFM")
+            B = dense.shape[0]
+        out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        if fits:
+            if True:        # (kept as a block: the body below predates the `fits` hoist)
                 # K-fused: gather -> FM (split-TF32 side columns + x^2 term) -> tower -> sigmoid(0.5*(fm+dnn)), ONE launch
                 side, sq_w, cb = self._fm_side(D)
-                ids, kind, ids_ld = ids_arg(ids)
+                if records is None:
+                    ids, kind, ids_ld = ids_arg(ids)
+                else:
+                    kind, ids_ld = _lib.IDS_PACKED, 0
                 ev = None
                 if self.events is not None:
                     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
                     ev[0].record()
                 stack.run_ctr_fused(E, ids, kind, ids_ld, dense, B, self.dnn.hidden[0][0], side, sq_w, mode=1,
                                     n_side=self.fm.k, combine=cb, sigmoid=True, err_flag=self.err_flag(), out=out,
-                                    cluster=self.cluster, side_key=("fm", self.fm._version))
+                                    cluster=self.cluster, side_key=("fm", self.fm._version), records=records, n_dense=D)
                 if ev:
                     ev[1].record()
                     self.events.append(tuple(ev))

@@ -1,0 +1,116 @@
+"""GPU + host: compact transport records (csrc/transport.cu, utils/transport.py) -- pack on the host, decode either inside the
+whole-model kernel (CTRHOT_IDS_PACKED) or by ctrhot_rows_unpack -- against the plain (dense, ids) path: the records carry the
+same numbers, so every result must be IDENTICAL, bit for bit (ids are integers, dense floats are copied)."""
+import numpy as np
+import pytest
+import torch
+
+from recommender_system_b200 import _lib
+from recommender_system_b200.model.criteo import DCN, DeepFM
+from recommender_system_b200.utils import synth
+from recommender_system_b200.utils.pipeline import HostPipeline
+from recommender_system_b200.utils.transport import PackedRows, RowLayout
+
+
+def test_layout_widths_follow_the_vocabulary(lib):
+    lay = RowLayout([256, 257, 65536, 65537, 1 << 24, (1 << 24) + 1, 3], n_dense=13)
+    assert lay.widths == [1, 2, 2, 3, 3, 4, 1]
+    assert lay.rec_bytes == (52 + 16 + 3) // 4 * 4
+    k = RowLayout(synth.KAGGLE_VOCAB, 13)
+    assert k.rec_bytes == 104 and sum(k.widths) == 52           # 156 B per sample as int32
+
+
+def test_host_pack_round_trips_and_reports_ids_that_do_not_fit(lib):
+    rng = np.random.default_rng(0)
+    vocab = [256, 300, 70000, 20_000_000, 5, 65536]
+    lay = RowLayout(vocab, n_dense=3)
+    B = 10_001                                                  # several threads, ragged last chunk
+    dense = rng.random((B, 3), dtype=np.float32)
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], 1).astype(np.int32)
+    ids[0] = np.asarray(vocab) - 1
+    rec = lay.pack(dense, ids)
+    assert rec.shape == (B, lay.rec_bytes)
+    # decode on the host, independently of the C code
+    got_dense = rec[:, :12].copy().view(np.float32).reshape(B, 3)
+    np.testing.assert_array_equal(got_dense, dense)
+    for f in range(len(vocab)):
+        off, w = int(lay.desc_host[f]) & 0xFFFF, int(lay.desc_host[f]) >> 16
+        v = sum(rec[:, off + b].astype(np.int64) << (8 * b) for b in range(w))
+        np.testing.assert_array_equal(v, ids[:, f])
+    np.testing.assert_array_equal(rec, lay.pack(dense, ids, threads=1))
+    bad = ids.copy()
+    bad[77, 0] = 256                                            # one past what a byte holds
+    with pytest.raises(IndexError):
+        lay.pack(dense, bad)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B", [1, 127, 1000, 65536])
+def test_unpack_kernel_is_exact(lib, B):
+    rng = np.random.default_rng(B)
+    vocab = synth.KAGGLE_VOCAB
+    lay = RowLayout(vocab, 13)
+    dense, ids = synth.criteo_batch(B, vocab, seed=B)
+    ids[-1] = np.asarray(vocab) - 1
+    rec = torch.from_numpy(lay.pack(dense, ids)).cuda()
+    d, i = lay.unpack(rec)
+    np.testing.assert_array_equal(d.cpu().numpy(), dense)
+    np.testing.assert_array_equal(i.cpu().numpy(), ids)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,vocab_name", [(1, "sample"), (300, "sample"), (5000, "sample"), (65536, "kaggle")])
+def test_deepfm_on_records_equals_deepfm_on_dense_and_ids(lib, B, vocab_name):
+    vocab = synth.KAGGLE_VOCAB if vocab_name == "kaggle" else synth.SAMPLE_VOCAB
+    m = DeepFM(synth.criteo_feature_columns(vocab, 16), 10, 1e-4, 1e-4, [256, 128, 64], 1, "relu", embed_dim=16)
+    m.build(None)
+    lay = RowLayout.from_feature_columns(m.feature_columns if hasattr(m, "feature_columns")
+                                         else [m.dense_feature_columns, m.sparse_feature_columns])
+    dense, ids = synth.criteo_batch(B, vocab, seed=7 + B)
+    ids[B // 2] = np.asarray(vocab) - 1                          # the last row of every table, every width saturated
+    want = m((dense, ids)).cpu().numpy()
+    launches = _lib.LAUNCHES[0]
+    got = m(PackedRows(lay, torch.from_numpy(lay.pack(dense, ids)).cuda())).cpu().numpy()
+    assert _lib.LAUNCHES[0] - launches == 1                     # decoded inside the whole-model kernel: no unpack pass
+    np.testing.assert_array_equal(got, want)
+    # an id beyond its table (but inside its byte width) is reported like on the int32 path
+    f = 1 if vocab_name == "kaggle" else 0                      # a field whose vocabulary does not fill its width
+    bad = ids.copy()
+    bad[0, f] = vocab[f]
+    with pytest.raises(IndexError):
+        m(PackedRows(lay, torch.from_numpy(lay.pack(dense, bad)).cuda()))
+
+
+@pytest.mark.gpu
+def test_other_models_take_records_through_the_unpack_kernel(lib):
+    vocab = synth.SAMPLE_VOCAB
+    m = DCN(synth.criteo_feature_columns(vocab, 16), [64, 32], 1, "relu", 3, embed_dim=16)
+    m.build(None)
+    lay = RowLayout(vocab, 13)
+    dense, ids = synth.criteo_batch(777, vocab, seed=3)
+    want = m((dense, ids)).cpu().numpy()
+    got = m(PackedRows(lay, torch.from_numpy(lay.pack(dense, ids)).cuda())).cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_host_pipeline_with_records(lib):
+    vocab = synth.SAMPLE_VOCAB
+    m = DeepFM(synth.criteo_feature_columns(vocab, 16), 10, 1e-4, 1e-4, [256, 128, 64], 1, "relu", embed_dim=16, check_ids=False)
+    m.build(None)
+    lay = RowLayout(vocab, 13)
+    B = 4096
+    pipe = HostPipeline(m, B, depth=3, layout=lay)
+    batches = [synth.criteo_batch(B, vocab, seed=40 + i) for i in range(5)]
+    recs = [torch.from_numpy(lay.pack(d, i)).pin_memory() for d, i in batches]
+    outs = []
+    tickets = []
+    for j, r in enumerate(recs):
+        tickets.append(pipe.submit_packed(r))
+        if j >= 2:
+            outs.append(pipe.result(tickets[j - 2]).copy())
+    outs += [r.copy() for r in pipe.drain()]
+    assert len(outs) == 5
+    for (d, i), o in zip(batches, outs):
+        np.testing.assert_array_equal(o, m((d, i)).cpu().numpy())
+    assert pipe.h2d_bytes_packed == B * lay.rec_bytes
