@@ -43,6 +43,7 @@ typedef enum {
   CTRHOT_EID = -4          /* an embedding id was out of range */
 } ctrhot_status;
 
+enum { CTRHOT_LAUNCH_OVERLAP = 0x100 };   /* OR into `cluster` of the whole-model entry points, see ctrhot_ctr_fused_tf32 */
 enum { CTRHOT_IDS_I32 = 0, CTRHOT_IDS_F32 = 1, CTRHOT_IDS_PACKED = 2 /* transport records, see ctrhot_rows_* */ };
 enum { CTRHOT_ACT_NONE = 0, CTRHOT_ACT_RELU = 1, CTRHOT_ACT_PRELU = 2, CTRHOT_ACT_DICE = 3,
        CTRHOT_ACT_SIGMOID = 4, CTRHOT_ACT_TANH = 5 };
@@ -215,7 +216,12 @@ int ctrhot_tower_gather_tf32(const float* arena, const int64_t* row_off, int F, 
  *                  a = 1; a += a * S[l] + h_combine[l];  out = a * S[L] + h_combine[L] + wy * y + bias
  *                  (the L cross layers of interaction.py:75-83 collapse to these scalars because x_l = a_l x_0 + c_l)
  * apply_sigmoid != 0 applies the model's final sigmoid.  h_combine is a HOST array (<= 24 floats).
- * cluster: 0 = auto, else 1 | 2 | 4 CTAs share each weight chunk through TMA multicast.
+ * cluster: 0 = auto, else 1 | 2 | 4 CTAs share each weight chunk through TMA multicast.  OR-ing CTRHOT_LAUNCH_OVERLAP into it
+ *          allows this launch to begin while the PREVIOUS launch of this entry point in the same stream (made with the same
+ *          flag) is still finishing its last tiles (programmatic dependent launch): 65 536 samples are 512 tiles on 148 SMs,
+ *          so 80 SMs would otherwise idle through the last quarter of every launch.  The caller promises that the two
+ *          launches are independent: no input of this one (ids, dense, records, tables, weights) is written by that one, and
+ *          `out` buffers differ.  Launches made without the flag are ordered as usual.
  * CTRHOT_ESHAPE when the tower does not fit (TMEM columns / shared memory / activation kind): use the layered path. */
 int64_t ctrhot_fused_pack_bytes(int n, int n1);
 int ctrhot_fused_pack(const float* W1, const float* side, int n, int n1, int D, void* packed, void* stream);
@@ -249,6 +255,20 @@ int ctrhot_ctr_fused_packed_tf32(const float* arena, const int64_t* row_off, int
                                  const ctrhot_dense_desc* h_layers, int n_layers,
                                  const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                                  int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
+/* Plans: ctrhot_ctr_fused_tf32 / _packed_tf32 with everything but the batch frozen, for loops that call them every ~70 us
+ * (the argument checks, shared-memory sizing and cluster choice are done once).  create: arguments as for the two entry points
+ * above -- ids_kind I32 / F32 with ids_ld, dense_ld; or PACKED with ids_ld = record bytes, pack_desc, dense_off.  The plan is
+ * a few hundred bytes of HOST memory (destroy frees it); the device pointers inside (tables, packed weights, sq_w, pack_desc,
+ * err_flag) must stay valid and unchanged -- re-create the plan when weights are re-packed.
+ * run: `batch` = ids [M, ids_ld] (with `dense` [M, dense_ld]) or the records (then `dense` is ignored). */
+int ctrhot_fused_plan_create(const float* arena, const int64_t* row_off, int F, int k,
+                             int ids_kind, int64_t ids_ld, const int32_t* pack_desc, int dense_off,
+                             int64_t dense_ld, int D,
+                             const ctrhot_dense_desc* h_layers, int n_layers,
+                             const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                             int apply_sigmoid, int cluster, int* err_flag, void** plan);
+int ctrhot_fused_plan_run(const void* plan, const void* batch, const float* dense, int64_t M, float* out, void* stream);
+int ctrhot_fused_plan_destroy(void* plan);
 /* The same kernel over ROW-SHARDED tables (8(e), config 5): arenas = HOST array of G device pointers (arena of owner g;
  * this rank's own at index `rank`, the peers' mapped by ctrhot_peer_open), row_off = device int64 [G, F+1], ids = GLOBAL
  * row numbers: row id of field f is read at arenas[id mod G] + (row_off[id mod G][f] + id div G) * k -- the gather warps

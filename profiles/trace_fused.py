@@ -46,6 +46,14 @@ if hasattr(lib, "ctrhot_debug_fused_trace2") and lib.ctrhot_debug_fused_trace2(b
     for i, n in enumerate(n2):
         tot = m[3] if i < 4 else m[5] if i < 6 else m[7]
         print("   %-24s %10.0f cyc (%.1f%% of its role)" % (n, m[i], 100 * m[i] / tot))
+buf3 = (ctypes.c_ulonglong * (256 * 8))()
+if hasattr(lib, "ctrhot_debug_fused_trace3") and lib.ctrhot_debug_fused_trace3(buf3) == 0:
+    t3 = np.frombuffer(buf3, dtype=np.uint64).reshape(256, 8).astype(np.float64)
+    t3 = t3[t3[:, 2] > 0]
+    print("   stager per chunk: load + math %.0f cyc, TMEM store + hand-off %.0f cyc (%.0f chunks per CTA)" % (
+        (t3[:, 0] / t3[:, 2]).mean(), (t3[:, 1] / t3[:, 2]).mean(), t3[:, 2].mean()))
+    print("   gather per chunk: id fetch %.0f cyc, copy issue (after the stage is free) %.0f cyc" % (
+        (t3[:, 3] / t3[:, 2]).mean(), (t3[:, 4] / t3[:, 2]).mean()))
 tb = (ctypes.c_ulonglong * (256 * 4))()
 if lib.ctrhot_debug_fused_times(tb) == 0:
     tt = np.frombuffer(tb, dtype=np.uint64).reshape(256, 4).astype(np.float64)
@@ -53,3 +61,12 @@ if lib.ctrhot_debug_fused_times(tb) == 0:
     print("CTA entry -> MMA loop begin %.1f us, MMA loop %.1f us, loop end -> exit %.1f us; first entry -> last exit %.1f us" % (
         (tt[:, 1] - tt[:, 0]).mean() / 1e3, (tt[:, 2] - tt[:, 1]).mean() / 1e3, (tt[:, 3] - tt[:, 2]).mean() / 1e3,
         (tt[:, 3].max() - tt[:, 0].min()) / 1e3))
+if lib.ctrhot_debug_fused_times(tb) == 0:
+    t0 = tt[:, 0].min()
+    ent, lb, le, ex = (tt[:, i] - t0 for i in range(4))
+    q = lambda a: "min %.1f  p10 %.1f  median %.1f  p90 %.1f  max %.1f us" % tuple(np.percentile(a, [0, 10, 50, 90, 100]) / 1e3)
+    print("per-CTA timeline (globaltimer, relative to the first CTA's entry):")
+    print("   entry        ", q(ent))
+    print("   MMA loop end ", q(le))
+    print("   exit         ", q(ex))
+    print("   loop length  ", q(le - lb))

@@ -18,6 +18,7 @@ LIB_PATH = os.environ.get("CTRHOT_LIB") or os.path.join(PKG, "libctrhot.so")
 
 OK, EARG, ESHAPE, ECUDA, EID = 0, -1, -2, -3, -4
 IDS_I32, IDS_F32, IDS_PACKED = 0, 1, 2
+LAUNCH_OVERLAP = 0x100
 ACT_NONE, ACT_RELU, ACT_PRELU, ACT_DICE, ACT_SIGMOID, ACT_TANH = 0, 1, 2, 3, 4, 5
 ACT_BY_NAME = {None: ACT_NONE, "linear": ACT_NONE, "relu": ACT_RELU, "prelu": ACT_PRELU, "dice": ACT_DICE,
                "sigmoid": ACT_SIGMOID, "tanh": ACT_TANH}

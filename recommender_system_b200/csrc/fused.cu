@@ -28,6 +28,7 @@
 //               CLUSTER so one L2 read feeds C SMs.
 // TMEM columns: D1/H1 at 0, DS (32) next, then a region shared in time by the A ring (2..4 slots of x|x_lo, live during
 // layer 1) and D2/H2, D3 (live afterwards).  HBM traffic = ids + dense + each needed row once + 4 B out.
+#include <new>
 #include "common.cuh"
 #include "tc05.cuh"
 #include "mlp.cuh"
@@ -73,6 +74,7 @@ struct FuParams {
   const float* sq_w;                                       // [KC1*32] internal order or NULL
   int mode; int n_side; float cb[FU_NCB];
   int apply_sigmoid;
+  int overlap;                                             // CTRHOT_LAUNCH_OVERLAP: let the next launch in the stream start early
   int ds_col;                                              // TMEM column of the side accumulator
   int a_col, n_as, a_w;                                    // TMEM A ring: first column, slots, columns per slot (x | x_lo = 64
                                                            // with side products, x = 32 without)
@@ -246,7 +248,9 @@ __device__ __forceinline__ float fu_last_chunk(uint32_t taddr, const float* sb, 
 }
 
 #ifndef FU_EXP_
-#define FU_EXP_ 0         // tuning builds only: bit 0 drops the N=32 side MMA, bit 1 the N=16 one (results are then wrong)
+#define FU_EXP_ 0         // tuning builds only (results are then wrong): bit 0 drops the N=32 side MMA, bit 1 the N=16 one,
+                          // bit 2: stager skips the row LDS, bit 3: skips q, bit 4: skips x_lo,
+                          // bit 6: ids from a hash instead of loads, bit 7: rows of tables of <= 64 rows are not fetched
 #endif
 #ifdef FU_TRACE
 // tuning builds only (profiles/build_variants.py TRACE=1): cycles the MMA thread of every CTA spent waiting, per cause
@@ -255,6 +259,9 @@ __device__ unsigned long long fu_times[256][4];     // globaltimer ns: CTA entry
 // cycles other roles waited: [0] stager on full_raw, [1] stager on a_free, [2] stager on last_free, [3] stager total,
 // [4] gather on empty_raw, [5] gather total, [6] epilogue (warp 0) on d_full, [7] epilogue total
 __device__ unsigned long long fu_trace2[256][8];
+// [0] stager: cycles from a chunk's rows being ready to their last use in registers (LDS + q + x_lo + side sums),
+// [1] stager: cycles from the A slot being free to the a_full arrive (tcgen05.st x2 + wait::st + fences), [2] chunks
+__device__ unsigned long long fu_trace3[256][8];
 #define FU_T2(var, stmt) do { const long long t0_ = clock64(); stmt; var += clock64() - t0_; } while (0)
 __device__ __forceinline__ unsigned long long fu_now() {
   unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t;
@@ -273,6 +280,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
 #ifdef FU_TRACE
   if (threadIdx.x == 0 && blockIdx.x < 256) fu_times[blockIdx.x][0] = fu_now();
 #endif
+  // Programmatic dependent launch, opt-in: a following launch that was ALLOWED to (same flag) may start its CTAs on the SMs
+  // this launch's CTAs leave -- a batch of 512 tiles on 148 SMs ends with 80 SMs idle for a quarter of the kernel.  Nothing
+  // here waits for the previous launch (no griddepcontrol.wait): the caller promises that consecutive launches are independent.
+  if (p.overlap && threadIdx.x == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t base = (raw_addr + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - raw_addr);
@@ -394,8 +405,12 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     };
     Cur cf{0, f0, part0, first_row0}, ci = cf;
     int n_fetched = 0;
+    long long t2_fetch = 0, t2_issue = 0; (void)t2_fetch; (void)t2_issue;
     auto fetch = [&](int32_t (&reg)[8]) {
       if (n_fetched >= total_chunks) return;
+#ifdef FU_TRACE
+      const long long tf0 = clock64();
+#endif
       ++n_fetched;
       if (cf.f < p.F) {
         if (p.ids == nullptr) {                            // rows mode: row m of the tile IS row m of the matrix
@@ -420,6 +435,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
               reg[i] = (int32_t)(__funnelshift_r(lo, hi, sh) & mask);
             }
           }
+        } else if (FU_EXP_ & 64) {                        // tuning: ids from a hash, no id loads at all (timing only)
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            reg[i] = (int32_t)((((uint32_t)(cf.row0 + rsub + 16 * i) * 2654435761u + (uint32_t)cf.f * 40503u) >> 4) % s_fn[cf.f]);
         } else {
           const int32_t* src = static_cast<const int32_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + cf.f;   // int32 or float bits
 #pragma unroll
@@ -428,6 +447,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         }
       }
       advance(cf);
+#ifdef FU_TRACE
+      t2_fetch += clock64() - tf0;
+#endif
     };
     int rs = 0; uint32_t rph = 0;                        // raw stage of the next issue and its phase
     constexpr bool wide_on = WIDE;
@@ -435,6 +457,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     auto issue = [&](int g, const int32_t (&reg)[8]) {
       const int s = rs;
       FU_T2(t2_wait, mbar_wait(empty_raw(s), rph ^ 1u));
+#ifdef FU_TRACE
+      const long long ti0 = clock64();
+#endif
       if (++rs == p.nr) { rs = 0; rph ^= 1u; }
       const uint32_t dst = dst0 + (uint32_t)s * RAW_STRIDE;
       // wide tail of the stage: [128 rows][4 slots] floats; this thread owns a slot when its piece is the first of a field
@@ -448,7 +473,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         wdst = r_base + (uint32_t)s * RAW_STRIDE + FU_TILE_BYTES + (uint32_t)rsub * 16u + (k4 < 8 ? (uint32_t)(c / k4) * 4u : 0u);
         wbase = reinterpret_cast<const float* const*>(fptr + mp.wb)[ci.f];
       }
-      if (ci.f < p.F) {
+      if ((FU_EXP_ & 128) && ci.f < p.F && s_fn[ci.f] <= 64u) {
+        // tuning: tiny tables cost nothing (as if their rows came from a shared-memory copy)
+      } else if (ci.f < p.F) {
         const char* fb = reinterpret_cast<const char*>(s_fb[ci.f]) + ci.part * 16;
         const uint32_t nrow = s_fn[ci.f];
         bool bad = false;
@@ -508,6 +535,9 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       }
       cp_async_mbar_arrive_noinc(full_raw(s));
       advance(ci);
+#ifdef FU_TRACE
+      t2_issue += clock64() - ti0;
+#endif
     };
     static_assert(FU_PF == 3, "the loop below is unrolled for three id register sets");
 #ifdef FU_TRACE
@@ -521,7 +551,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       if (g + 2 < total_chunks) { issue(g + 2, rc); fetch(rc); }
     }
 #ifdef FU_TRACE
-    if (tg == 0 && blockIdx.x < 256) { fu_trace2[blockIdx.x][4] = t2_wait; fu_trace2[blockIdx.x][5] = clock64() - t2_begin; }
+    if (tg == 0 && blockIdx.x < 256) {
+      fu_trace2[blockIdx.x][4] = t2_wait; fu_trace2[blockIdx.x][5] = clock64() - t2_begin;
+      fu_trace3[blockIdx.x][3] = t2_fetch; fu_trace3[blockIdx.x][4] = t2_issue;
+    }
 #endif
   } else if (warp >= 12 && warp < 16) {
     // ================================================================ stager: smem chunk -> TMEM A ring (x | x_lo), q = sum x^2 sq_w
@@ -533,10 +566,14 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     uint32_t sa = 0, pa = 0;                            // A slot and its phase
     int sr = 0; uint32_t pr = 0;                        // raw stage and its phase
     const bool with_lo = (p.a_w == 64);
-    long long s2_raw = 0, s2_af = 0, s2_lf = 0; (void)s2_raw; (void)s2_af; (void)s2_lf;
+    long long s2_raw = 0, s2_af = 0, s2_lf = 0, s2_math = 0, s2_store = 0;
+    (void)s2_raw; (void)s2_af; (void)s2_lf; (void)s2_math; (void)s2_store;
 #ifdef FU_TRACE
     const long long s2_begin = clock64();
 #endif
+    // (Loading the rows of chunk g + 1 while chunk g is processed was built and measured SLOWER, 76.5 -> 81.8 us per step:
+    //  the stager is not the pace-setter -- the gather is, at ~1 700 cycles per chunk against 936 of MMA work and ~690 here;
+    //  profiles/r02_fused_notes.md.)
     for (int lt = 0; lt < n_my; ++lt) {
       float q = 0.f;
       float S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f;     // CUDA-core side products (DCN: x . w_l and x . final_w)
@@ -551,25 +588,24 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       }
       for (int kc = 0; kc < KC1; ++kc) {
         FU_T2(s2_raw, mbar_wait(full_raw(sr), pr));
+#ifdef FU_TRACE
+        const long long s2_t0 = clock64();
+#endif
         const uint32_t raw = src0 + sr * RAW_STRIDE;
-        const float* sq = fptr + mp.sq + kc * 32;
-        float x[32], lo[32];
+        float x[32];
 #pragma unroll
         for (int cc = 0; cc < 8; ++cc) {
-          const float4 v = lds128(raw + (((uint32_t)cc ^ rx) << 4));
+          const float4 v = (FU_EXP_ & 4) ? make_float4(0.25f, 0.5f, 0.125f, 1.f) : lds128(raw + (((uint32_t)cc ^ rx) << 4));
           x[4 * cc + 0] = v.x; x[4 * cc + 1] = v.y; x[4 * cc + 2] = v.z; x[4 * cc + 3] = v.w;
         }
-        if (p.sq_w) {                                   // FM's sum x^2 (sum_c v^2) term
+        const float* sq = fptr + mp.sq + kc * 32;
+        if (p.sq_w && !(FU_EXP_ & 8)) {                 // FM's sum x^2 (sum_c v^2) term
 #pragma unroll
           for (int cc = 0; cc < 8; ++cc) {
             const float4 w = *reinterpret_cast<const float4*>(sq + cc * 4);
             q = fmaf(x[4 * cc + 0] * x[4 * cc + 0], w.x, q); q = fmaf(x[4 * cc + 1] * x[4 * cc + 1], w.y, q);
             q = fmaf(x[4 * cc + 2] * x[4 * cc + 2], w.z, q); q = fmaf(x[4 * cc + 3] * x[4 * cc + 3], w.w, q);
           }
-        }
-        if (with_lo) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) lo[j] = x[j] - trunc_tf32(x[j]);
         }
         if (WIDE) {
           // the fields whose first piece lies in this chunk left their wide weight in the stage tail, in field order
@@ -609,17 +645,31 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
           }
           fptr[mp.q + (lt & 1) * FU_BM + row] = v;
         }
+#ifdef FU_TRACE
+        s2_math += clock64() - s2_t0;
+#endif
         mbar_arrive(empty_raw(sr));                     // the chunk is in registers: the gather may refill the stage
         if (++sr == p.nr) { sr = 0; pr ^= 1u; }
         // the A ring shares its TMEM columns with the later layers' accumulators: wait until the previous tile is done with them
         if (NL > 1 && kc == 0 && lt > 0) FU_T2(s2_lf, mbar_wait(last_free, (uint32_t)(lt - 1) & 1u));
         FU_T2(s2_af, mbar_wait(a_free(sa), pa ^ 1u));
+#ifdef FU_TRACE
+        const long long s2_t1 = clock64();
+#endif
         tc_fence_after();
         tmem_st32(t_lane + sa * (uint32_t)p.a_w, x);
-        if (with_lo) tmem_st32(t_lane + sa * 64u + 32u, lo);
+        if (with_lo) {
+          // x_lo = x - trunc_tf32(x): what the tensor pipe drops of x (it truncates its operands to TF32)
+#pragma unroll
+          if (!(FU_EXP_ & 16)) for (int j = 0; j < 32; ++j) x[j] = x[j] - trunc_tf32(x[j]);
+          tmem_st32(t_lane + sa * 64u + 32u, x);
+        }
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(a_full(sa));
+#ifdef FU_TRACE
+        s2_store += clock64() - s2_t1;
+#endif
         if (++sa == (uint32_t)n_as) { sa = 0; pa ^= 1u; }
       }
     }
@@ -627,6 +677,7 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
     if (row == 0 && blockIdx.x < 256) {
       fu_trace2[blockIdx.x][0] = s2_raw; fu_trace2[blockIdx.x][1] = s2_af; fu_trace2[blockIdx.x][2] = s2_lf;
       fu_trace2[blockIdx.x][3] = clock64() - s2_begin;
+      fu_trace3[blockIdx.x][0] = s2_math; fu_trace3[blockIdx.x][1] = s2_store; fu_trace3[blockIdx.x][2] = (long long)n_my * KC1;
     }
 #endif
   } else if (warp == 16) {
@@ -667,9 +718,10 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
                                    (uint32_t)((kc | k) != 0));
               // (folding the side columns into the main MMA as two N = 144 halves was measured SLOWER, 88.9 -> 92.5 us:
               //  an MMA wider than 128 columns costs the full 138 cycles; kept in git history only)
-              if (side_on) mma_tf32_ts(ds_t, a_hi + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
+              if (side_on && !(FU_EXP_ & 1))
+                mma_tf32_ts(ds_t, a_hi + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc32, (uint32_t)((kc | k) != 0));
             }
-            if (side_on) {
+            if (side_on && !(FU_EXP_ & 2)) {
 #pragma unroll
               for (int k = 0; k < 4; ++k)
                 mma_tf32_ts(ds_t, a_lo + (uint32_t)(8 * k), ds + (uint64_t)(2 * k), idesc16, 1u);
@@ -944,6 +996,9 @@ extern "C" int ctrhot_debug_fused_trace(unsigned long long* h_out) {
 extern "C" int ctrhot_debug_fused_trace2(unsigned long long* h_out) {
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace2, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
 }
+extern "C" int ctrhot_debug_fused_trace3(unsigned long long* h_out) {
+  return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace3, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
+}
 extern "C" int ctrhot_debug_fused_times(unsigned long long* h_out) {
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_times, sizeof(unsigned long long) * 256 * 4) == cudaSuccess ? 0 : -3;
 }
@@ -992,11 +1047,16 @@ int fu_launch(const FuParams& p0, size_t smem, cudaStream_t st) {
   cfg.blockDim = dim3(FU_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  if (p.overlap) {
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.numAttrs = 2;
+  }
   const int n_clusters = p.n_super < max_clusters ? p.n_super : max_clusters;
   cfg.gridDim = dim3(n_clusters * C);
   CTRHOT_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, p), "ctrhot_ctr_fused_tf32 launch");
@@ -1021,6 +1081,11 @@ int fu_launch_nl(const FuParams& p, int nl, size_t smem, cudaStream_t st, bool w
   }
 }
 
+// A prepared whole-model launch: everything but the batch (ids / records, dense, row count, out) frozen.
+struct FuPlan {
+  FuParams p; int nl; size_t smem; bool wide; int cluster; int dense_off; bool packed;
+};
+
 struct FuExtra {
   const float* add_vec = nullptr; float out_scale = 1.f, add_scale = 1.f, add_const = 0.f;   // tower-mode post
   float* h_out = nullptr; int64_t h_ld = 0;                                                  // store mode
@@ -1028,7 +1093,10 @@ struct FuExtra {
   const float* wide_w = nullptr; const int64_t* wide_off = nullptr; const float* wide_dense = nullptr;   // Wide&Deep wide term
   int64_t wide_dense_ld = 0; int wide_D = 0; const float* wide_dw = nullptr;
   const int32_t* pack_desc = nullptr;                                                        // CTRHOT_IDS_PACKED
+  struct FuPlan* capture = nullptr;      // plan creation: keep the prepared launch instead of making it
 };
+
+int fu_dispatch(const FuParams& p, int nl, size_t smem, bool wide, int cluster, cudaStream_t st);
 
 // peers[0..G): arena of owner g (this rank's own at its index; the others mapped through ctrhot_peer_open); G = 1 is the
 // unsharded case.  row_off is [G, F+1].
@@ -1058,7 +1126,10 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   if (n_combine < 0 || n_combine > FU_NCB || (n_combine > 0 && !h_combine)) return CTRHOT_EARG;
   if (mode == FU_MODE_DEEPFM && n_combine < 1) return CTRHOT_EARG;
   if (mode == FU_MODE_DCN && n_combine < n_side + 3) return CTRHOT_EARG;
+  const int overlap = (cluster & CTRHOT_LAUNCH_OVERLAP) ? 1 : 0;
+  cluster &= ~CTRHOT_LAUNCH_OVERLAP;
   if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4) return CTRHOT_EARG;
+  if (overlap && (ex.h_out || rows_mode)) return CTRHOT_EARG;        // chained launches read what the previous one wrote
   if (k % 4 != 0 || !aligned16(arena) || F > 63) return CTRHOT_ESHAPE;
   // h_out: ONE hidden layer whose activations go to HBM (no final Dense); otherwise hidden layers + the final Dense(h -> 1)
   if (h_out ? (n_layers != 1 || mode == FU_MODE_DEEPFM) : (n_layers < 2 || n_layers > FU_MAXL + 1)) return CTRHOT_ESHAPE;
@@ -1114,7 +1185,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   p.M = M; p.n_tiles = (int)((M + FU_BM - 1) / FU_BM);
   p.w_out = h_out ? nullptr : o.weight; p.b_out = h_out ? nullptr : o.bias; p.sq_w = sq_w;
   p.h_out = h_out; p.h_ld = h_ld;
-  p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid;
+  p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid; p.overlap = overlap;
   for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
   p.add_vec = ex.add_vec; p.out_scale = ex.out_scale; p.add_scale = ex.add_scale; p.add_const = ex.add_const;
@@ -1144,7 +1215,14 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
     if (fits) break;
   }
   if (!fits) return CTRHOT_ESHAPE;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (ex.capture) {
+    ex.capture->p = p; ex.capture->nl = nl; ex.capture->smem = smem; ex.capture->wide = wide; ex.capture->cluster = cluster;
+    return CTRHOT_OK;
+  }
+  return fu_dispatch(p, nl, smem, wide, cluster, static_cast<cudaStream_t>(stream));
+}
+
+int fu_dispatch(const FuParams& p, int nl, size_t smem, bool wide, int cluster, cudaStream_t st) {
   int C = cluster;
   if (C == 0) {
     // larger clusters share each weight chunk among more CTAs (less L2 traffic) but leave SMs idle when a GPC's SM count
@@ -1206,6 +1284,72 @@ extern "C" int ctrhot_ctr_fused_packed_tf32(const float* arena, const int64_t* r
   return fu_entry(&arena, 1, 0, row_off, 0, F, k, records, CTRHOT_IDS_PACKED, rec_bytes, D > 0 ? dense : nullptr, rec_bytes / 4,
                   D, M, h_layers, n_layers, sq_w, mode, n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag,
                   stream, ex);
+}
+
+// ---------------------------------------------------------------- plans: one cheap call per batch
+// ctrhot_ctr_fused_tf32 / _packed_tf32 validate their ~25 arguments, size shared memory and pick a cluster shape on every
+// call; a serving loop calls them every ~70 us with the same model.  A plan does that once: create freezes everything but the
+// batch, run takes the batch.  Host memory only (a few hundred bytes, freed by destroy); the device pointers inside (tables,
+// packed weights, sq_w, pack_desc, err_flag) must stay valid and unchanged for the plan's lifetime -- re-create it when the
+// weights are re-packed.  ids_kind I32 / F32: `batch` = ids [M, ids_ld], `dense` [M, dense_ld]; PACKED: `batch` = records
+// (ids_ld = record bytes), dense is taken from the records at dense_off and the `dense` argument of run is ignored.
+extern "C" int ctrhot_fused_plan_create(const float* arena, const int64_t* row_off, int F, int k,
+                                        int ids_kind, int64_t ids_ld, const int32_t* pack_desc, int dense_off,
+                                        int64_t dense_ld, int D,
+                                        const ctrhot_dense_desc* h_layers, int n_layers,
+                                        const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
+                                        int apply_sigmoid, int cluster, int* err_flag, void** plan) {
+  if (!arena || !plan) return CTRHOT_EARG;
+  FuPlan* pl = new (std::nothrow) FuPlan();
+  if (!pl) return CTRHOT_EARG;
+  FuExtra ex;
+  ex.capture = pl;
+  pl->packed = (ids_kind == CTRHOT_IDS_PACKED);
+  pl->dense_off = dense_off;
+  // representative batch pointers for the argument checks: any aligned non-null address (nothing is launched)
+  const void* fake = arena;
+  float* fake_out = const_cast<float*>(arena);
+  int rc;
+  if (pl->packed) {
+    if (!pack_desc || ids_ld <= 0 || ids_ld % 4 != 0 || dense_off < 0 || dense_off % 4 != 0 ||
+        (int64_t)dense_off + 4 * (int64_t)D > ids_ld) { delete pl; return CTRHOT_EARG; }
+    ex.pack_desc = pack_desc;
+    rc = fu_entry(&arena, 1, 0, row_off, 0, F, k, fake, CTRHOT_IDS_PACKED, ids_ld, D > 0 ? arena : nullptr, ids_ld / 4, D, 128,
+                  h_layers, n_layers, sq_w, mode, n_side, h_combine, n_combine, apply_sigmoid, cluster, fake_out, err_flag,
+                  nullptr, ex);
+  } else {
+    rc = fu_entry(&arena, 1, 0, row_off, 0, F, k, fake, ids_kind, ids_ld, D > 0 ? arena : nullptr, dense_ld, D, 128, h_layers,
+                  n_layers, sq_w, mode, n_side, h_combine, n_combine, apply_sigmoid, cluster, fake_out, err_flag, nullptr, ex);
+  }
+  if (rc != CTRHOT_OK) { delete pl; return rc; }
+  *plan = pl;
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_fused_plan_run(const void* plan, const void* batch, const float* dense, int64_t M, float* out,
+                                     void* stream) {
+  const FuPlan* pl = static_cast<const FuPlan*>(plan);
+  if (!pl || !batch || !out || M < 0) return CTRHOT_EARG;
+  if (M == 0) return CTRHOT_OK;
+  FuParams p = pl->p;
+  if (pl->packed) {
+    if (!aligned16(batch)) return CTRHOT_EARG;
+    p.ids = batch;
+    p.dense = p.D > 0 ? reinterpret_cast<const float*>(static_cast<const char*>(batch) + pl->dense_off) : nullptr;
+  } else {
+    if (p.D > 0 && !dense) return CTRHOT_EARG;
+    p.ids = batch;
+    p.dense = dense;
+  }
+  p.M = M;
+  p.n_tiles = (int)((M + FU_BM - 1) / FU_BM);
+  p.out = out;
+  return fu_dispatch(p, pl->nl, pl->smem, pl->wide, pl->cluster, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ctrhot_fused_plan_destroy(void* plan) {
+  delete static_cast<FuPlan*>(plan);
+  return CTRHOT_OK;
 }
 
 // DNNLayer.call (DL/layer/interaction.py:40-46) on an activation matrix that already lives in HBM: the same persistent

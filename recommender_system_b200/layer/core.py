@@ -97,6 +97,19 @@ def _ids_to_device(ids, device):
     return t.to(device, non_blocking=True)
 
 
+class _Plan:
+    """Owner of one ctrhot_fused_plan handle (host memory inside the library)."""
+
+    def __init__(self, handle):
+        self.handle = handle
+
+    def __del__(self):
+        try:
+            _lib.load().ctrhot_fused_plan_destroy(self.handle)
+        except Exception:
+            pass
+
+
 class DenseStack:
     """Host driver for a chain of Dense layers: descriptor array, packed weights, workspace.
 
@@ -110,6 +123,7 @@ class DenseStack:
         self.precision = precision
         self.layers = []
         self._packed = {}
+        self._plans = {}
         self._ws = None
         self._key = None
         self.allow_fused = True
@@ -118,6 +132,7 @@ class DenseStack:
         if self._key != version:
             self.layers = layers
             self._packed = {}
+            self._plans = {}               # plans hold pointers into the packed weights of the old version
             self._key = version
             self._descs_tmpl = None
 
@@ -379,6 +394,29 @@ class DenseStack:
         arr[0].packed = ptr(self._packed[key])
         if out is None:
             out = torch.empty((B, 1), dtype=torch.float32, device=E.arena.device)
+        if getattr(E, "peers", None) is None:
+            # unsharded: a prepared launch (ctrhot_fused_plan_*), created once per (weights, input layout, launch options)
+            if records is not None:
+                batch, dl, lay = records.records, 0, records.layout
+                layout_key = (_lib.IDS_PACKED, int(batch.stride(0)), lay.dense_off, id(lay))
+            else:
+                batch, dl, lay = ids, 0 if dense is None else int(dense.stride(0)), None
+                layout_key = (int(kind), int(ids_ld), dl, None)
+            pkey = (key, layout_key, D, int(mode), int(n_side), tuple(float(c) for c in combine), bool(sigmoid), int(cluster),
+                    ptr(E.arena), ptr(err_flag), ptr(sq_w))
+            plan = self._plans.get(pkey)
+            if plan is None:
+                cb = (ctypes.c_float * max(len(combine), 1))(*[float(c) for c in combine])
+                h = ctypes.c_void_p()
+                _lib.check(_lib.load().ctrhot_fused_plan_create(
+                    ptr(E.arena), ptr(E.row_off), E.F, E.k, layout_key[0], layout_key[1],
+                    ptr(lay.desc(batch.device)) if lay is not None else None, lay.dense_off if lay is not None else 0, dl, D,
+                    arr, len(arr), ptr(sq_w), int(mode), int(n_side), cb, len(combine), int(bool(sigmoid)), int(cluster),
+                    ptr(err_flag), ctypes.byref(h)), "ctrhot_fused_plan_create")
+                plan = self._plans[pkey] = _Plan(h)
+            _lib.call("ctrhot_fused_plan_run", plan.handle, ptr(batch), ptr(dense) if records is None else None, B, ptr(out),
+                      stream_ptr())
+            return out
         cb = (ctypes.c_float * max(len(combine), 1))(*[float(c) for c in combine])
         if records is not None:
             # compact transport records (utils/transport.py): ids decoded by the gather warps, dense read in place

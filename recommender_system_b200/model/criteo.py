@@ -127,6 +127,9 @@ class DeepFM(_EmbedTowerModel):
         self.fused = True
         self.whole = True           # one persistent kernel for the whole forward (ctrhot_ctr_fused_tf32) when it fits
         self.cluster = 0            # CTAs sharing each weight chunk by TMA multicast (0 = auto)
+        # True: consecutive forward calls on one stream may overlap at their edges (CTRHOT_LAUNCH_OVERLAP, include/ctrhot.h).
+        # Only for independent batches: the inputs of a call must not be produced by the previous call.
+        self.overlap_launches = False
         self.events = None          # bench hook: list receiving (front_start, front_end, tower_end) CUDA events
         self._side = None
         self.embed_layer._err_flag = self.err_flag()
@@ -157,6 +160,8 @@ class DeepFM(_EmbedTowerModel):
         E = self.embed_layer
         D = len(self.dense_feature_columns)
         records, fits = None, False
+        if self.device.type != "cuda":                      # before anything touches torch.cuda: fail as the library, loudly
+            raise _lib.CtrhotError("DeepFM: inputs/weights must live on a CUDA device -- there is no CPU fallback")
         if self.fused and self.whole and self.dnn.output_dim == 1 and self.fm.k < 16:
             stack = self.dnn.stack
             stack.set_layers(self._tower_layers(self.dnn, D), (self.dnn._version, D))
@@ -185,7 +190,8 @@ class DeepFM(_EmbedTowerModel):
                     ev[0].record()
                 stack.run_ctr_fused(E, ids, kind, ids_ld, dense, B, self.dnn.hidden[0][0], side, sq_w, mode=1,
                                     n_side=self.fm.k, combine=cb, sigmoid=True, err_flag=self.err_flag(), out=out,
-                                    cluster=self.cluster, side_key=("fm", self.fm._version), records=records, n_dense=D)
+                                    cluster=self.cluster | (_lib.LAUNCH_OVERLAP if self.overlap_launches else 0),
+                                    side_key=("fm", self.fm._version), records=records, n_dense=D)
                 if ev:
                     ev[1].record()
                     self.events.append(tuple(ev))

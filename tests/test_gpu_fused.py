@@ -336,3 +336,30 @@ def test_widedeep_onehot_narrower_than_vocab(lib):
     for one in (True, False):
         m.one_launch = one
         logit_close(npy(m((dense, ids)))[:, 0], want)
+
+
+@pytest.mark.parametrize("packed", [False, True])
+def test_overlapped_launches_give_the_same_results(lib, packed):
+    """CTRHOT_LAUNCH_OVERLAP (programmatic dependent launch): 12 back-to-back forward calls on independent batches, each
+    allowed to start while the previous one drains its last tiles, must produce exactly what ordinary launches produce."""
+    from recommender_system_b200.utils.transport import PackedRows, RowLayout
+    vocab = synth.SAMPLE_VOCAB
+    m = DeepFM(synth.criteo_feature_columns(vocab, 16), 10, 1e-4, 1e-4, [256, 128, 64], 1, "relu", embed_dim=16, check_ids=False)
+    m.build(None)
+    lay = RowLayout(vocab, 13)
+    B = 148 * 128 * 2 + 128 * 40 + 17                      # an uneven last wave: some SMs finish a tile earlier than others
+    batches = [synth.criteo_batch(B, vocab, seed=100 + i) for i in range(4)]
+    if packed:
+        ins = [PackedRows(lay, torch.from_numpy(lay.pack(d, i)).cuda()) for d, i in batches]
+    else:
+        ins = [(torch.from_numpy(d).cuda(), torch.from_numpy(i).cuda()) for d, i in batches]
+    want = [m(x).clone() for x in ins]
+    torch.cuda.synchronize()
+    m.overlap_launches = True
+    outs = [m(ins[j % 4]) for j in range(12)]
+    torch.cuda.synchronize()
+    for j, o in enumerate(outs):
+        assert torch.equal(o, want[j % 4]), j
+    # an ordinary launch after overlapped ones is ordered as usual
+    m.overlap_launches = False
+    assert torch.equal(m(ins[0]), want[0])
