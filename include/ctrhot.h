@@ -231,6 +231,22 @@ int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int
                           const ctrhot_dense_desc* h_layers, int n_layers,
                           const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                           int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
+/* ---- 8(f) rank 2, the input step: create_criteo_dataset, DL/utils/dataset.py:36-66 (read_csv :38, fillna :42-43,
+ * MinMaxScaler :46, LabelEncoder per column :51-52) -----------------------------------------------------------------------
+ * ctrhot_criteo_parse_tsv: text = the file's bytes on the DEVICE; line_start = device int64 [N + 1] (byte offset of every
+ *   line, then the end of the last one).  Per line: label (int8, when has_label), 13 counts -> dense_raw float64 [N, 13] (NaN
+ *   = empty field, as pandas reads it), 26 tokens -> int64 [N, 26]: the 32-bit value of the 8 lowercase hex digits, -1 for an
+ *   empty field (for fixed-width lowercase hex the string order LabelEncoder sorts by is the numeric order, and the fill value
+ *   '-1' sorts first).  Malformed fields set *err_flag.
+ * ctrhot_criteo_encode: dense[r, c] = fp32(x * d_scale[c] + d_min[c]) with x = 0 for NaN, evaluated in float64 as
+ *   MinMaxScaler.transform does (two rounded operations); ids[r, f] = index of tokens[r, f] in vocab[vocab_off[f] ..
+ *   vocab_off[f + 1]) (sorted distinct values of the column = LabelEncoder.classes_), -1 and *err_flag when absent
+ *   (LabelEncoder raises on unseen labels).  All pointers DEVICE. */
+int ctrhot_criteo_parse_tsv(const void* text, const int64_t* line_start, int64_t N, int has_label, int8_t* label,
+                            double* dense_raw, int64_t* tokens, int* err_flag, void* stream);
+int ctrhot_criteo_encode(const double* dense_raw, const int64_t* tokens, int64_t N, const double* d_scale,
+                         const double* d_min, const int64_t* vocab, const int64_t* vocab_off, float* dense,
+                         int64_t dense_ld, int32_t* ids, int64_t ids_ld, int* err_flag, void* stream);
 /* ---- transport records: the copy on the left of the path (the reference passes one float64 [B, 39]
  * matrix, DL/utils/dataset.py:61, DL/model/deepFM.py:24 -- 312 B per sample; the int32 fast path above takes 156 B) --------
  *   record = [ dense: D x float32 (bit-exact) | id_f in width[f] little-endian bytes, f = 0..F-1 | zero pad to 4 bytes ]

@@ -67,6 +67,44 @@ def make_criteo():
     print("criteo_cfg1.npz: X_test", Xte_o.shape, "nnz/row", float((Xte_o != 0).sum(1).mean()))
 
 
+def make_criteo_raw():
+    """``criteo_raw.npz``: the RAW columns of the bundled train_1w.txt (10 000 rows) as integers -- labels, the 13 count
+    features (with a missing mask) and the 26 categorical tokens as the 32-bit values of their 8 hex digits (with a missing
+    mask) -- plus ``test_index``: which raw rows the reference loader's seeded split (see make_criteo) put in X_test, in order.
+    Data, not code: this is what the GPU input step (csrc/encode.cu) is fed on the GPU box, where /root/reference does not
+    exist; tests/test_gpu_encode.py re-serialises it to TSV text and must reproduce criteo_cfg1.npz (the reference loader's
+    own output) from it."""
+    import pandas as pd
+    from sklearn.model_selection import train_test_split
+    names = ["label"] + ["I%d" % i for i in range(1, 14)] + ["C%d" % i for i in range(1, 27)]
+    df = pd.read_csv(CRITEO, sep="\t", header=None, names=names, dtype={n: str for n in names if n.startswith("C")})
+    N = len(df)
+    dense = df[names[1:14]]
+    dense_missing = dense.isna().to_numpy()
+    dense_raw = dense.fillna(0).to_numpy().astype(np.int64)
+    assert np.array_equal(dense_raw.astype(np.float64), dense.fillna(0).to_numpy().astype(np.float64))   # counts are integers
+    tok = df[names[14:]]
+    tok_missing = tok.isna().to_numpy()
+    toks = np.zeros((N, 26), dtype=np.uint32)
+    for j, c in enumerate(names[14:]):
+        col = tok[c]
+        ok = ~col.isna()
+        assert col[ok].str.fullmatch(r"[0-9a-f]{8}").all(), c        # fixed-width lowercase hex: string order == numeric order
+        toks[ok.to_numpy(), j] = col[ok].map(lambda t: int(t, 16)).to_numpy().astype(np.uint32)
+    np.random.seed(0)
+    _, test_index = train_test_split(np.arange(N), test_size=0.2)    # same RNG draw as make_criteo's split of X
+    # proof that this IS the reference's split: its X_test dense block equals the MinMax-scaled rows at test_index
+    z = np.load(os.path.join(HERE, "criteo_cfg1.npz"))
+    filled = dense.fillna(0).to_numpy().astype(np.float64)
+    lo, hi = filled.min(0), filled.max(0)
+    scaled = (filled - lo) / np.where(hi > lo, hi - lo, 1.0)
+    assert np.allclose(scaled[test_index].astype(np.float32), z["dense"], atol=1e-7), "test_index does not reproduce the split"
+    np.savez_compressed(os.path.join(HERE, "criteo_raw.npz"), label=df["label"].to_numpy().astype(np.int8),
+                        dense_raw=dense_raw, dense_missing=dense_missing, tokens=toks, token_missing=tok_missing,
+                        test_index=test_index.astype(np.int64))
+    print("criteo_raw.npz:", N, "rows;", int(dense_missing.sum()), "missing counts,", int(tok_missing.sum()), "missing tokens")
+
+
 def make_layers():
     from oracle import ctr_oracle as O
     from oracle.synth import tiny_case
@@ -82,6 +120,7 @@ def make_layers():
 if __name__ == "__main__":
     if os.path.isdir(REF_DL):
         make_criteo()
+        make_criteo_raw()
     else:
         print("reference not mounted; skipping criteo_cfg1.npz")
     make_layers()
