@@ -231,6 +231,19 @@ int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off, int F, int
                           const ctrhot_dense_desc* h_layers, int n_layers,
                           const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                           int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream);
+/* ---- 8(f) rank 4, the remaining towers (each a Dense stack -- ctrhot_mlp_* / ctrhot_tower_* -- plus one pass below) --------
+ * ctrhot_residual_relu_f32: out = relu(x + y)                               ResLayer.call, DL/layer/interaction.py:271-278
+ * ctrhot_mmoe_combine_f32 : out[t][b, h] = sum_e softmax(gate[b, t*E : (t+1)*E])[e] * expert[b, h*E + e]
+ *                           mmoe_layer.call, DL/layer/interaction.py:481-509.  expert = relu(x @ expert_matrix.view(in, H*E) +
+ *                           expert_bias.view(H*E)) -- the reference's [in, hidden, E] weight IS that [in, H*E] matrix in memory;
+ *                           gate = x @ [gate_0 | .. | gate_{T-1}] + biases.  out: T matrices [B, out_ld] out_task_stride apart.
+ * ctrhot_lau_concat_f32   : out[b*T + t, :] = [q_b, k_bt, q_b - k_bt, q_b * k_bt]   LocalActivationUnit.call, DL/layer/core.py:96-101 */
+int ctrhot_residual_relu_f32(const float* x, int64_t x_ld, const float* y, int64_t y_ld, int64_t M, int N,
+                             float* out, int64_t out_ld, void* stream);
+int ctrhot_mmoe_combine_f32(const float* expert, int64_t e_ld, const float* gate, int64_t g_ld, int64_t B, int H,
+                            int E, int T, float* out, int64_t out_task_stride, int64_t out_ld, void* stream);
+int ctrhot_lau_concat_f32(const float* query, int64_t q_ld, const float* keys, int64_t k_ld, int64_t B, int T, int K,
+                          float* out, int64_t out_ld, void* stream);
 /* ---- 8(f) rank 2, the input step: create_criteo_dataset, DL/utils/dataset.py:36-66 (read_csv :38, fillna :42-43,
  * MinMaxScaler :46, LabelEncoder per column :51-52) -----------------------------------------------------------------------
  * ctrhot_criteo_parse_tsv: text = the file's bytes on the DEVICE; line_start = device int64 [N + 1] (byte offset of every

@@ -430,3 +430,80 @@ def ffm_sparse(inputs, vocab_sizes, w0, w, v, n_dense=13):
     tot = np.sum(field_f, axis=1)
     inter = 0.5 * (np.sum(tot * tot, axis=1, keepdims=True) - np.sum(field_f * field_f, axis=(1, 2))[:, None])
     return lin + inter
+
+
+# --------------------------------------------------------------------------- the remaining towers
+def res_layer(x, hidden, out):
+    """ResLayer.call, DL/layer/interaction.py:271-278: ``relu(x + Dense_out(relu-Dense chain(x)))``; ``out`` maps back to
+    the input width (:269)."""
+    h = x
+    for kernel, bias in hidden:
+        h = np.maximum(h @ kernel + bias, 0)
+    h = h @ out[0] + out[1]
+    return np.maximum(x + h, 0)
+
+
+def deepcrossing_model(inputs, tables, res_layers, final, n_dense=13):
+    """DeepCrossing.call, DL/model/deepCrossing.py:25-32: x = [dense, Embed(ids)]; the residual units; Dense(1, sigmoid).
+    res_layers: list of (hidden pairs, out pair); final = (kernel [d,1], bias [1])."""
+    dense_inputs, sparse_inputs = inputs[:, :n_dense], inputs[:, n_dense:]
+    emb = embed_layer(sparse_inputs, tables)
+    x = np.concatenate([dense_inputs.astype(emb.dtype), emb], axis=-1)
+    for hidden, out in res_layers:
+        x = res_layer(x, hidden, out)
+    return sigmoid(x @ final[0] + final[1])
+
+
+def mmoe_layer(x, expert_matrix, expert_bias, gate_matrix, gate_bias):
+    """mmoe_layer.call, DL/layer/interaction.py:481-509.  expert_matrix [in, hidden, E], expert_bias [hidden, E] or None,
+    gate_matrix: list over tasks of [in, E], gate_bias: list of [E] or None.  -> list over tasks of [B, hidden]."""
+    E = expert_matrix.shape[2]
+    expert_output = np.transpose(np.stack([x @ expert_matrix[:, :, i] for i in range(E)], axis=0), (1, 2, 0))  # [B, hidden, E]
+    if expert_bias is not None:
+        expert_output = expert_output + expert_bias
+    expert_output = np.maximum(expert_output, 0)
+    outs = []
+    for t, gate in enumerate(gate_matrix):
+        g = x @ gate
+        if gate_bias is not None:
+            g = g + gate_bias[t]
+        g = softmax_last(g)                                                   # [B, E]
+        g = np.tile(g[:, None, :], (1, expert_output.shape[1], 1))            # [B, hidden, E]
+        outs.append(np.sum(g * expert_output, axis=-1))
+    return outs
+
+
+def tower_layer(x, hidden, out, act="relu"):
+    """tower_layer.call, DL/layer/interaction.py:518-523: DNNLayer without the dropout."""
+    return dnn_layer(x, hidden, out, act)
+
+
+def mmoe_model(x, expert_matrix, expert_bias, gate_matrix, gate_bias, towers, act="relu"):
+    """MMOE.call, DL/model/mmoe.py:24-32.  towers: list over tasks of (hidden pairs, out pair)."""
+    outs = mmoe_layer(x, expert_matrix, expert_bias, gate_matrix, gate_bias)
+    return [tower_layer(o, h, w, act) for o, (h, w) in zip(outs, towers)]
+
+
+def deepctr_dnn(x, kernels, biases, act="relu", bn=None, output_activation=None, dice=None):
+    """DNN.call, DL/layer/core.py:181-199 (the DeepCTR multi-layer perceptron): per layer ``tensordot(x, kernel) + bias``,
+    optional BatchNormalization (inference, eps 1e-3) BEFORE the activation, then the activation (the last layer takes
+    ``output_activation`` when given), Dropout = identity.  Works on the last axis of an nD input.
+    bn: list of (mean, var, gamma, beta) or None; dice: list of (alphas, mean, var) when act == 'dice'."""
+    n = len(kernels)
+    for i in range(n):
+        x = np.tensordot(x, kernels[i], axes=(-1, 0)) + biases[i]
+        if bn is not None:
+            x = batchnorm_infer(x, bn[i][0], bn[i][1], bn[i][2], bn[i][3], eps=1e-3)
+        a = output_activation if (output_activation and i == n - 1) else act
+        x = globals()["dice"](x, *dice[i]) if a in ("dice", "Dice") else activation(a, x)
+    return x
+
+
+def local_activation_unit(query, keys, kernels, biases, out_kernel, out_bias, act="sigmoid", dice=None):
+    """LocalActivationUnit.call, DL/layer/core.py:92-107: query [B,1,K] repeated over T, ``[q, k, q-k, q*k]`` -> DNN ->
+    ``tensordot(., kernel [h,1]) + bias`` -> [B,T,1] (no mask, no softmax: those belong to the pooling layer)."""
+    T = keys.shape[1]
+    q = np.repeat(query, T, axis=1)
+    att_input = np.concatenate([q, keys, q - keys, q * keys], axis=-1)
+    att_out = deepctr_dnn(att_input, kernels, biases, act, dice=dice)
+    return np.tensordot(att_out, out_kernel, axes=(-1, 0)) + out_bias

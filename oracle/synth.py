@@ -366,6 +366,124 @@ def _run_afm(mode):
     return run
 
 
+
+# ------------------------------------------------------------------ the remaining towers
+def make_res(rng, n=D + F * 8):
+    a = {"x": f32(rng.uniform(-0.5, 1.0, size=(B, n)))}
+    _dense_stack(rng, [n, 24, 16, n], "res", a)
+    return a
+
+
+def run_res(a):
+    hidden, out = _get_stack(a, "res")
+    return O.res_layer(a["x"], hidden, out)
+
+
+def make_deepcrossing(rng, k=8):
+    vocab = _vocab(rng)
+    d = D + F * k
+    a = {"inputs": _criteo_inputs(rng, vocab), "vocab": vocab.astype(np.int64)}
+    for i, t in enumerate(_tables(rng, vocab, k)):
+        a["table%d" % i] = f32(t * 10.0)
+    for r in range(2):
+        _dense_stack(rng, [d, 24, 16, d], "res%d" % r, a)
+    a["final_k"] = f32(rng.uniform(-0.2, 0.2, (d, 1)))
+    a["final_b"] = f32(rng.normal(0, 0.1, (1,)))
+    return a
+
+
+def run_deepcrossing(a):
+    res = [_get_stack(a, "res%d" % r) for r in range(2)]
+    return O.deepcrossing_model(a["inputs"], _tables_of(a), res, (a["final_k"], a["final_b"]))
+
+
+def make_mmoe(rng, n_in=12, hidden=10, E=3, T=3):
+    a = {"x": f32(rng.uniform(-1.0, 2.0, (B, n_in))), "expert_matrix": f32(rng.normal(0, 0.3, (n_in, hidden, E))),
+         "expert_bias": f32(rng.normal(0, 0.2, (hidden, E)))}
+    for t in range(T):
+        a["gate_matrix%d" % t] = f32(rng.normal(0, 0.5, (n_in, E)))
+        a["gate_bias%d" % t] = f32(rng.normal(0, 0.3, (E,)))
+        _dense_stack(rng, [hidden, 20, 10, 1], "tower%d" % t, a)
+    return a
+
+
+def _mmoe_parts(a):
+    T = sum(1 for k in a if k.startswith("gate_matrix"))
+    return T, [a["gate_matrix%d" % t] for t in range(T)], [a["gate_bias%d" % t] for t in range(T)]
+
+
+def run_mmoe_layer(a):
+    T, gm, gb = _mmoe_parts(a)
+    return np.stack(O.mmoe_layer(a["x"], a["expert_matrix"], a["expert_bias"], gm, gb), axis=0)       # [T, B, hidden]
+
+
+def run_mmoe(a):
+    T, gm, gb = _mmoe_parts(a)
+    towers = [_get_stack(a, "tower%d" % t) for t in range(T)]
+    return np.stack(O.mmoe_model(a["x"], a["expert_matrix"], a["expert_bias"], gm, gb, towers), axis=0)  # [T, B, 1]
+
+
+def make_deepctr_dnn(rng, n=20, hidden=(16, 8)):
+    a = {"x": f32(rng.normal(0, 1.0, (B, T, n)))}
+    dims = [n] + list(hidden)
+    for i in range(len(hidden)):
+        lim = np.sqrt(6.0 / (dims[i] + dims[i + 1]))
+        a["kernel%d" % i] = f32(rng.uniform(-lim, lim, (dims[i], dims[i + 1])))
+        a["bias%d" % i] = f32(rng.normal(0, 0.1, (dims[i + 1],)))
+        a["bn_mean%d" % i] = f32(rng.normal(0, 0.1, (dims[i + 1],)))
+        a["bn_var%d" % i] = f32(rng.uniform(0.5, 1.5, (dims[i + 1],)))
+        a["bn_gamma%d" % i] = f32(rng.uniform(0.5, 1.5, (dims[i + 1],)))
+        a["bn_beta%d" % i] = f32(rng.normal(0, 0.1, (dims[i + 1],)))
+    return a
+
+
+def _dnn_parts(a):
+    n = sum(1 for k in a if k.startswith("kernel"))
+    return ([a["kernel%d" % i] for i in range(n)], [a["bias%d" % i] for i in range(n)],
+            [(a["bn_mean%d" % i], a["bn_var%d" % i], a["bn_gamma%d" % i], a["bn_beta%d" % i]) for i in range(n)])
+
+
+def run_deepctr_dnn_relu(a):
+    k, b, _ = _dnn_parts(a)
+    return O.deepctr_dnn(a["x"], k, b, "relu")
+
+
+def run_deepctr_dnn_bn_sigmoid(a):
+    k, b, bn = _dnn_parts(a)
+    return O.deepctr_dnn(a["x"], k, b, "sigmoid", bn=bn, output_activation="tanh")
+
+
+def make_lau(rng, K=8, hidden=(16, 8)):
+    a = {"query": f32(rng.normal(0, 0.5, (B, 1, K))), "keys": f32(rng.normal(0, 0.5, (B, T, K)))}
+    dims = [4 * K] + list(hidden)
+    for i in range(len(hidden)):
+        lim = np.sqrt(6.0 / (dims[i] + dims[i + 1]))
+        a["kernel%d" % i] = f32(rng.uniform(-lim, lim, (dims[i], dims[i + 1])))
+        a["bias%d" % i] = f32(rng.normal(0, 0.1, (dims[i + 1],)))
+        a["dice_a%d" % i] = f32(rng.uniform(0, 0.3, (dims[i + 1],)))
+        a["dice_m%d" % i] = f32(rng.normal(0, 0.1, (dims[i + 1],)))
+        a["dice_v%d" % i] = f32(rng.uniform(0.5, 1.5, (dims[i + 1],)))
+    a["out_k"] = f32(rng.uniform(-0.5, 0.5, (dims[-1], 1)))
+    a["out_b"] = f32(rng.normal(0, 0.1, (1,)))
+    return a
+
+
+def _lau_parts(a):
+    n = sum(1 for k in a if k.startswith("kernel"))
+    return ([a["kernel%d" % i] for i in range(n)], [a["bias%d" % i] for i in range(n)],
+            [(a["dice_a%d" % i], a["dice_m%d" % i], a["dice_v%d" % i]) for i in range(n)])
+
+
+def run_lau_sigmoid(a):
+    k, b, _ = _lau_parts(a)
+    return O.local_activation_unit(a["query"], a["keys"], k, b, a["out_k"], a["out_b"], "sigmoid")
+
+
+def run_lau_dice(a):
+    k, b, dice = _lau_parts(a)
+    return O.local_activation_unit(a["query"], a["keys"], k, b, a["out_k"], a["out_b"], "dice", dice=dice)
+
+
 CASES = {
     "embed": (make_embed, run_embed),
     "wide": (make_wide, run_wide),
@@ -387,6 +505,14 @@ CASES = {
     "afm_avg": (make_afm, _run_afm("avg")),
     "afm_max": (make_afm, _run_afm("max")),
     "afm_att": (make_afm, _run_afm("att")),
+    "res": (make_res, run_res),
+    "deepcrossing": (make_deepcrossing, run_deepcrossing),
+    "mmoe_layer": (make_mmoe, run_mmoe_layer),
+    "mmoe": (make_mmoe, run_mmoe),
+    "deepctr_dnn_relu": (make_deepctr_dnn, run_deepctr_dnn_relu),
+    "deepctr_dnn_bn_sigmoid": (make_deepctr_dnn, run_deepctr_dnn_bn_sigmoid),
+    "lau_sigmoid": (make_lau, run_lau_sigmoid),
+    "lau_dice": (make_lau, run_lau_dice),
 }
 
 

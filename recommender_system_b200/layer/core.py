@@ -473,3 +473,113 @@ def dense_params(layer, name, in_dim, out_dim):
     k = layer.add_weight(name + "/kernel", (in_dim, out_dim), init_glorot_uniform)
     b = layer.add_weight(name + "/bias", (out_dim,), init_zeros)
     return k, b
+
+
+# ---------------------------------------------------------------- the DeepCTR-lineage layers of layer/core.py
+from .base import init_ones, init_zeros as _zeros  # noqa: E402
+
+
+class DNN(Layer):
+    """``DNN(hidden_units, activation='relu', l2_reg=0, dropout_rate=0, use_bn=False, output_activation=None, seed=1024)`` --
+    DL/layer/core.py:123-220, the DeepCTR multi-layer perceptron on the LAST axis of an nD input.  Per layer: Dense, optional
+    BatchNormalization BEFORE the activation (inference form, eps 1e-3: folded into the layer's weights), activation
+    ('relu' / 'sigmoid' / 'tanh' / 'linear' / 'dice'); the last layer takes ``output_activation`` when given.  Dropout is the
+    identity.  Weight names follow the reference: kernel0.., bias0.. (core.py:153-161)."""
+
+    def __init__(self, hidden_units, activation="relu", l2_reg=0, dropout_rate=0, use_bn=False, output_activation=None,
+                 seed=1024, precision="tf32", device=None, **kwargs):
+        super().__init__(device)
+        self.hidden_units = list(hidden_units)
+        self.activation, self.output_activation = activation, output_activation
+        self.use_bn = use_bn
+        self.stack = DenseStack(precision)
+        self._layers = None
+
+    def _act_of(self, i):
+        a = self.output_activation if (self.output_activation and i == len(self.hidden_units) - 1) else self.activation
+        a = "dice" if a in ("dice", "Dice") else a
+        if a not in _lib.ACT_BY_NAME or a == "prelu":
+            raise ValueError("unsupported activation %r" % (a,))
+        return a
+
+    def build(self, input_shape):
+        dims = [int(input_shape[-1])] + self.hidden_units
+        n = len(self.hidden_units)
+        self.kernels = [self.add_weight("kernel%d" % i, (dims[i], dims[i + 1]), init_glorot_uniform) for i in range(n)]
+        self.bias = [self.add_weight("bias%d" % i, (dims[i + 1],), _zeros) for i in range(n)]
+        self.bn = ([tuple(self.add_weight("bn_%d/%s" % (i, nm), (dims[i + 1],), init)
+                          for nm, init in (("moving_mean", _zeros), ("moving_variance", init_ones), ("gamma", init_ones),
+                                           ("beta", _zeros))) for i in range(n)] if self.use_bn else None)
+        self.dice = {i: tuple(self.add_weight("dice_%d/%s" % (i, nm), (dims[i + 1],), init)
+                              for nm, init in (("alpha", _zeros), ("moving_mean", _zeros), ("moving_variance", init_ones)))
+                     for i in range(n) if self._act_of(i) == "dice"}
+
+    def layer_dicts(self):
+        if self._layers is None or self._layers[0] != self._version:
+            ls = []
+            for i, (k, b) in enumerate(zip(self.kernels, self.bias)):
+                if self.bn is not None:
+                    mean, var, gamma, beta = self.bn[i]
+                    s = gamma / torch.sqrt(var + 1e-3)
+                    k, b = (k * s[None, :]).contiguous(), ((b - mean) * s + beta).contiguous()
+                a = self._act_of(i)
+                d = {"kernel": k, "bias": b, "act": _lib.ACT_BY_NAME[a]}
+                if a == "dice":
+                    d["act_param"] = torch.stack(self.dice[i]).contiguous()
+                    d["dice_eps"] = 1e-9
+                ls.append(d)
+            self._layers = (self._version, ls)
+        return self._layers[1]
+
+    def call(self, inputs, training=None, **kwargs):
+        x = as_device_f32(inputs, self.device)
+        require_cuda(x, "DNN")
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1])
+        if not self.hidden_units:
+            return x
+        self.stack.set_layers(self.layer_dicts(), self._version)
+        y = self.stack.run(x2)
+        return y.reshape(*lead, y.shape[-1])
+
+
+class LocalActivationUnit(Layer):
+    """``LocalActivationUnit(hidden_units=(64, 32), activation='sigmoid', l2_reg=0, dropout_rate=0, use_bn=False, seed=1024)``
+    -- DL/layer/core.py:28-120: ``[q, k, q-k, q*k]`` (query repeated over T) -> DNN -> Dense(1) -> ``[B, T, 1]`` scores (no
+    mask, no softmax).  The concat is built by ctrhot_lau_concat_f32; DNN and the final ``kernel [h,1]`` / ``bias`` run as one
+    Dense stack."""
+
+    def __init__(self, hidden_units=(64, 32), activation="sigmoid", l2_reg=0, dropout_rate=0, use_bn=False, seed=1024,
+                 precision="tf32", device=None, **kwargs):
+        super().__init__(device)
+        self.hidden_units = list(hidden_units)
+        self.dnn = self.track(DNN(hidden_units, activation, l2_reg, dropout_rate, use_bn, seed=seed, precision=precision,
+                                  device=self.device))
+        self.stack = DenseStack(precision)
+
+    def build(self, input_shape):
+        if not isinstance(input_shape, (list, tuple)) or len(input_shape) != 2:
+            raise ValueError("A `LocalActivationUnit` layer should be called on a list of 2 inputs")
+        K = int(input_shape[0][-1])
+        size = 4 * K if len(self.hidden_units) == 0 else self.hidden_units[-1]
+        self.kernel = self.add_weight("kernel", (size, 1), init_glorot_uniform)
+        self.bias = self.add_weight("bias", (1,), _zeros)
+        if not self.dnn.built:
+            self.dnn.build((None, 4 * K))
+            self.dnn.built = True
+
+    def call(self, inputs, training=None, **kwargs):
+        query, keys = inputs
+        q = as_device_f32(query, self.device)
+        k = as_device_f32(keys, self.device)
+        require_cuda(k, "LocalActivationUnit")
+        if q.dim() != 3 or k.dim() != 3 or q.shape[1] != 1 or q.shape[2] != k.shape[2]:
+            raise ValueError("LocalActivationUnit needs inputs of shape (None,1,embedding_size) and (None,T,embedding_size)")
+        B, T, K = k.shape
+        q2, k2 = q.reshape(B, K), k.reshape(B * T, K)
+        a = torch.empty((B * T, 4 * K), dtype=torch.float32, device=k.device)
+        _lib.call("ctrhot_lau_concat_f32", ptr(q2), q2.stride(0), ptr(k2), k2.stride(0), B, T, K, ptr(a), a.stride(0), stream_ptr())
+        ls = list(self.dnn.layer_dicts()) if self.hidden_units else []
+        ls.append({"kernel": self.kernel, "bias": self.bias, "act": _lib.ACT_NONE})
+        self.stack.set_layers(ls, (self._version, self.dnn._version))
+        return self.stack.run(a).reshape(B, T, 1)

@@ -367,3 +367,85 @@ class Attention(Layer):
                   cand_ld, B, T, arr, len(arr), ptr(self.out_kernel), ptr(self.out_bias), ptr(att), att.stride(0),
                   ptr(item), item.stride(0), ptr(check_flag), stream_ptr())
         return att, item
+
+
+# ---------------------------------------------------------------- the remaining towers
+class ResLayer(Layer):
+    """``ResLayer(hidden_units)`` -- interaction.py:261-278: ``relu(x + Dense_in(relu-Dense chain(x)))``.  The chain runs on
+    the tensor pipe (DenseStack), the residual add + ReLU is one more pass (ctrhot_residual_relu_f32)."""
+
+    def __init__(self, hidden_units, precision="tf32", device=None):
+        super().__init__(device)
+        self.hidden_units = list(hidden_units)
+        self.stack = DenseStack(precision)
+
+    def build(self, input_shape):
+        n = int(input_shape[-1])
+        dims = [n] + self.hidden_units
+        self.dense_layer = [dense_params(self, "dense_%d" % i, dims[i], dims[i + 1]) for i in range(len(self.hidden_units))]
+        self.output_layer = dense_params(self, "output", dims[-1], n)                # Dense(input width), interaction.py:269
+
+    def call(self, inputs, *args, **kwargs):
+        x = as_device_f32(inputs, self.device)
+        require_cuda(x, "ResLayer")
+        ls = [{"kernel": k, "bias": b, "act": _lib.ACT_RELU} for k, b in self.dense_layer]
+        ls.append({"kernel": self.output_layer[0], "bias": self.output_layer[1], "act": _lib.ACT_NONE})
+        self.stack.set_layers(ls, self._version)
+        y = self.stack.run(x)
+        out = torch.empty((x.shape[0], x.shape[1]), dtype=torch.float32, device=x.device)
+        _lib.call("ctrhot_residual_relu_f32", ptr(x), x.stride(0), ptr(y), y.stride(0), x.shape[0], x.shape[1], ptr(out),
+                  out.stride(0), stream_ptr())
+        return out
+
+
+class mmoe_layer(Layer):
+    """``mmoe_layer(hidden_units, num_experts, num_tasks, use_expert_bias=True, use_gate_bias=True)`` -- interaction.py:429-509.
+    The reference multiplies by ``expert_matrix[:, :, i]`` expert by expert and by every gate separately; here the experts are
+    ONE Dense layer (the [in, hidden, E] weight is an [in, hidden*E] matrix in memory) and the gates another, both on the
+    tensor pipe, followed by one kernel that applies each task's softmax over the experts and sums (ctrhot_mmoe_combine_f32).
+    Returns the list of ``num_tasks`` tensors ``[B, hidden_units]``."""
+
+    def __init__(self, hidden_units, num_experts, num_tasks, use_expert_bias=True, use_gate_bias=True, precision="tf32",
+                 device=None, **kwargs):
+        super().__init__(device)
+        self.hidden_units, self.num_experts, self.num_tasks = int(hidden_units), int(num_experts), int(num_tasks)
+        self.use_expert_bias, self.use_gate_bias = use_expert_bias, use_gate_bias
+        self.experts, self.gates = DenseStack(precision), DenseStack(precision)
+        self._cat = None
+
+    def build(self, input_shape):
+        n, H, E = int(input_shape[-1]), self.hidden_units, self.num_experts
+        self.expert_matrix = self.add_weight("expert_matrix", (n, H, E), init_random_normal)
+        self.expert_bias = self.add_weight("expert_bias", (H, E), init_random_normal) if self.use_expert_bias else None
+        self.gate_matrix = [self.add_weight("gate_matrix%d" % i, (n, E), init_random_normal) for i in range(self.num_tasks)]
+        self.gate_bias = ([self.add_weight("gate_bias%d" % i, (E,), init_random_normal) for i in range(self.num_tasks)]
+                          if self.use_gate_bias else None)
+
+    def call(self, inputs, *args, **kwargs):
+        x = as_device_f32(inputs, self.device)
+        require_cuda(x, "mmoe_layer")
+        B, H, E, T = x.shape[0], self.hidden_units, self.num_experts, self.num_tasks
+        if self._cat is None or self._cat[0] != self._version:
+            n = self.expert_matrix.shape[0]
+            ek = self.expert_matrix.reshape(n, H * E).contiguous()
+            eb = (self.expert_bias.reshape(-1) if self.expert_bias is not None
+                  else torch.zeros(H * E, device=self.device)).contiguous()
+            gk = torch.cat(self.gate_matrix, dim=1).contiguous()
+            gb = (torch.cat(self.gate_bias) if self.gate_bias is not None else torch.zeros(T * E, device=self.device)).contiguous()
+            self._cat = (self._version, ek, eb, gk, gb)
+        _, ek, eb, gk, gb = self._cat
+        self.experts.set_layers([{"kernel": ek, "bias": eb, "act": _lib.ACT_RELU}], self._version)
+        self.gates.set_layers([{"kernel": gk, "bias": gb, "act": _lib.ACT_NONE}], self._version)
+        ex = self.experts.run(x)
+        g = self.gates.run(x)
+        out = torch.empty((T, B, H), dtype=torch.float32, device=x.device)
+        _lib.call("ctrhot_mmoe_combine_f32", ptr(ex), ex.stride(0), ptr(g), g.stride(0), B, H, E, T, ptr(out), out.stride(0),
+                  out.stride(1), stream_ptr())
+        return [out[t] for t in range(T)]
+
+
+class tower_layer(DNNLayer):
+    """``tower_layer(hidden_units, output_dim, activation='relu')`` -- interaction.py:512-523: DNNLayer without the dropout."""
+
+    def __init__(self, hidden_units, output_dim, activation="relu", precision="tf32", device=None):
+        super().__init__(hidden_units, output_dim, activation, 0.0, precision=precision, device=device)

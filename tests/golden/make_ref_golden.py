@@ -48,6 +48,9 @@ from model.pnn import PNN  # noqa: E402
 from model.din import DIN  # noqa: E402
 from model.nfm import NFM  # noqa: E402
 from model.afm import AFM  # noqa: E402
+from model.deepCrossing import DeepCrossing  # noqa: E402
+from model.mmoe import MMOE  # noqa: E402
+from tf_shim import ops as SO  # noqa: E402
 import model.pnn as ref_pnn  # noqa: E402
 import model.nfm as ref_nfm  # noqa: E402
 
@@ -341,11 +344,104 @@ def r_din(a):
     return two_pass(m, x, inj)
 
 
+
+# ------------------------------------------------------------------ the remaining towers
+def _inj_res(o, a, prefix):
+    hidden, out = synth._get_stack(a, prefix)
+    assert len(o.dense_layer) == len(hidden)
+    for lyr, (k, b) in zip(o.dense_layer, hidden):
+        put_dense(lyr, k, b)
+    put_dense(o.output_layer, *out)                            # Dense(input width), built in ResLayer.build (:268-269)
+
+
+def r_res(a):
+    hidden, _ = synth._get_stack(a, "res")
+    return two_pass(RI.ResLayer([k.shape[1] for k, _ in hidden]), a["x"], lambda o: _inj_res(o, a, "res"))
+
+
+def r_deepcrossing(a):
+    hidden, _ = synth._get_stack(a, "res0")
+    m = DeepCrossing(fcols(a["vocab"]), 32, [k.shape[1] for k, _ in hidden], 2)
+
+    def inj(o):
+        put_tables(o.embed_layer.emb_layers, synth._tables_of(a))
+        for r, lyr in enumerate(o.res_layer):
+            _inj_res(lyr, a, "res%d" % r)
+        put_dense(o.output_layer, a["final_k"], a["final_b"])
+    return two_pass(m, a["inputs"], inj)
+
+
+def _inj_mmoe(o, a):
+    T, gm, gb = synth._mmoe_parts(a)
+    put(o, "expert_matrix", a["expert_matrix"])
+    put(o, "expert_bias", a["expert_bias"])
+    for t in range(T):
+        put(o, "gate_matrix", gm[t], t)
+        put(o, "gate_bias", gb[t], t)
+
+
+def r_mmoe_layer(a):
+    n_in, hidden, E = a["expert_matrix"].shape
+    T, _, _ = synth._mmoe_parts(a)
+    lyr = RI.mmoe_layer(hidden, E, T)
+    lyr(a["x"])
+    _inj_mmoe(lyr, a)
+    return np.stack([np.asarray(t) for t in lyr(a["x"])], axis=0)
+
+
+def r_mmoe(a):
+    n_in, hidden, E = a["expert_matrix"].shape
+    T, _, _ = synth._mmoe_parts(a)
+    h0, _ = synth._get_stack(a, "tower0")
+    m = MMOE(hidden, E, T, [k.shape[1] for k, _ in h0], 1)
+    m(a["x"])
+    _inj_mmoe(m.mmoe_layer, a)
+    for t, tw in enumerate(m.tower_layer):
+        put_dnn(tw, a, "tower%d" % t)
+    return np.stack([np.asarray(t) for t in m(a["x"])], axis=0)
+
+
+def _r_deepctr_dnn(act, use_bn, out_act):
+    def run(a):
+        ks, bs, bn = synth._dnn_parts(a)
+        lyr = RC.DNN([k.shape[1] for k in ks], act, use_bn=use_bn, output_activation=out_act)
+
+        def inj(o):
+            for i in range(len(ks)):
+                put(o, "kernels", ks[i], i)
+                put(o, "bias", bs[i], i)
+                if use_bn:
+                    put(o.bn_layers[i], "moving_mean", bn[i][0]); put(o.bn_layers[i], "moving_variance", bn[i][1])
+                    put(o.bn_layers[i], "gamma", bn[i][2]); put(o.bn_layers[i], "beta", bn[i][3])
+        return two_pass(lyr, SO._t(a["x"]), inj)
+    return run
+
+
+def _r_lau(act):
+    def run(a):
+        ks, bs, dice = synth._lau_parts(a)
+        lyr = RC.LocalActivationUnit([k.shape[1] for k in ks], act)
+        x = [SO._t(a["query"]), SO._t(a["keys"])]
+
+        def inj(o):
+            put(o, "kernel", a["out_k"]); put(o, "bias", a["out_b"])
+            for i in range(len(ks)):
+                put(o.dnn, "kernels", ks[i], i)
+                put(o.dnn, "bias", bs[i], i)
+                if act == "dice":
+                    _inj_dice(o.dnn.activation_layers[i], *dice[i])
+        return two_pass(lyr, x, inj)
+    return run
+
+
 RUNNERS = {
     "embed": r_embed, "wide": r_wide, "fm": r_fm, "dnn": r_dnn, "cross": r_cross, "ffm": r_ffm, "inner": r_inner,
     "outer": r_outer, "dice": r_dice, "att": r_att, "att_dice": r_att_dice, "deepfm": r_deepfm,
     "widedeep": r_widedeep, "dcn": r_dcn, "pnn": r_pnn, "din": r_din, "nfm": r_nfm,
     "afm_avg": _r_afm("avg"), "afm_max": _r_afm("max"), "afm_att": _r_afm("att"),
+    "res": r_res, "deepcrossing": r_deepcrossing, "mmoe_layer": r_mmoe_layer, "mmoe": r_mmoe,
+    "deepctr_dnn_relu": _r_deepctr_dnn("relu", False, None), "deepctr_dnn_bn_sigmoid": _r_deepctr_dnn("sigmoid", True, "tanh"),
+    "lau_sigmoid": _r_lau("sigmoid"), "lau_dice": _r_lau("dice"),
 }
 MODEL_WRAPPERS = {"fm": r_fm_model, "ffm": r_ffm_model}
 
