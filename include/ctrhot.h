@@ -409,6 +409,27 @@ int ctrhot_din_attention_gather_tf32(const float* table, int64_t V, int K,
                                      float* att_out, int64_t att_ld, float* item_out, int64_t item_ld,
                                      void* workspace, int64_t workspace_bytes, int* err_flag, void* stream);
 
+/* ---- R16 DIN.call's front end in ONE launch (DL/model/din.py:56-90) ------------------------------------------
+ * candidate lookup (din.py:78-79), history lookup (:76-77), the attention unit (:81, interaction.py:369-406), the other
+ * sparse lookups (:65-69) and the dense columns (:60-61), written as the tower's input matrix (the concat of din.py:84-90):
+ *     emb[b] = [ att (K) | item (K) | extras at their columns | dense at dense_col ]      emb_ld % 4 == 0, 16-byte aligned
+ * The mask is hist id != 0 (din.py:80).  K in {32, 64}, T <= 128, exactly two hidden Dense (PReLU[T,h] or ReLU), h1 <= 96,
+ * h2 <= 64; CTRHOT_ESHAPE otherwise (use ctrhot_din_attention_gather_* + ctrhot_gather_f32 then).  TF32 multiply, fp32
+ * accumulate; the first layer is evaluated as q (W1a + W1c) + k ((W1b - W1c) + diag(q) W1d): a per-sample [K, h1] weight
+ * matrix built in shared memory, so that layer 1 reads the gathered rows in place.
+ * packed = ctrhot_din_fwd_pack(...) (re-pack when the weights change); workspace = ctrhot_din_fwd_workspace_bytes(B, h1).
+ * h_extras: n_extras (<= 8) x 6 int64 on the HOST: {table (device pointer) [rows, dim], rows, dim, ids (device pointer, one id
+ * per sample, same ids_kind as the history), ids_ld, first column in emb}.  Bad ids: zero row + *err_flag = 1. */
+int64_t ctrhot_din_fwd_pack_bytes(int T, int K, int h1, int h2);
+int ctrhot_din_fwd_pack(const ctrhot_dense_desc* h_layers, int n_layers, const float* out_w, const float* out_b,
+                        int T, int K, void* packed, void* stream);
+int64_t ctrhot_din_fwd_workspace_bytes(int64_t B, int h1);
+int ctrhot_din_fwd_tf32(const float* table, int64_t V, int K, const void* hist_ids, int ids_kind, int64_t hist_ld,
+                        const void* cand_ids, int64_t cand_ld, int64_t B, int T, const void* packed, int h1, int h2,
+                        float* emb, int64_t emb_ld, const int64_t* h_extras, int n_extras,
+                        const float* dense, int64_t dense_ld, int n_dense, int dense_col,
+                        void* workspace, int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R12/R14 fused model front ends ------------------------------------------
  * gather -> x=[dense, embed] -> FM (DeepFM, DL/model/deepFM.py:24-28) or L cross
  * layers (DCN, DL/model/dcn.py:25-29) in ONE kernel; the gathered rows are

@@ -273,6 +273,7 @@ class Attention(Layer):
         self.precision = precision          # 'tf32': tcgen05 unit (csrc/din_tc.cu) when the shape fits; 'fp32': CUDA cores
         self._descs = None
         self._tc = None
+        self._fwd = None
 
     def build(self, input_shape):
         q_shape, k_shape = input_shape[0], input_shape[1]
@@ -367,6 +368,49 @@ class Attention(Layer):
                   cand_ld, B, T, arr, len(arr), ptr(self.out_kernel), ptr(self.out_bias), ptr(att), att.stride(0),
                   ptr(item), item.stride(0), ptr(check_flag), stream_ptr())
         return att, item
+
+    def front_fits(self, T, K):
+        """Does ctrhot_din_fwd_tf32 (the one-launch DIN front end) take this unit at history length T, key width K?"""
+        if not (self.precision == "tf32" and self.activation == "prelu" and len(self.layers) == 2):
+            return False
+        h1, h2 = self.hidden_units
+        return _lib.load().ctrhot_din_fwd_pack_bytes(T, K, h1, h2) > 0
+
+    def front(self, table, hist_ids, cand_ids, emb, extras=(), dense=None, dense_col=0, check_flag=None):
+        """DIN.call's front end in ONE launch: ``emb[:, :K]`` = attention output, ``emb[:, K:2K]`` = candidate rows,
+        ``extras`` = [(table [rows, dim], ids [B,1], first column)] other sparse lookups, ``dense`` [B, n] copied to
+        ``emb[:, dense_col:]`` (DL/model/din.py:56-90; csrc/din_fwd.cu).  ``emb`` is a [B, ld] matrix with ld % 4 == 0."""
+        hist_ids, kind, hist_ld = ids_arg(hist_ids)
+        cand_ids, kind2, cand_ld = ids_arg(cand_ids)
+        if kind2 != kind:
+            cand_ids = cand_ids.to(hist_ids.dtype)
+        B, T = hist_ids.shape
+        V, K = table.shape
+        h1, h2 = self.hidden_units
+        arr, _keep = self.descs()
+        if self._fwd is None or self._fwd[0] != (self._version, T, K):
+            nbytes = _lib.load().ctrhot_din_fwd_pack_bytes(T, K, h1, h2)
+            if nbytes <= 0:
+                raise ValueError("Attention.front: this shape needs call_gather (see front_fits)")
+            blob = torch.empty(nbytes // 4, dtype=torch.float32, device=self.device)
+            _lib.call("ctrhot_din_fwd_pack", arr, len(arr), ptr(self.out_kernel), ptr(self.out_bias), T, K, ptr(blob),
+                      stream_ptr())
+            self._fwd = ((self._version, T, K), blob)
+        ex = np.zeros((max(len(extras), 1), 6), dtype=np.int64)
+        keep = []
+        for i, (tab, ids, col) in enumerate(extras):
+            ids, k3, ld3 = ids_arg(ids)
+            if k3 != kind:
+                ids = ids.to(hist_ids.dtype)
+            keep.append(ids)
+            ex[i] = (tab.data_ptr(), tab.shape[0], tab.shape[1], ids.data_ptr(), ids.stride(0), col)
+        ws = torch.empty(_lib.query("ctrhot_din_fwd_workspace_bytes", B, h1) // 4 + 4, dtype=torch.float32, device=self.device)
+        n_dense = 0 if dense is None else dense.shape[1]
+        _lib.call("ctrhot_din_fwd_tf32", ptr(table), V, K, ptr(hist_ids), kind, hist_ld, ptr(cand_ids), cand_ld, B, T,
+                  ptr(self._fwd[1]), h1, h2, ptr(emb), emb.stride(0), ex.ctypes.data, len(extras),
+                  ptr(dense) if n_dense else None, dense.stride(0) if n_dense else 0, n_dense, dense_col,
+                  ptr(ws), ws.numel() * 4, ptr(check_flag), stream_ptr())
+        return emb
 
 
 # ---------------------------------------------------------------- SURVEY 8(f) rank 4: the remaining towers

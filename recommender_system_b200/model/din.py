@@ -97,6 +97,18 @@ class DIN(Model):
         a = np.asarray(v)
         return a
 
+    def _gather1(self, key, tab, ids, out_view, out_ld, flag):
+        """One table's rows for one id per row of ``ids`` [n, 1] into ``out_view`` (row stride ``out_ld``): ctrhot_gather_f32."""
+        from ..layer.base import ids_arg
+        if not hasattr(self, "_row_offs"):
+            self._row_offs = {}
+        cached = self._row_offs.get(key)               # built once: torch.tensor(..., device=) is a blocking copy
+        if cached is None or cached[0] != tab.shape[0]:
+            cached = self._row_offs[key] = (tab.shape[0], torch.tensor([0, tab.shape[0]], dtype=torch.int64, device=self.device))
+        ids2, kind, ld = ids_arg(ids)
+        _lib.call("ctrhot_gather_f32", ptr(tab), ptr(cached[1]), 1, tab.shape[1], ptr(ids2), kind, ld, ids2.shape[0], 0, 0, 0,
+                  ptr(out_view), out_ld, ptr(flag), stream_ptr())
+
     def call(self, inputs, training=None, mask=None):
         dev = self.device
         if not self.att_layer.built:
@@ -113,50 +125,48 @@ class DIN(Model):
         ld = (self.dcat + 3) // 4 * 4                           # 16-byte aligned rows for the tower kernel
         emb = torch.empty((B, ld), dtype=torch.float32, device=dev)[:, :self.dcat]
         K = self.K
-        direct = self.behavior_num == 1 and K % 4 == 0
-        if direct:
-            # the attention kernel writes [att | item] straight into the tower's input matrix (din.py:84-90's concat)
-            self.att_layer.call_gather(self.embed_seq_layers[0], hist[0], cand[:, 0:1], flag, out=(emb[:, :K], emb[:, K:2 * K]))
-        elif self.behavior_num == 1:
-            att, item = self.att_layer.call_gather(self.embed_seq_layers[0], hist[0], cand[:, 0:1], flag)
-        else:
-            keys, items = [], []
-            for i, tab in enumerate(self.embed_seq_layers):
-                h = hist[i].long()
-                c = cand[:, i].long()
-                if self.check and (int(h.min()) < 0 or int(h.max()) >= tab.shape[0] or int(c.min()) < 0
-                                   or int(c.max()) >= tab.shape[0]):
-                    raise IndexError("DIN: behaviour id out of range")
-                keys.append(tab[h])
-                items.append(tab[c])
-            key = torch.cat(keys, dim=-1)
-            item = torch.cat(items, dim=-1)
-            m = (hist[0] != 0).to(torch.float32)
-            att = self.att_layer([item, key, key, m])
-        if not direct:
-            emb[:, :K] = att
-            emb[:, K:2 * K] = item
-        col = 2 * K
-        for i, (f, tab) in enumerate(zip(self.other_sparse, self.embed_sparse_layers)):
-            ids = _ids_to_device(self._col(inputs, f["feat"]), dev)
-            ids = ids.reshape(B, -1)[:, :1]
-            e = tab.shape[1]
-            if not hasattr(self, "_row_offs"):
-                self._row_offs = {}
-            cached = self._row_offs.get(i)                 # built once: torch.tensor(..., device=) is a blocking copy
-            if cached is None or cached[0] != tab.shape[0]:
-                cached = self._row_offs[i] = (tab.shape[0], torch.tensor([0, tab.shape[0]], dtype=torch.int64, device=dev))
-            row_off = cached[1]
-            from ..layer.base import ids_arg
-            ids2, kind, ld = ids_arg(ids)
-            view = emb[:, col:col + e]
-            _lib.call("ctrhot_gather_f32", ptr(tab), ptr(row_off), 1, e, ptr(ids2), kind, ld, B, 0, 0, 0, ptr(view),
-                      emb.stride(0), ptr(flag), stream_ptr())
-            col += e
+        T = hist[0].shape[1]
+        others = [_ids_to_device(self._col(inputs, f["feat"]), dev).reshape(B, -1)[:, :1] for f in self.other_sparse]
+        dense = None
         if self.dense_num:
-            dense = torch.cat([as_device_f32(self._col(inputs, f["feat"]), dev).reshape(B, -1)
-                               for f in self.dense_feature_columns], dim=-1)
-            emb[:, col:col + self.dense_num] = dense
+            cols = [as_device_f32(self._col(inputs, f["feat"]), dev).reshape(B, -1) for f in self.dense_feature_columns]
+            dense = cols[0] if len(cols) == 1 else torch.cat(cols, dim=-1)
+        if self.behavior_num == 1 and len(others) <= 8 and self.att_layer.front_fits(T, K):
+            # ONE launch: candidate / history / other lookups, the attention unit and the dense columns write the tower's
+            # input matrix [att | item | other | dense] (din.py:84-90's concat) -- csrc/din_fwd.cu
+            extras, col = [], 2 * K
+            for tab, ids in zip(self.embed_sparse_layers, others):
+                extras.append((tab, ids, col))
+                col += tab.shape[1]
+            self.att_layer.front(self.embed_seq_layers[0], hist[0], cand[:, 0:1], emb, extras, dense, col, flag)
+        else:
+            if self.behavior_num == 1 and K % 4 == 0:
+                # the attention kernel writes [att | item] straight into the tower's input matrix
+                self.att_layer.call_gather(self.embed_seq_layers[0], hist[0], cand[:, 0:1], flag, out=(emb[:, :K], emb[:, K:2 * K]))
+            elif self.behavior_num == 1:
+                att, item = self.att_layer.call_gather(self.embed_seq_layers[0], hist[0], cand[:, 0:1], flag)
+                emb[:, :K] = att
+                emb[:, K:2 * K] = item
+            else:
+                # several behaviour features: key = concat of their rows (din.py:76-79).  Each table's rows go through the
+                # gather kernel into its columns of key [B*T, K] and of the item block of emb; bad ids raise the flag
+                key = torch.empty((B, T, K), dtype=torch.float32, device=dev)
+                off = 0
+                for i, tab in enumerate(self.embed_seq_layers):
+                    e = tab.shape[1]
+                    self._gather1(i + 1000, tab, hist[i].reshape(B * T, 1), key.view(B * T, K)[:, off:off + e], K, flag)
+                    self._gather1(i + 1000, tab, cand[:, i:i + 1], emb[:, K + off:K + off + e], emb.stride(0), flag)
+                    off += e
+                m = (hist[0] != 0).to(torch.float32)
+                att = self.att_layer([emb[:, K:2 * K], key, key, m])
+                emb[:, :K] = att
+            col = 2 * K
+            for i, (tab, ids) in enumerate(zip(self.embed_sparse_layers, others)):
+                e = tab.shape[1]
+                self._gather1(i, tab, ids, emb[:, col:col + e], emb.stride(0), flag)
+                col += e
+            if dense is not None:
+                emb[:, col:col + self.dense_num] = dense
         self.stack.set_layers(self._tower_layers(), self._version)
         out = self.stack.run(emb, final_sigmoid=True)
         if self.check:
