@@ -25,8 +25,9 @@ def main(specs):
     others = [os.path.join(B.OBJ, s[:-3] + ".o") for s in B._sources() if s != src_name]
     for spec in specs:
         tag = spec.replace("=", "").replace(",", "_")
-        defs = [(("-DFU_TRACE" if src_name == "fused.cu" else "-DDT_TRACE") if kv == "TRACE=1" else "-DDT_FIXED_ORDER" if kv == "FIXED=1" else "-DDT_OLD_WSUM" if kv == "OLDW=1" else "-DDT_LATE_ARRIVE" if kv == "LATE=1" else "-DDT_OLD_STAGER" if kv == "OLDS=1"
+        defs = [("-D" + kv[2:]) if kv.startswith("D:") else (("-DFU_TRACE" if src_name == "fused.cu" else "-DDT_TRACE") if kv == "TRACE=1" else "-DDT_FIXED_ORDER" if kv == "FIXED=1" else "-DDT_OLD_WSUM" if kv == "OLDW=1" else "-DDT_LATE_ARRIVE" if kv == "LATE=1" else "-DDT_OLD_STAGER" if kv == "OLDS=1"
                  else "-DFU_%s_=%s" % tuple(kv.split("="))) for kv in spec.split(",")]
+        tag = tag.replace("D:", "")
         obj = os.path.join(OUT, "%s_%s.o" % (src_name[:-3], tag))
         tag = src_name[:-3] + "_" + tag if src_name != "fused.cu" else tag
         lib = os.path.join(OUT, "libctrhot_%s.so" % tag)

@@ -152,6 +152,13 @@ __device__ __forceinline__ void df_ld16_nowait(uint32_t taddr, uint32_t (&r)[16]
         "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void df_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+         "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
 __device__ __forceinline__ void df_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float df_prelu(float v, float a) { return fmaxf(v, 0.f) + a * fminf(v, 0.f); }
 // round-to-nearest (ties away) TF32 of a finite value
@@ -193,9 +200,9 @@ __host__ __device__ inline DfSmem df_smem(const DfShape& s, int nraw) {
   m.stage0 = o; o += (uint32_t)nraw * m.stage_bytes;
   m.al1 = o; o += (uint32_t)s.T * s.N1p * 4u;
   m.al2 = o; o += (uint32_t)s.T * s.N2p * 4u;
-  m.small = o; o += (uint32_t)(2 * s.N2p + 4 + DF_BM + 16 + 4 * DF_BM + 64) * 4u;   // b2 | w3 | b3 | P[128] | red[16] | part[512] | row0[64]
+  m.small = o; o += (uint32_t)(2 * s.N2p + 4 + 2 * DF_BM + 16 + 4 * DF_BM + 64 + 4) * 4u;   // b2 | w3 | b3 | P[2][128] | red[16] | part[512] | row0[64] | aux[4]
   o = (o + 15u) & ~15u;
-  m.bars = o; o += 8u * (2 * DF_NRAW + 4 + 4 * DF_NSLOT) + 16u;
+  m.bars = o; o += 8u * (2 * DF_NRAW + 4 + 4 + 4 * DF_NSLOT) + 16u;
   // the layer-1 MMA reads 128 rows from every key chunk: the rows past SR of the LAST stage's last chunk must still be inside
   // the allocation (their contents are never used)
   const uint32_t reach = m.stage0 + (uint32_t)(nraw - 1) * m.stage_bytes + (uint32_t)(s.nchK - 1) * (uint32_t)s.SR * 128u + DF_BM * 128u;
@@ -203,11 +210,27 @@ __host__ __device__ inline DfSmem df_smem(const DfShape& s, int nraw) {
   return m;
 }
 
+#ifndef DF_SKIP_PAD
+#define DF_SKIP_PAD 1      // 1: rows of padding positions are not copied at all; 0: zero-fill copies (src-size 0)
+#endif
+#ifndef DF_SLEEP_
+#define DF_SLEEP_ 0        // ns of back-off between two polls of an mbarrier (0: spin on try_wait)
+#endif
+__device__ __forceinline__ void df_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) { if (DF_SLEEP_ > 0) __nanosleep(DF_SLEEP_); }
+}
 #ifdef DF_TRACE
 // tuning builds only: clock64 of pipeline events of CTA 0, [event][sample]
-__device__ long long df_trace[10][128];
-#define DF_MARK(ev, i) do { if (blockIdx.x == 0 && (i) < 128 && (threadIdx.x & 31) == 0) df_trace[ev][i] = clock64(); } while (0)
+__device__ long long df_trace[14][128];
+#ifndef DF_TRACE_CTA
+#define DF_TRACE_CTA 0
+#endif
+#define DF_MARK(ev, i) do { if (blockIdx.x == DF_TRACE_CTA && (i) < 128 && (threadIdx.x & 31) == 0) df_trace[ev][i] = clock64(); } while (0)
+__device__ unsigned long long df_cta[148][4];          // per CTA: globaltimer (ns) at kernel start, prologue end, last att, exit
+__device__ __forceinline__ unsigned long long df_gt() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define DF_CTA(k) do { if (threadIdx.x == 0 && blockIdx.x < 148) df_cta[blockIdx.x][k] = df_gt(); } while (0)
 #else
+#define DF_CTA(k) do { } while (0)
 #define DF_MARK(ev, i) do { } while (0)
 #endif
 
@@ -225,8 +248,9 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const uint32_t bars = base + mp.bars;
   auto full_raw = [&](int i) { return bars + 8u * i; };
-  auto raw_free = [&](int i) { return bars + 8u * (DF_NRAW + i); };
-  const uint32_t mb = bars + 8u * (2 * DF_NRAW);
+  auto p_full = [&](int i) { return bars + 8u * (DF_NRAW + i); };          // softmax weights of sample i in s_P[i & 1]
+  auto p_free = [&](int i) { return bars + 8u * (DF_NRAW + 2 + i); };
+  const uint32_t mb = bars + 8u * (2 * DF_NRAW + 4);
   auto ws_full = [&](int i) { return mb + 8u * i; };
   auto ws_free = [&](int i) { return mb + 8u * (2 + i); };
   auto d1_full = [&](int i) { return mb + 8u * (4 + i); };
@@ -237,13 +261,15 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
   volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(bp + (slot_addr - base));
   float* f_small = reinterpret_cast<float*>(bp + mp.small);
   float* s_b2 = f_small; float* s_w3 = s_b2 + s.N2p; float* s_b3 = s_w3 + s.N2p;
-  float* s_P = s_b3 + 4; float* s_red = s_P + DF_BM; float* s_part = s_red + 16;
-  float* s_row0 = s_part + 4 * DF_BM;            // table row 0: the key of every padding position (history id 0)
+  float* s_P = s_b3 + 4; float* s_red = s_P + 2 * DF_BM; float* s_part = s_red + 16;   // s_P: two samples
+  float* s_row0 = s_part + 4 * DF_BM;
+  float* s_aux = s_row0 + 64;                   // [2][2]: 1 / sum, all-masked flag            // table row 0: the key of every padding position (history id 0)
   const int T = s.T, K = s.K;
   const uint32_t keys_bytes = (uint32_t)s.nchK * (uint32_t)s.SR * 128u;   // header offset inside a stage
 
   if (tid == 0) {
-    for (int i = 0; i < DF_NRAW; ++i) { mbar_init(full_raw(i), 256); mbar_init(raw_free(i), 128); }
+    for (int i = 0; i < DF_NRAW; ++i) mbar_init(full_raw(i), 256);
+    for (int i = 0; i < 2; ++i) { mbar_init(p_full(i), 128); mbar_init(p_free(i), 128); }
     for (int i = 0; i < 2; ++i) { mbar_init(ws_full(i), DF_NBLD); mbar_init(ws_free(i), 1); }
     for (int i = 0; i < DF_NSLOT; ++i) {
       mbar_init(d1_full(i), 1); mbar_init(h1_ready(i), 128); mbar_init(d2_full(i), 1); mbar_init(d2_free(i), 128);
@@ -273,20 +299,30 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
   const uint32_t tmem_base = *slot_ptr;
   const int64_t n_my = (p.B > blockIdx.x) ? (p.B - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
+  if (tid == 0) DF_MARK(7, 0);
+  DF_CTA(0);
   // ================================================================ prologue (all warps): per-sample lookups and u
-  // For this CTA's samples, PB at a time: ids -> candidate rows (to emb[:, K:2K] and to shared memory) + other-feature rows and
+  // For this CTA's samples, PB at a time: ids -> candidate rows (to emb[:, K:2K] and to shared memory), other-feature rows and
   // dense columns (to emb) -> u = q (W1a + W1c) + b1 in fp32 (to the workspace; the gather warps fetch it back per sample).
-  // The key stages are not in use yet: they hold the candidate rows and the ids.
+  // The key stages and the Ws buffers are not in use yet: they hold the candidate rows, the ids and Wq.
+  // (Everything in this kernel is written as ROLLED loops on purpose: the first version, unrolled the usual way, was 132 KB of
+  // SASS with a hot set of ~64 KB, and ran at 77 % instruction-cache hit rate with the GPC-level instruction cache at 81 % of
+  // its request peak -- instruction fetch, not any pipe, bounded it.  profiles/r02_din_fwd.md.)
   {
     float* sq = reinterpret_cast<float*>(bp + mp.stage0);
     const int QS = K + 4, nf = 1 + p.n_extra;
     int PB = (int)(((uint32_t)nraw * mp.stage_bytes) / (uint32_t)(QS * 4 + nf * 4));
     if (PB > DF_BM) PB = DF_BM;
+    if (PB >= 4) PB &= ~3;                                  // the u tiles take four samples at a time
     int32_t* pid = reinterpret_cast<int32_t*>(sq + (size_t)PB * QS);
     const int N1p = s.N1p;
-    const int groups = DF_THREADS / N1p, un = tid % N1p, ug = tid / N1p;
+    float* sWq = reinterpret_cast<float*>(bp + mp.ws);
+    for (int i = tid; i < K * N1p / 4; i += DF_THREADS)
+      reinterpret_cast<float4*>(sWq)[i] = __ldg(reinterpret_cast<const float4*>(p.packed + s.o_wq) + i);
+#pragma unroll 1
     for (int64_t i0 = 0; i0 < n_my; i0 += PB) {
       const int ns = (int)((n_my - i0 < PB) ? (n_my - i0) : PB);
+#pragma unroll 1
       for (int e = tid; e < ns * nf; e += DF_THREADS) {
         const int f = e / ns, si = e - f * ns;
         const int64_t b = blockIdx.x + (i0 + si) * (int64_t)gridDim.x;
@@ -300,6 +336,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       __syncthreads();
       {                                                       // candidate rows, 16 bytes per element, four loads in flight
         const int q4n = K / 4, n_el = ns * q4n;
+#pragma unroll 1
         for (int e0 = 0; e0 < n_el; e0 += DF_THREADS * 4) {
           float4 v[4];
 #pragma unroll
@@ -307,9 +344,8 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
             const int e = e0 + tid + DF_THREADS * u;
             v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (e < n_el) {
-              const int si = e / q4n, c4 = e - si * q4n;
-              const int32_t id = pid[si];
-              if (id >= 0) v[u] = __ldg(reinterpret_cast<const float4*>(p.table + (int64_t)id * K) + c4);
+              const int32_t id = pid[e / q4n];
+              if (id >= 0) v[u] = __ldg(reinterpret_cast<const float4*>(p.table + (int64_t)id * K) + (e % q4n));
             }
           }
 #pragma unroll
@@ -324,128 +360,183 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
           }
         }
       }
+#pragma unroll 1
       for (int f = 0; f < p.n_extra; ++f) {                   // other sparse features: Embedding rows straight into emb
         const float* tab = p.extra[f].table;
         const int dim = p.extra[f].dim, col = p.extra[f].col, n_el = ns * dim;
         const int32_t* idf = pid + (f + 1) * PB;
-        for (int e0 = 0; e0 < n_el; e0 += DF_THREADS * 8) {
-          float v[8];
+#pragma unroll 1
+        for (int e0 = 0; e0 < n_el; e0 += DF_THREADS * 4) {
+          float v[4];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
+          for (int u = 0; u < 4; ++u) {
             const int e = e0 + tid + DF_THREADS * u;
             v[u] = 0.f;
             if (e < n_el) {
-              const int si = e / dim, c = e - si * dim;
+              const int si = e / dim;
               const int32_t id = idf[si];
-              if (id >= 0) v[u] = ldg_nc_f1(tab + (int64_t)id * dim + c);
+              if (id >= 0) v[u] = ldg_nc_f1(tab + (int64_t)id * dim + (e - si * dim));
             }
           }
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
+          for (int u = 0; u < 4; ++u) {
             const int e = e0 + tid + DF_THREADS * u;
             if (e < n_el) {
-              const int si = e / dim, c = e - si * dim;
+              const int si = e / dim;
               const int64_t b = blockIdx.x + (i0 + si) * (int64_t)gridDim.x;
-              p.emb[b * p.emb_ld + col + c] = v[u];
+              p.emb[b * p.emb_ld + col + (e - si * dim)] = v[u];
             }
           }
         }
       }
+#pragma unroll 1
       for (int e = tid; e < ns * p.n_dense; e += DF_THREADS) { // dense columns
         const int si = e / p.n_dense, c = e - si * p.n_dense;
         const int64_t b = blockIdx.x + (i0 + si) * (int64_t)gridDim.x;
         p.emb[b * p.emb_ld + p.dense_col + c] = __ldg(p.dense + b * p.dense_ld + c);
       }
       __syncthreads();
-      if (ug < groups) {                                      // u[s][n]: thread = (column n, sample group), Wq read once per (c, n)
-        constexpr int MAXS = 20;
-        const int per = (ns + groups - 1) / groups;
-        const float* Wq = p.packed + s.o_wq;
-        float acc[MAXS];
-        const float bias = __ldg(p.packed + s.o_b1 + un);
+      // u[s][n] = b1[n] + sum_c q_s[c] Wq[c][n]: a 4-sample x 4-column tile per thread (8 shared-memory loads per 64 FMA; one
+      // (sample, column) per thread made this loop shared-memory-bound: 22 K wavefronts per batch)
+      {
+        const int n4n = N1p / 4, n_tiles = ((ns + 3) / 4) * n4n;
+#pragma unroll 1
+        for (int e = tid; e < n_tiles; e += DF_THREADS) {
+          const int s4 = e / n4n, n0 = 4 * (e - s4 * n4n);
+          const float4 bias = __ldg(reinterpret_cast<const float4*>(p.packed + s.o_b1 + n0));
+          float4 acc[4];
 #pragma unroll
-        for (int i = 0; i < MAXS; ++i) acc[i] = bias;
-        for (int c0 = 0; c0 < K; c0 += 4) {
-          float w[4];
+          for (int r = 0; r < 4; ++r) acc[r] = bias;
+          const float* q0 = sq + (size_t)(4 * s4) * QS;      // rows past ns hold stale (finite or not) data: never stored
+#pragma unroll 1
+          for (int c0 = 0; c0 < K; c0 += 4) {
+            float4 w[4], q[4];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) w[u] = __ldg(Wq + (size_t)(c0 + u) * N1p + un);
+            for (int u = 0; u < 4; ++u) w[u] = *reinterpret_cast<const float4*>(sWq + (c0 + u) * N1p + n0);
 #pragma unroll
-          for (int i = 0; i < MAXS; ++i) {
-            const int si = ug * per + i;
-            if (i < per && si < ns) {
-              const float4 q = *reinterpret_cast<const float4*>(sq + (size_t)si * QS + c0);
-              acc[i] = fmaf(q.x, w[0], acc[i]); acc[i] = fmaf(q.y, w[1], acc[i]);
-              acc[i] = fmaf(q.z, w[2], acc[i]); acc[i] = fmaf(q.w, w[3], acc[i]);
+            for (int r = 0; r < 4; ++r) q[r] = *reinterpret_cast<const float4*>(q0 + (size_t)r * QS + c0);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              acc[r].x = fmaf(q[r].x, w[0].x, acc[r].x); acc[r].y = fmaf(q[r].x, w[0].y, acc[r].y);
+              acc[r].z = fmaf(q[r].x, w[0].z, acc[r].z); acc[r].w = fmaf(q[r].x, w[0].w, acc[r].w);
+              acc[r].x = fmaf(q[r].y, w[1].x, acc[r].x); acc[r].y = fmaf(q[r].y, w[1].y, acc[r].y);
+              acc[r].z = fmaf(q[r].y, w[1].z, acc[r].z); acc[r].w = fmaf(q[r].y, w[1].w, acc[r].w);
+              acc[r].x = fmaf(q[r].z, w[2].x, acc[r].x); acc[r].y = fmaf(q[r].z, w[2].y, acc[r].y);
+              acc[r].z = fmaf(q[r].z, w[2].z, acc[r].z); acc[r].w = fmaf(q[r].z, w[2].w, acc[r].w);
+              acc[r].x = fmaf(q[r].w, w[3].x, acc[r].x); acc[r].y = fmaf(q[r].w, w[3].y, acc[r].y);
+              acc[r].z = fmaf(q[r].w, w[3].z, acc[r].z); acc[r].w = fmaf(q[r].w, w[3].w, acc[r].w);
             }
           }
-        }
 #pragma unroll
-        for (int i = 0; i < MAXS; ++i) {
-          const int si = ug * per + i;
-          if (i < per && si < ns) {
-            const int64_t b = blockIdx.x + (i0 + si) * (int64_t)gridDim.x;
-            p.U[b * N1p + un] = acc[i];
+          for (int r = 0; r < 4; ++r) {
+            const int si = 4 * s4 + r;
+            if (si < ns) {
+              const int64_t b = blockIdx.x + (i0 + si) * (int64_t)gridDim.x;
+              *reinterpret_cast<float4*>(p.U + b * N1p + n0) = acc[r];
+            }
           }
         }
       }
       __syncthreads();
     }
   }
+  // Rows of padding positions (history id 0) are never fetched and never used (softmax weight exactly 0; an all-padding history
+  // is answered with table row 0 directly): what the stage holds there must only be finite -- zeros now, stale keys later.
+  for (uint32_t i = tid; i < (uint32_t)nraw * mp.stage_bytes / 16u; i += DF_THREADS)
+    df_sts128(base + mp.stage0 + 16u * i, 0.f, 0.f, 0.f, 0.f);
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (tid == 0) DF_MARK(8, 0);
+  DF_CTA(1);
 
   if (warp >= 4 && warp < 8) {
     // ================================================================ gather
     // Thread tg fetches the history id of row tg (two samples ahead); the 128 ids go through the stage header (the mask needs
     // them there anyway); then PPR adjacent threads copy one key row together (coalesced 16-byte pieces) into the swizzled
-    // K-major layout the layer-1 MMA reads.
+    // K-major layout the layer-1 MMA reads.  The stage's LAST reader is this warp group itself: before it refills a stage it
+    // forms att(j) = (1 / sum) sum_t P_t k_t of the sample j that holds it (no "stage free" barrier).
     const int tg = tid - 128;
     const int PPR = K / 4;                                   // 16-byte pieces per key row (8 or 16)
     const int c = tg % PPR, rsub = tg / PPR, rpp = DF_BM / PPR;  // this thread: piece c of rows rsub + rpp * j, j < PPR
     const uint32_t rowbytes = (uint32_t)K * 4u;
     const uint32_t chunk = (uint32_t)(c >> 3) * ((uint32_t)s.SR * 128u), pc = (uint32_t)(c & 7);
+    const int G = rpp;                                       // weighted sum: thread = (four columns 4 c .., rows rsub, rsub + G, ...)
+    const uint8_t* ksub = bp + mp.stage0 + chunk;
+    auto finish = [&](int64_t j, int stj) {
+      const int pb = (int)(j & 1);
+      const int64_t b = blockIdx.x + j * gridDim.x;
+      df_wait(p_full(pb), (uint32_t)((j >> 1) & 1));
+      const float* P = s_P + pb * DF_BM;
+      const uint8_t* kt = ksub + (uint32_t)stj * mp.stage_bytes;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+      for (int r = rsub; r < T; r += G) {
+        const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4));
+        const float p0 = P[r];
+        a.x = fmaf(p0, k0.x, a.x); a.y = fmaf(p0, k0.y, a.y); a.z = fmaf(p0, k0.z, a.z); a.w = fmaf(p0, k0.w, a.w);
+      }
+      *reinterpret_cast<float4*>(s_part + (size_t)rsub * K + 4 * c) = a;
+      const float inv = s_aux[2 * pb], all_masked = s_aux[2 * pb + 1];
+      named_bar_sync(2, 128);                                // partial sums complete; every thread is done with the stage and P
+      mbar_arrive(p_free(pb));
+      if (tg < K) {
+        float o = 0.f;
+#pragma unroll 4
+        for (int gg = 0; gg < G; ++gg) o += s_part[gg * K + tg];
+        // every position masked: the softmax is uniform over T copies of table row 0 (interaction.py:399-404)
+        p.emb[b * p.emb_ld + tg] = (all_masked != 0.f) ? s_row0[tg] : o * inv;
+      }
+      if (tg == 0) DF_MARK(9, j);
+    };
     auto fetch = [&](int64_t i) -> int32_t {
       if (i >= n_my || tg >= T) return 0;
       const int64_t b = blockIdx.x + i * gridDim.x;
       return __ldg(static_cast<const int32_t*>(p.hist_ids) + b * p.hist_ld + tg);
     };
-    int st = 0; uint32_t sph = 0;
-    auto issue = [&](int64_t i, int32_t raw_id) {
+    int st = 0;
+    int32_t ra = fetch(0), rb = fetch(1);
+#pragma unroll 1
+    for (int64_t i = 0; i < n_my; ++i) {
+      const int32_t rc = fetch(i + 2);
       const int64_t b = blockIdx.x + i * gridDim.x;
-      mbar_wait(raw_free(st), sph ^ 1u);
+      if (i >= nraw) finish(i - nraw, st);
       const uint32_t stage = base + mp.stage0 + (uint32_t)st * mp.stage_bytes;
       const uint32_t hdr = stage + keys_bytes;
       int32_t* ids_s = reinterpret_cast<int32_t*>(bp + (hdr - base));
       {
-        const int32_t id = (IDKIND == CTRHOT_IDS_I32) ? raw_id : __float2int_rz(__int_as_float(raw_id));
+        const int32_t id = (IDKIND == CTRHOT_IDS_I32) ? ra : __float2int_rz(__int_as_float(ra));
         const bool ok = tg >= T || (id >= 0 && (int64_t)id < p.V);
         if (!ok && p.err_flag) *p.err_flag = 1;
         ids_s[tg] = (tg < T) ? (ok ? id : -1) : 0;           // -1: out of range -> zero row, not masked
       }
-      named_bar_sync(2, 128);
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int r = rsub + rpp * j;
-        if (j < PPR && r < s.SR) {
-          const int32_t id = ids_s[r];
-          // id 0 = padding (masked: softmax weight exactly 0 unless the WHOLE history is padding): its key is table row 0,
-          // which epilogue 2 adds from smem in that one case; the stage row is zero-filled
-          const bool ok = r < T && id > 0;
-          cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
-                     reinterpret_cast<const char*>(p.table) + (ok ? (uint64_t)(uint32_t)id * rowbytes : 0ull) + (uint32_t)c * 16u,
-                     ok ? 16u : 0u);
-        }
+      named_bar_sync(2, 128);                                // (also: the final reduction of finish() has read s_part)
+      const char* src0 = reinterpret_cast<const char*>(p.table) + (uint32_t)c * 16u;
+#pragma unroll 2
+      for (int r = rsub; r < s.SR; r += rpp) {
+        const int32_t id = ids_s[r];
+        // id 0 = padding (masked: softmax weight exactly 0 unless the WHOLE history is padding): its key is table row 0,
+        // which is added from smem in that one case; the stage row is zero-filled
+        const bool ok = r < T && id > 0;
+        cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
+                   src0 + (ok ? (uint64_t)(uint32_t)id * rowbytes : 0ull), ok ? 16u : 0u);
       }
       if (tg < PPR) cp_async16(hdr + DF_HDR_Q + tg * 16u, p.emb + b * p.emb_ld + K + tg * 4, 16u);
       else if (tg < PPR + s.N1p / 4) cp_async16(hdr + DF_HDR_U + (tg - PPR) * 16u, p.U + b * s.N1p + (tg - PPR) * 4, 16u);
       cp_async_mbar_arrive_noinc(full_raw(st));
       mbar_arrive(full_raw(st));                             // releases the ids written with plain stores
       if (tg == 0) DF_MARK(0, i);
-      if (++st == nraw) { st = 0; sph ^= 1u; }
-    };
-    int32_t ra = fetch(0), rb = fetch(1), rc;
-    for (int64_t i = 0; i < n_my; i += 3) {
-      rc = fetch(i + 2); issue(i, ra);
-      if (i + 1 < n_my) { ra = fetch(i + 3); issue(i + 1, rb); }
-      if (i + 2 < n_my) { rb = fetch(i + 4); issue(i + 2, rc); }
+      if (++st == nraw) st = 0;
+      ra = rb; rb = rc;
+    }
+    {                                                        // the last nraw samples
+      int64_t j = n_my > nraw ? n_my - nraw : 0;
+      int stj = (int)(j % nraw);
+#pragma unroll 1
+      for (; j < n_my; ++j) {
+        finish(j, stj);
+        named_bar_sync(2, 128);                              // s_part is rewritten by the next finish()
+        if (++stj == nraw) stj = 0;
+      }
     }
   } else if (warp >= 8 && warp < 16) {
     // ================================================================ builders: Ws(i) = tf32((W1b - W1c) + diag(q_i) W1d)
@@ -464,13 +555,14 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
     const uint32_t dst0 = base + mp.ws + (uint32_t)(cq >> 3) * ((uint32_t)s.N1p * 128u);
     const uint32_t piece = (uint32_t)(cq & 7);
     int st = 0; uint32_t sph = 0;
+#pragma unroll 1
     for (int64_t i = 0; i < n_my; ++i) {
       const int wbuf = (int)(i & 1);
       const uint32_t hq = base + mp.stage0 + (uint32_t)st * mp.stage_bytes + keys_bytes + DF_HDR_Q;
-      mbar_wait(full_raw(st), sph);
+      df_wait(full_raw(st), sph);
       if (tb == 0) DF_MARK(1, i);
       const float4 q = df_lds128(hq + (uint32_t)cq * 16u);
-      mbar_wait(ws_free(wbuf), (uint32_t)((i >> 1) & 1) ^ 1u);
+      df_wait(ws_free(wbuf), (uint32_t)((i >> 1) & 1) ^ 1u);
       const uint32_t dst = dst0 + (uint32_t)wbuf * mp.ws_bytes;
 #pragma unroll
       for (int j = 0; j < DF_MAXPASS; ++j) {
@@ -492,7 +584,8 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
     // Whatever is ready goes first, finishing samples before starting new ones: L2(i2) needs H1(i2) and a free D2 slot;
     // L1(i1) needs Ws(i1) (which implies keys(i1)) and must not overwrite H1(i1 - NS) before L2(i1 - NS) was issued.
     int64_t i1 = 0, i2 = 0;
-    int slot1 = 0, slot2 = 0, st1 = 0; uint32_t ph1 = 0, ph2 = 0;
+    int slot1 = 0, slot2 = 0, st1 = 0; uint32_t ph2 = 0;
+#pragma unroll 1
     while (i2 < n_my) {
       bool did = false;
       if (i2 < i1) {
@@ -503,6 +596,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
           if (elect_one()) {
             const uint32_t a_t = tmem_base + (uint32_t)(slot2 * s.slot_cols);
             const uint32_t d_t = a_t + (uint32_t)s.N1p;
+#pragma unroll 1
             for (int kk = 0; kk < s.N1p / 8; ++kk) {
               const uint64_t db = make_desc_sw128(w2 + (uint32_t)(kk >> 2) * (uint32_t)s.N2p * 128u) + (uint64_t)(2 * (kk & 3));
               mma_tf32_ts(d_t, a_t + (uint32_t)(8 * kk), db, idesc2, (uint32_t)(kk != 0));
@@ -525,6 +619,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
             const uint32_t keys = base + mp.stage0 + (uint32_t)st1 * mp.stage_bytes;
             const uint32_t ws = base + mp.ws + (uint32_t)wbuf * mp.ws_bytes;
             const uint32_t d_t = tmem_base + (uint32_t)(slot1 * s.slot_cols);
+#pragma unroll 1
             for (int kk = 0; kk < K / 8; ++kk) {
               const uint64_t da = make_desc_sw128(keys + (uint32_t)(kk >> 2) * (uint32_t)s.SR * 128u) + (uint64_t)(2 * (kk & 3));
               const uint64_t db = make_desc_sw128(ws + (uint32_t)(kk >> 2) * (uint32_t)s.N1p * 128u) + (uint64_t)(2 * (kk & 3));
@@ -535,54 +630,50 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
           }
           __syncwarp();
           ++i1;
-          if (++slot1 == NS) { slot1 = 0; ph1 ^= 1u; }
+          if (++slot1 == NS) slot1 = 0;
           if (++st1 == nraw) st1 = 0;
         }
       }
     }
-    (void)ph1;
   } else if (warp < 4) {
     // ================================================================ epilogue 1 (warps 0-3): thread t = TMEM lane t
+    // 16 columns per step of a rolled loop; the next step's TMEM load is in flight while this one is processed in place.
     const int t = tid;
     const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
     const int tr = t < T ? t : 0;
     const float* al1 = reinterpret_cast<const float*>(bp + mp.al1) + (size_t)tr * s.N1p;
     const int x1 = df_alpha_sw(s.N1p, tr);
-    const bool exact = (s.h1 == s.N1p);
-    auto chunk = [&](uint32_t (&r)[16], int n0, const float* u, uint32_t d_t) {
-      float acc[16];
-#pragma unroll
-      for (int j = 0; j < 16; j += 4) {
-        const float4 uu = *reinterpret_cast<const float4*>(u + n0 + j);
-        const float4 aa = *reinterpret_cast<const float4*>(al1 + ((((n0 + j) >> 2) ^ x1) << 2));
-        acc[j + 0] = df_tf32(df_prelu(__uint_as_float(r[j + 0]) + uu.x, aa.x));
-        acc[j + 1] = df_tf32(df_prelu(__uint_as_float(r[j + 1]) + uu.y, aa.y));
-        acc[j + 2] = df_tf32(df_prelu(__uint_as_float(r[j + 2]) + uu.z, aa.z));
-        acc[j + 3] = df_tf32(df_prelu(__uint_as_float(r[j + 3]) + uu.w, aa.w));
-      }
-      if (!exact) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) if (n0 + j >= s.h1) acc[j] = 0.f;
-      }
-      tmem_st16(d_t + (uint32_t)n0, acc);
-    };
+    const int N1p = s.N1p, h1 = s.h1;
     int st = 0, slot = 0; uint32_t ph = 0;
+#pragma unroll 1
     for (int64_t i = 0; i < n_my; ++i) {
       const float* u = reinterpret_cast<const float*>(bp + mp.stage0 + (uint32_t)st * mp.stage_bytes + keys_bytes + DF_HDR_U);
-      mbar_wait(d1_full(slot), ph);
+      df_wait(d1_full(slot), ph);
       if (t == 0) DF_MARK(3, i);
       tc_fence_after();
       const uint32_t d_t = t_lane + (uint32_t)(slot * s.slot_cols);
-      uint32_t r0[16], r1[16];                              // two chunks in flight: load n+1 while n is processed
-      df_ld16_nowait(d_t, r0);
-      df_ld_wait();
-      for (int n0 = 0; n0 < s.N1p; n0 += 32) {
-        if (n0 + 16 < s.N1p) df_ld16_nowait(d_t + (uint32_t)(n0 + 16), r1);
-        chunk(r0, n0, u, d_t);
+      uint32_t a[16], nx[16];
+      df_ld16_nowait(d_t, nx);
+#pragma unroll 1
+      for (int n0 = 0; n0 < N1p; n0 += 16) {
         df_ld_wait();
-        if (n0 + 32 < s.N1p) df_ld16_nowait(d_t + (uint32_t)(n0 + 32), r0);
-        if (n0 + 16 < s.N1p) chunk(r1, n0 + 16, u, d_t);
-        df_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) a[j] = nx[j];
+        if (n0 + 16 < N1p) df_ld16_nowait(d_t + (uint32_t)(n0 + 16), nx);
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) {
+          const float4 uu = *reinterpret_cast<const float4*>(u + n0 + j);
+          const float4 aa = *reinterpret_cast<const float4*>(al1 + ((((n0 + j) >> 2) ^ x1) << 2));
+          a[j + 0] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 0]) + uu.x, aa.x)));
+          a[j + 1] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 1]) + uu.y, aa.y)));
+          a[j + 2] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 2]) + uu.z, aa.z)));
+          a[j + 3] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 3]) + uu.w, aa.w)));
+        }
+        if (n0 + 16 > h1) {                                   // zero the padding columns (they are layer 2's K padding)
+#pragma unroll
+          for (int j = 0; j < 16; ++j) if (n0 + j >= h1) a[j] = 0u;
+        }
+        df_st16(d_t + (uint32_t)n0, a);
       }
       tmem_st_wait();
       tc_fence_before();
@@ -592,42 +683,50 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       if (++slot == NS) { slot = 0; ph ^= 1u; }
     }
   } else {
-    // ================================================================ epilogue 2 (warps 17-20): scores, softmax, weighted sum
+    // ================================================================ epilogue 2 (warps 17-20): scores and softmax
+    // -> s_P[i & 1][t] = exp(s_t - max) (not normalised), s_aux[i & 1] = {1 / sum, "every position is masked"}; the weighted sum
+    // over the keys is the gather warps' last act on the stage before they refill it.
     const int q4 = warp & 3;
     const int t = q4 * 32 + lane;
     const uint32_t t_lane = tmem_base + ((uint32_t)(q4 * 32) << 16);
     const int tr = t < T ? t : 0;
     const float* al2 = reinterpret_cast<const float*>(bp + mp.al2) + (size_t)tr * s.N2p;
     const int x2 = df_alpha_sw(s.N2p, tr);
-    const int NQ = K / 4, G = DF_BM / NQ, cq = t % NQ, g = t / NQ;   // column quads, row groups
+    const int N2p = s.N2p;
+    const bool live = t < T;
     int st = 0, slot = 0; uint32_t ph = 0;
+#pragma unroll 1
     for (int64_t i = 0; i < n_my; ++i) {
-      const int64_t b = blockIdx.x + i * gridDim.x;
-      const uint32_t stage_off = mp.stage0 + (uint32_t)st * mp.stage_bytes;
-      const int32_t* ids_s = reinterpret_cast<const int32_t*>(bp + stage_off + keys_bytes);
-      mbar_wait(d2_full(slot), ph);
+      const int pb = (int)(i & 1);
+      const int32_t* ids_s = reinterpret_cast<const int32_t*>(bp + mp.stage0 + (uint32_t)st * mp.stage_bytes + keys_bytes);
+      df_wait(d2_full(slot), ph);
       if (lane == 0 && q4 == 0) DF_MARK(5, i);
       tc_fence_after();
       const uint32_t d_t = t_lane + (uint32_t)(slot * s.slot_cols + s.N1p);
       float sc = s_b3[0];
-      for (int n0 = 0; n0 < s.N2p; n0 += 16) {
-        float acc[16];
-        tmem_ld16(d_t + (uint32_t)n0, acc);
+      uint32_t v[16], nx[16];
+      df_ld16_nowait(d_t, nx);
+#pragma unroll 1
+      for (int n0 = 0; n0 < N2p; n0 += 16) {
+        df_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = nx[j];
+        if (n0 + 16 < N2p) df_ld16_nowait(d_t + (uint32_t)(n0 + 16), nx);
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
-          const float4 bb = *reinterpret_cast<const float4*>(s_b2 + n0 + j);
-          const float4 aa = *reinterpret_cast<const float4*>(al2 + ((((n0 + j) >> 2) ^ x2) << 2));
-          const float4 ww = *reinterpret_cast<const float4*>(s_w3 + n0 + j);
-          sc = fmaf(df_prelu(acc[j + 0] + bb.x, aa.x), ww.x, sc);
-          sc = fmaf(df_prelu(acc[j + 1] + bb.y, aa.y), ww.y, sc);
-          sc = fmaf(df_prelu(acc[j + 2] + bb.z, aa.z), ww.z, sc);
-          sc = fmaf(df_prelu(acc[j + 3] + bb.w, aa.w), ww.w, sc);
+          const int n = n0 + j;
+          const float4 bb = *reinterpret_cast<const float4*>(s_b2 + n);
+          const float4 aa = *reinterpret_cast<const float4*>(al2 + (((n >> 2) ^ x2) << 2));
+          const float4 ww = *reinterpret_cast<const float4*>(s_w3 + n);
+          sc = fmaf(df_prelu(__uint_as_float(v[j + 0]) + bb.x, aa.x), ww.x, sc);
+          sc = fmaf(df_prelu(__uint_as_float(v[j + 1]) + bb.y, aa.y), ww.y, sc);
+          sc = fmaf(df_prelu(__uint_as_float(v[j + 2]) + bb.z, aa.z), ww.z, sc);
+          sc = fmaf(df_prelu(__uint_as_float(v[j + 3]) + bb.w, aa.w), ww.w, sc);
         }
       }
       tc_fence_before();
       mbar_arrive(d2_free(slot));
       // mask (interaction.py:399-401: where(mask == 0, -2^32 + 1, s)), rows past T do not exist
-      const bool live = t < T;
       if (live && ids_s[t] == 0) sc = -4294967295.0f;
       if (!live) sc = -INFINITY;
       float m = sc;
@@ -640,40 +739,17 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       float sum = e;
 #pragma unroll
       for (int o = 16; o >= 1; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      df_wait(p_free(pb), (uint32_t)((i >> 1) & 1) ^ 1u);    // the gather warps are done with P(i - 2)
       if (lane == 0) s_red[4 + q4] = sum;
+      s_P[pb * DF_BM + t] = e;
       named_bar_sync(1, 128);
-      sum = (s_red[4] + s_red[5]) + (s_red[6] + s_red[7]);
-      s_P[t] = e / sum;
-      named_bar_sync(1, 128);
-      // att[c] = sum_t p_t k[t][c]: thread = (four columns 4 cq .., group g of rows t = g, g + G, ...)
-      {
-        const uint8_t* kt = bp + stage_off + (uint32_t)(cq >> 3) * ((uint32_t)s.SR * 128u);
-        const uint32_t pq = (uint32_t)(cq & 7);
-        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
-        int r = g;
-        for (; r + G < T; r += 2 * G) {
-          const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pq ^ (uint32_t)(r & 7)) << 4));
-          const float4 k1 = *reinterpret_cast<const float4*>(kt + (uint32_t)(r + G) * 128u + ((pq ^ (uint32_t)((r + G) & 7)) << 4));
-          const float p0 = s_P[r], p1 = s_P[r + G];
-          a0.x = fmaf(p0, k0.x, a0.x); a0.y = fmaf(p0, k0.y, a0.y); a0.z = fmaf(p0, k0.z, a0.z); a0.w = fmaf(p0, k0.w, a0.w);
-          a1.x = fmaf(p1, k1.x, a1.x); a1.y = fmaf(p1, k1.y, a1.y); a1.z = fmaf(p1, k1.z, a1.z); a1.w = fmaf(p1, k1.w, a1.w);
-        }
-        if (r < T) {
-          const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pq ^ (uint32_t)(r & 7)) << 4));
-          const float p0 = s_P[r];
-          a0.x = fmaf(p0, k0.x, a0.x); a0.y = fmaf(p0, k0.y, a0.y); a0.z = fmaf(p0, k0.z, a0.z); a0.w = fmaf(p0, k0.w, a0.w);
-        }
-        *reinterpret_cast<float4*>(s_part + (size_t)g * K + 4 * cq) = make_float4(a0.x + a1.x, a0.y + a1.y, a0.z + a1.z, a0.w + a1.w);
+      if (t == 0) {
+        s_aux[2 * pb] = 1.f / ((s_red[4] + s_red[5]) + (s_red[6] + s_red[7]));
+        s_aux[2 * pb + 1] = (m == -4294967295.0f) ? 1.f : 0.f;   // every position masked: uniform over T copies of table row 0
       }
-      named_bar_sync(1, 128);
-      mbar_arrive(raw_free(st));                             // keys no longer needed: the gather may refill the stage
-      if (t < K) {
-        float o = 0.f;
-        for (int gg = 0; gg < G; ++gg) o += s_part[gg * K + t];
-        // every position masked: the softmax is uniform over T copies of table row 0 (whose rows were not fetched)
-        if (m == -4294967295.0f) o += s_row0[t];
-        p.emb[b * p.emb_ld + t] = o;
-      }
+      // s_red[0..3] is next written after this barrier, s_red[4..7] after the next one, and thread 0 takes part in both:
+      // nobody overwrites what it is reading here
+      mbar_arrive(p_full(pb));
       if (lane == 0 && q4 == 0) DF_MARK(6, i);
       if (++st == nraw) st = 0;
       if (++slot == NS) { slot = 0; ph ^= 1u; }
@@ -681,6 +757,8 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
   }
   tc_fence_before();
   __syncthreads();
+  if (tid == 0) DF_MARK(13, 0);
+  DF_CTA(3);
   if (warp == 16) { tc_fence_after(); tmem_dealloc(tmem_base, 512u); }
 }
 
@@ -778,7 +856,10 @@ extern "C" int ctrhot_din_fwd_tf32(const float* table, int64_t V, int K, const v
 }
 
 #ifdef DF_TRACE
+extern "C" int ctrhot_debug_din_fwd_cta(unsigned long long* h_out) {
+  return cudaMemcpyFromSymbol(h_out, ctrhot::df_cta, sizeof(unsigned long long) * 148 * 4) == cudaSuccess ? 0 : -3;
+}
 extern "C" int ctrhot_debug_din_fwd_trace(long long* h_out) {
-  return cudaMemcpyFromSymbol(h_out, ctrhot::df_trace, sizeof(long long) * 10 * 128) == cudaSuccess ? 0 : -3;
+  return cudaMemcpyFromSymbol(h_out, ctrhot::df_trace, sizeof(long long) * 14 * 128) == cudaSuccess ? 0 : -3;
 }
 #endif
