@@ -32,7 +32,8 @@ namespace ctrhot {
 using namespace tc;
 
 constexpr int DF_BM = 128;
-constexpr int DF_THREADS = 21 * 32;
+constexpr int DF_THREADS = 24 * 32;          // (ptxas budgets registers for a multiple of 4 warps: 21 warps cost what 24 do)
+constexpr int DF_NSUM = 96;                  // threads of the weighted-sum group (warps 21-23)
 constexpr int DF_NRAW = 4;                   // key stages (fewer if shared memory is short)
 constexpr int DF_NSLOT = 4;                  // TMEM slots [D1/H1 | D2]
 constexpr int DF_NBLD = 256;                 // builder threads
@@ -250,6 +251,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
   auto full_raw = [&](int i) { return bars + 8u * i; };
   auto p_full = [&](int i) { return bars + 8u * (DF_NRAW + i); };          // softmax weights of sample i in s_P[i & 1]
   auto p_free = [&](int i) { return bars + 8u * (DF_NRAW + 2 + i); };
+  auto raw_free = [&](int i) { return bars + 8u * (DF_NRAW + 4 + i); };    // att of the stage's sample is formed: refill it
   const uint32_t mb = bars + 8u * (2 * DF_NRAW + 4);
   auto ws_full = [&](int i) { return mb + 8u * i; };
   auto ws_free = [&](int i) { return mb + 8u * (2 + i); };
@@ -269,7 +271,8 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
 
   if (tid == 0) {
     for (int i = 0; i < DF_NRAW; ++i) mbar_init(full_raw(i), 256);
-    for (int i = 0; i < 2; ++i) { mbar_init(p_full(i), 128); mbar_init(p_free(i), 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(p_full(i), 128); mbar_init(p_free(i), DF_NSUM); }
+    for (int i = 0; i < DF_NRAW; ++i) mbar_init(raw_free(i), DF_NSUM);
     for (int i = 0; i < 2; ++i) { mbar_init(ws_full(i), DF_NBLD); mbar_init(ws_free(i), 1); }
     for (int i = 0; i < DF_NSLOT; ++i) {
       mbar_init(d1_full(i), 1); mbar_init(h1_ready(i), 128); mbar_init(d2_full(i), 1); mbar_init(d2_free(i), 128);
@@ -460,46 +463,18 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
     const int c = tg % PPR, rsub = tg / PPR, rpp = DF_BM / PPR;  // this thread: piece c of rows rsub + rpp * j, j < PPR
     const uint32_t rowbytes = (uint32_t)K * 4u;
     const uint32_t chunk = (uint32_t)(c >> 3) * ((uint32_t)s.SR * 128u), pc = (uint32_t)(c & 7);
-    const int G = rpp;                                       // weighted sum: thread = (four columns 4 c .., rows rsub, rsub + G, ...)
-    const uint8_t* ksub = bp + mp.stage0 + chunk;
-    auto finish = [&](int64_t j, int stj) {
-      const int pb = (int)(j & 1);
-      const int64_t b = blockIdx.x + j * gridDim.x;
-      df_wait(p_full(pb), (uint32_t)((j >> 1) & 1));
-      const float* P = s_P + pb * DF_BM;
-      const uint8_t* kt = ksub + (uint32_t)stj * mp.stage_bytes;
-      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 2
-      for (int r = rsub; r < T; r += G) {
-        const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4));
-        const float p0 = P[r];
-        a.x = fmaf(p0, k0.x, a.x); a.y = fmaf(p0, k0.y, a.y); a.z = fmaf(p0, k0.z, a.z); a.w = fmaf(p0, k0.w, a.w);
-      }
-      *reinterpret_cast<float4*>(s_part + (size_t)rsub * K + 4 * c) = a;
-      const float inv = s_aux[2 * pb], all_masked = s_aux[2 * pb + 1];
-      named_bar_sync(2, 128);                                // partial sums complete; every thread is done with the stage and P
-      mbar_arrive(p_free(pb));
-      if (tg < K) {
-        float o = 0.f;
-#pragma unroll 4
-        for (int gg = 0; gg < G; ++gg) o += s_part[gg * K + tg];
-        // every position masked: the softmax is uniform over T copies of table row 0 (interaction.py:399-404)
-        p.emb[b * p.emb_ld + tg] = (all_masked != 0.f) ? s_row0[tg] : o * inv;
-      }
-      if (tg == 0) DF_MARK(9, j);
-    };
     auto fetch = [&](int64_t i) -> int32_t {
       if (i >= n_my || tg >= T) return 0;
       const int64_t b = blockIdx.x + i * gridDim.x;
       return __ldg(static_cast<const int32_t*>(p.hist_ids) + b * p.hist_ld + tg);
     };
-    int st = 0;
+    int st = 0; uint32_t sph = 0;
     int32_t ra = fetch(0), rb = fetch(1);
 #pragma unroll 1
     for (int64_t i = 0; i < n_my; ++i) {
       const int32_t rc = fetch(i + 2);
       const int64_t b = blockIdx.x + i * gridDim.x;
-      if (i >= nraw) finish(i - nraw, st);
+      df_wait(raw_free(st), sph ^ 1u);                       // warps 21-23 have formed att of the sample that held this stage
       const uint32_t stage = base + mp.stage0 + (uint32_t)st * mp.stage_bytes;
       const uint32_t hdr = stage + keys_bytes;
       int32_t* ids_s = reinterpret_cast<int32_t*>(bp + (hdr - base));
@@ -509,7 +484,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
         if (!ok && p.err_flag) *p.err_flag = 1;
         ids_s[tg] = (tg < T) ? (ok ? id : -1) : 0;           // -1: out of range -> zero row, not masked
       }
-      named_bar_sync(2, 128);                                // (also: the final reduction of finish() has read s_part)
+      named_bar_sync(2, 128);
       const char* src0 = reinterpret_cast<const char*>(p.table) + (uint32_t)c * 16u;
 #pragma unroll 2
       for (int r = rsub; r < s.SR; r += rpp) {
@@ -525,18 +500,8 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       cp_async_mbar_arrive_noinc(full_raw(st));
       mbar_arrive(full_raw(st));                             // releases the ids written with plain stores
       if (tg == 0) DF_MARK(0, i);
-      if (++st == nraw) st = 0;
+      if (++st == nraw) { st = 0; sph ^= 1u; }
       ra = rb; rb = rc;
-    }
-    {                                                        // the last nraw samples
-      int64_t j = n_my > nraw ? n_my - nraw : 0;
-      int stj = (int)(j % nraw);
-#pragma unroll 1
-      for (; j < n_my; ++j) {
-        finish(j, stj);
-        named_bar_sync(2, 128);                              // s_part is rewritten by the next finish()
-        if (++stj == nraw) stj = 0;
-      }
     }
   } else if (warp >= 8 && warp < 16) {
     // ================================================================ builders: Ws(i) = tf32((W1b - W1c) + diag(q_i) W1d)
@@ -682,7 +647,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       if (++st == nraw) st = 0;
       if (++slot == NS) { slot = 0; ph ^= 1u; }
     }
-  } else {
+  } else if (warp < 21) {
     // ================================================================ epilogue 2 (warps 17-20): scores and softmax
     // -> s_P[i & 1][t] = exp(s_t - max) (not normalised), s_aux[i & 1] = {1 / sum, "every position is masked"}; the weighted sum
     // over the keys is the gather warps' last act on the stage before they refill it.
@@ -753,6 +718,44 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       if (lane == 0 && q4 == 0) DF_MARK(6, i);
       if (++st == nraw) st = 0;
       if (++slot == NS) { slot = 0; ph ^= 1u; }
+    }
+  } else {
+    // ================================================================ weighted sum (warps 21-23): att(j) = (1 / sum) sum_t P_t k_t
+    // The stage's last reader: thread = (four columns 4 c .., rows rsub, rsub + G, ...); when it is done the gather may refill.
+    const int tq = tid - 21 * 32;
+    const int NQ = K / 4, c = tq % NQ, rsub = tq / NQ, G = DF_NSUM / NQ;
+    const uint32_t pc = (uint32_t)(c & 7);
+    const uint8_t* ksub = bp + mp.stage0 + (uint32_t)(c >> 3) * ((uint32_t)s.SR * 128u);
+    int stj = 0;
+#pragma unroll 1
+    for (int64_t j = 0; j < n_my; ++j) {
+      const int pb = (int)(j & 1);
+      const int64_t b = blockIdx.x + j * gridDim.x;
+      df_wait(p_full(pb), (uint32_t)((j >> 1) & 1));
+      const float* P = s_P + pb * DF_BM;
+      const uint8_t* kt = ksub + (uint32_t)stj * mp.stage_bytes;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+      for (int r = rsub; r < T; r += G) {
+        const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4));
+        const float p0 = P[r];
+        a.x = fmaf(p0, k0.x, a.x); a.y = fmaf(p0, k0.y, a.y); a.z = fmaf(p0, k0.z, a.z); a.w = fmaf(p0, k0.w, a.w);
+      }
+      const float inv = s_aux[2 * pb], all_masked = s_aux[2 * pb + 1];
+      named_bar_sync(3, DF_NSUM);                            // the previous sample's partial sums have been read
+      *reinterpret_cast<float4*>(s_part + (size_t)rsub * K + 4 * c) = a;
+      named_bar_sync(3, DF_NSUM);                            // partial sums complete; every thread is done with the stage and P
+      mbar_arrive(p_free(pb));
+      mbar_arrive(raw_free(stj));
+      if (tq < K) {
+        float o = 0.f;
+#pragma unroll 2
+        for (int gg = 0; gg < G; ++gg) o += s_part[gg * K + tq];
+        // every position masked: the softmax is uniform over T copies of table row 0 (interaction.py:399-404)
+        p.emb[b * p.emb_ld + tq] = (all_masked != 0.f) ? s_row0[tq] : o * inv;
+      }
+      if (tq == 0) DF_MARK(9, j);
+      if (++stj == nraw) stj = 0;
     }
   }
   tc_fence_before();
