@@ -37,8 +37,8 @@ constexpr int DF_NSUM = 96;                  // threads of the weighted-sum grou
 constexpr int DF_NRAW = 4;                   // key stages (fewer if shared memory is short)
 constexpr int DF_NSLOT = 4;                  // TMEM slots [D1/H1 | D2]
 constexpr int DF_NBLD = 256;                 // builder threads
-constexpr int DF_HDR_BYTES = 2048;           // per stage: ids[128] int32 | q[<=64] at 512 | u[<=96] at 1024   (keeps stages 1024-aligned)
-constexpr int DF_HDR_Q = 512, DF_HDR_U = 1024;
+constexpr int DF_HDR_BYTES = 2048;           // per stage: ids[128] int32 | q[<=64] at 512 | q of the NEXT sample at 768 | u[<=96] at 1024
+constexpr int DF_HDR_Q = 512, DF_HDR_QN = 768, DF_HDR_U = 1024;   // (2048 keeps the stages 1024-aligned)
 constexpr int DF_MAX_EXTRA = 8;
 constexpr int DF_MAXPASS = 6;                // builder passes: ceil(N1p / (256 / (K/4))) <= 6  (K = 64, N1p = 96)
 
@@ -212,7 +212,7 @@ __host__ __device__ inline DfSmem df_smem(const DfShape& s, int nraw) {
 }
 
 #ifndef DF_SKIP_PAD
-#define DF_SKIP_PAD 1      // 1: rows of padding positions are not copied at all; 0: zero-fill copies (src-size 0)
+#define DF_SKIP_PAD 0      // 1: padding positions (history id 0) cost no row copy, no epilogue arithmetic, no weighted-sum read
 #endif
 #ifndef DF_SLEEP_
 #define DF_SLEEP_ 0        // ns of back-off between two polls of an mbarrier (0: spin on try_wait)
@@ -486,17 +486,24 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       }
       named_bar_sync(2, 128);
       const char* src0 = reinterpret_cast<const char*>(p.table) + (uint32_t)c * 16u;
-#pragma unroll 2
+      // (shared-memory loads take ~250 cycles in this kernel: all of a thread's ids are fetched before the first copy is issued)
+#pragma unroll 8
       for (int r = rsub; r < s.SR; r += rpp) {
         const int32_t id = ids_s[r];
         // id 0 = padding (masked: softmax weight exactly 0 unless the WHOLE history is padding): its key is table row 0,
         // which is added from smem in that one case; the stage row is zero-filled
         const bool ok = r < T && id > 0;
-        cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
-                   src0 + (ok ? (uint64_t)(uint32_t)id * rowbytes : 0ull), ok ? 16u : 0u);
+        // (skipped rows keep what they held: zeros from the start of the launch or an earlier sample's keys -- finite, and
+        // multiplied by a softmax weight of exactly 0)
+        if (!DF_SKIP_PAD || id != 0)
+          cp_async16(stage + chunk + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4),
+                     src0 + (ok ? (uint64_t)(uint32_t)id * rowbytes : 0ull), ok ? 16u : 0u);
       }
-      if (tg < PPR) cp_async16(hdr + DF_HDR_Q + tg * 16u, p.emb + b * p.emb_ld + K + tg * 4, 16u);
-      else if (tg < PPR + s.N1p / 4) cp_async16(hdr + DF_HDR_U + (tg - PPR) * 16u, p.U + b * s.N1p + (tg - PPR) * 4, 16u);
+      // q of the NEXT sample travels with this one: its layer-1 weights are built while its own rows are still in flight
+      if (tg < PPR) {
+        if (i == 0) cp_async16(hdr + DF_HDR_Q + tg * 16u, p.emb + b * p.emb_ld + K + tg * 4, 16u);
+        if (i + 1 < n_my) cp_async16(hdr + DF_HDR_QN + tg * 16u, p.emb + (b + gridDim.x) * p.emb_ld + K + tg * 4, 16u);
+      } else if (tg < PPR + s.N1p / 4) cp_async16(hdr + DF_HDR_U + (tg - PPR) * 16u, p.U + b * s.N1p + (tg - PPR) * 4, 16u);
       cp_async_mbar_arrive_noinc(full_raw(st));
       mbar_arrive(full_raw(st));                             // releases the ids written with plain stores
       if (tg == 0) DF_MARK(0, i);
@@ -519,14 +526,9 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
     }
     const uint32_t dst0 = base + mp.ws + (uint32_t)(cq >> 3) * ((uint32_t)s.N1p * 128u);
     const uint32_t piece = (uint32_t)(cq & 7);
-    int st = 0; uint32_t sph = 0;
-#pragma unroll 1
-    for (int64_t i = 0; i < n_my; ++i) {
+    // Ws(i + 1) is built from the copy of q(i + 1) that arrived with sample i: one sample ahead of the rows it multiplies
+    auto build = [&](int64_t i, float4 q) {
       const int wbuf = (int)(i & 1);
-      const uint32_t hq = base + mp.stage0 + (uint32_t)st * mp.stage_bytes + keys_bytes + DF_HDR_Q;
-      df_wait(full_raw(st), sph);
-      if (tb == 0) DF_MARK(1, i);
-      const float4 q = df_lds128(hq + (uint32_t)cq * 16u);
       df_wait(ws_free(wbuf), (uint32_t)((i >> 1) & 1) ^ 1u);
       const uint32_t dst = dst0 + (uint32_t)wbuf * mp.ws_bytes;
 #pragma unroll
@@ -537,9 +539,18 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
                     df_tf32(fmaf(q.x, wd[j].x, wb[j].x)), df_tf32(fmaf(q.y, wd[j].y, wb[j].y)),
                     df_tf32(fmaf(q.z, wd[j].z, wb[j].z)), df_tf32(fmaf(q.w, wd[j].w, wb[j].w)));
       }
-      fence_proxy_async_smem();                              // Ws (and, transitively, the cp.async key rows) -> the MMA's proxy
+      fence_proxy_async_smem();                              // generic-proxy writes -> the MMA's (async) proxy
       mbar_arrive(ws_full(wbuf));
       if (tb == 0) DF_MARK(2, i);
+    };
+    int st = 0; uint32_t sph = 0;
+#pragma unroll 1
+    for (int64_t i = 0; i < n_my; ++i) {
+      const uint32_t hdr = base + mp.stage0 + (uint32_t)st * mp.stage_bytes + keys_bytes;
+      df_wait(full_raw(st), sph);
+      if (tb == 0) DF_MARK(1, i);
+      if (i == 0) build(0, df_lds128(hdr + DF_HDR_Q + (uint32_t)cq * 16u));
+      if (i + 1 < n_my) build(i + 1, df_lds128(hdr + DF_HDR_QN + (uint32_t)cq * 16u));
       if (++st == nraw) { st = 0; sph ^= 1u; }
     }
   } else if (warp == 16) {
@@ -547,9 +558,9 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
     const uint32_t idesc1 = make_idesc_tf32(DF_BM, (uint32_t)s.N1p), idesc2 = make_idesc_tf32(DF_BM, (uint32_t)s.N2p);
     const uint32_t w2 = base + mp.w2;
     // Whatever is ready goes first, finishing samples before starting new ones: L2(i2) needs H1(i2) and a free D2 slot;
-    // L1(i1) needs Ws(i1) (which implies keys(i1)) and must not overwrite H1(i1 - NS) before L2(i1 - NS) was issued.
+    // L1(i1) needs Ws(i1) and keys(i1), and must not overwrite H1(i1 - NS) before L2(i1 - NS) was issued.
     int64_t i1 = 0, i2 = 0;
-    int slot1 = 0, slot2 = 0, st1 = 0; uint32_t ph2 = 0;
+    int slot1 = 0, slot2 = 0, st1 = 0; uint32_t ph2 = 0, sph1 = 0;
 #pragma unroll 1
     while (i2 < n_my) {
       bool did = false;
@@ -575,7 +586,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       }
       if (!did && i1 < n_my && i1 - i2 < NS) {
         const int wbuf = (int)(i1 & 1);
-        bool r = mbar_test_wait(ws_full(wbuf), (uint32_t)((i1 >> 1) & 1));
+        bool r = mbar_test_wait(ws_full(wbuf), (uint32_t)((i1 >> 1) & 1)) && mbar_test_wait(full_raw(st1), sph1);
         r = __all_sync(0xffffffffu, r);
         if (r) {
           fence_proxy_async_smem();
@@ -596,7 +607,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
           __syncwarp();
           ++i1;
           if (++slot1 == NS) slot1 = 0;
-          if (++st1 == nraw) st1 = 0;
+          if (++st1 == nraw) { st1 = 0; sph1 ^= 1u; }
         }
       }
     }
@@ -615,6 +626,8 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       const float* u = reinterpret_cast<const float*>(bp + mp.stage0 + (uint32_t)st * mp.stage_bytes + keys_bytes + DF_HDR_U);
       df_wait(d1_full(slot), ph);
       if (t == 0) DF_MARK(3, i);
+      // a padding position's row of H1 feeds a score that the mask replaces: leave whatever layer 1 produced there (finite)
+      const bool dead = DF_SKIP_PAD && (t >= T || reinterpret_cast<const int32_t*>(u - (DF_HDR_U / 4))[t] == 0);
       tc_fence_after();
       const uint32_t d_t = t_lane + (uint32_t)(slot * s.slot_cols);
       uint32_t a[16], nx[16];
@@ -625,6 +638,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) a[j] = nx[j];
         if (n0 + 16 < N1p) df_ld16_nowait(d_t + (uint32_t)(n0 + 16), nx);
+        if (!dead) {
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
           const float4 uu = *reinterpret_cast<const float4*>(u + n0 + j);
@@ -633,6 +647,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
           a[j + 1] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 1]) + uu.y, aa.y)));
           a[j + 2] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 2]) + uu.z, aa.z)));
           a[j + 3] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 3]) + uu.w, aa.w)));
+        }
         }
         if (n0 + 16 > h1) {                                   // zero the padding columns (they are layer 2's K padding)
 #pragma unroll
@@ -669,6 +684,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       tc_fence_after();
       const uint32_t d_t = t_lane + (uint32_t)(slot * s.slot_cols + s.N1p);
       float sc = s_b3[0];
+      const bool dead = DF_SKIP_PAD && (!live || ids_s[t] == 0);
       uint32_t v[16], nx[16];
       df_ld16_nowait(d_t, nx);
 #pragma unroll 1
@@ -677,6 +693,7 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) v[j] = nx[j];
         if (n0 + 16 < N2p) df_ld16_nowait(d_t + (uint32_t)(n0 + 16), nx);
+        if (!dead)
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
           const int n = n0 + j;
@@ -735,11 +752,13 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
       const float* P = s_P + pb * DF_BM;
       const uint8_t* kt = ksub + (uint32_t)stj * mp.stage_bytes;
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 2
+#pragma unroll 6
       for (int r = rsub; r < T; r += G) {
-        const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4));
         const float p0 = P[r];
-        a.x = fmaf(p0, k0.x, a.x); a.y = fmaf(p0, k0.y, a.y); a.z = fmaf(p0, k0.z, a.z); a.w = fmaf(p0, k0.w, a.w);
+        if (!DF_SKIP_PAD || p0 != 0.f) {
+          const float4 k0 = *reinterpret_cast<const float4*>(kt + (uint32_t)r * 128u + ((pc ^ (uint32_t)(r & 7)) << 4));
+          a.x = fmaf(p0, k0.x, a.x); a.y = fmaf(p0, k0.y, a.y); a.z = fmaf(p0, k0.z, a.z); a.w = fmaf(p0, k0.w, a.w);
+        }
       }
       const float inv = s_aux[2 * pb], all_masked = s_aux[2 * pb + 1];
       named_bar_sync(3, DF_NSUM);                            // the previous sample's partial sums have been read
