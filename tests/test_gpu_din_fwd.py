@@ -132,3 +132,49 @@ def test_full_batch_properties(lib):
     want = O.din_attention(table[cand[sub, 0]].astype(np.float64), key, key, (hist[sub] != 0).astype(np.float64), dense,
                            (ws[6].astype(np.float64), ws[7].astype(np.float64)))
     assert np.max(np.abs(got[sub, :K] - want)) <= TOL
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_din_with_two_behaviour_features(lib, prec):
+    """behavior_feature_list of two features (DL/model/din.py:76-79: key = concat of their rows, mask from the first): the rows
+    go through the gather kernel and the attention unit, no eager indexing; against the oracle's DIN.call."""
+    from recommender_system_b200.layer import set_seed
+    from recommender_system_b200.model.din import DIN
+    set_seed(3)
+    B, T = 97, 9
+    fc = [[{"feat": "d0"}],
+          [{"feat": "o0", "feat_onehot_dim": 11, "embed_dim": 8}, {"feat": "seq_a", "feat_onehot_dim": 40, "embed_dim": 8},
+           {"feat": "seq_b", "feat_onehot_dim": 23, "embed_dim": 4}]]
+    m = DIN(fc, ["seq_a", "seq_b"], att_hidden_units=(16, 8), dnn_hidden_units=(16, 8), precision=prec)
+    m.build(None)
+    m.att_layer.build_for(T, 12)
+    rng = np.random.default_rng(5)
+    upd = {}
+    for n, w in m.named_weights().items():                       # non-trivial alphas / BN statistics / biases
+        if n.endswith("prelu_alpha"):
+            upd[n] = rng.uniform(0, 0.3, tuple(w.shape))
+        elif n.endswith("moving_variance") or n.endswith("gamma"):
+            upd[n] = rng.uniform(0.5, 1.5, tuple(w.shape))
+        elif n.endswith("bias") or n.endswith("beta") or n.endswith("moving_mean"):
+            upd[n] = rng.normal(0, 0.1, tuple(w.shape))
+    m.set_weights({n: np.asarray(v, np.float32) for n, v in upd.items()})
+    lens = rng.integers(0, T + 1, size=B)
+    lens[0], lens[1] = 0, T
+    ha = rng.integers(1, 40, size=(B, T)).astype(np.int32)
+    ha[np.arange(T)[None, :] >= lens[:, None]] = 0
+    hb = rng.integers(0, 23, size=(B, T)).astype(np.int32)          # the second feature does not carry the mask
+    cand = np.stack([rng.integers(1, 40, size=B), rng.integers(0, 23, size=B)], axis=1).astype(np.int32)
+    inputs = {"d0": np.asarray(rng.random((B, 1)), np.float32), "o0": rng.integers(0, 11, size=(B, 1)).astype(np.int32),
+              "seq_a": ha, "seq_b": hb, "movie_id": cand}
+    got = npy(m(inputs))
+    w = {n: npy(t) for n, t in m.named_weights().items()}
+    att = [(w["Attention_0/dense_%d/kernel" % i], w["Attention_0/dense_%d/bias" % i], w["Attention_0/dense_%d/prelu_alpha" % i])
+           for i in range(2)]
+    tw = [(w["dense_%d/kernel" % i], w["dense_%d/bias" % i], w["dense_%d/prelu_alpha" % i]) for i in range(2)]
+    want = O.din_model(inputs["d0"].astype(np.float64), inputs["o0"], np.stack([ha, hb], axis=2), cand,
+                       [w["embed_sparse_0/embeddings"]], [w["embed_seq_0/embeddings"], w["embed_seq_1/embeddings"]], att,
+                       (w["Attention_0/out/kernel"], w["Attention_0/out/bias"]),
+                       (w["bn/gamma"], w["bn/beta"], w["bn/moving_mean"], w["bn/moving_variance"]), tw,
+                       (w["out/kernel"], w["out/bias"]))
+    tol = 5e-6 if prec == "fp32" else TOL / 4
+    assert np.max(np.abs(got - want)) <= tol, np.max(np.abs(got - want))
