@@ -182,7 +182,10 @@ __device__ __forceinline__ float tf32_rna_fast(float x) {
 }
 
 // one 32-column chunk of a hidden layer's epilogue: acc -> act(acc + b) -> tf32 -> back to TMEM in place
-__device__ __forceinline__ void fu_hidden_chunk(uint32_t taddr, const float* sb, const float* sa, int c0, int N, bool relu) {
+#ifndef FU_CHUNK_INLINE
+#define FU_CHUNK_INLINE __noinline__
+#endif
+__device__ FU_CHUNK_INLINE void fu_hidden_chunk(uint32_t taddr, const float* sb, const float* sa, int c0, int N, bool relu) {
   float acc[32];
   tmem_ld32(taddr, acc);
   if (relu && c0 + 32 <= N) {
@@ -213,7 +216,7 @@ __device__ __forceinline__ void fu_hidden_chunk(uint32_t taddr, const float* sb,
 }
 
 // one 32-column chunk of the LAST hidden layer: returns sum_n act(acc + b)[n] * w_out[n]
-__device__ __forceinline__ float fu_last_chunk(uint32_t taddr, const float* sb, const float* sa, const float* sw,
+__device__ FU_CHUNK_INLINE float fu_last_chunk(uint32_t taddr, const float* sb, const float* sa, const float* sw,
                                                int c0, int N, bool relu) {
   float acc[32];
   tmem_ld32(taddr, acc);
