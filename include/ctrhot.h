@@ -430,6 +430,27 @@ int ctrhot_din_fwd_tf32(const float* table, int64_t V, int K, const void* hist_i
                         const float* dense, int64_t dense_ld, int n_dense, int dense_col,
                         void* workspace, int64_t workspace_bytes, int* err_flag, void* stream);
 
+/* ---- one SGD step of DeepFM, the step on the right of the path ------------------------------
+ * What compile_fit (DL/utils/compile_fit.py:9-15: SGD(lr), loss 'binary_crossentropy', model.fit) does to DeepFM
+ * (DL/model/deepFM.py:15-31) for one batch: forward, mean clipped BCE + the l2 regularisers of FMLayer.build
+ * (DL/layer/interaction.py:97-104: reg_w sum w1^2 + reg_v sum v^2), exact fp32 gradients, w <- w - lr * grad.
+ * UPDATED IN PLACE: the embedding arena (only the rows looked up; a row used by several samples gets the sum of their
+ * gradients, as keras' sparse SGD does), fm_w0 [1], fm_w1 [n,1], fm_v [n,k_fm] (n = D + F k), and weight / bias of every
+ * h_layers entry: n_layers - 1 hidden Dense with ReLU + the final Dense(h -> 1) (act NONE).  dropout in [0,1) is applied after
+ * every hidden layer (DNNLayer.call, interaction.py:40-46) with a stateless generator keyed by `seed` (pass a new seed per
+ * step): same distribution as keras' Dropout, not TensorFlow's random stream.  loss_out (DEVICE, 2 floats) = mean BCE of the
+ * batch BEFORE the update (without the regularisers, which is what keras prints minus its regularisation term) and the
+ * number of samples on the right side of 0.5.  ids [B, F] local row numbers; dense [B, D]; y [B] in {0, 1}.
+ * fp32 CUDA cores throughout (the reference trains at batch 32).  Bad ids: the row contributes zeros, *err_flag = 1. */
+int64_t ctrhot_deepfm_train_workspace_bytes(int64_t B, int n, int k_fm, const ctrhot_dense_desc* h_layers,
+                                            int n_layers);
+int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                 int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                                 int64_t B, float* fm_w0, float* fm_w1, float* fm_v, int k_fm, float reg_w,
+                                 float reg_v, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
+                                 float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                 int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R12/R14 fused model front ends ------------------------------------------
  * gather -> x=[dense, embed] -> FM (DeepFM, DL/model/deepFM.py:24-28) or L cross
  * layers (DCN, DL/model/dcn.py:25-29) in ONE kernel; the gathered rows are

@@ -507,3 +507,81 @@ def local_activation_unit(query, keys, kernels, biases, out_kernel, out_bias, ac
     att_input = np.concatenate([q, keys, q - keys, q * keys], axis=-1)
     att_out = deepctr_dnn(att_input, kernels, biases, act, dice=dice)
     return np.tensordot(att_out, out_kernel, axes=(-1, 0)) + out_bias
+
+
+# --------------------------------------------------------------------------- one SGD step of DeepFM
+# PARITY UNPINNED for this function: the reference trains through TensorFlow's autodiff and optimizer
+# (DL/utils/compile_fit.py:9-15), which cannot run in this container, and it ships no training fixtures.  The forward
+# half is the pinned `deepfm_model` above; the gradients are pinned by central finite differences of this file's own
+# loss (tests/test_oracle.py::test_deepfm_train_step_gradients).
+def deepfm_loss(dense, ids, tables, fm_w0, fm_w1, fm_v, hidden, out, y, reg_w, reg_v, drop_masks=None):
+    """keras' training loss of DeepFM for one batch: mean BCE(y, clip(p, 1e-7, 1-1e-7)) + reg_w*sum(w1^2) + reg_v*sum(v^2)
+    (binary_crossentropy; l2 regularisers of FMLayer.build, DL/layer/interaction.py:97-104).  hidden: [(kernel, bias)] with
+    ReLU; out: (kernel [h,1], bias [1]); drop_masks: per hidden layer a [B, h_l] array of 0 or 1/(1-rate) (Dropout in
+    training mode, interaction.py:40-46) or None.  -> (loss, mean_bce, p)"""
+    ids = ids_to_int(ids)
+    x = np.concatenate([np.asarray(dense, np.float64)] + [tables[f][ids[:, f]] for f in range(len(tables))], axis=1)
+    fm = fm_layer(x, fm_w0, fm_w1, fm_v)[:, 0]
+    h = x
+    for l, (k, b) in enumerate(hidden):
+        h = np.maximum(h @ k + b, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+    dnn = (h @ out[0] + out[1])[:, 0]
+    p = sigmoid(0.5 * (fm + dnn))
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    return bce + reg_w * float(np.sum(fm_w1 ** 2)) + reg_v * float(np.sum(fm_v ** 2)), bce, p
+
+
+def deepfm_train_step(dense, ids, tables, fm_w0, fm_w1, fm_v, hidden, out, y, lr, reg_w, reg_v, drop_masks=None):
+    """One step of keras SGD(lr) on `deepfm_loss` (what compile_fit's model.fit does per batch).  Analytic gradients;
+    returns the UPDATED (tables, fm_w0, fm_w1, fm_v, hidden, out), the mean BCE before the update and the number of correct
+    predictions.  Embedding rows looked up by several samples receive the sum of their gradients (np.add.at), rows that
+    were not looked up do not move."""
+    ids = ids_to_int(ids)
+    B, D, F = ids.shape[0], np.asarray(dense).shape[1], len(tables)
+    x = np.concatenate([np.asarray(dense, np.float64)] + [tables[f][ids[:, f]] for f in range(F)], axis=1)
+    xv = x @ fm_v
+    fm = (fm_w0 + x @ fm_w1)[:, 0] + 0.5 * (np.sum(xv ** 2, axis=1) - (x ** 2) @ np.sum(fm_v ** 2, axis=1))
+    acts = [x]
+    for l, (k, b) in enumerate(hidden):
+        h = np.maximum(acts[-1] @ k + b, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+        acts.append(h)
+    dnn = (acts[-1] @ out[0] + out[1])[:, 0]
+    p = sigmoid(0.5 * (fm + dnn))
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    correct = int(np.sum((p > 0.5) == (y > 0.5)))
+    dz = np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B          # d loss / d logit, logit = (fm + dnn) / 2
+    dhalf = 0.5 * dz
+    # tower
+    g = dhalf[:, None] @ out[0].T                                        # [B, h_L]
+    new_out = (out[0] - lr * (acts[-1].T @ dhalf[:, None]), out[1] - lr * np.sum(dhalf))
+    new_hidden = [None] * len(hidden)
+    for l in range(len(hidden) - 1, -1, -1):
+        k, b = hidden[l]
+        m = (acts[l + 1] > 0).astype(np.float64)
+        if drop_masks is not None:
+            m = m * np.max(drop_masks[l])                                # kept elements carry the 1/(1-rate) scale
+        g = g * m
+        gin = g @ k.T
+        new_hidden[l] = (k - lr * (acts[l].T @ g), b - lr * np.sum(g, axis=0))
+        g = gin
+    dx = g
+    # FM
+    vsq = np.sum(fm_v ** 2, axis=1)
+    dx = dx + dhalf[:, None] * (fm_w1[:, 0][None, :] + xv @ fm_v.T - x * vsq[None, :])
+    g_w1 = x.T @ dhalf[:, None] + 2 * reg_w * fm_w1
+    g_v = x.T @ (dhalf[:, None] * xv) - fm_v * ((x ** 2).T @ dhalf)[:, None] + 2 * reg_v * fm_v
+    new_w0, new_w1, new_v = fm_w0 - lr * np.sum(dhalf), fm_w1 - lr * g_w1, fm_v - lr * g_v
+    # embedding rows
+    new_tables = [t.copy() for t in tables]
+    off = D
+    for f in range(F):
+        kdim = tables[f].shape[1]
+        np.add.at(new_tables[f], ids[:, f], -lr * dx[:, off:off + kdim])
+        off += kdim
+    return (new_tables, new_w0, new_w1, new_v, new_hidden, new_out), bce, correct

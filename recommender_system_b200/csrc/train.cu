@@ -1,0 +1,344 @@
+// the step on the RIGHT of the hot path -- one SGD step of DeepFM, so that compile_fit
+// (DL/utils/compile_fit.py:9-15: SGD(lr), loss 'binary_crossentropy', model.fit over batches) works on the drop-in model.
+//
+//   forward   x = [dense | embedding rows]                         (DeepFM.call, DL/model/deepFM.py:23-31)
+//             fm = w0 + x w1 + 1/2 sum_f [(x v)_f^2 - (x^2)(v^2)_f]  (FMLayer.call, DL/layer/interaction.py:106-114)
+//             h_l = dropout(relu(h_{l-1} W_l + b_l)),  dnn = h_L w_out + b_out   (DNNLayer.call, interaction.py:40-46)
+//             p = sigmoid(1/2 (fm + dnn))
+//   loss      mean_b BCE(y_b, clip(p_b, 1e-7, 1 - 1e-7))  +  reg_w sum w1^2  +  reg_v sum v^2     (keras binary_crossentropy;
+//             l2 regularisers of FMLayer.build, interaction.py:97-104)
+//   backward  exact fp32 gradients of that loss; embedding rows get the gradient of the samples that looked them up
+//   update    w <- w - lr * grad (keras SGD, no momentum); embedding rows by atomic adds (keras sums duplicate indices)
+//
+// Everything is fp32 on the CUDA cores: the reference trains at batch 32 (compile_fit's default), where the step is a chain of
+// small launches and tensor-core tiles would be mostly padding.  One generic tiled GEMM serves the tower both ways and every
+// weight update (C = beta C + alpha op(A) op(B), strided operands).  Dropout uses a stateless hash of (seed, layer, element):
+// the mask of the forward pass is recomputed, not stored, in the backward pass; it cannot match TensorFlow's generator.
+#include "common.cuh"
+
+namespace ctrhot {
+
+constexpr int TR_T = 32;                       // GEMM tile
+constexpr int TR_MAXL = 8;
+
+// C[m, n] = beta * C[m, n] + alpha * sum_k A(m, k) B(k, n);  A(m, k) = A[m * am + k * ak], B(k, n) = B[k * bk + n * bn]
+__global__ void __launch_bounds__(256)
+tr_gemm_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float* __restrict__ Bm, int64_t bk, int64_t bn,
+               float* __restrict__ C, int64_t ldc, int M, int N, int K, float alpha, float beta) {
+  __shared__ float As[TR_T][TR_T + 1], Bs[TR_T][TR_T + 1];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;          // 16 x 16 threads, 2 x 2 outputs each
+  const int m0 = blockIdx.y * TR_T, n0 = blockIdx.x * TR_T;
+  float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+  for (int k0 = 0; k0 < K; k0 += TR_T) {
+    for (int e = threadIdx.x; e < TR_T * TR_T; e += 256) {
+      const int r = e / TR_T, c = e % TR_T;                        // As[k][m], Bs[k][n]
+      const int m = m0 + c, k = k0 + r;
+      As[r][c] = (m < M && k < K) ? A[(int64_t)m * am + (int64_t)k * ak] : 0.f;
+      const int n = n0 + c;
+      Bs[r][c] = (n < N && k < K) ? Bm[(int64_t)k * bk + (int64_t)n * bn] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int k = 0; k < TR_T; ++k) {
+      const float a0 = As[k][ty], a1 = As[k][ty + 16], b0 = Bs[k][tx], b1 = Bs[k][tx + 16];
+      acc[0][0] = fmaf(a0, b0, acc[0][0]); acc[0][1] = fmaf(a0, b1, acc[0][1]);
+      acc[1][0] = fmaf(a1, b0, acc[1][0]); acc[1][1] = fmaf(a1, b1, acc[1][1]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int m = m0 + ty + 16 * i, n = n0 + tx + 16 * j;
+      if (m < M && n < N) {
+        float* c = C + (int64_t)m * ldc + n;
+        *c = (beta == 0.f ? 0.f : beta * *c) + alpha * acc[i][j];
+      }
+    }
+}
+
+__device__ __forceinline__ float tr_uniform(uint64_t seed, uint32_t layer, uint64_t idx) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (idx + 1) + ((uint64_t)layer << 56);     // splitmix64
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+// x[b] = [dense_b (D) | rows of the F fields (F * k)]   (reference column order)
+template <int IDKIND>
+__global__ void tr_gather_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                                 const void* __restrict__ ids, int64_t ids_ld, const float* __restrict__ dense, int64_t dense_ld,
+                                 int D, int64_t B, float* __restrict__ x, int n, int* __restrict__ err_flag) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / n;
+    const int c = (int)(i - b * n);
+    float v;
+    if (c < D) {
+      v = dense[b * dense_ld + c];
+    } else {
+      const int f = (c - D) / k, e = (c - D) - f * k;
+      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      const int64_t rows = row_off[f + 1] - row_off[f];
+      const bool ok = id >= 0 && id < rows;
+      if (!ok && err_flag) *err_flag = 1;
+      v = ok ? arena[(row_off[f] + id) * k + e] : 0.f;
+    }
+    x[i] = v;
+  }
+}
+
+// one warp per sample: xv[b, f] = sum_j x_bj v_jf,  fm[b] = w0 + x.w1 + 1/2 sum_f (xv_f^2 - sum_j x_bj^2 v_jf^2)
+__global__ void tr_fm_fwd_kernel(const float* __restrict__ x, int n, int64_t B, const float* __restrict__ w0,
+                                 const float* __restrict__ w1, const float* __restrict__ v, int kf,
+                                 float* __restrict__ xv, float* __restrict__ fm) {
+  const int lane = threadIdx.x & 31;
+  const int64_t b = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  float lin = 0.f, sq = 0.f, acc[32];
+#pragma unroll
+  for (int f = 0; f < 32; ++f) acc[f] = 0.f;
+  for (int j = lane; j < n; j += 32) {
+    const float xj = x[b * n + j];
+    lin = fmaf(xj, w1[j], lin);
+#pragma unroll
+    for (int f = 0; f < 32; ++f)
+      if (f < kf) { const float vv = v[(int64_t)j * kf + f]; acc[f] = fmaf(xj, vv, acc[f]); sq = fmaf(xj * xj, vv * vv, sq); }
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) { lin += __shfl_xor_sync(0xffffffffu, lin, o); sq += __shfl_xor_sync(0xffffffffu, sq, o); }
+  float s1 = 0.f;
+#pragma unroll
+  for (int f = 0; f < 32; ++f) {
+    if (f < kf) {
+      float a = acc[f];
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+      if (lane == 0) xv[b * kf + f] = a;
+      s1 = fmaf(a, a, s1);
+    }
+  }
+  if (lane == 0) fm[b] = w0[0] + lin + 0.5f * (s1 - sq);
+}
+
+// h = dropout(relu(h + bias)) in place (h holds the GEMM result); mask recomputable from (seed, layer, element)
+__global__ void tr_bias_relu_drop_kernel(float* __restrict__ h, const float* __restrict__ bias, int N, int64_t B, int relu,
+                                         float rate, uint64_t seed, uint32_t layer) {
+  const float scale = rate > 0.f ? 1.f / (1.f - rate) : 1.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * N; i += (int64_t)gridDim.x * blockDim.x) {
+    float t = h[i] + (bias ? bias[i % N] : 0.f);
+    if (relu) t = fmaxf(t, 0.f);
+    if (rate > 0.f) t = (tr_uniform(seed, layer, (uint64_t)i) >= rate) ? t * scale : 0.f;
+    h[i] = t;
+  }
+}
+
+// p, per-sample loss / correctness and dz = dLoss/dlogit (loss = mean BCE over the batch, probabilities clipped like keras)
+__global__ void tr_loss_kernel(const float* __restrict__ fm, const float* __restrict__ dnn, const float* __restrict__ b_out,
+                               const float* __restrict__ y, int64_t B, float* __restrict__ dz, float* __restrict__ loss_out) {
+  __shared__ float s_loss[256], s_ok[256];
+  float l = 0.f, ok = 0.f;
+  for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
+    const float z = 0.5f * (fm[b] + dnn[b] + (b_out ? b_out[0] : 0.f));
+    const float p = 1.0f / (1.0f + __expf(-z));
+    const float eps = 1e-7f;
+    const float pc = fminf(fmaxf(p, eps), 1.f - eps);
+    const float yb = y[b];
+    l -= yb * __logf(pc) + (1.f - yb) * __logf(1.f - pc);
+    ok += ((p > 0.5f) == (yb > 0.5f)) ? 1.f : 0.f;
+    // d/dp of the clipped BCE is zero where the clip is active; times dp/dz = p (1 - p); times 1/B for the mean
+    const float g = (p > eps && p < 1.f - eps) ? (pc - yb) : 0.f;
+    dz[b] = g / (float)B;
+  }
+  s_loss[threadIdx.x] = l; s_ok[threadIdx.x] = ok;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o >= 1; o >>= 1) {               // fixed order: the reported loss is deterministic
+    if (threadIdx.x < o) { s_loss[threadIdx.x] += s_loss[threadIdx.x + o]; s_ok[threadIdx.x] += s_ok[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { loss_out[0] = s_loss[0] / (float)B; loss_out[1] = s_ok[0]; }
+}
+
+// g[b, n] *= (h[b, n] > 0 ? dropout scale : 0): the derivative of dropout(relu(.)) at the stored activation
+__global__ void tr_relu_drop_bwd_kernel(float* __restrict__ g, const float* __restrict__ h, int64_t total, int relu, float rate,
+                                        uint64_t seed, uint32_t layer) {
+  const float scale = rate > 0.f ? 1.f / (1.f - rate) : 1.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    float m = 1.f;
+    if (rate > 0.f) m = (tr_uniform(seed, layer, (uint64_t)i) >= rate) ? scale : 0.f;
+    if (relu && !(h[i] > 0.f)) m = 0.f;
+    g[i] *= m;
+  }
+}
+
+// out[n] = beta * out[n] + alpha * sum_b w_b A[b, n] (w = NULL: ones); one thread per column, fixed order over b
+__global__ void tr_colsum_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ w, int64_t B, int N,
+                                 int square, float* __restrict__ out, float alpha, float beta) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float s = 0.f;
+  for (int64_t b = 0; b < B; ++b) {
+    const float a = A[b * lda + n];
+    s = fmaf(w ? w[b] : 1.f, square ? a * a : a, s);
+  }
+  out[n] = (beta == 0.f ? 0.f : beta * out[n]) + alpha * s;
+}
+
+// dx[b, j] += dfm_b (w1_j + sum_f v_jf xv_bf - x_bj sum_f v_jf^2);  also t[b, f] = dfm_b xv_bf (the right factor of dv)
+__global__ void tr_fm_bwd_kernel(const float* __restrict__ x, int n, int64_t B, const float* __restrict__ dz,
+                                 const float* __restrict__ w1, const float* __restrict__ v, int kf,
+                                 const float* __restrict__ xv, float* __restrict__ dx, float* __restrict__ t) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / n;
+    const int j = (int)(i - b * n);
+    const float dfm = 0.5f * dz[b];
+    float s = w1[j], vsq = 0.f;
+    for (int f = 0; f < kf; ++f) { const float vv = v[(int64_t)j * kf + f]; s = fmaf(vv, xv[b * kf + f], s); vsq = fmaf(vv, vv, vsq); }
+    dx[i] += dfm * (s - x[i] * vsq);
+    if (j < kf) t[b * kf + j] = dfm * xv[b * kf + j];
+  }
+}
+
+// v[j, f] *= decay + lr * s2[j]   (the -x_j^2 v_jf part of dv and the l2 regulariser, before the GEMM adds -lr x^T t)
+__global__ void tr_scale_rows_kernel(float* __restrict__ v, int n, int kf, const float* __restrict__ s2, float decay, float lr) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n * kf; i += gridDim.x * blockDim.x)
+    v[i] *= decay + lr * s2[i / kf];
+}
+
+// arena rows -= lr * dx[b, D + f k + e]: atomic adds (a row looked up by several samples gets the sum, as keras' sparse SGD)
+template <int IDKIND>
+__global__ void tr_embed_sgd_kernel(float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                                    const void* __restrict__ ids, int64_t ids_ld, int D, int64_t B, const float* __restrict__ dx,
+                                    int n, float lr) {
+  const int fk = F * k;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * fk; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / fk;
+    const int c = (int)(i - b * fk), f = c / k, e = c - f * k;
+    const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+    if (id >= 0 && id < row_off[f + 1] - row_off[f])
+      atomicAdd(arena + (row_off[f] + id) * k + e, -lr * dx[b * n + D + c]);
+  }
+}
+
+}  // namespace ctrhot
+
+using namespace ctrhot;
+
+namespace {
+struct TrLayout { int64_t x, xv, fm, dnn, dz, t, s2, dx, g0, g1, h[TR_MAXL], total; int maxw; };
+bool tr_layout(int64_t B, int n, int kf, const ctrhot_dense_desc* L, int n_layers, TrLayout& w) {
+  if (!L || n_layers < 2 || n_layers > TR_MAXL || B < 0 || n <= 0 || kf < 1 || kf > 32) return false;
+  if (L[0].in_dim != n || L[n_layers - 1].out_dim != 1) return false;
+  int64_t o = 0;
+  auto take = [&](int64_t cnt) { const int64_t at = o; o += (cnt + 3) / 4 * 4; return at; };
+  w.maxw = n;
+  for (int l = 0; l < n_layers; ++l) {
+    if (l > 0 && L[l].in_dim != L[l - 1].out_dim) return false;
+    if (l < n_layers - 1 && L[l].act != CTRHOT_ACT_RELU) return false;
+    if (!L[l].weight) return false;
+    if (L[l].out_dim > w.maxw) w.maxw = L[l].out_dim;
+  }
+  w.x = take(B * n); w.xv = take(B * kf); w.fm = take(B); w.dnn = take(B); w.dz = take(B); w.t = take(B * kf);
+  w.s2 = take(n); w.dx = take(B * n); w.g0 = take(B * (int64_t)w.maxw); w.g1 = take(B * (int64_t)w.maxw);
+  for (int l = 0; l < n_layers - 1; ++l) w.h[l] = take(B * (int64_t)L[l].out_dim);
+  w.total = o;
+  return true;
+}
+inline int tr_grid(int64_t total, int block) {
+  int64_t g = (total + block - 1) / block;
+  if (g > (int64_t)kNumSMs * 32) g = (int64_t)kNumSMs * 32;
+  return g < 1 ? 1 : (int)g;
+}
+inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, const float* Bm, int64_t bk, int64_t bn, float* C,
+                    int64_t ldc, int M, int N, int K, float alpha, float beta) {
+  dim3 grid((N + TR_T - 1) / TR_T, (M + TR_T - 1) / TR_T);
+  tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
+}
+}  // namespace
+
+extern "C" int64_t ctrhot_deepfm_train_workspace_bytes(int64_t B, int n, int k_fm, const ctrhot_dense_desc* h_layers,
+                                                       int n_layers) {
+  TrLayout w;
+  if (!tr_layout(B, n, k_fm, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  return w.total * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                            int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                                            int64_t B, float* fm_w0, float* fm_w1, float* fm_v, int k_fm, float reg_w,
+                                            float reg_v, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
+                                            float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                            int64_t workspace_bytes, int* err_flag, void* stream) {
+  if (!arena || !row_off || !ids || !y || !fm_w0 || !fm_w1 || !fm_v || !loss_out || !workspace || F <= 0 || k <= 0 || D < 0 ||
+      (D > 0 && !dense) || B <= 0 || ids_ld < F || (D > 0 && dense_ld < D)) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (!(dropout >= 0.f && dropout < 1.f) || !(lr >= 0.f)) return CTRHOT_EARG;
+  const int n = D + F * k;
+  TrLayout w;
+  if (!tr_layout(B, n, k_fm, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < w.total * (int64_t)sizeof(float) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  float *x = ws + w.x, *xv = ws + w.xv, *fm = ws + w.fm, *dnn = ws + w.dnn, *dz = ws + w.dz, *t = ws + w.t, *s2 = ws + w.s2,
+        *dx = ws + w.dx;
+  const int NH = n_layers - 1;                                   // hidden layers; layer NH is Dense(h -> 1)
+  const int M = (int)B;
+  // ---- forward
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_gather_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag);
+  else
+    tr_gather_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag);
+  tr_fm_fwd_kernel<<<(int)((B + 7) / 8), 256, 0, st>>>(x, n, B, fm_w0, fm_w1, fm_v, k_fm, xv, fm);
+  const float* in = x;
+  int in_dim = n;
+  for (int l = 0; l < NH; ++l) {
+    float* h = ws + w.h[l];
+    const int N = h_layers[l].out_dim;
+    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
+    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l);
+    in = h; in_dim = N;
+  }
+  tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, dnn, 1, M, 1, in_dim, 1.f, 0.f);
+  tr_loss_kernel<<<1, 256, 0, st>>>(fm, dnn, h_layers[NH].bias, y, B, dz, loss_out);
+  // ---- backward through the tower: g = dLoss/d(pre-activation) of the current layer, [B, out_dim]
+  float* g = ws + w.g0;
+  float* gn = ws + w.g1;
+  // d dnn = 1/2 dz; Dense(h -> 1): g_prev = 1/2 dz w_out^T (before w_out moves), then w_out, b_out
+  {
+    float* wo = const_cast<float*>(h_layers[NH].weight);
+    tr_gemm(st, dz, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 0.5f, 0.f);                 // [B,1] x [1,h]: B(k=0, n) = wo[n]
+    tr_gemm(st, in, 1, in_dim, dz, 1, 1, wo, 1, in_dim, 1, M, -0.5f * lr, 1.f);           // w_out -= lr * h^T (dz / 2)
+    if (h_layers[NH].bias)
+      tr_colsum_kernel<<<1, 32, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
+    float* tmp = g; g = gn; gn = tmp;
+  }
+  for (int l = NH - 1; l >= 0; --l) {
+    const int N = h_layers[l].out_dim, Kd = h_layers[l].in_dim;
+    const float* h = ws + w.h[l];
+    const float* hin = l > 0 ? ws + w.h[l - 1] : x;
+    float* W = const_cast<float*>(h_layers[l].weight);
+    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l);
+    // gradient w.r.t. this layer's input with the OLD weights: [B,N] x [N,Kd]  (B(k, n) = W[n * N + k])
+    float* dst = l > 0 ? gn : dx;
+    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);                           // W -= lr * in^T g
+    if (h_layers[l].bias)
+      tr_colsum_kernel<<<(N + 127) / 128, 128, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
+  }
+  // ---- FM backward (old w1, v), then its updates: w0, w1 = (1 - 2 lr reg_w) w1 - lr x^T dfm, v likewise with its -x^2 v part
+  tr_fm_bwd_kernel<<<tr_grid(B * n, 256), 256, 0, st>>>(x, n, B, dz, fm_w1, fm_v, k_fm, xv, dx, t);
+  tr_colsum_kernel<<<1, 32, 0, st>>>(dz, 1, nullptr, B, 1, 0, fm_w0, -0.5f * lr, 1.f);
+  tr_colsum_kernel<<<(n + 127) / 128, 128, 0, st>>>(x, n, dz, B, n, 0, fm_w1, -0.5f * lr, 1.f - 2.f * lr * reg_w);
+  tr_colsum_kernel<<<(n + 127) / 128, 128, 0, st>>>(x, n, dz, B, n, 1, s2, 0.5f, 0.f);  // s2[j] = sum_b dfm_b x_bj^2
+  tr_scale_rows_kernel<<<tr_grid((int64_t)n * k_fm, 256), 256, 0, st>>>(fm_v, n, k_fm, s2, 1.f - 2.f * lr * reg_v, lr);
+  tr_gemm(st, x, 1, n, t, k_fm, 1, fm_v, k_fm, n, k_fm, M, -lr, 1.f);                      // v -= lr * x^T (dfm xv)
+  // ---- embedding rows
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr);
+  else
+    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr);
+  CTRHOT_LAUNCH_OK("ctrhot_deepfm_train_step_f32");
+  return CTRHOT_OK;
+}

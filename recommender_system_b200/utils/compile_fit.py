@@ -1,0 +1,90 @@
+"""Drop-in for the reference's ``utils/compile_fit.py`` (DL/utils/compile_fit.py:9-15):
+
+    compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01) -> model
+
+``tf.data`` batches of ``batch_size`` in order (no shuffling: keras does not shuffle a Dataset), ``SGD(sgd)``, loss
+``binary_crossentropy``, metric accuracy, ``epochs`` passes.  Each batch is ONE call of ``ctrhot_deepfm_train_step_f32``
+(csrc/train.cu): forward, clipped BCE + FMLayer's l2 regularisers, exact fp32 gradients, in-place SGD on the embedding
+rows that were looked up, the FM weights and the tower.  SURVEY 8(f) rank 3; built for DeepFM (the reference's flagship
+``__main__``, DL/model/deepFM.py:34-57) -- other models raise NotImplementedError.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .. import _lib
+from ..layer.base import as_device_f32, ids_arg, ptr, stream_ptr
+
+
+class _DeepFMTrainer:
+    """Owns the layer descriptors and the workspace of one (model, batch size)."""
+
+    def __init__(self, model, dropout=None):
+        from ..model.criteo import DeepFM
+        if not isinstance(model, DeepFM):
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM only (SURVEY 8(f) rank 3)")
+        self.m = model
+        if not model.dnn.built:
+            model.build(None)
+        if model.dnn.activation != "relu" or model.dnn.output_dim != 1:
+            raise NotImplementedError("compile_fit: DNNLayer(activation='relu', output_dim=1) only")
+        self.dropout = float(model.dnn.dropout if dropout is None else dropout)
+        layers = [(k, b, _lib.ACT_RELU) for k, b in model.dnn.hidden] + [(model.dnn.output[0], model.dnn.output[1], _lib.ACT_NONE)]
+        self.desc = (_lib.DenseDesc * len(layers))()
+        for d, (k, b, act) in zip(self.desc, layers):
+            d.weight, d.bias, d.in_dim, d.out_dim, d.act = ptr(k), ptr(b), int(k.shape[0]), int(k.shape[1]), act
+        self._keep = layers
+        self.ws = None
+        self.loss = torch.zeros(2, dtype=torch.float32, device=model.device)
+        self.flag = model.err_flag()
+        self.step = 0
+
+    def train_on_batch(self, dense, ids, y, lr, seed=0):
+        """dense [B, D] float32, ids [B, F] int32 / float, y [B] float32, all on the device -> device tensor
+        [mean BCE before the update, number of correct predictions] (read it when you need it: no sync here)."""
+        m, E = self.m, self.m.embed_layer
+        ids, kind, ids_ld = ids_arg(ids)
+        B, D = ids.shape[0], dense.shape[1]
+        n = D + E.F * E.k
+        need = _lib.query("ctrhot_deepfm_train_workspace_bytes", B, n, m.fm.k, self.desc, len(self.desc))
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=m.device)
+        _lib.call("ctrhot_deepfm_train_step_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(dense),
+                  dense.stride(0), D, ptr(y), B, ptr(m.fm.w0), ptr(m.fm.w1), ptr(m.fm.v), m.fm.k, float(m.fm.reg_w),
+                  float(m.fm.reg_b), self.desc, len(self.desc), float(lr), self.dropout, int(seed) & (2 ** 64 - 1),
+                  ptr(self.loss), ptr(self.ws), self.ws.numel() * 4, ptr(self.flag), stream_ptr())
+        self.step += 1
+        return self.loss
+
+    def done(self):
+        """The weights moved in place: invalidate every packed copy the forward path keeps."""
+        for layer in (self.m.embed_layer, self.m.fm, self.m.dnn, self.m):
+            layer._bump()
+
+
+def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True):
+    """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
+    ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
+    (loss, accuracy) pairs are left in ``model.history``."""
+    tr = _DeepFMTrainer(model, dropout)
+    dev = model.device
+    D = len(model.dense_feature_columns)
+    Xd = as_device_f32(X, dev)
+    yd = as_device_f32(np.asarray(y, dtype=np.float32).reshape(-1) if not isinstance(y, torch.Tensor) else y.reshape(-1), dev)
+    N = Xd.shape[0]
+    model.history = []
+    for ep in range(epochs):
+        tot = torch.zeros(2, dtype=torch.float64, device=dev)
+        for s in range(0, N, batch_size):
+            e = min(N, s + batch_size)
+            out = tr.train_on_batch(Xd[s:e, :D], Xd[s:e, D:], yd[s:e], sgd, seed=seed * 1000003 + tr.step)
+            tot[0] += out[0].double() * (e - s)
+            tot[1] += out[1].double()
+        loss, acc = (tot / N).tolist()
+        _lib.check(_lib.load().ctrhot_check_flag(ptr(tr.flag), stream_ptr()), "compile_fit")
+        model.history.append((loss, acc))
+        if verbose:
+            print("Epoch %d/%d - loss: %.4f - accuracy: %.4f" % (ep + 1, epochs, loss, acc))
+    tr.done()
+    return model

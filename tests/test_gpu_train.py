@@ -1,0 +1,148 @@
+"""GPU parity for SURVEY 8(f) rank 3: one SGD step of DeepFM (ctrhot_deepfm_train_step_f32, csrc/train.cu) and the
+compile_fit drop-in (DL/utils/compile_fit.py:9-15) against the float64 oracle `deepfm_train_step`, whose gradients are
+pinned by finite differences (tests/test_oracle.py).  PARITY UNPINNED against the reference itself: TensorFlow's autodiff
+and optimizer cannot run here and the reference ships no training fixtures.
+
+Checked: every updated weight after one step (fp32 arithmetic: 1e-5 relative to the size of the weights' update), rows that
+were not looked up bit-unchanged, duplicate ids summed, the reported loss / accuracy, dropout with the kernel's own stateless
+masks reproduced in NumPy, ragged last batches and a decreasing loss over epochs through compile_fit.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ctr_oracle as O
+from recommender_system_b200.layer import set_seed
+from recommender_system_b200.model.criteo import DeepFM
+from recommender_system_b200.utils.compile_fit import _DeepFMTrainer, compile_fit
+
+pytestmark = pytest.mark.gpu
+
+
+def npy(t):
+    return t.detach().cpu().numpy().astype(np.float64)
+
+
+def make_model(vocab, k_embed, k_fm, hidden, dropout=0.0, seed=1):
+    set_seed(seed)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": int(v), "embed_dim": k_embed} for i, v in enumerate(vocab)]]
+    m = DeepFM(fc, k_fm, 1e-2, 2e-2, list(hidden), 1, "relu", embed_dim=k_embed, precision="fp32")
+    m.build(None)
+    m.dnn.dropout = dropout
+    rng = np.random.default_rng(seed)
+    upd = {}
+    for n, w in m.named_weights().items():                       # keras' zero biases / w0 would hide mistakes in their gradients
+        if n.endswith("bias") or n.endswith("w0"):
+            upd[n] = rng.normal(0, 0.1, tuple(w.shape))
+        elif n.endswith("/v") or n.endswith("/w1"):
+            upd[n] = rng.normal(0, 0.1, tuple(w.shape))
+    m.set_weights({n: np.asarray(v, np.float32) for n, v in upd.items()})
+    return m
+
+
+def params(m):
+    E = m.embed_layer
+    tables = [npy(t) for t in E.emb_layers]
+    hidden = [(npy(k), npy(b)) for k, b in m.dnn.hidden]
+    return tables, npy(m.fm.w0), npy(m.fm.w1), npy(m.fm.v), hidden, (npy(m.dnn.output[0]), npy(m.dnn.output[1]))
+
+
+def batch(vocab, B, seed, dup=True):
+    rng = np.random.default_rng(seed)
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1).astype(np.int32)
+    if dup and B > 3:
+        ids[1], ids[2, :5] = ids[0], ids[0, :5]                  # whole-row and partial duplicates
+    dense = rng.random((B, 13)).astype(np.float32)
+    y = rng.integers(0, 2, B).astype(np.float32)
+    return dense, ids, y
+
+
+def kernel_masks(seed, hidden, B, rate):
+    """The stateless dropout masks of csrc/train.cu (splitmix64 of (seed, layer, element)) in NumPy."""
+    out = []
+    with np.errstate(over="ignore"):
+        for l, h in enumerate(hidden):
+            idx = np.arange(B * h, dtype=np.uint64)
+            z = np.uint64(seed) + np.uint64(0x9E3779B97F4A7C15) * (idx + np.uint64(1)) + (np.uint64(l) << np.uint64(56))
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            z = z ^ (z >> np.uint64(31))
+            u = (z >> np.uint64(40)).astype(np.float32) * np.float32(1.0 / 16777216.0)
+            out.append(((u >= np.float32(rate)).astype(np.float64) / (1.0 - rate)).reshape(B, h))
+    return out
+
+
+def close(got, want, before, what):
+    scale = max(np.max(np.abs(want - before)), 1e-12)            # size of the update itself
+    err = np.max(np.abs(got - want))
+    assert err <= 2e-5 * scale + 2e-7 * max(np.max(np.abs(want)), 1.0), (what, err, scale)
+
+
+@pytest.mark.parametrize("B,vocab,k_embed,k_fm,hidden,rate", [
+    (32, [50, 7, 1000, 3] + [20] * 22, 8, 10, (256, 128, 64), 0.0),      # the reference's compile_fit batch and tower
+    (1, [11] * 26, 4, 4, (16,), 0.0),
+    (257, [50, 7, 1000, 3] + [20] * 22, 16, 8, (64, 32), 0.2),
+    (4096, [5000] * 26, 8, 10, (256, 128, 64), 0.2),
+])
+def test_one_step_against_the_oracle(lib, B, vocab, k_embed, k_fm, hidden, rate):
+    m = make_model(vocab, k_embed, k_fm, hidden, rate)
+    dense, ids, y = batch(vocab, B, seed=B)
+    before = params(m)
+    lr, seed = 0.05, 12345
+    tr = _DeepFMTrainer(m)
+    dev = m.device
+    out = tr.train_on_batch(torch.from_numpy(dense).to(dev), torch.from_numpy(ids).to(dev), torch.from_numpy(y).to(dev), lr, seed=seed)
+    torch.cuda.synchronize()
+    tr.done()
+    masks = kernel_masks(seed, hidden, B, rate) if rate > 0 else None
+    want, bce, correct = O.deepfm_train_step(dense.astype(np.float64), ids, before[0], before[1], before[2], before[3], before[4],
+                                             before[5], y.astype(np.float64), lr, 1e-2, 2e-2, masks)
+    got = params(m)
+    assert abs(float(out[0]) - bce) <= 2e-6 * max(1.0, bce) and int(out[1]) == correct
+    for f in range(len(vocab)):
+        close(got[0][f], want[0][f], before[0][f], "table %d" % f)
+        untouched = np.setdiff1d(np.arange(vocab[f]), ids[:, f])
+        np.testing.assert_array_equal(got[0][f][untouched], before[0][f][untouched])      # rows not looked up do not move
+    close(got[1], want[1], before[1], "w0"); close(got[2], want[2], before[2], "w1"); close(got[3], want[3], before[3], "v")
+    for l in range(len(hidden)):
+        close(got[4][l][0], want[4][l][0], before[4][l][0], "kernel %d" % l)
+        close(got[4][l][1], want[4][l][1], before[4][l][1], "bias %d" % l)
+    close(got[5][0], want[5][0], before[5][0], "out kernel"); close(got[5][1], want[5][1], before[5][1], "out bias")
+
+
+def test_float_ids_and_bad_ids(lib):
+    vocab = [9] * 26
+    m1, m2 = make_model(vocab, 4, 4, (8,)), make_model(vocab, 4, 4, (8,))
+    dense, ids, y = batch(vocab, 40, seed=3)
+    dev = m1.device
+    for m, conv in ((m1, lambda a: a), (m2, lambda a: a.astype(np.float32))):
+        tr = _DeepFMTrainer(m)
+        tr.train_on_batch(torch.from_numpy(dense).to(dev), torch.from_numpy(conv(ids)).to(dev), torch.from_numpy(y).to(dev), 0.1)
+    torch.cuda.synchronize()
+    for a, b in zip(params(m1)[0], params(m2)[0]):
+        np.testing.assert_allclose(a, b, rtol=0, atol=1e-7)      # (atomic adds: the order of duplicate rows may differ)
+    ids[3, 5] = 9                                                # one past the table: raises like the forward path
+    with pytest.raises(IndexError):
+        compile_fit(m1, np.concatenate([dense, ids.astype(np.float32)], axis=1), y, batch_size=16, epochs=1, verbose=False)
+
+
+def test_compile_fit_learns_and_predicts(lib):
+    """compile_fit on data with a planted rule (the label is decided by which half of its vocabulary one id falls in): keras'
+    printed loss falls, accuracy rises, and the trained weights are what the forward path then uses."""
+    vocab = [40] * 26
+    m = make_model(vocab, 8, 10, (64, 32), dropout=0.2, seed=2)
+    rng = np.random.default_rng(0)
+    N = 4000 + 17                                                # ragged last batch
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    dense = rng.random((N, 13))
+    y = (ids[:, 0] < 20).astype(np.float32)
+    X = np.concatenate([dense, ids], axis=1).astype(np.float32)
+    p0 = npy(m(X))[:, 0]
+    compile_fit(m, X, y, batch_size=32, epochs=8, sgd=0.1, verbose=False)
+    losses = [l for l, _ in m.history]
+    assert losses[-1] < 0.8 * losses[0] and m.history[-1][1] > m.history[0][1] + 0.05, m.history
+    p1 = npy(m(X))[:, 0]                                          # the forward path sees the trained weights (versions bumped)
+    assert np.mean((p1 > 0.5) == (y > 0.5)) > np.mean((p0 > 0.5) == (y > 0.5)) + 0.05
+    want = O.deepfm_loss(dense, ids, *params(m)[:5], params(m)[5], y.astype(np.float64), 0.0, 0.0)[2]
+    assert np.max(np.abs(p1 - want)) <= 2e-5

@@ -144,3 +144,13 @@ def test_synth_batches():
     assert (z >= 0).all() and (z < np.array(synth.KAGGLE_VOCAB)).all()
     b = synth.din_batch(512, 100, 1000, 50, seed=2)
     assert b["movies_seq"].shape == (512, 100) and (b["movies_seq"].sum(1) == 0).any()
+
+
+def test_compile_fit_signature_matches_the_reference():
+    """DL/utils/compile_fit.py:9: compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01)."""
+    import inspect
+    from recommender_system_b200.utils.compile_fit import compile_fit
+    sig = inspect.signature(compile_fit)
+    names = list(sig.parameters)
+    assert names[:6] == ["model", "X", "y", "batch_size", "epochs", "sgd"]
+    assert [sig.parameters[n].default for n in names[3:6]] == [32, 10, 0.01]

@@ -139,3 +139,46 @@ def test_bi_interaction_is_the_sum_of_pairwise_products():
         for j in range(i + 1, 7):
             want += e[:, i] * e[:, j]
     np.testing.assert_allclose(O.bi_interaction(e), want, rtol=1e-12, atol=1e-12)
+
+
+def test_deepfm_train_step_gradients():
+    """the oracle's analytic SGD step against central finite differences of its own loss (the forward
+    half of that loss is the pinned deepfm_model).  Duplicate ids, dropout masks and both regularisers are in play."""
+    rng = np.random.default_rng(0)
+    B, D, F, k, kf = 9, 3, 4, 4, 5
+    vocab = [7, 5, 11, 3]
+    tables = [rng.normal(0, 0.3, (v, k)) for v in vocab]
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], 1)
+    ids[1] = ids[0]
+    dense, y = rng.random((B, D)), rng.integers(0, 2, B).astype(float)
+    n = D + F * k
+    w0, w1, v = rng.normal(0, 0.1, 1), rng.normal(0, 0.1, (n, 1)), rng.normal(0, 0.1, (n, kf))
+    hidden = [(rng.normal(0, 0.3, (n, 8)), rng.normal(0, 0.1, 8)), (rng.normal(0, 0.3, (8, 6)), rng.normal(0, 0.1, 6))]
+    out = (rng.normal(0, 0.3, (6, 1)), rng.normal(0, 0.1, 1))
+    masks = [(rng.random((B, 8)) >= 0.2) / 0.8, (rng.random((B, 6)) >= 0.2) / 0.8]
+    lr, rw, rv = 0.1, 1e-2, 2e-2
+    new, bce, correct = O.deepfm_train_step(dense, ids, tables, w0, w1, v, hidden, out, y, lr, rw, rv, masks)
+    base = dict(tables=tables, w0=w0, w1=w1, v=v, hidden=hidden, out=out)
+
+    def loss(**kw):
+        a = dict(base, **kw)
+        return O.deepfm_loss(dense, ids, a["tables"], a["w0"], a["w1"], a["v"], a["hidden"], a["out"], y, rw, rv, masks)[0]
+
+    def fd(arr, put, idx, eps=1e-6):
+        a = arr.copy(); a[idx] += eps; lp = loss(**put(a)); a[idx] -= 2 * eps; lm = loss(**put(a))
+        return (lp - lm) / (2 * eps)
+
+    assert abs(loss() - (bce + rw * np.sum(w1 ** 2) + rv * np.sum(v ** 2))) < 1e-12 and 0 <= correct <= B
+    checks = [(v, new[3], lambda a: {"v": a}, [(0, 0), (5, 2), (18, 4)]),
+              (w1, new[2], lambda a: {"w1": a}, [(0, 0), (4, 0), (18, 0)]),
+              (w0, new[1], lambda a: {"w0": a}, [(0,)]),
+              (hidden[0][0], new[4][0][0], lambda a: {"hidden": [(a, hidden[0][1]), hidden[1]]}, [(0, 0), (7, 3), (18, 7)]),
+              (hidden[1][1], new[4][1][1], lambda a: {"hidden": [hidden[0], (hidden[1][0], a)]}, [(j,) for j in range(6)]),
+              (out[0], new[5][0], lambda a: {"out": (a, out[1])}, [(j, 0) for j in range(6)]),
+              (out[1], new[5][1], lambda a: {"out": (out[0], a)}, [(0,)]),
+              (tables[0], new[0][0], lambda a: {"tables": [a] + tables[1:]}, [(i, j) for i in range(7) for j in range(4)]),
+              (tables[2], new[0][2], lambda a: {"tables": tables[:2] + [a] + tables[3:]}, [(i, 1) for i in range(11)])]
+    for arr, upd, put, idxs in checks:
+        g = (arr - upd) / lr
+        for idx in idxs:
+            assert abs(fd(arr, put, idx) - g[idx]) < 1e-8, (idx, fd(arr, put, idx), g[idx])
