@@ -247,7 +247,62 @@ def secondary(dev, rank):
                      "tensor_TFLOPs": flops * B / ms / 1e9, "tensor_frac": flops * B / ms / 1e9 / (pk["tf"] / 2),
                      "hbm_frac": algo * B / ms / 1e6 / pk["hbm_gbs"]}
         del mm
+    out["deepfm_train"] = train_leg(dev, timeit)
     return out
+
+
+def train_leg(dev, timeit):
+    """SGD steps per second of DeepFM through ctrhot_deepfm_train_step_f32 (what compile_fit runs per
+    batch) at the reference's batch size 32 and at 4096, beside the same step on the host cores (the reference's op
+    structure in torch-CPU with autograd: oracle/cpu_ref_torch.py)."""
+    import numpy as np
+    import torch
+    from oracle import cpu_ref_torch as R
+    from recommender_system_b200.layer import set_seed
+    from recommender_system_b200.model.criteo import DeepFM
+    from recommender_system_b200.utils import synth
+    from recommender_system_b200.utils.compile_fit import _DeepFMTrainer
+    vocab = [1000] * 26
+    set_seed(5)
+    m = DeepFM(synth.criteo_feature_columns(vocab, 8), 10, 1e-4, 1e-4, [256, 128, 64], 1, "relu", embed_dim=8,
+               precision="fp32", check_ids=False, device=dev)
+    m.build(None)
+    tr = _DeepFMTrainer(m, dropout=0.0)
+    res = {"metric": "DeepFM SGD steps/s (forward + backward + update, fp32)", "vocab": "26 x 1000, emb 8, fm k 10, tower 256-128-64"}
+    for B in (32, 4096):
+        dense, ids = synth.criteo_batch(B, vocab, seed=3)
+        y = (np.random.default_rng(4).random(B) < 0.3).astype(np.float32)
+        d, i, yy = (torch.from_numpy(a).to(dev) for a in (dense, ids, y))
+        # the same step on the CPU: parameters as autograd leaves, keras' loss, plain SGD
+        ct, cf, ch, co = cpu_weights(m)
+        tabs = [t.clone().requires_grad_(True) for t in ct]
+        fm = [t.clone().requires_grad_(True) for t in cf]
+        hid = [(k.clone().requires_grad_(True), b.clone().requires_grad_(True)) for k, b in ch]
+        outl = (co[0].clone().requires_grad_(True), co[1].clone().requires_grad_(True))
+        leaves = tabs + fm + [t for kb in hid for t in kb] + list(outl)
+        X = torch.from_numpy(np.concatenate([dense, ids.astype(np.float32)], axis=1))
+        yt = torch.from_numpy(y)
+
+        def cpu_step():
+            p = R.deepfm(X, tabs, fm, hid, outl)[:, 0].clamp(1e-7, 1 - 1e-7)
+            loss = -(yt * p.log() + (1 - yt) * (1 - p).log()).mean()
+            total = loss + 1e-4 * (fm[1] ** 2).sum() + 1e-4 * (fm[2] ** 2).sum()
+            grads = torch.autograd.grad(total, leaves)
+            with torch.no_grad():
+                for t, g in zip(leaves, grads):
+                    t -= 0.01 * g
+            return float(loss.detach())
+        gpu_loss = float(tr.train_on_batch(d, i, yy, 0.01)[0])          # first step of both: same weights, same batch
+        cpu_loss = cpu_step()
+        ms = timeit(lambda: tr.train_on_batch(d, i, yy, 0.01), 50, 5)
+        t0 = time.perf_counter()
+        n_cpu = 0
+        while time.perf_counter() - t0 < 1.5:
+            cpu_step(); n_cpu += 1
+        cpu_ms = (time.perf_counter() - t0) / n_cpu * 1e3
+        res["B%d" % B] = {"gpu_steps_per_s": 1e3 / ms, "gpu_samples_per_s": B / ms * 1e3, "cpu_steps_per_s": 1e3 / cpu_ms,
+                          "cpu_cores": torch.get_num_threads(), "first_step_loss_gpu": gpu_loss, "first_step_loss_cpu": cpu_loss}
+    return res
 
 
 def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, k=128, B=262144,

@@ -172,17 +172,28 @@ __global__ void tr_relu_drop_bwd_kernel(float* __restrict__ g, const float* __re
   }
 }
 
-// out[n] = beta * out[n] + alpha * sum_b w_b A[b, n] (w = NULL: ones); one thread per column, fixed order over b
-__global__ void tr_colsum_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ w, int64_t B, int N,
-                                 int square, float* __restrict__ out, float alpha, float beta) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+// out[n] = beta * out[n] + alpha * sum_b w_b A[b, n] (w = NULL: ones).  Block = 32 columns x 32 row groups; every thread sums
+// its rows in order, the 32 partial sums of a column are added in a fixed order: deterministic for a given B
+__global__ void __launch_bounds__(1024)
+tr_colsum_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ w, int64_t B, int N,
+                 int square, float* __restrict__ out, float alpha, float beta) {
+  __shared__ float part[32][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + cx;
   float s = 0.f;
-  for (int64_t b = 0; b < B; ++b) {
-    const float a = A[b * lda + n];
-    s = fmaf(w ? w[b] : 1.f, square ? a * a : a, s);
+  if (n < N)
+    for (int64_t b = ry; b < B; b += 32) {
+      const float a = A[b * lda + n];
+      s = fmaf(w ? w[b] : 1.f, square ? a * a : a, s);
+    }
+  part[ry][cx] = s;
+  __syncthreads();
+  if (ry == 0 && n < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int r = 0; r < 32; ++r) t += part[r][cx];
+    out[n] = (beta == 0.f ? 0.f : beta * out[n]) + alpha * t;
   }
-  out[n] = (beta == 0.f ? 0.f : beta * out[n]) + alpha * s;
 }
 
 // dx[b, j] += dfm_b (w1_j + sum_f v_jf xv_bf - x_bj sum_f v_jf^2);  also t[b, f] = dfm_b xv_bf (the right factor of dv)
@@ -310,7 +321,7 @@ extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off
     tr_gemm(st, dz, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 0.5f, 0.f);                 // [B,1] x [1,h]: B(k=0, n) = wo[n]
     tr_gemm(st, in, 1, in_dim, dz, 1, 1, wo, 1, in_dim, 1, M, -0.5f * lr, 1.f);           // w_out -= lr * h^T (dz / 2)
     if (h_layers[NH].bias)
-      tr_colsum_kernel<<<1, 32, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
+      tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
     float* tmp = g; g = gn; gn = tmp;
   }
   for (int l = NH - 1; l >= 0; --l) {
@@ -324,14 +335,14 @@ extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off
     tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);                           // W -= lr * in^T g
     if (h_layers[l].bias)
-      tr_colsum_kernel<<<(N + 127) / 128, 128, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- FM backward (old w1, v), then its updates: w0, w1 = (1 - 2 lr reg_w) w1 - lr x^T dfm, v likewise with its -x^2 v part
   tr_fm_bwd_kernel<<<tr_grid(B * n, 256), 256, 0, st>>>(x, n, B, dz, fm_w1, fm_v, k_fm, xv, dx, t);
-  tr_colsum_kernel<<<1, 32, 0, st>>>(dz, 1, nullptr, B, 1, 0, fm_w0, -0.5f * lr, 1.f);
-  tr_colsum_kernel<<<(n + 127) / 128, 128, 0, st>>>(x, n, dz, B, n, 0, fm_w1, -0.5f * lr, 1.f - 2.f * lr * reg_w);
-  tr_colsum_kernel<<<(n + 127) / 128, 128, 0, st>>>(x, n, dz, B, n, 1, s2, 0.5f, 0.f);  // s2[j] = sum_b dfm_b x_bj^2
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, fm_w0, -0.5f * lr, 1.f);
+  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 0, fm_w1, -0.5f * lr, 1.f - 2.f * lr * reg_w);
+  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 1, s2, 0.5f, 0.f);  // s2[j] = sum_b dfm_b x_bj^2
   tr_scale_rows_kernel<<<tr_grid((int64_t)n * k_fm, 256), 256, 0, st>>>(fm_v, n, k_fm, s2, 1.f - 2.f * lr * reg_v, lr);
   tr_gemm(st, x, 1, n, t, k_fm, 1, fm_v, k_fm, n, k_fm, M, -lr, 1.f);                      // v -= lr * x^T (dfm xv)
   // ---- embedding rows
