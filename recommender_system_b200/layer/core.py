@@ -40,7 +40,9 @@ class EmbedLayer(Layer):
         if init == "uniform" and total * self.k > (1 << 24) and self.device.type == "cuda":
             # large arenas: same U(-0.05, 0.05) law, generated on the device (no multi-GB host staging)
             g = torch.Generator(device=self.device)
-            g.manual_seed(20240 + total)
+            from .base import _GEN
+            g.manual_seed(_GEN["seed"] * 1000003 + total)          # follows set_seed like every other initialiser
+            _GEN["seed"] += 1
             self.arena = torch.empty((total, self.k), dtype=torch.float32, device=self.device)
             self.arena.uniform_(-0.05, 0.05, generator=g)
             self._weights["embeddings"] = self.arena

@@ -264,6 +264,8 @@ class Attention(Layer):
     PReLU) layers whose alpha is [T,h] (Keras builds PReLU over input_shape[1:]); 'dice': Dice
     layers only, no Dense projection, then Dense(1)."""
 
+    debug_checks = False        # True: also compare value with key element-wise when they are distinct tensors (device sync)
+
     def __init__(self, hidden_units, activation="prelu", device=None, precision="tf32"):
         super().__init__(device)
         self.hidden_units = list(hidden_units)
@@ -328,7 +330,10 @@ class Attention(Layer):
         require_cuda(key, "Attention")
         if value is not key:
             value = as_device_f32(value, self.device)
-            if value.data_ptr() != key.data_ptr() and not torch.equal(value, key):
+            # DIN passes seq_embed for both (DL/model/din.py:81).  Comparing two distinct tensors element-wise would synchronise
+            # the device on every call: shapes are checked always, contents only under Attention.debug_checks
+            if value.data_ptr() != key.data_ptr() and (tuple(value.shape) != tuple(key.shape) or
+                                                        (Attention.debug_checks and not torch.equal(value, key))):
                 raise ValueError("Attention: value must equal key (DIN passes seq_embed for both, DL/model/din.py:81)")
         B, T, K = key.shape
         arr, _keep = self.descs()

@@ -183,11 +183,22 @@ class ShardedEmbedding:
         """value(f, global row, col) from the counter-based hash: any rank can regenerate any row (oracle.synth.hash_table_value)."""
         _lib.call("ctrhot_shard_init_hash_f32", ptr(self.arena), ptr(self.row_off), self.total_rows, self.F, self.k,
                   self.G, self.rank, int(seed), stream_ptr())
+        self._fence_peers()
 
     def set_global_tables(self, tables):
         """Tests: take this rank's rows out of full tables (list of [V_f, k] arrays)."""
         parts = [torch.as_tensor(np.asarray(t)[self.rank::self.G], dtype=torch.float32) for t in tables]
         self.arena.copy_(torch.cat(parts, dim=0).to(self.device))
+        self._fence_peers()
+
+    def _fence_peers(self):
+        """The arena is peer-visible once connected: a fill must have finished on EVERY rank before any rank's kernels may read
+        rows over NVLink again (filling before connect() needs nothing: connect() itself synchronises and rendezvouses)."""
+        if self.peers is not None:
+            torch.cuda.synchronize(self.device)
+            import torch.distributed as dist
+            if self.G > 1 and dist.is_available() and dist.is_initialized():
+                dist.barrier()
 
     # -- the three CUDA steps
     def _route(self, ids):
