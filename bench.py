@@ -240,9 +240,11 @@ def secondary(dev, rank):
 
         def run_model():
             mm(cins[it[0] % 4]); it[0] += 1
+        mm.overlap_launches = True              # one-launch models only (Wide&Deep); DCN cfg 3 chains launches through HBM: ignored
         l0 = _lib.LAUNCHES[0]
         ms = timeit(run_model, 50, 10)
         out[name] = {"metric": "forward samples/s", "value": B / ms * 1e3, "ms_per_step": ms, "batch": B,
+                     "launch_overlap": name == "widedeep_cfg2b",
                      "launches_per_step": (_lib.LAUNCHES[0] - l0) / 60.0,
                      "tensor_TFLOPs": flops * B / ms / 1e9, "tensor_frac": flops * B / ms / 1e9 / (pk["tf"] / 2),
                      "hbm_frac": algo * B / ms / 1e6 / pk["hbm_gbs"]}
@@ -500,6 +502,7 @@ def main():
     ap.add_argument("--sharded-rows", type=int, default=10_000_000, help="rows per table of the config-5 measurement")
     ap.add_argument("--cluster", type=int, default=0, help="CTAs sharing each weight chunk by TMA multicast (0 = auto)")
     ap.add_argument("--no-overlap", action="store_true", help="ordinary stream order between steps (no programmatic dependent launch)")
+    ap.add_argument("--no-bind", action="store_true", help="N > 1: do not narrow each rank's CPU affinity to its GPU's NUMA node")
     ap.add_argument("--two-kernel", action="store_true", help="front (gather+FM) + tower kernels instead of the fused one")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ctrhot" else args.warmup
@@ -528,6 +531,11 @@ def main():
     NB = 4
     host = [synth.criteo_batch(B, vocab, seed=1234 + 97 * rank + i) for i in range(NB)]
     dev_in = [(torch.from_numpy(d).to(dev), torch.from_numpy(i).to(dev)) for d, i in host]
+    # N > 1: each rank allocates (first-touches) its pinned staging buffers and feeds from the NUMA node its GPU hangs off
+    # (utils/numa.py); at N = 1 the affinity is left alone so that the packer and the CPU baseline see every core
+    from recommender_system_b200.utils.numa import bound_to_gpu
+    binder = bound_to_gpu(local, enable=(world > 1 and not args.no_bind))
+    binder.__enter__()
     pinned = [(torch.from_numpy(d).pin_memory(), torch.from_numpy(i).pin_memory()) for d, i in host]
 
     def barrier():
@@ -637,6 +645,7 @@ def main():
                             model(__import__("recommender_system_b200.utils.transport", fromlist=["PackedRows"]).PackedRows(
                                 layout, recs[0].to(dev)))))
     h2d, d2h = pipe.h2d_bytes_packed, pipe.d2h_bytes
+    binder.__exit__(None, None, None)
     also = secondary(dev, rank) if (world == 1 and not args.no_secondary) else None
 
     if rank == 0:
@@ -682,7 +691,7 @@ def main():
                         "d2h_bytes_per_step": d2h, "steps": K2,
                         "input": "transport records, %d B/sample (13 float32 + ids at 1-3 bytes), one H2D copy per step, decoded "
                                  "in the whole-model kernel" % layout.rec_bytes,
-                        "bit_identical_to_int32_path": same, "host_pack_samples_per_s": pack_rate,
+                        "bit_identical_to_int32_path": same, "host_pack_samples_per_s": pack_rate, "host_affinity": binder.info,
                         "int32_input": {"value": B * world * K2 / t_int32, "h2d_bytes_per_step": pipe.h2d_bytes,
                                         "input": "(dense float32 [B,13], ids int32 [B,26]), two H2D copies per step"}},
                 "gpu_launches": launches, "clocks": clocks, "roofline": dom, "roofline_other": other,

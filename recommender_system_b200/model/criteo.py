@@ -295,8 +295,10 @@ class WideDeep(_EmbedTowerModel):
             _, dw, w0, wflat = self._wide_host
             out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
             ids2, kind, ids_ld = ids_arg(ids)
+            # overlap_launches: as for DeepFM -- consecutive calls on independent batches may overlap at their edges
             stack.run_widedeep(E, ids2, kind, ids_ld, B, self.deep.hidden[0][0], wflat, self.col_off, dense, D, dw, w0, 0.5,
-                               E.err_flag(), out)
+                               E.err_flag(), out,
+                               cluster=_lib.LAUNCH_OVERLAP if getattr(self, "overlap_launches", False) else 0)
             if self.check:
                 E.check_ids()
             return out
