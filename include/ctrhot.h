@@ -430,6 +430,15 @@ int ctrhot_din_fwd_tf32(const float* table, int64_t V, int K, const void* hist_i
                         const float* dense, int64_t dense_ld, int n_dense, int dense_col,
                         void* workspace, int64_t workspace_bytes, int* err_flag, void* stream);
 
+/* ---- 8(f) rank 4: AttentionSequencePoolingLayer.call, DL/layer/sequence.py:242-276, after its LocalActivationUnit ------------
+ * s_t = valid(t) ? scores[b, t] : (weight_normalization ? -2^32 + 1 : 0);  p = weight_normalization ? softmax over T : s;
+ * return_score ? out[b, 0:T] = p : out[b, 0:E] = sum_t p_t keys[b, t, :].   valid(t) = mask[b, t] != 0 (uint8, the keras mask
+ * of supports_masking=True) or, with mask NULL, t < lengths[b] (tf.sequence_mask(keys_length, T)).  keys [B, T, E], the
+ * sample stride key_ld_b >= T * E. */
+int ctrhot_seq_attn_pool_f32(const float* scores, int64_t score_ld, const float* keys, int64_t key_ld_b,
+                             const uint8_t* mask, int64_t mask_ld, const int32_t* lengths, int64_t B, int T, int E,
+                             int weight_normalization, int return_score, float* out, int64_t out_ld, void* stream);
+
 /* ---- one SGD step of DeepFM, the step on the right of the path ------------------------------
  * What compile_fit (DL/utils/compile_fit.py:9-15: SGD(lr), loss 'binary_crossentropy', model.fit) does to DeepFM
  * (DL/model/deepFM.py:15-31) for one batch: forward, mean clipped BCE + the l2 regularisers of FMLayer.build

@@ -509,6 +509,20 @@ def local_activation_unit(query, keys, kernels, biases, out_kernel, out_bias, ac
     return np.tensordot(att_out, out_kernel, axes=(-1, 0)) + out_bias
 
 
+def attention_sequence_pooling(query, keys, key_mask, kernels, biases, out_kernel, out_bias, act="sigmoid",
+                               weight_normalization=False, return_score=False, dice=None):
+    """AttentionSequencePoolingLayer.call, DL/layer/sequence.py:242-276: scores = LocalActivationUnit([query, keys]) [B,T,1]
+    -> transpose [B,1,T] -> where(key_mask, scores, paddings) with paddings -2^32+1 (weight_normalization) or 0 -> softmax over T
+    (weight_normalization only) -> @ keys [B,1,E] (or the scores themselves when return_score).  key_mask [B,T] bool: the
+    layer's ``mask[-1]`` (supports_masking) or ``sequence_mask(keys_length, T)``."""
+    score = np.transpose(local_activation_unit(query, keys, kernels, biases, out_kernel, out_bias, act, dice=dice), (0, 2, 1))
+    pad = (-2.0 ** 32 + 1) if weight_normalization else 0.0
+    out = np.where(np.asarray(key_mask, bool)[:, None, :], score, pad)
+    if weight_normalization:
+        out = softmax_last(out)
+    return out if return_score else out @ keys
+
+
 # --------------------------------------------------------------------------- SURVEY 8(f) rank 3: one SGD step of DeepFM
 # PARITY UNPINNED for this function: the reference trains through TensorFlow's autodiff and optimizer
 # (DL/utils/compile_fit.py:9-15), which cannot run in this container, and it ships no training fixtures.  The forward

@@ -484,6 +484,23 @@ def run_lau_dice(a):
     return O.local_activation_unit(a["query"], a["keys"], k, b, a["out_k"], a["out_b"], "dice", dice=dice)
 
 
+def make_seqpool(rng, K=8, hidden=(16, 8)):
+    a = make_lau(rng, K, hidden)
+    lens = rng.integers(0, T + 1, size=B)
+    lens[0], lens[1 % B] = 0, T                                # an empty and a full sequence
+    a["key_mask"] = (np.arange(T)[None, :] < lens[:, None])
+    a["keys_length"] = lens.reshape(B, 1).astype(np.int32)
+    return a
+
+
+def _run_seqpool(wn, ret, act="sigmoid"):
+    def run(a):
+        k, b, dice = _lau_parts(a)
+        return O.attention_sequence_pooling(a["query"], a["keys"], a["key_mask"], k, b, a["out_k"], a["out_b"], act,
+                                            weight_normalization=wn, return_score=ret, dice=dice if act == "dice" else None)
+    return run
+
+
 CASES = {
     "embed": (make_embed, run_embed),
     "wide": (make_wide, run_wide),
@@ -513,6 +530,9 @@ CASES = {
     "deepctr_dnn_bn_sigmoid": (make_deepctr_dnn, run_deepctr_dnn_bn_sigmoid),
     "lau_sigmoid": (make_lau, run_lau_sigmoid),
     "lau_dice": (make_lau, run_lau_dice),
+    "seqpool_softmax": (make_seqpool, _run_seqpool(True, False)),
+    "seqpool_plain": (make_seqpool, _run_seqpool(False, False)),
+    "seqpool_score": (make_seqpool, _run_seqpool(True, True)),
 }
 
 

@@ -32,7 +32,7 @@ class DenseDesc(ctypes.Structure):
                 ("reserved", ctypes.c_int32)]
 
 
-_SCALARS = {"int8_t": ctypes.c_int8, "double": ctypes.c_double, "uint64_t": ctypes.c_uint64, "int": ctypes.c_int, "int32_t": ctypes.c_int32, "int64_t": ctypes.c_int64, "float": ctypes.c_float}
+_SCALARS = {"uint8_t": ctypes.c_uint8, "int8_t": ctypes.c_int8, "double": ctypes.c_double, "uint64_t": ctypes.c_uint64, "int": ctypes.c_int, "int32_t": ctypes.c_int32, "int64_t": ctypes.c_int64, "float": ctypes.c_float}
 
 
 def _ctype(decl):

@@ -145,6 +145,7 @@ using namespace ctrhot;
 
 extern "C" int ctrhot_shard_init_hash_f32(float* arena, const int64_t* row_off, int64_t total_rows, int F, int k,
                                           int G, int rank, uint64_t seed, void* stream) {
+  CTRHOT_RANGE("ctrhot_shard_init_hash_f32");
   if (!arena || !row_off || F <= 0 || k <= 0 || G <= 0 || rank < 0 || rank >= G || total_rows < 0) return CTRHOT_EARG;
   if (total_rows == 0) return CTRHOT_OK;
   int64_t g = (total_rows * k + 255) / 256;
@@ -170,6 +171,7 @@ extern "C" const char* ctrhot_status_str(int status) {
 extern "C" const char* ctrhot_last_cuda_error(void) { return g_err; }
 
 extern "C" int ctrhot_check_flag(int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_check_flag");
   if (!err_flag) return CTRHOT_EARG;
   int h = 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -190,6 +192,7 @@ extern "C" int64_t ctrhot_shard_route_workspace_bytes(int64_t B, int F, int G) {
 extern "C" int ctrhot_shard_route_ids(const int32_t* ids, int64_t B, int F, int G,
                                       int32_t* send_local_row, int32_t* send_field, int32_t* send_slot,
                                       int32_t* counts, void* workspace, int64_t workspace_bytes, void* stream) {
+  CTRHOT_RANGE("ctrhot_shard_route_ids");
   if (!ids || !send_local_row || !send_field || !send_slot || !counts || !workspace) return CTRHOT_EARG;
   if (B < 0 || F <= 0 || G <= 0 || G > 1024 || B * F > 2147483647LL) return CTRHOT_EARG;
   if (workspace_bytes < ctrhot_shard_route_workspace_bytes(B, F, G)) return CTRHOT_EARG;
@@ -217,6 +220,7 @@ extern "C" int ctrhot_shard_route_ids(const int32_t* ids, int64_t B, int F, int 
 extern "C" int ctrhot_shard_gather_pack(const float* arena, const int64_t* row_off, int F, int k,
                                         const int32_t* local_row, const int32_t* field, int64_t n,
                                         float* rows, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_shard_gather_pack");
   if (!arena || !row_off || !local_row || !field || !rows || F <= 0 || k <= 0 || n < 0) return CTRHOT_EARG;
   if (k % 4 != 0 || !aligned16(arena) || !aligned16(rows)) return CTRHOT_ESHAPE;
   if (n == 0) return CTRHOT_OK;
@@ -230,6 +234,7 @@ extern "C" int ctrhot_shard_gather_pack(const float* arena, const int64_t* row_o
 
 extern "C" int ctrhot_shard_unpack(const float* rows, const int32_t* slot, int64_t n, int F, int k, int D,
                                    float* x, int64_t x_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_shard_unpack");
   if (!rows || !slot || !x || F <= 0 || k <= 0 || n < 0 || D < 0 || x_ld < (int64_t)D + (int64_t)F * k) return CTRHOT_EARG;
   if (k % 4 != 0 || !aligned16(rows)) return CTRHOT_ESHAPE;
   if (n == 0) return CTRHOT_OK;

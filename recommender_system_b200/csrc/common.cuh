@@ -1,6 +1,7 @@
 // Shared device/host helpers for libctrhot (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 #include "ctrhot.h"
 
@@ -21,6 +22,16 @@ void set_error_text(const char* text);
     }                                                       \
   } while (0)
 #define CTRHOT_LAUNCH_OK(where) CTRHOT_CUDA_OK(cudaGetLastError(), where)
+
+// NVTX range around every compute entry point (SURVEY 5 build note): named like the symbol, so a timeline reads in the C-ABI's
+// vocabulary.  Header-only nvtx3: a few nanoseconds when no tool is attached.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#define CTRHOT_RANGE(name) ::ctrhot::NvtxRange _ctrhot_nvtx_range(name)
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

@@ -218,6 +218,7 @@ extern "C" int ctrhot_din_attention_f32(const float* query, int64_t q_ld, const 
                                         const ctrhot_dense_desc* h_layers, int n_layers,
                                         const float* out_w, const float* out_b, float* out,
                                         int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_din_attention_f32");
   if (!query || !key || !mask || !out || !out_w || B < 0 || T <= 0 || K <= 0) return CTRHOT_EARG;
   if (q_ld < K || key_ld_b < (int64_t)T * K || out_ld < K || (n_layers > 0 && !h_layers)) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
@@ -233,6 +234,7 @@ extern "C" int ctrhot_din_attention_gather_f32(const float* table, int64_t V, in
                                                const float* out_w, const float* out_b, float* att_out,
                                                int64_t att_ld, float* item_out, int64_t item_ld,
                                                int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_din_attention_gather_f32");
   if (!table || !hist_ids || !cand_ids || !att_out || !out_w || B < 0 || T <= 0 || K <= 0 || V <= 0)
     return CTRHOT_EARG;
   if (hist_ld < T || cand_ld < 1 || att_ld < K || (item_out && item_ld < K) || (n_layers > 0 && !h_layers))

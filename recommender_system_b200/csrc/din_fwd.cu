@@ -809,6 +809,7 @@ extern "C" int64_t ctrhot_din_fwd_pack_bytes(int T, int K, int h1, int h2) {
 
 extern "C" int ctrhot_din_fwd_pack(const ctrhot_dense_desc* h_layers, int n_layers, const float* out_w, const float* out_b,
                                    int T, int K, void* packed, void* stream) {
+  CTRHOT_RANGE("ctrhot_din_fwd_pack");
   if (!h_layers || !out_w || !packed || !aligned16(packed)) return CTRHOT_EARG;
   if (!df_layers_ok(h_layers, n_layers, K)) return CTRHOT_ESHAPE;
   DfShape s;
@@ -834,6 +835,7 @@ extern "C" int ctrhot_din_fwd_tf32(const float* table, int64_t V, int K, const v
                                    float* emb, int64_t emb_ld, const int64_t* h_extras, int n_extras,
                                    const float* dense, int64_t dense_ld, int n_dense, int dense_col,
                                    void* workspace, int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_din_fwd_tf32");
   if (!table || !hist_ids || !cand_ids || !packed || !emb || !workspace || B < 0 || V <= 0) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
   if (n_extras < 0 || n_extras > DF_MAX_EXTRA || (n_extras > 0 && !h_extras) || n_dense < 0 || (n_dense > 0 && !dense)) return CTRHOT_EARG;
@@ -879,9 +881,11 @@ extern "C" int ctrhot_din_fwd_tf32(const float* table, int64_t V, int K, const v
 
 #ifdef DF_TRACE
 extern "C" int ctrhot_debug_din_fwd_cta(unsigned long long* h_out) {
+  CTRHOT_RANGE("ctrhot_debug_din_fwd_cta");
   return cudaMemcpyFromSymbol(h_out, ctrhot::df_cta, sizeof(unsigned long long) * 148 * 4) == cudaSuccess ? 0 : -3;
 }
 extern "C" int ctrhot_debug_din_fwd_trace(long long* h_out) {
+  CTRHOT_RANGE("ctrhot_debug_din_fwd_trace");
   return cudaMemcpyFromSymbol(h_out, ctrhot::df_trace, sizeof(long long) * 14 * 128) == cudaSuccess ? 0 : -3;
 }
 #endif

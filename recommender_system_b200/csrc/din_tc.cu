@@ -610,6 +610,7 @@ extern "C" int64_t ctrhot_din_pack_bytes(int T, int K, int h1, int h2) {
 
 extern "C" int ctrhot_din_pack(const ctrhot_dense_desc* h_layers, int n_layers, const float* out_w, const float* out_b,
                                int T, int K, void* packed, void* stream) {
+  CTRHOT_RANGE("ctrhot_din_pack");
   if (!h_layers || !out_w || !packed || !aligned16(packed)) return CTRHOT_EARG;
   if (!din_layers_ok(h_layers, n_layers, K)) return CTRHOT_ESHAPE;
   DinShape s;
@@ -636,6 +637,7 @@ extern "C" int ctrhot_din_attention_gather_tf32(const float* table, int64_t V, i
                                                 const void* packed, int h1, int h2,
                                                 float* att_out, int64_t att_ld, float* item_out, int64_t item_ld,
                                                 void* workspace, int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_din_attention_gather_tf32");
   if (!table || !hist_ids || !cand_ids || !packed || !att_out || !item_out || !workspace || B < 0 || V <= 0) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
   DinShape s;
@@ -682,6 +684,7 @@ extern "C" int ctrhot_din_attention_gather_tf32(const float* table, int64_t V, i
 
 #ifdef DT_TRACE
 extern "C" int ctrhot_debug_din_trace(long long* h_out) {
+  CTRHOT_RANGE("ctrhot_debug_din_trace");
   return cudaMemcpyFromSymbol(h_out, ctrhot::dt_trace, sizeof(long long) * 8 * 128) == cudaSuccess ? 0 : -3;
 }
 #endif

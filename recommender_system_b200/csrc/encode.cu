@@ -115,6 +115,7 @@ using namespace ctrhot;
 
 extern "C" int ctrhot_criteo_parse_tsv(const void* text, const int64_t* line_start, int64_t N, int has_label, int8_t* label,
                                        double* dense_raw, int64_t* tokens, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_criteo_parse_tsv");
   if (!text || !line_start || N < 0 || !dense_raw || !tokens || (has_label && !label)) return CTRHOT_EARG;
   if (N == 0) return CTRHOT_OK;
   int64_t grid = (N + 127) / 128;
@@ -128,6 +129,7 @@ extern "C" int ctrhot_criteo_parse_tsv(const void* text, const int64_t* line_sta
 extern "C" int ctrhot_criteo_encode(const double* dense_raw, const int64_t* tokens, int64_t N, const double* d_scale,
                                     const double* d_min, const int64_t* vocab, const int64_t* vocab_off, float* dense,
                                     int64_t dense_ld, int32_t* ids, int64_t ids_ld, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_criteo_encode");
   if (!dense_raw || !tokens || N < 0 || !d_scale || !d_min || !vocab || !vocab_off || !dense || !ids || dense_ld < ENC_D ||
       ids_ld < ENC_F) return CTRHOT_EARG;
   if (N == 0) return CTRHOT_OK;

@@ -981,6 +981,7 @@ extern "C" int64_t ctrhot_fused_pack_bytes(int n, int n1) {
 }
 
 extern "C" int ctrhot_fused_pack(const float* W1, const float* side, int n, int n1, int D, void* packed, void* stream) {
+  CTRHOT_RANGE("ctrhot_fused_pack");
   if (!W1 || !packed || n <= 0 || n1 <= 0 || n1 > FU_MAXN1 || D < 0 || D > n || !aligned16(packed)) return CTRHOT_EARG;
   const int KC1 = (n + 31) / 32, BN1 = fu_round(n1, 16);
   const int64_t total = (int64_t)KC1 * (BN1 + 2 * FU_SIDE) * 32;
@@ -994,15 +995,19 @@ extern "C" int ctrhot_fused_pack(const float* W1, const float* side, int n, int 
 
 #ifdef FU_TRACE
 extern "C" int ctrhot_debug_fused_trace(unsigned long long* h_out) {
+  CTRHOT_RANGE("ctrhot_debug_fused_trace");
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
 }
 extern "C" int ctrhot_debug_fused_trace2(unsigned long long* h_out) {
+  CTRHOT_RANGE("ctrhot_debug_fused_trace2");
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace2, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
 }
 extern "C" int ctrhot_debug_fused_trace3(unsigned long long* h_out) {
+  CTRHOT_RANGE("ctrhot_debug_fused_trace3");
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_trace3, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : -3;
 }
 extern "C" int ctrhot_debug_fused_times(unsigned long long* h_out) {
+  CTRHOT_RANGE("ctrhot_debug_fused_times");
   return cudaMemcpyFromSymbol(h_out, ctrhot::fu_times, sizeof(unsigned long long) * 256 * 4) == cudaSuccess ? 0 : -3;
 }
 #endif
@@ -1251,6 +1256,7 @@ extern "C" int ctrhot_ctr_fused_tf32(const float* arena, const int64_t* row_off,
                                      const ctrhot_dense_desc* h_layers, int n_layers,
                                      const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                                      int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_ctr_fused_tf32");
   if (!arena) return CTRHOT_EARG;
   return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, h_layers, n_layers, sq_w, mode,
                   n_side, h_combine, n_combine, apply_sigmoid, cluster, out, err_flag, stream);
@@ -1263,6 +1269,7 @@ extern "C" int ctrhot_ctr_fused_sharded_tf32(const void* const* arenas, const in
                                              const float* sq_w, int mode, int n_side, const float* h_combine,
                                              int n_combine, int apply_sigmoid, int cluster, float* out, int* err_flag,
                                              void* stream) {
+  CTRHOT_RANGE("ctrhot_ctr_fused_sharded_tf32");
   if (!arenas || G < 1 || G > FU_MAXG) return CTRHOT_EARG;
   const float* peers[FU_MAXG];
   for (int g = 0; g < G; ++g) peers[g] = static_cast<const float*>(arenas[g]);
@@ -1279,6 +1286,7 @@ extern "C" int ctrhot_ctr_fused_packed_tf32(const float* arena, const int64_t* r
                                             const ctrhot_dense_desc* h_layers, int n_layers,
                                             const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                                             int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_ctr_fused_packed_tf32");
   if (!arena || !records || !pack_desc || rec_bytes <= 0 || rec_bytes % 4 != 0 || dense_off < 0 || dense_off % 4 != 0 ||
       (int64_t)dense_off + 4 * (int64_t)D > rec_bytes || !aligned16(records)) return CTRHOT_EARG;
   FuExtra ex;
@@ -1302,6 +1310,7 @@ extern "C" int ctrhot_fused_plan_create(const float* arena, const int64_t* row_o
                                         const ctrhot_dense_desc* h_layers, int n_layers,
                                         const float* sq_w, int mode, int n_side, const float* h_combine, int n_combine,
                                         int apply_sigmoid, int cluster, int* err_flag, void** plan) {
+  CTRHOT_RANGE("ctrhot_fused_plan_create");
   if (!arena || !plan) return CTRHOT_EARG;
   FuPlan* pl = new (std::nothrow) FuPlan();
   if (!pl) return CTRHOT_EARG;
@@ -1331,6 +1340,7 @@ extern "C" int ctrhot_fused_plan_create(const float* arena, const int64_t* row_o
 
 extern "C" int ctrhot_fused_plan_run(const void* plan, const void* batch, const float* dense, int64_t M, float* out,
                                      void* stream) {
+  CTRHOT_RANGE("ctrhot_fused_plan_run");
   const FuPlan* pl = static_cast<const FuPlan*>(plan);
   if (!pl || !batch || !out || M < 0) return CTRHOT_EARG;
   if (M == 0) return CTRHOT_OK;
@@ -1351,6 +1361,7 @@ extern "C" int ctrhot_fused_plan_run(const void* plan, const void* batch, const 
 }
 
 extern "C" int ctrhot_fused_plan_destroy(void* plan) {
+  CTRHOT_RANGE("ctrhot_fused_plan_destroy");
   delete static_cast<FuPlan*>(plan);
   return CTRHOT_OK;
 }
@@ -1362,6 +1373,7 @@ extern "C" int ctrhot_fused_plan_destroy(void* plan) {
 extern "C" int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M,
                                       const ctrhot_dense_desc* h_layers, int n_layers, int apply_sigmoid, int cluster,
                                       float* out, void* stream) {
+  CTRHOT_RANGE("ctrhot_tower_rows_tf32");
   if (!x || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
   const int r = K % 4, k = K - r;
   return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, h_layers,
@@ -1373,6 +1385,7 @@ extern "C" int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64
 // ctrhot_tower_rows_tf32 with the last hidden layer + the final Dense).  h[m, 0:N] = tf32(act(x_m W + b)), h[m, N:h_ld) = 0.
 extern "C" int ctrhot_dense_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M, const ctrhot_dense_desc* layer,
                                       float* h, int64_t h_ld, int cluster, void* stream) {
+  CTRHOT_RANGE("ctrhot_dense_rows_tf32");
   if (!x || !layer || !h || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
   const int r = K % 4, k = K - r;
   FuExtra ex;
@@ -1389,6 +1402,7 @@ extern "C" int ctrhot_ctr_tower_tf32(const float* arena, const int64_t* row_off,
                                      const ctrhot_dense_desc* h_layers, int n_layers,
                                      const float* add_vec, float scale, int apply_sigmoid, int cluster,
                                      float* out, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_ctr_tower_tf32");
   if (!arena) return CTRHOT_EARG;
   FuExtra ex;
   ex.add_vec = add_vec; ex.out_scale = scale; ex.add_scale = scale;
@@ -1409,6 +1423,7 @@ extern "C" int ctrhot_widedeep_fused_tf32(const float* arena, const int64_t* row
                                           const float* wide_w, const int64_t* wide_off, const float* wide_dense,
                                           int64_t wide_dense_ld, int wide_D, const float* h_dw, float w0, float scale,
                                           int apply_sigmoid, int cluster, float* out, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_widedeep_fused_tf32");
   if (!arena || !wide_w || !wide_off) return CTRHOT_EARG;
   FuExtra ex;
   ex.out_scale = scale; ex.add_scale = scale; ex.add_const = scale * w0;
@@ -1427,6 +1442,7 @@ extern "C" int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* ro
                                            const ctrhot_dense_desc* layer, const float* cc_w, int n_side,
                                            const float* h_combine, int n_combine, float* h, int64_t h_ld, float* side_out,
                                            int cluster, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_dcn_first_layer_tf32");
   if (!arena || !cc_w || !side_out || !h) return CTRHOT_EARG;
   FuExtra ex;
   ex.h_out = h; ex.h_ld = h_ld; ex.cc_w = cc_w; ex.side_out = side_out;
@@ -1439,6 +1455,7 @@ extern "C" int ctrhot_tower_rows_post_tf32(const float* x, int64_t x_ld, int K, 
                                            const ctrhot_dense_desc* h_layers, int n_layers,
                                            const float* add_vec, float y_scale, float add_scale, float add_const,
                                            int apply_sigmoid, int cluster, float* out, void* stream) {
+  CTRHOT_RANGE("ctrhot_tower_rows_post_tf32");
   if (!x || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
   const int r = K % 4, k = K - r;
   FuExtra ex;

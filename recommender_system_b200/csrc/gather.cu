@@ -647,6 +647,7 @@ extern "C" int ctrhot_gather_f32(const float* arena, const int64_t* row_off, int
                                  const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
                                  const float* dense, int64_t dense_ld, int D,
                                  float* out, int64_t out_ld, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_gather_f32");
   if (!arena || !row_off || !ids || !out || F <= 0 || k <= 0 || B < 0 || D < 0) return CTRHOT_EARG;
   if (D > 0 && !dense) return CTRHOT_EARG;
   if (out_ld < (int64_t)D + (int64_t)F * k) return CTRHOT_EARG;
@@ -679,6 +680,7 @@ extern "C" int ctrhot_nfm_bi_f32(const float* arena, const int64_t* row_off, int
                                  const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
                                  const float* dense, int64_t dense_ld, int D,
                                  float* out, int64_t out_ld, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_nfm_bi_f32");
   if (!arena || !row_off || !ids || !out || F <= 0 || k <= 0 || B < 0 || D < 0) return CTRHOT_EARG;
   if (D > 0 && !dense) return CTRHOT_EARG;
   if (out_ld < (int64_t)D + k) return CTRHOT_EARG;
@@ -701,6 +703,7 @@ extern "C" int ctrhot_afm_pool_f32(const float* arena, const int64_t* row_off, i
                                    const void* ids, int ids_kind, int64_t ids_ld, int64_t B, int mode,
                                    const float* out_w, const float* out_b, int n_sigmoid, float* out, int* err_flag,
                                    void* stream) {
+  CTRHOT_RANGE("ctrhot_afm_pool_f32");
   if (!arena || !row_off || !ids || !out || !out_w || !out_b || F < 2 || k <= 0 || B < 0) return CTRHOT_EARG;
   if (mode < 0 || mode > 2 || n_sigmoid < 0 || n_sigmoid > 2) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
@@ -726,6 +729,7 @@ extern "C" int64_t ctrhot_fm_planes_bytes(int n, int kfm) {
 
 extern "C" int ctrhot_fm_pack_planes(const float* w1, const float* v, int n, int kfm, int D,
                                      float* planes, void* stream) {
+  CTRHOT_RANGE("ctrhot_fm_pack_planes");
   if (!w1 || (!v && kfm > 0) || !planes || n <= 0 || kfm < 0 || D < 0 || D > n) return CTRHOT_EARG;
   const int n_pad = (n + 31) / 32 * 32;
   fm_pack_planes_kernel<<<(n_pad + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -735,6 +739,7 @@ extern "C" int ctrhot_fm_pack_planes(const float* w1, const float* v, int n, int
 }
 
 extern "C" int ctrhot_permute_cols(const float* src, int rows, int n, int D, float* dst, void* stream) {
+  CTRHOT_RANGE("ctrhot_permute_cols");
   if (!src || !dst || rows <= 0 || n <= 0 || D < 0 || D > n) return CTRHOT_EARG;
   const int n_pad = (n + 31) / 32 * 32;
   dim3 grid((n_pad + 127) / 128, rows);
@@ -773,6 +778,7 @@ extern "C" int ctrhot_deepfm_front_f32(const float* arena, const int64_t* row_of
                                        const float* w0, const float* planes, int kfm,
                                        float* x, int64_t x_ld, float* fm_out, int* err_flag,
                                        void* stream) {
+  CTRHOT_RANGE("ctrhot_deepfm_front_f32");
   if (!w0 || !planes || !fm_out) return CTRHOT_EARG;
   FRONT_COMMON_CHECKS();
   const int k4 = k / 4;
@@ -811,6 +817,7 @@ extern "C" int ctrhot_dcn_front_f32(const float* arena, const int64_t* row_off, 
                                     int L, const float* cw, const float* cb, const float* final_w,
                                     float* x, int64_t x_ld, float* cross_out, int64_t cross_ld,
                                     float* cross_dot, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_dcn_front_f32");
   if (L < 0 || (L > 0 && (!cw || !cb)) || (final_w && !cross_dot)) return CTRHOT_EARG;
   FRONT_COMMON_CHECKS();
   if (cross_out && (cross_ld < n || cross_ld % 4 != 0 || cross_ld > n_pad + 32 || !aligned16(cross_out)))
@@ -839,6 +846,7 @@ extern "C" int ctrhot_dcn_front_f32(const float* arena, const int64_t* row_off, 
 extern "C" int ctrhot_combine_sigmoid_f32(const float* a, const float* b_, const float* b_scale,
                                           const float* bias, float scale, int64_t B, float* out,
                                           void* stream) {
+  CTRHOT_RANGE("ctrhot_combine_sigmoid_f32");
   if (!a || !out || B < 0) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
   combine_sigmoid_kernel<<<(unsigned)((B + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(

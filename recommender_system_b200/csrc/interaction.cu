@@ -1034,6 +1034,7 @@ using namespace ctrhot;
 
 extern "C" int ctrhot_wide_dense_f32(const float* x, int64_t x_ld, int64_t n, int64_t B,
                                      const float* w0, const float* w, float* out, void* stream) {
+  CTRHOT_RANGE("ctrhot_wide_dense_f32");
   if (!x || !w0 || !w || !out || n <= 0 || B < 0 || x_ld < n) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
   wide_dense_kernel<<<warp_grid(B, 8), 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w, out);
@@ -1045,6 +1046,7 @@ extern "C" int ctrhot_wide_onehot_f32(const float* dense, int64_t dense_ld, int 
                                       const int32_t* dense_col, const void* ids, int ids_kind,
                                       int64_t ids_ld, int F, const int64_t* col_off, int64_t B,
                                       const float* w0, const float* w, float* out, void* stream) {
+  CTRHOT_RANGE("ctrhot_wide_onehot_f32");
   if (!w0 || !w || !out || B < 0 || D < 0 || F < 0 || !IDS_OK(ids_kind)) return CTRHOT_EARG;
   if ((D > 0 && (!dense || !dense_col)) || (F > 0 && (!ids || !col_off))) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
@@ -1061,6 +1063,7 @@ extern "C" int ctrhot_wide_onehot_f32(const float* dense, int64_t dense_ld, int 
 extern "C" int ctrhot_fm_dense_f32(const float* x, int64_t x_ld, int64_t n, int64_t B,
                                    const float* w0, const float* w1, const float* v, int kfm,
                                    float* out, int apply_sigmoid, void* stream) {
+  CTRHOT_RANGE("ctrhot_fm_dense_f32");
   if (!x || !w0 || !w1 || !out || n <= 0 || B < 0 || x_ld < n || kfm < 0) return CTRHOT_EARG;
   if (kfm > 0 && !v) return CTRHOT_EARG;
   if (kfm > 31) return CTRHOT_ESHAPE;
@@ -1105,6 +1108,7 @@ extern "C" int ctrhot_fm_onehot_f32(const float* dense, int64_t dense_ld, int D,
                                     int64_t ids_ld, int F, const int64_t* col_off, int64_t B,
                                     const float* w0, const float* w1, const float* v, int kfm,
                                     float* out, int apply_sigmoid, void* stream) {
+  CTRHOT_RANGE("ctrhot_fm_onehot_f32");
   if (!w0 || !w1 || !out || B < 0 || D < 0 || F < 0 || kfm < 0 || !IDS_OK(ids_kind)) return CTRHOT_EARG;
   if ((D > 0 && (!dense || !dense_col)) || (F > 0 && (!ids || !col_off)) || (kfm > 0 && !v)) return CTRHOT_EARG;
   if (kfm > 31) return CTRHOT_ESHAPE;
@@ -1123,6 +1127,7 @@ extern "C" int ctrhot_ffm_onehot_f32(const float* dense, int64_t dense_ld, int D
                                      int ids_kind, int64_t ids_ld, int F, const int64_t* col_off,
                                      int64_t B, const float* w0, const float* w, const float* v,
                                      int field_num, int k, float* out, int apply_sigmoid, void* stream) {
+  CTRHOT_RANGE("ctrhot_ffm_onehot_f32");
   if (!w0 || !w || !v || !out || B < 0 || D < 0 || F < 0 || field_num <= 0 || k <= 0 || !IDS_OK(ids_kind))
     return CTRHOT_EARG;
   if ((D > 0 && !dense) || (F > 0 && (!ids || !col_off))) return CTRHOT_EARG;
@@ -1145,6 +1150,7 @@ extern "C" int ctrhot_ffm_onehot_f32(const float* dense, int64_t dense_ld, int D
 
 extern "C" int ctrhot_pnn_inner_f32(const float* e, int64_t e_ld, int F, int k, int64_t B,
                                     float* out, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_pnn_inner_f32");
   const int P = F * (F - 1) / 2;
   if (!e || !out || F < 2 || k <= 0 || B < 0 || e_ld < (int64_t)F * k || out_ld < P) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
@@ -1168,6 +1174,7 @@ extern "C" int ctrhot_pnn_inner_f32(const float* e, int64_t e_ld, int F, int k, 
 
 extern "C" int ctrhot_pnn_outer_f32(const float* e, int64_t e_ld, int F, int k, int64_t B,
                                     const float* W, float* out, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_pnn_outer_f32");
   const int P = F * (F - 1) / 2;
   if (!e || !W || !out || F < 2 || k <= 0 || B < 0 || e_ld < (int64_t)F * k || out_ld < P) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
@@ -1220,6 +1227,7 @@ extern "C" int ctrhot_pnn_outer_f32(const float* e, int64_t e_ld, int F, int k, 
 extern "C" int ctrhot_cross_f32(const float* x, int64_t x_ld, int d, int64_t B, int L,
                                 const float* w, const float* b, float* out, int64_t out_ld,
                                 const float* final_w, float* dot, void* stream) {
+  CTRHOT_RANGE("ctrhot_cross_f32");
   if (!x || d <= 0 || B < 0 || L < 0 || x_ld < d || (L > 0 && (!w || !b))) return CTRHOT_EARG;
   if (!out && !final_w) return CTRHOT_EARG;
   if ((out && out_ld < d) || (final_w && !dot)) return CTRHOT_EARG;
@@ -1255,6 +1263,7 @@ extern "C" int ctrhot_cross_f32(const float* x, int64_t x_ld, int d, int64_t B, 
 
 extern "C" int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas,
                                const float* mean, const float* var, float eps, float* out, void* stream) {
+  CTRHOT_RANGE("ctrhot_dice_f32");
   if (!x || !alphas || !mean || !var || !out || rows < 0 || h <= 0) return CTRHOT_EARG;
   const int64_t total = rows * h;
   if (total == 0) return CTRHOT_OK;

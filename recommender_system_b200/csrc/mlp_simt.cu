@@ -91,6 +91,7 @@ extern "C" int64_t ctrhot_mlp_workspace_bytes(int64_t M, const ctrhot_dense_desc
 extern "C" int ctrhot_mlp_f32(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_desc* h_layers,
                               int n_layers, float* out, int64_t out_ld, void* workspace,
                               int64_t workspace_bytes, void* stream) {
+  CTRHOT_RANGE("ctrhot_mlp_f32");
   if (!x || !h_layers || n_layers <= 0 || !out || M < 0) return CTRHOT_EARG;
   if (x_ld < h_layers[0].in_dim || out_ld < h_layers[n_layers - 1].out_dim) return CTRHOT_EARG;
   for (int l = 0; l < n_layers; ++l) {
@@ -155,6 +156,7 @@ static int mlp_static_scratch_ptr(float** out) {
 
 extern "C" int ctrhot_mlp_f32_static(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_desc* h_layers,
                                      int n_layers, float* out, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_mlp_f32_static");
   if (!x || !h_layers || n_layers <= 0 || !out || M < 0) return CTRHOT_EARG;
   if (x_ld < h_layers[0].in_dim || out_ld < h_layers[n_layers - 1].out_dim) return CTRHOT_EARG;
   for (int l = 0; l < n_layers; ++l) {

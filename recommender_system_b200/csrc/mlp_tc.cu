@@ -373,6 +373,7 @@ using namespace ctrhot;
 
 // tuning only: device buffer of kNumSMs * 4 counters filled by the next per-layer launches (NULL switches it off)
 extern "C" int ctrhot_debug_tc_trace(uint64_t* d_buf) {
+  CTRHOT_RANGE("ctrhot_debug_tc_trace");
   ctrhot::g_tc_trace = reinterpret_cast<unsigned long long*>(d_buf);
   return CTRHOT_OK;
 }
@@ -384,6 +385,7 @@ extern "C" int64_t ctrhot_mlp_pack_bytes(int in_dim, int out_dim) {
 }
 
 extern "C" int ctrhot_mlp_pack(const float* weight, int in_dim, int out_dim, void* packed, void* stream) {
+  CTRHOT_RANGE("ctrhot_mlp_pack");
   if (!weight || !packed || in_dim <= 0 || out_dim <= 0) return CTRHOT_EARG;
   if (!aligned16(packed)) return CTRHOT_EARG;
   const TcGeom g = tc_geom(in_dim, out_dim);
@@ -399,6 +401,7 @@ extern "C" int ctrhot_mlp_pack(const float* weight, int in_dim, int out_dim, voi
 extern "C" int ctrhot_mlp_tf32(const float* x, int64_t x_ld, int64_t M, const ctrhot_dense_desc* h_layers,
                                int n_layers, float* out, int64_t out_ld, void* workspace,
                                int64_t workspace_bytes, void* stream) {
+  CTRHOT_RANGE("ctrhot_mlp_tf32");
   if (!x || !h_layers || n_layers <= 0 || !out || M < 0) return CTRHOT_EARG;
   if (x_ld < h_layers[0].in_dim || out_ld < h_layers[n_layers - 1].out_dim) return CTRHOT_EARG;
   for (int l = 0; l < n_layers; ++l) {

@@ -106,9 +106,11 @@ shard_lookup_peer_kernel(const __grid_constant__ PeerArenas arenas, const int64_
 
 using namespace ctrhot;
 
-extern "C" int ctrhot_peer_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
+extern "C" int ctrhot_peer_handle_bytes(void) {
+  CTRHOT_RANGE("ctrhot_peer_handle_bytes"); return (int)sizeof(cudaIpcMemHandle_t); }
 
 extern "C" int ctrhot_peer_alloc(int64_t bytes, void** ptr) {
+  CTRHOT_RANGE("ctrhot_peer_alloc");
   if (!ptr || bytes < 0) return CTRHOT_EARG;
   *ptr = nullptr;
   CTRHOT_CUDA_OK(cudaMalloc(ptr, (size_t)(bytes > 0 ? bytes : 256)), "ctrhot_peer_alloc");
@@ -116,11 +118,13 @@ extern "C" int ctrhot_peer_alloc(int64_t bytes, void** ptr) {
 }
 
 extern "C" int ctrhot_peer_free(void* ptr) {
+  CTRHOT_RANGE("ctrhot_peer_free");
   if (ptr) CTRHOT_CUDA_OK(cudaFree(ptr), "ctrhot_peer_free");
   return CTRHOT_OK;
 }
 
 extern "C" int ctrhot_peer_export(void* ptr, void* handle_out) {
+  CTRHOT_RANGE("ctrhot_peer_export");
   if (!ptr || !handle_out) return CTRHOT_EARG;
   cudaIpcMemHandle_t h;
   CTRHOT_CUDA_OK(cudaIpcGetMemHandle(&h, ptr), "ctrhot_peer_export");
@@ -129,6 +133,7 @@ extern "C" int ctrhot_peer_export(void* ptr, void* handle_out) {
 }
 
 extern "C" int ctrhot_peer_open(const void* handle, void** ptr) {
+  CTRHOT_RANGE("ctrhot_peer_open");
   if (!handle || !ptr) return CTRHOT_EARG;
   cudaIpcMemHandle_t h;
   memcpy(&h, handle, sizeof(h));
@@ -138,6 +143,7 @@ extern "C" int ctrhot_peer_open(const void* handle, void** ptr) {
 }
 
 extern "C" int ctrhot_peer_enable(int peer_device) {
+  CTRHOT_RANGE("ctrhot_peer_enable");
   // one process driving several GPUs: let kernels on the current device dereference peer_device's allocations
   const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
   if (e == cudaErrorPeerAccessAlreadyEnabled) { (void)cudaGetLastError(); return CTRHOT_OK; }
@@ -146,6 +152,7 @@ extern "C" int ctrhot_peer_enable(int peer_device) {
 }
 
 extern "C" int ctrhot_peer_close(void* ptr) {
+  CTRHOT_RANGE("ctrhot_peer_close");
   if (ptr) CTRHOT_CUDA_OK(cudaIpcCloseMemHandle(ptr), "ctrhot_peer_close");
   return CTRHOT_OK;
 }
@@ -153,6 +160,7 @@ extern "C" int ctrhot_peer_close(void* ptr) {
 extern "C" int ctrhot_shard_lookup_peer_f32(const void* const* arenas, const int64_t* row_off, int F, int k, int G,
                                             const int32_t* ids, int64_t B, int D, const float* dense, int64_t dense_ld,
                                             float* x, int64_t x_ld, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_shard_lookup_peer_f32");
   if (!arenas || !row_off || !ids || !x || F <= 0 || G <= 0 || G > kMaxPeers || k <= 0 || (k & 3) || D < 0 || B < 0)
     return CTRHOT_EARG;
   if (x_ld < D + (int64_t)F * k || (dense && dense_ld < D)) return CTRHOT_ESHAPE;

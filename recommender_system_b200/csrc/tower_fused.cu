@@ -348,6 +348,7 @@ extern "C" int ctrhot_tower_fused_tf32(const float* x, int64_t x_ld, int64_t M,
                                        const ctrhot_dense_desc* h_layers, int n_layers,
                                        const float* y_scale, const float* add_vec, const float* add_bias,
                                        float scale, int apply_sigmoid, float* out, void* stream) {
+  CTRHOT_RANGE("ctrhot_tower_fused_tf32");
   if (!x || !out || M < 0) return CTRHOT_EARG;
   if (x_ld % 4 != 0 || !aligned16(x)) return CTRHOT_ESHAPE;
   FtParams p{};
@@ -368,6 +369,7 @@ extern "C" int ctrhot_tower_gather_tf32(const float* arena, const int64_t* row_o
                                         const ctrhot_dense_desc* h_layers, int n_layers,
                                         const float* y_scale, const float* add_vec, const float* add_bias,
                                         float scale, int apply_sigmoid, float* out, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_tower_gather_tf32");
   if (!arena || !row_off || !ids || !out || F <= 0 || k <= 0 || M < 0 || D < 0) return CTRHOT_EARG;
   if (D > 0 && !dense) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;

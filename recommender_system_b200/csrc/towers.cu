@@ -67,6 +67,7 @@ using namespace ctrhot;
 
 extern "C" int ctrhot_residual_relu_f32(const float* x, int64_t x_ld, const float* y, int64_t y_ld, int64_t M, int N,
                                         float* out, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_residual_relu_f32");
   if (!x || !y || !out || M < 0 || N <= 0 || x_ld < N || y_ld < N || out_ld < N) return CTRHOT_EARG;
   if (M == 0) return CTRHOT_OK;
   residual_relu_kernel<<<grid1d(M * N, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, x_ld, y, y_ld, M, N, out, out_ld);
@@ -76,6 +77,7 @@ extern "C" int ctrhot_residual_relu_f32(const float* x, int64_t x_ld, const floa
 
 extern "C" int ctrhot_mmoe_combine_f32(const float* expert, int64_t e_ld, const float* gate, int64_t g_ld, int64_t B, int H,
                                        int E, int T, float* out, int64_t out_task_stride, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_mmoe_combine_f32");
   if (!expert || !gate || !out || B < 0 || H <= 0 || E <= 0 || T <= 0 || e_ld < (int64_t)H * E || g_ld < (int64_t)T * E ||
       out_ld < H) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
@@ -87,10 +89,79 @@ extern "C" int ctrhot_mmoe_combine_f32(const float* expert, int64_t e_ld, const 
 
 extern "C" int ctrhot_lau_concat_f32(const float* query, int64_t q_ld, const float* keys, int64_t k_ld, int64_t B, int T, int K,
                                      float* out, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_lau_concat_f32");
   if (!query || !keys || !out || B < 0 || T <= 0 || K <= 0 || q_ld < K || k_ld < K || out_ld < 4 * (int64_t)K) return CTRHOT_EARG;
   if (B == 0) return CTRHOT_OK;
   lau_concat_kernel<<<grid1d(B * T * K, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(query, q_ld, keys, k_ld, B, T, K, out,
                                                                                           out_ld);
   CTRHOT_LAUNCH_OK("ctrhot_lau_concat_f32");
+  return CTRHOT_OK;
+}
+
+// ---- AttentionSequencePoolingLayer.call, DL/layer/sequence.py:242-276 (the part after the LocalActivationUnit) --------------
+// s_t = valid(t) ? score[b, t] : (weight_normalization ? -2^32 + 1 : 0);  p = weight_normalization ? softmax_T(s) : s;
+// return_score ? out[b, t] = p_t : out[b, e] = sum_t p_t keys[b, t, e].  valid(t) = mask[b, t] != 0 (keras mask) or t < lengths[b]
+// (tf.sequence_mask of keys_length).  One CTA per sample.
+namespace ctrhot {
+__global__ void __launch_bounds__(128)
+seq_attn_pool_kernel(const float* __restrict__ scores, int64_t score_ld, const float* __restrict__ keys, int64_t key_ld_b,
+                     const uint8_t* __restrict__ mask, int64_t mask_ld, const int32_t* __restrict__ lengths, int T, int E,
+                     int wn, int ret, float* __restrict__ out, int64_t out_ld) {
+  extern __shared__ float sp[];                              // [T] weights
+  __shared__ float red[4];
+  const int64_t b = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const float pad = wn ? -4294967295.0f : 0.f;
+  float m = -INFINITY;
+  for (int t = tid; t < T; t += 128) {
+    const bool ok = mask ? mask[b * mask_ld + t] != 0 : t < lengths[b];
+    const float s = ok ? scores[b * score_ld + t] : pad;
+    sp[t] = s;
+    m = fmaxf(m, s);
+  }
+  if (wn) {
+    m = warp_max(m);
+    if (lane == 0) red[w] = m;
+    __syncthreads();
+    m = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+    __syncthreads();
+    float sum = 0.f;
+    for (int t = tid; t < T; t += 128) { const float e = __expf(sp[t] - m); sp[t] = e; sum += e; }
+    sum = warp_sum(sum);
+    if (lane == 0) red[w] = sum;
+    __syncthreads();
+    const float inv = 1.f / ((red[0] + red[1]) + (red[2] + red[3]));
+    for (int t = tid; t < T; t += 128) sp[t] *= inv;
+  }
+  __syncthreads();
+  if (ret) {
+    for (int t = tid; t < T; t += 128) out[b * out_ld + t] = sp[t];
+    return;
+  }
+  const float* kb = keys + b * key_ld_b;
+  for (int e = tid; e < E; e += 128) {
+    float a0 = 0.f, a1 = 0.f;
+    int t = 0;
+    for (; t + 1 < T; t += 2) { a0 = fmaf(sp[t], kb[(int64_t)t * E + e], a0); a1 = fmaf(sp[t + 1], kb[(int64_t)(t + 1) * E + e], a1); }
+    if (t < T) a0 = fmaf(sp[t], kb[(int64_t)t * E + e], a0);
+    out[b * out_ld + e] = a0 + a1;
+  }
+}
+}  // namespace ctrhot
+
+extern "C" int ctrhot_seq_attn_pool_f32(const float* scores, int64_t score_ld, const float* keys, int64_t key_ld_b,
+                                        const uint8_t* mask, int64_t mask_ld, const int32_t* lengths, int64_t B, int T, int E,
+                                        int weight_normalization, int return_score, float* out, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_seq_attn_pool_f32");
+  if (!scores || !keys || !out || (!mask && !lengths) || B < 0 || T < 1 || E < 1 || score_ld < T || key_ld_b < (int64_t)T * E ||
+      (mask && mask_ld < T) || out_ld < (return_score ? T : E)) return CTRHOT_EARG;
+  if ((size_t)T * sizeof(float) > 200u * 1024u) return CTRHOT_ESHAPE;
+  if (B == 0) return CTRHOT_OK;
+  const size_t smem = (size_t)T * sizeof(float);
+  if (smem > 48u * 1024u)
+    CTRHOT_CUDA_OK(cudaFuncSetAttribute(ctrhot::seq_attn_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "seq_attn_pool attr");
+  ctrhot::seq_attn_pool_kernel<<<(unsigned)B, 128, smem, static_cast<cudaStream_t>(stream)>>>(
+      scores, score_ld, keys, key_ld_b, mask, mask_ld, lengths, T, E, weight_normalization, return_score, out, out_ld);
+  CTRHOT_LAUNCH_OK("ctrhot_seq_attn_pool_f32");
   return CTRHOT_OK;
 }

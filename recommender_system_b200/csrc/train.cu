@@ -281,6 +281,7 @@ extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off
                                             float reg_v, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
                                             float dropout, uint64_t seed, float* loss_out, void* workspace,
                                             int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_deepfm_train_step_f32");
   if (!arena || !row_off || !ids || !y || !fm_w0 || !fm_w1 || !fm_v || !loss_out || !workspace || F <= 0 || k <= 0 || D < 0 ||
       (D > 0 && !dense) || B <= 0 || ids_ld < F || (D > 0 && dense_ld < D)) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;

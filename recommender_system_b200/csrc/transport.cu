@@ -47,6 +47,7 @@ using namespace ctrhot;
 // h_vocab [F] -> h_desc [F] = (byte offset of field f in the record) | (width in bytes) << 16; returns the record size in bytes
 // (a multiple of 4), or a negative status.  The dense block sits at byte 0.
 extern "C" int ctrhot_rows_layout(const int64_t* h_vocab, int F, int D, int32_t* h_desc) {
+  CTRHOT_RANGE("ctrhot_rows_layout");
   if (!h_vocab || !h_desc || F <= 0 || D < 0) return CTRHOT_EARG;
   int64_t off = 4 * (int64_t)D;
   for (int f = 0; f < F; ++f) {
@@ -64,6 +65,7 @@ extern "C" int ctrhot_rows_layout(const int64_t* h_vocab, int F, int D, int32_t*
 // Returns CTRHOT_EID if some id does not fit its field's width (nothing is truncated silently: the record then holds 0).
 extern "C" int ctrhot_rows_pack_host(const float* h_dense, int64_t dense_ld, const int32_t* h_ids, int64_t ids_ld, int64_t B,
                                      const int32_t* h_desc, int F, int D, int64_t rec_bytes, void* h_records, int n_threads) {
+  CTRHOT_RANGE("ctrhot_rows_pack_host");
   if (!h_ids || !h_desc || !h_records || B < 0 || F <= 0 || D < 0 || (D > 0 && !h_dense) || rec_bytes <= 0) return CTRHOT_EARG;
   if (ids_ld < F || (D > 0 && dense_ld < D)) return CTRHOT_EARG;
   int64_t end = 4 * (int64_t)D;
@@ -113,6 +115,7 @@ extern "C" int ctrhot_rows_pack_host(const float* h_dense, int64_t dense_ld, con
 // that takes (dense, ids).  desc: DEVICE int32 [F].
 extern "C" int ctrhot_rows_unpack(const void* records, int64_t rec_bytes, const int32_t* desc, int F, int dense_off, int D,
                                   int64_t M, float* dense, int64_t dense_ld, int32_t* ids, int64_t ids_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_rows_unpack");
   if (!records || !desc || !ids || F <= 0 || D < 0 || M < 0 || rec_bytes <= 0 || rec_bytes % 4 != 0 || dense_off < 0 ||
       dense_off % 4 != 0 || (D > 0 && !dense) || ids_ld < F || (D > 0 && dense_ld < D)) return CTRHOT_EARG;
   if ((reinterpret_cast<uintptr_t>(records) & 3u) != 0) return CTRHOT_EARG;

@@ -1,0 +1,66 @@
+"""Drop-in for the attention pooling of the reference's ``layer/sequence.py`` (DL/layer/sequence.py:180-290):
+
+``AttentionSequencePoolingLayer(att_hidden_units=(80, 40), att_activation='sigmoid', weight_normalization=False,
+return_score=False, supports_masking=False)``; ``call([query [B,1,E], keys [B,T,E], keys_length [B,1]])`` -> ``[B,1,E]``
+(``[B,1,T]`` with ``return_score``); with ``supports_masking=True``: ``call([query, keys], mask=[None, key_mask [B,T]])``.
+
+The LocalActivationUnit scores run on the tensor-pipe tower (layer/core.py), the mask / softmax / weighted sum is one launch
+(ctrhot_seq_attn_pool_f32).  The reference's ``keys_length`` branch raises as written (``as_list[1]`` subscripts a method,
+sequence.py:248); it is implemented here as DeepCTR means it: ``tf.sequence_mask(keys_length, T)``.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import _lib
+from .base import Layer, as_device_f32, ptr, require_cuda, stream_ptr
+from .core import LocalActivationUnit
+
+
+class AttentionSequencePoolingLayer(Layer):
+    def __init__(self, att_hidden_units=(80, 40), att_activation="sigmoid", weight_normalization=False, return_score=False,
+                 supports_masking=False, precision="tf32", device=None, **kwargs):
+        super().__init__(device)
+        self.att_hidden_units = list(att_hidden_units)
+        self.att_activation = att_activation
+        self.weight_normalization = bool(weight_normalization)
+        self.return_score = bool(return_score)
+        self.supports_masking = bool(supports_masking)
+        # LocalActivationUnit(hidden, activation, l2_reg=0, dropout_rate=0, use_bn=False, seed=1024) -- sequence.py:238-239
+        self.local_att = self.track(LocalActivationUnit(self.att_hidden_units, att_activation, 0, 0, False, seed=1024,
+                                                        precision=precision, device=self.device))
+
+    def build(self, input_shape):
+        if not self.supports_masking:
+            if not isinstance(input_shape, (list, tuple)) or len(input_shape) != 3:
+                raise ValueError("A `AttentionSequencePoolingLayer` layer should be called on a list of 3 inputs")
+        if not self.local_att.built:
+            self.local_att.build(list(input_shape[:2]))
+            self.local_att.built = True
+
+    def call(self, inputs, mask=None, training=None, **kwargs):
+        if self.supports_masking:
+            if mask is None:
+                raise ValueError("When supports_masking=True,input must support masking")
+            queries, keys = inputs
+            key_mask, lengths = mask[-1], None
+        else:
+            queries, keys, lengths = inputs
+            key_mask = None
+        keys = as_device_f32(keys, self.device)
+        require_cuda(keys, "AttentionSequencePoolingLayer")
+        if keys.stride(2) != 1 or keys.stride(1) != keys.shape[2]:
+            keys = keys.contiguous()
+        B, T, E = keys.shape
+        score = self.local_att([queries, keys], training=training).reshape(B, T)
+        if key_mask is not None:
+            m = torch.as_tensor(key_mask).to(self.device)
+            m = (m != 0).to(torch.uint8).reshape(B, T).contiguous()
+            mp, mld, lp = ptr(m), T, None
+        else:
+            ln = torch.as_tensor(lengths).to(self.device).reshape(B).to(torch.int32).contiguous()
+            mp, mld, lp = None, 0, ptr(ln)
+        out = torch.empty((B, 1, T if self.return_score else E), dtype=torch.float32, device=self.device)
+        _lib.call("ctrhot_seq_attn_pool_f32", ptr(score), score.stride(0), ptr(keys), keys.stride(0), mp, mld, lp, B, T, E,
+                  int(self.weight_normalization), int(self.return_score), ptr(out), out.stride(0), stream_ptr())
+        return out

@@ -434,6 +434,36 @@ def _r_lau(act):
     return run
 
 
+def _r_seqpool(wn, ret):
+    """AttentionSequencePoolingLayer, DL/layer/sequence.py:180-276.  With ``supports_masking=False`` the reference's call()
+    raises as written (``keys.get_shape().as_list[1]``: a method is subscripted, :252): asserted here.  The same body runs
+    unmodified with ``supports_masking=True`` and the key mask handed in as keras would (``mask[-1]``)."""
+    import layer.sequence as RS
+
+    def run(a):
+        ks, bs, _ = synth._lau_parts(a)
+        x = [SO._t(a["query"]), SO._t(a["keys"])]
+        broken = RS.AttentionSequencePoolingLayer([k.shape[1] for k in ks], "sigmoid", weight_normalization=wn, return_score=ret)
+        try:
+            broken(x + [SO._t(a["keys_length"])])
+            raise AssertionError("the reference's keys_length path was expected to raise")
+        except (TypeError, AttributeError):                    # TensorShape.as_list is a method (TypeError in TF); the shim's shape is a tuple
+            pass
+        lyr = RS.AttentionSequencePoolingLayer([k.shape[1] for k in ks], "sigmoid", weight_normalization=wn, return_score=ret,
+                                               supports_masking=True)
+        mask = [None, SO._t(a["key_mask"])]
+
+        def inj(o):
+            put(o.local_att, "kernel", a["out_k"]); put(o.local_att, "bias", a["out_b"])
+            for i in range(len(ks)):
+                put(o.local_att.dnn, "kernels", ks[i], i)
+                put(o.local_att.dnn, "bias", bs[i], i)
+        lyr(x, mask=mask)                                      # first pass builds the weights
+        inj(lyr)
+        return np.asarray(lyr(x, mask=mask))
+    return run
+
+
 RUNNERS = {
     "embed": r_embed, "wide": r_wide, "fm": r_fm, "dnn": r_dnn, "cross": r_cross, "ffm": r_ffm, "inner": r_inner,
     "outer": r_outer, "dice": r_dice, "att": r_att, "att_dice": r_att_dice, "deepfm": r_deepfm,
@@ -442,6 +472,7 @@ RUNNERS = {
     "res": r_res, "deepcrossing": r_deepcrossing, "mmoe_layer": r_mmoe_layer, "mmoe": r_mmoe,
     "deepctr_dnn_relu": _r_deepctr_dnn("relu", False, None), "deepctr_dnn_bn_sigmoid": _r_deepctr_dnn("sigmoid", True, "tanh"),
     "lau_sigmoid": _r_lau("sigmoid"), "lau_dice": _r_lau("dice"),
+    "seqpool_softmax": _r_seqpool(True, False), "seqpool_plain": _r_seqpool(False, False), "seqpool_score": _r_seqpool(True, True),
 }
 MODEL_WRAPPERS = {"fm": r_fm_model, "ffm": r_ffm_model}
 

@@ -64,6 +64,7 @@ def install():
         return sys.modules["tensorflow"]
     layer_attrs = {n: getattr(L, n) for n in _LAYER_NAMES}
     tf = _mod("tensorflow", **{n: getattr(O, n) for n in O.__all__})
+    tf.__version__ = "2.9.0"          # the reference branches on it (layer/sequence.py:268, layer/utils.py); a TF 2 answer
     _mod("tensorflow.nn", softmax=O.softmax, sigmoid=O.sigmoid, relu=O.relu, bias_add=O.bias_add)
     _mod("tensorflow.strings", to_hash_bucket_fast=O.to_hash_bucket_fast, as_string=O.as_string)
     _mod("tensorflow.python")

@@ -119,6 +119,51 @@ def test_local_activation_unit(golden, lib, prec, act):
     assert got.shape == want.shape and err(got, want) <= TOL[prec]
 
 
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+@pytest.mark.parametrize("case", ["seqpool_softmax", "seqpool_plain", "seqpool_score"])
+def test_attention_sequence_pooling(golden, lib, prec, case):
+    """AttentionSequencePoolingLayer (DL/layer/sequence.py:180-276) against the reference's own output: with the keras mask
+    (the path that runs as written) and with keys_length (the path the reference means; it raises there as written)."""
+    from recommender_system_b200.layer.sequence import AttentionSequencePoolingLayer
+    a, want = S.load_case(golden, case)
+    ks, bs, _ = S._lau_parts(a)
+    wn, ret = case != "seqpool_plain", case == "seqpool_score"
+    w = {"LocalActivationUnit_0/kernel": a["out_k"], "LocalActivationUnit_0/bias": a["out_b"]}
+    for i in range(len(ks)):
+        w["LocalActivationUnit_0/DNN_0/kernel%d" % i], w["LocalActivationUnit_0/DNN_0/bias%d" % i] = ks[i], bs[i]
+    for masking in (True, False):
+        L = AttentionSequencePoolingLayer([k.shape[1] for k in ks], "sigmoid", weight_normalization=wn, return_score=ret,
+                                          supports_masking=masking, precision=prec)
+        L.build([a["query"].shape, a["keys"].shape, a["keys_length"].shape])
+        L.set_weights(w)
+        if masking:
+            got = npy(L([a["query"], a["keys"]], mask=[None, a["key_mask"]]))
+        else:
+            got = npy(L([a["query"], a["keys"], a["keys_length"]]))
+        assert got.shape == want.shape and err(got, want) <= TOL[prec], (masking, err(got, want))
+
+
+def test_attention_sequence_pooling_at_din_shape(lib):
+    """B = 3 000, T = 100, E = 64, 80-40 against the float64 oracle, ragged lengths incl. empty and full sequences."""
+    from recommender_system_b200.layer.sequence import AttentionSequencePoolingLayer
+    rng = np.random.default_rng(11)
+    B, T, E = 3000, 100, 64
+    q = np.asarray(rng.normal(0, 0.5, (B, 1, E)), np.float32)
+    keys = np.asarray(rng.normal(0, 0.5, (B, T, E)), np.float32)
+    lens = rng.integers(0, T + 1, size=(B, 1)).astype(np.int32)
+    lens[0], lens[1] = 0, T
+    L = AttentionSequencePoolingLayer((80, 40), "sigmoid", weight_normalization=True, precision="fp32")
+    L.build([q.shape, keys.shape, lens.shape])
+    got = npy(L([q, keys, lens]))
+    wt = {n: npy(t) for n, t in L.named_weights().items()}
+    ks = [wt["LocalActivationUnit_0/DNN_0/kernel%d" % i] for i in range(2)]
+    bs = [wt["LocalActivationUnit_0/DNN_0/bias%d" % i] for i in range(2)]
+    want = O.attention_sequence_pooling(q.astype(np.float64), keys.astype(np.float64), np.arange(T)[None, :] < lens, ks, bs,
+                                        wt["LocalActivationUnit_0/kernel"], wt["LocalActivationUnit_0/bias"], "sigmoid", True, False)
+    assert np.max(np.abs(got - want)) <= 2e-5
+    np.testing.assert_allclose(got[0, 0], keys[0].astype(np.float64).mean(0), rtol=1e-5, atol=1e-6)     # empty: uniform over T
+
+
 def test_towers_at_size(lib):
     """Ragged, larger shapes against the float64 oracle: DeepCrossing at the reference script's own settings (hidden 256-256,
     4 residual units, deepCrossing.py:37-39) on 5 000 samples; MMoE with 8 experts / 3 tasks on 10 001 rows; the local
