@@ -302,7 +302,20 @@ def train_leg(dev, timeit):
         while time.perf_counter() - t0 < 1.5:
             cpu_step(); n_cpu += 1
         cpu_ms = (time.perf_counter() - t0) / n_cpu * 1e3
+        # the same step as ONE captured CUDA graph replayed per batch (what compile_fit does): rows [row0, row0 + B) of a
+        # 64-batch device matrix, the control block rewinds every 64 replays
+        Xg = torch.from_numpy(np.tile(np.concatenate([dense, ids.astype(np.float32)], axis=1), (64, 1))).to(dev)
+        yg = torch.from_numpy(np.tile(y, 64)).to(dev)
+        tr.capture(Xg, yg, B, 0.01)
+        rep = [0]
+
+        def graph_step():
+            if rep[0] % 64 == 0:
+                tr.epoch_begin()
+            tr.graph.replay(); rep[0] += 1
+        ms_g = timeit(graph_step, 128, 8)
         res["B%d" % B] = {"gpu_steps_per_s": 1e3 / ms, "gpu_samples_per_s": B / ms * 1e3, "cpu_steps_per_s": 1e3 / cpu_ms,
+                          "gpu_graph_steps_per_s": 1e3 / ms_g, "gpu_graph_samples_per_s": B / ms_g * 1e3,
                           "cpu_cores": torch.get_num_threads(), "first_step_loss_gpu": gpu_loss, "first_step_loss_cpu": cpu_loss}
     return res
 

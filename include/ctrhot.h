@@ -459,6 +459,18 @@ int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off, int F, in
                                  float reg_v, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
                                  float dropout, uint64_t seed, float* loss_out, void* workspace,
                                  int64_t workspace_bytes, int* err_flag, void* stream);
+/* The same step driven by a 32-byte DEVICE control block {uint64 step; int64 row0; float acc_loss; float acc_correct; int64 pad}
+ * (caller-owned, 8-byte aligned, zero it before an epoch): the batch is rows [row0, row0 + B) of ids / dense / y, `step` is added
+ * to the dropout seed, the batch's summed BCE and correct count are added to acc_*, and the LAST kernel of the step does
+ * step += 1, row0 += B.  Nothing about a batch is in the launch parameters any more, so one captured CUDA graph of this call
+ * (no allocation, no synchronisation inside) is replayed once per batch: at the reference's batch size of 32 the step is ~25
+ * small launches and the graph removes their host cost. */
+int ctrhot_deepfm_train_step_ctl_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids,
+                                     int ids_kind, int64_t ids_ld, const float* dense, int64_t dense_ld, int D,
+                                     const float* y, int64_t B, float* fm_w0, float* fm_w1, float* fm_v, int k_fm,
+                                     float reg_w, float reg_v, const ctrhot_dense_desc* h_layers, int n_layers,
+                                     float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                     int64_t workspace_bytes, int* err_flag, void* d_ctl, void* stream);
 
 /* ---- R12/R14 fused model front ends ------------------------------------------
  * gather -> x=[dense, embed] -> FM (DeepFM, DL/model/deepFM.py:24-28) or L cross

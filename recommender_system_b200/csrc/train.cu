@@ -21,6 +21,18 @@ namespace ctrhot {
 constexpr int TR_T = 32;                       // GEMM tile
 constexpr int TR_MAXL = 8;
 
+// Optional device-resident control block (ctrhot_deepfm_train_step_ctl_f32): lets ONE captured CUDA graph of the step be
+// replayed over consecutive batches -- the kernels read the batch's first row and the step number from here, and the last
+// kernel of the step advances them.  32 bytes, caller-owned.
+struct TrCtl {
+  unsigned long long step;       // added to the dropout seed
+  long long row0;                // first row of this batch inside ids / dense / y
+  float acc_loss;                // += (sum over the batch of the per-sample BCE) -- an epoch's running total
+  float acc_correct;             // += number of correct predictions
+  long long reserved;
+};
+__global__ void tr_advance_kernel(TrCtl* ctl, long long B) { ctl->step += 1; ctl->row0 += B; }
+
 // C[m, n] = beta * C[m, n] + alpha * sum_k A(m, k) B(k, n);  A(m, k) = A[m * am + k * ak], B(k, n) = B[k * bk + n * bn]
 __global__ void __launch_bounds__(256)
 tr_gemm_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float* __restrict__ Bm, int64_t bk, int64_t bn,
@@ -70,16 +82,18 @@ __device__ __forceinline__ float tr_uniform(uint64_t seed, uint32_t layer, uint6
 template <int IDKIND>
 __global__ void tr_gather_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
                                  const void* __restrict__ ids, int64_t ids_ld, const float* __restrict__ dense, int64_t dense_ld,
-                                 int D, int64_t B, float* __restrict__ x, int n, int* __restrict__ err_flag) {
+                                 int D, int64_t B, float* __restrict__ x, int n, int* __restrict__ err_flag,
+                                 const TrCtl* __restrict__ ctl) {
+  const int64_t r0 = ctl ? ctl->row0 : 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t b = i / n;
     const int c = (int)(i - b * n);
     float v;
     if (c < D) {
-      v = dense[b * dense_ld + c];
+      v = dense[(b + r0) * dense_ld + c];
     } else {
       const int f = (c - D) / k, e = (c - D) - f * k;
-      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      const int64_t id = IdLoad<IDKIND>::at(ids, (b + r0) * ids_ld + f);
       const int64_t rows = row_off[f + 1] - row_off[f];
       const bool ok = id >= 0 && id < rows;
       if (!ok && err_flag) *err_flag = 1;
@@ -124,8 +138,9 @@ __global__ void tr_fm_fwd_kernel(const float* __restrict__ x, int n, int64_t B, 
 
 // h = dropout(relu(h + bias)) in place (h holds the GEMM result); mask recomputable from (seed, layer, element)
 __global__ void tr_bias_relu_drop_kernel(float* __restrict__ h, const float* __restrict__ bias, int N, int64_t B, int relu,
-                                         float rate, uint64_t seed, uint32_t layer) {
+                                         float rate, uint64_t seed, uint32_t layer, const TrCtl* __restrict__ ctl) {
   const float scale = rate > 0.f ? 1.f / (1.f - rate) : 1.f;
+  if (ctl) seed += ctl->step;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * N; i += (int64_t)gridDim.x * blockDim.x) {
     float t = h[i] + (bias ? bias[i % N] : 0.f);
     if (relu) t = fmaxf(t, 0.f);
@@ -136,9 +151,11 @@ __global__ void tr_bias_relu_drop_kernel(float* __restrict__ h, const float* __r
 
 // p, per-sample loss / correctness and dz = dLoss/dlogit (loss = mean BCE over the batch, probabilities clipped like keras)
 __global__ void tr_loss_kernel(const float* __restrict__ fm, const float* __restrict__ dnn, const float* __restrict__ b_out,
-                               const float* __restrict__ y, int64_t B, float* __restrict__ dz, float* __restrict__ loss_out) {
+                               const float* __restrict__ y, int64_t B, float* __restrict__ dz, float* __restrict__ loss_out,
+                               TrCtl* __restrict__ ctl) {
   __shared__ float s_loss[256], s_ok[256];
   float l = 0.f, ok = 0.f;
+  if (ctl) y += ctl->row0;
   for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
     const float z = 0.5f * (fm[b] + dnn[b] + (b_out ? b_out[0] : 0.f));
     const float p = 1.0f / (1.0f + __expf(-z));
@@ -157,13 +174,17 @@ __global__ void tr_loss_kernel(const float* __restrict__ fm, const float* __rest
     if (threadIdx.x < o) { s_loss[threadIdx.x] += s_loss[threadIdx.x + o]; s_ok[threadIdx.x] += s_ok[threadIdx.x + o]; }
     __syncthreads();
   }
-  if (threadIdx.x == 0) { loss_out[0] = s_loss[0] / (float)B; loss_out[1] = s_ok[0]; }
+  if (threadIdx.x == 0) {
+    loss_out[0] = s_loss[0] / (float)B; loss_out[1] = s_ok[0];
+    if (ctl) { ctl->acc_loss += s_loss[0]; ctl->acc_correct += s_ok[0]; }
+  }
 }
 
 // g[b, n] *= (h[b, n] > 0 ? dropout scale : 0): the derivative of dropout(relu(.)) at the stored activation
 __global__ void tr_relu_drop_bwd_kernel(float* __restrict__ g, const float* __restrict__ h, int64_t total, int relu, float rate,
-                                        uint64_t seed, uint32_t layer) {
+                                        uint64_t seed, uint32_t layer, const TrCtl* __restrict__ ctl) {
   const float scale = rate > 0.f ? 1.f / (1.f - rate) : 1.f;
+  if (ctl) seed += ctl->step;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     float m = 1.f;
     if (rate > 0.f) m = (tr_uniform(seed, layer, (uint64_t)i) >= rate) ? scale : 0.f;
@@ -221,12 +242,13 @@ __global__ void tr_scale_rows_kernel(float* __restrict__ v, int n, int kf, const
 template <int IDKIND>
 __global__ void tr_embed_sgd_kernel(float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
                                     const void* __restrict__ ids, int64_t ids_ld, int D, int64_t B, const float* __restrict__ dx,
-                                    int n, float lr) {
+                                    int n, float lr, const TrCtl* __restrict__ ctl) {
   const int fk = F * k;
+  const int64_t r0 = ctl ? ctl->row0 : 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * fk; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t b = i / fk;
     const int c = (int)(i - b * fk), f = c / k, e = c - f * k;
-    const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+    const int64_t id = IdLoad<IDKIND>::at(ids, (b + r0) * ids_ld + f);
     if (id >= 0 && id < row_off[f + 1] - row_off[f])
       atomicAdd(arena + (row_off[f] + id) * k + e, -lr * dx[b * n + D + c]);
   }
@@ -275,13 +297,12 @@ extern "C" int64_t ctrhot_deepfm_train_workspace_bytes(int64_t B, int n, int k_f
   return w.total * (int64_t)sizeof(float);
 }
 
-extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
-                                            int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
-                                            int64_t B, float* fm_w0, float* fm_w1, float* fm_v, int k_fm, float reg_w,
-                                            float reg_v, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
-                                            float dropout, uint64_t seed, float* loss_out, void* workspace,
-                                            int64_t workspace_bytes, int* err_flag, void* stream) {
-  CTRHOT_RANGE("ctrhot_deepfm_train_step_f32");
+static int tr_step(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                   int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                   int64_t B, float* fm_w0, float* fm_w1, float* fm_v, int k_fm, float reg_w,
+                   float reg_v, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
+                   float dropout, uint64_t seed, float* loss_out, void* workspace,
+                   int64_t workspace_bytes, int* err_flag, TrCtl* ctl, void* stream) {
   if (!arena || !row_off || !ids || !y || !fm_w0 || !fm_w1 || !fm_v || !loss_out || !workspace || F <= 0 || k <= 0 || D < 0 ||
       (D > 0 && !dense) || B <= 0 || ids_ld < F || (D > 0 && dense_ld < D)) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
@@ -298,9 +319,9 @@ extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off
   const int M = (int)B;
   // ---- forward
   if (ids_kind == CTRHOT_IDS_I32)
-    tr_gather_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag);
+    tr_gather_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag, ctl);
   else
-    tr_gather_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag);
+    tr_gather_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag, ctl);
   tr_fm_fwd_kernel<<<(int)((B + 7) / 8), 256, 0, st>>>(x, n, B, fm_w0, fm_w1, fm_v, k_fm, xv, fm);
   const float* in = x;
   int in_dim = n;
@@ -308,11 +329,11 @@ extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off
     float* h = ws + w.h[l];
     const int N = h_layers[l].out_dim;
     tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
-    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l);
+    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, ctl);
     in = h; in_dim = N;
   }
   tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, dnn, 1, M, 1, in_dim, 1.f, 0.f);
-  tr_loss_kernel<<<1, 256, 0, st>>>(fm, dnn, h_layers[NH].bias, y, B, dz, loss_out);
+  tr_loss_kernel<<<1, 256, 0, st>>>(fm, dnn, h_layers[NH].bias, y, B, dz, loss_out, ctl);
   // ---- backward through the tower: g = dLoss/d(pre-activation) of the current layer, [B, out_dim]
   float* g = ws + w.g0;
   float* gn = ws + w.g1;
@@ -330,7 +351,7 @@ extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off
     const float* h = ws + w.h[l];
     const float* hin = l > 0 ? ws + w.h[l - 1] : x;
     float* W = const_cast<float*>(h_layers[l].weight);
-    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l);
+    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, ctl);
     // gradient w.r.t. this layer's input with the OLD weights: [B,N] x [N,Kd]  (B(k, n) = W[n * N + k])
     float* dst = l > 0 ? gn : dx;
     tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
@@ -348,9 +369,34 @@ extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off
   tr_gemm(st, x, 1, n, t, k_fm, 1, fm_v, k_fm, n, k_fm, M, -lr, 1.f);                      // v -= lr * x^T (dfm xv)
   // ---- embedding rows
   if (ids_kind == CTRHOT_IDS_I32)
-    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr);
+    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr, ctl);
   else
-    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr);
+    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr, ctl);
+  if (ctl) tr_advance_kernel<<<1, 1, 0, st>>>(ctl, (long long)B);
   CTRHOT_LAUNCH_OK("ctrhot_deepfm_train_step_f32");
   return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                            int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                                            int64_t B, float* fm_w0, float* fm_w1, float* fm_v, int k_fm, float reg_w,
+                                            float reg_v, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
+                                            float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                            int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_deepfm_train_step_f32");
+  return tr_step(arena, row_off, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, y, B, fm_w0, fm_w1, fm_v, k_fm, reg_w, reg_v,
+                 h_layers, n_layers, lr, dropout, seed, loss_out, workspace, workspace_bytes, err_flag, nullptr, stream);
+}
+
+extern "C" int ctrhot_deepfm_train_step_ctl_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids,
+                                                int ids_kind, int64_t ids_ld, const float* dense, int64_t dense_ld, int D,
+                                                const float* y, int64_t B, float* fm_w0, float* fm_w1, float* fm_v, int k_fm,
+                                                float reg_w, float reg_v, const ctrhot_dense_desc* h_layers, int n_layers,
+                                                float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                                int64_t workspace_bytes, int* err_flag, void* d_ctl, void* stream) {
+  CTRHOT_RANGE("ctrhot_deepfm_train_step_ctl_f32");
+  if (!d_ctl || (reinterpret_cast<uintptr_t>(d_ctl) & 7u)) return CTRHOT_EARG;
+  return tr_step(arena, row_off, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, y, B, fm_w0, fm_w1, fm_v, k_fm, reg_w, reg_v,
+                 h_layers, n_layers, lr, dropout, seed, loss_out, workspace, workspace_bytes, err_flag,
+                 static_cast<TrCtl*>(d_ctl), stream);
 }

@@ -645,7 +645,11 @@ class PNN(Model):
         fk = E.F * E.k
         P = E.F * (E.F - 1) // 2
         ld = _pad32(self.width)
-        buf = torch.zeros((B, ld), dtype=torch.float32, device=self.device)
+        # every column below `width` is written by the gather / product kernels; only the K padding of the tower's first layer
+        # has to be zero (garbage times a zero weight row could be NaN), not the whole [B, ld] buffer
+        buf = torch.empty((B, ld), dtype=torch.float32, device=self.device)
+        if ld > self.width:
+            buf[:, self.width:].zero_()
         E.gather(ids, out=buf, out_ld=ld)
         z = buf.as_strided((B, E.F, E.k), (ld, E.k, 1))
         col = fk

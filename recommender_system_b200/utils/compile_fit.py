@@ -57,31 +57,80 @@ class _DeepFMTrainer:
         self.step += 1
         return self.loss
 
+    # ---- one captured CUDA graph per (data set, batch size), replayed once per batch
+    def capture(self, X, y, batch_size, lr, seed=0):
+        """``X`` [N, D + F] float32 on the device (the reference's matrix: ids as float columns), ``y`` [N].  Captures ONE graph
+        of ctrhot_deepfm_train_step_ctl_f32 whose batch is ``rows [row0, row0 + batch_size)`` with row0 in a device control
+        block that the step itself advances: `replay()` then costs one graph launch per batch instead of ~25 kernel launches."""
+        m, E = self.m, self.m.embed_layer
+        D = X.shape[1] - E.F
+        n = D + E.F * E.k
+        need = _lib.query("ctrhot_deepfm_train_workspace_bytes", batch_size, n, m.fm.k, self.desc, len(self.desc))
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=m.device)
+        self.ctl = torch.zeros(4, dtype=torch.int64, device=m.device)          # {step, row0, (acc_loss, acc_correct), pad}
+        self._graph_keep = (X, y)
+        ids = X[:, D:]
+        args = (ptr(E.arena), ptr(E.row_off), E.F, E.k, ids.data_ptr(), _lib.IDS_F32, X.stride(0), X.data_ptr(), X.stride(0), D,
+                ptr(y), batch_size, ptr(m.fm.w0), ptr(m.fm.w1), ptr(m.fm.v), m.fm.k, float(m.fm.reg_w), float(m.fm.reg_b),
+                self.desc, len(self.desc), float(lr), self.dropout, int(seed) & (2 ** 64 - 1), ptr(self.loss), ptr(self.ws),
+                self.ws.numel() * 4, ptr(self.flag), ptr(self.ctl))
+        torch.cuda.synchronize(m.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            _lib.call("ctrhot_deepfm_train_step_ctl_f32", *args, stream_ptr())
+        return self.graph
+
+    def epoch_begin(self):
+        self.ctl[1:3].zero_()                                                  # row0 and the two accumulators; step keeps counting
+
+    def replay(self, n_batches):
+        for _ in range(n_batches):
+            self.graph.replay()
+        self.step += n_batches
+
+    def epoch_totals(self):
+        """-> (sum of the per-sample BCE, number of correct predictions) of the replayed batches (synchronises)."""
+        acc = self.ctl[2:3].view(torch.float32).tolist()
+        return float(acc[0]), float(acc[1])
+
     def done(self):
         """The weights moved in place: invalidate every packed copy the forward path keeps."""
-        for layer in (self.m.embed_layer, self.m.fm, self.m.dnn, self.m):
-            layer._bump()
+        self.m._bump()
 
 
-def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True):
+def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True, use_graph=True):
     """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
-    (loss, accuracy) pairs are left in ``model.history``."""
+    (loss, accuracy) pairs are left in ``model.history``.  ``use_graph``: the full batches of an epoch replay one captured CUDA
+    graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
     tr = _DeepFMTrainer(model, dropout)
     dev = model.device
     D = len(model.dense_feature_columns)
-    Xd = as_device_f32(X, dev)
+    Xd = as_device_f32(X, dev).contiguous()
     yd = as_device_f32(np.asarray(y, dtype=np.float32).reshape(-1) if not isinstance(y, torch.Tensor) else y.reshape(-1), dev)
     N = Xd.shape[0]
+    n_full = N // batch_size if use_graph else 0
+    if n_full:
+        tr.capture(Xd, yd, batch_size, sgd, seed=seed * 1000003)
     model.history = []
     for ep in range(epochs):
         tot = torch.zeros(2, dtype=torch.float64, device=dev)
-        for s in range(0, N, batch_size):
+        if n_full:
+            tr.epoch_begin()
+            tr.replay(n_full)
+        for s in range(n_full * batch_size, N, batch_size):
             e = min(N, s + batch_size)
             out = tr.train_on_batch(Xd[s:e, :D], Xd[s:e, D:], yd[s:e], sgd, seed=seed * 1000003 + tr.step)
+            if n_full:
+                tr.ctl[0] += 1                                 # the graph's step counter numbers EVERY batch (dropout seeds)
             tot[0] += out[0].double() * (e - s)
             tot[1] += out[1].double()
-        loss, acc = (tot / N).tolist()
+        loss_sum, correct = tot.tolist()
+        if n_full:
+            a, b = tr.epoch_totals()
+            loss_sum, correct = loss_sum + a, correct + b
+        loss, acc = loss_sum / N, correct / N
         _lib.check(_lib.load().ctrhot_check_flag(ptr(tr.flag), stream_ptr()), "compile_fit")
         model.history.append((loss, acc))
         if verbose:

@@ -146,3 +146,30 @@ def test_compile_fit_learns_and_predicts(lib):
     assert np.mean((p1 > 0.5) == (y > 0.5)) > np.mean((p0 > 0.5) == (y > 0.5)) + 0.05
     want = O.deepfm_loss(dense, ids, *params(m)[:5], params(m)[5], y.astype(np.float64), 0.0, 0.0)[2]
     assert np.max(np.abs(p1 - want)) <= 2e-5
+
+
+@pytest.mark.parametrize("rate", [0.0, 0.2])
+def test_graph_replay_equals_call_by_call(lib, rate):
+    """compile_fit replays one captured CUDA graph per full batch (ctrhot_deepfm_train_step_ctl_f32: the batch's first row and the
+    step number live in a device control block): same weights and the same epoch loss / accuracy as launching every batch by
+    hand, incl. the ragged last batch and the dropout masks."""
+    vocab = [30] * 26
+    rng = np.random.default_rng(1)
+    N = 32 * 20 + 11
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.concatenate([rng.random((N, 13)), ids], axis=1).astype(np.float32)
+    y = (ids[:, 3] < 15).astype(np.float32)
+    ms = []
+    for use_graph in (True, False):
+        m = make_model(vocab, 8, 10, (32, 16), dropout=rate, seed=4)
+        compile_fit(m, X, y, batch_size=32, epochs=3, sgd=0.05, seed=7, verbose=False, use_graph=use_graph)
+        ms.append(m)
+    for (l1, a1), (l2, a2) in zip(ms[0].history, ms[1].history):
+        assert abs(l1 - l2) <= 1e-5 * max(1.0, abs(l2)) and abs(a1 - a2) <= 1.5 / N, (ms[0].history, ms[1].history)
+    pa, pb = params(ms[0]), params(ms[1])
+    for ta, tb in zip(pa[0], pb[0]):
+        np.testing.assert_allclose(ta, tb, rtol=0, atol=2e-6)            # atomic adds: the order of duplicate rows may differ
+    np.testing.assert_allclose(pa[3], pb[3], rtol=0, atol=2e-6)
+    for (ka, ba), (kb, bb) in zip(pa[4], pb[4]):
+        np.testing.assert_allclose(ka, kb, rtol=0, atol=2e-6)
+        np.testing.assert_allclose(ba, bb, rtol=0, atol=2e-6)
