@@ -1232,6 +1232,11 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
 
 int fu_dispatch(const FuParams& p, int nl, size_t smem, bool wide, int cluster, cudaStream_t st) {
   int C = cluster;
+  // Overlapped launches (CTRHOT_LAUNCH_OVERLAP): the next launch's CTAs take the SMs this one leaves idle at its tail, which
+  // only works SM by SM -- a cluster needs 2 or 4 free SMs of one GPC at once, and 4-clusters occupy 132 of the 148 SMs to begin
+  // with.  Measured at cfg 2a (profiles/cluster_overlap_sweep.py): 58.4 us per step with single CTAs, 60.9 with pairs, 67.0 with
+  // clusters of 4 (without overlap the three are within 1 %: 75-77 us).
+  if (C == 0 && p.overlap) C = 1;
   if (C == 0) {
     // larger clusters share each weight chunk among more CTAs (less L2 traffic) but leave SMs idle when a GPC's SM count
     // is not a multiple of the cluster size: take 4 unless 2 saves a whole wave of tiles
