@@ -394,6 +394,7 @@ def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, 
         m = ShardedDeepFM(vocab, k, fm_k=10, hidden_units=(256, 128, 64), device=dev, rank=rank, world=world, exchange=mode)
         m.build()
         m.cluster = int(os.environ.get("CTRHOT_CFG5_CLUSTER", "0"))      # tuning knob for profiles/; 0 = the library's choice
+        m.overlap_launches = (mode == "fused") and not os.environ.get("CTRHOT_CFG5_NO_OVERLAP")   # independent batches
         m.embed.init_hash(1234)
         it = [0]
 
@@ -401,7 +402,7 @@ def sharded_cfg5(dev, rank, world, steps=10, warm=3, rows_per_table=10_000_000, 
             m(ins[it[0] % 2]); it[0] += 1
         ms = timed(step, steps, warm)
         m.embed.check_ids()
-        r = {"value": B / ms * 1e3, "unit": "samples/s", "ms_per_step": ms}
+        r = {"value": B / ms * 1e3, "unit": "samples/s", "ms_per_step": ms, "launch_overlap": bool(m.overlap_launches)}
         if mode != "fused":                                   # the lookup alone (x written to HBM), for the gather roofline
             x = torch.empty((Bl, m.x_ld), dtype=torch.float32, device=dev)
 

@@ -345,14 +345,23 @@ int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M,
  * kernel (two MMA column halves when out_dim > 256): h[m, 0:out_dim] = tf32(act(x_m W + b)), h[m, out_dim:h_ld) = 0.
  * Chains layers too wide for TMEM through HBM (DCN cfg 3's 400-wide tower, DL/model/dcn.py:45); the last hidden layer
  * and the final Dense(h -> 1) then go through ctrhot_tower_rows_tf32 (one hidden layer may be up to 416 wide there). */
+/* CHAINED LAUNCHES (wait_flags / signal_flags / epoch; all NULL / 0 = plain stream order): each launch publishes tile t (rows
+ * [128 t, 128 t + 128)) of its output by storing `epoch` into signal_flags[t] (int32 [ceil(M / 128)], device), and a launch whose
+ * input is another launch's output waits for wait_flags[t] == epoch before its first read of tile t.  With the flags in place
+ * `cluster` may carry CTRHOT_LAUNCH_OVERLAP: launch l + 1 then starts on the SMs launch l frees while it finishes its last
+ * tiles (512 tiles on 148 SMs leave 80 SMs idle for the last quarter of every launch otherwise).  Use a new epoch per
+ * forward pass and keep x / h in buffers that the overlapping neighbour launches do not write (the caller's contract:
+ * layer/core.py alternates two workspaces). */
 int ctrhot_dense_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M, const ctrhot_dense_desc* layer,
-                           float* h, int64_t h_ld, int cluster, void* stream);
+                           float* h, int64_t h_ld, int cluster, const int32_t* wait_flags, int32_t* signal_flags,
+                           int epoch, void* stream);
 /* ctrhot_tower_rows_tf32 with an affine post:
  *   out[m] = (sigmoid of) y_scale * Dense(h->1)(tower(x[m, :])) + add_scale * add_vec[m] + add_const     (add_vec may be NULL) */
 int ctrhot_tower_rows_post_tf32(const float* x, int64_t x_ld, int K, int64_t M,
                                 const ctrhot_dense_desc* h_layers, int n_layers,
                                 const float* add_vec, float y_scale, float add_scale, float add_const,
-                                int apply_sigmoid, int cluster, float* out, void* stream);
+                                int apply_sigmoid, int cluster, float* out, const int32_t* wait_flags, int epoch,
+                                void* stream);
 /* DCN.call (DL/model/dcn.py:24-34) with a tower too wide to chain through TMEM (cfg 3: 400-400-400), FIRST launch:
  * gather -> { the L <= 3 cross layers collapsed to scalars (see mode 2 of ctrhot_ctr_fused_tf32), exact fp32 on the CUDA
  * cores | first Dense layer (out_dim <= 416) on the tensor pipe }.  h[m, :] = tf32(act(x_m W1 + b1)) and
@@ -365,7 +374,7 @@ int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* row_off, int 
                                 const float* dense, int64_t dense_ld, int D, int64_t M,
                                 const ctrhot_dense_desc* layer, const float* cc_w, int n_side,
                                 const float* h_combine, int n_combine, float* h, int64_t h_ld, float* side_out,
-                                int cluster, int* err_flag, void* stream);
+                                int cluster, int* err_flag, int32_t* signal_flags, int epoch, void* stream);
 
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,

@@ -81,6 +81,10 @@ struct FuParams {
   int nr;                                                  // raw-row ring stages in use (<= FU_NR)
   int side_rows;                                           // rows of [s_hi | s_lo] behind W1 in every first-layer chunk (32 or 0)
   float* h_out; int64_t h_ld;                              // single hidden layer: act(x W + b), TF32-rounded, to HBM (no final dot)
+  // chained launches (rows of one launch are the input of the next): tile t of the next launch may be read once
+  // signal_flags[t] == epoch; a launch in rows mode waits on wait_flags[t] before its first copy of tile t.  Lets launch l + 1
+  // start (programmatic dependent launch) while launch l is still finishing its last tiles.
+  const int* wait_flags; int* signal_flags; int epoch;
   int nb;                                                  // W ring stages in use (<= FU_NB)
   const float* add_vec; float out_scale, add_scale, add_const;   // tower mode: out = out_scale * y + add_scale * add_vec[m] + add_const
   const float* cc_w; int cc_n;                             // DCN with few cross layers: side products on the CUDA cores (stager),
@@ -464,6 +468,12 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
       const long long ti0 = clock64();
 #endif
       if (++rs == p.nr) { rs = 0; rph ^= 1u; }
+      if (p.wait_flags != nullptr && ci.kc == 0 && ci.row0 < p.M) {
+        // first chunk of a tile whose rows the previous launch writes: wait until that launch has published the tile
+        const int* fl = p.wait_flags + ci.row0 / FU_BM;
+        int v;
+        do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(fl) : "memory"); } while (v != p.epoch);
+      }
       const uint32_t dst = dst0 + (uint32_t)s * RAW_STRIDE;
       // wide tail of the stage: [128 rows][4 slots] floats; this thread owns a slot when its piece is the first of a field
       bool wide_here = false;
@@ -900,6 +910,15 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
               }
             }
           }
+          if (p.signal_flags != nullptr) {
+            // publish the tile: every epilogue thread's stores, then one release store of the epoch
+            __threadfence();
+            named_bar_sync(7, 256);
+            if (tid == 0) {
+              int* fl = p.signal_flags + (((int64_t)cid + (int64_t)lt * ncl) * C + crank);
+              asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(fl), "r"(p.epoch) : "memory");
+            }
+          }
           tc_fence_before();
           mbar_arrive(last_free);
         } else {
@@ -1101,6 +1120,7 @@ struct FuExtra {
   const float* wide_w = nullptr; const int64_t* wide_off = nullptr; const float* wide_dense = nullptr;   // Wide&Deep wide term
   int64_t wide_dense_ld = 0; int wide_D = 0; const float* wide_dw = nullptr;
   const int32_t* pack_desc = nullptr;                                                        // CTRHOT_IDS_PACKED
+  const int* wait_flags = nullptr; int* signal_flags = nullptr; int epoch = 0;               // chained launches (FuParams)
   struct FuPlan* capture = nullptr;      // plan creation: keep the prepared launch instead of making it
 };
 
@@ -1137,7 +1157,9 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   const int overlap = (cluster & CTRHOT_LAUNCH_OVERLAP) ? 1 : 0;
   cluster &= ~CTRHOT_LAUNCH_OVERLAP;
   if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4) return CTRHOT_EARG;
-  if (overlap && (ex.h_out || rows_mode)) return CTRHOT_EARG;        // chained launches read what the previous one wrote
+  // chained launches read what the previous one wrote: they may overlap only under the per-tile flags
+  if (overlap && ((ex.h_out && !ex.signal_flags) || (rows_mode && !ex.wait_flags))) return CTRHOT_EARG;
+  if ((ex.wait_flags && !rows_mode) || (ex.signal_flags && !ex.h_out)) return CTRHOT_EARG;
   if (k % 4 != 0 || !aligned16(arena) || F > 63) return CTRHOT_ESHAPE;
   // h_out: ONE hidden layer whose activations go to HBM (no final Dense); otherwise hidden layers + the final Dense(h -> 1)
   if (h_out ? (n_layers != 1 || mode == FU_MODE_DEEPFM) : (n_layers < 2 || n_layers > FU_MAXL + 1)) return CTRHOT_ESHAPE;
@@ -1193,6 +1215,7 @@ int fu_entry(const float* const* peers, int G, int rank, const int64_t* row_off,
   p.M = M; p.n_tiles = (int)((M + FU_BM - 1) / FU_BM);
   p.w_out = h_out ? nullptr : o.weight; p.b_out = h_out ? nullptr : o.bias; p.sq_w = sq_w;
   p.h_out = h_out; p.h_ld = h_ld;
+  p.wait_flags = ex.wait_flags; p.signal_flags = ex.signal_flags; p.epoch = ex.epoch;
   p.mode = mode; p.n_side = n_side; p.apply_sigmoid = apply_sigmoid; p.overlap = overlap;
   for (int i = 0; i < n_combine; ++i) p.cb[i] = h_combine[i];
   p.out = out; p.err_flag = err_flag; p.b_stage_bytes = bmax;
@@ -1389,12 +1412,14 @@ extern "C" int ctrhot_tower_rows_tf32(const float* x, int64_t x_ld, int K, int64
 // too wide to be chained through TMEM (DCN cfg 3: 429 -> 400 -> 400 -> 400 -> 1 runs as store, store, then
 // ctrhot_tower_rows_tf32 with the last hidden layer + the final Dense).  h[m, 0:N] = tf32(act(x_m W + b)), h[m, N:h_ld) = 0.
 extern "C" int ctrhot_dense_rows_tf32(const float* x, int64_t x_ld, int K, int64_t M, const ctrhot_dense_desc* layer,
-                                      float* h, int64_t h_ld, int cluster, void* stream) {
+                                      float* h, int64_t h_ld, int cluster, const int32_t* wait_flags, int32_t* signal_flags,
+                                      int epoch, void* stream) {
   CTRHOT_RANGE("ctrhot_dense_rows_tf32");
   if (!x || !layer || !h || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
   const int r = K % 4, k = K - r;
   FuExtra ex;
   ex.h_out = h; ex.h_ld = h_ld;
+  ex.wait_flags = wait_flags; ex.signal_flags = signal_flags; ex.epoch = epoch;
   return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, layer, 1,
                   nullptr, FU_MODE_TOWER, 0, nullptr, 0, 0, cluster, nullptr, nullptr, stream, ex);
 }
@@ -1446,11 +1471,12 @@ extern "C" int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* ro
                                            const float* dense, int64_t dense_ld, int D, int64_t M,
                                            const ctrhot_dense_desc* layer, const float* cc_w, int n_side,
                                            const float* h_combine, int n_combine, float* h, int64_t h_ld, float* side_out,
-                                           int cluster, int* err_flag, void* stream) {
+                                           int cluster, int* err_flag, int32_t* signal_flags, int epoch, void* stream) {
   CTRHOT_RANGE("ctrhot_dcn_first_layer_tf32");
   if (!arena || !cc_w || !side_out || !h) return CTRHOT_EARG;
   FuExtra ex;
   ex.h_out = h; ex.h_ld = h_ld; ex.cc_w = cc_w; ex.side_out = side_out;
+  ex.signal_flags = signal_flags; ex.epoch = epoch;
   return fu_entry(&arena, 1, 0, row_off, 0, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, M, layer, 1, nullptr,
                   FU_MODE_DCN, n_side, h_combine, n_combine, 0, cluster, nullptr, err_flag, stream, ex);
 }
@@ -1459,12 +1485,14 @@ extern "C" int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* ro
 extern "C" int ctrhot_tower_rows_post_tf32(const float* x, int64_t x_ld, int K, int64_t M,
                                            const ctrhot_dense_desc* h_layers, int n_layers,
                                            const float* add_vec, float y_scale, float add_scale, float add_const,
-                                           int apply_sigmoid, int cluster, float* out, void* stream) {
+                                           int apply_sigmoid, int cluster, float* out, const int32_t* wait_flags, int epoch,
+                                           void* stream) {
   CTRHOT_RANGE("ctrhot_tower_rows_post_tf32");
   if (!x || K < 4 || x_ld < K || x_ld % 4 != 0 || x_ld > 0x7FFFFFFF || !aligned16(x)) return CTRHOT_EARG;
   const int r = K % 4, k = K - r;
   FuExtra ex;
   ex.add_vec = add_vec; ex.out_scale = y_scale; ex.add_scale = add_scale; ex.add_const = add_const;
+  ex.wait_flags = wait_flags; ex.epoch = epoch;
   return fu_entry(&x, 1, 0, nullptr, (int)x_ld, 1, k, nullptr, CTRHOT_IDS_I32, 0, r ? x + k : nullptr, x_ld, r, M, h_layers,
                   n_layers, nullptr, FU_MODE_TOWER, 0, nullptr, 0, apply_sigmoid, cluster, out, nullptr, stream, ex);
 }

@@ -127,6 +127,8 @@ class DenseStack:
         self._packed = {}
         self._plans = {}
         self._ws = None
+        self._flags, self._epoch = None, 0
+        self.chain_launches = True      # wide towers: launch l + 1 may start under the tail of launch l (per-tile ready flags)
         self._key = None
         self.allow_fused = True
 
@@ -263,7 +265,7 @@ class DenseStack:
                 h_ld = (n1 + 31) // 32 * 32
                 h = self._ws[(l & 1) * M * mx:(l & 1) * M * mx + M * h_ld].view(M, h_ld)
                 _lib.call("ctrhot_dense_rows_tf32", ptr(cur), cur_ld, K, M, ctypes.pointer(arr[l]), ptr(h), h_ld, 0,
-                          stream_ptr())
+                          None, None, 0, stream_ptr())
                 cur, cur_ld = h, h_ld
             else:
                 _lib.call("ctrhot_tower_rows_tf32", ptr(cur), cur_ld, K, M, ctypes.pointer(arr[l]), 2, int(bool(sigmoid)), 0,
@@ -286,29 +288,46 @@ class DenseStack:
             _lib.call("ctrhot_fused_pack", ptr(first_kernel_ref.contiguous()), None, n_in, n1, D, ptr(buf), stream_ptr())
             self._packed[key] = buf
         mx = max((arr[i].out_dim + 31) // 32 * 32 for i in range(n - 1))
-        if self._ws is None or self._ws.numel() < 2 * B * mx + B or self._ws.device != dense.device:
-            self._ws = torch.empty(2 * B * mx + B, dtype=torch.float32, device=dense.device)
-        side = self._ws[2 * B * mx:2 * B * mx + B]
+        # Chained launches: with per-tile "ready" flags launch l + 1 starts on the SMs launch l frees while it finishes its last
+        # tiles (include/ctrhot.h).  Needs every launch to fill the GPU (then "all CTAs of a launch have started" implies that
+        # every earlier launch is complete, so only neighbours overlap) and buffers no neighbour writes: two workspaces used in
+        # turn, because the first launch of a call overlaps the last launch of the previous call.
+        n_tiles = (B + 127) // 128
+        chain = self.chain_launches and n_tiles >= 148 and n >= 3
+        per = (2 * B * mx + B + 31) // 32 * 32              # (the second workspace starts 16-byte aligned for any B)
+        if self._ws is None or self._ws.numel() < 2 * per or self._ws.device != dense.device:
+            self._ws = torch.empty(2 * per, dtype=torch.float32, device=dense.device)
+            self._flags, self._epoch = None, 0
+        if chain and (self._flags is None or self._flags.shape[2] < n_tiles):
+            self._flags = torch.zeros((2, n, n_tiles), dtype=torch.int32, device=dense.device)
+            self._epoch = 0
+        self._epoch += 1
+        par = self._epoch & 1
+        ws = self._ws[par * per:(par + 1) * per]
+        fl = (lambda l: ptr(self._flags[par, l])) if chain else (lambda l: None)
+        ep = self._epoch if chain else 0
+        cl = int(cluster) | (_lib.LAUNCH_OVERLAP if chain else 0)
+        side = ws[2 * B * mx:2 * B * mx + B]
         cb = (ctypes.c_float * len(combine))(*[float(c) for c in combine])
         h_ld = (n1 + 31) // 32 * 32
-        h = self._ws[:B * h_ld].view(B, h_ld)
+        h = ws[:B * h_ld].view(B, h_ld)
         arr[0].packed = ptr(self._packed[key])
         _lib.call("ctrhot_dcn_first_layer_tf32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(dense),
                   dense.stride(0), D, B, ctypes.pointer(arr[0]), ptr(cc_w), int(n_side), cb, len(combine), ptr(h), h_ld,
-                  ptr(side), int(cluster), ptr(err_flag), stream_ptr())
+                  ptr(side), cl, ptr(err_flag), fl(0), ep, stream_ptr())
         cur, cur_ld = h, h_ld
         for l in range(1, n - 1):
             K, nl = arr[l].in_dim, arr[l].out_dim
             arr[l].packed = ptr(self._rows_pack(l, K, nl))
             if l < n - 2:
                 h_ld = (nl + 31) // 32 * 32
-                h = self._ws[(l & 1) * B * mx:(l & 1) * B * mx + B * h_ld].view(B, h_ld)
-                _lib.call("ctrhot_dense_rows_tf32", ptr(cur), cur_ld, K, B, ctypes.pointer(arr[l]), ptr(h), h_ld, 0,
-                          stream_ptr())
+                h = ws[(l & 1) * B * mx:(l & 1) * B * mx + B * h_ld].view(B, h_ld)
+                _lib.call("ctrhot_dense_rows_tf32", ptr(cur), cur_ld, K, B, ctypes.pointer(arr[l]), ptr(h), h_ld, cl,
+                          fl(l - 1), fl(l), ep, stream_ptr())
                 cur, cur_ld = h, h_ld
             else:
                 _lib.call("ctrhot_tower_rows_post_tf32", ptr(cur), cur_ld, K, B, ctypes.pointer(arr[l]), 2, ptr(side),
-                          float(wy), 1.0, float(bias), 1, 0, ptr(out), stream_ptr())
+                          float(wy), 1.0, float(bias), 1, cl, ptr(out), fl(l - 1), ep, stream_ptr())
         return out
 
     def run_ctr_tower(self, E, ids, kind, ids_ld, dense, B, first_kernel_ref, add_vec=None, scale=1.0, sigmoid=False,

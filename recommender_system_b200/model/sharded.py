@@ -261,6 +261,7 @@ class ShardedDeepFM(Model):
                              "NVLink) or 'fused' (whole-model kernel gathering from the peers)")
         self.exchange = exchange
         self.cluster = 0                                        # CTAs sharing a weight chunk in the fused kernel (0 = auto)
+        self.overlap_launches = False                           # exchange='fused': consecutive calls on independent batches may overlap (CTRHOT_LAUNCH_OVERLAP)
         if rank is None:
             rank = dist.get_rank(group) if dist.is_initialized() else 0
         if world is None:
@@ -330,5 +331,6 @@ class ShardedDeepFM(Model):
         out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
         stack.run_ctr_fused(E, ids, _lib.IDS_I32, ids.stride(0), dense.contiguous(), B, self.dnn.hidden[0][0], side, sq_w,
                             mode=1, n_side=self.fm.k, combine=cb, sigmoid=True, err_flag=E.err, out=out,
-                            cluster=self.cluster, side_key=("fm", self.fm._version))
+                            cluster=self.cluster | (_lib.LAUNCH_OVERLAP if self.overlap_launches else 0),
+                            side_key=("fm", self.fm._version))
         return out

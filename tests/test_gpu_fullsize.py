@@ -94,6 +94,31 @@ def test_dcn_cfg3_full_batch_on_the_kaggle_arena(lib):
     np.testing.assert_array_equal(got[perm], got_p)
 
 
+def test_dcn_cfg3_chained_launches_equal_stream_order(lib):
+    """The three launches of DCN cfg 3 overlap at their edges under per-tile ready flags (DenseStack.chain_launches): twelve
+    back-to-back forwards over alternating batches -- so that every launch runs next to its neighbours, also across calls --
+    must give bit for bit what plain stream order gives, and a ragged batch (partial last tile) too."""
+    set_seed(3)
+    k, vocab = 16, [5000] * 26
+    m = DCN(synth.criteo_feature_columns(vocab, k), [400, 400, 400], 1, "relu", 3, embed_dim=k, precision="tf32", check_ids=False)
+    m.build(None)
+    dev = m.device
+    for B in (65536, 148 * 128 + 77):
+        batches = []
+        for i in range(3):
+            d, ids = synth.criteo_batch(B, vocab, seed=40 + i)
+            batches.append((torch.from_numpy(d).to(dev), torch.from_numpy(ids).to(dev)))
+        stack = m.dense_layer.stack
+        stack.chain_launches = False
+        want = [m(b).clone() for b in batches]
+        torch.cuda.synchronize()
+        stack.chain_launches = True
+        outs = [m(batches[i % 3]) for i in range(12)]
+        torch.cuda.synchronize()
+        for i, o in enumerate(outs):
+            assert torch.equal(o, want[i % 3]), (B, i, float((o - want[i % 3]).abs().max()))
+
+
 def test_din_cfg4_whole_model(lib):
     set_seed(4)
     B, T, K, v_item, v_user = 16384, 100, 64, 10_000_000, 192404
