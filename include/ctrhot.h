@@ -448,6 +448,18 @@ int ctrhot_seq_attn_pool_f32(const float* scores, int64_t score_ld, const float*
                              const uint8_t* mask, int64_t mask_ld, const int32_t* lengths, int64_t B, int T, int E,
                              int weight_normalization, int return_score, float* out, int64_t out_ld, void* stream);
 
+/* ---- 8(f) rank 4: AUGRU (DIEN), AUGRUCell.call DL/layer/activation.py:113-142 unrolled over time as rnn_augru does without a
+ * mask (:237-244; AUGRU.call, DL/layer/sequence.py:293-395) --------------------------------------------------------------------
+ *   z = ra(x_t Wz + h Uz) * att[b, t];  r = ra(x_t Wr + h Ur);  hh = act(x_t Wh + (r * h) Uh);  h <- z h + (1 - z) hh   (no biases)
+ * x [B, T, E] (sample stride x_ld_b), att [B, T]; kernel [E, 3H], recurrent_kernel [H, 3H] hold the z | r | h blocks; h0 [B, H] or
+ * NULL (zeros, keras' initial state); seq_out [B, T, H] and / or last_out [B, H].  recurrent_hard_sigmoid: 0 = sigmoid (what the
+ * reference's cell runs with under TF 2: keras' GRUCell.__init__ overwrites the 'hard_sigmoid' AUGRUCell sets, activation.py:97-100),
+ * 1 = clip(0.2 v + 0.5, 0, 1); linear_activation: 0 = tanh.  fp32 CUDA cores; 3H <= 1024 and the weights must fit shared memory. */
+int ctrhot_augru_f32(const float* x, int64_t x_ld_b, const float* att, int64_t att_ld, const float* kernel,
+                     const float* recurrent_kernel, const float* h0, int64_t B, int T, int E, int H,
+                     int recurrent_hard_sigmoid, int linear_activation, float* seq_out, float* last_out,
+                     void* stream);
+
 /* ---- one SGD step of DeepFM, the step on the right of the path ------------------------------
  * What compile_fit (DL/utils/compile_fit.py:9-15: SGD(lr), loss 'binary_crossentropy', model.fit) does to DeepFM
  * (DL/model/deepFM.py:15-31) for one batch: forward, mean clipped BCE + the l2 regularisers of FMLayer.build

@@ -523,6 +523,37 @@ def attention_sequence_pooling(query, keys, key_mask, kernels, biases, out_kerne
     return out if return_score else out @ keys
 
 
+def hard_sigmoid(x):
+    """keras.backend.hard_sigmoid: clip(0.2 x + 0.5, 0, 1)."""
+    return np.clip(0.2 * x + 0.5, 0.0, 1.0)
+
+
+def augru_cell(x, h, att, kernel, recurrent_kernel, recurrent_activation="sigmoid", activation="tanh"):
+    """AUGRUCell.call, DL/layer/activation.py:113-142 (no biases): z = ra(x Wz + h Uz) * att; r = ra(x Wr + h Ur);
+    hh = act(x Wh + (r * h) Uh); h' = z h + (1 - z) hh.  kernel [E, 3H] and recurrent_kernel [H, 3H] hold the z | r | h blocks.
+    Under TF 2 the cell's activations are tanh / SIGMOID whatever its constructor is given: keras' GRUCell.__init__ overwrites
+    the attributes AUGRUCell sets before calling it (activation.py:97-100)."""
+    H = recurrent_kernel.shape[0]
+    ra = sigmoid if recurrent_activation == "sigmoid" else hard_sigmoid
+    act = np.tanh if activation == "tanh" else (lambda v: v)
+    z = ra(x @ kernel[:, :H] + h @ recurrent_kernel[:, :H]) * att
+    r = ra(x @ kernel[:, H:2 * H] + h @ recurrent_kernel[:, H:2 * H])
+    hh = act(x @ kernel[:, 2 * H:] + (r * h) @ recurrent_kernel[:, 2 * H:])
+    return z * h + (1 - z) * hh
+
+
+def augru(x, att, kernel, recurrent_kernel, h0=None, recurrent_activation="sigmoid", activation="tanh"):
+    """rnn_augru without a mask, DL/layer/activation.py:237-244 (what AUGRU.call, DL/layer/sequence.py:293-395, unrolls):
+    h_t = cell(x[:, t], h_{t-1}, att[:, t, :]); -> (last output [B,H], outputs [B,T,H])."""
+    B, T, _ = x.shape
+    h = np.zeros((B, recurrent_kernel.shape[0]), x.dtype) if h0 is None else h0
+    outs = []
+    for t in range(T):
+        h = augru_cell(x[:, t], h, att[:, t, :], kernel, recurrent_kernel, recurrent_activation, activation)
+        outs.append(h)
+    return h, np.stack(outs, axis=1)
+
+
 # --------------------------------------------------------------------------- SURVEY 8(f) rank 3: one SGD step of DeepFM
 # PARITY UNPINNED for this function: the reference trains through TensorFlow's autodiff and optimizer
 # (DL/utils/compile_fit.py:9-15), which cannot run in this container, and it ships no training fixtures.  The forward

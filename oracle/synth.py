@@ -501,6 +501,16 @@ def _run_seqpool(wn, ret, act="sigmoid"):
     return run
 
 
+def make_augru(rng, E=6, H=8):
+    lim = np.sqrt(6.0 / (E + 3 * H))
+    return {"x": f32(rng.normal(0, 0.7, (B, T, E))), "att": f32(rng.random((B, T, 1))),
+            "kernel": f32(rng.uniform(-lim, lim, (E, 3 * H))), "rkernel": f32(rng.uniform(-0.6, 0.6, (H, 3 * H)))}
+
+
+def run_augru(a):
+    return O.augru(a["x"], a["att"], a["kernel"], a["rkernel"])[1]
+
+
 CASES = {
     "embed": (make_embed, run_embed),
     "wide": (make_wide, run_wide),
@@ -533,6 +543,7 @@ CASES = {
     "seqpool_softmax": (make_seqpool, _run_seqpool(True, False)),
     "seqpool_plain": (make_seqpool, _run_seqpool(False, False)),
     "seqpool_score": (make_seqpool, _run_seqpool(True, True)),
+    "augru": (make_augru, run_augru),
 }
 
 

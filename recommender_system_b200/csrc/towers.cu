@@ -165,3 +165,112 @@ extern "C" int ctrhot_seq_attn_pool_f32(const float* scores, int64_t score_ld, c
   CTRHOT_LAUNCH_OK("ctrhot_seq_attn_pool_f32");
   return CTRHOT_OK;
 }
+
+// ---- AUGRU: AUGRUCell.call (DL/layer/activation.py:113-142) unrolled over time as rnn_augru does without a mask (:237-244) ----
+//   z = ra(x Wz + h Uz) * att_t;  r = ra(x Wr + h Ur);  hh = act(x Wh + (r * h) Uh);  h' = z h + (1 - z) hh      (no biases)
+// Sequential in T, parallel over samples: a CTA of 3H threads (thread = gate column) carries AS samples through all T steps,
+// weights [E + H, 3H] resident in shared memory, 8 FMAs per weight read.
+namespace ctrhot {
+constexpr int AS = 8;
+__device__ __forceinline__ float augru_ra(float v, int hard) {
+  return hard ? fminf(fmaxf(0.2f * v + 0.5f, 0.f), 1.f) : 1.0f / (1.0f + __expf(-v));
+}
+__global__ void augru_kernel(const float* __restrict__ x, int64_t x_ld_b, const float* __restrict__ att, int64_t att_ld,
+                             const float* __restrict__ Wk, const float* __restrict__ Uk, const float* __restrict__ h0,
+                             int64_t B, int T, int E, int H, int ra_hard, int act_linear, float* __restrict__ seq_out,
+                             float* __restrict__ last_out) {
+  extern __shared__ float sm[];
+  const int G = 3 * H, j = threadIdx.x;
+  float* sW = sm;                       // [E][3H]
+  float* sU = sW + (size_t)E * G;       // [H][3H]
+  float* xs = sm + (((size_t)(E + H) * G + 3) & ~(size_t)3);   // [E][AS], 16-byte aligned for the float4 reads
+  float* hs = xs + E * AS;              // [H][AS]
+  float* rh = hs + H * AS;              // [H][AS]
+  float* zs = rh + H * AS;              // [H][AS]
+  for (int i = j; i < E * G; i += G) sW[i] = __ldg(Wk + i);
+  for (int i = j; i < H * G; i += G) sU[i] = __ldg(Uk + i);
+  for (int64_t b0 = (int64_t)blockIdx.x * AS; b0 < B; b0 += (int64_t)gridDim.x * AS) {
+    const int ns = (int)((B - b0 < AS) ? (B - b0) : AS);
+    __syncthreads();
+    for (int i = j; i < H * AS; i += G) {
+      const int h = i / AS, s = i - h * AS;
+      hs[i] = (h0 && s < ns) ? h0[(b0 + s) * H + h] : 0.f;
+    }
+    for (int t = 0; t < T; ++t) {
+      for (int i = j; i < E * AS; i += G) {
+        const int s = i / E, e = i - s * E;                        // coalesced over e
+        xs[e * AS + s] = (s < ns) ? x[(b0 + s) * x_ld_b + (int64_t)t * E + e] : 0.f;
+      }
+      __syncthreads();
+      float acc[AS];
+#pragma unroll
+      for (int s = 0; s < AS; ++s) acc[s] = 0.f;
+      for (int e = 0; e < E; ++e) {
+        const float w = sW[e * G + j];
+        const float4 a = *reinterpret_cast<const float4*>(xs + e * AS), b = *reinterpret_cast<const float4*>(xs + e * AS + 4);
+        acc[0] = fmaf(a.x, w, acc[0]); acc[1] = fmaf(a.y, w, acc[1]); acc[2] = fmaf(a.z, w, acc[2]); acc[3] = fmaf(a.w, w, acc[3]);
+        acc[4] = fmaf(b.x, w, acc[4]); acc[5] = fmaf(b.y, w, acc[5]); acc[6] = fmaf(b.z, w, acc[6]); acc[7] = fmaf(b.w, w, acc[7]);
+      }
+      if (j < 2 * H) {
+        for (int h = 0; h < H; ++h) {
+          const float w = sU[h * G + j];
+          const float4 a = *reinterpret_cast<const float4*>(hs + h * AS), b = *reinterpret_cast<const float4*>(hs + h * AS + 4);
+          acc[0] = fmaf(a.x, w, acc[0]); acc[1] = fmaf(a.y, w, acc[1]); acc[2] = fmaf(a.z, w, acc[2]); acc[3] = fmaf(a.w, w, acc[3]);
+          acc[4] = fmaf(b.x, w, acc[4]); acc[5] = fmaf(b.y, w, acc[5]); acc[6] = fmaf(b.z, w, acc[6]); acc[7] = fmaf(b.w, w, acc[7]);
+        }
+        if (j < H) {
+#pragma unroll
+          for (int s = 0; s < AS; ++s)
+            zs[j * AS + s] = augru_ra(acc[s], ra_hard) * (s < ns ? att[(b0 + s) * att_ld + t] : 0.f);
+        } else {
+#pragma unroll
+          for (int s = 0; s < AS; ++s) rh[(j - H) * AS + s] = augru_ra(acc[s], ra_hard) * hs[(j - H) * AS + s];
+        }
+      }
+      __syncthreads();
+      if (j >= 2 * H) {
+        const int u = j - 2 * H;
+        for (int h = 0; h < H; ++h) {
+          const float w = sU[h * G + j];
+          const float4 a = *reinterpret_cast<const float4*>(rh + h * AS), b = *reinterpret_cast<const float4*>(rh + h * AS + 4);
+          acc[0] = fmaf(a.x, w, acc[0]); acc[1] = fmaf(a.y, w, acc[1]); acc[2] = fmaf(a.z, w, acc[2]); acc[3] = fmaf(a.w, w, acc[3]);
+          acc[4] = fmaf(b.x, w, acc[4]); acc[5] = fmaf(b.y, w, acc[5]); acc[6] = fmaf(b.z, w, acc[6]); acc[7] = fmaf(b.w, w, acc[7]);
+        }
+#pragma unroll
+        for (int s = 0; s < AS; ++s) {
+          const float hh = act_linear ? acc[s] : tanhf(acc[s]);
+          const float z = zs[u * AS + s];
+          const float hn = z * hs[u * AS + s] + (1.f - z) * hh;
+          hs[u * AS + s] = hn;
+          if (s < ns) {
+            if (seq_out) seq_out[((b0 + s) * T + t) * H + u] = hn;
+            if (last_out && t == T - 1) last_out[(b0 + s) * H + u] = hn;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+}  // namespace ctrhot
+
+extern "C" int ctrhot_augru_f32(const float* x, int64_t x_ld_b, const float* att, int64_t att_ld, const float* kernel,
+                                const float* recurrent_kernel, const float* h0, int64_t B, int T, int E, int H,
+                                int recurrent_hard_sigmoid, int linear_activation, float* seq_out, float* last_out,
+                                void* stream) {
+  CTRHOT_RANGE("ctrhot_augru_f32");
+  if (!x || !att || !kernel || !recurrent_kernel || (!seq_out && !last_out) || B < 0 || T < 1 || E < 1 || H < 1 ||
+      x_ld_b < (int64_t)T * E || att_ld < T) return CTRHOT_EARG;
+  if (3 * H > 1024) return CTRHOT_ESHAPE;
+  const size_t smem = ((((size_t)(E + H) * 3 * H + 3) & ~(size_t)3) + (size_t)(E + 3 * H) * ctrhot::AS) * sizeof(float);
+  if (smem > 227u * 1024u) return CTRHOT_ESHAPE;
+  if (B == 0) return CTRHOT_OK;
+  CTRHOT_CUDA_OK(cudaFuncSetAttribute(ctrhot::augru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "augru attr");
+  int64_t groups = (B + ctrhot::AS - 1) / ctrhot::AS;
+  int64_t grid = groups < (int64_t)ctrhot::kNumSMs * 2 ? groups : (int64_t)ctrhot::kNumSMs * 2;
+  ctrhot::augru_kernel<<<(int)grid, 3 * H, smem, static_cast<cudaStream_t>(stream)>>>(
+      x, x_ld_b, att, att_ld, kernel, recurrent_kernel, h0, B, T, E, H, recurrent_hard_sigmoid, linear_activation, seq_out,
+      last_out);
+  CTRHOT_LAUNCH_OK("ctrhot_augru_f32");
+  return CTRHOT_OK;
+}

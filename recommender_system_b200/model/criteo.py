@@ -429,7 +429,8 @@ class DCN(_EmbedTowerModel):
                 ids, kind, ids_ld = ids_arg(ids)
                 stack.run_ctr_fused(E, ids, kind, ids_ld, dense, B, self.dense_layer.hidden[0][0], side, None, mode=2,
                                     n_side=self.cross_layer.layer_num, combine=cb, sigmoid=True,
-                                    err_flag=self.err_flag(), out=out, cluster=self.cluster,
+                                    err_flag=self.err_flag(), out=out,
+                                    cluster=self.cluster | (_lib.LAUNCH_OVERLAP if getattr(self, "overlap_launches", False) else 0),
                                     side_key=("dcn", self._version, self.cross_layer._version))
                 if self.check:
                     self.check_ids()

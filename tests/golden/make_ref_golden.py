@@ -464,6 +464,25 @@ def _r_seqpool(wn, ret):
     return run
 
 
+def r_augru(a):
+    """AUGRUCell.call (DL/layer/activation.py:113-142) stepped by the reference's own rnn_augru (:145-263), both unmodified, with
+    the step closure of AUGRU.call (DL/layer/sequence.py:354-360).  The AUGRU layer object itself needs keras' RNN base class
+    (state handling, ragged inputs) and is not constructed; its call() does nothing else on this path."""
+    import layer.activation as RA
+    cell = RA.AUGRUCell(a["rkernel"].shape[0], recurrent_activation="hard_sigmoid")      # (the base class resets it: see tf_shim)
+    cell.build((None, a["kernel"].shape[0]))
+    put(cell, "kernel", a["kernel"]); put(cell, "recurrent_kernel", a["rkernel"])
+
+    def step(inputs, states, att_score):
+        output, new_states = cell.call(inputs, states, att_score=att_score)
+        return output, (new_states if isinstance(new_states, (list, tuple)) else [new_states])
+    x, att = SO._t(a["x"]), SO._t(a["att"])
+    h0 = [SO._t(np.zeros((x.shape[0], a["rkernel"].shape[0]), x.dtype))]
+    last, outs, _ = RA.rnn_augru(step, x, h0, att_score=att)
+    assert np.array_equal(np.asarray(last), np.asarray(outs)[:, -1])
+    return np.asarray(outs)
+
+
 RUNNERS = {
     "embed": r_embed, "wide": r_wide, "fm": r_fm, "dnn": r_dnn, "cross": r_cross, "ffm": r_ffm, "inner": r_inner,
     "outer": r_outer, "dice": r_dice, "att": r_att, "att_dice": r_att_dice, "deepfm": r_deepfm,
@@ -473,6 +492,7 @@ RUNNERS = {
     "deepctr_dnn_relu": _r_deepctr_dnn("relu", False, None), "deepctr_dnn_bn_sigmoid": _r_deepctr_dnn("sigmoid", True, "tanh"),
     "lau_sigmoid": _r_lau("sigmoid"), "lau_dice": _r_lau("dice"),
     "seqpool_softmax": _r_seqpool(True, False), "seqpool_plain": _r_seqpool(False, False), "seqpool_score": _r_seqpool(True, True),
+    "augru": r_augru,
 }
 MODEL_WRAPPERS = {"fm": r_fm_model, "ffm": r_ffm_model}
 

@@ -53,7 +53,7 @@ def _mod(name, **attrs):
 
 
 _LAYER_NAMES = ("Layer", "Dense", "Dropout", "Embedding", "BatchNormalization", "PReLU", "Flatten", "Concatenate",
-                "Add", "Activation", "Lambda")
+                "Add", "Activation", "Lambda", "GRUCell")
 
 
 def install():
@@ -73,10 +73,19 @@ def install():
          glorot_normal_initializer=O.glorot_normal, glorot_uniform_initializer=O.glorot_uniform)
     _mod("tensorflow.python.ops.init_ops_v2", Zeros=O.Zeros, glorot_normal=O.glorot_normal,
          glorot_uniform=O.glorot_uniform)
-    for n in ("lookup_ops", "array_ops", "math_ops"):
+    for n in ("lookup_ops", "math_ops"):
         _mod("tensorflow.python.ops." + n)
+    import numpy as _np
+    _mod("tensorflow.python.ops.array_ops", transpose=O.transpose, stack=O.stack, expand_dims=O.expand_dims, tile=O.tile,
+         unstack=lambda x, axis=0: [O._t(v) for v in _np.moveaxis(_np.asarray(x), axis, 0)],
+         shape=lambda x: _np.asarray(_np.shape(x)), where_v2=O.where)
     _mod("tensorflow.python.util")
-    _mod("tensorflow.python.util.nest")
+    # the three nest functions rnn_augru (DL/layer/activation.py:145-263) uses, for flat (non-nested) structures and lists
+    _seq = (list, tuple)
+    _mod("tensorflow.python.util.nest", is_nested=lambda x: isinstance(x, _seq),
+         flatten=lambda x: [v for y in x for v in ([y] if not isinstance(y, _seq) else y)] if isinstance(x, _seq) else [x],
+         map_structure=lambda f, x: type(x)(f(v) for v in x) if isinstance(x, _seq) else f(x),
+         pack_sequence_as=lambda ref, flat: type(ref)(flat) if isinstance(ref, _seq) else flat[0])
     _mod("tensorflow.python.framework")
     _mod("tensorflow.python.framework.dtypes")
     _mod("tensorflow.python.framework.ops")
@@ -86,7 +95,7 @@ def install():
         _mod(root + ".models", Model=L.Model)
         _mod(root + ".regularizers", l2=L.l2)
         _mod(root + ".backend", repeat_elements=O.repeat_elements, zeros_like=O.zeros_like,
-             expand_dims=O.expand_dims)
+             expand_dims=O.expand_dims, dot=O.matmul)
         _mod(root + ".activations", get=L.get_activation)
         _mod(root + ".optimizers")
         _mod(root + ".losses")

@@ -33,7 +33,8 @@ def get_activation(a):
     if callable(a):
         return a
     return {"relu": O.relu, "sigmoid": O.sigmoid, "tanh": lambda x: O._t(np.tanh(np.asarray(x))),
-            "softmax": O.softmax}[a]
+            "softmax": O.softmax,
+            "hard_sigmoid": lambda x: O._t(np.clip(0.2 * np.asarray(x) + 0.5, 0.0, 1.0))}[a]      # keras.backend.hard_sigmoid
 
 
 class Layer:
@@ -202,3 +203,18 @@ class Lambda(Layer):
 
     def call(self, inputs, *args, **kwargs):
         return self.function(inputs)
+
+
+class GRUCell(Layer):
+    """Only the constructor behaviour the reference's AUGRUCell (DL/layer/activation.py:91-100) runs into: under TF 2,
+    ``tensorflow.python.keras.layers.GRUCell`` is recurrent_v2.GRUCell, whose __init__(units, activation='tanh',
+    recurrent_activation='sigmoid', ...) assigns ``self.activation`` / ``self.recurrent_activation`` from ITS OWN arguments.
+    AUGRUCell sets both attributes first and then calls ``super().__init__(units, **kwargs)`` without forwarding them, so the
+    base class overwrites them with tanh / sigmoid whatever AUGRUCell was given."""
+
+    def __init__(self, units, activation="tanh", recurrent_activation="sigmoid", use_bias=True, **kwargs):
+        super().__init__(**kwargs)
+        self.units = units
+        self.activation = get_activation(activation)
+        self.recurrent_activation = get_activation(recurrent_activation)
+        self.use_bias = use_bias

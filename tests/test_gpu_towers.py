@@ -164,6 +164,36 @@ def test_attention_sequence_pooling_at_din_shape(lib):
     np.testing.assert_allclose(got[0, 0], keys[0].astype(np.float64).mean(0), rtol=1e-5, atol=1e-6)     # empty: uniform over T
 
 
+def test_augru_against_the_reference_cell(golden, lib):
+    """AUGRU (DL/layer/sequence.py:293-395) against the reference's own AUGRUCell.call stepped by its rnn_augru (both unmodified
+    under the shim): the sequence of hidden states and the last one."""
+    from recommender_system_b200.layer.sequence import AUGRU
+    a, want = S.load_case(golden, "augru")
+    for seq in (True, False):
+        L = AUGRU(a["rkernel"].shape[0], return_sequence=seq)
+        L.build(a["x"].shape)
+        L.set_weights({"kernel": a["kernel"], "recurrent_kernel": a["rkernel"]})
+        got = npy(L(a["x"], att_score=a["att"]))
+        assert err(got, want if seq else want[:, -1]) <= 2e-6, err(got, want if seq else want[:, -1])
+
+
+@pytest.mark.parametrize("B,T,E,H,hard", [(1, 1, 4, 4, 0), (77, 9, 5, 7, 1), (3000, 100, 64, 64, 0), (1025, 50, 18, 36, 1)])
+def test_augru_shapes(lib, B, T, E, H, hard):
+    """Ragged batches, odd widths, DIEN's shape (T = 100, 64 -> 64), both recurrent activations, a non-zero initial state."""
+    from recommender_system_b200.layer.sequence import AUGRU
+    rng = np.random.default_rng(B + T)
+    x = np.asarray(rng.normal(0, 0.7, (B, T, E)), np.float32)
+    att = np.asarray(rng.random((B, T, 1)), np.float32)
+    h0 = np.asarray(rng.normal(0, 0.3, (B, H)), np.float32)
+    L = AUGRU(H, return_sequence=True, recurrent_activation="hard_sigmoid" if hard else "sigmoid", as_written=False)
+    L.build(x.shape)
+    got = npy(L(x, att_score=att, initial_state=h0))
+    k, rk = npy(L.kernel), npy(L.recurrent_kernel)
+    want = O.augru(x.astype(np.float64), att.astype(np.float64), k, rk, h0.astype(np.float64),
+                   "hard_sigmoid" if hard else "sigmoid")[1]
+    assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))
+
+
 def test_towers_at_size(lib):
     """Ragged, larger shapes against the float64 oracle: DeepCrossing at the reference script's own settings (hidden 256-256,
     4 residual units, deepCrossing.py:37-39) on 5 000 samples; MMoE with 8 experts / 3 tasks on 10 001 rows; the local
