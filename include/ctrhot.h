@@ -493,6 +493,13 @@ int ctrhot_deepfm_train_step_ctl_f32(float* arena, const int64_t* row_off, int F
                                      float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
                                      int64_t workspace_bytes, int* err_flag, void* d_ctl, void* stream);
 
+/* FM under compile_fit (DL/model/fm.py:14-23: p = sigmoid(FMLayer(x)) on the dense one-hot matrix x [B, n], x_ld == n): one SGD
+ * step on mean clipped BCE + reg_w sum w1^2 + reg_v sum v^2, weights updated in place; loss_out as above. */
+int64_t ctrhot_fm_train_workspace_bytes(int64_t B, int n, int k_fm);
+int ctrhot_fm_train_step_f32(const float* x, int64_t x_ld, int n, const float* y, int64_t B, float* fm_w0,
+                             float* fm_w1, float* fm_v, int k_fm, float reg_w, float reg_v, float lr,
+                             float* loss_out, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ---- R12/R14 fused model front ends ------------------------------------------
  * gather -> x=[dense, embed] -> FM (DeepFM, DL/model/deepFM.py:24-28) or L cross
  * layers (DCN, DL/model/dcn.py:25-29) in ONE kernel; the gathered rows are

@@ -630,3 +630,18 @@ def deepfm_train_step(dense, ids, tables, fm_w0, fm_w1, fm_v, hidden, out, y, lr
         np.add.at(new_tables[f], ids[:, f], -lr * dx[:, off:off + kdim])
         off += kdim
     return (new_tables, new_w0, new_w1, new_v, new_hidden, new_out), bce, correct
+
+
+def fm_train_step(x, fm_w0, fm_w1, fm_v, y, lr, reg_w, reg_v):
+    """One step of keras SGD(lr) on FM (DL/model/fm.py:14-23: p = sigmoid(FMLayer(x))): mean clipped BCE + the l2 regularisers
+    of FMLayer.build.  PARITY UNPINNED against the reference like deepfm_train_step; gradients pinned by finite differences.
+    -> ((w0, w1, v) updated, mean BCE before the update, number of correct predictions)."""
+    B = x.shape[0]
+    xv = x @ fm_v
+    p = sigmoid(fm_layer(x, fm_w0, fm_w1, fm_v)[:, 0])
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    dz = np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B
+    g_w1 = x.T @ dz[:, None] + 2 * reg_w * fm_w1
+    g_v = x.T @ (dz[:, None] * xv) - fm_v * ((x ** 2).T @ dz)[:, None] + 2 * reg_v * fm_v
+    return (fm_w0 - lr * np.sum(dz), fm_w1 - lr * g_w1, fm_v - lr * g_v), bce, int(np.sum((p > 0.5) == (y > 0.5)))

@@ -211,6 +211,9 @@ __host__ __device__ inline DfSmem df_smem(const DfShape& s, int nraw) {
   return m;
 }
 
+#ifndef DF_ROUND_H1
+#define DF_ROUND_H1 1      // 1: H1 is rounded to nearest TF32 before layer 2 reads it; 0: left to the MMA's truncation
+#endif
 #ifndef DF_SKIP_PAD
 #define DF_SKIP_PAD 0      // 1: padding positions (history id 0) cost no row copy, no epilogue arithmetic, no weighted-sum read
 #endif
@@ -643,10 +646,10 @@ din_fwd_kernel(const __grid_constant__ DfParams p) {
         for (int j = 0; j < 16; j += 4) {
           const float4 uu = *reinterpret_cast<const float4*>(u + n0 + j);
           const float4 aa = *reinterpret_cast<const float4*>(al1 + ((((n0 + j) >> 2) ^ x1) << 2));
-          a[j + 0] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 0]) + uu.x, aa.x)));
-          a[j + 1] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 1]) + uu.y, aa.y)));
-          a[j + 2] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 2]) + uu.z, aa.z)));
-          a[j + 3] = __float_as_uint(df_tf32(df_prelu(__uint_as_float(a[j + 3]) + uu.w, aa.w)));
+          a[j + 0] = __float_as_uint(DF_ROUND_H1 ? df_tf32(df_prelu(__uint_as_float(a[j + 0]) + uu.x, aa.x)) : df_prelu(__uint_as_float(a[j + 0]) + uu.x, aa.x));
+          a[j + 1] = __float_as_uint(DF_ROUND_H1 ? df_tf32(df_prelu(__uint_as_float(a[j + 1]) + uu.y, aa.y)) : df_prelu(__uint_as_float(a[j + 1]) + uu.y, aa.y));
+          a[j + 2] = __float_as_uint(DF_ROUND_H1 ? df_tf32(df_prelu(__uint_as_float(a[j + 2]) + uu.z, aa.z)) : df_prelu(__uint_as_float(a[j + 2]) + uu.z, aa.z));
+          a[j + 3] = __float_as_uint(DF_ROUND_H1 ? df_tf32(df_prelu(__uint_as_float(a[j + 3]) + uu.w, aa.w)) : df_prelu(__uint_as_float(a[j + 3]) + uu.w, aa.w));
         }
         }
         if (n0 + 16 > h1) {                                   // zero the padding columns (they are layer 2's K padding)

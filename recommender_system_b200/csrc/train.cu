@@ -152,12 +152,12 @@ __global__ void tr_bias_relu_drop_kernel(float* __restrict__ h, const float* __r
 // p, per-sample loss / correctness and dz = dLoss/dlogit (loss = mean BCE over the batch, probabilities clipped like keras)
 __global__ void tr_loss_kernel(const float* __restrict__ fm, const float* __restrict__ dnn, const float* __restrict__ b_out,
                                const float* __restrict__ y, int64_t B, float* __restrict__ dz, float* __restrict__ loss_out,
-                               TrCtl* __restrict__ ctl) {
+                               TrCtl* __restrict__ ctl, float zscale) {
   __shared__ float s_loss[256], s_ok[256];
   float l = 0.f, ok = 0.f;
   if (ctl) y += ctl->row0;
   for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
-    const float z = 0.5f * (fm[b] + dnn[b] + (b_out ? b_out[0] : 0.f));
+    const float z = zscale * (fm[b] + (dnn ? dnn[b] : 0.f) + (b_out ? b_out[0] : 0.f));   // 1/2 (fm + dnn): DeepFM; fm: FM
     const float p = 1.0f / (1.0f + __expf(-z));
     const float eps = 1e-7f;
     const float pc = fminf(fmaxf(p, eps), 1.f - eps);
@@ -220,14 +220,16 @@ tr_colsum_kernel(const float* __restrict__ A, int64_t lda, const float* __restri
 // dx[b, j] += dfm_b (w1_j + sum_f v_jf xv_bf - x_bj sum_f v_jf^2);  also t[b, f] = dfm_b xv_bf (the right factor of dv)
 __global__ void tr_fm_bwd_kernel(const float* __restrict__ x, int n, int64_t B, const float* __restrict__ dz,
                                  const float* __restrict__ w1, const float* __restrict__ v, int kf,
-                                 const float* __restrict__ xv, float* __restrict__ dx, float* __restrict__ t) {
+                                 const float* __restrict__ xv, float* __restrict__ dx, float* __restrict__ t, float gscale) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t b = i / n;
     const int j = (int)(i - b * n);
-    const float dfm = 0.5f * dz[b];
-    float s = w1[j], vsq = 0.f;
-    for (int f = 0; f < kf; ++f) { const float vv = v[(int64_t)j * kf + f]; s = fmaf(vv, xv[b * kf + f], s); vsq = fmaf(vv, vv, vsq); }
-    dx[i] += dfm * (s - x[i] * vsq);
+    const float dfm = gscale * dz[b];
+    if (dx) {                                              // (a model whose x is its input needs no gradient for it)
+      float s = w1[j], vsq = 0.f;
+      for (int f = 0; f < kf; ++f) { const float vv = v[(int64_t)j * kf + f]; s = fmaf(vv, xv[b * kf + f], s); vsq = fmaf(vv, vv, vsq); }
+      dx[i] += dfm * (s - x[i] * vsq);
+    }
     if (j < kf) t[b * kf + j] = dfm * xv[b * kf + j];
   }
 }
@@ -288,6 +290,20 @@ inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, con
   dim3 grid((N + TR_T - 1) / TR_T, (M + TR_T - 1) / TR_T);
   tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
 }
+// FM backward and update with d loss / d fm = gscale * dz:  w0, w1 = (1 - 2 lr reg_w) w1 - lr x^T dfm, and v with its -x^2 v part
+// folded into a per-row scale (old w1 / v are used for dx, which is formed first; dx may be NULL)
+static void tr_fm_update(cudaStream_t st, const float* x, int n, int64_t B, const float* dz, float gscale, float* fm_w0,
+                         float* fm_w1, float* fm_v, int k_fm, float reg_w, float reg_v, float lr, const float* xv, float* t,
+                         float* s2, float* dx) {
+  const int M = (int)B;
+  const int nb = dx ? n : k_fm;                            // without dx only t = dfm * xv is formed: B x k_fm elements
+  tr_fm_bwd_kernel<<<tr_grid(B * nb, 256), 256, 0, st>>>(x, nb, B, dz, fm_w1, fm_v, k_fm, xv, dx, t, gscale);
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, fm_w0, -gscale * lr, 1.f);
+  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 0, fm_w1, -gscale * lr, 1.f - 2.f * lr * reg_w);
+  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 1, s2, gscale, 0.f);   // s2[j] = sum_b dfm_b x_bj^2
+  tr_scale_rows_kernel<<<tr_grid((int64_t)n * k_fm, 256), 256, 0, st>>>(fm_v, n, k_fm, s2, 1.f - 2.f * lr * reg_v, lr);
+  tr_gemm(st, x, 1, n, t, k_fm, 1, fm_v, k_fm, n, k_fm, M, -lr, 1.f);                      // v -= lr * x^T (dfm xv)
+}
 }  // namespace
 
 extern "C" int64_t ctrhot_deepfm_train_workspace_bytes(int64_t B, int n, int k_fm, const ctrhot_dense_desc* h_layers,
@@ -333,7 +349,7 @@ static int tr_step(float* arena, const int64_t* row_off, int F, int k, const voi
     in = h; in_dim = N;
   }
   tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, dnn, 1, M, 1, in_dim, 1.f, 0.f);
-  tr_loss_kernel<<<1, 256, 0, st>>>(fm, dnn, h_layers[NH].bias, y, B, dz, loss_out, ctl);
+  tr_loss_kernel<<<1, 256, 0, st>>>(fm, dnn, h_layers[NH].bias, y, B, dz, loss_out, ctl, 0.5f);
   // ---- backward through the tower: g = dLoss/d(pre-activation) of the current layer, [B, out_dim]
   float* g = ws + w.g0;
   float* gn = ws + w.g1;
@@ -360,13 +376,8 @@ static int tr_step(float* arena, const int64_t* row_off, int F, int k, const voi
       tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
-  // ---- FM backward (old w1, v), then its updates: w0, w1 = (1 - 2 lr reg_w) w1 - lr x^T dfm, v likewise with its -x^2 v part
-  tr_fm_bwd_kernel<<<tr_grid(B * n, 256), 256, 0, st>>>(x, n, B, dz, fm_w1, fm_v, k_fm, xv, dx, t);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, fm_w0, -0.5f * lr, 1.f);
-  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 0, fm_w1, -0.5f * lr, 1.f - 2.f * lr * reg_w);
-  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 1, s2, 0.5f, 0.f);  // s2[j] = sum_b dfm_b x_bj^2
-  tr_scale_rows_kernel<<<tr_grid((int64_t)n * k_fm, 256), 256, 0, st>>>(fm_v, n, k_fm, s2, 1.f - 2.f * lr * reg_v, lr);
-  tr_gemm(st, x, 1, n, t, k_fm, 1, fm_v, k_fm, n, k_fm, M, -lr, 1.f);                      // v -= lr * x^T (dfm xv)
+  // ---- FM backward (old w1, v), then its updates
+  tr_fm_update(st, x, n, B, dz, 0.5f, fm_w0, fm_w1, fm_v, k_fm, reg_w, reg_v, lr, xv, t, s2, dx);
   // ---- embedding rows
   if (ids_kind == CTRHOT_IDS_I32)
     tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr, ctl);
@@ -399,4 +410,30 @@ extern "C" int ctrhot_deepfm_train_step_ctl_f32(float* arena, const int64_t* row
   return tr_step(arena, row_off, F, k, ids, ids_kind, ids_ld, dense, dense_ld, D, y, B, fm_w0, fm_w1, fm_v, k_fm, reg_w, reg_v,
                  h_layers, n_layers, lr, dropout, seed, loss_out, workspace, workspace_bytes, err_flag,
                  static_cast<TrCtl*>(d_ctl), stream);
+}
+
+
+// ---- FM (DL/model/fm.py:14-23: p = sigmoid(FMLayer(x)) on the dense one-hot matrix) under compile_fit -----------------------
+extern "C" int64_t ctrhot_fm_train_workspace_bytes(int64_t B, int n, int k_fm) {
+  if (B < 0 || n <= 0 || k_fm < 1 || k_fm > 32) return CTRHOT_ESHAPE;
+  return (2 * (B * k_fm + 3) / 4 * 4 + 2 * ((B + 3) / 4 * 4) + (n + 3) / 4 * 4) * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_fm_train_step_f32(const float* x, int64_t x_ld, int n, const float* y, int64_t B, float* fm_w0,
+                                        float* fm_w1, float* fm_v, int k_fm, float reg_w, float reg_v, float lr,
+                                        float* loss_out, void* workspace, int64_t workspace_bytes, void* stream) {
+  CTRHOT_RANGE("ctrhot_fm_train_step_f32");
+  if (!x || !y || !fm_w0 || !fm_w1 || !fm_v || !loss_out || !workspace || B <= 0 || n <= 0 || x_ld != n || !(lr >= 0.f))
+    return CTRHOT_EARG;                                     // (dense rows only: x_ld == n)
+  if (k_fm < 1 || k_fm > 32) return CTRHOT_ESHAPE;
+  if (workspace_bytes < ctrhot_fm_train_workspace_bytes(B, n, k_fm) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  const int64_t bk = (B * k_fm + 3) / 4 * 4, b4 = (B + 3) / 4 * 4;
+  float *xv = ws, *t = ws + bk, *fm = ws + 2 * bk, *dz = fm + b4, *s2 = dz + b4;
+  tr_fm_fwd_kernel<<<(int)((B + 7) / 8), 256, 0, st>>>(x, n, B, fm_w0, fm_w1, fm_v, k_fm, xv, fm);
+  tr_loss_kernel<<<1, 256, 0, st>>>(fm, nullptr, nullptr, y, B, dz, loss_out, nullptr, 1.0f);
+  tr_fm_update(st, x, n, B, dz, 1.0f, fm_w0, fm_w1, fm_v, k_fm, reg_w, reg_v, lr, xv, t, s2, nullptr);
+  CTRHOT_LAUNCH_OK("ctrhot_fm_train_step_f32");
+  return CTRHOT_OK;
 }

@@ -6,7 +6,8 @@
 ``binary_crossentropy``, metric accuracy, ``epochs`` passes.  Each batch is ONE call of ``ctrhot_deepfm_train_step_f32``
 (csrc/train.cu): forward, clipped BCE + FMLayer's l2 regularisers, exact fp32 gradients, in-place SGD on the embedding
 rows that were looked up, the FM weights and the tower.  SURVEY 8(f) rank 3; built for DeepFM (the reference's flagship
-``__main__``, DL/model/deepFM.py:34-57) -- other models raise NotImplementedError.
+``__main__``, DL/model/deepFM.py:34-57) and for FM on its dense one-hot matrix (DL/model/fm.py:26-45, BASELINE config 1;
+``ctrhot_fm_train_step_f32``) -- other models raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -23,7 +24,7 @@ class _DeepFMTrainer:
     def __init__(self, model, dropout=None):
         from ..model.criteo import DeepFM
         if not isinstance(model, DeepFM):
-            raise NotImplementedError("compile_fit: the training step exists for DeepFM only (SURVEY 8(f) rank 3)")
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM and FM only (SURVEY 8(f) rank 3)")
         self.m = model
         if not model.dnn.built:
             model.build(None)
@@ -99,11 +100,57 @@ class _DeepFMTrainer:
         self.m._bump()
 
 
+class _FMTrainer:
+    """FM (DL/model/fm.py:14-23) on its dense one-hot matrix: ctrhot_fm_train_step_f32 per batch."""
+
+    def __init__(self, model):
+        self.m, self.ws, self.step = model, None, 0
+        self.loss = torch.zeros(2, dtype=torch.float32, device=model.device)
+
+    def train_on_batch(self, x, y, lr):
+        fm = self.m.fm
+        if not fm.built:
+            self.m.build((None, x.shape[1]))
+        B, n = x.shape
+        need = _lib.query("ctrhot_fm_train_workspace_bytes", B, n, fm.k)
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=self.m.device)
+        _lib.call("ctrhot_fm_train_step_f32", ptr(x), x.stride(0), n, ptr(y), B, ptr(fm.w0), ptr(fm.w1), ptr(fm.v), fm.k,
+                  float(fm.reg_w), float(fm.reg_b), float(lr), ptr(self.loss), ptr(self.ws), self.ws.numel() * 4, stream_ptr())
+        self.step += 1
+        return self.loss
+
+
+def _fit_fm(model, X, y, batch_size, epochs, sgd, verbose):
+    tr = _FMTrainer(model)
+    dev = model.device
+    Xd = as_device_f32(X, dev).contiguous()
+    yd = as_device_f32(np.asarray(y, dtype=np.float32).reshape(-1) if not isinstance(y, torch.Tensor) else y.reshape(-1), dev)
+    N = Xd.shape[0]
+    model.history = []
+    for ep in range(epochs):
+        tot = torch.zeros(2, dtype=torch.float64, device=dev)
+        for s in range(0, N, batch_size):
+            e = min(N, s + batch_size)
+            out = tr.train_on_batch(Xd[s:e], yd[s:e], sgd)
+            tot[0] += out[0].double() * (e - s)
+            tot[1] += out[1].double()
+        loss, acc = (tot / N).tolist()
+        model.history.append((loss, acc))
+        if verbose:
+            print("Epoch %d/%d - loss: %.4f - accuracy: %.4f" % (ep + 1, epochs, loss, acc))
+    model._bump()
+    return model
+
+
 def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True, use_graph=True):
     """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
     (loss, accuracy) pairs are left in ``model.history``.  ``use_graph``: the full batches of an epoch replay one captured CUDA
     graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
+    from ..model.criteo import FM
+    if isinstance(model, FM):
+        return _fit_fm(model, X, y, batch_size, epochs, sgd, verbose)
     tr = _DeepFMTrainer(model, dropout)
     dev = model.device
     D = len(model.dense_feature_columns)

@@ -173,3 +173,40 @@ def test_graph_replay_equals_call_by_call(lib, rate):
     for (ka, ba), (kb, bb) in zip(pa[4], pb[4]):
         np.testing.assert_allclose(ka, kb, rtol=0, atol=2e-6)
         np.testing.assert_allclose(ba, bb, rtol=0, atol=2e-6)
+
+
+def test_fm_step_and_compile_fit(lib):
+    """FM (DL/model/fm.py:14-23) on a dense one-hot matrix shaped like the reference's (13 dense columns + one-hot blocks):
+    one step against the oracle's fm_train_step, then compile_fit learns a planted rule."""
+    from recommender_system_b200.model.criteo import FM
+    from recommender_system_b200.utils.compile_fit import _FMTrainer
+    rng = np.random.default_rng(2)
+    vocab = [30, 7, 120, 50]
+    N, n = 2000 + 13, 13 + sum(vocab)
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.zeros((N, n), np.float32)
+    X[:, :13] = rng.random((N, 13))
+    off = 13
+    for f, v in enumerate(vocab):
+        X[np.arange(N), off + ids[:, f]] = 1.0
+        off += v
+    y = (ids[:, 0] < 15).astype(np.float32)
+    set_seed(9)
+    m = FM(8, 1e-2, 2e-2)
+    m.build((None, n))
+    m.set_weights({"FMLayer_0/w0": np.asarray([0.05], np.float32)})
+    w = {k: npy(t) for k, t in m.named_weights().items()}
+    before = (w["FMLayer_0/w0"], w["FMLayer_0/w1"], w["FMLayer_0/v"])
+    tr = _FMTrainer(m)
+    dev = m.device
+    out = tr.train_on_batch(torch.from_numpy(X[:257]).to(dev), torch.from_numpy(y[:257]).to(dev), 0.1)
+    torch.cuda.synchronize()
+    want, bce, correct = O.fm_train_step(X[:257].astype(np.float64), *before, y[:257].astype(np.float64), 0.1, 1e-2, 2e-2)
+    assert abs(float(out[0]) - bce) <= 2e-6 and int(out[1]) == correct
+    w = {k: npy(t) for k, t in m.named_weights().items()}
+    close(w["FMLayer_0/w0"], want[0], before[0], "w0"); close(w["FMLayer_0/w1"], want[1], before[1], "w1")
+    close(w["FMLayer_0/v"], want[2], before[2], "v")
+    compile_fit(m, X, y, batch_size=32, epochs=6, sgd=0.1, verbose=False)
+    assert m.history[-1][0] < 0.8 * m.history[0][0] and m.history[-1][1] > 0.85, m.history
+    p = npy(m(X))[:, 0]
+    assert np.mean((p > 0.5) == (y > 0.5)) > 0.85

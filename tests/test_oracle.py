@@ -182,3 +182,24 @@ def test_deepfm_train_step_gradients():
         g = (arr - upd) / lr
         for idx in idxs:
             assert abs(fd(arr, put, idx) - g[idx]) < 1e-8, (idx, fd(arr, put, idx), g[idx])
+
+
+def test_fm_train_step_gradients():
+    rng = np.random.default_rng(1)
+    B, n, k = 11, 9, 4
+    x, y = rng.normal(0, 1, (B, n)), rng.integers(0, 2, B).astype(float)
+    w0, w1, v = rng.normal(0, 0.1, 1), rng.normal(0, 0.2, (n, 1)), rng.normal(0, 0.2, (n, k))
+    lr, rw, rv = 0.1, 1e-2, 2e-2
+    new, bce, _ = O.fm_train_step(x, w0, w1, v, y, lr, rw, rv)
+
+    def loss(w0_, w1_, v_):
+        p = np.clip(O.sigmoid(O.fm_layer(x, w0_, w1_, v_)[:, 0]), 1e-7, 1 - 1e-7)
+        return np.mean(-(y * np.log(p) + (1 - y) * np.log(1 - p))) + rw * np.sum(w1_ ** 2) + rv * np.sum(v_ ** 2)
+    eps = 1e-6
+    for idx in [(0, 0), (4, 2), (8, 3)]:
+        a, b = v.copy(), v.copy(); a[idx] += eps; b[idx] -= eps
+        assert abs((loss(w0, w1, a) - loss(w0, w1, b)) / (2 * eps) - ((v - new[2]) / lr)[idx]) < 1e-8
+    for i in (0, 5):
+        a, b = w1.copy(), w1.copy(); a[i, 0] += eps; b[i, 0] -= eps
+        assert abs((loss(w0, a, v) - loss(w0, b, v)) / (2 * eps) - ((w1 - new[1]) / lr)[i, 0]) < 1e-8
+    assert abs((loss(w0 + eps, w1, v) - loss(w0 - eps, w1, v)) / (2 * eps) - ((w0 - new[0]) / lr)[0]) < 1e-8
