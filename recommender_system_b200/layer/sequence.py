@@ -73,7 +73,7 @@ class AUGRU(Layer):
     ``recurrent_kernel [units, 3 units]`` (z | r | h blocks, no biases).  One launch (ctrhot_augru_f32), zero initial state.
 
     Under TF 2 the reference's cell runs with tanh / SIGMOID whatever it is given (keras' GRUCell constructor overwrites the
-    attributes AUGRUCell sets first, activation.py:97-100; pinned in tests/golden/ref_layers.npz case 'augru'); this class does
+    attributes AUGRUCell sets first, activation.py:97-100; pinned by the committed reference golden, case 'augru'); this class does
     the same by default.  ``as_written=False`` uses the constructor's activations instead.  The masked branch of rnn_augru
     (activation.py:214-236) is not implemented: DIEN passes no mask."""
 
