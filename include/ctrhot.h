@@ -376,6 +376,23 @@ int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* row_off, int 
                                 const float* h_combine, int n_combine, float* h, int64_t h_ld, float* side_out,
                                 int cluster, int* err_flag, int32_t* signal_flags, int epoch, void* stream);
 
+/* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
+ * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
+ * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).
+ *   out[b, 0 : F k)              = arena[row_off[f] + ids[b, f], :]                        (bit-exact)
+ *   out[b, F k : F k + P)        = <e_i, e_j>, pairs row-major over i < j                  (if do_inner)
+ *   out[b, .. : .. + P)          = sum_a e_j[a] sum_c W[a, p, c] e_i[c]                    W = [k, P, k]
+ *   out[b, width : out_ld)       = 0
+ * The inner sum of the outer product runs on the tensor pipe as a three-term TF32 split (fp32-accurate: <= 1e-5 relative),
+ * the rest on the CUDA cores from the same shared-memory tile.  k == 8 (the reference's embed_dim), 2 <= F <= 28;
+ * out 16-byte aligned, out_ld % 4 == 0.  packed = ctrhot_pnn_pack(W) (ctrhot_pnn_pack_bytes bytes, re-pack when W changes). */
+int64_t ctrhot_pnn_pack_bytes(int F, int k);
+int ctrhot_pnn_pack(const float* W, int F, int k, void* packed, void* stream);
+int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, int F, int k,
+                         const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
+                         const void* packed, int do_inner, float* out, int64_t out_ld,
+                         int* err_flag, void* stream);
+
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,
                     const float* var, float eps, float* out, void* stream);

@@ -1,0 +1,412 @@
+// R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch (DL/model/pnn.py:28-49,
+// DL/layer/interaction.py:166-215).  The gathered rows of 128 samples live in shared memory only: they are the A operand of
+// the outer product's contraction, the q / p vectors of the epilogue and the source of the flat columns; what reaches HBM is
+// the product vector the tower reads.
+//
+// The outer product  out[b, p] = sum_a e_j[a] * (sum_c W[a, p, c] e_i[c])  is a contraction with per-pair weights
+// (k^2 FMA per pair: 20.8 K per sample at F = 26, k = 8), so its inner sum runs on the tensor pipe:
+//     D[b, (slot, a)] = sum_c E_i[b, c] * Wb[(slot, a), c]        M = 128 samples, N = 8 x slots of run i, K = 8 (one TF32 k-step)
+// with fp32 accuracy from a three-term split (A = At + Al, W = Wh + Wl:  At Wh + Al Wh + At Wl; At is what the MMA reads from
+// the fp32 tile itself -- it truncates --, Al = tf32(x - At) is built per 4-field panel, Wh / Wl are packed once), and the
+// outer sum  sum_a D[b, (slot, a)] e_j[b, a]  plus the inner product <e_i, e_j> run in the epilogue warps on TMEM lanes = rows.
+//
+// shared memory (k = 8, F <= 28):  E tile  ceil(F/4) panels of [128 rows x 128 B] (4 fields per 128-byte row, 128-byte
+// swizzle: field f is k-slice f % 4 of panel f / 4), two Al panels, a 3-deep ring of 16 KB W tiles (one 256-column chunk:
+// k-slices {hi, lo} x {columns 0..127, 128..255}), per-warp transpose buffers for coalesced stores.
+// TMEM: two 256-column accumulators (MMA of chunk c + 1 under the epilogue of chunk c).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace ctrhot {
+using namespace tc;
+namespace {
+
+constexpr int PF_K = 8;
+constexpr int PF_BM = 128;
+constexpr int PF_MAXF = 28;
+constexpr int PF_MAXSLOT = 416;                 // 13 chunks of 32 pair slots
+constexpr int PF_MAXOPS = 128;
+constexpr int PF_NEPI = 8, PF_NGAT = 4;         // epilogue warps 0-7, gather/builder warps 8-11, MMA 12, W producer 13
+constexpr int PF_THREADS = (PF_NEPI + PF_NGAT + 2) * 32;
+constexpr int PF_WRING = 3;
+constexpr uint32_t PF_PANEL = 16384;
+// packed buffer: header, slot tables, MMA op list, then one 16 KB W tile per chunk
+constexpr int PF_O_IJ = 64, PF_O_P = PF_O_IJ + 2 * PF_MAXSLOT, PF_O_OPS = PF_O_P + 2 * PF_MAXSLOT;
+constexpr int PF_TAB_BYTES = PF_O_OPS + 4 * PF_MAXOPS;   // 2240
+constexpr int PF_O_W = 4096;
+
+struct PfPlan { int F, P, nslots, nch, nops, npa; };
+__host__ __device__ inline PfPlan pf_plan(int F) {
+  PfPlan q;
+  q.F = F; q.P = F * (F - 1) / 2;
+  int ns = 0, nops = 0;
+  for (int i = 0; i < F - 1; ++i) {
+    const int len = F - 1 - i, plen = len + (len & 1);
+    int s = ns;
+    while (s < ns + plen) { int e = (s / 16 + 1) * 16; if (e > ns + plen) e = ns + plen; ++nops; s = e; }
+    ns += plen;
+  }
+  q.nslots = ns; q.nch = (ns + 31) / 32; q.nops = nops; q.npa = (F - 2) / 4 + 1;
+  return q;
+}
+
+// one block: thread 0 lays out the pair slots (run i = pairs (i, i+1..F-1), padded to an even count so that every MMA has
+// N % 16 == 0) and the op list; then all threads split W[a, p, c] into tf32 hi / lo in the tiles' swizzled layout
+__global__ void pnn_pack_kernel(const float* __restrict__ W, int F, uint8_t* __restrict__ packed) {
+  const PfPlan q = pf_plan(F);
+  int32_t* hdr = reinterpret_cast<int32_t*>(packed);
+  uint16_t* ij = reinterpret_cast<uint16_t*>(packed + PF_O_IJ);
+  int16_t* sp = reinterpret_cast<int16_t*>(packed + PF_O_P);
+  uint32_t* ops = reinterpret_cast<uint32_t*>(packed + PF_O_OPS);
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    hdr[0] = F; hdr[1] = q.P; hdr[2] = q.nslots; hdr[3] = q.nch; hdr[4] = q.nops; hdr[5] = q.npa;
+    int ns = 0, no = 0, p = 0;
+    for (int i = 0; i < F - 1; ++i) {
+      const int len = F - 1 - i, plen = len + (len & 1);
+      for (int t = 0; t < plen; ++t) {
+        if (t < len) { ij[ns + t] = (uint16_t)((i << 8) | (i + 1 + t)); sp[ns + t] = (int16_t)p++; }
+        else { ij[ns + t] = 0xFFFFu; sp[ns + t] = -1; }
+      }
+      int s = ns;
+      while (s < ns + plen) {
+        int e = (s / 16 + 1) * 16; if (e > ns + plen) e = ns + plen;
+        ops[no++] = ((uint32_t)(s / 32) << 24) | ((uint32_t)(s % 32) << 16) | ((uint32_t)(e - s) << 8) | (uint32_t)i;
+        s = e;
+      }
+      ns += plen;
+    }
+    for (int t = ns; t < PF_MAXSLOT; ++t) { ij[t] = 0xFFFFu; sp[t] = -1; }
+    for (int t = no; t < PF_MAXOPS; ++t) ops[t] = 0xFFFFFFFFu;
+  }
+  __syncthreads();
+  // tile of chunk c: row n' (0..127), k-slice s: 0 hi / 1 lo of column n', 2 hi / 3 lo of column 128 + n'; column n = slot * 8 + a
+  const int total = q.nch * 256 * PF_K;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+    const int c = t & 7, n = (t >> 3) & 255, ch = t >> 11;
+    const int slot = ch * 32 + (n >> 3), a = n & 7;
+    const int p = (slot < PF_MAXSLOT) ? sp[slot] : -1;
+    const float w = (p >= 0) ? W[((size_t)a * q.P + p) * PF_K + c] : 0.f;
+    const float hi = to_tf32_rna(w), lo = to_tf32_rna(w - hi);
+    const uint32_t row = n & 127, half = n >> 7;
+    uint8_t* tile = packed + PF_O_W + (size_t)ch * PF_PANEL;
+    *reinterpret_cast<float*>(tile + sw128_offset(row, half * 4 + (c >> 2)) + (c & 3) * 4) = hi;
+    *reinterpret_cast<float*>(tile + sw128_offset(row, half * 4 + 2 + (c >> 2)) + (c & 3) * 4) = lo;
+  }
+}
+
+struct PfParams {
+  const float* arena; const int64_t* row_off; const void* ids; int64_t ids_ld; int64_t B;
+  const uint8_t* packed; float* out; int64_t out_ld; int* err_flag;
+  int F, do_inner, col_inner, col_outer, width;
+};
+
+struct PfSmem { uint32_t e, lo, wr, stg, tab, bars, total; };
+__host__ __device__ inline PfSmem pf_smem(int F) {
+  PfSmem m;
+  const uint32_t npan = (uint32_t)(F + 3) / 4;
+  m.e = 0; m.lo = npan * PF_PANEL; m.wr = m.lo + 2 * PF_PANEL; m.stg = m.wr + PF_WRING * PF_PANEL;
+  m.tab = m.stg + PF_NEPI * 32 * 17 * 4; m.bars = m.tab + ((PF_TAB_BYTES + 15) / 16) * 16;
+  m.total = m.bars + 192;
+  return m;
+}
+
+template <int IDKIND>
+__global__ void __launch_bounds__(PF_THREADS, 1)
+pnn_front_kernel(const __grid_constant__ PfParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t base = (raw_addr + 1023u) & ~1023u;
+  uint8_t* bp = smem_raw + (base - raw_addr);
+  const int F = p.F;
+  const PfSmem mp = pf_smem(F);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const uint32_t bars = base + mp.bars;
+  const uint32_t e_full = bars, e_free = bars + 8;
+  auto lo_full = [&](int i) { return bars + 16u + 8u * i; };
+  auto lo_free = [&](int i) { return bars + 32u + 8u * i; };
+  auto w_full = [&](int i) { return bars + 48u + 8u * i; };
+  auto w_free = [&](int i) { return bars + 72u + 8u * i; };
+  auto d_full = [&](int i) { return bars + 96u + 8u * i; };
+  auto d_free = [&](int i) { return bars + 112u + 8u * i; };
+  const uint32_t slot_addr = bars + 128u;
+  volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(bp + mp.bars + 128);
+  const int32_t* hdr = reinterpret_cast<const int32_t*>(bp + mp.tab);
+  const uint16_t* t_ij = reinterpret_cast<const uint16_t*>(bp + mp.tab + PF_O_IJ);
+  const int16_t* t_p = reinterpret_cast<const int16_t*>(bp + mp.tab + PF_O_P);
+  const uint32_t* t_ops = reinterpret_cast<const uint32_t*>(bp + mp.tab + PF_O_OPS);
+
+  if (tid == 0) {
+    mbar_init(e_full, PF_NGAT * 32); mbar_init(e_free, PF_NEPI);
+    for (int i = 0; i < 2; ++i) { mbar_init(lo_full(i), PF_NGAT * 32); mbar_init(lo_free(i), 1); }
+    for (int i = 0; i < PF_WRING; ++i) { mbar_init(w_full(i), 1); mbar_init(w_free(i), 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(d_full(i), 1); mbar_init(d_free(i), PF_NEPI); }
+    mbar_fence_init();
+  }
+  for (int i = tid; i < PF_TAB_BYTES / 4; i += PF_THREADS)
+    reinterpret_cast<uint32_t*>(bp + mp.tab)[i] = __ldg(reinterpret_cast<const uint32_t*>(p.packed) + i);
+  if (warp == PF_NEPI + PF_NGAT) { tmem_alloc(slot_addr, 512u); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *slot_ptr;
+  const int nch = hdr[3], nops = hdr[4], npa = hdr[5];
+  const int64_t n_tiles = (p.B + PF_BM - 1) / PF_BM;
+  const int64_t my_tiles = (n_tiles > blockIdx.x) ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+  if (warp < PF_NEPI) {
+    // ================================================================ epilogue: lanes = rows, warp = (lane quarter, column half)
+    const int q = warp & 3, h = warp >> 2;
+    const uint32_t row = (uint32_t)(q * 32 + lane);
+    float* stg = reinterpret_cast<float*>(bp + mp.stg) + warp * 32 * 17;
+    uint32_t dc = 0;
+#pragma unroll 1
+    for (int64_t it = 0; it < my_tiles; ++it) {
+      const int64_t b0 = (blockIdx.x + it * gridDim.x) * PF_BM;
+      mbar_wait(e_full, (uint32_t)(it & 1));
+      int cur_i = -1;
+      float ei[PF_K];
+#pragma unroll
+      for (int a = 0; a < PF_K; ++a) ei[a] = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < nch; ++c, ++dc) {
+        const uint32_t buf = dc & 1u;
+        mbar_wait(d_full(buf), (dc >> 1) & 1u);
+        tc_fence_after();
+        float vo[16], vi[16];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float d[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)h * 128u + (uint32_t)g * 32u, d);
+#pragma unroll
+          for (int s = 0; s < 4; ++s) {
+            const int slot = c * 32 + h * 16 + g * 4 + s;
+            const uint32_t ij = t_ij[slot];
+            float o = 0.f, n = 0.f;
+            if (ij != 0xFFFFu) {
+              const int i = (int)(ij >> 8), j = (int)(ij & 255u);
+              if (i != cur_i) {
+                const uint8_t* pi = bp + mp.e + (uint32_t)(i >> 2) * PF_PANEL;
+                const float4 x0 = *reinterpret_cast<const float4*>(pi + sw128_offset(row, (uint32_t)(i & 3) * 2));
+                const float4 x1 = *reinterpret_cast<const float4*>(pi + sw128_offset(row, (uint32_t)(i & 3) * 2 + 1));
+                ei[0] = x0.x; ei[1] = x0.y; ei[2] = x0.z; ei[3] = x0.w; ei[4] = x1.x; ei[5] = x1.y; ei[6] = x1.z; ei[7] = x1.w;
+                cur_i = i;
+              }
+              const uint8_t* pj = bp + mp.e + (uint32_t)(j >> 2) * PF_PANEL;
+              const float4 y0 = *reinterpret_cast<const float4*>(pj + sw128_offset(row, (uint32_t)(j & 3) * 2));
+              const float4 y1 = *reinterpret_cast<const float4*>(pj + sw128_offset(row, (uint32_t)(j & 3) * 2 + 1));
+              const float ej[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+#pragma unroll
+              for (int a = 0; a < PF_K; ++a) { o = fmaf(d[s * 8 + a], ej[a], o); n = fmaf(ei[a], ej[a], n); }
+            }
+            vo[g * 4 + s] = o; vi[g * 4 + s] = n;
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(d_free(buf));
+        // transpose through the warp's buffer: lanes = 2 rows x 16 consecutive pair columns per store
+        const int sl = c * 32 + h * 16 + (lane & 15);
+        const int pcol = t_p[sl];
+#pragma unroll 1
+        for (int pass = p.do_inner ? 0 : 1; pass < 2; ++pass) {
+          __syncwarp();
+#pragma unroll
+          for (int s = 0; s < 16; ++s) stg[lane * 17 + s] = pass ? vo[s] : vi[s];
+          __syncwarp();
+          const int colb = pass ? p.col_outer : p.col_inner;
+          if (pcol >= 0) {
+#pragma unroll 4
+            for (int r2 = 0; r2 < 16; ++r2) {
+              const int r = 2 * r2 + (lane >> 4);
+              const int64_t b = b0 + q * 32 + r;
+              if (b < p.B) p.out[b * p.out_ld + colb + pcol] = stg[r * 17 + (lane & 15)];
+            }
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(e_free);
+    }
+  } else if (warp < PF_NEPI + PF_NGAT) {
+    // ================================================================ gather (thread = row) + flat columns + Al panels
+    const int gt = tid - PF_NEPI * 32, gw = warp - PF_NEPI;
+    const int npan = (F + 3) / 4;
+    uint32_t lp = 0;                                               // Al panel sequence number (buffer lp & 1)
+#pragma unroll 1
+    for (int64_t it = 0; it < my_tiles; ++it) {
+      const int64_t b0 = (blockIdx.x + it * gridDim.x) * PF_BM;
+      if (it > 0) mbar_wait(e_free, (uint32_t)((it - 1) & 1));
+      const int64_t b = b0 + gt;
+      const bool live = b < p.B;
+#pragma unroll 1
+      for (int f = 0; f < 4 * npan; ++f) {
+        const float* src = p.arena;
+        uint32_t nb = 0;
+        if (live && f < F) {
+          const int64_t id = IdLoad<IDKIND>::at(p.ids, b * p.ids_ld + f);
+          const int64_t r0 = __ldg(p.row_off + f), r1 = __ldg(p.row_off + f + 1);
+          if (id >= 0 && id < r1 - r0) { src = p.arena + (r0 + id) * PF_K; nb = 16; }
+          else if (p.err_flag) *p.err_flag = 1;
+        }
+        const uint32_t dst = base + mp.e + (uint32_t)(f >> 2) * PF_PANEL;
+        cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2), src, nb);
+        cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2 + 1), src + 4, nb);
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      fence_proxy_async_smem();
+      mbar_arrive(e_full);
+      named_bar_sync(1, PF_NGAT * 32);
+      // flat columns [0, F k) and the zero padding [width, out_ld): coalesced 16-byte stores, rows of this warp
+#pragma unroll 1
+      for (int r = gw * 32; r < gw * 32 + 32; ++r) {
+        const int64_t br = b0 + r;
+        if (br >= p.B) break;
+        float* orow = p.out + br * p.out_ld;
+        for (int l = lane; l < 2 * F; l += 32) {
+          const int f = l >> 1;
+          const float4 v = *reinterpret_cast<const float4*>(bp + mp.e + (uint32_t)(f >> 2) * PF_PANEL +
+                                                            sw128_offset((uint32_t)r, (uint32_t)(f & 3) * 2 + (l & 1)));
+          *reinterpret_cast<float4*>(orow + 4 * l) = v;
+        }
+        for (int l = p.width + lane; l < p.out_ld; l += 32) orow[l] = 0.f;
+      }
+      // Al = tf32(x - trunc_tf32(x)) for the panels that hold a run's field i, two panels ahead of the MMAs at most
+#pragma unroll 1
+      for (int m = 0; m < npa; ++m, ++lp) {
+        const uint32_t bf = lp & 1u;
+        mbar_wait(lo_free(bf), ((lp >> 1) & 1u) ^ 1u);
+        const float4* s4 = reinterpret_cast<const float4*>(bp + mp.e + (uint32_t)m * PF_PANEL);
+        float4* d4 = reinterpret_cast<float4*>(bp + mp.lo + bf * PF_PANEL);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          float4 x = s4[gt + 128 * u];
+          x.x = to_tf32_rna(x.x - __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u));
+          x.y = to_tf32_rna(x.y - __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u));
+          x.z = to_tf32_rna(x.z - __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u));
+          x.w = to_tf32_rna(x.w - __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u));
+          d4[gt + 128 * u] = x;
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(lo_full(bf));
+      }
+    }
+  } else if (warp == PF_NEPI + PF_NGAT) {
+    // ================================================================ MMA issuer (converged warp, one elected lane issues)
+    uint32_t wc = 0, dc = 0, lp = 0;
+#pragma unroll 1
+    for (int64_t it = 0; it < my_tiles; ++it) {
+      mbar_wait(e_full, (uint32_t)(it & 1));
+      int cur_pan = -1, oi = 0;
+#pragma unroll 1
+      for (int c = 0; c < nch; ++c, ++wc, ++dc) {
+        const uint32_t st = wc % PF_WRING, buf = dc & 1u;
+        mbar_wait(w_full(st), (wc / PF_WRING) & 1u);
+        mbar_wait(d_free(buf), ((dc >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t wt = base + mp.wr + st * PF_PANEL;
+#pragma unroll 1
+        while (oi < nops && (int)(t_ops[oi] >> 24) == c) {
+          const uint32_t op = t_ops[oi++];
+          const uint32_t s0 = (op >> 16) & 255u, ns = (op >> 8) & 255u, i = op & 255u;
+          const int pan = (int)(i >> 2);
+          if (pan != cur_pan) {
+            if (cur_pan >= 0) { if (elect_one()) mma_commit(lo_free((lp - 1) & 1u)); __syncwarp(); }
+            mbar_wait(lo_full(lp & 1u), (lp >> 1) & 1u);
+            tc_fence_after();
+            ++lp; cur_pan = pan;
+          }
+          const uint32_t half = s0 >> 4, sh = s0 & 15u;
+          const uint64_t a_hi = make_desc_sw128(base + mp.e + (uint32_t)pan * PF_PANEL + (i & 3u) * 32u);
+          const uint64_t a_lo = make_desc_sw128(base + mp.lo + ((lp - 1) & 1u) * PF_PANEL + (i & 3u) * 32u);
+          const uint64_t b_hi = make_desc_sw128(wt + sh * 1024u + half * 64u);
+          const uint64_t b_lo = make_desc_sw128(wt + sh * 1024u + half * 64u + 32u);
+          const uint32_t idesc = make_idesc_tf32(PF_BM, ns * 8u);
+          const uint32_t dcol = tmem_base + buf * 256u + s0 * 8u;
+          if (elect_one()) {
+            mma_tf32_ss(dcol, a_hi, b_hi, idesc, 0u);
+            mma_tf32_ss(dcol, a_lo, b_hi, idesc, 1u);
+            mma_tf32_ss(dcol, a_hi, b_lo, idesc, 1u);
+          }
+          __syncwarp();
+        }
+        if (elect_one()) { mma_commit(d_full(buf)); mma_commit(w_free(st)); }
+        __syncwarp();
+      }
+      if (elect_one()) mma_commit(lo_free((lp - 1) & 1u));
+      __syncwarp();
+    }
+  } else {
+    // ================================================================ W producer: one 16 KB tile per chunk through the ring
+    uint32_t wc = 0;
+#pragma unroll 1
+    for (int64_t it = 0; it < my_tiles; ++it) {
+#pragma unroll 1
+      for (int c = 0; c < nch; ++c, ++wc) {
+        const uint32_t st = wc % PF_WRING;
+        mbar_wait(w_free(st), ((wc / PF_WRING) & 1u) ^ 1u);
+        if (lane == 0) {
+          mbar_arrive_expect_tx(w_full(st), PF_PANEL);
+          bulk_g2s(base + mp.wr + st * PF_PANEL, p.packed + PF_O_W + (size_t)c * PF_PANEL, PF_PANEL, w_full(st));
+        }
+        __syncwarp();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == PF_NEPI + PF_NGAT) { tc_fence_after(); tmem_dealloc(tmem_base, 512u); }
+}
+
+}  // namespace
+}  // namespace ctrhot
+
+using namespace ctrhot;
+
+extern "C" int64_t ctrhot_pnn_pack_bytes(int F, int k) {
+  if (k != PF_K || F < 2 || F > PF_MAXF) return CTRHOT_ESHAPE;
+  return (int64_t)PF_O_W + (int64_t)pf_plan(F).nch * PF_PANEL;
+}
+
+extern "C" int ctrhot_pnn_pack(const float* W, int F, int k, void* packed, void* stream) {
+  CTRHOT_RANGE("ctrhot_pnn_pack");
+  if (!W || !packed) return CTRHOT_EARG;
+  if (k != PF_K || F < 2 || F > PF_MAXF || !aligned16(packed)) return CTRHOT_ESHAPE;
+  pnn_pack_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(W, F, static_cast<uint8_t*>(packed));
+  CTRHOT_LAUNCH_OK("ctrhot_pnn_pack");
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, int F, int k,
+                                    const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
+                                    const void* packed, int do_inner, float* out, int64_t out_ld,
+                                    int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_pnn_front_f32");
+  if (!arena || !row_off || !ids || !packed || !out || B < 0 || ids_ld < F) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (k != PF_K || F < 2 || F > PF_MAXF) return CTRHOT_ESHAPE;
+  const PfPlan q = pf_plan(F);
+  const int width = F * k + q.P * (do_inner ? 2 : 1);
+  if (out_ld < width || out_ld % 4 != 0 || !aligned16(out) || !aligned16(arena) || !aligned16(packed)) return CTRHOT_ESHAPE;
+  if (B == 0) return CTRHOT_OK;
+  PfParams p;
+  p.arena = arena; p.row_off = row_off; p.ids = ids; p.ids_ld = ids_ld; p.B = B;
+  p.packed = static_cast<const uint8_t*>(packed); p.out = out; p.out_ld = out_ld; p.err_flag = err_flag;
+  p.F = F; p.do_inner = do_inner ? 1 : 0; p.col_inner = F * k; p.col_outer = F * k + (do_inner ? q.P : 0); p.width = width;
+  const size_t smem = pf_smem(F).total + 1024;
+  const int64_t n_tiles = (B + PF_BM - 1) / PF_BM;
+  const int grid = (int)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (ids_kind == CTRHOT_IDS_I32) {
+    CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_front_kernel<CTRHOT_IDS_I32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "pnn_front attr");
+    pnn_front_kernel<CTRHOT_IDS_I32><<<grid, PF_THREADS, smem, st>>>(p);
+  } else {
+    CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_front_kernel<CTRHOT_IDS_F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "pnn_front attr");
+    pnn_front_kernel<CTRHOT_IDS_F32><<<grid, PF_THREADS, smem, st>>>(p);
+  }
+  CTRHOT_LAUNCH_OK("ctrhot_pnn_front_f32");
+  return CTRHOT_OK;
+}

@@ -229,6 +229,26 @@ class OuterProductLayer(Layer):
                   stream_ptr())
         return out
 
+    # ---- the one-launch front of PNN.call (gather -> flat | inner | outer), csrc/pnn_fwd.cu
+    def front_fits(self):
+        return self.built and self.k == 8 and 2 <= self.field_num <= 28
+
+    def front(self, embed_layer, ids, do_inner, out, out_ld):
+        """``out[b] = [rows | <e_i, e_j> | e_j^T W_p e_i | 0]`` straight from the tables (DL/model/pnn.py:28-49)."""
+        pk = getattr(self, "_front_pack", None)
+        if pk is None or pk[0] != self._version:
+            n = _lib.query("ctrhot_pnn_pack_bytes", self.field_num, self.k)
+            buf = torch.empty(n, dtype=torch.uint8, device=self.device)
+            _lib.call("ctrhot_pnn_pack", ptr(self.w), self.field_num, self.k, ptr(buf), stream_ptr())
+            pk = self._front_pack = (self._version, buf)
+        ids, kind, ids_ld = ids_arg(ids)
+        E = embed_layer
+        _lib.call("ctrhot_pnn_front_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ids.shape[0],
+                  ptr(pk[1]), 1 if do_inner else 0, ptr(out), out_ld, ptr(E.err_flag()), stream_ptr())
+        if E.check:
+            E.check_ids()
+        return out
+
 
 class Dice(Layer):
     """``Dice(axis=-1, epsilon=1e-9)`` -- interaction.py:410-425; inference BN (moving stats, no gamma/beta)."""

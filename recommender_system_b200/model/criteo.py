@@ -618,6 +618,7 @@ class PNN(Model):
         if use_fgcnn:
             raise NotImplementedError("FGCNN branch (pnn.py:33-35) is outside the hot path (SURVEY 2.1 C8)")
         self.mode = mode
+        self.fused_front = True          # False: gather / inner / outer as separate launches (the only path for k != 8)
         self.dense_feature_columns, self.sparse_feature_columns = feature_columns
         self.dnn_layer = self.track(DNNLayer(hidden_units, output_dim, activation, dropout, precision=precision,
                                              device=self.device))
@@ -649,6 +650,10 @@ class PNN(Model):
         # every column below `width` is written by the gather / product kernels; only the K padding of the tower's first layer
         # has to be zero (garbage times a zero weight row could be NaN), not the whole [B, ld] buffer
         buf = torch.empty((B, ld), dtype=torch.float32, device=self.device)
+        if self.fused_front and self.mode != "inner" and self.outer_product_layer.front_fits():
+            # gather + both product layers in one launch, the rows never reach HBM as an intermediate (csrc/pnn_fwd.cu)
+            self.outer_product_layer.front(E, ids, self.mode == "both", buf, ld)
+            return self.dnn_layer(buf[:, :self.width], x_ld=ld)
         if ld > self.width:
             buf[:, self.width:].zero_()
         E.gather(ids, out=buf, out_ld=ld)
