@@ -33,8 +33,8 @@ constexpr int PF_THREADS = (PF_NEPI + PF_NGAT + 2) * 32;
 constexpr int PF_WRING = 3;
 constexpr uint32_t PF_PANEL = 16384;
 // packed buffer: header, slot tables, MMA op list, then one 16 KB W tile per chunk
-constexpr int PF_O_IJ = 64, PF_O_P = PF_O_IJ + 2 * PF_MAXSLOT, PF_O_OPS = PF_O_P + 2 * PF_MAXSLOT;
-constexpr int PF_TAB_BYTES = PF_O_OPS + 4 * PF_MAXOPS;   // 2240
+constexpr int PF_O_IJ = 64, PF_O_P = PF_O_IJ + 4 * PF_MAXSLOT, PF_O_OPS = PF_O_P + 2 * PF_MAXSLOT;
+constexpr int PF_TAB_BYTES = PF_O_OPS + 4 * PF_MAXOPS;   // 3072
 constexpr int PF_O_W = 4096;
 
 struct PfPlan { int F, P, nslots, nch, nops, npa; };
@@ -57,7 +57,7 @@ __host__ __device__ inline PfPlan pf_plan(int F) {
 __global__ void pnn_pack_kernel(const float* __restrict__ W, int F, uint8_t* __restrict__ packed) {
   const PfPlan q = pf_plan(F);
   int32_t* hdr = reinterpret_cast<int32_t*>(packed);
-  uint16_t* ij = reinterpret_cast<uint16_t*>(packed + PF_O_IJ);
+  uint32_t* ij = reinterpret_cast<uint32_t*>(packed + PF_O_IJ);   // i << 20 | byte offset of field j in the E tile
   int16_t* sp = reinterpret_cast<int16_t*>(packed + PF_O_P);
   uint32_t* ops = reinterpret_cast<uint32_t*>(packed + PF_O_OPS);
   if (threadIdx.x == 0 && blockIdx.x == 0) {
@@ -66,8 +66,9 @@ __global__ void pnn_pack_kernel(const float* __restrict__ W, int F, uint8_t* __r
     for (int i = 0; i < F - 1; ++i) {
       const int len = F - 1 - i, plen = len + (len & 1);
       for (int t = 0; t < plen; ++t) {
-        if (t < len) { ij[ns + t] = (uint16_t)((i << 8) | (i + 1 + t)); sp[ns + t] = (int16_t)p++; }
-        else { ij[ns + t] = 0xFFFFu; sp[ns + t] = -1; }
+        const int j = (t < len) ? i + 1 + t : i;                 // a padding slot reads field i and stores nothing
+        ij[ns + t] = ((uint32_t)i << 20) | ((uint32_t)(j >> 2) * PF_PANEL + (uint32_t)(j & 3) * 32u);
+        sp[ns + t] = (t < len) ? (int16_t)p++ : (int16_t)-1;
       }
       int s = ns;
       while (s < ns + plen) {
@@ -77,7 +78,7 @@ __global__ void pnn_pack_kernel(const float* __restrict__ W, int F, uint8_t* __r
       }
       ns += plen;
     }
-    for (int t = ns; t < PF_MAXSLOT; ++t) { ij[t] = 0xFFFFu; sp[t] = -1; }
+    for (int t = ns; t < PF_MAXSLOT; ++t) { ij[t] = 0u; sp[t] = -1; }
     for (int t = no; t < PF_MAXOPS; ++t) ops[t] = 0xFFFFFFFFu;
   }
   __syncthreads();
@@ -108,7 +109,7 @@ __host__ __device__ inline PfSmem pf_smem(int F) {
   const uint32_t npan = (uint32_t)(F + 3) / 4;
   m.e = 0; m.lo = npan * PF_PANEL; m.wr = m.lo + 2 * PF_PANEL; m.stg = m.wr + PF_WRING * PF_PANEL;
   m.tab = m.stg + PF_NEPI * 32 * 17 * 4; m.bars = m.tab + ((PF_TAB_BYTES + 15) / 16) * 16;
-  m.total = m.bars + 192;
+  m.total = m.bars + 192 + 8 * (PF_MAXF + 4);
   return m;
 }
 
@@ -134,7 +135,7 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
   const uint32_t slot_addr = bars + 128u;
   volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(bp + mp.bars + 128);
   const int32_t* hdr = reinterpret_cast<const int32_t*>(bp + mp.tab);
-  const uint16_t* t_ij = reinterpret_cast<const uint16_t*>(bp + mp.tab + PF_O_IJ);
+  const uint32_t* t_sl = reinterpret_cast<const uint32_t*>(bp + mp.tab + PF_O_IJ);
   const int16_t* t_p = reinterpret_cast<const int16_t*>(bp + mp.tab + PF_O_P);
   const uint32_t* t_ops = reinterpret_cast<const uint32_t*>(bp + mp.tab + PF_O_OPS);
 
@@ -147,6 +148,8 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
   }
   for (int i = tid; i < PF_TAB_BYTES / 4; i += PF_THREADS)
     reinterpret_cast<uint32_t*>(bp + mp.tab)[i] = __ldg(reinterpret_cast<const uint32_t*>(p.packed) + i);
+  int64_t* s_off = reinterpret_cast<int64_t*>(bp + mp.bars + 192);
+  for (int i = tid; i <= PF_MAXF; i += PF_THREADS) s_off[i] = (i <= F) ? __ldg(p.row_off + i) : 0;
   if (warp == PF_NEPI + PF_NGAT) { tmem_alloc(slot_addr, 512u); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
@@ -161,12 +164,18 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
     const int q = warp & 3, h = warp >> 2;
     const uint32_t row = (uint32_t)(q * 32 + lane);
     float* stg = reinterpret_cast<float*>(bp + mp.stg) + warp * 32 * 17;
+    const uint8_t* erow = bp + mp.e + row * 128u;                  // this row in panel 0; a field's bytes are at (offset ^ r7)
+    const uint32_t r7 = (row & 7u) << 4;
+    const float* srd = stg + (lane >> 4) * 17 + (lane & 15);       // transposed read: rows 2 r2 + (lane >> 4), column lane & 15
     uint32_t dc = 0;
 #pragma unroll 1
     for (int64_t it = 0; it < my_tiles; ++it) {
       const int64_t b0 = (blockIdx.x + it * gridDim.x) * PF_BM;
+      const int64_t rem = p.B - (b0 + q * 32);
+      const int nrow = rem > 32 ? 32 : (int)rem;                   // rows of this warp that exist (may be <= 0)
+      float* orow = p.out + (b0 + q * 32 + (lane >> 4)) * p.out_ld;
       mbar_wait(e_full, (uint32_t)(it & 1));
-      int cur_i = -1;
+      uint32_t cur_i = 0xFFFFFFFFu;
       float ei[PF_K];
 #pragma unroll
       for (int a = 0; a < PF_K; ++a) ei[a] = 0.f;
@@ -177,52 +186,51 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
         tc_fence_after();
         float vo[16], vi[16];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float d[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)h * 128u + (uint32_t)g * 32u, d);
+        for (int g = 0; g < 8; ++g) {
+          float d[16];
+          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)h * 128u + (uint32_t)g * 16u, d);
 #pragma unroll
-          for (int s = 0; s < 4; ++s) {
-            const int slot = c * 32 + h * 16 + g * 4 + s;
-            const uint32_t ij = t_ij[slot];
-            float o = 0.f, n = 0.f;
-            if (ij != 0xFFFFu) {
-              const int i = (int)(ij >> 8), j = (int)(ij & 255u);
-              if (i != cur_i) {
-                const uint8_t* pi = bp + mp.e + (uint32_t)(i >> 2) * PF_PANEL;
-                const float4 x0 = *reinterpret_cast<const float4*>(pi + sw128_offset(row, (uint32_t)(i & 3) * 2));
-                const float4 x1 = *reinterpret_cast<const float4*>(pi + sw128_offset(row, (uint32_t)(i & 3) * 2 + 1));
-                ei[0] = x0.x; ei[1] = x0.y; ei[2] = x0.z; ei[3] = x0.w; ei[4] = x1.x; ei[5] = x1.y; ei[6] = x1.z; ei[7] = x1.w;
-                cur_i = i;
-              }
-              const uint8_t* pj = bp + mp.e + (uint32_t)(j >> 2) * PF_PANEL;
-              const float4 y0 = *reinterpret_cast<const float4*>(pj + sw128_offset(row, (uint32_t)(j & 3) * 2));
-              const float4 y1 = *reinterpret_cast<const float4*>(pj + sw128_offset(row, (uint32_t)(j & 3) * 2 + 1));
-              const float ej[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
-#pragma unroll
-              for (int a = 0; a < PF_K; ++a) { o = fmaf(d[s * 8 + a], ej[a], o); n = fmaf(ei[a], ej[a], n); }
+          for (int s = 0; s < 2; ++s) {
+            const uint32_t sw = t_sl[c * 32 + h * 16 + g * 2 + s];           // warp-uniform: i << 20 | byte offset of field j
+            if ((sw >> 20) != cur_i) {
+              cur_i = sw >> 20;
+              const uint32_t oi = (((cur_i >> 2) * PF_PANEL) | ((cur_i & 3u) * 32u)) ^ r7;
+              const float4 x0 = *reinterpret_cast<const float4*>(erow + oi);
+              const float4 x1 = *reinterpret_cast<const float4*>(erow + (oi ^ 16u));
+              ei[0] = x0.x; ei[1] = x0.y; ei[2] = x0.z; ei[3] = x0.w; ei[4] = x1.x; ei[5] = x1.y; ei[6] = x1.z; ei[7] = x1.w;
             }
-            vo[g * 4 + s] = o; vi[g * 4 + s] = n;
+            const uint32_t oj = (sw & 0xFFFFFu) ^ r7;
+            const float4 y0 = *reinterpret_cast<const float4*>(erow + oj);
+            const float4 y1 = *reinterpret_cast<const float4*>(erow + (oj ^ 16u));
+            const float ej[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+            float o = 0.f, n = 0.f;
+#pragma unroll
+            for (int a = 0; a < PF_K; ++a) { o = fmaf(d[s * 8 + a], ej[a], o); n = fmaf(ei[a], ej[a], n); }
+            vo[g * 2 + s] = o; vi[g * 2 + s] = n;
           }
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(d_free(buf));
-        // transpose through the warp's buffer: lanes = 2 rows x 16 consecutive pair columns per store
-        const int sl = c * 32 + h * 16 + (lane & 15);
-        const int pcol = t_p[sl];
+        // transpose through the warp's buffer: one store = 2 rows x 16 consecutive pair columns (padding slots have no column)
+        const int pcol = t_p[c * 32 + h * 16 + (lane & 15)];
 #pragma unroll 1
         for (int pass = p.do_inner ? 0 : 1; pass < 2; ++pass) {
           __syncwarp();
 #pragma unroll
           for (int s = 0; s < 16; ++s) stg[lane * 17 + s] = pass ? vo[s] : vi[s];
           __syncwarp();
-          const int colb = pass ? p.col_outer : p.col_inner;
-          if (pcol >= 0) {
-#pragma unroll 4
-            for (int r2 = 0; r2 < 16; ++r2) {
-              const int r = 2 * r2 + (lane >> 4);
-              const int64_t b = b0 + q * 32 + r;
-              if (b < p.B) p.out[b * p.out_ld + colb + pcol] = stg[r * 17 + (lane & 15)];
+          float* op = orow + (pass ? p.col_outer : p.col_inner) + pcol;
+          const int lim = (pcol >= 0) ? nrow - (lane >> 4) : 0;               // row 2 r2 + (lane >> 4) exists iff 2 r2 < lim
+#pragma unroll
+          for (int r0 = 0; r0 < 16; r0 += 8) {
+            float v[8];
+#pragma unroll
+            for (int r2 = 0; r2 < 8; ++r2) v[r2] = srd[(r0 + r2) * 34];
+#pragma unroll
+            for (int r2 = 0; r2 < 8; ++r2) {
+              if (2 * (r0 + r2) < lim) *op = v[r2];
+              op += 2 * p.out_ld;
             }
           }
         }
@@ -235,48 +243,47 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
     const int gt = tid - PF_NEPI * 32, gw = warp - PF_NEPI;
     const int npan = (F + 3) / 4;
     uint32_t lp = 0;                                               // Al panel sequence number (buffer lp & 1)
+    // this row's F ids, fetched one tile AHEAD (all loads in flight at once): -1 = out of range / no such row
+    int32_t rid[PF_MAXF];
+    auto load_ids = [&](int64_t it) {
+      const int64_t b = (blockIdx.x + it * gridDim.x) * PF_BM + gt;
+      const bool live = it < my_tiles && b < p.B;
+#pragma unroll
+      for (int f = 0; f < PF_MAXF; ++f) {
+        int64_t v = (live && f < F) ? IdLoad<IDKIND>::at(p.ids, b * p.ids_ld + f) : 0;
+        rid[f] = (v < 0 || v > 0x7FFFFFFF) ? -1 : (int32_t)v;
+      }
+    };
+    load_ids(0);
 #pragma unroll 1
     for (int64_t it = 0; it < my_tiles; ++it) {
       const int64_t b0 = (blockIdx.x + it * gridDim.x) * PF_BM;
       if (it > 0) mbar_wait(e_free, (uint32_t)((it - 1) & 1));
-      const int64_t b = b0 + gt;
-      const bool live = b < p.B;
-#pragma unroll 1
-      for (int f = 0; f < 4 * npan; ++f) {
-        const float* src = p.arena;
-        uint32_t nb = 0;
-        if (live && f < F) {
-          const int64_t id = IdLoad<IDKIND>::at(p.ids, b * p.ids_ld + f);
-          const int64_t r0 = __ldg(p.row_off + f), r1 = __ldg(p.row_off + f + 1);
-          if (id >= 0 && id < r1 - r0) { src = p.arena + (r0 + id) * PF_K; nb = 16; }
-          else if (p.err_flag) *p.err_flag = 1;
+      const bool live = b0 + gt < p.B;
+#pragma unroll
+      for (int f = 0; f < PF_MAXF; ++f) {
+        if (f < 4 * npan) {
+          const float* src = p.arena;
+          uint32_t nb = 0;
+          if (live && f < F) {
+            const int64_t r0 = s_off[f], r1 = s_off[f + 1];
+            if (rid[f] >= 0 && rid[f] < r1 - r0) { src = p.arena + (r0 + rid[f]) * PF_K; nb = 16; }
+            else if (p.err_flag) *p.err_flag = 1;
+          }
+          const uint32_t dst = base + mp.e + (uint32_t)(f >> 2) * PF_PANEL;
+          cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2), src, nb);
+          cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2 + 1), src + 4, nb);
         }
-        const uint32_t dst = base + mp.e + (uint32_t)(f >> 2) * PF_PANEL;
-        cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2), src, nb);
-        cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2 + 1), src + 4, nb);
       }
+      load_ids(it + 1);
       cp_async_commit();
       cp_async_wait<0>();
       fence_proxy_async_smem();
       mbar_arrive(e_full);
       named_bar_sync(1, PF_NGAT * 32);
-      // flat columns [0, F k) and the zero padding [width, out_ld): coalesced 16-byte stores, rows of this warp
-#pragma unroll 1
-      for (int r = gw * 32; r < gw * 32 + 32; ++r) {
-        const int64_t br = b0 + r;
-        if (br >= p.B) break;
-        float* orow = p.out + br * p.out_ld;
-        for (int l = lane; l < 2 * F; l += 32) {
-          const int f = l >> 1;
-          const float4 v = *reinterpret_cast<const float4*>(bp + mp.e + (uint32_t)(f >> 2) * PF_PANEL +
-                                                            sw128_offset((uint32_t)r, (uint32_t)(f & 3) * 2 + (l & 1)));
-          *reinterpret_cast<float4*>(orow + 4 * l) = v;
-        }
-        for (int l = p.width + lane; l < p.out_ld; l += 32) orow[l] = 0.f;
-      }
-      // Al = tf32(x - trunc_tf32(x)) for the panels that hold a run's field i, two panels ahead of the MMAs at most
-#pragma unroll 1
-      for (int m = 0; m < npa; ++m, ++lp) {
+      // Al = tf32(x - trunc_tf32(x)) for the panels that hold a run's field i (at most two ahead of the MMAs); the first two
+      // are on the critical path of the tile and go before the flat columns
+      auto build_lo = [&](int m) {
         const uint32_t bf = lp & 1u;
         mbar_wait(lo_free(bf), ((lp >> 1) & 1u) ^ 1u);
         const float4* s4 = reinterpret_cast<const float4*>(bp + mp.e + (uint32_t)m * PF_PANEL);
@@ -292,7 +299,27 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
         }
         fence_proxy_async_smem();
         mbar_arrive(lo_full(bf));
+        ++lp;
+      };
+      const int n_first = npa < 2 ? npa : 2;
+#pragma unroll 1
+      for (int m = 0; m < n_first; ++m) build_lo(m);
+      // flat columns [0, F k) and the zero padding [width, out_ld): coalesced 16-byte stores, rows of this warp
+#pragma unroll 1
+      for (int r = gw * 32; r < gw * 32 + 32; ++r) {
+        const int64_t br = b0 + r;
+        if (br >= p.B) break;
+        float* orow = p.out + br * p.out_ld;
+        for (int l = lane; l < 2 * F; l += 32) {
+          const int f = l >> 1;
+          const float4 v = *reinterpret_cast<const float4*>(bp + mp.e + (uint32_t)(f >> 2) * PF_PANEL +
+                                                            sw128_offset((uint32_t)r, (uint32_t)(f & 3) * 2 + (l & 1)));
+          *reinterpret_cast<float4*>(orow + 4 * l) = v;
+        }
+        for (int l = p.width + lane; l < p.out_ld; l += 32) orow[l] = 0.f;
       }
+#pragma unroll 1
+      for (int m = n_first; m < npa; ++m) build_lo(m);
     }
   } else if (warp == PF_NEPI + PF_NGAT) {
     // ================================================================ MMA issuer (converged warp, one elected lane issues)
