@@ -249,6 +249,43 @@ def secondary(dev, rank):
                      "tensor_TFLOPs": flops * B / ms / 1e9, "tensor_frac": flops * B / ms / 1e9 / (pk["tf"] / 2),
                      "hbm_frac": algo * B / ms / 1e6 / pk["hbm_gbs"]}
         del mm
+    # PNN (DL/model/pnn.py, the reference's embed_dim = 8, mode "both", tower 256-128-64): the one-launch front
+    # (csrc/pnn_fwd.cu: gather -> flat | inner | outer, rows in shared memory, the outer product's inner sum on tcgen05)
+    # against the same three steps as separate launches, and the whole model
+    from recommender_system_b200.model.criteo import PNN
+    set_seed(1)
+    pm = PNN(synth.criteo_feature_columns(synth.KAGGLE_VOCAB, 8), "both", [256, 128, 64], 1, embed_dim=8, precision="tf32",
+             check_ids=False, device=dev)
+    pm.build(None)
+    Ep, OPl, IPl = pm.embed_layer, pm.outer_product_layer, pm.inner_product_layer
+    Fp, Pp = Ep.F, Ep.F * (Ep.F - 1) // 2
+    wd = Fp * 8 + 2 * Pp
+    pld = (wd + 31) // 32 * 32
+    pbuf = torch.empty((B, pld), dtype=torch.float32, device=dev)
+    pids = [c[1] for c in cins]
+
+    def pnn_front():
+        OPl.front(Ep, pids[it[0] % 4], True, pbuf, pld); it[0] += 1
+
+    def pnn_separate():
+        Ep.gather(pids[it[0] % 4], out=pbuf, out_ld=pld); it[0] += 1
+        zz = pbuf.as_strided((B, Fp, 8), (pld, 8, 1))
+        IPl(zz, out=pbuf[:, Fp * 8:Fp * 8 + Pp])
+        OPl(zz, out=pbuf[:, Fp * 8 + Pp:wd])
+
+    def pnn_model():
+        pm(cins[it[0] % 4]); it[0] += 1
+    ms_f, ms_s = timeit(pnn_front, 30, 5), timeit(pnn_separate, 20, 3)
+    l0 = _lib.LAUNCHES[0]
+    ms_m = timeit(pnn_model, 30, 5)
+    palgo = Fp * 4 + Fp * 8 * 4 + wd * 4                      # ids + rows read + product vector written, per sample
+    out["pnn_k8_both"] = {"metric": "PNN forward samples/s (embed_dim 8, inner + outer products, tower 256-128-64)",
+                          "value": B / ms_m * 1e3, "ms_per_step": ms_m, "batch": B,
+                          "launches_per_step": (_lib.LAUNCHES[0] - l0) / 35.0,
+                          "front_ms_one_launch": ms_f, "front_ms_separate_launches": ms_s,
+                          "front_hbm_frac": palgo * B / ms_f / 1e6 / pk["hbm_gbs"],
+                          "outer_product_TFLOPs_fp32_equiv": 2 * Pp * 64 * B / ms_f / 1e9}
+    del pm, pbuf
     out["deepfm_train"] = train_leg(dev, timeit)
     return out
 

@@ -11,11 +11,18 @@
 // outer sum  sum_a D[b, (slot, a)] e_j[b, a]  plus the inner product <e_i, e_j> run in the epilogue warps on TMEM lanes = rows.
 //
 // shared memory (k = 8, F <= 28):  E tile  ceil(F/4) panels of [128 rows x 128 B] (4 fields per 128-byte row, 128-byte
-// swizzle: field f is k-slice f % 4 of panel f / 4), two Al panels, a 3-deep ring of 16 KB W tiles (one 256-column chunk:
+// swizzle: field f is k-slice f % 4 of panel f / 4), two Al panels, a 2-deep ring of 16 KB W tiles (one 256-column chunk:
 // k-slices {hi, lo} x {columns 0..127, 128..255}), per-warp transpose buffers for coalesced stores.
 // TMEM: two 256-column accumulators (MMA of chunk c + 1 under the epilogue of chunk c).
+//
+// Measured (B = 65 536, F = 26, one B200): 0.157 ms inner + outer, 0.130 ms outer only -- against 0.665 / 0.610 ms for gather +
+// InnerProductLayer + OuterProductLayer as separate launches.  What bounds it (profiles/r02_pnn_front.md): the epilogue warps
+// (two per scheduler) run ~1 000 dependent instructions per 16 pair slots -- table word -> row of field j from shared memory ->
+// 16 FMA -> transpose -> store -- at ~0.3 IPC; removing the global stores, the TMEM loads or the transposes each moves the
+// time by < 20 %, the tensor pipe is 5 % busy and HBM traffic (256 MB) would take 40 us.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -30,7 +37,7 @@ constexpr int PF_MAXSLOT = 416;                 // 13 chunks of 32 pair slots
 constexpr int PF_MAXOPS = 128;
 constexpr int PF_NEPI = 8, PF_NGAT = 4;         // epilogue warps 0-7, gather/builder warps 8-11, MMA 12, W producer 13
 constexpr int PF_THREADS = (PF_NEPI + PF_NGAT + 2) * 32;
-constexpr int PF_WRING = 3;
+constexpr int PF_WRING = 2;
 constexpr uint32_t PF_PANEL = 16384;
 // packed buffer: header, slot tables, MMA op list, then one 16 KB W tile per chunk
 constexpr int PF_O_IJ = 64, PF_O_P = PF_O_IJ + 4 * PF_MAXSLOT, PF_O_OPS = PF_O_P + 2 * PF_MAXSLOT;
@@ -62,9 +69,16 @@ __global__ void pnn_pack_kernel(const float* __restrict__ W, int F, uint8_t* __r
   uint32_t* ops = reinterpret_cast<uint32_t*>(packed + PF_O_OPS);
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     hdr[0] = F; hdr[1] = q.P; hdr[2] = q.nslots; hdr[3] = q.nch; hdr[4] = q.nops; hdr[5] = q.npa;
+    // bytes 32..47: per chunk, the E panels no later chunk reads (panel m: fields 4m..4m+3 are last used by run 4m+3, the
+    // panel of field F-1 by the last run) -- the epilogue frees them for the next tile's gather as it goes
+    uint8_t* cf = packed + 32;
+    for (int c = 0; c < 16; ++c) cf[c] = 0;
+    const int npan = (F + 3) / 4;
     int ns = 0, no = 0, p = 0;
     for (int i = 0; i < F - 1; ++i) {
       const int len = F - 1 - i, plen = len + (len & 1);
+      for (int m = 0; m < npan; ++m)
+        if (i == ((m == npan - 1) ? F - 2 : 4 * m + 3)) cf[(ns + plen - 1) / 32] |= (uint8_t)(1u << m);
       for (int t = 0; t < plen; ++t) {
         const int j = (t < len) ? i + 1 + t : i;                 // a padding slot reads field i and stores nothing
         ij[ns + t] = ((uint32_t)i << 20) | ((uint32_t)(j >> 2) * PF_PANEL + (uint32_t)(j & 3) * 32u);
@@ -108,12 +122,20 @@ __host__ __device__ inline PfSmem pf_smem(int F) {
   PfSmem m;
   const uint32_t npan = (uint32_t)(F + 3) / 4;
   m.e = 0; m.lo = npan * PF_PANEL; m.wr = m.lo + 2 * PF_PANEL; m.stg = m.wr + PF_WRING * PF_PANEL;
-  m.tab = m.stg + PF_NEPI * 32 * 17 * 4; m.bars = m.tab + ((PF_TAB_BYTES + 15) / 16) * 16;
+  m.tab = m.stg + PF_NEPI * 2 * 32 * 17 * 4; m.bars = m.tab + ((PF_TAB_BYTES + 15) / 16) * 16;
   m.total = m.bars + 192 + 8 * (PF_MAXF + 4);
   return m;
 }
 
-template <int IDKIND>
+#ifdef PF_TRACE
+#define PF_T0() long long _t = clock64()
+#define PF_ACC(k) do { long long _n = clock64(); tr[k] += _n - _t; _t = _n; } while (0)
+#else
+#define PF_T0() do { } while (0)
+#define PF_ACC(k) do { } while (0)
+#endif
+
+template <int IDKIND, bool INNER>
 __global__ void __launch_bounds__(PF_THREADS, 1)
 pnn_front_kernel(const __grid_constant__ PfParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -125,7 +147,8 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const uint32_t bars = base + mp.bars;
-  const uint32_t e_full = bars, e_free = bars + 8;
+  const uint32_t e_full = bars;
+  auto p_free = [&](int i) { return bars + 136u + 8u * i; };      // E panel i is dead for this tile (8 epilogue warps)
   auto lo_full = [&](int i) { return bars + 16u + 8u * i; };
   auto lo_free = [&](int i) { return bars + 32u + 8u * i; };
   auto w_full = [&](int i) { return bars + 48u + 8u * i; };
@@ -135,12 +158,14 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
   const uint32_t slot_addr = bars + 128u;
   volatile uint32_t* slot_ptr = reinterpret_cast<volatile uint32_t*>(bp + mp.bars + 128);
   const int32_t* hdr = reinterpret_cast<const int32_t*>(bp + mp.tab);
+  const uint8_t* t_cf = bp + mp.tab + 32;
   const uint32_t* t_sl = reinterpret_cast<const uint32_t*>(bp + mp.tab + PF_O_IJ);
   const int16_t* t_p = reinterpret_cast<const int16_t*>(bp + mp.tab + PF_O_P);
   const uint32_t* t_ops = reinterpret_cast<const uint32_t*>(bp + mp.tab + PF_O_OPS);
 
   if (tid == 0) {
-    mbar_init(e_full, PF_NGAT * 32); mbar_init(e_free, PF_NEPI);
+    mbar_init(e_full, PF_NGAT * 32);
+    for (int i = 0; i < 7; ++i) mbar_init(p_free(i), PF_NEPI);
     for (int i = 0; i < 2; ++i) { mbar_init(lo_full(i), PF_NGAT * 32); mbar_init(lo_free(i), 1); }
     for (int i = 0; i < PF_WRING; ++i) { mbar_init(w_full(i), 1); mbar_init(w_free(i), 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(d_full(i), 1); mbar_init(d_free(i), PF_NEPI); }
@@ -159,14 +184,20 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
   const int64_t n_tiles = (p.B + PF_BM - 1) / PF_BM;
   const int64_t my_tiles = (n_tiles > blockIdx.x) ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
+#ifdef PF_TRACE
+  long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const long long t_start = clock64();
+#endif
   if (warp < PF_NEPI) {
     // ================================================================ epilogue: lanes = rows, warp = (lane quarter, column half)
     const int q = warp & 3, h = warp >> 2;
     const uint32_t row = (uint32_t)(q * 32 + lane);
-    float* stg = reinterpret_cast<float*>(bp + mp.stg) + warp * 32 * 17;
+    float* so = reinterpret_cast<float*>(bp + mp.stg) + warp * 2 * 32 * 17;   // outer values [row][17], then the inner ones
+    float* si = so + 32 * 17;
     const uint8_t* erow = bp + mp.e + row * 128u;                  // this row in panel 0; a field's bytes are at (offset ^ r7)
     const uint32_t r7 = (row & 7u) << 4;
-    const float* srd = stg + (lane >> 4) * 17 + (lane & 15);       // transposed read: rows 2 r2 + (lane >> 4), column lane & 15
+    const uint32_t erow_a = base + mp.e + row * 128u;
+    const int rd = (lane >> 4) * 17 + (lane & 15);                 // transposed read: rows 2 r2 + (lane >> 4), column lane & 15
     uint32_t dc = 0;
 #pragma unroll 1
     for (int64_t it = 0; it < my_tiles; ++it) {
@@ -174,7 +205,9 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
       const int64_t rem = p.B - (b0 + q * 32);
       const int nrow = rem > 32 ? 32 : (int)rem;                   // rows of this warp that exist (may be <= 0)
       float* orow = p.out + (b0 + q * 32 + (lane >> 4)) * p.out_ld;
+      PF_T0();
       mbar_wait(e_full, (uint32_t)(it & 1));
+      PF_ACC(0);
       uint32_t cur_i = 0xFFFFFFFFu;
       float ei[PF_K];
 #pragma unroll
@@ -184,59 +217,92 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
         const uint32_t buf = dc & 1u;
         mbar_wait(d_full(buf), (dc >> 1) & 1u);
         tc_fence_after();
-        float vo[16], vi[16];
+        PF_ACC(1);
+        // 16 columns (two pair slots) per TMEM load, the next load in flight under the FMAs of the current one
+        const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)h * 128u;
+        uint32_t dA[16], dB[16];
+        tmem_ld16_issue(tcol, dA);
+        tmem_ld16_wait(dA);
+        // the 16 slot words of this half chunk (warp-uniform) and the rows of field j, one slot AHEAD of its FMAs;
+        // straight-line code on purpose: the loads of later slots are scheduled under the FMAs of earlier ones
+        uint32_t swv[16];
+        {
+          const uint4* t4 = reinterpret_cast<const uint4*>(t_sl + c * 32 + h * 16);
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          float d[16];
-          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)h * 128u + (uint32_t)g * 16u, d);
-#pragma unroll
-          for (int s = 0; s < 2; ++s) {
-            const uint32_t sw = t_sl[c * 32 + h * 16 + g * 2 + s];           // warp-uniform: i << 20 | byte offset of field j
-            if ((sw >> 20) != cur_i) {
-              cur_i = sw >> 20;
-              const uint32_t oi = (((cur_i >> 2) * PF_PANEL) | ((cur_i & 3u) * 32u)) ^ r7;
-              const float4 x0 = *reinterpret_cast<const float4*>(erow + oi);
-              const float4 x1 = *reinterpret_cast<const float4*>(erow + (oi ^ 16u));
-              ei[0] = x0.x; ei[1] = x0.y; ei[2] = x0.z; ei[3] = x0.w; ei[4] = x1.x; ei[5] = x1.y; ei[6] = x1.z; ei[7] = x1.w;
-            }
-            const uint32_t oj = (sw & 0xFFFFFu) ^ r7;
-            const float4 y0 = *reinterpret_cast<const float4*>(erow + oj);
-            const float4 y1 = *reinterpret_cast<const float4*>(erow + (oj ^ 16u));
-            const float ej[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
-            float o = 0.f, n = 0.f;
-#pragma unroll
-            for (int a = 0; a < PF_K; ++a) { o = fmaf(d[s * 8 + a], ej[a], o); n = fmaf(ei[a], ej[a], n); }
-            vo[g * 2 + s] = o; vi[g * 2 + s] = n;
+          for (int u = 0; u < 4; ++u) { const uint4 t = t4[u]; swv[4 * u] = t.x; swv[4 * u + 1] = t.y; swv[4 * u + 2] = t.z; swv[4 * u + 3] = t.w; }
+        }
+        float4 yA0, yA1, yB0, yB1;
+        {
+          const uint32_t oj = (swv[0] & 0xFFFFFu) ^ r7;
+          yA0 = *reinterpret_cast<const float4*>(erow + oj); yA1 = *reinterpret_cast<const float4*>(erow + (oj ^ 16u));
+        }
+        auto one_slot = [&](const uint32_t* d, int sl, const float4& y0, const float4& y1, float4& n0, float4& n1) {
+          if (sl + 1 < 16) {
+            const uint32_t oj = (swv[sl + 1] & 0xFFFFFu) ^ r7;
+            n0 = *reinterpret_cast<const float4*>(erow + oj); n1 = *reinterpret_cast<const float4*>(erow + (oj ^ 16u));
           }
+          if (INNER) {                                                        // a new run: its field i (predicated, no branch)
+            const uint32_t ni = swv[sl] >> 20;
+            const uint32_t oi = (((ni >> 2) * PF_PANEL) | ((ni & 3u) * 32u)) ^ r7;
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %8, %9;\n\t"
+                         "@p ld.shared.v4.f32 {%0,%1,%2,%3}, [%10];\n\t@p ld.shared.v4.f32 {%4,%5,%6,%7}, [%11];\n\t}"
+                         : "+f"(ei[0]), "+f"(ei[1]), "+f"(ei[2]), "+f"(ei[3]), "+f"(ei[4]), "+f"(ei[5]), "+f"(ei[6]), "+f"(ei[7])
+                         : "r"(ni), "r"(cur_i), "r"(erow_a + oi), "r"(erow_a + (oi ^ 16u)));
+            cur_i = ni;
+          }
+          const float ej[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+          float o = 0.f, n = 0.f;
+#pragma unroll
+          for (int a = 0; a < PF_K; ++a) {
+            o = fmaf(__uint_as_float(d[a]), ej[a], o);
+            if (INNER) n = fmaf(ei[a], ej[a], n);
+          }
+          so[lane * 17 + sl] = o;
+          if (INNER) si[lane * 17 + sl] = n;
+        };
+        auto two_slots = [&](const uint32_t (&d)[16], int g) {
+          one_slot(d, 2 * g, yA0, yA1, yB0, yB1);
+          one_slot(d + 8, 2 * g + 1, yB0, yB1, yA0, yA1);
+        };
+#pragma unroll
+        for (int g = 0; g < 8; g += 2) {
+          tmem_ld16_issue(tcol + (uint32_t)(g + 1) * 16u, dB);
+          two_slots(dA, g);
+          tmem_ld16_wait(dB);
+          if (g + 2 < 8) tmem_ld16_issue(tcol + (uint32_t)(g + 2) * 16u, dA);
+          two_slots(dB, g + 1);
+          if (g + 2 < 8) tmem_ld16_wait(dA);
         }
         tc_fence_before();
         __syncwarp();
+        PF_ACC(2);
         if (lane == 0) mbar_arrive(d_free(buf));
-        // transpose through the warp's buffer: one store = 2 rows x 16 consecutive pair columns (padding slots have no column)
+        // transposed write-out: one store = 2 rows x 16 consecutive pair columns (padding slots have no column)
         const int pcol = t_p[c * 32 + h * 16 + (lane & 15)];
-#pragma unroll 1
-        for (int pass = p.do_inner ? 0 : 1; pass < 2; ++pass) {
-          __syncwarp();
+        const int lim = (pcol >= 0) ? nrow - (lane >> 4) : 0;                 // row 2 r2 + (lane >> 4) exists iff 2 r2 < lim
+        const int64_t ld2 = 2 * p.out_ld;
 #pragma unroll
-          for (int s = 0; s < 16; ++s) stg[lane * 17 + s] = pass ? vo[s] : vi[s];
-          __syncwarp();
+        for (int pass = INNER ? 0 : 1; pass < 2; ++pass) {
+          const float* src = (pass ? so : si) + rd;
           float* op = orow + (pass ? p.col_outer : p.col_inner) + pcol;
-          const int lim = (pcol >= 0) ? nrow - (lane >> 4) : 0;               // row 2 r2 + (lane >> 4) exists iff 2 r2 < lim
 #pragma unroll
           for (int r0 = 0; r0 < 16; r0 += 8) {
             float v[8];
 #pragma unroll
-            for (int r2 = 0; r2 < 8; ++r2) v[r2] = srd[(r0 + r2) * 34];
+            for (int r2 = 0; r2 < 8; ++r2) v[r2] = src[(r0 + r2) * 34];
 #pragma unroll
             for (int r2 = 0; r2 < 8; ++r2) {
-              if (2 * (r0 + r2) < lim) *op = v[r2];
-              op += 2 * p.out_ld;
+              if (2 * (r0 + r2) < lim) asm volatile("st.global.f32 [%0], %1;" :: "l"(op), "f"(v[r2]) : "memory");
+              op += ld2;
             }
           }
         }
+        __syncwarp();
+        PF_ACC(3);
+        if (lane == 0) {
+          for (uint32_t fm = t_cf[c]; fm; fm &= fm - 1) mbar_arrive(p_free(__ffs((int)fm) - 1));
+        }
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(e_free);
     }
   } else if (warp < PF_NEPI + PF_NGAT) {
     // ================================================================ gather (thread = row) + flat columns + Al panels
@@ -258,11 +324,12 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
 #pragma unroll 1
     for (int64_t it = 0; it < my_tiles; ++it) {
       const int64_t b0 = (blockIdx.x + it * gridDim.x) * PF_BM;
-      if (it > 0) mbar_wait(e_free, (uint32_t)((it - 1) & 1));
+      PF_T0();
       const bool live = b0 + gt < p.B;
 #pragma unroll
       for (int f = 0; f < PF_MAXF; ++f) {
         if (f < 4 * npan) {
+          if ((f & 3) == 0 && it > 0) mbar_wait(p_free(f >> 2), (uint32_t)((it - 1) & 1));
           const float* src = p.arena;
           uint32_t nb = 0;
           if (live && f < F) {
@@ -275,9 +342,11 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
           cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2 + 1), src + 4, nb);
         }
       }
+      PF_ACC(0);
       load_ids(it + 1);
       cp_async_commit();
       cp_async_wait<0>();
+      PF_ACC(1);
       fence_proxy_async_smem();
       mbar_arrive(e_full);
       named_bar_sync(1, PF_NGAT * 32);
@@ -303,37 +372,51 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
       };
       const int n_first = npa < 2 ? npa : 2;
 #pragma unroll 1
+      PF_ACC(2);
       for (int m = 0; m < n_first; ++m) build_lo(m);
+      PF_ACC(3);
       // flat columns [0, F k) and the zero padding [width, out_ld): coalesced 16-byte stores, rows of this warp
-#pragma unroll 1
-      for (int r = gw * 32; r < gw * 32 + 32; ++r) {
-        const int64_t br = b0 + r;
-        if (br >= p.B) break;
-        float* orow = p.out + br * p.out_ld;
-        for (int l = lane; l < 2 * F; l += 32) {
-          const int f = l >> 1;
-          const float4 v = *reinterpret_cast<const float4*>(bp + mp.e + (uint32_t)(f >> 2) * PF_PANEL +
-                                                            sw128_offset((uint32_t)r, (uint32_t)(f & 3) * 2 + (l & 1)));
-          *reinterpret_cast<float4*>(orow + 4 * l) = v;
+      {
+        const int64_t remr = p.B - (b0 + gw * 32);
+        const int nr = remr > 32 ? 32 : (int)remr;
+        const int l1 = lane + 32;                                          // second 16-byte piece of the row, if 2 F > 32
+        const uint32_t o0 = (uint32_t)(lane >> 3) * PF_PANEL, c0 = (uint32_t)(lane & 7);
+        const uint32_t o1 = (uint32_t)(l1 >> 3) * PF_PANEL, c1 = (uint32_t)(l1 & 7);
+        const bool h0 = lane < 2 * F, h1 = l1 < 2 * F;
+#pragma unroll 4
+        for (int r = 0; r < nr; ++r) {
+          const uint32_t rr = (uint32_t)(gw * 32 + r);
+          float* orow = p.out + (b0 + rr) * p.out_ld;
+          const uint8_t* er = bp + mp.e + rr * 128u;
+          float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+          if (h0) v0 = *reinterpret_cast<const float4*>(er + o0 + ((c0 ^ (rr & 7u)) << 4));
+          if (h1) v1 = *reinterpret_cast<const float4*>(er + o1 + ((c1 ^ (rr & 7u)) << 4));
+          if (h0) *reinterpret_cast<float4*>(orow + 4 * lane) = v0;
+          if (h1) *reinterpret_cast<float4*>(orow + 4 * l1) = v1;
+          for (int l = p.width + lane; l < p.out_ld; l += 32) orow[l] = 0.f;
         }
-        for (int l = p.width + lane; l < p.out_ld; l += 32) orow[l] = 0.f;
       }
-#pragma unroll 1
+      PF_ACC(4);
       for (int m = n_first; m < npa; ++m) build_lo(m);
+      PF_ACC(5);
     }
   } else if (warp == PF_NEPI + PF_NGAT) {
     // ================================================================ MMA issuer (converged warp, one elected lane issues)
     uint32_t wc = 0, dc = 0, lp = 0;
 #pragma unroll 1
     for (int64_t it = 0; it < my_tiles; ++it) {
+      PF_T0();
       mbar_wait(e_full, (uint32_t)(it & 1));
+      PF_ACC(0);
       int cur_pan = -1, oi = 0;
 #pragma unroll 1
       for (int c = 0; c < nch; ++c, ++wc, ++dc) {
         const uint32_t st = wc % PF_WRING, buf = dc & 1u;
         mbar_wait(w_full(st), (wc / PF_WRING) & 1u);
+        PF_ACC(1);
         mbar_wait(d_free(buf), ((dc >> 1) & 1u) ^ 1u);
         tc_fence_after();
+        PF_ACC(2);
         const uint32_t wt = base + mp.wr + st * PF_PANEL;
 #pragma unroll 1
         while (oi < nops && (int)(t_ops[oi] >> 24) == c) {
@@ -342,8 +425,10 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
           const int pan = (int)(i >> 2);
           if (pan != cur_pan) {
             if (cur_pan >= 0) { if (elect_one()) mma_commit(lo_free((lp - 1) & 1u)); __syncwarp(); }
+            PF_ACC(3);
             mbar_wait(lo_full(lp & 1u), (lp >> 1) & 1u);
             tc_fence_after();
+            PF_ACC(4);
             ++lp; cur_pan = pan;
           }
           const uint32_t half = s0 >> 4, sh = s0 & 15u;
@@ -362,6 +447,7 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
         }
         if (elect_one()) { mma_commit(d_full(buf)); mma_commit(w_free(st)); }
         __syncwarp();
+        PF_ACC(3);
       }
       if (elect_one()) mma_commit(lo_free((lp - 1) & 1u));
       __syncwarp();
@@ -383,6 +469,10 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
       }
     }
   }
+#ifdef PF_TRACE
+  if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 5 || warp == 8 || warp == 12))
+    printf("w%d tiles %d total %lld : %lld %lld %lld %lld %lld %lld\n", warp, (int)my_tiles, clock64() - t_start, tr[0], tr[1], tr[2], tr[3], tr[4], tr[5]);
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == PF_NEPI + PF_NGAT) { tc_fence_after(); tmem_dealloc(tmem_base, 512u); }
@@ -427,13 +517,15 @@ extern "C" int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, 
   const int64_t n_tiles = (B + PF_BM - 1) / PF_BM;
   const int grid = (int)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (ids_kind == CTRHOT_IDS_I32) {
-    CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_front_kernel<CTRHOT_IDS_I32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "pnn_front attr");
-    pnn_front_kernel<CTRHOT_IDS_I32><<<grid, PF_THREADS, smem, st>>>(p);
-  } else {
-    CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_front_kernel<CTRHOT_IDS_F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "pnn_front attr");
-    pnn_front_kernel<CTRHOT_IDS_F32><<<grid, PF_THREADS, smem, st>>>(p);
-  }
+#define PF_LAUNCH(KIND, INN)                                                                                              \
+  do {                                                                                                                    \
+    CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_front_kernel<KIND, INN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), \
+                   "pnn_front attr");                                                                                     \
+    pnn_front_kernel<KIND, INN><<<grid, PF_THREADS, smem, st>>>(p);                                                       \
+  } while (0)
+  if (ids_kind == CTRHOT_IDS_I32) { if (do_inner) PF_LAUNCH(CTRHOT_IDS_I32, true); else PF_LAUNCH(CTRHOT_IDS_I32, false); }
+  else { if (do_inner) PF_LAUNCH(CTRHOT_IDS_F32, true); else PF_LAUNCH(CTRHOT_IDS_F32, false); }
+#undef PF_LAUNCH
   CTRHOT_LAUNCH_OK("ctrhot_pnn_front_f32");
   return CTRHOT_OK;
 }
