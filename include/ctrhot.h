@@ -244,6 +244,15 @@ int ctrhot_mmoe_combine_f32(const float* expert, int64_t e_ld, const float* gate
                             int E, int T, float* out, int64_t out_task_stride, int64_t out_ld, void* stream);
 int ctrhot_lau_concat_f32(const float* query, int64_t q_ld, const float* keys, int64_t k_ld, int64_t B, int T, int K,
                           float* out, int64_t out_ld, void* stream);
+/* ---- 8(f) rank 2, Hash.call without a vocabulary file, DL/layer/utils.py:35-56 -------------------------------------------
+ * out[i] = FarmHash Fingerprint64(str(x[i])) % nb   with nb = num_buckets - (mask_zero ? 1 : 0)   (tf.strings.to_hash_bucket_fast),
+ * shifted up by one with the value "0" -> 0 when mask_zero (utils.py:52-54).  _int: x = DEVICE int32 / int64 [N], hashed as its
+ * decimal string (tf.as_string, :37-38).  _bytes: strings of len[i] <= 64 bytes at s + i * stride (longer: out = -1, *err_flag).
+ * Pinned on the example in TensorFlow's documentation of the op (["Hello", "TensorFlow", "2.x"], 3 -> [0, 2, 2]): lengths 1-16,
+ * i.e. every integer of up to 16 digits; the 17-64 byte branches follow the published FarmHash source unpinned. */
+int ctrhot_hash_bucket_int(const void* x, int is_i64, int64_t N, int64_t num_buckets, int mask_zero, int64_t* out, void* stream);
+int ctrhot_hash_bucket_bytes(const uint8_t* s, int64_t stride, const int32_t* len, int64_t N, int64_t num_buckets,
+                             int mask_zero, int64_t* out, int* err_flag, void* stream);
 /* ---- 8(f) rank 2, the input step: create_criteo_dataset, DL/utils/dataset.py:36-66 (read_csv :38, fillna :42-43,
  * MinMaxScaler :46, LabelEncoder per column :51-52) -----------------------------------------------------------------------
  * ctrhot_criteo_parse_tsv: text = the file's bytes on the DEVICE; line_start = device int64 [N + 1] (byte offset of every

@@ -645,3 +645,71 @@ def fm_train_step(x, fm_w0, fm_w1, fm_v, y, lr, reg_w, reg_v):
     g_w1 = x.T @ dz[:, None] + 2 * reg_w * fm_w1
     g_v = x.T @ (dz[:, None] * xv) - fm_v * ((x ** 2).T @ dz)[:, None] + 2 * reg_v * fm_v
     return (fm_w0 - lr * np.sum(dz), fm_w1 - lr * g_w1, fm_v - lr * g_v), bce, int(np.sum((p > 0.5) == (y > 0.5)))
+
+
+# --------------------------------------------------------------------------- 8(f) rank 2: Hash (DL/layer/utils.py:21-56)
+# tf.strings.to_hash_bucket_fast is FarmHash Fingerprint64 (farmhashna::Hash64, google/farmhash, not vendored by the reference:
+# TensorFlow links it) modulo num_buckets.  Restated from the published algorithm.  PIN: the example in TensorFlow's own
+# documentation of the op, to_hash_bucket_fast(["Hello", "TensorFlow", "2.x"], 3) == [0, 2, 2], which exercises the 4-7, 8-16 and
+# 1-3 byte branches (every decimal int32 / most int64 ids), and Fingerprint64("") == k2.  The 17-32 and 33-64 byte branches follow
+# the same source but have no vector here: "parity unpinned" for ids of 17+ digits and long strings.
+_M64 = (1 << 64) - 1
+_K0, _K1, _K2 = 0xc3a5c85c97cb3127, 0xb492b66fbe98f273, 0x9ae16a3b2f90404f
+
+
+def _rot(v, s):
+    return ((v >> s) | (v << (64 - s))) & _M64 if s else v
+
+
+def _hl16(u, v, mul):
+    a = ((u ^ v) * mul) & _M64
+    a ^= a >> 47
+    b = ((v ^ a) * mul) & _M64
+    b ^= b >> 47
+    return (b * mul) & _M64
+
+
+def farm_fingerprint64(s):
+    """farmhashna::Hash64 for len(s) <= 64 bytes (HashLen0to16 / HashLen17to32 / HashLen33to64)."""
+    n = len(s)
+    f64 = lambda i: int.from_bytes(s[i:i + 8], "little")
+    f32 = lambda i: int.from_bytes(s[i:i + 4], "little")
+    mul = (_K2 + 2 * n) & _M64
+    if n == 0:
+        return _K2
+    if n < 4:
+        y = (s[0] + (s[n >> 1] << 8)) & 0xffffffff
+        z = (n + (s[n - 1] << 2)) & 0xffffffff
+        v = ((y * _K2) & _M64) ^ ((z * _K0) & _M64)
+        return ((v ^ (v >> 47)) * _K2) & _M64
+    if n < 8:
+        return _hl16((n + (f32(0) << 3)) & _M64, f32(n - 4), mul)
+    if n <= 16:
+        a, b = (f64(0) + _K2) & _M64, f64(n - 8)
+        return _hl16((_rot(b, 37) * mul + a) & _M64, ((_rot(a, 25) + b) * mul) & _M64, mul)
+    if n <= 32:
+        a, b, c, d = (f64(0) * _K1) & _M64, f64(8), (f64(n - 8) * mul) & _M64, (f64(n - 16) * _K2) & _M64
+        return _hl16((_rot((a + b) & _M64, 43) + _rot(c, 30) + d) & _M64, (a + _rot((b + _K2) & _M64, 18) + c) & _M64, mul)
+    if n <= 64:
+        a, b, c, d = (f64(0) * _K2) & _M64, f64(8), (f64(n - 8) * mul) & _M64, (f64(n - 16) * _K2) & _M64
+        y = (_rot((a + b) & _M64, 43) + _rot(c, 30) + d) & _M64
+        z = _hl16(y, (a + _rot((b + _K2) & _M64, 18) + c) & _M64, mul)
+        e, f = (f64(16) * mul) & _M64, f64(24)
+        g, h = ((y + f64(n - 32)) * mul) & _M64, ((z + f64(n - 24)) * mul) & _M64
+        return _hl16((_rot((e + f) & _M64, 43) + _rot(g, 30) + h) & _M64, (e + _rot((f + a) & _M64, 18) + g) & _M64, mul)
+    raise NotImplementedError("strings over 64 bytes")
+
+
+def hash_layer(x, num_buckets, mask_zero=False):
+    """Hash.call without a vocabulary file, DL/layer/utils.py:35-56: integers go through tf.as_string (decimal), strings as they
+    are; bucket = Fingerprint64 % (num_buckets - mask_zero); with mask_zero the buckets shift up by one and the value "0" maps
+    to 0.  -> int64 array of x's shape."""
+    a = np.asarray(x)
+    flat = a.reshape(-1)
+    nb = num_buckets - 1 if mask_zero else num_buckets
+    out = np.empty(flat.shape, np.int64)
+    for i, v in enumerate(flat):
+        s = v if isinstance(v, bytes) else (v.encode() if isinstance(v, str) else str(int(v)).encode())
+        h = farm_fingerprint64(s) % nb
+        out[i] = (h + 1) * (s != b"0") if mask_zero else h
+    return out.reshape(a.shape)

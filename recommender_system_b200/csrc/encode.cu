@@ -109,6 +109,93 @@ __global__ void criteo_encode_kernel(const double* __restrict__ dense_raw, const
   }
 }
 
+// ---------------------------------------------------------------- Hash (DL/layer/utils.py:21-56)
+// tf.strings.to_hash_bucket_fast = FarmHash Fingerprint64 (farmhashna::Hash64) % num_buckets of the value's string form
+// (tf.as_string: decimal for integers).  The string sits in 64-bit words w[] (little endian, zero past the end); Fetch64 at a
+// byte offset is a funnel shift of two words.  Lengths <= 64 (HashLen0to16 / 17to32 / 33to64): every decimal integer is <= 20.
+namespace fh {
+constexpr uint64_t k0 = 0xc3a5c85c97cb3127ull, k1 = 0xb492b66fbe98f273ull, k2 = 0x9ae16a3b2f90404full;
+__device__ __forceinline__ uint64_t rot(uint64_t v, int s) { return (v >> s) | (v << (64 - s)); }
+__device__ __forceinline__ uint64_t f64(const uint64_t* w, int off) {
+  const int i = off >> 3, sh = (off & 7) * 8;
+  const uint64_t lo = w[i] >> sh;
+  return sh ? (lo | (w[i + 1] << (64 - sh))) : lo;
+}
+__device__ __forceinline__ uint64_t f32(const uint64_t* w, int off) { return f64(w, off) & 0xffffffffull; }
+__device__ __forceinline__ uint64_t byte_at(const uint64_t* w, int off) { return (w[off >> 3] >> ((off & 7) * 8)) & 0xffull; }
+__device__ __forceinline__ uint64_t hl16(uint64_t u, uint64_t v, uint64_t mul) {
+  uint64_t a = (u ^ v) * mul;
+  a ^= a >> 47;
+  uint64_t b = (v ^ a) * mul;
+  b ^= b >> 47;
+  return b * mul;
+}
+__device__ uint64_t fingerprint64(const uint64_t* w, int n) {
+  const uint64_t mul = k2 + 2ull * (uint64_t)n;
+  if (n == 0) return k2;
+  if (n < 4) {
+    const uint32_t y = (uint32_t)byte_at(w, 0) + ((uint32_t)byte_at(w, n >> 1) << 8);
+    const uint32_t z = (uint32_t)n + ((uint32_t)byte_at(w, n - 1) << 2);
+    const uint64_t v = ((uint64_t)y * k2) ^ ((uint64_t)z * k0);
+    return (v ^ (v >> 47)) * k2;
+  }
+  if (n < 8) return hl16((uint64_t)n + (f32(w, 0) << 3), f32(w, n - 4), mul);
+  if (n <= 16) {
+    const uint64_t a = f64(w, 0) + k2, b = f64(w, n - 8);
+    return hl16(rot(b, 37) * mul + a, (rot(a, 25) + b) * mul, mul);
+  }
+  if (n <= 32) {
+    const uint64_t a = f64(w, 0) * k1, b = f64(w, 8), c = f64(w, n - 8) * mul, d = f64(w, n - 16) * k2;
+    return hl16(rot(a + b, 43) + rot(c, 30) + d, a + rot(b + k2, 18) + c, mul);
+  }
+  const uint64_t a = f64(w, 0) * k2, b = f64(w, 8), c = f64(w, n - 8) * mul, d = f64(w, n - 16) * k2;
+  const uint64_t y = rot(a + b, 43) + rot(c, 30) + d;
+  const uint64_t z = hl16(y, a + rot(b + k2, 18) + c, mul);
+  const uint64_t e = f64(w, 16) * mul, f = f64(w, 24), g = (y + f64(w, n - 32)) * mul, h = (z + f64(w, n - 24)) * mul;
+  return hl16(rot(e + f, 43) + rot(g, 30) + h, e + rot(f + a, 18) + g, mul);
+}
+}  // namespace fh
+
+template <typename T>
+__global__ void hash_bucket_int_kernel(const T* __restrict__ x, int64_t N, uint64_t nb, int mask_zero, int64_t* __restrict__ out) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < N; r += (int64_t)gridDim.x * blockDim.x) {
+    const long long v = (long long)x[r];
+    unsigned long long mag = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
+    // decimal digits, most significant first, after an optional '-': tf.as_string
+    int nd = 1;
+    for (unsigned long long t = mag; t >= 10ull; t /= 10ull) ++nd;
+    const int n = nd + (v < 0 ? 1 : 0);
+    uint64_t w[4] = {0ull, 0ull, 0ull, 0ull};
+    for (int pos = n - 1; pos >= (v < 0 ? 1 : 0); --pos) {
+      w[pos >> 3] |= (uint64_t)(48 + (int)(mag % 10ull)) << ((pos & 7) * 8);
+      mag /= 10ull;
+    }
+    if (v < 0) w[0] |= (uint64_t)'-';
+    const uint64_t h = fh::fingerprint64(w, n) % nb;
+    out[r] = mask_zero ? (v == 0 ? 0ll : (long long)(h + 1ull)) : (long long)h;
+  }
+}
+
+__global__ void hash_bucket_bytes_kernel(const uint8_t* __restrict__ s, int64_t stride, const int32_t* __restrict__ len, int64_t N,
+                                         uint64_t nb, int mask_zero, int64_t* __restrict__ out, int* __restrict__ err_flag) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < N; r += (int64_t)gridDim.x * blockDim.x) {
+    const int n = len[r];
+    if (n < 0 || n > 64 || n > stride) {
+      if (err_flag) *err_flag = 1;
+      out[r] = -1;
+      continue;
+    }
+    uint64_t w[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) w[i] = 0ull;
+    const uint8_t* p = s + r * stride;
+    for (int i = 0; i < n; ++i) w[i >> 3] |= (uint64_t)p[i] << ((i & 7) * 8);
+    const uint64_t h = fh::fingerprint64(w, n) % nb;
+    const bool is_zero = (n == 1 && p[0] == (uint8_t)'0');
+    out[r] = mask_zero ? (is_zero ? 0ll : (long long)(h + 1ull)) : (long long)h;
+  }
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -139,5 +226,36 @@ extern "C" int ctrhot_criteo_encode(const double* dense_raw, const int64_t* toke
   criteo_encode_kernel<<<(int)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dense_raw, tokens, N, d_scale, d_min, vocab,
                                                                                  vocab_off, dense, dense_ld, ids, ids_ld, err_flag);
   CTRHOT_LAUNCH_OK("ctrhot_criteo_encode");
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_hash_bucket_int(const void* x, int is_i64, int64_t N, int64_t num_buckets, int mask_zero, int64_t* out,
+                                      void* stream) {
+  CTRHOT_RANGE("ctrhot_hash_bucket_int");
+  if (!x || !out || N < 0) return CTRHOT_EARG;
+  const int64_t nb = num_buckets - (mask_zero ? 1 : 0);
+  if (nb < 1) return CTRHOT_EARG;
+  if (N == 0) return CTRHOT_OK;
+  int64_t grid = (N + 255) / 256;
+  if (grid > (int64_t)kNumSMs * 16) grid = (int64_t)kNumSMs * 16;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (is_i64) hash_bucket_int_kernel<int64_t><<<(int)grid, 256, 0, st>>>(static_cast<const int64_t*>(x), N, (uint64_t)nb, mask_zero, out);
+  else hash_bucket_int_kernel<int32_t><<<(int)grid, 256, 0, st>>>(static_cast<const int32_t*>(x), N, (uint64_t)nb, mask_zero, out);
+  CTRHOT_LAUNCH_OK("ctrhot_hash_bucket_int");
+  return CTRHOT_OK;
+}
+
+extern "C" int ctrhot_hash_bucket_bytes(const uint8_t* s, int64_t stride, const int32_t* len, int64_t N, int64_t num_buckets,
+                                        int mask_zero, int64_t* out, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_hash_bucket_bytes");
+  if (!s || !len || !out || N < 0 || stride < 1) return CTRHOT_EARG;
+  const int64_t nb = num_buckets - (mask_zero ? 1 : 0);
+  if (nb < 1) return CTRHOT_EARG;
+  if (N == 0) return CTRHOT_OK;
+  int64_t grid = (N + 127) / 128;
+  if (grid > (int64_t)kNumSMs * 16) grid = (int64_t)kNumSMs * 16;
+  hash_bucket_bytes_kernel<<<(int)grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(s, stride, len, N, (uint64_t)nb, mask_zero,
+                                                                                     out, err_flag);
+  CTRHOT_LAUNCH_OK("ctrhot_hash_bucket_bytes");
   return CTRHOT_OK;
 }

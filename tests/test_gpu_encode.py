@@ -122,3 +122,31 @@ def test_throughput_report(lib, raw):
     if os.path.isdir(out):
         open(os.path.join(out, "r02_input_step.txt"), "w").write(msg + "\n")
     assert dr.shape[0] == 200000
+
+
+# ------------------------------------------------------------------ Hash (DL/layer/utils.py:21-56)
+def test_hash_layer_matches_tensorflows_documented_example_and_the_oracle(lib):
+    """tf.strings.to_hash_bucket_fast(["Hello", "TensorFlow", "2.x"], 3) == [0, 2, 2] is the example in TensorFlow's documentation
+    of the op (the pin of the FarmHash restatement); then integers as their decimal strings, mask_zero, negatives, 17-19 digit
+    values and strings up to 64 bytes against oracle.hash_layer."""
+    import torch
+    from oracle import ctr_oracle as O
+    from recommender_system_b200.layer import Hash
+    got = Hash(3)(np.array([b"Hello", b"TensorFlow", b"2.x"])).cpu().numpy()
+    assert got.tolist() == [0, 2, 2]
+    rng = np.random.default_rng(0)
+    x32 = np.concatenate([[0, 1, 9, 10, 99, 100, 2147483647, -1, -2147483648], rng.integers(0, 10 ** 9, 5000)]).astype(np.int32)
+    for nb, mz in ((1000, False), (1000, True), (7, True), (2 ** 40, False)):
+        np.testing.assert_array_equal(Hash(nb, mask_zero=mz)(x32).cpu().numpy(), O.hash_layer(x32, nb, mz))
+    x64 = np.concatenate([[0, 10 ** 15, 10 ** 16, 10 ** 17 + 3, 9223372036854775807, -9223372036854775808, -(10 ** 18)],
+                          rng.integers(0, 2 ** 62, 3000)]).astype(np.int64)
+    x64 = x64[:x64.size // 7 * 7].reshape(-1, 7)                                      # a [B, 7] id matrix, already on the device
+    np.testing.assert_array_equal(Hash(100003, mask_zero=True)(torch.from_numpy(x64).cuda()).cpu().numpy(),
+                                  O.hash_layer(x64, 100003, True))
+    words = [bytes(rng.integers(33, 127, n).astype(np.uint8)) for n in list(range(1, 65)) * 3] + [b"0", b"00", b""]
+    np.testing.assert_array_equal(Hash(65536, mask_zero=True)(np.array(words, dtype=object)).cpu().numpy(),
+                                  O.hash_layer(words, 65536, True))
+    with pytest.raises(NotImplementedError):
+        Hash(10, vocabulary_path="vocab.csv")
+    with pytest.raises(NotImplementedError):
+        Hash(10)(np.array([1.5, 2.0], np.float32))

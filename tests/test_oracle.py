@@ -203,3 +203,11 @@ def test_fm_train_step_gradients():
         a, b = w1.copy(), w1.copy(); a[i, 0] += eps; b[i, 0] -= eps
         assert abs((loss(w0, a, v) - loss(w0, b, v)) / (2 * eps) - ((w1 - new[1]) / lr)[i, 0]) < 1e-8
     assert abs((loss(w0 + eps, w1, v) - loss(w0 - eps, w1, v)) / (2 * eps) - ((w0 - new[0]) / lr)[0]) < 1e-8
+
+
+def test_farm_fingerprint_pins():
+    """TensorFlow's documented example of to_hash_bucket_fast and FarmHash's value for the empty string."""
+    assert O.hash_layer([b"Hello", b"TensorFlow", b"2.x"], 3).tolist() == [0, 2, 2]
+    assert O.farm_fingerprint64(b"") == 0x9ae16a3b2f90404f
+    got = O.hash_layer(np.array([[0, 5], [123456789012, 7]]), 10, True)
+    assert got.shape == (2, 2) and got[0, 0] == 0 and np.all(got[got != 0] >= 1) and np.all(got <= 9)
