@@ -394,13 +394,16 @@ int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* row_off, int 
  *   out[b, width : out_ld)       = 0
  * The inner sum of the outer product runs on the tensor pipe as a three-term TF32 split (fp32-accurate: <= 1e-5 relative),
  * the rest on the CUDA cores from the same shared-memory tile.  k == 8 (the reference's embed_dim), 2 <= F <= 28;
- * out 16-byte aligned, out_ld % 4 == 0.  packed = ctrhot_pnn_pack(W) (ctrhot_pnn_pack_bytes bytes, re-pack when W changes). */
+ * out 16-byte aligned, out_ld % 4 == 0.  packed = ctrhot_pnn_pack(W) (ctrhot_pnn_pack_bytes bytes, re-pack when W changes).
+ * signal_flags / epoch / launch: CHAINED LAUNCHES as for ctrhot_dense_rows_tf32 -- tile t (rows [128 t, 128 t + 128)) of `out` is
+ * published by storing epoch into signal_flags[t]; with launch = CTRHOT_LAUNCH_OVERLAP the tower launched behind it
+ * (ctrhot_tower_rows_post_tf32 with wait_flags) may start on the SMs this kernel frees.  NULL / 0 / 0 = plain stream order. */
 int64_t ctrhot_pnn_pack_bytes(int F, int k);
 int ctrhot_pnn_pack(const float* W, int F, int k, void* packed, void* stream);
 int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, int F, int k,
                          const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
                          const void* packed, int do_inner, float* out, int64_t out_ld,
-                         int* err_flag, void* stream);
+                         int* err_flag, int32_t* signal_flags, int epoch, int launch, void* stream);
 
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,

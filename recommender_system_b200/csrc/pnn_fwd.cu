@@ -115,6 +115,7 @@ struct PfParams {
   const float* arena; const int64_t* row_off; const void* ids; int64_t ids_ld; int64_t B;
   const uint8_t* packed; float* out; int64_t out_ld; int* err_flag;
   int F, do_inner, col_inner, col_outer, width;
+  int32_t* signal_flags; int epoch, overlap;   // chained launches: tile t of `out` is published by storing epoch into signal_flags[t]
 };
 
 struct PfSmem { uint32_t e, lo, wr, stg, tab, bars, total; };
@@ -180,6 +181,8 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *slot_ptr;
+  // the tower launched behind this kernel may start on the SMs it frees (it waits for signal_flags, not for this grid)
+  if (p.overlap && threadIdx.x == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int nch = hdr[3], nops = hdr[4], npa = hdr[5];
   const int64_t n_tiles = (p.B + PF_BM - 1) / PF_BM;
   const int64_t my_tiles = (n_tiles > blockIdx.x) ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
@@ -350,6 +353,12 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
       fence_proxy_async_smem();
       mbar_arrive(e_full);
       named_bar_sync(1, PF_NGAT * 32);
+      // tile it - 1 is complete in HBM: its last E panel was released (every epilogue warp is past its last store) and every
+      // gather warp is past its flat columns (the barrier above)
+      if (p.signal_flags && it > 0 && gt == 0) {
+        __threadfence();
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p.signal_flags + (blockIdx.x + (it - 1) * gridDim.x)), "r"(p.epoch) : "memory");
+      }
       // Al = tf32(x - trunc_tf32(x)) for the panels that hold a run's field i (at most two ahead of the MMAs); the first two
       // are on the critical path of the tile and go before the flat columns
       auto build_lo = [&](int m) {
@@ -399,6 +408,14 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
       PF_ACC(4);
       for (int m = n_first; m < npa; ++m) build_lo(m);
       PF_ACC(5);
+    }
+    if (p.signal_flags && my_tiles > 0) {                            // the CTA's last tile
+      for (int m = 0; m < npan; ++m) mbar_wait(p_free(m), (uint32_t)((my_tiles - 1) & 1));
+      named_bar_sync(1, PF_NGAT * 32);
+      if (gt == 0) {
+        __threadfence();
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p.signal_flags + (blockIdx.x + (my_tiles - 1) * gridDim.x)), "r"(p.epoch) : "memory");
+      }
     }
   } else if (warp == PF_NEPI + PF_NGAT) {
     // ================================================================ MMA issuer (converged warp, one elected lane issues)
@@ -500,7 +517,7 @@ extern "C" int ctrhot_pnn_pack(const float* W, int F, int k, void* packed, void*
 extern "C" int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, int F, int k,
                                     const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
                                     const void* packed, int do_inner, float* out, int64_t out_ld,
-                                    int* err_flag, void* stream) {
+                                    int* err_flag, int32_t* signal_flags, int epoch, int launch, void* stream) {
   CTRHOT_RANGE("ctrhot_pnn_front_f32");
   if (!arena || !row_off || !ids || !packed || !out || B < 0 || ids_ld < F) return CTRHOT_EARG;
   if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
@@ -512,6 +529,7 @@ extern "C" int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, 
   PfParams p;
   p.arena = arena; p.row_off = row_off; p.ids = ids; p.ids_ld = ids_ld; p.B = B;
   p.packed = static_cast<const uint8_t*>(packed); p.out = out; p.out_ld = out_ld; p.err_flag = err_flag;
+  p.signal_flags = signal_flags; p.epoch = epoch; p.overlap = (launch & CTRHOT_LAUNCH_OVERLAP) && signal_flags ? 1 : 0;
   p.F = F; p.do_inner = do_inner ? 1 : 0; p.col_inner = F * k; p.col_outer = F * k + (do_inner ? q.P : 0); p.width = width;
   const size_t smem = pf_smem(F).total + 1024;
   const int64_t n_tiles = (B + PF_BM - 1) / PF_BM;

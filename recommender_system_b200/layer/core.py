@@ -199,8 +199,10 @@ class DenseStack:
         _lib.call("ctrhot_tower_fused_tf32", ptr(x), x_ld, M, arr, len(arr), *self._post(post), ptr(out), stream_ptr())
         return out
 
-    def run_rows(self, x, x_ld, sigmoid, out):
-        """Tower over a matrix in HBM through the persistent whole-model kernel (no ids: row m of x feeds row m)."""
+    def run_rows(self, x, x_ld, sigmoid, out, wait_flags=None, epoch=0):
+        """Tower over a matrix in HBM through the persistent whole-model kernel (no ids: row m of x feeds row m).
+        ``wait_flags`` / ``epoch``: x is being written by the launch in front (chained launches, include/ctrhot.h): this launch
+        may start before that one has finished and waits per 128-row tile."""
         arr = self.descs()
         K, n1 = arr[0].in_dim, arr[0].out_dim
         r = K % 4
@@ -213,6 +215,10 @@ class DenseStack:
             _lib.call("ctrhot_fused_pack", ptr(W1r), None, K, n1, r, ptr(buf), stream_ptr())
             self._packed[key] = buf
         arr[0].packed = ptr(self._packed[key])
+        if wait_flags is not None:
+            _lib.call("ctrhot_tower_rows_post_tf32", ptr(x), x_ld, K, x.shape[0], arr, len(arr), None, 1.0, 0.0, 0.0,
+                      int(bool(sigmoid)), _lib.LAUNCH_OVERLAP, ptr(out), ptr(wait_flags), int(epoch), stream_ptr())
+            return out
         _lib.call("ctrhot_tower_rows_tf32", ptr(x), x_ld, K, x.shape[0], arr, len(arr), int(bool(sigmoid)), 0, ptr(out),
                   stream_ptr())
         return out

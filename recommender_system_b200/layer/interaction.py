@@ -233,8 +233,9 @@ class OuterProductLayer(Layer):
     def front_fits(self):
         return self.built and self.k == 8 and 2 <= self.field_num <= 28
 
-    def front(self, embed_layer, ids, do_inner, out, out_ld):
-        """``out[b] = [rows | <e_i, e_j> | e_j^T W_p e_i | 0]`` straight from the tables (DL/model/pnn.py:28-49)."""
+    def front(self, embed_layer, ids, do_inner, out, out_ld, signal_flags=None, epoch=0):
+        """``out[b] = [rows | <e_i, e_j> | e_j^T W_p e_i | 0]`` straight from the tables (DL/model/pnn.py:28-49).
+        ``signal_flags`` / ``epoch``: publish ``out`` per 128-row tile for a tower launched behind (chained launches)."""
         pk = getattr(self, "_front_pack", None)
         if pk is None or pk[0] != self._version:
             n = _lib.query("ctrhot_pnn_pack_bytes", self.field_num, self.k)
@@ -244,7 +245,8 @@ class OuterProductLayer(Layer):
         ids, kind, ids_ld = ids_arg(ids)
         E = embed_layer
         _lib.call("ctrhot_pnn_front_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ids.shape[0],
-                  ptr(pk[1]), 1 if do_inner else 0, ptr(out), out_ld, ptr(E.err_flag()), stream_ptr())
+                  ptr(pk[1]), 1 if do_inner else 0, ptr(out), out_ld, ptr(E.err_flag()), ptr(signal_flags), int(epoch),
+                  _lib.LAUNCH_OVERLAP if signal_flags is not None else 0, stream_ptr())
         if E.check:
             E.check_ids()
         return out

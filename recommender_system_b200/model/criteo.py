@@ -619,6 +619,8 @@ class PNN(Model):
             raise NotImplementedError("FGCNN branch (pnn.py:33-35) is outside the hot path (SURVEY 2.1 C8)")
         self.mode = mode
         self.fused_front = True          # False: gather / inner / outer as separate launches (the only path for k != 8)
+        self.chain_launches = True       # front -> tower under per-tile flags with overlapping launches (large batches)
+        self._chain = None
         self.dense_feature_columns, self.sparse_feature_columns = feature_columns
         self.dnn_layer = self.track(DNNLayer(hidden_units, output_dim, activation, dropout, precision=precision,
                                              device=self.device))
@@ -649,11 +651,30 @@ class PNN(Model):
         ld = _pad32(self.width)
         # every column below `width` is written by the gather / product kernels; only the K padding of the tower's first layer
         # has to be zero (garbage times a zero weight row could be NaN), not the whole [B, ld] buffer
-        buf = torch.empty((B, ld), dtype=torch.float32, device=self.device)
         if self.fused_front and self.mode != "inner" and self.outer_product_layer.front_fits():
             # gather + both product layers in one launch, the rows never reach HBM as an intermediate (csrc/pnn_fwd.cu)
+            st = self.dnn_layer.stack
+            arr = st.descs()
+            n_tiles = (B + 127) // 128
+            chain = (self.chain_launches and n_tiles >= 148 and st.precision == "tf32" and ld % 4 == 0
+                     and st.ctr_fused_ok(1, 4, arr) and arr[-1].out_dim == 1)
+            if chain:
+                # the tower starts on the SMs the front frees and waits per tile: two alternating product buffers (the next
+                # call's front must not write what this call's tower still reads) and a new epoch per call
+                c = self._chain
+                if c is None or c[0].shape[0] < B or c[0].shape[1] != ld:
+                    c = self._chain = [torch.empty((2 * B, ld), dtype=torch.float32, device=self.device),
+                                       torch.zeros(n_tiles, dtype=torch.int32, device=self.device), 0]
+                c[2] += 1
+                half = c[0].shape[0] // 2
+                buf = c[0][(c[2] & 1) * half:(c[2] & 1) * half + B]
+                self.outer_product_layer.front(E, ids, self.mode == "both", buf, ld, c[1], c[2])
+                out = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+                return st.run_rows(buf[:, :self.width], ld, False, out, c[1], c[2])
+            buf = torch.empty((B, ld), dtype=torch.float32, device=self.device)
             self.outer_product_layer.front(E, ids, self.mode == "both", buf, ld)
             return self.dnn_layer(buf[:, :self.width], x_ld=ld)
+        buf = torch.empty((B, ld), dtype=torch.float32, device=self.device)
         if ld > self.width:
             buf[:, self.width:].zero_()
         E.gather(ids, out=buf, out_ld=ld)

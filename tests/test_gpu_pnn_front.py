@@ -107,3 +107,22 @@ def test_pnn_model_fused_front_equals_layer_path_and_oracle(lib, mode):
     want = O.pnn_model(x.astype(np.float64), [t.astype(np.float64) for t in tabs], mode, hidden, out,
                        outer_w=W.astype(np.float64))
     assert np.max(np.abs(got - want)) <= 2e-3, np.max(np.abs(got - want))
+
+
+def test_pnn_chained_launches_equal_stream_order(lib):
+    """Front -> tower under per-tile flags with overlapping launches (two alternating product buffers, a new epoch per call)
+    gives bit-identical logits to plain stream order, call after call on different batches."""
+    B, F = 148 * 128 * 2 + 77, 26
+    m, vocab, tabs, W, rng = make(F, 3000, 31, mode="both", hidden=(256, 128, 64))
+    xs = []
+    for i in range(3):
+        ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1).astype(np.float32)
+        xs.append(torch.from_numpy(np.concatenate([S.f32(rng.random((B, 13))), ids], axis=1)).cuda())
+    m.chain_launches = False
+    want = [m(x).clone() for x in xs]
+    m.chain_launches = True
+    got = [m(xs[i % 3]).clone() for i in range(7)]
+    torch.cuda.synchronize()
+    assert m._chain is not None and m._chain[2] == 7
+    for i in range(7):
+        assert torch.equal(got[i], want[i % 3]), i
