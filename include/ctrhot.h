@@ -404,6 +404,11 @@ int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, int F, int 
                          const void* ids, int ids_kind, int64_t ids_ld, int64_t B,
                          const void* packed, int do_inner, float* out, int64_t out_ld,
                          int* err_flag, int32_t* signal_flags, int epoch, int launch, void* stream);
+/* The two product layers on an already gathered e [B, F, 8] (row stride e_ld, 16-byte aligned, e_ld % 4 == 0) by the same kernel:
+ * out[b, 0:P) = <e_i, e_j> (if do_inner), out[b, .. + P) = e_j^T W_p e_i (columns beyond are not touched).  InnerProductLayer.call /
+ * OuterProductLayer.call, DL/layer/interaction.py:170-183 / 201-215, for the reference's embed_dim (k == 8, F <= 28). */
+int ctrhot_pnn_products_f32(const float* e, int64_t e_ld, int F, int k, int64_t B, const void* packed, int do_inner,
+                            float* out, int64_t out_ld, void* stream);
 
 /* Dice.call, interaction.py:422-425, elementwise over x[rows, h] */
 int ctrhot_dice_f32(const float* x, int64_t rows, int h, const float* alphas, const float* mean,

@@ -51,6 +51,13 @@ line("pnn_inner_f32 [B,26,16] -> [B,325]", t(lambda: ip(rot(es), out=out_p)), F 
 op = OuterProductLayer(device=dev)
 op.build(es[0].shape)
 line("pnn_outer_f32 [B,26,16] -> [B,325]", t(lambda: op(rot(es), out=out_p)), F * k * 4 + 325 * 4, "W [16,325,16] = 333 KB in L2")
+# the reference's own PNN shape (embed_dim 8): OuterProductLayer on the tensor pipe (csrc/pnn_fwd.cu) vs the CUDA-core kernel
+e8 = [torch.rand((B, F, 8), device=dev, generator=g) - 0.5 for _ in range(3)]
+op8 = OuterProductLayer(device=dev)
+op8.build(e8[0].shape)
+line("pnn_outer_f32 [B,26,8] -> [B,325], tcgen05 3xTF32", t(lambda: op8(rot(e8), out=out_p)), F * 8 * 4 + 325 * 4, "W [8,325,8] = 83 KB")
+op8.tensor_pipe = False
+line("pnn_outer_f32 [B,26,8] -> [B,325], CUDA cores", t(lambda: op8(rot(e8), out=out_p)), F * 8 * 4 + 325 * 4, "")
 xs = [torch.rand((B, 448), device=dev, generator=g)[:, :429] for _ in range(3)]
 cl = CrossLayer(3, device=dev)
 cl.build((None, 429))

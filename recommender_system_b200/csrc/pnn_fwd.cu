@@ -115,7 +115,8 @@ struct PfParams {
   const float* arena; const int64_t* row_off; const void* ids; int64_t ids_ld; int64_t B;
   const uint8_t* packed; float* out; int64_t out_ld; int* err_flag;
   int F, do_inner, col_inner, col_outer, width;
-  int32_t* signal_flags; int epoch, overlap;   // chained launches: tile t of `out` is published by storing epoch into signal_flags[t]
+  int32_t* signal_flags; int epoch, overlap;
+  int write_flat;          // 0: products only (ids == NULL: `arena` is a gathered [B, F, 8] matrix with row stride ids_ld)   // chained launches: tile t of `out` is published by storing epoch into signal_flags[t]
 };
 
 struct PfSmem { uint32_t e, lo, wr, stg, tab, bars, total; };
@@ -175,7 +176,7 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
   for (int i = tid; i < PF_TAB_BYTES / 4; i += PF_THREADS)
     reinterpret_cast<uint32_t*>(bp + mp.tab)[i] = __ldg(reinterpret_cast<const uint32_t*>(p.packed) + i);
   int64_t* s_off = reinterpret_cast<int64_t*>(bp + mp.bars + 192);
-  for (int i = tid; i <= PF_MAXF; i += PF_THREADS) s_off[i] = (i <= F) ? __ldg(p.row_off + i) : 0;
+  for (int i = tid; i <= PF_MAXF; i += PF_THREADS) s_off[i] = (i <= F && p.row_off) ? __ldg(p.row_off + i) : 0;
   if (warp == PF_NEPI + PF_NGAT) { tmem_alloc(slot_addr, 512u); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
@@ -319,7 +320,7 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
       const bool live = it < my_tiles && b < p.B;
 #pragma unroll
       for (int f = 0; f < PF_MAXF; ++f) {
-        int64_t v = (live && f < F) ? IdLoad<IDKIND>::at(p.ids, b * p.ids_ld + f) : 0;
+        int64_t v = (live && f < F && p.ids) ? IdLoad<IDKIND>::at(p.ids, b * p.ids_ld + f) : 0;
         rid[f] = (v < 0 || v > 0x7FFFFFFF) ? -1 : (int32_t)v;
       }
     };
@@ -336,9 +337,12 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
           const float* src = p.arena;
           uint32_t nb = 0;
           if (live && f < F) {
-            const int64_t r0 = s_off[f], r1 = s_off[f + 1];
-            if (rid[f] >= 0 && rid[f] < r1 - r0) { src = p.arena + (r0 + rid[f]) * PF_K; nb = 16; }
-            else if (p.err_flag) *p.err_flag = 1;
+            if (!p.ids) { src = p.arena + (b0 + gt) * p.ids_ld + f * PF_K; nb = 16; }      // rows of an [B, F, 8] matrix
+            else {
+              const int64_t r0 = s_off[f], r1 = s_off[f + 1];
+              if (rid[f] >= 0 && rid[f] < r1 - r0) { src = p.arena + (r0 + rid[f]) * PF_K; nb = 16; }
+              else if (p.err_flag) *p.err_flag = 1;
+            }
           }
           const uint32_t dst = base + mp.e + (uint32_t)(f >> 2) * PF_PANEL;
           cp_async16(dst + sw128_offset((uint32_t)gt, (uint32_t)(f & 3) * 2), src, nb);
@@ -400,8 +404,8 @@ pnn_front_kernel(const __grid_constant__ PfParams p) {
           float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
           if (h0) v0 = *reinterpret_cast<const float4*>(er + o0 + ((c0 ^ (rr & 7u)) << 4));
           if (h1) v1 = *reinterpret_cast<const float4*>(er + o1 + ((c1 ^ (rr & 7u)) << 4));
-          if (h0) *reinterpret_cast<float4*>(orow + 4 * lane) = v0;
-          if (h1) *reinterpret_cast<float4*>(orow + 4 * l1) = v1;
+          if (h0 && p.write_flat) *reinterpret_cast<float4*>(orow + 4 * lane) = v0;
+          if (h1 && p.write_flat) *reinterpret_cast<float4*>(orow + 4 * l1) = v1;
           for (int l = p.width + lane; l < p.out_ld; l += 32) orow[l] = 0.f;
         }
       }
@@ -529,6 +533,7 @@ extern "C" int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, 
   PfParams p;
   p.arena = arena; p.row_off = row_off; p.ids = ids; p.ids_ld = ids_ld; p.B = B;
   p.packed = static_cast<const uint8_t*>(packed); p.out = out; p.out_ld = out_ld; p.err_flag = err_flag;
+  p.write_flat = 1;
   p.signal_flags = signal_flags; p.epoch = epoch; p.overlap = (launch & CTRHOT_LAUNCH_OVERLAP) && signal_flags ? 1 : 0;
   p.F = F; p.do_inner = do_inner ? 1 : 0; p.col_inner = F * k; p.col_outer = F * k + (do_inner ? q.P : 0); p.width = width;
   const size_t smem = pf_smem(F).total + 1024;
@@ -545,5 +550,37 @@ extern "C" int ctrhot_pnn_front_f32(const float* arena, const int64_t* row_off, 
   else { if (do_inner) PF_LAUNCH(CTRHOT_IDS_F32, true); else PF_LAUNCH(CTRHOT_IDS_F32, false); }
 #undef PF_LAUNCH
   CTRHOT_LAUNCH_OK("ctrhot_pnn_front_f32");
+  return CTRHOT_OK;
+}
+
+// InnerProductLayer / OuterProductLayer on an already gathered e [B, F, 8] (row stride e_ld) by the same kernel:
+// out[b, 0:P) = <e_i, e_j> (if do_inner), then out[b, .. + P) = e_j^T W_p e_i; columns beyond are not touched.
+extern "C" int ctrhot_pnn_products_f32(const float* e, int64_t e_ld, int F, int k, int64_t B, const void* packed, int do_inner,
+                                       float* out, int64_t out_ld, void* stream) {
+  CTRHOT_RANGE("ctrhot_pnn_products_f32");
+  if (!e || !packed || !out || B < 0 || e_ld < (int64_t)F * k) return CTRHOT_EARG;
+  if (k != PF_K || F < 2 || F > PF_MAXF) return CTRHOT_ESHAPE;
+  const PfPlan q = pf_plan(F);
+  const int width = q.P * (do_inner ? 2 : 1);
+  if (out_ld < width || out_ld > 0x7FFFFFFF || e_ld % 4 != 0 || !aligned16(e) || !aligned16(packed)) return CTRHOT_ESHAPE;
+  if (B == 0) return CTRHOT_OK;
+  PfParams p;
+  p.arena = e; p.row_off = nullptr; p.ids = nullptr; p.ids_ld = e_ld; p.B = B;
+  p.packed = static_cast<const uint8_t*>(packed); p.out = out; p.out_ld = out_ld; p.err_flag = nullptr;
+  p.write_flat = 0; p.signal_flags = nullptr; p.epoch = 0; p.overlap = 0;
+  p.F = F; p.do_inner = do_inner ? 1 : 0; p.col_inner = 0; p.col_outer = do_inner ? q.P : 0;
+  p.width = (int)out_ld;                                   // nothing outside [0, width) of a row is written (out may be a view)
+  const size_t smem = pf_smem(F).total + 1024;
+  const int64_t n_tiles = (B + PF_BM - 1) / PF_BM;
+  const int grid = (int)(n_tiles < kNumSMs ? n_tiles : kNumSMs);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (do_inner) {
+    CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_front_kernel<CTRHOT_IDS_I32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "pnn_products attr");
+    pnn_front_kernel<CTRHOT_IDS_I32, true><<<grid, PF_THREADS, smem, st>>>(p);
+  } else {
+    CTRHOT_CUDA_OK(cudaFuncSetAttribute(pnn_front_kernel<CTRHOT_IDS_I32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "pnn_products attr");
+    pnn_front_kernel<CTRHOT_IDS_I32, false><<<grid, PF_THREADS, smem, st>>>(p);
+  }
+  CTRHOT_LAUNCH_OK("ctrhot_pnn_products_f32");
   return CTRHOT_OK;
 }

@@ -212,6 +212,7 @@ class OuterProductLayer(Layer):
 
     def __init__(self, device=None):
         super().__init__(device)
+        self.tensor_pipe = True          # k = 8: tcgen05 path (False: the CUDA-core kernels, any k)
 
     def build(self, input_shape):
         self.field_num = int(input_shape[1])
@@ -225,9 +226,24 @@ class OuterProductLayer(Layer):
         B, F, k = e.shape
         if out is None:
             out = _out(B, self.device, self.pair_num)
+        if (self.tensor_pipe and self.front_fits() and B >= 128 and e.stride(2) == 1 and e.stride(1) == k
+                and e.stride(0) % 4 == 0 and e.data_ptr() % 16 == 0 and out.stride(1) == 1):
+            # k = 8: the contraction on tcgen05 as a three-term TF32 split (fp32-accurate), csrc/pnn_fwd.cu
+            _lib.call("ctrhot_pnn_products_f32", ptr(e), e.stride(0), F, k, B, ptr(self._pack()), 0, ptr(out), out.stride(0),
+                      stream_ptr())
+            return out
         _lib.call("ctrhot_pnn_outer_f32", ptr(e), e.stride(0), F, k, B, ptr(self.w), ptr(out), out.stride(0),
                   stream_ptr())
         return out
+
+    def _pack(self):
+        pk = getattr(self, "_front_pack", None)
+        if pk is None or pk[0] != self._version:
+            n = _lib.query("ctrhot_pnn_pack_bytes", self.field_num, self.k)
+            buf = torch.empty(n, dtype=torch.uint8, device=self.device)
+            _lib.call("ctrhot_pnn_pack", ptr(self.w), self.field_num, self.k, ptr(buf), stream_ptr())
+            pk = self._front_pack = (self._version, buf)
+        return pk[1]
 
     # ---- the one-launch front of PNN.call (gather -> flat | inner | outer), csrc/pnn_fwd.cu
     def front_fits(self):
@@ -236,12 +252,7 @@ class OuterProductLayer(Layer):
     def front(self, embed_layer, ids, do_inner, out, out_ld, signal_flags=None, epoch=0):
         """``out[b] = [rows | <e_i, e_j> | e_j^T W_p e_i | 0]`` straight from the tables (DL/model/pnn.py:28-49).
         ``signal_flags`` / ``epoch``: publish ``out`` per 128-row tile for a tower launched behind (chained launches)."""
-        pk = getattr(self, "_front_pack", None)
-        if pk is None or pk[0] != self._version:
-            n = _lib.query("ctrhot_pnn_pack_bytes", self.field_num, self.k)
-            buf = torch.empty(n, dtype=torch.uint8, device=self.device)
-            _lib.call("ctrhot_pnn_pack", ptr(self.w), self.field_num, self.k, ptr(buf), stream_ptr())
-            pk = self._front_pack = (self._version, buf)
+        pk = (None, self._pack())
         ids, kind, ids_ld = ids_arg(ids)
         E = embed_layer
         _lib.call("ctrhot_pnn_front_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ids.shape[0],

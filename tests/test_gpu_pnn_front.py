@@ -126,3 +126,26 @@ def test_pnn_chained_launches_equal_stream_order(lib):
     assert m._chain is not None and m._chain[2] == 7
     for i in range(7):
         assert torch.equal(got[i], want[i % 3]), i
+
+
+@pytest.mark.parametrize("B,F", [(128, 26), (4099, 26), (1000, 5), (300, 28)])
+def test_outer_product_layer_k8_on_the_tensor_pipe(lib, B, F):
+    """OuterProductLayer.call (DL/layer/interaction.py:201-215) on a gathered [B, F, 8] tensor: the tcgen05 path against the float64
+    oracle and against the CUDA-core kernel; written into a strided view without touching the columns around it."""
+    from recommender_system_b200.layer import OuterProductLayer
+    rng = np.random.default_rng(B + F)
+    e = S.f32(rng.uniform(-0.5, 0.5, (B, F, 8)))
+    P = F * (F - 1) // 2
+    W = S.f32(rng.normal(0, 0.1, (8, P, 8)))
+    op = OuterProductLayer()
+    op.build(e.shape)
+    op.set_weights([W])
+    want = O.outer_product_layer(e.astype(np.float64), W.astype(np.float64))
+    ed = torch.from_numpy(e).cuda()
+    big = torch.full((B, P + 40), 7.0, dtype=torch.float32, device="cuda")
+    l0 = __import__("recommender_system_b200")._lib.LAUNCHES[0]
+    op(ed, out=big[:, 8:8 + P])
+    close_rel(big[:, 8:8 + P].cpu().numpy(), want)
+    assert torch.all(big[:, :8] == 7.0) and torch.all(big[:, 8 + P:] == 7.0)
+    op.tensor_pipe = False
+    close_rel(npy(op(ed)), want)
