@@ -512,23 +512,32 @@ fm_dense_reg_kernel(const float* __restrict__ x, int64_t x_ld, int n, int64_t B,
   }
   __syncthreads();
   const float bias = __ldg(w0);
-  for (int64_t b0 = warp * S; b0 < B; b0 += nwarps * S) {
-    float4 xv[S][NQ];
+  // the rows of the next S samples are requested as soon as the FMAs over the current ones are done (xv is dead from there on),
+  // so their latency runs under the shuffle reductions; the first version's capture had 57 % of its stall samples on the first use
+  // of a freshly loaded row at 16 resident warps per SM
+  float4 xv[S][NQ];
+  auto fetch = [&](int64_t b0) {
 #pragma unroll
     for (int s = 0; s < S; ++s) {
 #pragma unroll
       for (int i = 0; i < NQ; ++i) {
         const int q = lane + 32 * i;
-        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (q < n4 && b0 + s < B) {
-          t = ldg_nc_f4(x + (b0 + s) * x_ld + 4 * q);
-          if (4 * q + 3 >= n) {                          // last piece: columns past n are not part of x
-            if (4 * q + 1 >= n) t.y = 0.f;
-            if (4 * q + 2 >= n) t.z = 0.f;
-            t.w = 0.f;
-          }
+        xv[s][i] = (q < n4 && b0 + s < B) ? ldg_nc_f4(x + (b0 + s) * x_ld + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  };
+  fetch(warp * S);
+  for (int64_t b0 = warp * S; b0 < B; b0 += nwarps * S) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        if (q < n4 && 4 * q + 3 >= n) {                  // last piece: columns past n are not part of x
+          if (4 * q + 1 >= n) xv[s][i].y = 0.f;
+          if (4 * q + 2 >= n) xv[s][i].z = 0.f;
+          xv[s][i].w = 0.f;
         }
-        xv[s][i] = t;
       }
     }
     float acc[S][KF + 2];
@@ -554,6 +563,7 @@ fm_dense_reg_kernel(const float* __restrict__ x, int64_t x_ld, int n, int64_t B,
                            fmaf(xv[s][i].z * xv[s][i].z, w.z, fmaf(xv[s][i].w * xv[s][i].w, w.w, acc[s][KF + 1]))));
       }
     }
+    fetch(b0 + nwarps * S);
 #pragma unroll
     for (int s = 0; s < S; ++s) {
       // reduce-scatter of the KF + 2 partial sums (padded to 16): 31 shuffles instead of 5 per value, then one more
@@ -841,6 +851,20 @@ cross_reg_kernel(const float* __restrict__ x, int64_t x_ld, int d, int64_t B, in
   for (int j = threadIdx.x; j < dp; j += blockDim.x) s_f[j] = (final_w && j < d) ? __ldg(final_w + j) : 0.f;
   __syncthreads();
   const bool out_vec = out && ((out_ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  // the rows of the NEXT S samples are fetched while the current ones are worked on (the capture of the first version showed
+  // 46 % of the warp slots filled and a third of all stall samples on the first use of the loaded row: latency, not bandwidth)
+  float4 xn[S][NQ];
+  auto fetch = [&](int64_t b0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+#pragma unroll
+      for (int i = 0; i < NQ; ++i) {
+        const int q = lane + 32 * i;
+        xn[s][i] = (q < d4 && b0 + s < B) ? ldg_nc_f4(x + (b0 + s) * x_ld + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  };
+  fetch(warp * S);
   for (int64_t b0 = warp * S; b0 < B; b0 += nwarps * S) {
     float4 x0[S][NQ], xl[S][NQ];
 #pragma unroll
@@ -848,18 +872,16 @@ cross_reg_kernel(const float* __restrict__ x, int64_t x_ld, int d, int64_t B, in
 #pragma unroll
       for (int i = 0; i < NQ; ++i) {
         const int q = lane + 32 * i;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (q < d4 && b0 + s < B) {
-          v = ldg_nc_f4(x + (b0 + s) * x_ld + 4 * q);
-          if (4 * q + 3 >= d) {                        // last piece: whatever lies behind column d is not part of x
-            if (4 * q + 1 >= d) v.y = 0.f;
-            if (4 * q + 2 >= d) v.z = 0.f;
-            v.w = 0.f;
-          }
+        float4 v = xn[s][i];
+        if (q < d4 && 4 * q + 3 >= d) {                // last piece: whatever lies behind column d is not part of x
+          if (4 * q + 1 >= d) v.y = 0.f;
+          if (4 * q + 2 >= d) v.z = 0.f;
+          v.w = 0.f;
         }
         x0[s][i] = v; xl[s][i] = v;
       }
     }
+    fetch(b0 + nwarps * S);
     for (int l = 0; l < L; ++l) {
       const float4* wl = reinterpret_cast<const float4*>(s_w + (size_t)l * dp);
       const float4* bl = reinterpret_cast<const float4*>(s_b + (size_t)l * dp);
@@ -1241,8 +1263,12 @@ extern "C" int ctrhot_cross_f32(const float* x, int64_t x_ld, int d, int64_t B, 
     do {                                                                                                              \
       CTRHOT_CUDA_OK(cudaFuncSetAttribute(cross_reg_kernel<NQ, S>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
                                           (int)sm2), "cross attr");                                                  \
-      cross_reg_kernel<NQ, S><<<warp_grid(B, 8 * S), 256, sm2, ST(stream)>>>(x, x_ld, d, B, L, w, b, out, out_ld,     \
-                                                                            final_w, dot);                           \
+      int occ = 0;                                                                                                    \
+      CTRHOT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cross_reg_kernel<NQ, S>, 256, sm2), "cross occ"); \
+      /* persistent: one wave of resident CTAs, every warp walks its share (a capped grid of several waves left 13 % idle) */ \
+      int64_t g_ = (B + 8 * S - 1) / (8 * S);                                                                         \
+      if (occ > 0 && g_ > (int64_t)kNumSMs * occ) g_ = (int64_t)kNumSMs * occ;                                        \
+      cross_reg_kernel<NQ, S><<<(int)g_, 256, sm2, ST(stream)>>>(x, x_ld, d, B, L, w, b, out, out_ld, final_w, dot);  \
     } while (0)
     if (nq <= 1) CROSS_LAUNCH(1, 4);
     else if (nq <= 2) CROSS_LAUNCH(2, 4);
