@@ -851,6 +851,8 @@ cross_reg_kernel(const float* __restrict__ x, int64_t x_ld, int d, int64_t B, in
   for (int j = threadIdx.x; j < dp; j += blockDim.x) s_f[j] = (final_w && j < d) ? __ldg(final_w + j) : 0.f;
   __syncthreads();
   const bool out_vec = out && ((out_ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  const bool out_full = out_vec && out_ld >= dp;       // rows padded to whole 16-byte pieces: the last piece is stored whole (its
+                                                       // columns past d are zeros: x, w and b are zero there)
   // the rows of the NEXT S samples are fetched while the current ones are worked on (the capture of the first version showed
   // 46 % of the warp slots filled and a third of all stall samples on the first use of the loaded row: latency, not bandwidth)
   float4 xn[S][NQ];
@@ -924,9 +926,9 @@ cross_reg_kernel(const float* __restrict__ x, int64_t x_ld, int d, int64_t B, in
         for (int i = 0; i < NQ; ++i) {
           const int q = lane + 32 * i;
           if (q >= d4) continue;
-          if (out_vec && 4 * q + 3 < d) stg_na_f4(row + 4 * q, xl[s][i]);
+          if (out_vec && (4 * q + 3 < d || out_full)) stg_na_f4(row + 4 * q, xl[s][i]);
         }
-        if (!out_vec || (d & 3)) {
+        if (!out_vec || ((d & 3) && !out_full)) {
           // rows that are not 16-byte aligned (out_ld = d = 429): the row goes through a per-warp smem slab so that every
           // store instruction writes 32 CONSECUTIVE floats (4 sectors per instruction instead of 16; shuffles were slower)
           float* slab = s_f + dp + (size_t)(threadIdx.x >> 5) * dp;
@@ -1020,6 +1022,21 @@ dice_vec_kernel(const float* __restrict__ x, int64_t total4, int h4, const float
     const float p = 1.0f / (1.0f + expf(-(t - s_m[c]) * s_r[c]));
     return s_a[c] * (1.0f - p) * t + p * t;
   };
+  // four loads in flight per thread (one was 32 KB per SM at full occupancy: short of what the HBM latency needs)
+  for (; i + 3 * stride < total4; i += 4 * stride) {
+    float4 v[4];
+    int c[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      v[u] = ldg_nc_f4(x + (i + u * stride) * 4);
+      c[u] = c4 * 4;
+      c4 += step;
+      if (c4 >= h4) c4 -= h4;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      stg_na_f4(out + (i + u * stride) * 4, make_float4(one(v[u].x, c[u]), one(v[u].y, c[u] + 1), one(v[u].z, c[u] + 2), one(v[u].w, c[u] + 3)));
+  }
   for (; i < total4; i += stride) {
     const float4 v = ldg_nc_f4(x + i * 4);
     const int c = c4 * 4;

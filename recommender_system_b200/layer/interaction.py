@@ -106,7 +106,9 @@ class CrossLayer(Layer):
         x = as_device_f32(inputs, self.device)
         require_cuda(x, "CrossLayer")
         w, b = self.stacked()
-        out = torch.empty_like(x)
+        d = x.shape[1]
+        # rows padded to whole 16-byte pieces (a [B, d] view of them is returned): every store of the kernel is a full float4
+        out = torch.empty((x.shape[0], (d + 3) // 4 * 4), dtype=torch.float32, device=x.device)[:, :d]
         _lib.call("ctrhot_cross_f32", ptr(x), x.stride(0), x.shape[1], x.shape[0], self.layer_num, ptr(w), ptr(b),
                   ptr(out), out.stride(0), 0, 0, stream_ptr())
         return out
