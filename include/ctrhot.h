@@ -385,6 +385,21 @@ int ctrhot_dcn_first_layer_tf32(const float* arena, const int64_t* row_off, int 
                                 const float* h_combine, int n_combine, float* h, int64_t h_ld, float* side_out,
                                 int cluster, int* err_flag, int32_t* signal_flags, int epoch, void* stream);
 
+/* ---- 8(f) rank 3, DCN under compile_fit (DL/model/dcn.py:15-34, CrossLayer DL/layer/interaction.py:49-83) ---------------------
+ * One step of keras SGD(lr) on mean clipped BCE + CrossLayer's l2 regularisers (reg_w sum w_l^2 + reg_b sum b_l^2 per layer),
+ * updating in place: the embedding rows that were looked up, the L cross weights / biases (h_cross_w / h_cross_b: HOST arrays of
+ * L device pointers to the [n, 1] vectors), the tower (h_layers as for ctrhot_deepfm_train_step_f32: ReLU hidden layers with
+ * Dropout, then Dense(h -> 1)) and the final Dense(n + 1 -> 1) (final_k [n + 1], final_b [1]).  Cross backward per layer, with
+ * g = dL/dx_{l+1} and c = g . x_0:  dw_l = sum_b c x_l,  db_l = sum_b g,  dL/dx_l = g + c w_l,  dL/dx_0 += g s_l.
+ * n = D + F k <= 1024, L <= 8.  loss_out = {mean BCE before the update, correct predictions}.  fp32 CUDA cores. */
+int64_t ctrhot_dcn_train_workspace_bytes(int64_t B, int n, int L, const ctrhot_dense_desc* h_layers, int n_layers);
+int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                              int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y, int64_t B,
+                              const int64_t* h_cross_w, const int64_t* h_cross_b, int L, float reg_w, float reg_b,
+                              const ctrhot_dense_desc* h_layers, int n_layers, float* final_k, float* final_b,
+                              float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
+                              int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

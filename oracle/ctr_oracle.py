@@ -713,3 +713,87 @@ def hash_layer(x, num_buckets, mask_zero=False):
         h = farm_fingerprint64(s) % nb
         out[i] = (h + 1) * (s != b"0") if mask_zero else h
     return out.reshape(a.shape)
+
+
+def dcn_loss(dense, ids, tables, cross_ws, cross_bs, hidden, out, final, y, reg_w, reg_b, drop_masks=None):
+    """What keras minimises for DCN (DL/model/dcn.py:15-34 under compile_fit): mean clipped BCE + CrossLayer's l2 regularisers
+    (interaction.py:59-70: reg_w sum w_l^2 + reg_b sum b_l^2 per layer).  -> (total, bce, p)."""
+    ids = ids_to_int(ids)
+    x = np.concatenate([np.asarray(dense, np.float64)] + [tables[f][ids[:, f]] for f in range(len(tables))], axis=1)
+    xl = x
+    for w, b in zip(cross_ws, cross_bs):
+        xl = x * (xl @ w) + b[:, 0][None, :] + xl
+    h = x
+    for l, (k, bb) in enumerate(hidden):
+        h = np.maximum(h @ k + bb, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+    d = h @ out[0] + out[1]
+    p = sigmoid(np.concatenate([xl, d], axis=1) @ final[0] + final[1])[:, 0]
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    reg = sum(reg_w * float(np.sum(w ** 2)) for w in cross_ws) + sum(reg_b * float(np.sum(b ** 2)) for b in cross_bs)
+    return bce + reg, bce, p
+
+
+def dcn_train_step(dense, ids, tables, cross_ws, cross_bs, hidden, out, final, y, lr, reg_w, reg_b, drop_masks=None):
+    """One step of keras SGD(lr) on `dcn_loss`; analytic gradients (PARITY UNPINNED against the reference like deepfm_train_step,
+    pinned by finite differences).  Cross layer l: x_{l+1} = x_0 s_l + b_l + x_l with s_l = x_l . w_l, so with g = dL/dx_{l+1} and
+    c = g . x_0:  dw_l = sum_b c x_l,  db_l = sum_b g,  dL/dx_l = g + c w_l,  dL/dx_0 += g s_l.
+    -> ((tables, cross_ws, cross_bs, hidden, out, final) updated, mean BCE before the update, number of correct predictions)."""
+    ids = ids_to_int(ids)
+    B, D, F = ids.shape[0], np.asarray(dense).shape[1], len(tables)
+    x = np.concatenate([np.asarray(dense, np.float64)] + [tables[f][ids[:, f]] for f in range(F)], axis=1)
+    n = x.shape[1]
+    xs, ss = [x], []
+    for w, b in zip(cross_ws, cross_bs):
+        s = xs[-1] @ w                                                   # [B, 1]
+        ss.append(s)
+        xs.append(x * s + b[:, 0][None, :] + xs[-1])
+    acts = [x]
+    for l, (k, bb) in enumerate(hidden):
+        h = np.maximum(acts[-1] @ k + bb, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+        acts.append(h)
+    d = acts[-1] @ out[0] + out[1]                                       # [B, 1]
+    fk, fb = final
+    p = sigmoid(xs[-1] @ fk[:n] + d * fk[n] + fb)[:, 0]
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    correct = int(np.sum((p > 0.5) == (y > 0.5)))
+    dz = (np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B)[:, None]   # [B, 1]
+    new_final = (fk - lr * np.concatenate([xs[-1].T @ dz, d.T @ dz], axis=0), fb - lr * np.sum(dz))
+    # tower, from d dnn = dz * fk[n]
+    gd = dz * fk[n, 0]
+    g = gd @ out[0].T
+    new_out = (out[0] - lr * (acts[-1].T @ gd), out[1] - lr * np.sum(gd))
+    new_hidden = [None] * len(hidden)
+    for l in range(len(hidden) - 1, -1, -1):
+        k, bb = hidden[l]
+        m = (acts[l + 1] > 0).astype(np.float64)
+        if drop_masks is not None:
+            m = m * np.max(drop_masks[l])
+        g = g * m
+        gin = g @ k.T
+        new_hidden[l] = (k - lr * (acts[l].T @ g), bb - lr * np.sum(g, axis=0))
+        g = gin
+    dx = g
+    # cross layers, last to first
+    g = dz @ fk[:n].T                                                    # dL/dx_L
+    dx0 = np.zeros_like(x)
+    new_ws, new_bs = [None] * len(cross_ws), [None] * len(cross_bs)
+    for l in range(len(cross_ws) - 1, -1, -1):
+        c = np.sum(g * x, axis=1, keepdims=True)
+        new_ws[l] = cross_ws[l] - lr * (xs[l].T @ c + 2 * reg_w * cross_ws[l])
+        new_bs[l] = cross_bs[l] - lr * (np.sum(g, axis=0)[:, None] + 2 * reg_b * cross_bs[l])
+        dx0 = dx0 + g * ss[l]
+        g = g + c @ cross_ws[l].T
+    dx = dx + g + dx0
+    new_tables = [t.copy() for t in tables]
+    off = D
+    for f in range(F):
+        kdim = tables[f].shape[1]
+        np.add.at(new_tables[f], ids[:, f], -lr * dx[:, off:off + kdim])
+        off += kdim
+    return (new_tables, new_ws, new_bs, new_hidden, new_out, new_final), bce, correct

@@ -256,6 +256,86 @@ __global__ void tr_embed_sgd_kernel(float* __restrict__ arena, const int64_t* __
   }
 }
 
+// ---------------------------------------------------------------- DCN (DL/model/dcn.py:15-34): cross layers, forward and backward
+// One warp per sample.  x_{l+1} = x_0 s_l + b_l + x_l with s_l = x_l . w_l (CrossLayer.call, interaction.py:75-83); the rows
+// x_1 .. x_L and the scalars s_l are kept for the backward pass; zc[b] = x_L . fk[0:n] is the cross half of the logit.
+constexpr int TR_NJ = 32;                                       // columns per lane: n <= 1024
+struct TrCross { const float* w[TR_MAXL]; const float* b[TR_MAXL]; };
+__global__ void __launch_bounds__(256)
+tr_cross_fwd_kernel(const float* __restrict__ x, int n, int64_t B, int L, TrCross cw, const float* __restrict__ fk,
+                    float* __restrict__ XL, float* __restrict__ S, float* __restrict__ zc) {
+  const int lane = threadIdx.x & 31;
+  const int64_t b = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  float x0[TR_NJ], xl[TR_NJ];
+#pragma unroll
+  for (int i = 0; i < TR_NJ; ++i) {
+    const int j = lane + 32 * i;
+    x0[i] = j < n ? x[b * n + j] : 0.f;
+    xl[i] = x0[i];
+  }
+  for (int l = 0; l < L; ++l) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < TR_NJ; ++i) { const int j = lane + 32 * i; if (j < n) s = fmaf(xl[i], cw.w[l][j], s); }
+    s = warp_sum(s);
+    if (lane == 0) S[(int64_t)l * B + b] = s;
+#pragma unroll
+    for (int i = 0; i < TR_NJ; ++i) {
+      const int j = lane + 32 * i;
+      if (j < n) { xl[i] = fmaf(x0[i], s, cw.b[l][j]) + xl[i]; XL[((int64_t)l * B + b) * n + j] = xl[i]; }
+    }
+  }
+  float z = 0.f;
+#pragma unroll
+  for (int i = 0; i < TR_NJ; ++i) { const int j = lane + 32 * i; if (j < n) z = fmaf(xl[i], fk[j], z); }
+  z = warp_sum(z);
+  if (lane == 0) zc[b] = z;
+}
+// out[b] = a[b] (or 0) + v[b] * s[0]
+__global__ void tr_axpy_scalar_kernel(const float* __restrict__ a, const float* __restrict__ v, const float* __restrict__ s,
+                                      int64_t B, float* __restrict__ out) {
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < B; b += (int64_t)gridDim.x * blockDim.x)
+    out[b] = (a ? a[b] : 0.f) + v[b] * s[0];
+}
+// g = dL/dx_{l+1}, from g_L = dz fk[0:n] down: G[l] = g (for db_l), C[l] = c = g . x_0 (for dw_l = sum_b c x_l),
+// dx_0 += g s_l, g += c w_l (the OLD w_l: the updates run after this kernel); finally dx[b] += g + dx_0
+__global__ void __launch_bounds__(256)
+tr_cross_bwd_kernel(const float* __restrict__ x, int n, int64_t B, int L, TrCross cw, const float* __restrict__ fk,
+                    const float* __restrict__ dz, const float* __restrict__ S, float* __restrict__ G, float* __restrict__ C,
+                    float* __restrict__ dx) {
+  const int lane = threadIdx.x & 31;
+  const int64_t b = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  float x0[TR_NJ], g[TR_NJ], d0[TR_NJ];
+  const float dzb = dz[b];
+#pragma unroll
+  for (int i = 0; i < TR_NJ; ++i) {
+    const int j = lane + 32 * i;
+    x0[i] = j < n ? x[b * n + j] : 0.f;
+    g[i] = j < n ? dzb * fk[j] : 0.f;
+    d0[i] = 0.f;
+  }
+  for (int l = L - 1; l >= 0; --l) {
+    float c = 0.f;
+#pragma unroll
+    for (int i = 0; i < TR_NJ; ++i) {
+      const int j = lane + 32 * i;
+      if (j < n) { G[((int64_t)l * B + b) * n + j] = g[i]; c = fmaf(g[i], x0[i], c); }
+    }
+    c = warp_sum(c);
+    if (lane == 0) C[(int64_t)l * B + b] = c;
+    const float s = S[(int64_t)l * B + b];
+#pragma unroll
+    for (int i = 0; i < TR_NJ; ++i) {
+      const int j = lane + 32 * i;
+      if (j < n) { d0[i] = fmaf(g[i], s, d0[i]); g[i] = fmaf(c, cw.w[l][j], g[i]); }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < TR_NJ; ++i) { const int j = lane + 32 * i; if (j < n) dx[b * n + j] += g[i] + d0[i]; }
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -435,5 +515,129 @@ extern "C" int ctrhot_fm_train_step_f32(const float* x, int64_t x_ld, int n, con
   tr_loss_kernel<<<1, 256, 0, st>>>(fm, nullptr, nullptr, y, B, dz, loss_out, nullptr, 1.0f);
   tr_fm_update(st, x, n, B, dz, 1.0f, fm_w0, fm_w1, fm_v, k_fm, reg_w, reg_v, lr, xv, t, s2, nullptr);
   CTRHOT_LAUNCH_OK("ctrhot_fm_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- DCN training step (DL/model/dcn.py under compile_fit)
+namespace {
+struct TrDcnLayout { int64_t x, XL, S, G, C, zc, zt, d, dz, gd, dx, g0, g1, h[TR_MAXL], total; int maxw; };
+bool tr_dcn_layout(int64_t B, int n, int L, const ctrhot_dense_desc* Ld, int n_layers, TrDcnLayout& w) {
+  if (!Ld || n_layers < 2 || n_layers > TR_MAXL || B < 0 || n <= 0 || n > 32 * TR_NJ || L < 1 || L > TR_MAXL) return false;
+  if (Ld[0].in_dim != n || Ld[n_layers - 1].out_dim != 1) return false;
+  int64_t o = 0;
+  auto take = [&](int64_t cnt) { const int64_t at = o; o += (cnt + 3) / 4 * 4; return at; };
+  w.maxw = n;
+  for (int l = 0; l < n_layers; ++l) {
+    if (l > 0 && Ld[l].in_dim != Ld[l - 1].out_dim) return false;
+    if (l < n_layers - 1 && Ld[l].act != CTRHOT_ACT_RELU) return false;
+    if (!Ld[l].weight) return false;
+    if (Ld[l].out_dim > w.maxw) w.maxw = Ld[l].out_dim;
+  }
+  w.x = take(B * n); w.XL = take((int64_t)L * B * n); w.S = take((int64_t)L * B); w.G = take((int64_t)L * B * n);
+  w.C = take((int64_t)L * B); w.zc = take(B); w.zt = take(B); w.d = take(B); w.dz = take(B); w.gd = take(B); w.dx = take(B * n);
+  w.g0 = take(B * (int64_t)w.maxw); w.g1 = take(B * (int64_t)w.maxw);
+  for (int l = 0; l < n_layers - 1; ++l) w.h[l] = take(B * (int64_t)Ld[l].out_dim);
+  w.total = o;
+  return true;
+}
+}  // namespace
+
+extern "C" int64_t ctrhot_dcn_train_workspace_bytes(int64_t B, int n, int L, const ctrhot_dense_desc* h_layers, int n_layers) {
+  TrDcnLayout w;
+  if (!tr_dcn_layout(B, n, L, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  return w.total * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                         int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y, int64_t B,
+                                         const int64_t* h_cross_w, const int64_t* h_cross_b, int L, float reg_w, float reg_b,
+                                         const ctrhot_dense_desc* h_layers, int n_layers, float* final_k, float* final_b,
+                                         float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                         int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_dcn_train_step_f32");
+  if (!arena || !row_off || !ids || !y || !h_cross_w || !h_cross_b || !final_k || !final_b || !loss_out || !workspace || F <= 0 ||
+      k <= 0 || D < 0 || (D > 0 && !dense) || B <= 0 || ids_ld < F || (D > 0 && dense_ld < D)) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (!(dropout >= 0.f && dropout < 1.f) || !(lr >= 0.f)) return CTRHOT_EARG;
+  const int n = D + F * k;
+  TrDcnLayout w;
+  if (!tr_dcn_layout(B, n, L, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < w.total * (int64_t)sizeof(float) || !aligned16(workspace)) return CTRHOT_EARG;
+  TrCross cw;
+  for (int l = 0; l < L; ++l) {
+    cw.w[l] = reinterpret_cast<const float*>((uintptr_t)h_cross_w[l]);
+    cw.b[l] = reinterpret_cast<const float*>((uintptr_t)h_cross_b[l]);
+    if (!cw.w[l] || !cw.b[l]) return CTRHOT_EARG;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  float *x = ws + w.x, *XL = ws + w.XL, *S = ws + w.S, *G = ws + w.G, *C = ws + w.C, *zc = ws + w.zc, *zt = ws + w.zt,
+        *d = ws + w.d, *dz = ws + w.dz, *gd = ws + w.gd, *dx = ws + w.dx;
+  const int NH = n_layers - 1, M = (int)B;
+  const int wgrid = (int)((B + 7) / 8);
+  // ---- forward: x, cross layers, tower, logit = x_L . fk[0:n] + d fk[n] + fb
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_gather_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag, nullptr);
+  else
+    tr_gather_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, n, err_flag, nullptr);
+  tr_cross_fwd_kernel<<<wgrid, 256, 0, st>>>(x, n, B, L, cw, final_k, XL, S, zc);
+  const float* in = x;
+  int in_dim = n;
+  for (int l = 0; l < NH; ++l) {
+    float* h = ws + w.h[l];
+    const int N = h_layers[l].out_dim;
+    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
+    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    in = h; in_dim = N;
+  }
+  tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, d, 1, M, 1, in_dim, 1.f, 0.f);
+  {
+    // d[b] += b_d  (one element per sample; the tower's last bias), then zt = zc + d * fk[n]
+    if (h_layers[NH].bias) tr_bias_relu_drop_kernel<<<tr_grid(B, 256), 256, 0, st>>>(d, h_layers[NH].bias, 1, B, 0, 0.f, 0, 0, nullptr);
+    tr_axpy_scalar_kernel<<<tr_grid(B, 256), 256, 0, st>>>(zc, d, final_k + n, B, zt);
+  }
+  tr_loss_kernel<<<1, 256, 0, st>>>(zt, nullptr, final_b, y, B, dz, loss_out, nullptr, 1.0f);
+  tr_axpy_scalar_kernel<<<tr_grid(B, 256), 256, 0, st>>>(nullptr, dz, final_k + n, B, gd);      // d loss / d d = dz fk[n] (old fk)
+  // ---- backward through the tower from gd
+  float* g = ws + w.g0;
+  float* gn = ws + w.g1;
+  {
+    float* wo = const_cast<float*>(h_layers[NH].weight);
+    tr_gemm(st, gd, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 1.f, 0.f);
+    tr_gemm(st, in, 1, in_dim, gd, 1, 1, wo, 1, in_dim, 1, M, -lr, 1.f);
+    if (h_layers[NH].bias)
+      tr_colsum_kernel<<<1, 1024, 0, st>>>(gd, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
+    float* tmp = g; g = gn; gn = tmp;
+  }
+  for (int l = NH - 1; l >= 0; --l) {
+    const int N = h_layers[l].out_dim, Kd = h_layers[l].in_dim;
+    const float* h = ws + w.h[l];
+    const float* hin = l > 0 ? ws + w.h[l - 1] : x;
+    float* W = const_cast<float*>(h_layers[l].weight);
+    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    float* dst = l > 0 ? gn : dx;
+    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
+    if (h_layers[l].bias)
+      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
+  }
+  // ---- cross layers backward (old w_l, old fk), dx += its share; then the updates of w_l, b_l and of the final Dense
+  tr_cross_bwd_kernel<<<wgrid, 256, 0, st>>>(x, n, B, L, cw, final_k, dz, S, G, C, dx);
+  for (int l = 0; l < L; ++l) {
+    const float* xin = l > 0 ? XL + (int64_t)(l - 1) * B * n : x;
+    tr_gemm(st, xin, 1, n, C + (int64_t)l * B, 1, 1, const_cast<float*>(cw.w[l]), 1, n, 1, M, -lr, 1.f - 2.f * lr * reg_w);
+    tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(G + (int64_t)l * B * n, n, nullptr, B, n, 0, const_cast<float*>(cw.b[l]), -lr,
+                                                     1.f - 2.f * lr * reg_b);
+  }
+  tr_gemm(st, XL + (int64_t)(L - 1) * B * n, 1, n, dz, 1, 1, final_k, 1, n, 1, M, -lr, 1.f);   // fk[0:n] -= lr x_L^T dz
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(d, 1, dz, B, 1, 0, final_k + n, -lr, 1.f);              // fk[n]   -= lr sum_b d dz
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
+  // ---- embedding rows
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr, nullptr);
+  else
+    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr, nullptr);
+  CTRHOT_LAUNCH_OK("ctrhot_dcn_train_step_f32");
   return CTRHOT_OK;
 }

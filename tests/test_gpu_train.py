@@ -210,3 +210,82 @@ def test_fm_step_and_compile_fit(lib):
     assert m.history[-1][0] < 0.8 * m.history[0][0] and m.history[-1][1] > 0.85, m.history
     p = npy(m(X))[:, 0]
     assert np.mean((p > 0.5) == (y > 0.5)) > 0.85
+
+
+# ------------------------------------------------------------------ DCN (DL/model/dcn.py under compile_fit)
+def make_dcn(vocab, k_embed, L, hidden, dropout=0.0, seed=1):
+    from recommender_system_b200.model.criteo import DCN
+    set_seed(seed)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": int(v), "embed_dim": k_embed} for i, v in enumerate(vocab)]]
+    m = DCN(fc, list(hidden), 1, "relu", L, 1e-2, 2e-2, embed_dim=k_embed, precision="fp32")
+    m.build(None)
+    m.dense_layer.dropout = dropout
+    rng = np.random.default_rng(seed)
+    upd = {}
+    for n, w in m.named_weights().items():
+        if n.endswith("bias"):                                    # keras' zero biases would hide mistakes in their gradients
+            upd[n] = rng.normal(0, 0.1, tuple(w.shape))
+    m.set_weights({n: np.asarray(v, np.float32) for n, v in upd.items()})
+    return m
+
+
+def dcn_params(m):
+    tables = [npy(t) for t in m.embed_layer.emb_layers]
+    ws = [npy(t) for t in m.cross_layer.cross_weight]
+    bs = [npy(t) for t in m.cross_layer.cross_bias]
+    hidden = [(npy(k), npy(b)) for k, b in m.dense_layer.hidden]
+    out = (npy(m.dense_layer.output[0]), npy(m.dense_layer.output[1]))
+    return tables, ws, bs, hidden, out, (npy(m.out_kernel), npy(m.out_bias))
+
+
+@pytest.mark.parametrize("B,vocab,k_embed,L,hidden,rate", [
+    (32, [50, 7, 1000, 3] + [20] * 22, 8, 6, (256, 128, 64), 0.0),        # the reference's __main__: layer_num 6, batch 32
+    (1, [11] * 26, 4, 1, (16,), 0.0),
+    (257, [50, 7, 1000, 3] + [20] * 22, 16, 3, (64, 32), 0.2),
+    (4096, [5000] * 26, 16, 3, (400, 400, 400), 0.2),                     # BASELINE config 3's cross depth and tower
+])
+def test_dcn_one_step_against_the_oracle(lib, B, vocab, k_embed, L, hidden, rate):
+    from recommender_system_b200.utils.compile_fit import _DCNTrainer
+    m = make_dcn(vocab, k_embed, L, hidden, rate)
+    dense, ids, y = batch(vocab, B, seed=B + 1)
+    before = dcn_params(m)
+    lr, seed = 0.05, 4321
+    tr = _DCNTrainer(m)
+    dev = m.device
+    out = tr.train_on_batch(torch.from_numpy(dense).to(dev), torch.from_numpy(ids).to(dev), torch.from_numpy(y).to(dev), lr, seed=seed)
+    torch.cuda.synchronize()
+    masks = kernel_masks(seed, hidden, B, rate) if rate > 0 else None
+    want, bce, correct = O.dcn_train_step(dense.astype(np.float64), ids, *before, y.astype(np.float64), lr, 1e-2, 2e-2, masks)
+    got = dcn_params(m)
+    assert abs(float(out[0]) - bce) <= 2e-6 * max(1.0, bce) and int(out[1]) == correct
+    for f in range(len(vocab)):
+        close(got[0][f], want[0][f], before[0][f], "table %d" % f)
+        untouched = np.setdiff1d(np.arange(vocab[f]), ids[:, f])
+        np.testing.assert_array_equal(got[0][f][untouched], before[0][f][untouched])
+    for l in range(L):
+        close(got[1][l], want[1][l], before[1][l], "cross w %d" % l)
+        close(got[2][l], want[2][l], before[2][l], "cross b %d" % l)
+    for l in range(len(hidden)):
+        close(got[3][l][0], want[3][l][0], before[3][l][0], "kernel %d" % l)
+        close(got[3][l][1], want[3][l][1], before[3][l][1], "bias %d" % l)
+    close(got[4][0], want[4][0], before[4][0], "dnn out kernel"); close(got[4][1], want[4][1], before[4][1], "dnn out bias")
+    close(got[5][0], want[5][0], before[5][0], "final kernel"); close(got[5][1], want[5][1], before[5][1], "final bias")
+
+
+def test_dcn_compile_fit_learns_and_serves(lib):
+    """compile_fit(DCN, X, y) lowers the loss on a planted rule; the forward path (whole-model kernel, re-packed after the
+    weights moved) then agrees with the float64 oracle on the trained weights."""
+    vocab = [30, 7, 120, 50] + [9] * 22
+    rng = np.random.default_rng(3)
+    N = 1500 + 17
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.concatenate([rng.random((N, 13)), ids], axis=1).astype(np.float32)
+    y = (ids[:, 0] < 15).astype(np.float32)
+    m = make_dcn(vocab, 8, 3, (64, 32), 0.0, seed=5)
+    compile_fit(m, X, y, batch_size=32, epochs=6, sgd=0.1, verbose=False)
+    assert m.history[-1][0] < 0.7 * m.history[0][0] and m.history[-1][1] > 0.9, m.history
+    p = dcn_params(m)
+    want = O.dcn_model(X[:300].astype(np.float64), p[0], p[1], p[2], p[3], p[4], p[5])
+    got = npy(m(X[:300]))
+    assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))

@@ -211,3 +211,53 @@ def test_farm_fingerprint_pins():
     assert O.farm_fingerprint64(b"") == 0x9ae16a3b2f90404f
     got = O.hash_layer(np.array([[0, 5], [123456789012, 7]]), 10, True)
     assert got.shape == (2, 2) and got[0, 0] == 0 and np.all(got[got != 0] >= 1) and np.all(got <= 9)
+
+
+def test_dcn_train_step_gradients():
+    """oracle.dcn_train_step's analytic update against central finite differences of oracle.dcn_loss (duplicate ids, dropout
+    masks, both regularisers, 3 cross layers)."""
+    rng = np.random.default_rng(7)
+    B, D, F, k, L = 9, 3, 4, 4, 3
+    vocab = [5, 7, 3, 6]
+    tables = [rng.normal(0, 0.3, (v, k)) for v in vocab]
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1)
+    ids[1] = ids[0]
+    dense = rng.random((B, D))
+    n = D + F * k
+    ws = [rng.normal(0, 0.2, (n, 1)) for _ in range(L)]
+    bs = [rng.normal(0, 0.2, (n, 1)) for _ in range(L)]
+    hidden = [(rng.normal(0, 0.3, (n, 8)), rng.normal(0, 0.1, 8)), (rng.normal(0, 0.3, (8, 5)), rng.normal(0, 0.1, 5))]
+    out = (rng.normal(0, 0.3, (5, 1)), rng.normal(0, 0.1, 1))
+    final = (rng.normal(0, 0.3, (n + 1, 1)), rng.normal(0, 0.1, 1))
+    y = rng.integers(0, 2, B).astype(float)
+    masks = [(rng.random((B, 8)) >= 0.25) / 0.75, (rng.random((B, 5)) >= 0.25) / 0.75]
+    lr, rw, rb = 0.05, 1e-2, 2e-2
+    new, bce, _ = O.dcn_train_step(dense, ids, tables, ws, bs, hidden, out, final, y, lr, rw, rb, masks)
+    base = O.dcn_loss(dense, ids, tables, ws, bs, hidden, out, final, y, rw, rb, masks)
+    assert abs(base[1] - bce) < 1e-12
+    eps = 1e-6
+
+    def fd(obj, idx, rebuild):
+        a, b = obj.copy(), obj.copy()
+        a[idx] += eps; b[idx] -= eps
+        return (O.dcn_loss(*rebuild(a), y, rw, rb, masks)[0] - O.dcn_loss(*rebuild(b), y, rw, rb, masks)[0]) / (2 * eps)
+
+    def args(tables_=tables, ws_=ws, bs_=bs, hidden_=hidden, out_=out, final_=final):
+        return dense, ids, tables_, ws_, bs_, hidden_, out_, final_
+
+    for l in range(L):
+        for idx in [(0, 0), (n - 1, 0), (5, 0)]:
+            gw = fd(ws[l], idx, lambda a: args(ws_=ws[:l] + [a] + ws[l + 1:]))
+            assert abs(gw - ((ws[l] - new[1][l]) / lr)[idx]) < 1e-7
+            gb = fd(bs[l], idx, lambda a: args(bs_=bs[:l] + [a] + bs[l + 1:]))
+            assert abs(gb - ((bs[l] - new[2][l]) / lr)[idx]) < 1e-7
+    for idx in [(0, 0), (n, 0), (7, 0)]:
+        gf = fd(final[0], idx, lambda a: args(final_=(a, final[1])))
+        assert abs(gf - ((final[0] - new[5][0]) / lr)[idx]) < 1e-7
+    gk = fd(hidden[0][0], (4, 3), lambda a: args(hidden_=[(a, hidden[0][1]), hidden[1]]))
+    assert abs(gk - ((hidden[0][0] - new[3][0][0]) / lr)[4, 3]) < 1e-7
+    go = fd(out[0], (2, 0), lambda a: args(out_=(a, out[1])))
+    assert abs(go - ((out[0] - new[4][0]) / lr)[2, 0]) < 1e-7
+    for f, r in [(0, int(ids[0, 0])), (2, int(ids[3, 2]))]:
+        gt = fd(tables[f], (r, 1), lambda a: args(tables_=tables[:f] + [a] + tables[f + 1:]))
+        assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, 1]) < 1e-7
