@@ -400,6 +400,19 @@ int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, int F, int k
                               float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
                               int64_t workspace_bytes, int* err_flag, void* stream);
 
+/* ---- 8(f) rank 3, PNN's own training loop, DL/model/pnn.py:74-85 (batch 32, SGD(0.01), loss = mean binary_crossentropy(y, model(X))
+ * with PNN.call's RAW output: keras clips it to [1e-7, 1 - 1e-7], so d loss / dz = (z - y) / (z (1 - z)) / B inside the clip and 0
+ * outside; tape.gradient(loss) leaves the layers' regularisers out).  mode: 1 inner, 2 outer, 3 both (tower input =
+ * [rows | inner | outer], no FGCNN branch).  Product layers backward, pair p = (i, j), i < j, upstream gi_p / go_p:
+ * de_i += gi e_j + go W_p^T e_j,  de_j += gi e_i + go W_p e_i,  dW[a, p, c] = sum_b go e_j[a] e_i[c].  Updates in place: the
+ * looked-up arena rows, outer_w [k, P, k], the tower.  loss_out = {loss before the update, predictions with z > 0.5 == y}. */
+int64_t ctrhot_pnn_train_workspace_bytes(int64_t B, int F, int k, int mode, const ctrhot_dense_desc* h_layers, int n_layers);
+int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                              int64_t ids_ld, const float* y, int64_t B, float* outer_w, int mode,
+                              const ctrhot_dense_desc* h_layers, int n_layers, float lr, float dropout,
+                              uint64_t seed, float* loss_out, void* workspace, int64_t workspace_bytes,
+                              int* err_flag, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

@@ -797,3 +797,93 @@ def dcn_train_step(dense, ids, tables, cross_ws, cross_bs, hidden, out, final, y
         np.add.at(new_tables[f], ids[:, f], -lr * dx[:, off:off + kdim])
         off += kdim
     return (new_tables, new_ws, new_bs, new_hidden, new_out, new_final), bce, correct
+
+
+# keras' binary_crossentropy clips in the output's dtype: epsilon_ = float32(1e-7) and the upper bound is the float32 value of
+# 1 - epsilon_ = 0.99999988 (not 1 - 1e-7).  It matters for PNN, whose raw output reaches the clip on a fair share of samples.
+_BCE_LO = float(np.float32(1e-7))
+_BCE_HI = float(np.float32(1.0) - np.float32(1e-7))
+
+
+def pnn_loss(ids, tables, outer_w, hidden, out, y, mode, drop_masks=None):
+    """What the reference's own PNN training loop minimises (DL/model/pnn.py:74-85): tf.reduce_mean(binary_crossentropy(y, pre))
+    with pre = model(X) -- PNN.call ends WITHOUT a sigmoid (:52-53), so keras' BCE clips the raw output to [1e-7, 1 - 1e-7] and
+    takes logs of that; tape.gradient(loss, ...) leaves the layers' regularisers out.  -> (bce, pre)."""
+    ids = ids_to_int(ids)
+    z = np.stack([tables[f][ids[:, f]] for f in range(len(tables))], axis=1)
+    feats = [z.reshape(z.shape[0], -1)]
+    if mode in ("inner", "both"):
+        feats.append(inner_product_layer(z))
+    if mode in ("outer", "both"):
+        feats.append(outer_product_layer(z, outer_w))
+    h = np.concatenate(feats, axis=1)
+    for l, (k, bb) in enumerate(hidden):
+        h = np.maximum(h @ k + bb, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+    pre = (h @ out[0] + out[1])[:, 0]
+    pc = np.clip(pre, _BCE_LO, _BCE_HI)
+    return float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc)))), pre
+
+
+def pnn_train_step(ids, tables, outer_w, hidden, out, y, lr, mode, drop_masks=None):
+    """One step of SGD(lr) on `pnn_loss` (PARITY UNPINNED against the reference, pinned by finite differences).  With pair p = (i, j),
+    i < j:  inner_p = <e_i, e_j>,  outer_p = sum_a e_j[a] sum_c W[a, p, c] e_i[c]; for upstream gradients gi_p, go_p:
+    de_i += gi e_j + go W_p^T e_j,  de_j += gi e_i + go W_p e_i,  dW[a, p, c] = sum_b go e_j[a] e_i[c].  The clipped BCE on a raw
+    output has gradient (pre - y) / (pre (1 - pre)) / B inside (1e-7, 1 - 1e-7) and zero outside.
+    -> ((tables, outer_w, hidden, out) updated, loss before the update, number of correct predictions (pre > 0.5))."""
+    ids = ids_to_int(ids)
+    B, F = ids.shape[0], len(tables)
+    K = tables[0].shape[1]
+    z = np.stack([tables[f][ids[:, f]] for f in range(F)], axis=1)       # [B, F, K]
+    row, col = pair_index(F)
+    P = len(row)
+    feats = [z.reshape(B, -1)]
+    if mode in ("inner", "both"):
+        feats.append(inner_product_layer(z))
+    if mode in ("outer", "both"):
+        feats.append(outer_product_layer(z, outer_w))
+    acts = [np.concatenate(feats, axis=1)]
+    for l, (k, bb) in enumerate(hidden):
+        h = np.maximum(acts[-1] @ k + bb, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+        acts.append(h)
+    pre = (acts[-1] @ out[0] + out[1])[:, 0]
+    pc = np.clip(pre, _BCE_LO, _BCE_HI)
+    loss = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    correct = int(np.sum((pre > 0.5) == (y > 0.5)))
+    dz = (np.where((pre > _BCE_LO) & (pre < _BCE_HI), (pc - y) / (pc * (1 - pc)), 0.0) / B)[:, None]
+    g = dz @ out[0].T
+    new_out = (out[0] - lr * (acts[-1].T @ dz), out[1] - lr * np.sum(dz))
+    new_hidden = [None] * len(hidden)
+    for l in range(len(hidden) - 1, -1, -1):
+        k, bb = hidden[l]
+        m = (acts[l + 1] > 0).astype(np.float64)
+        if drop_masks is not None:
+            m = m * np.max(drop_masks[l])
+        g = g * m
+        gin = g @ k.T
+        new_hidden[l] = (k - lr * (acts[l].T @ g), bb - lr * np.sum(g, axis=0))
+        g = gin
+    de = g[:, :F * K].reshape(B, F, K).copy()
+    colp = F * K
+    new_w = outer_w
+    ei, ej = z[:, row, :], z[:, col, :]                                  # [B, P, K]
+    if mode in ("inner", "both"):
+        gi = g[:, colp:colp + P]
+        colp += P
+        np.add.at(de, (slice(None), row), gi[:, :, None] * ej)
+        np.add.at(de, (slice(None), col), gi[:, :, None] * ei)
+    if mode in ("outer", "both"):
+        go = g[:, colp:colp + P]
+        # W[a, p, c]: t_i[b, p, c] = sum_a W[a, p, c] e_j[b, p, a];  t_j[b, p, a] = sum_c W[a, p, c] e_i[b, p, c]
+        t_i = np.einsum("apc,bpa->bpc", outer_w, ej)
+        t_j = np.einsum("apc,bpc->bpa", outer_w, ei)
+        np.add.at(de, (slice(None), row), go[:, :, None] * t_i)
+        np.add.at(de, (slice(None), col), go[:, :, None] * t_j)
+        new_w = outer_w - lr * np.einsum("bp,bpa,bpc->apc", go, ej, ei)
+    new_tables = [t.copy() for t in tables]
+    for f in range(F):
+        np.add.at(new_tables[f], ids[:, f], -lr * de[:, f, :])
+    return (new_tables, new_w, new_hidden, new_out), loss, correct

@@ -83,7 +83,8 @@ template <int IDKIND>
 __global__ void tr_gather_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
                                  const void* __restrict__ ids, int64_t ids_ld, const float* __restrict__ dense, int64_t dense_ld,
                                  int D, int64_t B, float* __restrict__ x, int n, int* __restrict__ err_flag,
-                                 const TrCtl* __restrict__ ctl) {
+                                 const TrCtl* __restrict__ ctl, int64_t x_ld = 0) {
+  if (x_ld == 0) x_ld = n;
   const int64_t r0 = ctl ? ctl->row0 : 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t b = i / n;
@@ -99,7 +100,7 @@ __global__ void tr_gather_kernel(const float* __restrict__ arena, const int64_t*
       if (!ok && err_flag) *err_flag = 1;
       v = ok ? arena[(row_off[f] + id) * k + e] : 0.f;
     }
-    x[i] = v;
+    x[b * x_ld + c] = v;
   }
 }
 
@@ -334,6 +335,74 @@ tr_cross_bwd_kernel(const float* __restrict__ x, int n, int64_t B, int L, TrCros
   }
 #pragma unroll
   for (int i = 0; i < TR_NJ; ++i) { const int j = lane + 32 * i; if (j < n) dx[b * n + j] += g[i] + d0[i]; }
+}
+
+// ---------------------------------------------------------------- PNN (DL/model/pnn.py:74-85, the reference's own training loop)
+// keras' binary_crossentropy on the model's RAW output (PNN.call has no sigmoid): p = clip(z, 1e-7, 1 - 1e-7),
+// loss = mean -(y log p + (1 - y) log(1 - p)), d loss / dz = (p - y) / (p (1 - p)) / B inside the clip and 0 outside.
+__global__ void tr_raw_bce_kernel(const float* __restrict__ z, const float* __restrict__ b_out, const float* __restrict__ y,
+                                  int64_t B, float* __restrict__ dz, float* __restrict__ loss_out) {
+  __shared__ float s_loss[256], s_ok[256];
+  float l = 0.f, ok = 0.f;
+  for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
+    const float zz = z[b] + (b_out ? b_out[0] : 0.f);
+    const float eps = 1e-7f;
+    const float pc = fminf(fmaxf(zz, eps), 1.f - eps);
+    const float yb = y[b];
+    l -= yb * __logf(pc) + (1.f - yb) * __logf(1.f - pc);
+    ok += ((zz > 0.5f) == (yb > 0.5f)) ? 1.f : 0.f;
+    dz[b] = (zz > eps && zz < 1.f - eps) ? (pc - yb) / (pc * (1.f - pc)) / (float)B : 0.f;
+  }
+  s_loss[threadIdx.x] = l; s_ok[threadIdx.x] = ok;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o >= 1; o >>= 1) {
+    if (threadIdx.x < o) { s_loss[threadIdx.x] += s_loss[threadIdx.x + o]; s_ok[threadIdx.x] += s_ok[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { loss_out[0] = s_loss[0] / (float)B; loss_out[1] = s_ok[0]; }
+}
+__device__ __forceinline__ int tr_pair(int i, int j, int F) { return i * (2 * F - i - 1) / 2 + (j - i - 1); }   // i < j
+// Product layers backward, one thread per (sample, field f, component t): with pair p = (i, j), i < j, upstream gi_p (inner) and
+// go_p (outer):  de_i[c] += gi e_j[c] + go sum_a W[a, p, c] e_j[a];  de_j[a] += gi e_i[a] + go sum_c W[a, p, c] e_i[c].
+// dx's flat columns (already holding the tower's gradient for them) are updated in place; its product columns are read.
+__global__ void tr_pnn_prod_bwd_kernel(const float* __restrict__ x, int n, int64_t B, int F, int K, int P,
+                                       const float* __restrict__ W, int col_in, int col_out, float* __restrict__ dx) {
+  const int fk = F * K;
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < B * fk; i0 += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i0 / fk;
+    const int c0 = (int)(i0 - b * fk), f = c0 / K, t = c0 - f * K;
+    const float* e = x + b * n;
+    const float* g = dx + b * n;
+    float acc = 0.f;
+    for (int o = 0; o < F; ++o) {
+      if (o == f) continue;
+      const bool first = f < o;                              // f plays e_i (index c) when it is the smaller field of the pair
+      const int p = first ? tr_pair(f, o, F) : tr_pair(o, f, F);
+      const float* eo = e + o * K;
+      if (col_in >= 0) acc = fmaf(g[col_in + p], eo[t], acc);
+      if (col_out >= 0) {
+        float s = 0.f;
+        if (first) { for (int a = 0; a < K; ++a) s = fmaf(W[((int64_t)a * P + p) * K + t], eo[a], s); }
+        else { for (int c = 0; c < K; ++c) s = fmaf(W[((int64_t)t * P + p) * K + c], eo[c], s); }
+        acc = fmaf(g[col_out + p], s, acc);
+      }
+    }
+    dx[b * n + c0] += acc;
+  }
+}
+// W[a, p, c] -= lr sum_b go[b, p] e_j[b, a] e_i[b, c]   (one thread per weight, batch summed in order: deterministic)
+__global__ void tr_pnn_dw_kernel(const float* __restrict__ x, int n, int64_t B, int F, int K, int P, const float* __restrict__ dx,
+                                 int col_out, float* __restrict__ W, float lr) {
+  const int total = K * P * K;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int c = idx % K, p = (idx / K) % P, a = idx / (K * P);
+    int i = 0, rem = p;
+    while (rem >= F - 1 - i) { rem -= F - 1 - i; ++i; }
+    const int j = i + 1 + rem;
+    float s = 0.f;
+    for (int64_t b = 0; b < B; ++b) s = fmaf(dx[b * n + col_out + p] * x[b * n + j * K + a], x[b * n + i * K + c], s);
+    W[idx] -= lr * s;
+  }
 }
 
 }  // namespace ctrhot
@@ -639,5 +708,110 @@ extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, i
   else
     tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr, nullptr);
   CTRHOT_LAUNCH_OK("ctrhot_dcn_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- PNN training step (DL/model/pnn.py:74-85)
+namespace {
+struct TrPnnLayout { int64_t x, z, dz, dx, g0, g1, h[TR_MAXL], total; int maxw, n, P; };
+bool tr_pnn_layout(int64_t B, int F, int k, int mode, const ctrhot_dense_desc* Ld, int n_layers, TrPnnLayout& w) {
+  if (!Ld || n_layers < 2 || n_layers > TR_MAXL || B < 0 || F < 2 || k < 1 || mode < 1 || mode > 3) return false;
+  w.P = F * (F - 1) / 2;
+  w.n = F * k + w.P * (mode == 3 ? 2 : 1);
+  if (Ld[0].in_dim != w.n || Ld[n_layers - 1].out_dim != 1) return false;
+  int64_t o = 0;
+  auto take = [&](int64_t cnt) { const int64_t at = o; o += (cnt + 3) / 4 * 4; return at; };
+  w.maxw = w.n;
+  for (int l = 0; l < n_layers; ++l) {
+    if (l > 0 && Ld[l].in_dim != Ld[l - 1].out_dim) return false;
+    if (l < n_layers - 1 && Ld[l].act != CTRHOT_ACT_RELU) return false;
+    if (!Ld[l].weight) return false;
+    if (Ld[l].out_dim > w.maxw) w.maxw = Ld[l].out_dim;
+  }
+  w.x = take(B * w.n); w.z = take(B); w.dz = take(B); w.dx = take(B * w.n);
+  w.g0 = take(B * (int64_t)w.maxw); w.g1 = take(B * (int64_t)w.maxw);
+  for (int l = 0; l < n_layers - 1; ++l) w.h[l] = take(B * (int64_t)Ld[l].out_dim);
+  w.total = o;
+  return true;
+}
+}  // namespace
+
+extern "C" int64_t ctrhot_pnn_train_workspace_bytes(int64_t B, int F, int k, int mode, const ctrhot_dense_desc* h_layers,
+                                                    int n_layers) {
+  TrPnnLayout w;
+  if (!tr_pnn_layout(B, F, k, mode, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  return w.total * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                         int64_t ids_ld, const float* y, int64_t B, float* outer_w, int mode,
+                                         const ctrhot_dense_desc* h_layers, int n_layers, float lr, float dropout,
+                                         uint64_t seed, float* loss_out, void* workspace, int64_t workspace_bytes,
+                                         int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_pnn_train_step_f32");
+  if (!arena || !row_off || !ids || !y || !loss_out || !workspace || B <= 0 || ids_ld < F) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (!(dropout >= 0.f && dropout < 1.f) || !(lr >= 0.f) || ((mode & 2) && !outer_w)) return CTRHOT_EARG;
+  TrPnnLayout w;
+  if (!tr_pnn_layout(B, F, k, mode, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < w.total * (int64_t)sizeof(float) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  float *x = ws + w.x, *z = ws + w.z, *dz = ws + w.dz, *dx = ws + w.dx;
+  const int n = w.n, P = w.P, fk = F * k, NH = n_layers - 1, M = (int)B;
+  const int col_in = (mode & 1) ? fk : -1, col_out = (mode & 2) ? fk + ((mode & 1) ? P : 0) : -1;
+  // ---- forward: x = [rows | inner | outer] (exact fp32 product kernels), tower, raw output
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_gather_kernel<CTRHOT_IDS_I32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, nullptr, 0, 0, B, x, fk, err_flag, nullptr, n);
+  else
+    tr_gather_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, nullptr, 0, 0, B, x, fk, err_flag, nullptr, n);
+  int rc = CTRHOT_OK;
+  if (mode & 1) rc = ctrhot_pnn_inner_f32(x, n, F, k, B, x + col_in, n, stream);
+  if (rc != CTRHOT_OK) return rc;
+  if (mode & 2) rc = ctrhot_pnn_outer_f32(x, n, F, k, B, outer_w, x + col_out, n, stream);
+  if (rc != CTRHOT_OK) return rc;
+  const float* in = x;
+  int in_dim = n;
+  for (int l = 0; l < NH; ++l) {
+    float* h = ws + w.h[l];
+    const int N = h_layers[l].out_dim;
+    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
+    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    in = h; in_dim = N;
+  }
+  tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, z, 1, M, 1, in_dim, 1.f, 0.f);
+  tr_raw_bce_kernel<<<1, 256, 0, st>>>(z, h_layers[NH].bias, y, B, dz, loss_out);
+  // ---- backward through the tower
+  float* g = ws + w.g0;
+  float* gn = ws + w.g1;
+  {
+    float* wo = const_cast<float*>(h_layers[NH].weight);
+    tr_gemm(st, dz, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 1.f, 0.f);
+    tr_gemm(st, in, 1, in_dim, dz, 1, 1, wo, 1, in_dim, 1, M, -lr, 1.f);
+    if (h_layers[NH].bias)
+      tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
+    float* tmp = g; g = gn; gn = tmp;
+  }
+  for (int l = NH - 1; l >= 0; --l) {
+    const int N = h_layers[l].out_dim, Kd = h_layers[l].in_dim;
+    const float* h = ws + w.h[l];
+    const float* hin = l > 0 ? ws + w.h[l - 1] : x;
+    float* W = const_cast<float*>(h_layers[l].weight);
+    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    float* dst = l > 0 ? gn : dx;
+    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
+    if (h_layers[l].bias)
+      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
+  }
+  // ---- product layers backward into dx's flat columns (old W), then W, then the embedding rows
+  tr_pnn_prod_bwd_kernel<<<tr_grid(B * fk, 256), 256, 0, st>>>(x, n, B, F, k, P, outer_w, col_in, col_out, dx);
+  if (mode & 2) tr_pnn_dw_kernel<<<tr_grid((int64_t)k * P * k, 128), 128, 0, st>>>(x, n, B, F, k, P, dx, col_out, outer_w, lr);
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dx, n, lr, nullptr);
+  else
+    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dx, n, lr, nullptr);
+  CTRHOT_LAUNCH_OK("ctrhot_pnn_train_step_f32");
   return CTRHOT_OK;
 }

@@ -261,3 +261,45 @@ def test_dcn_train_step_gradients():
     for f, r in [(0, int(ids[0, 0])), (2, int(ids[3, 2]))]:
         gt = fd(tables[f], (r, 1), lambda a: args(tables_=tables[:f] + [a] + tables[f + 1:]))
         assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, 1]) < 1e-7
+
+
+@pytest.mark.parametrize("mode", ["both", "inner", "outer"])
+def test_pnn_train_step_gradients(mode):
+    """oracle.pnn_train_step against central finite differences of oracle.pnn_loss: duplicate ids, dropout masks, raw outputs on
+    both sides of keras' clip (inside (0, 1): gradient, outside: none)."""
+    rng = np.random.default_rng(11)
+    B, F, K = 10, 5, 4
+    vocab = [6, 4, 7, 5, 3]
+    tables = [rng.normal(0, 0.5, (v, K)) for v in vocab]
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1)
+    ids[1] = ids[0]
+    P = F * (F - 1) // 2
+    W = rng.normal(0, 0.3, (K, P, K))
+    n = F * K + P * (2 if mode == "both" else 1)
+    hidden = [(rng.normal(0, 0.3, (n, 7)), rng.normal(0, 0.1, 7)), (rng.normal(0, 0.4, (7, 5)), rng.normal(0, 0.1, 5))]
+    out = (rng.normal(0, 0.5, (5, 1)), np.array([0.45]))
+    y = rng.integers(0, 2, B).astype(float)
+    masks = [(rng.random((B, 7)) >= 0.25) / 0.75, (rng.random((B, 5)) >= 0.25) / 0.75]
+    lr = 0.05
+    new, loss, _ = O.pnn_train_step(ids, tables, W, hidden, out, y, lr, mode, masks)
+    base, pre = O.pnn_loss(ids, tables, W, hidden, out, y, mode, masks)
+    assert abs(base - loss) < 1e-12
+    assert np.any((pre > 0.01) & (pre < 0.99)) and np.all(np.abs(pre - 1e-7) > 1e-3) and np.all(np.abs(pre - 1 + 1e-7) > 1e-3)
+    eps = 1e-6
+
+    def fd(obj, idx, rebuild):
+        a, b = obj.copy(), obj.copy()
+        a[idx] += eps; b[idx] -= eps
+        return (O.pnn_loss(*rebuild(a), y, mode, masks)[0] - O.pnn_loss(*rebuild(b), y, mode, masks)[0]) / (2 * eps)
+
+    for f, r, c in [(0, int(ids[0, 0]), 1), (3, int(ids[4, 3]), 2), (4, int(ids[2, 4]), 0)]:
+        gt = fd(tables[f], (r, c), lambda a: (ids, tables[:f] + [a] + tables[f + 1:], W, hidden, out))
+        assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, c]) < 1e-6
+    if mode != "inner":
+        for idx in [(0, 0, 0), (3, P - 1, 2), (1, 4, 3)]:
+            gw = fd(W, idx, lambda a: (ids, tables, a, hidden, out))
+            assert abs(gw - ((W - new[1]) / lr)[idx]) < 1e-6
+    gk = fd(hidden[0][0], (n - 1, 3), lambda a: (ids, tables, W, [(a, hidden[0][1]), hidden[1]], out))
+    assert abs(gk - ((hidden[0][0] - new[2][0][0]) / lr)[n - 1, 3]) < 1e-6
+    go = fd(out[0], (2, 0), lambda a: (ids, tables, W, hidden, (a, out[1])))
+    assert abs(go - ((out[0] - new[3][0]) / lr)[2, 0]) < 1e-6
