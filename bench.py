@@ -354,6 +354,26 @@ def train_leg(dev, timeit):
         res["B%d" % B] = {"gpu_steps_per_s": 1e3 / ms, "gpu_samples_per_s": B / ms * 1e3, "cpu_steps_per_s": 1e3 / cpu_ms,
                           "gpu_graph_steps_per_s": 1e3 / ms_g, "gpu_graph_samples_per_s": B / ms_g * 1e3,
                           "cpu_cores": torch.get_num_threads(), "first_step_loss_gpu": gpu_loss, "first_step_loss_cpu": cpu_loss}
+    # the other models compile_fit trains (call by call, the reference's batch of 32): DCN with its __main__'s 6 cross layers
+    # (DL/model/dcn.py:44-45) and PNN's own loop in mode "both" (DL/model/pnn.py:62-85)
+    from recommender_system_b200.model.criteo import DCN, PNN
+    from recommender_system_b200.utils.compile_fit import _DCNTrainer, _PNNTrainer
+    fc = synth.criteo_feature_columns(vocab, 8)
+    dense, ids = synth.criteo_batch(32, vocab, seed=3)
+    y = (np.random.default_rng(4).random(32) < 0.3).astype(np.float32)
+    d, i, yy = (torch.from_numpy(a).to(dev) for a in (dense, ids, y))
+    set_seed(5)
+    md = DCN(fc, [256, 128, 64], 1, "relu", 6, embed_dim=8, precision="fp32", check_ids=False, device=dev)
+    md.build(None)
+    td = _DCNTrainer(md, dropout=0.0)
+    ms_d = timeit(lambda: td.train_on_batch(d, i, yy, 0.01), 50, 5)
+    set_seed(5)
+    mp = PNN(fc, "both", [256, 128, 64], 1, "relu", 0.0, embed_dim=8, precision="fp32", check_ids=False, device=dev)
+    mp.build(None)
+    tp = _PNNTrainer(mp, dropout=0.0)
+    ms_p = timeit(lambda: tp.train_on_batch(i, yy, 0.01), 50, 5)
+    res["other_models_B32"] = {"dcn_L6_steps_per_s": 1e3 / ms_d, "pnn_both_steps_per_s": 1e3 / ms_p,
+                               "note": "call by call (no graph replay), fp32 CUDA cores"}
     return res
 
 
