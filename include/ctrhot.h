@@ -413,6 +413,19 @@ int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, int F, int k
                               uint64_t seed, float* loss_out, void* workspace, int64_t workspace_bytes,
                               int* err_flag, void* stream);
 
+/* ---- 8(f) rank 3, WideDeep under compile_fit (DL/model/wideDeep.py:14-34; WideLayer DL/layer/interaction.py:11-26 with its
+ * l2(1e-4) on w) -- p = sigmoid(0.5 (wide + deep)), the wide input [dense | dense again | one 0/1 block per field]
+ * (DL/utils/dataset.py:53-58) never materialised: col_off = DEVICE int64 [F + 1], first wide column of every field (2 D + ...),
+ * ids at or beyond a field's width have no column.  Updates in place: w0, w [n_wide] (decay on all of it, the dense columns
+ * twice, the looked-up one-hot columns by atomic adds), the arena rows, the tower (which sees the embeddings only). */
+int64_t ctrhot_widedeep_train_workspace_bytes(int64_t B, int n, const ctrhot_dense_desc* h_layers, int n_layers);
+int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                   int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                                   int64_t B, float* wide_w0, float* wide_w, const int64_t* col_off, int64_t n_wide,
+                                   float reg_w, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
+                                   float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                   int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

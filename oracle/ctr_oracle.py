@@ -887,3 +887,76 @@ def pnn_train_step(ids, tables, outer_w, hidden, out, y, lr, mode, drop_masks=No
     for f in range(F):
         np.add.at(new_tables[f], ids[:, f], -lr * de[:, f, :])
     return (new_tables, new_w, new_hidden, new_out), loss, correct
+
+
+def _widedeep_wide_input(dense, ids, widths):
+    """The wide input as the reference's loader lays it out for Wide&Deep (DL/utils/dataset.py:53-58): the dense block, the
+    get_dummies frame -- which starts with the dense block AGAIN -- and one 0/1 block per sparse field (width = labels seen)."""
+    B = ids.shape[0]
+    blocks = [np.asarray(dense, np.float64), np.asarray(dense, np.float64)]
+    for f, wd in enumerate(widths):
+        oh = np.zeros((B, wd))
+        ok = ids[:, f] < wd
+        oh[np.arange(B)[ok], ids[ok, f]] = 1.0
+        blocks.append(oh)
+    return np.concatenate(blocks, axis=1)
+
+
+def widedeep_loss(dense, ids, tables, wide_w0, wide_w, widths, hidden, out, y, reg_w, drop_masks=None):
+    """keras' objective for WideDeep (DL/model/wideDeep.py:14-34 under compile_fit): mean clipped BCE of
+    sigmoid(0.5 (wide + deep)) + WideLayer's l2(1e-4) on w (interaction.py:19-22).  -> (total, bce, p)."""
+    ids = ids_to_int(ids)
+    xw = _widedeep_wide_input(dense, ids, widths)
+    wide = (wide_w0 + xw @ wide_w)[:, 0]
+    h = np.concatenate([tables[f][ids[:, f]] for f in range(len(tables))], axis=1)
+    for l, (k, bb) in enumerate(hidden):
+        h = np.maximum(h @ k + bb, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+    deep = (h @ out[0] + out[1])[:, 0]
+    p = sigmoid(0.5 * (wide + deep))
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    return bce + reg_w * float(np.sum(wide_w ** 2)), bce, p
+
+
+def widedeep_train_step(dense, ids, tables, wide_w0, wide_w, widths, hidden, out, y, lr, reg_w, drop_masks=None):
+    """One step of keras SGD(lr) on `widedeep_loss` (PARITY UNPINNED against the reference, pinned by finite differences).
+    -> ((tables, wide_w0, wide_w, hidden, out) updated, mean BCE before the update, number of correct predictions)."""
+    ids = ids_to_int(ids)
+    B, F = ids.shape[0], len(tables)
+    xw = _widedeep_wide_input(dense, ids, widths)
+    wide = (wide_w0 + xw @ wide_w)[:, 0]
+    acts = [np.concatenate([tables[f][ids[:, f]] for f in range(F)], axis=1)]
+    for l, (k, bb) in enumerate(hidden):
+        h = np.maximum(acts[-1] @ k + bb, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+        acts.append(h)
+    deep = (acts[-1] @ out[0] + out[1])[:, 0]
+    p = sigmoid(0.5 * (wide + deep))
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    correct = int(np.sum((p > 0.5) == (y > 0.5)))
+    dh = (0.5 * np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B)[:, None]
+    new_w0 = wide_w0 - lr * np.sum(dh)
+    new_w = wide_w - lr * (xw.T @ dh + 2 * reg_w * wide_w)
+    g = dh @ out[0].T
+    new_out = (out[0] - lr * (acts[-1].T @ dh), out[1] - lr * np.sum(dh))
+    new_hidden = [None] * len(hidden)
+    for l in range(len(hidden) - 1, -1, -1):
+        k, bb = hidden[l]
+        m = (acts[l + 1] > 0).astype(np.float64)
+        if drop_masks is not None:
+            m = m * np.max(drop_masks[l])
+        g = g * m
+        gin = g @ k.T
+        new_hidden[l] = (k - lr * (acts[l].T @ g), bb - lr * np.sum(g, axis=0))
+        g = gin
+    new_tables = [t.copy() for t in tables]
+    off = 0
+    for f in range(F):
+        kdim = tables[f].shape[1]
+        np.add.at(new_tables[f], ids[:, f], -lr * g[:, off:off + kdim])
+        off += kdim
+    return (new_tables, new_w0, new_w, new_hidden, new_out), bce, correct

@@ -405,6 +405,38 @@ __global__ void tr_pnn_dw_kernel(const float* __restrict__ x, int n, int64_t B, 
   }
 }
 
+// ---------------------------------------------------------------- Wide&Deep (DL/model/wideDeep.py:14-34): the wide side on ids
+// wide input = [dense (D) | dense again (D) | one 0/1 block per field] (DL/utils/dataset.py:53-58), never materialised:
+// wide[b] = w0 + sum_j dense_bj (w_j + w_{D+j}) + sum_f [id_bf < width_f] w[col_off[f] + id_bf]
+template <int IDKIND>
+__global__ void tr_wide_fwd_kernel(const float* __restrict__ dense, int64_t dense_ld, int D, const void* __restrict__ ids,
+                                   int64_t ids_ld, int F, const int64_t* __restrict__ col_off, const float* __restrict__ w0,
+                                   const float* __restrict__ w, int64_t B, float* __restrict__ wide) {
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < B; b += (int64_t)gridDim.x * blockDim.x) {
+    float s = w0[0];
+    for (int j = 0; j < D; ++j) s = fmaf(dense[b * dense_ld + j], w[j] + w[D + j], s);
+    for (int f = 0; f < F; ++f) {
+      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      if (id >= 0 && id < col_off[f + 1] - col_off[f]) s += w[col_off[f] + id];
+    }
+    wide[b] = s;
+  }
+}
+__global__ void tr_scale_kernel(float* __restrict__ w, int64_t n, float a) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) w[i] *= a;
+}
+// w[col_off[f] + id] -= lr * gscale * dz[b]   (one thread per (sample, field); columns hit by several samples add up)
+template <int IDKIND>
+__global__ void tr_wide_onehot_sgd_kernel(const void* __restrict__ ids, int64_t ids_ld, int F, const int64_t* __restrict__ col_off,
+                                          const float* __restrict__ dz, float gl, int64_t B, float* __restrict__ w) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * F; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / F;
+    const int f = (int)(i - b * F);
+    const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+    if (id >= 0 && id < col_off[f + 1] - col_off[f]) atomicAdd(w + col_off[f] + id, -gl * dz[b]);
+  }
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -813,5 +845,114 @@ extern "C" int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, i
   else
     tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dx, n, lr, nullptr);
   CTRHOT_LAUNCH_OK("ctrhot_pnn_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- Wide&Deep training step
+namespace {
+struct TrWdLayout { int64_t x, wide, dnn, dz, dx, g0, g1, h[TR_MAXL], total; int maxw; };
+bool tr_wd_layout(int64_t B, int n, const ctrhot_dense_desc* Ld, int n_layers, TrWdLayout& w) {
+  if (!Ld || n_layers < 2 || n_layers > TR_MAXL || B < 0 || n <= 0) return false;
+  if (Ld[0].in_dim != n || Ld[n_layers - 1].out_dim != 1) return false;
+  int64_t o = 0;
+  auto take = [&](int64_t cnt) { const int64_t at = o; o += (cnt + 3) / 4 * 4; return at; };
+  w.maxw = n;
+  for (int l = 0; l < n_layers; ++l) {
+    if (l > 0 && Ld[l].in_dim != Ld[l - 1].out_dim) return false;
+    if (l < n_layers - 1 && Ld[l].act != CTRHOT_ACT_RELU) return false;
+    if (!Ld[l].weight) return false;
+    if (Ld[l].out_dim > w.maxw) w.maxw = Ld[l].out_dim;
+  }
+  w.x = take(B * n); w.wide = take(B); w.dnn = take(B); w.dz = take(B); w.dx = take(B * n);
+  w.g0 = take(B * (int64_t)w.maxw); w.g1 = take(B * (int64_t)w.maxw);
+  for (int l = 0; l < n_layers - 1; ++l) w.h[l] = take(B * (int64_t)Ld[l].out_dim);
+  w.total = o;
+  return true;
+}
+}  // namespace
+
+extern "C" int64_t ctrhot_widedeep_train_workspace_bytes(int64_t B, int n, const ctrhot_dense_desc* h_layers, int n_layers) {
+  TrWdLayout w;
+  if (!tr_wd_layout(B, n, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  return w.total * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                              int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                                              int64_t B, float* wide_w0, float* wide_w, const int64_t* col_off, int64_t n_wide,
+                                              float reg_w, const ctrhot_dense_desc* h_layers, int n_layers, float lr,
+                                              float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                              int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_widedeep_train_step_f32");
+  if (!arena || !row_off || !ids || !y || !wide_w0 || !wide_w || !col_off || !loss_out || !workspace || F <= 0 || k <= 0 || D < 0 ||
+      (D > 0 && !dense) || B <= 0 || ids_ld < F || (D > 0 && dense_ld < D) || n_wide < 2 * (int64_t)D) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (!(dropout >= 0.f && dropout < 1.f) || !(lr >= 0.f)) return CTRHOT_EARG;
+  const int n = F * k;                                           // the deep side sees the embeddings only
+  TrWdLayout w;
+  if (!tr_wd_layout(B, n, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < w.total * (int64_t)sizeof(float) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  float *x = ws + w.x, *wide = ws + w.wide, *dnn = ws + w.dnn, *dz = ws + w.dz, *dx = ws + w.dx;
+  const int NH = n_layers - 1, M = (int)B;
+  // ---- forward
+  if (ids_kind == CTRHOT_IDS_I32) {
+    tr_gather_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, nullptr, 0, 0, B, x, n, err_flag, nullptr);
+    tr_wide_fwd_kernel<CTRHOT_IDS_I32><<<tr_grid(B, 128), 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, wide_w0, wide_w, B, wide);
+  } else {
+    tr_gather_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, nullptr, 0, 0, B, x, n, err_flag, nullptr);
+    tr_wide_fwd_kernel<CTRHOT_IDS_F32><<<tr_grid(B, 128), 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, wide_w0, wide_w, B, wide);
+  }
+  const float* in = x;
+  int in_dim = n;
+  for (int l = 0; l < NH; ++l) {
+    float* h = ws + w.h[l];
+    const int N = h_layers[l].out_dim;
+    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
+    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    in = h; in_dim = N;
+  }
+  tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, dnn, 1, M, 1, in_dim, 1.f, 0.f);
+  tr_loss_kernel<<<1, 256, 0, st>>>(wide, dnn, h_layers[NH].bias, y, B, dz, loss_out, nullptr, 0.5f);
+  // ---- backward through the tower (d deep = dz / 2)
+  float* g = ws + w.g0;
+  float* gn = ws + w.g1;
+  {
+    float* wo = const_cast<float*>(h_layers[NH].weight);
+    tr_gemm(st, dz, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 0.5f, 0.f);
+    tr_gemm(st, in, 1, in_dim, dz, 1, 1, wo, 1, in_dim, 1, M, -0.5f * lr, 1.f);
+    if (h_layers[NH].bias)
+      tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
+    float* tmp = g; g = gn; gn = tmp;
+  }
+  for (int l = NH - 1; l >= 0; --l) {
+    const int N = h_layers[l].out_dim, Kd = h_layers[l].in_dim;
+    const float* h = ws + w.h[l];
+    const float* hin = l > 0 ? ws + w.h[l - 1] : x;
+    float* W = const_cast<float*>(h_layers[l].weight);
+    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    float* dst = l > 0 ? gn : dx;
+    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
+    if (h_layers[l].bias)
+      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
+  }
+  // ---- wide side: w <- (1 - 2 lr reg) w - lr x_w^T (dz / 2) over [dense | dense | one-hot], w0
+  tr_scale_kernel<<<tr_grid(n_wide, 256), 256, 0, st>>>(wide_w, n_wide, 1.f - 2.f * lr * reg_w);
+  if (D > 0) {
+    tr_colsum_kernel<<<(D + 31) / 32, 1024, 0, st>>>(dense, dense_ld, dz, B, D, 0, wide_w, -0.5f * lr, 1.f);
+    tr_colsum_kernel<<<(D + 31) / 32, 1024, 0, st>>>(dense, dense_ld, dz, B, D, 0, wide_w + D, -0.5f * lr, 1.f);
+  }
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, wide_w0, -0.5f * lr, 1.f);
+  if (ids_kind == CTRHOT_IDS_I32) {
+    tr_wide_onehot_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F, 256), 256, 0, st>>>(ids, ids_ld, F, col_off, dz, 0.5f * lr, B, wide_w);
+    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dx, n, lr, nullptr);
+  } else {
+    tr_wide_onehot_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F, 256), 256, 0, st>>>(ids, ids_ld, F, col_off, dz, 0.5f * lr, B, wide_w);
+    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dx, n, lr, nullptr);
+  }
+  CTRHOT_LAUNCH_OK("ctrhot_widedeep_train_step_f32");
   return CTRHOT_OK;
 }

@@ -9,7 +9,8 @@ rows that were looked up, the FM weights and the tower.  SURVEY 8(f) rank 3; bui
 ``__main__``, DL/model/deepFM.py:34-57) and for FM on its dense one-hot matrix (DL/model/fm.py:26-45, BASELINE config 1;
 ``ctrhot_fm_train_step_f32``) and for DCN (DL/model/dcn.py:37-49: cross layers + tower + the final Dense over their concat;
 ``ctrhot_dcn_train_step_f32``) and for PNN (the loop of DL/model/pnn.py:74-85, which compile_fit reproduces for it: BCE on
-the raw output, no regularisers; ``ctrhot_pnn_train_step_f32``) -- other models raise NotImplementedError.
+the raw output, no regularisers; ``ctrhot_pnn_train_step_f32``) and for WideDeep (DL/model/wideDeep.py:37-49; ``ctrhot_widedeep_train_step_f32``)
+-- other models raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -26,7 +27,7 @@ class _DeepFMTrainer:
     def __init__(self, model, dropout=None):
         from ..model.criteo import DeepFM
         if not isinstance(model, DeepFM):
-            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, PNN and FM only (SURVEY 8(f) rank 3)")
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, PNN and FM only (SURVEY 8(f) rank 3)")
         self.m = model
         if not model.dnn.built:
             model.build(None)
@@ -274,12 +275,80 @@ def _fit_pnn(model, X, y, batch_size, epochs, sgd, dropout, seed, verbose):
     return model
 
 
+class _WideDeepTrainer:
+    """WideDeep (DL/model/wideDeep.py:14-34): ctrhot_widedeep_train_step_f32 per batch -- the wide logit and its gradient on the
+    ids (the one-hot matrix is never built), the deep tower on the embeddings, WideLayer's l2(1e-4) on w."""
+
+    REG_W = 1e-4                                                  # WideLayer.build, DL/layer/interaction.py:19-22
+
+    def __init__(self, model, dropout=None):
+        self.m = model
+        if not model.deep.built:
+            model.build(None)
+        dl = model.deep
+        if dl.activation != "relu" or dl.output_dim != 1:
+            raise NotImplementedError("compile_fit: DNNLayer(activation='relu', output_dim=1) only")
+        self.dropout = float(dl.dropout if dropout is None else dropout)
+        layers = [(k, b, _lib.ACT_RELU) for k, b in dl.hidden] + [(dl.output[0], dl.output[1], _lib.ACT_NONE)]
+        self.desc = (_lib.DenseDesc * len(layers))()
+        for d, (k, b, act) in zip(self.desc, layers):
+            d.weight, d.bias, d.in_dim, d.out_dim, d.act = ptr(k), ptr(b), int(k.shape[0]), int(k.shape[1]), act
+        self._keep = layers
+        self.ws = None
+        self.loss = torch.zeros(2, dtype=torch.float32, device=model.device)
+        self.flag = model.embed_layer.err_flag()
+        self.step = 0
+
+    def train_on_batch(self, dense, ids, y, lr, seed=0):
+        m, E = self.m, self.m.embed_layer
+        ids, kind, ids_ld = ids_arg(ids)
+        B, D = ids.shape[0], dense.shape[1]
+        n = E.F * E.k
+        need = _lib.query("ctrhot_widedeep_train_workspace_bytes", B, n, self.desc, len(self.desc))
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=m.device)
+        _lib.call("ctrhot_widedeep_train_step_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(dense),
+                  dense.stride(0), D, ptr(y), B, ptr(m.wide.w0), ptr(m.wide.w), ptr(m.col_off), m.n_wide, self.REG_W, self.desc,
+                  len(self.desc), float(lr), self.dropout, int(seed) & (2 ** 64 - 1), ptr(self.loss), ptr(self.ws),
+                  self.ws.numel() * 4, ptr(self.flag), stream_ptr())
+        self.step += 1
+        return self.loss
+
+
+def _fit_rows(tr, model, X, y, batch_size, epochs, sgd, seed, verbose):
+    """The batch loop shared by the trainers that take (dense, ids, y): batches in order, per-epoch loss / accuracy."""
+    dev = model.device
+    D = len(model.dense_feature_columns)
+    F = model.embed_layer.F
+    Xd = as_device_f32(X, dev).contiguous()
+    yd = as_device_f32(np.asarray(y, dtype=np.float32).reshape(-1) if not isinstance(y, torch.Tensor) else y.reshape(-1), dev)
+    N = Xd.shape[0]
+    model.history = []
+    for ep in range(epochs):
+        tot = torch.zeros(2, dtype=torch.float64, device=dev)
+        for s in range(0, N, batch_size):
+            e = min(N, s + batch_size)
+            out = tr.train_on_batch(Xd[s:e, :D], Xd[s:e, D:D + F], yd[s:e], sgd, seed=seed * 1000003 + tr.step)
+            tot[0] += out[0].double() * (e - s)
+            tot[1] += out[1].double()
+        loss, acc = (tot / N).tolist()
+        _lib.check(_lib.load().ctrhot_check_flag(ptr(tr.flag), stream_ptr()), "compile_fit")
+        model.history.append((loss, acc))
+        if verbose:
+            print("Epoch %d/%d - loss: %.4f - accuracy: %.4f" % (ep + 1, epochs, loss, acc))
+    model._bump()
+    return model
+
+
 def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True, use_graph=True):
     """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
     (loss, accuracy) pairs are left in ``model.history``.  ``use_graph``: the full batches of an epoch replay one captured CUDA
     graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
-    from ..model.criteo import DCN, FM, PNN
+    from ..model.criteo import DCN, FM, PNN, WideDeep
+    if isinstance(model, WideDeep):
+        # the one-hot columns of the reference's [B, 39 + n_onehot] matrix are implied by the ids (model.onehot_width)
+        return _fit_rows(_WideDeepTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)
     if isinstance(model, PNN):
         return _fit_pnn(model, X, y, batch_size, epochs, sgd, dropout, seed, verbose)
     if isinstance(model, FM):

@@ -303,3 +303,39 @@ def test_pnn_train_step_gradients(mode):
     assert abs(gk - ((hidden[0][0] - new[2][0][0]) / lr)[n - 1, 3]) < 1e-6
     go = fd(out[0], (2, 0), lambda a: (ids, tables, W, hidden, (a, out[1])))
     assert abs(go - ((out[0] - new[3][0]) / lr)[2, 0]) < 1e-6
+
+
+def test_widedeep_train_step_gradients():
+    rng = np.random.default_rng(13)
+    B, D, F, K = 9, 3, 4, 4
+    vocab, widths = [6, 4, 7, 5], [6, 3, 7, 5]                    # field 1: ids 3 (not seen by get_dummies) have no wide column
+    tables = [rng.normal(0, 0.5, (v, K)) for v in vocab]
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1)
+    ids[1] = ids[0]
+    ids[2, 1] = 3
+    dense = rng.random((B, D))
+    nw = 2 * D + sum(widths)
+    w0, w = rng.normal(0, 0.1, 1), rng.normal(0, 0.3, (nw, 1))
+    hidden = [(rng.normal(0, 0.3, (F * K, 7)), rng.normal(0, 0.1, 7)), (rng.normal(0, 0.4, (7, 5)), rng.normal(0, 0.1, 5))]
+    out = (rng.normal(0, 0.5, (5, 1)), rng.normal(0, 0.1, 1))
+    y = rng.integers(0, 2, B).astype(float)
+    masks = [(rng.random((B, 7)) >= 0.25) / 0.75, (rng.random((B, 5)) >= 0.25) / 0.75]
+    lr, reg = 0.05, 1e-2
+    new, bce, _ = O.widedeep_train_step(dense, ids, tables, w0, w, widths, hidden, out, y, lr, reg, masks)
+    eps = 1e-6
+
+    def fd(obj, idx, rebuild):
+        a, b = obj.copy(), obj.copy()
+        a[idx] += eps; b[idx] -= eps
+        return (O.widedeep_loss(*rebuild(a), y, reg, masks)[0] - O.widedeep_loss(*rebuild(b), y, reg, masks)[0]) / (2 * eps)
+
+    for idx in [(0, 0), (D + 1, 0), (2 * D + int(ids[0, 0]), 0), (nw - 1, 0)]:
+        gw = fd(w, idx, lambda a: (dense, ids, tables, w0, a, widths, hidden, out))
+        assert abs(gw - ((w - new[2]) / lr)[idx]) < 1e-7
+    g0 = fd(w0, (0,), lambda a: (dense, ids, tables, a, w, widths, hidden, out))
+    assert abs(g0 - ((w0 - new[1]) / lr)[0]) < 1e-7
+    for f, r, c in [(0, int(ids[0, 0]), 1), (3, int(ids[4, 3]), 2)]:
+        gt = fd(tables[f], (r, c), lambda a: (dense, ids, tables[:f] + [a] + tables[f + 1:], w0, w, widths, hidden, out))
+        assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, c]) < 1e-7
+    gk = fd(hidden[0][0], (5, 3), lambda a: (dense, ids, tables, w0, w, widths, [(a, hidden[0][1]), hidden[1]], out))
+    assert abs(gk - ((hidden[0][0] - new[3][0][0]) / lr)[5, 3]) < 1e-7
