@@ -201,9 +201,12 @@ def test_ffm_at_the_reference_shape(lib):
     np.testing.assert_allclose(got, O.sigmoid(lay), rtol=0, atol=2e-6)     # FFM.call = sigmoid of it (ffm.py:20-23)
 
 
-def test_pnn_both_full_batch(lib):
+@pytest.mark.parametrize("k", [16, 8])
+def test_pnn_both_full_batch(lib, k):
+    """k = 16: gather + product kernels + tower as separate launches; k = 8 (the reference's embed_dim): the one-launch front
+    (csrc/pnn_fwd.cu) with the tower chained behind it under per-tile flags, and OuterProductLayer on the tensor pipe."""
     set_seed(6)
-    B, k = 65536, 16
+    B = 65536
     rng = np.random.default_rng(9)
     vocab = [int(x) for x in rng.integers(1000, 200000, 26)]
     m = PNN(synth.criteo_feature_columns(vocab, k), "both", [256, 128, 64], 1, embed_dim=k, precision="tf32")
