@@ -117,6 +117,19 @@ def test_throughput_report(lib, raw):
     msg = ("input step: %d rows, %.1f MB of TSV: parse + fit + transform %.1f ms (%.2f M rows/s, copy of the text included); "
            "transform alone %.3f ms (%.1f M rows/s); reference loader: 1.0 s for 10 000 rows in 'DeepFM' mode = 0.01 M rows/s"
            % (dr.shape[0], len(text) / 1e6, dt * 1e3, dr.shape[0] / dt / 1e6, tr * 1e3, dr.shape[0] / tr / 1e6))
+    # the Hash layer (DL/layer/utils.py:21-56) on a [65 536, 26] int32 id matrix: ids in, int64 buckets out
+    from recommender_system_b200.layer import Hash
+    hx = torch.randint(0, 10 ** 9, (65536, 26), dtype=torch.int32, device="cuda")
+    hl = Hash(1000003, mask_zero=True)
+    hl(hx)
+    e0.record()
+    for _ in range(20):
+        hl(hx)
+    e1.record()
+    torch.cuda.synchronize()
+    th = e0.elapsed_time(e1) / 20 * 1e-3
+    msg += ("\nHash layer: %d ids (decimal string -> FarmHash Fingerprint64 -> bucket) in %.3f ms = %.1f G ids/s, %.0f GB/s of "
+            "ids + buckets" % (hx.numel(), th * 1e3, hx.numel() / th / 1e9, hx.numel() * 12 / th / 1e9))
     print(msg)
     out = os.path.join(os.path.dirname(HERE), "gpurun_out")
     if os.path.isdir(out):
