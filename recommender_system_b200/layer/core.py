@@ -302,8 +302,14 @@ class DenseStack:
         chain = self.chain_launches and n_tiles >= 148 and n >= 3
         per = (2 * B * mx + B + 31) // 32 * 32              # (the second workspace starts 16-byte aligned for any B)
         if self._ws is None or self._ws.numel() < 2 * per or self._ws.device != dense.device:
+            if self._ws is not None:
+                torch.cuda.current_stream().synchronize()   # the previous call may still read the buffers being replaced
             self._ws = torch.empty(2 * per, dtype=torch.float32, device=dense.device)
             self._flags, self._epoch = None, 0
+        # the two workspaces sit at FIXED offsets of the allocation, whatever this call's batch size: a call's first launch may
+        # start while the previous call's last one still reads its buffers (overlapping launches), so the regions of consecutive
+        # calls must not move against each other when B changes (a ragged last batch followed by a full one)
+        per = self._ws.numel() // 2 // 32 * 32
         if chain and (self._flags is None or self._flags.shape[2] < n_tiles):
             self._flags = torch.zeros((2, n, n_tiles), dtype=torch.int32, device=dense.device)
             self._epoch = 0

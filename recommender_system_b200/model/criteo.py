@@ -662,7 +662,7 @@ class PNN(Model):
                 # the tower starts on the SMs the front frees and waits per tile: two alternating product buffers (the next
                 # call's front must not write what this call's tower still reads) and a new epoch per call
                 c = self._chain
-                if c is None or c[0].shape[0] < B or c[0].shape[1] != ld:
+                if c is None or c[0].shape[0] < 2 * B or c[0].shape[1] != ld:      # capacity: two buffers of B rows each
                     c = self._chain = [torch.empty((2 * B, ld), dtype=torch.float32, device=self.device),
                                        torch.zeros(n_tiles, dtype=torch.int32, device=self.device), 0]
                 c[2] += 1

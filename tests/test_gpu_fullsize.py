@@ -117,6 +117,20 @@ def test_dcn_cfg3_chained_launches_equal_stream_order(lib):
         torch.cuda.synchronize()
         for i, o in enumerate(outs):
             assert torch.equal(o, want[i % 3]), (B, i, float((o - want[i % 3]).abs().max()))
+    # batch sizes changing from call to call (a ragged last batch, then a full one): the two workspaces must not move
+    sizes = [40000, 65536, 148 * 128 + 77, 65536, 30000, 65536]
+    seq = []
+    for j, Bj in enumerate(sizes):
+        d, ids = synth.criteo_batch(Bj, vocab, seed=60 + j)
+        seq.append((torch.from_numpy(d).to(dev), torch.from_numpy(ids).to(dev)))
+    stack.chain_launches = False
+    want = [m(b).clone() for b in seq]
+    torch.cuda.synchronize()
+    stack.chain_launches = True
+    outs = [m(b) for b in seq + seq]
+    torch.cuda.synchronize()
+    for i, o in enumerate(outs):
+        assert torch.equal(o, want[i % len(seq)]), (i, sizes[i % len(seq)])
 
 
 def test_din_cfg4_whole_model(lib):

@@ -126,6 +126,15 @@ def test_pnn_chained_launches_equal_stream_order(lib):
     assert m._chain is not None and m._chain[2] == 7
     for i in range(7):
         assert torch.equal(got[i], want[i % 3]), i
+    # a larger batch after a smaller one re-sizes the two product buffers and the flags; a smaller one reuses them
+    for Bn in (B + 5000, B - 3000):
+        ids = np.stack([rng.integers(0, v, Bn) for v in vocab], axis=1).astype(np.float32)
+        x = torch.from_numpy(np.concatenate([S.f32(rng.random((Bn, 13))), ids], axis=1)).cuda()
+        a = m(x).clone()
+        m.chain_launches = False
+        b = m(x).clone()
+        m.chain_launches = True
+        assert a.shape == (Bn, 1) and torch.equal(a, b), Bn
 
 
 @pytest.mark.parametrize("B,F", [(128, 26), (4099, 26), (1000, 5), (300, 28)])
