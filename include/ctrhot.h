@@ -102,6 +102,14 @@ int ctrhot_wide_dense_f32(const float* x, int64_t x_ld, int64_t n, int64_t B,
 int ctrhot_fm_dense_f32(const float* x, int64_t x_ld, int64_t n, int64_t B,
                         const float* w0, const float* w1, const float* v, int kfm,
                         float* out, int apply_sigmoid, void* stream);
+/* ctrhot_fm_dense_f32 for few rows of many columns (the reference's FM on its dense one-hot matrix, DL/model/fm.py:26-45:
+ * 2 000 x 43 604): the columns are split across CTAs so that the launch fills the GPU; partial sums in `workspace`
+ * (ctrhot_fm_dense_ws_bytes; 0 = the shape does not need it), added in a fixed order by a finishing pass.  Falls through to
+ * ctrhot_fm_dense_f32 when the workspace is absent / too small. */
+int64_t ctrhot_fm_dense_ws_bytes(int64_t n, int64_t B, int kfm);
+int ctrhot_fm_dense_ws_f32(const float* x, int64_t x_ld, int64_t n, int64_t B, const float* w0, const float* w1,
+                           const float* v, int kfm, float* out, int apply_sigmoid, void* workspace,
+                           int64_t workspace_bytes, void* stream);
 /* one-hot form = north_star's (sum v)^2 - sum v^2 over gathered rows */
 int ctrhot_fm_onehot_f32(const float* dense, int64_t dense_ld, int D, const int32_t* dense_col,
                          const void* ids, int ids_kind, int64_t ids_ld, int F,

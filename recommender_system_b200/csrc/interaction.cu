@@ -248,7 +248,13 @@ template <int KF>
 __global__ void __launch_bounds__(256)
 fm_dense_wide_v4_kernel(const float* __restrict__ x, int64_t x_ld, int64_t n, int64_t B,
                         const float* __restrict__ w0, const float* __restrict__ w1,
-                        const float* __restrict__ v, int kfm, float* __restrict__ out, int apply_sigmoid) {
+                        const float* __restrict__ v, int kfm, float* __restrict__ out, int apply_sigmoid,
+                        float* __restrict__ part = nullptr, int64_t cols_per_split = 0) {
+  // part != NULL: few samples, many columns (the reference's own FM case: 2 000 rows x 43 604 one-hot columns would fill 63 CTAs):
+  // blockIdx.y takes the column range [y, y + 1) * cols_per_split and leaves its KF + 2 partial sums per sample in
+  // part[y][b][0 .. KF + 2) = {sum_j x_j v_jc (c < KF), sum_j x_j^2 sum_c v_jc^2, x . w1}; fm_dense_finish_kernel adds them in order
+  const int64_t j_begin = part ? (int64_t)blockIdx.y * cols_per_split : 0;
+  const int64_t j_end = part ? (j_begin + cols_per_split < n ? j_begin + cols_per_split : n) : n;
   __shared__ __align__(16) float vs[(KF + 1) * FMW_TJ];       // planes 0..kfm-1 = v[:, c], plane kfm = w1; zero past n
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const int64_t ngroups = (B + 3) >> 2;
@@ -267,8 +273,8 @@ fm_dense_wide_v4_kernel(const float* __restrict__ x, int64_t x_ld, int64_t n, in
 #pragma unroll
       for (int c = 0; c < KF; ++c) s[i][c] = 0.f;
     }
-    for (int64_t jt = 0; jt < n; jt += FMW_TJ) {
-      const int tj = (int)((n - jt < FMW_TJ) ? n - jt : FMW_TJ);
+    for (int64_t jt = j_begin; jt < j_end; jt += FMW_TJ) {
+      const int tj = (int)((j_end - jt < FMW_TJ) ? j_end - jt : FMW_TJ);
       __syncthreads();                                         // the previous tile is no longer being read
       for (int idx = threadIdx.x; idx < FMW_TJ * kfm; idx += 256) {
         const int jl = idx / kfm, c = idx - jl * kfm;
@@ -348,20 +354,39 @@ fm_dense_wide_v4_kernel(const float* __restrict__ x, int64_t x_ld, int64_t n, in
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       float inter = 0.f;
+      float* prow = part ? part + (((int64_t)blockIdx.y * B) + (b0 + i < B ? b0 + i : 0)) * (KF + 2) : nullptr;
 #pragma unroll
       for (int c = 0; c < KF; ++c) {
         if (c < kfm) {
           const float tot = warp_sum(s[i][c]) + __shfl_sync(0xffffffffu, sps[i], c);
           inter = fmaf(tot, tot, inter);
-        }
+          if (prow && lane == 0 && b0 + i < B) prow[c] = tot;
+        } else if (prow && lane == 0 && b0 + i < B) prow[c] = 0.f;
       }
       const float tt = warp_sum(t[i] + (lane < kfm ? spt[i] : 0.f));
       const float ll = warp_sum(lin[i] + (lane == kfm ? sps[i] : 0.f));
       if (lane == 0 && b0 + i < B) {
+        if (prow) { prow[KF] = tt; prow[KF + 1] = ll; continue; }
         const float r = __ldg(w0) + ll + 0.5f * (inter - tt);
         out[b0 + i] = apply_sigmoid ? 1.0f / (1.0f + expf(-r)) : r;
       }
     }
+  }
+}
+
+// out[b] = w0 + sum_y ll + 1/2 (sum_c (sum_y s_c)^2 - sum_y tt), the column splits added in order (deterministic)
+__global__ void fm_dense_finish_kernel(const float* __restrict__ part, int nsplit, int64_t B, int KF2, const float* __restrict__ w0,
+                                       float* __restrict__ out, int apply_sigmoid) {
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < B; b += (int64_t)gridDim.x * blockDim.x) {
+    float inter = 0.f, tt = 0.f, ll = 0.f;
+    for (int c = 0; c < KF2 - 2; ++c) {
+      float tot = 0.f;
+      for (int y = 0; y < nsplit; ++y) tot += part[((int64_t)y * B + b) * KF2 + c];
+      inter = fmaf(tot, tot, inter);
+    }
+    for (int y = 0; y < nsplit; ++y) { tt += part[((int64_t)y * B + b) * KF2 + KF2 - 2]; ll += part[((int64_t)y * B + b) * KF2 + KF2 - 1]; }
+    const float r = __ldg(w0) + ll + 0.5f * (inter - tt);
+    out[b] = apply_sigmoid ? 1.0f / (1.0f + expf(-r)) : r;
   }
 }
 
@@ -1139,6 +1164,49 @@ extern "C" int ctrhot_fm_dense_f32(const float* x, int64_t x_ld, int64_t n, int6
     fm_dense_kernel<<<warp_grid(B, 8), 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid);
   }
   CTRHOT_LAUNCH_OK("ctrhot_fm_dense_f32");
+  return CTRHOT_OK;
+}
+
+// ctrhot_fm_dense_f32 for FEW rows of MANY columns (FM on the reference's dense one-hot matrix, DL/model/fm.py:26-45): the columns
+// are split over blockIdx.y so that the launch fills the GPU, partial sums in the caller's workspace, a finishing pass.
+static int fm_dense_split_plan(int64_t n, int64_t B, int kfm, int* nsplit, int64_t* cols, int* KF) {
+  *nsplit = 0;
+  if (n < 4096 || kfm < 1 || kfm > 16 || B < 1) return 0;
+  const int64_t nb = ((B + 3) / 4 + 7) / 8;
+  if (nb >= (int64_t)kNumSMs * 2) return 0;                                 // enough row blocks already
+  const int64_t tiles = (n + FMW_TJ - 1) / FMW_TJ;
+  int64_t want = ((int64_t)kNumSMs * 4 + nb - 1) / nb;
+  if (want > tiles / 4) want = tiles / 4;                                   // at least four 256-column tiles per split
+  if (want < 2) return 0;
+  const int64_t tps = (tiles + want - 1) / want;
+  *cols = tps * FMW_TJ;
+  *nsplit = (int)((tiles + tps - 1) / tps);
+  *KF = kfm <= 8 ? 8 : (kfm <= 12 ? 12 : 16);
+  return 1;
+}
+extern "C" int64_t ctrhot_fm_dense_ws_bytes(int64_t n, int64_t B, int kfm) {
+  int ns, KF; int64_t cols;
+  if (!fm_dense_split_plan(n, B, kfm, &ns, &cols, &KF)) return 0;
+  return (int64_t)ns * B * (KF + 2) * (int64_t)sizeof(float);
+}
+extern "C" int ctrhot_fm_dense_ws_f32(const float* x, int64_t x_ld, int64_t n, int64_t B, const float* w0, const float* w1,
+                                      const float* v, int kfm, float* out, int apply_sigmoid, void* workspace,
+                                      int64_t workspace_bytes, void* stream) {
+  CTRHOT_RANGE("ctrhot_fm_dense_ws_f32");
+  int ns, KF; int64_t cols;
+  if (!x || !w0 || !w1 || !out || n <= 0 || B < 0 || x_ld < n || kfm < 0 || (kfm > 0 && !v)) return CTRHOT_EARG;
+  if (B == 0) return CTRHOT_OK;
+  if (!workspace || !(x_ld % 4 == 0 && aligned16(x)) || !fm_dense_split_plan(n, B, kfm, &ns, &cols, &KF) ||
+      workspace_bytes < (int64_t)ns * B * (KF + 2) * (int64_t)sizeof(float))
+    return ctrhot_fm_dense_f32(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid, stream);
+  float* part = static_cast<float*>(workspace);
+  const int64_t nb = ((B + 3) / 4 + 7) / 8;
+  dim3 grid((unsigned)nb, (unsigned)ns);
+  if (KF == 8) fm_dense_wide_v4_kernel<8><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid, part, cols);
+  else if (KF == 12) fm_dense_wide_v4_kernel<12><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid, part, cols);
+  else fm_dense_wide_v4_kernel<16><<<grid, 256, 0, ST(stream)>>>(x, x_ld, n, B, w0, w1, v, kfm, out, apply_sigmoid, part, cols);
+  fm_dense_finish_kernel<<<(int)((B + 255) / 256), 256, 0, ST(stream)>>>(part, ns, B, KF + 2, w0, out, apply_sigmoid);
+  CTRHOT_LAUNCH_OK("ctrhot_fm_dense_ws_f32");
   return CTRHOT_OK;
 }
 

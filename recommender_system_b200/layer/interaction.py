@@ -133,6 +133,15 @@ class FMLayer(Layer):
         x = as_device_f32(inputs, self.device)
         require_cuda(x, "FMLayer")
         out = _out(x.shape[0], self.device)
+        need = _lib.query("ctrhot_fm_dense_ws_bytes", x.shape[1], x.shape[0], self.k) if x.shape[0] > 0 else 0
+        if need > 0:
+            # few rows of many columns (the reference's FM on its dense one-hot matrix): columns split across CTAs
+            ws = getattr(self, "_split_ws", None)
+            if ws is None or ws.numel() * 4 < need or ws.device != x.device:
+                ws = self._split_ws = torch.empty(need // 4, dtype=torch.float32, device=x.device)
+            _lib.call("ctrhot_fm_dense_ws_f32", ptr(x), x.stride(0), x.shape[1], x.shape[0], ptr(self.w0), ptr(self.w1),
+                      ptr(self.v), self.k, ptr(out), int(apply_sigmoid), ptr(ws), ws.numel() * 4, stream_ptr())
+            return out
         _lib.call("ctrhot_fm_dense_f32", ptr(x), x.stride(0), x.shape[1], x.shape[0], ptr(self.w0), ptr(self.w1),
                   ptr(self.v), self.k, ptr(out), int(apply_sigmoid), stream_ptr())
         return out
