@@ -682,7 +682,7 @@ def main():
     from recommender_system_b200.utils.pipeline import HostPipeline
     from recommender_system_b200.utils.transport import RowLayout
     # host buffers in the library's transport format (utils/transport.py, csrc/transport.cu): 13 float32 + ids at the byte
-    # width their vocabulary needs = 104 B per sample on this vocabulary; packed ONCE here, like the int32 buffers above are
+    # bit width their vocabulary needs = 96 B per sample on this vocabulary; packed ONCE here, like the int32 buffers above are
     # built once -- the per-step work is the copy.  The packer's own host throughput is reported beside it.
     layout = RowLayout(vocab, 13)
     t0 = time.perf_counter()
@@ -760,7 +760,7 @@ def main():
                            "launch_overlap": bool(model.overlap_launches)},
                 "e2e": {"value": B * world * K2 / t_e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h, "steps": K2,
-                        "input": "transport records, %d B/sample (13 float32 + ids at 1-3 bytes), one H2D copy per step, decoded "
+                        "input": "transport records, %d B/sample (13 float32 + every id at the bit width its vocabulary needs), one H2D copy per step, decoded "
                                  "in the whole-model kernel" % layout.rec_bytes,
                         "bit_identical_to_int32_path": same, "host_pack_samples_per_s": pack_rate, "host_affinity": binder.info,
                         "int32_input": {"value": B * world * K2 / t_int32, "h2d_bytes_per_step": pipe.h2d_bytes,

@@ -291,6 +291,9 @@ int ctrhot_criteo_encode(const double* dense_raw, const int64_t* tokens, int64_t
  *                        the dense columns are read in place: ONE host-to-device copy per batch, no unpack pass.
  *                        records 16-byte aligned, rec_bytes % 4 == 0, pack_desc = DEVICE int32 [F]. */
 int ctrhot_rows_layout(const int64_t* h_vocab, int F, int D, int32_t* h_desc);
+/* the same at BIT granularity (width = ceil(log2(vocab)) bits): h_desc[f] = 0x80000000 | bits << 24 | bit offset; every consumer of
+ * a descriptor (pack, unpack, the whole-model kernels) takes either form.  96 B per sample on the Criteo-Kaggle cardinalities. */
+int ctrhot_rows_layout_bits(const int64_t* h_vocab, int F, int D, int32_t* h_desc);
 int ctrhot_rows_pack_host(const float* h_dense, int64_t dense_ld, const int32_t* h_ids, int64_t ids_ld, int64_t B,
                           const int32_t* h_desc, int F, int D, int64_t rec_bytes, void* h_records, int n_threads);
 int ctrhot_rows_unpack(const void* records, int64_t rec_bytes, const int32_t* desc, int F, int dense_off, int D,

@@ -35,6 +35,13 @@ struct NvtxRange {
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// Transport-record field descriptors (csrc/transport.cu): byte-granular  (byte offset) | (width in bytes) << 16,  or, with
+// bit 31 set, bit-granular  (bit offset, 24 bits) | (width in bits, <= 32) << 24.  -> bit offset inside the record, width in bits.
+__host__ __device__ __forceinline__ void rows_field(uint32_t d, uint32_t& bit_off, uint32_t& bits) {
+  if (d & 0x80000000u) { bit_off = d & 0xFFFFFFu; bits = (d >> 24) & 0x7Fu; }
+  else { bit_off = (d & 0xFFFFu) * 8u; bits = (d >> 16) * 8u; }
+}
+
 // ---------------------------------------------------------------- device
 __device__ __forceinline__ float4 ldg_nc_f4(const float* p) {
   float4 r;

@@ -426,17 +426,18 @@ ctr_fused_kernel(const __grid_constant__ FuParams p) {
         } else if (p.ids_kind == CTRHOT_IDS_PACKED) {
           // compact transport records: field f is `w` little-endian bytes at byte `off` of each record (any alignment).
           // Two aligned 32-bit loads + a funnel shift; neighbouring fields share the words, so these hit L1.
-          const uint32_t d = (uint32_t)reinterpret_cast<const int32_t*>(fptr + mp.pk)[cf.f];
-          const uint32_t w8 = (d >> 16) * 8u;
+          uint32_t bit_off, w8;                                          // byte- or bit-granular field (common.cuh)
+          rows_field((uint32_t)reinterpret_cast<const int32_t*>(fptr + mp.pk)[cf.f], bit_off, w8);
           const uint32_t mask = w8 >= 32u ? 0xFFFFFFFFu : ((1u << w8) - 1u);
-          const uint8_t* rec = static_cast<const uint8_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + (d & 0xFFFFu);
+          const uint8_t* rec = static_cast<const uint8_t*>(p.ids) + (cf.row0 + rsub) * p.ids_ld + (bit_off >> 3);
+          const uint32_t bsh = bit_off & 7u;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             reg[i] = 0;
             if (cf.row0 + rsub + 16 * i < p.M) {
               const uintptr_t a = reinterpret_cast<uintptr_t>(rec + (int64_t)(16 * i) * p.ids_ld);
               const uint32_t* al = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-              const uint32_t sh = (uint32_t)(a & 3u) * 8u;
+              const uint32_t sh = (uint32_t)(a & 3u) * 8u + bsh;             // <= 31
               const uint32_t lo = __ldg(al);
               const uint32_t hi = (sh + w8 > 32u) ? __ldg(al + 1) : 0u;    // never beyond the record: it ends on a word
               reg[i] = (int32_t)(__funnelshift_r(lo, hi, sh) & mask);

@@ -1,8 +1,8 @@
 """Compact transport records for Criteo-shaped batches (csrc/transport.cu): the host-to-device copy on the left of the hot
 path.  The reference feeds ``model(X)`` one float64 ``[B, 39]`` matrix (DL/utils/dataset.py:61,
-DL/model/deepFM.py:24); a record keeps the 13 dense float32 bit-exact and stores every id at the byte width its
-``feat_onehot_dim`` needs -- 104 B per sample instead of 156 (int32 ids) or 312 (the reference's matrix) on the
-Criteo-Kaggle cardinalities.
+DL/model/deepFM.py:24); a record keeps the 13 dense float32 bit-exact and stores every id at the bit width its
+``feat_onehot_dim`` needs -- 96 B per sample instead of 156 (int32 ids) or 312 (the reference's matrix) on the
+Criteo-Kaggle cardinalities (104 B with whole-byte fields, ``bits=False``).
 
     layout = RowLayout.from_feature_columns(feature_columns)         # widths from feat_onehot_dim
     rec = layout.pack(dense, ids)                                    # host: uint8 [B, rec_bytes] (C, multi-threaded)
@@ -20,14 +20,17 @@ from .. import _lib
 
 
 class RowLayout:
-    def __init__(self, vocab, n_dense=13):
+    def __init__(self, vocab, n_dense=13, bits=True):
+        """``bits=True``: every id at the BIT width its vocabulary needs (96 B per sample on the Criteo-Kaggle cardinalities);
+        ``bits=False``: whole bytes (104 B).  ``widths``: per field, in bits / in bytes."""
         self.vocab = [int(v) for v in vocab]
         self.F, self.D = len(self.vocab), int(n_dense)
+        self.bits = bool(bits)
         v = (ctypes.c_int64 * self.F)(*self.vocab)
         d = (ctypes.c_int32 * self.F)()
-        self.rec_bytes = _lib.query("ctrhot_rows_layout", v, self.F, self.D, d)
+        self.rec_bytes = _lib.query("ctrhot_rows_layout_bits" if self.bits else "ctrhot_rows_layout", v, self.F, self.D, d)
         self.desc_host = np.frombuffer(d, dtype=np.int32).copy()
-        self.widths = [int(x) >> 16 for x in self.desc_host]
+        self.widths = [(int(x) >> 24) & 0x7F if self.bits else int(x) >> 16 for x in self.desc_host]
         self.dense_off = 0
         self._dev = {}
 

@@ -13,17 +13,49 @@ from recommender_system_b200.utils.transport import PackedRows, RowLayout
 
 
 def test_layout_widths_follow_the_vocabulary(lib):
-    lay = RowLayout([256, 257, 65536, 65537, 1 << 24, (1 << 24) + 1, 3], n_dense=13)
+    lay = RowLayout([256, 257, 65536, 65537, 1 << 24, (1 << 24) + 1, 3], n_dense=13, bits=False)
     assert lay.widths == [1, 2, 2, 3, 3, 4, 1]
     assert lay.rec_bytes == (52 + 16 + 3) // 4 * 4
-    k = RowLayout(synth.KAGGLE_VOCAB, 13)
+    k = RowLayout(synth.KAGGLE_VOCAB, 13, bits=False)
     assert k.rec_bytes == 104 and sum(k.widths) == 52           # 156 B per sample as int32
+    # bit-granular (the default): ceil(log2(vocab)) bits per id, at least one
+    lb = RowLayout([256, 257, 65536, 65537, 1 << 24, (1 << 24) + 1, 3, 1, 2], n_dense=13)
+    assert lb.widths == [8, 9, 16, 17, 24, 25, 2, 1, 1]
+    assert lb.rec_bytes == (52 * 8 + sum(lb.widths) + 31) // 32 * 4
+    kb = RowLayout(synth.KAGGLE_VOCAB, 13)
+    assert kb.rec_bytes == 96 and sum(kb.widths) == 321
+
+
+@pytest.mark.parametrize("bits", [True, False])
+def test_host_pack_round_trips_in_both_layouts(lib, bits):
+    """Decoded on the host independently of the C code, bit by bit."""
+    rng = np.random.default_rng(1)
+    vocab = [256, 300, 70000, 20_000_000, 5, 65536, 1, 2, (1 << 31) - 1, 3]
+    lay = RowLayout(vocab, n_dense=3, bits=bits)
+    B = 4097
+    dense = rng.random((B, 3), dtype=np.float32)
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], 1).astype(np.int32)
+    ids[0] = np.asarray(vocab) - 1
+    rec = lay.pack(dense, ids)
+    np.testing.assert_array_equal(rec[:, :12].copy().view(np.float32).reshape(B, 3), dense)
+    allbits = np.unpackbits(rec, axis=1, bitorder="little").astype(np.int64)          # [B, 8 rec_bytes], LSB first
+    for f in range(len(vocab)):
+        d = int(lay.desc_host[f]) & 0xFFFFFFFF
+        off, w = (d & 0xFFFFFF, (d >> 24) & 0x7F) if d >> 31 else ((d & 0xFFFF) * 8, (d >> 16) * 8)
+        v = sum(allbits[:, off + b] << b for b in range(w))
+        np.testing.assert_array_equal(v, ids[:, f])
+    np.testing.assert_array_equal(rec, lay.pack(dense, ids, threads=1))
+    bad = ids.copy()
+    bad[5, 1] = 512                                             # 300 needs 9 bits / 2 bytes: 512 fits neither... in bits
+    if bits:
+        with pytest.raises(IndexError):
+            lay.pack(dense, bad)
 
 
 def test_host_pack_round_trips_and_reports_ids_that_do_not_fit(lib):
     rng = np.random.default_rng(0)
     vocab = [256, 300, 70000, 20_000_000, 5, 65536]
-    lay = RowLayout(vocab, n_dense=3)
+    lay = RowLayout(vocab, n_dense=3, bits=False)
     B = 10_001                                                  # several threads, ragged last chunk
     dense = rng.random((B, 3), dtype=np.float32)
     ids = np.stack([rng.integers(0, v, B) for v in vocab], 1).astype(np.int32)
