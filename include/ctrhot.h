@@ -437,6 +437,17 @@ int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_off, int F, 
                                    float dropout, uint64_t seed, float* loss_out, void* workspace,
                                    int64_t workspace_bytes, int* err_flag, void* stream);
 
+/* ---- 8(f) rank 3, DeepCrossing under compile_fit (DL/model/deepCrossing.py:14-32; ResLayer DL/layer/interaction.py:261-278) ---
+ * x_0 = [dense | rows]; unit r: x_{r+1} = relu(x_r + Dense_n(relu-Dense chain(x_r))); p = sigmoid(Dense_1(x_R)); mean clipped BCE,
+ * no regularisers, no dropout.  h_layers = n_res groups of per_res descriptors (per_res - 1 ReLU layers, then the unit's Dense back
+ * to width n = D + F k, act none; every layer with a bias).  Updates in place: arena rows, all units, final_k [n], final_b [1]. */
+int64_t ctrhot_deepcrossing_train_workspace_bytes(int64_t B, int n, const ctrhot_dense_desc* h_layers, int n_res, int per_res);
+int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                       int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                                       int64_t B, const ctrhot_dense_desc* h_layers, int n_res, int per_res,
+                                       float* final_k, float* final_b, float lr, float* loss_out, void* workspace,
+                                       int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

@@ -960,3 +960,50 @@ def widedeep_train_step(dense, ids, tables, wide_w0, wide_w, widths, hidden, out
         np.add.at(new_tables[f], ids[:, f], -lr * g[:, off:off + kdim])
         off += kdim
     return (new_tables, new_w0, new_w, new_hidden, new_out), bce, correct
+
+
+def deepcrossing_train_step(dense, ids, tables, res_layers, final, y, lr):
+    """One step of keras SGD(lr) on the mean clipped BCE of DeepCrossing (DL/model/deepCrossing.py:14-32 under compile_fit; no
+    regularisers, no dropout).  res_layers: list of (hidden pairs, out pair).  PARITY UNPINNED against the reference, pinned by
+    finite differences of `deepcrossing_model`'s loss.
+    -> ((tables, res_layers, final) updated, mean BCE before the update, number of correct predictions)."""
+    ids = ids_to_int(ids)
+    B, D, F = ids.shape[0], np.asarray(dense).shape[1], len(tables)
+    x = np.concatenate([np.asarray(dense, np.float64)] + [tables[f][ids[:, f]] for f in range(F)], axis=1)
+    xs, hs = [x], []
+    for hidden, out in res_layers:
+        acts = [xs[-1]]
+        for k, b in hidden:
+            acts.append(np.maximum(acts[-1] @ k + b, 0.0))
+        hs.append(acts)
+        xs.append(np.maximum(xs[-1] + acts[-1] @ out[0] + out[1], 0.0))
+    p = sigmoid(xs[-1] @ final[0] + final[1])[:, 0]
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    correct = int(np.sum((p > 0.5) == (y > 0.5)))
+    dz = (np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B)[:, None]
+    new_final = (final[0] - lr * (xs[-1].T @ dz), final[1] - lr * np.sum(dz))
+    g = dz @ final[0].T
+    new_res = [None] * len(res_layers)
+    for r in range(len(res_layers) - 1, -1, -1):
+        hidden, out = res_layers[r]
+        acts = hs[r]
+        gm = g * (xs[r + 1] > 0)
+        new_out = (out[0] - lr * (acts[-1].T @ gm), out[1] - lr * np.sum(gm, axis=0))
+        gh = gm @ out[0].T
+        new_hidden = [None] * len(hidden)
+        for l in range(len(hidden) - 1, -1, -1):
+            k, b = hidden[l]
+            gh = gh * (acts[l + 1] > 0)
+            gin = gh @ k.T
+            new_hidden[l] = (k - lr * (acts[l].T @ gh), b - lr * np.sum(gh, axis=0))
+            gh = gin
+        new_res[r] = (new_hidden, new_out)
+        g = gm + gh
+    new_tables = [t.copy() for t in tables]
+    off = D
+    for f in range(F):
+        kdim = tables[f].shape[1]
+        np.add.at(new_tables[f], ids[:, f], -lr * g[:, off:off + kdim])
+        off += kdim
+    return (new_tables, new_res, new_final), bce, correct

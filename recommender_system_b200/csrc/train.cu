@@ -437,6 +437,21 @@ __global__ void tr_wide_onehot_sgd_kernel(const void* __restrict__ ids, int64_t 
   }
 }
 
+// ---------------------------------------------------------------- DeepCrossing (DL/model/deepCrossing.py:14-32): residual units
+// out = relu(x + h)   (ResLayer.call, DL/layer/interaction.py:277-278)
+__global__ void tr_residual_relu_kernel(const float* __restrict__ x, const float* __restrict__ h, int64_t total, float* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = fmaxf(x[i] + h[i], 0.f);
+}
+// gm = g where the unit's output is positive, else 0 (the derivative of that relu)
+__global__ void tr_mask_copy_kernel(const float* __restrict__ g, const float* __restrict__ xo, int64_t total, float* __restrict__ gm) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
+    gm[i] = xo[i] > 0.f ? g[i] : 0.f;
+}
+__global__ void tr_add_kernel(float* __restrict__ a, const float* __restrict__ b, int64_t total) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) a[i] += b[i];
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -954,5 +969,110 @@ extern "C" int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_o
     tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dx, n, lr, nullptr);
   }
   CTRHOT_LAUNCH_OK("ctrhot_widedeep_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- DeepCrossing training step
+// h_layers = n_res groups of per_res descriptors: per_res - 1 ReLU Dense layers, then the unit's Dense back to width n (act none)
+namespace {
+constexpr int TR_MAXRES = 8;
+struct TrDxLayout { int64_t xs, z, dz, g, gm, ga, gb, act[TR_MAXRES][TR_MAXL], total; int maxw; };
+bool tr_dx_layout(int64_t B, int n, const ctrhot_dense_desc* Ld, int n_res, int per_res, TrDxLayout& w) {
+  if (!Ld || n_res < 1 || n_res > TR_MAXRES || per_res < 2 || per_res > TR_MAXL || B < 0 || n <= 0) return false;
+  int64_t o = 0;
+  auto take = [&](int64_t cnt) { const int64_t at = o; o += (cnt + 3) / 4 * 4; return at; };
+  w.maxw = n;
+  for (int r = 0; r < n_res; ++r)
+    for (int l = 0; l < per_res; ++l) {
+      const ctrhot_dense_desc& d = Ld[r * per_res + l];
+      if (!d.weight || !d.bias) return false;
+      if (d.in_dim != (l == 0 ? n : Ld[r * per_res + l - 1].out_dim)) return false;
+      if (l < per_res - 1 ? d.act != CTRHOT_ACT_RELU : (d.act != CTRHOT_ACT_NONE || d.out_dim != n)) return false;
+      if (d.out_dim > w.maxw) w.maxw = d.out_dim;
+    }
+  w.xs = take((int64_t)(n_res + 1) * B * n); w.z = take(B); w.dz = take(B);
+  w.g = take(B * n); w.gm = take(B * n); w.ga = take(B * (int64_t)w.maxw); w.gb = take(B * (int64_t)w.maxw);
+  for (int r = 0; r < n_res; ++r)
+    for (int l = 0; l < per_res; ++l) w.act[r][l] = take(B * (int64_t)Ld[r * per_res + l].out_dim);
+  w.total = o;
+  return true;
+}
+}  // namespace
+
+extern "C" int64_t ctrhot_deepcrossing_train_workspace_bytes(int64_t B, int n, const ctrhot_dense_desc* h_layers, int n_res,
+                                                             int per_res) {
+  TrDxLayout w;
+  if (!tr_dx_layout(B, n, h_layers, n_res, per_res, w)) return CTRHOT_ESHAPE;
+  return w.total * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                                  int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y,
+                                                  int64_t B, const ctrhot_dense_desc* h_layers, int n_res, int per_res,
+                                                  float* final_k, float* final_b, float lr, float* loss_out, void* workspace,
+                                                  int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_deepcrossing_train_step_f32");
+  if (!arena || !row_off || !ids || !y || !final_k || !final_b || !loss_out || !workspace || F <= 0 || k <= 0 || D < 0 ||
+      (D > 0 && !dense) || B <= 0 || ids_ld < F || (D > 0 && dense_ld < D) || !(lr >= 0.f)) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  const int n = D + F * k;
+  TrDxLayout w;
+  if (!tr_dx_layout(B, n, h_layers, n_res, per_res, w)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < w.total * (int64_t)sizeof(float) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  float *xs = ws + w.xs, *z = ws + w.z, *dz = ws + w.dz, *g = ws + w.g, *gm = ws + w.gm;
+  const int M = (int)B;
+  const int64_t Bn = B * n;
+  // ---- forward: x_0 = [dense | rows]; unit r: relu chain, Dense back to n, x_{r+1} = relu(x_r + h)
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_gather_kernel<CTRHOT_IDS_I32><<<tr_grid(Bn, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, xs, n, err_flag, nullptr);
+  else
+    tr_gather_kernel<CTRHOT_IDS_F32><<<tr_grid(Bn, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, xs, n, err_flag, nullptr);
+  for (int r = 0; r < n_res; ++r) {
+    const float* in = xs + (int64_t)r * Bn;
+    int in_dim = n;
+    for (int l = 0; l < per_res; ++l) {
+      const ctrhot_dense_desc& d = h_layers[r * per_res + l];
+      float* h = ws + w.act[r][l];
+      tr_gemm(st, in, in_dim, 1, d.weight, d.out_dim, 1, h, d.out_dim, M, d.out_dim, in_dim, 1.f, 0.f);
+      tr_bias_relu_drop_kernel<<<tr_grid(B * d.out_dim, 256), 256, 0, st>>>(h, d.bias, d.out_dim, B, l < per_res - 1, 0.f, 0, 0, nullptr);
+      in = h; in_dim = d.out_dim;
+    }
+    tr_residual_relu_kernel<<<tr_grid(Bn, 256), 256, 0, st>>>(xs + (int64_t)r * Bn, in, Bn, xs + (int64_t)(r + 1) * Bn);
+  }
+  const float* xR = xs + (int64_t)n_res * Bn;
+  tr_gemm(st, xR, n, 1, final_k, 1, 1, z, 1, M, 1, n, 1.f, 0.f);
+  tr_loss_kernel<<<1, 256, 0, st>>>(z, nullptr, final_b, y, B, dz, loss_out, nullptr, 1.0f);
+  // ---- backward: g = dL/dx_R = dz fk^T (old fk), then the final Dense
+  tr_gemm(st, dz, 1, 1, final_k, 0, 1, g, n, M, n, 1, 1.f, 0.f);
+  tr_gemm(st, xR, 1, n, dz, 1, 1, final_k, 1, n, 1, M, -lr, 1.f);
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
+  for (int r = n_res - 1; r >= 0; --r) {
+    tr_mask_copy_kernel<<<tr_grid(Bn, 256), 256, 0, st>>>(g, xs + (int64_t)(r + 1) * Bn, Bn, gm);   // through the unit's relu
+    const float* gcur = gm;                                  // gradient at the current layer's pre-activation
+    float* ga = ws + w.ga;
+    float* gb = ws + w.gb;
+    for (int l = per_res - 1; l >= 0; --l) {
+      const ctrhot_dense_desc& d = h_layers[r * per_res + l];
+      const int N = d.out_dim, Kd = d.in_dim;
+      const float* hin = l > 0 ? ws + w.act[r][l - 1] : xs + (int64_t)r * Bn;
+      float* W = const_cast<float*>(d.weight);
+      if (l < per_res - 1) {                                 // relu of this hidden layer (gcur is writable here: ga / gb)
+        tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(const_cast<float*>(gcur), ws + w.act[r][l], B * N, 1, 0.f, 0, 0, nullptr);
+      }
+      float* dst = l > 0 ? (gcur == ga ? gb : ga) : g;       // the unit's input gradient lands in g, then the skip path is added
+      tr_gemm(st, gcur, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+      tr_gemm(st, hin, 1, Kd, gcur, N, 1, W, N, Kd, N, M, -lr, 1.f);
+      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(gcur, N, nullptr, B, N, 0, const_cast<float*>(d.bias), -lr, 1.f);
+      gcur = dst;
+    }
+    tr_add_kernel<<<tr_grid(Bn, 256), 256, 0, st>>>(g, gm, Bn);
+  }
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, g, n, lr, nullptr);
+  else
+    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, g, n, lr, nullptr);
+  CTRHOT_LAUNCH_OK("ctrhot_deepcrossing_train_step_f32");
   return CTRHOT_OK;
 }

@@ -9,8 +9,8 @@ rows that were looked up, the FM weights and the tower.  SURVEY 8(f) rank 3; bui
 ``__main__``, DL/model/deepFM.py:34-57) and for FM on its dense one-hot matrix (DL/model/fm.py:26-45, BASELINE config 1;
 ``ctrhot_fm_train_step_f32``) and for DCN (DL/model/dcn.py:37-49: cross layers + tower + the final Dense over their concat;
 ``ctrhot_dcn_train_step_f32``) and for PNN (the loop of DL/model/pnn.py:74-85, which compile_fit reproduces for it: BCE on
-the raw output, no regularisers; ``ctrhot_pnn_train_step_f32``) and for WideDeep (DL/model/wideDeep.py:37-49; ``ctrhot_widedeep_train_step_f32``)
--- other models raise NotImplementedError.
+the raw output, no regularisers; ``ctrhot_pnn_train_step_f32``) and for WideDeep (DL/model/wideDeep.py:37-49; ``ctrhot_widedeep_train_step_f32``) and DeepCrossing
+(DL/model/deepCrossing.py:35-47; ``ctrhot_deepcrossing_train_step_f32``) -- other models raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -27,7 +27,7 @@ class _DeepFMTrainer:
     def __init__(self, model, dropout=None):
         from ..model.criteo import DeepFM
         if not isinstance(model, DeepFM):
-            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, PNN and FM only (SURVEY 8(f) rank 3)")
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, PNN and FM only (SURVEY 8(f) rank 3)")
         self.m = model
         if not model.dnn.built:
             model.build(None)
@@ -340,12 +340,52 @@ def _fit_rows(tr, model, X, y, batch_size, epochs, sgd, seed, verbose):
     return model
 
 
+class _DeepCrossingTrainer:
+    """DeepCrossing (DL/model/deepCrossing.py:14-32): ctrhot_deepcrossing_train_step_f32 per batch -- the residual units'
+    Dense chains, their relu(x + h), the final Dense(1, sigmoid); no dropout, no regularisers."""
+
+    def __init__(self, model, dropout=None):
+        self.m = model
+        if not hasattr(model, "output_layer"):
+            model.build(None)
+        layers = []
+        for r in model.res_layer:
+            layers += [(k, b, _lib.ACT_RELU) for k, b in r.dense_layer] + [(r.output_layer[0], r.output_layer[1], _lib.ACT_NONE)]
+        self.per_res = len(model.res_layer[0].dense_layer) + 1
+        self.desc = (_lib.DenseDesc * len(layers))()
+        for d, (k, b, act) in zip(self.desc, layers):
+            d.weight, d.bias, d.in_dim, d.out_dim, d.act = ptr(k), ptr(b), int(k.shape[0]), int(k.shape[1]), act
+        self._keep = layers
+        self.ws = None
+        self.loss = torch.zeros(2, dtype=torch.float32, device=model.device)
+        self.flag = model.embed_layer.err_flag()
+        self.step = 0
+
+    def train_on_batch(self, dense, ids, y, lr, seed=0):
+        m, E = self.m, self.m.embed_layer
+        ids, kind, ids_ld = ids_arg(ids)
+        B, D = ids.shape[0], dense.shape[1]
+        n = D + E.F * E.k
+        n_res = len(m.res_layer)
+        need = _lib.query("ctrhot_deepcrossing_train_workspace_bytes", B, n, self.desc, n_res, self.per_res)
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=m.device)
+        _lib.call("ctrhot_deepcrossing_train_step_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(dense),
+                  dense.stride(0), D, ptr(y), B, self.desc, n_res, self.per_res, ptr(m.output_layer[0]), ptr(m.output_layer[1]),
+                  float(lr), ptr(self.loss), ptr(self.ws), self.ws.numel() * 4, ptr(self.flag), stream_ptr())
+        self.step += 1
+        return self.loss
+
+
 def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True, use_graph=True):
     """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
     (loss, accuracy) pairs are left in ``model.history``.  ``use_graph``: the full batches of an epoch replay one captured CUDA
     graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
     from ..model.criteo import DCN, FM, PNN, WideDeep
+    from ..model.deepCrossing import DeepCrossing
+    if isinstance(model, DeepCrossing):
+        return _fit_rows(_DeepCrossingTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)
     if isinstance(model, WideDeep):
         # the one-hot columns of the reference's [B, 39 + n_onehot] matrix are implied by the ids (model.onehot_width)
         return _fit_rows(_WideDeepTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)

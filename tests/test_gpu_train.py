@@ -437,3 +437,66 @@ def test_widedeep_compile_fit_learns_and_serves(lib):
     want = O.widedeep_model(np.concatenate([X[:300].astype(np.float64), xw[:, 13:]], axis=1), t, (w0, w), hid, out)
     got = npy(m((X[:300, :13], ids[:300].astype(np.int32))))
     assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))
+
+
+# ------------------------------------------------------------------ DeepCrossing (DL/model/deepCrossing.py under compile_fit)
+def make_deepcrossing(vocab, k_embed, hidden, n_res, seed=1):
+    from recommender_system_b200.model.deepCrossing import DeepCrossing
+    set_seed(seed)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": int(v), "embed_dim": k_embed} for i, v in enumerate(vocab)]]
+    m = DeepCrossing(fc, 32, list(hidden), n_res, embed_dim=k_embed, precision="fp32")
+    m.build(None)
+    rng = np.random.default_rng(seed)
+    upd = {n: rng.normal(0, 0.1, tuple(w.shape)) for n, w in m.named_weights().items() if n.endswith("bias")}
+    m.set_weights({n: np.asarray(v, np.float32) for n, v in upd.items()})
+    return m
+
+
+def deepcrossing_params(m):
+    tables = [npy(t) for t in m.embed_layer.emb_layers]
+    res = [([(npy(k), npy(b)) for k, b in r.dense_layer], (npy(r.output_layer[0]), npy(r.output_layer[1]))) for r in m.res_layer]
+    return tables, res, (npy(m.output_layer[0]), npy(m.output_layer[1]))
+
+
+@pytest.mark.parametrize("B,k_embed,hidden,n_res", [(32, 8, (256, 256), 4), (1, 4, (16,), 1), (300, 16, (64, 32), 2)])
+def test_deepcrossing_one_step_against_the_oracle(lib, B, k_embed, hidden, n_res):
+    """(32, 8, (256, 256), 4) is the reference's __main__ (deepCrossing.py:37-40) at compile_fit's batch size."""
+    from recommender_system_b200.utils.compile_fit import _DeepCrossingTrainer
+    vocab = [50, 7, 1000, 3] + [20] * 22
+    m = make_deepcrossing(vocab, k_embed, hidden, n_res)
+    dense, ids, y = batch(vocab, B, seed=B + 4)
+    t, res, fin = deepcrossing_params(m)
+    lr = 0.05
+    tr = _DeepCrossingTrainer(m)
+    dev = m.device
+    out = tr.train_on_batch(torch.from_numpy(dense).to(dev), torch.from_numpy(ids).to(dev), torch.from_numpy(y).to(dev), lr)
+    torch.cuda.synchronize()
+    want, bce, correct = O.deepcrossing_train_step(dense.astype(np.float64), ids, t, res, fin, y.astype(np.float64), lr)
+    g = deepcrossing_params(m)
+    assert abs(float(out[0]) - bce) <= 2e-6 * max(1.0, bce) and int(out[1]) == correct
+    for f in range(len(vocab)):
+        close(g[0][f], want[0][f], t[f], "table %d" % f)
+    for r in range(n_res):
+        for l in range(len(hidden)):
+            close(g[1][r][0][l][0], want[1][r][0][l][0], res[r][0][l][0], "unit %d kernel %d" % (r, l))
+            close(g[1][r][0][l][1], want[1][r][0][l][1], res[r][0][l][1], "unit %d bias %d" % (r, l))
+        close(g[1][r][1][0], want[1][r][1][0], res[r][1][0], "unit %d out kernel" % r)
+        close(g[1][r][1][1], want[1][r][1][1], res[r][1][1], "unit %d out bias" % r)
+    close(g[2][0], want[2][0], fin[0], "final kernel"); close(g[2][1], want[2][1], fin[1], "final bias")
+
+
+def test_deepcrossing_compile_fit_learns_and_serves(lib):
+    vocab = [30, 7, 120, 50] + [9] * 22
+    rng = np.random.default_rng(3)
+    N = 1500 + 11
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.concatenate([rng.random((N, 13)), ids], axis=1).astype(np.float32)
+    y = (ids[:, 0] < 15).astype(np.float32)
+    m = make_deepcrossing(vocab, 8, (64, 32), 2, seed=5)
+    compile_fit(m, X, y, batch_size=32, epochs=10, sgd=0.2, verbose=False)
+    assert m.history[-1][0] < 0.8 * m.history[0][0] and m.history[-1][1] > 0.8, m.history
+    t, res, fin = deepcrossing_params(m)
+    want = O.deepcrossing_model(X[:300].astype(np.float64), t, res, fin)
+    got = npy(m(X[:300]))
+    assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))

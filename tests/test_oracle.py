@@ -339,3 +339,49 @@ def test_widedeep_train_step_gradients():
         assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, c]) < 1e-7
     gk = fd(hidden[0][0], (5, 3), lambda a: (dense, ids, tables, w0, w, widths, [(a, hidden[0][1]), hidden[1]], out))
     assert abs(gk - ((hidden[0][0] - new[3][0][0]) / lr)[5, 3]) < 1e-7
+
+
+def test_deepcrossing_train_step_gradients():
+    rng = np.random.default_rng(17)
+    B, D, F, K, R = 8, 3, 4, 4, 3
+    vocab = [6, 4, 7, 5]
+    tables = [rng.normal(0, 0.5, (v, K)) for v in vocab]
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1)
+    ids[1] = ids[0]
+    dense = rng.random((B, D))
+    n = D + F * K
+    res = [([(rng.normal(0, 0.3, (n, 6)), rng.normal(0, 0.1, 6)), (rng.normal(0, 0.3, (6, 5)), rng.normal(0, 0.1, 5))],
+            (rng.normal(0, 0.3, (5, n)), rng.normal(0, 0.1, n))) for _ in range(R)]
+    final = (rng.normal(0, 0.3, (n, 1)), rng.normal(0, 0.1, 1))
+    y = rng.integers(0, 2, B).astype(float)
+    lr = 0.05
+    new, bce, _ = O.deepcrossing_train_step(dense, ids, tables, res, final, y, lr)
+
+    def loss(tables_, res_, final_):
+        X = np.concatenate([dense, ids.astype(float)], axis=1)
+        p = np.clip(O.deepcrossing_model(X, tables_, res_, final_, n_dense=D)[:, 0], 1e-7, 1 - 1e-7)
+        return np.mean(-(y * np.log(p) + (1 - y) * np.log(1 - p)))
+    assert abs(loss(tables, res, final) - bce) < 1e-12
+    eps = 1e-6
+
+    def fd(obj, idx, rebuild):
+        a, b = obj.copy(), obj.copy()
+        a[idx] += eps; b[idx] -= eps
+        return (loss(*rebuild(a)) - loss(*rebuild(b))) / (2 * eps)
+
+    def with_res(r, hidden=None, out=None):
+        h, o = res[r]
+        return res[:r] + [(hidden if hidden is not None else h, out if out is not None else o)] + res[r + 1:]
+    for r in range(R):
+        h, o = res[r]
+        gk = fd(h[0][0], (2, 3), lambda a: (tables, with_res(r, hidden=[(a, h[0][1]), h[1]]), final))
+        assert abs(gk - ((h[0][0] - new[1][r][0][0][0]) / lr)[2, 3]) < 1e-7
+        gb = fd(h[1][1], (4,), lambda a: (tables, with_res(r, hidden=[h[0], (h[1][0], a)]), final))
+        assert abs(gb - ((h[1][1] - new[1][r][0][1][1]) / lr)[4]) < 1e-7
+        go = fd(o[0], (1, n - 1), lambda a: (tables, with_res(r, out=(a, o[1])), final))
+        assert abs(go - ((o[0] - new[1][r][1][0]) / lr)[1, n - 1]) < 1e-7
+    gf = fd(final[0], (3, 0), lambda a: (tables, res, (a, final[1])))
+    assert abs(gf - ((final[0] - new[2][0]) / lr)[3, 0]) < 1e-7
+    for f, rr, c in [(0, int(ids[0, 0]), 1), (3, int(ids[4, 3]), 2)]:
+        gt = fd(tables[f], (rr, c), lambda a: (tables[:f] + [a] + tables[f + 1:], res, final))
+        assert abs(gt - ((tables[f] - new[0][f]) / lr)[rr, c]) < 1e-7
