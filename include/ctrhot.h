@@ -448,6 +448,20 @@ int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* row_off, int
                                        float* final_k, float* final_b, float lr, float* loss_out, void* workspace,
                                        int64_t workspace_bytes, int* err_flag, void* stream);
 
+/* ---- 8(f) ranks 1 + 3, NFM under compile_fit (DL/model/nfm.py:15-34 in training mode) -----------------------------------------
+ * x = [dense | 0.5 ((sum_f e_f)^2 - sum_f e_f^2)]; keras BatchNormalization on the BATCH's mean and biased variance (eps 1e-3), the
+ * moving statistics moved by m <- momentum m + (1 - momentum) stat (0.99); DNNLayer (ReLU + Dropout hidden layers, then
+ * Dense(output_dim), act none = the last descriptor); final Dense(output_dim -> 1); sigmoid; mean clipped BCE, no regularisers.
+ * Backward through all of it, the batch statistics included: gx = gamma rstd (g - mean_b g - xhat mean_b (g xhat)),
+ * d bi_c / d e_fc = S_c - e_fc.  Updates in place: arena rows, gamma / beta / moving stats, tower, final_k [output_dim], final_b. */
+int64_t ctrhot_nfm_train_workspace_bytes(int64_t B, int D, int F, int k, const ctrhot_dense_desc* h_layers, int n_layers);
+int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                              int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y, int64_t B,
+                              float* bn_gamma, float* bn_beta, float* bn_mean, float* bn_var, float momentum, float eps,
+                              const ctrhot_dense_desc* h_layers, int n_layers, float* final_k, float* final_b,
+                              float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
+                              int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

@@ -1007,3 +1007,62 @@ def deepcrossing_train_step(dense, ids, tables, res_layers, final, y, lr):
         np.add.at(new_tables[f], ids[:, f], -lr * g[:, off:off + kdim])
         off += kdim
     return (new_tables, new_res, new_final), bce, correct
+
+
+def nfm_train_forward(dense, ids, tables, bn, hidden, out, final, drop_masks=None, eps=1e-3):
+    """NFM.call in TRAINING mode (DL/model/nfm.py:24-34 as model.fit runs it): keras BatchNormalization normalises with the
+    batch's own mean and (biased) variance.  -> (p, cache)."""
+    ids = ids_to_int(ids)
+    emb = np.stack([tables[f][ids[:, f]] for f in range(len(tables))], axis=1)          # [B, F, k]
+    S = np.sum(emb, axis=1)
+    x = np.concatenate([np.asarray(dense, np.float64), 0.5 * (S ** 2 - np.sum(emb ** 2, axis=1))], axis=1)
+    mu, var = np.mean(x, axis=0), np.var(x, axis=0)
+    xhat = (x - mu) / np.sqrt(var + eps)
+    acts = [xhat * bn[2] + bn[3]]
+    for l, (k, b) in enumerate(hidden):
+        h = np.maximum(acts[-1] @ k + b, 0.0)
+        if drop_masks is not None:
+            h = h * drop_masks[l]
+        acts.append(h)
+    d = acts[-1] @ out[0] + out[1]
+    p = sigmoid(d @ final[0] + final[1])[:, 0]
+    return p, (emb, S, x, mu, var, xhat, acts, d)
+
+
+def nfm_train_step(dense, ids, tables, bn, hidden, out, final, y, lr, drop_masks=None, momentum=0.99, eps=1e-3):
+    """One step of keras SGD(lr) on the mean clipped BCE of NFM in training mode (PARITY UNPINNED against the reference, pinned by
+    finite differences THROUGH the batch statistics).  bn = (moving_mean, moving_var, gamma, beta); the moving statistics move by
+    keras' rule  m <- momentum m + (1 - momentum) batch_stat  (biased batch variance: the non-fused 2-D path).
+    -> ((tables, bn, hidden, out, final) updated, mean BCE before the update, number of correct predictions)."""
+    ids = ids_to_int(ids)
+    B, D, F = ids.shape[0], np.asarray(dense).shape[1], len(tables)
+    p, (emb, S, x, mu, var, xhat, acts, d) = nfm_train_forward(dense, ids, tables, bn, hidden, out, final, drop_masks, eps)
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    correct = int(np.sum((p > 0.5) == (y > 0.5)))
+    dz = (np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B)[:, None]
+    new_final = (final[0] - lr * (d.T @ dz), final[1] - lr * np.sum(dz))
+    gd = dz @ final[0].T                                                               # [B, od]
+    g = gd @ out[0].T
+    new_out = (out[0] - lr * (acts[-1].T @ gd), out[1] - lr * np.sum(gd, axis=0))
+    new_hidden = [None] * len(hidden)
+    for l in range(len(hidden) - 1, -1, -1):
+        k, b = hidden[l]
+        m = (acts[l + 1] > 0).astype(np.float64)
+        if drop_masks is not None:
+            m = m * np.max(drop_masks[l])
+        g = g * m
+        gin = g @ k.T
+        new_hidden[l] = (k - lr * (acts[l].T @ g), b - lr * np.sum(g, axis=0))
+        g = gin
+    # BatchNormalization backward (batch statistics are functions of x)
+    dgamma, dbeta = np.sum(g * xhat, axis=0), np.sum(g, axis=0)
+    rstd = 1.0 / np.sqrt(var + eps)
+    gx = bn[2] * rstd * (g - dbeta / B - xhat * dgamma / B)
+    new_bn = (momentum * bn[0] + (1 - momentum) * mu, momentum * bn[1] + (1 - momentum) * var, bn[2] - lr * dgamma, bn[3] - lr * dbeta)
+    # Bi-Interaction backward: d bi_c / d e_fc = S_c - e_fc
+    de = gx[:, None, D:] * (S[:, None, :] - emb)
+    new_tables = [t.copy() for t in tables]
+    for f in range(F):
+        np.add.at(new_tables[f], ids[:, f], -lr * de[:, f, :])
+    return (new_tables, new_bn, new_hidden, new_out, new_final), bce, correct

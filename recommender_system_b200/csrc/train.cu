@@ -452,6 +452,100 @@ __global__ void tr_add_kernel(float* __restrict__ a, const float* __restrict__ b
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) a[i] += b[i];
 }
 
+// ---------------------------------------------------------------- NFM (DL/model/nfm.py:15-34) in training mode
+// x[b] = [dense (D) | 0.5 ((sum_f e_f)^2 - sum_f e_f^2) (k)];  S[b, c] = sum_f e_fc is kept for the backward pass
+template <int IDKIND>
+__global__ void tr_nfm_bi_fwd_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                                     const void* __restrict__ ids, int64_t ids_ld, const float* __restrict__ dense, int64_t dense_ld,
+                                     int D, int64_t B, float* __restrict__ x, float* __restrict__ S, int* __restrict__ err_flag) {
+  const int n = D + k;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / n;
+    const int c = (int)(i - b * n);
+    if (c < D) { x[i] = dense[b * dense_ld + c]; continue; }
+    float s = 0.f, q = 0.f;
+    for (int f = 0; f < F; ++f) {
+      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      const bool ok = id >= 0 && id < row_off[f + 1] - row_off[f];
+      if (!ok && err_flag) *err_flag = 1;
+      const float e = ok ? arena[(row_off[f] + id) * k + (c - D)] : 0.f;
+      s += e; q = fmaf(e, e, q);
+    }
+    S[b * k + (c - D)] = s;
+    x[i] = 0.5f * (s * s - q);
+  }
+}
+// keras BatchNormalization, training: per column the batch mean and BIASED variance (two passes, fixed order), xhat, y = gamma
+// xhat + beta, and the moving statistics  m <- momentum m + (1 - momentum) stat.  One block of 256 threads per column.
+__global__ void __launch_bounds__(256)
+tr_bn_fwd_kernel(const float* __restrict__ x, int n, int64_t B, const float* __restrict__ gamma, const float* __restrict__ beta,
+                 float* __restrict__ mov_mean, float* __restrict__ mov_var, float momentum, float eps, float* __restrict__ xhat,
+                 float* __restrict__ y, float* __restrict__ rstd_out) {
+  __shared__ float red[256];
+  const int j = blockIdx.x;
+  float s = 0.f;
+  for (int64_t b = threadIdx.x; b < B; b += 256) s += x[b * n + j];
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o >= 1; o >>= 1) { if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+  const float mean = red[0] / (float)B;
+  __syncthreads();
+  float v = 0.f;
+  for (int64_t b = threadIdx.x; b < B; b += 256) { const float d = x[b * n + j] - mean; v = fmaf(d, d, v); }
+  red[threadIdx.x] = v;
+  __syncthreads();
+  for (int o = 128; o >= 1; o >>= 1) { if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+  const float var = red[0] / (float)B;
+  const float rstd = 1.0f / sqrtf(var + eps);
+  const float g = gamma[j], bt = beta[j];
+  for (int64_t b = threadIdx.x; b < B; b += 256) {
+    const float h = (x[b * n + j] - mean) * rstd;
+    xhat[b * n + j] = h;
+    y[b * n + j] = fmaf(g, h, bt);
+  }
+  if (threadIdx.x == 0) {
+    rstd_out[j] = rstd;
+    mov_mean[j] = momentum * mov_mean[j] + (1.f - momentum) * mean;
+    mov_var[j] = momentum * mov_var[j] + (1.f - momentum) * var;
+  }
+}
+// backward: dgamma = sum_b g xhat, dbeta = sum_b g, gx = gamma rstd (g - dbeta / B - xhat dgamma / B); then gamma, beta move
+__global__ void __launch_bounds__(256)
+tr_bn_bwd_kernel(const float* __restrict__ g, const float* __restrict__ xhat, int n, int64_t B, float* __restrict__ gamma,
+                 float* __restrict__ beta, const float* __restrict__ rstd, float lr, float* __restrict__ gx) {
+  __shared__ float r1[256], r2[256];
+  const int j = blockIdx.x;
+  float a = 0.f, c = 0.f;
+  for (int64_t b = threadIdx.x; b < B; b += 256) { const float gg = g[b * n + j]; a = fmaf(gg, xhat[b * n + j], a); c += gg; }
+  r1[threadIdx.x] = a; r2[threadIdx.x] = c;
+  __syncthreads();
+  for (int o = 128; o >= 1; o >>= 1) {
+    if ((int)threadIdx.x < o) { r1[threadIdx.x] += r1[threadIdx.x + o]; r2[threadIdx.x] += r2[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  const float dgamma = r1[0], dbeta = r2[0];
+  const float sc = gamma[j] * rstd[j], ib = 1.f / (float)B;
+  for (int64_t b = threadIdx.x; b < B; b += 256)
+    gx[b * n + j] = sc * (g[b * n + j] - dbeta * ib - xhat[b * n + j] * dgamma * ib);
+  __syncthreads();
+  if (threadIdx.x == 0) { gamma[j] -= lr * dgamma; beta[j] -= lr * dbeta; }
+}
+// Bi-Interaction backward: dE[b, f, c] = gx[b, D + c] (S[b, c] - e_fc), rows read from the arena BEFORE it moves
+template <int IDKIND>
+__global__ void tr_nfm_bi_bwd_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                                     const void* __restrict__ ids, int64_t ids_ld, int D, int64_t B, const float* __restrict__ gx,
+                                     const float* __restrict__ S, float* __restrict__ dE) {
+  const int fk = F * k, n = D + k;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * fk; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / fk;
+    const int r = (int)(i - b * fk), f = r / k, c = r - f * k;
+    const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+    const bool ok = id >= 0 && id < row_off[f + 1] - row_off[f];
+    const float e = ok ? arena[(row_off[f] + id) * k + c] : 0.f;
+    dE[i] = gx[b * n + D + c] * (S[b * k + c] - e);
+  }
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -1074,5 +1168,114 @@ extern "C" int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* r
   else
     tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, g, n, lr, nullptr);
   CTRHOT_LAUNCH_OK("ctrhot_deepcrossing_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- NFM training step (SURVEY 8(f) ranks 1 + 3)
+// h_layers: the DNNLayer's ReLU hidden layers (Dropout after each), then its Dense(output_dim) (act none); final_k [output_dim, 1]
+namespace {
+struct TrNfmLayout { int64_t x, S, xhat, y, rstd, d, z, dz, gd, gy, gx, dE, g0, g1, h[TR_MAXL], total; int maxw; };
+bool tr_nfm_layout(int64_t B, int n, int fk, int k, const ctrhot_dense_desc* Ld, int n_layers, TrNfmLayout& w) {
+  if (!Ld || n_layers < 2 || n_layers > TR_MAXL || B < 0 || n <= 0) return false;
+  if (Ld[0].in_dim != n) return false;
+  int64_t o = 0;
+  auto take = [&](int64_t cnt) { const int64_t at = o; o += (cnt + 3) / 4 * 4; return at; };
+  w.maxw = n;
+  for (int l = 0; l < n_layers; ++l) {
+    if (l > 0 && Ld[l].in_dim != Ld[l - 1].out_dim) return false;
+    if (Ld[l].act != (l < n_layers - 1 ? CTRHOT_ACT_RELU : CTRHOT_ACT_NONE)) return false;
+    if (!Ld[l].weight || !Ld[l].bias) return false;
+    if (Ld[l].out_dim > w.maxw) w.maxw = Ld[l].out_dim;
+  }
+  const int od = Ld[n_layers - 1].out_dim;
+  w.x = take(B * n); w.S = take(B * k); w.xhat = take(B * n); w.y = take(B * n); w.rstd = take(n); w.d = take(B * od);
+  w.z = take(B); w.dz = take(B); w.gd = take(B * od); w.gy = take(B * n); w.gx = take(B * n); w.dE = take(B * (int64_t)fk);
+  w.g0 = take(B * (int64_t)w.maxw); w.g1 = take(B * (int64_t)w.maxw);
+  for (int l = 0; l < n_layers - 1; ++l) w.h[l] = take(B * (int64_t)Ld[l].out_dim);
+  w.total = o;
+  return true;
+}
+}  // namespace
+
+extern "C" int64_t ctrhot_nfm_train_workspace_bytes(int64_t B, int D, int F, int k, const ctrhot_dense_desc* h_layers, int n_layers) {
+  TrNfmLayout w;
+  if (!tr_nfm_layout(B, D + k, F * k, k, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  return w.total * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                         int64_t ids_ld, const float* dense, int64_t dense_ld, int D, const float* y, int64_t B,
+                                         float* bn_gamma, float* bn_beta, float* bn_mean, float* bn_var, float momentum, float eps,
+                                         const ctrhot_dense_desc* h_layers, int n_layers, float* final_k, float* final_b,
+                                         float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
+                                         int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_nfm_train_step_f32");
+  if (!arena || !row_off || !ids || !y || !bn_gamma || !bn_beta || !bn_mean || !bn_var || !final_k || !final_b || !loss_out ||
+      !workspace || F <= 0 || k <= 0 || D < 0 || (D > 0 && !dense) || B <= 0 || ids_ld < F || (D > 0 && dense_ld < D))
+    return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (!(dropout >= 0.f && dropout < 1.f) || !(lr >= 0.f)) return CTRHOT_EARG;
+  const int n = D + k, fk = F * k;
+  TrNfmLayout w;
+  if (!tr_nfm_layout(B, n, fk, k, h_layers, n_layers, w)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < w.total * (int64_t)sizeof(float) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  float *x = ws + w.x, *S = ws + w.S, *xhat = ws + w.xhat, *yb = ws + w.y, *rstd = ws + w.rstd, *d = ws + w.d, *z = ws + w.z,
+        *dz = ws + w.dz, *gd = ws + w.gd, *gy = ws + w.gy, *gx = ws + w.gx, *dE = ws + w.dE;
+  const int NH = n_layers - 1, M = (int)B, od = h_layers[NH].out_dim;
+  // ---- forward: Bi-Interaction, BatchNormalization on the batch's statistics, tower, Dense(1)
+  if (ids_kind == CTRHOT_IDS_I32)
+    tr_nfm_bi_fwd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, S, err_flag);
+  else
+    tr_nfm_bi_fwd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, dense, dense_ld, D, B, x, S, err_flag);
+  tr_bn_fwd_kernel<<<n, 256, 0, st>>>(x, n, B, bn_gamma, bn_beta, bn_mean, bn_var, momentum, eps, xhat, yb, rstd);
+  const float* in = yb;
+  int in_dim = n;
+  for (int l = 0; l < NH; ++l) {
+    float* h = ws + w.h[l];
+    const int N = h_layers[l].out_dim;
+    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
+    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    in = h; in_dim = N;
+  }
+  tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, od, 1, d, od, M, od, in_dim, 1.f, 0.f);
+  tr_bias_relu_drop_kernel<<<tr_grid(B * od, 256), 256, 0, st>>>(d, h_layers[NH].bias, od, B, 0, 0.f, 0, 0, nullptr);
+  tr_gemm(st, d, od, 1, final_k, 1, 1, z, 1, M, 1, od, 1.f, 0.f);
+  tr_loss_kernel<<<1, 256, 0, st>>>(z, nullptr, final_b, y, B, dz, loss_out, nullptr, 1.0f);
+  // ---- backward: final Dense(1), the DNNLayer's output layer, its hidden layers
+  tr_gemm(st, dz, 1, 1, final_k, 0, 1, gd, od, M, od, 1, 1.f, 0.f);                         // gd = dz fk^T (old fk)
+  tr_gemm(st, d, 1, od, dz, 1, 1, final_k, 1, od, 1, M, -lr, 1.f);
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
+  float* g = ws + w.g0;
+  float* gn = ws + w.g1;
+  {
+    float* wo = const_cast<float*>(h_layers[NH].weight);
+    tr_gemm(st, gd, od, 1, wo, 1, od, g, in_dim, M, in_dim, od, 1.f, 0.f);                  // [B, od] x [od, h]: B(k, n) = wo[n * od + k]
+    tr_gemm(st, in, 1, in_dim, gd, od, 1, wo, od, in_dim, od, M, -lr, 1.f);
+    tr_colsum_kernel<<<(od + 31) / 32, 1024, 0, st>>>(gd, od, nullptr, B, od, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
+  }
+  for (int l = NH - 1; l >= 0; --l) {
+    const int N = h_layers[l].out_dim, Kd = h_layers[l].in_dim;
+    const float* h = ws + w.h[l];
+    const float* hin = l > 0 ? ws + w.h[l - 1] : yb;
+    float* W = const_cast<float*>(h_layers[l].weight);
+    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    float* dst = l > 0 ? gn : gy;
+    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
+    tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
+  }
+  // ---- BatchNormalization (gamma, beta move), Bi-Interaction, embedding rows
+  tr_bn_bwd_kernel<<<n, 256, 0, st>>>(gy, xhat, n, B, bn_gamma, bn_beta, rstd, lr, gx);
+  if (ids_kind == CTRHOT_IDS_I32) {
+    tr_nfm_bi_bwd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, gx, S, dE);
+    tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dE, fk, lr, nullptr);
+  } else {
+    tr_nfm_bi_bwd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, gx, S, dE);
+    tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dE, fk, lr, nullptr);
+  }
+  CTRHOT_LAUNCH_OK("ctrhot_nfm_train_step_f32");
   return CTRHOT_OK;
 }

@@ -10,7 +10,8 @@ rows that were looked up, the FM weights and the tower.  SURVEY 8(f) rank 3; bui
 ``ctrhot_fm_train_step_f32``) and for DCN (DL/model/dcn.py:37-49: cross layers + tower + the final Dense over their concat;
 ``ctrhot_dcn_train_step_f32``) and for PNN (the loop of DL/model/pnn.py:74-85, which compile_fit reproduces for it: BCE on
 the raw output, no regularisers; ``ctrhot_pnn_train_step_f32``) and for WideDeep (DL/model/wideDeep.py:37-49; ``ctrhot_widedeep_train_step_f32``) and DeepCrossing
-(DL/model/deepCrossing.py:35-47; ``ctrhot_deepcrossing_train_step_f32``) -- other models raise NotImplementedError.
+(DL/model/deepCrossing.py:35-47; ``ctrhot_deepcrossing_train_step_f32``) and NFM (DL/model/nfm.py:37-50, BatchNormalization in training
+mode; ``ctrhot_nfm_train_step_f32``) -- other models raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -27,7 +28,7 @@ class _DeepFMTrainer:
     def __init__(self, model, dropout=None):
         from ..model.criteo import DeepFM
         if not isinstance(model, DeepFM):
-            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, PNN and FM only (SURVEY 8(f) rank 3)")
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, NFM, PNN and FM only (SURVEY 8(f) rank 3)")
         self.m = model
         if not model.dnn.built:
             model.build(None)
@@ -377,13 +378,53 @@ class _DeepCrossingTrainer:
         return self.loss
 
 
+class _NFMTrainer:
+    """NFM (DL/model/nfm.py:15-34) in training mode: ctrhot_nfm_train_step_f32 per batch -- Bi-Interaction, BatchNormalization on
+    the batch's own statistics (moving statistics updated with keras' momentum 0.99), DNNLayer, the final Dense(1)."""
+
+    def __init__(self, model, dropout=None):
+        self.m = model
+        if not model.dnn_layers.built:
+            model.build(None)
+        dl = model.dnn_layers
+        if dl.activation != "relu":
+            raise NotImplementedError("compile_fit: DNNLayer(activation='relu') only")
+        self.dropout = float(dl.dropout if dropout is None else dropout)
+        layers = [(k, b, _lib.ACT_RELU) for k, b in dl.hidden] + [(dl.output[0], dl.output[1], _lib.ACT_NONE)]
+        self.desc = (_lib.DenseDesc * len(layers))()
+        for d, (k, b, act) in zip(self.desc, layers):
+            d.weight, d.bias, d.in_dim, d.out_dim, d.act = ptr(k), ptr(b), int(k.shape[0]), int(k.shape[1]), act
+        self._keep = layers
+        self.ws = None
+        self.loss = torch.zeros(2, dtype=torch.float32, device=model.device)
+        self.flag = model.err_flag()
+        self.step = 0
+
+    def train_on_batch(self, dense, ids, y, lr, seed=0):
+        m, E = self.m, self.m.emb_layers
+        ids, kind, ids_ld = ids_arg(ids)
+        B, D = ids.shape[0], dense.shape[1]
+        need = _lib.query("ctrhot_nfm_train_workspace_bytes", B, D, E.F, E.k, self.desc, len(self.desc))
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=m.device)
+        _lib.call("ctrhot_nfm_train_step_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(dense),
+                  dense.stride(0), D, ptr(y), B, ptr(m.bn_gamma), ptr(m.bn_beta), ptr(m.bn_mean), ptr(m.bn_var), 0.99, 1e-3,
+                  self.desc, len(self.desc), ptr(m.out_kernel), ptr(m.out_bias), float(lr), self.dropout,
+                  int(seed) & (2 ** 64 - 1), ptr(self.loss), ptr(self.ws), self.ws.numel() * 4, ptr(self.flag), stream_ptr())
+        self.step += 1
+        return self.loss
+
+
 def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True, use_graph=True):
     """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
     (loss, accuracy) pairs are left in ``model.history``.  ``use_graph``: the full batches of an epoch replay one captured CUDA
     graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
-    from ..model.criteo import DCN, FM, PNN, WideDeep
+    from ..model.criteo import DCN, FM, NFM, PNN, WideDeep
     from ..model.deepCrossing import DeepCrossing
+    if isinstance(model, NFM):
+        model.embed_layer = model.emb_layers                      # (_fit_rows reads the field count from .embed_layer)
+        return _fit_rows(_NFMTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)
     if isinstance(model, DeepCrossing):
         return _fit_rows(_DeepCrossingTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)
     if isinstance(model, WideDeep):

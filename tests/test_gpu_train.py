@@ -500,3 +500,76 @@ def test_deepcrossing_compile_fit_learns_and_serves(lib):
     want = O.deepcrossing_model(X[:300].astype(np.float64), t, res, fin)
     got = npy(m(X[:300]))
     assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))
+
+
+# ------------------------------------------------------------------ NFM (DL/model/nfm.py under compile_fit, BN in training mode)
+def make_nfm(vocab, k_embed, hidden, od=1, dropout=0.0, seed=1):
+    from recommender_system_b200.model.criteo import NFM
+    set_seed(seed)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": int(v), "embed_dim": k_embed} for i, v in enumerate(vocab)]]
+    m = NFM(fc, list(hidden), od, "relu", dropout, embed_dim=k_embed, precision="fp32")
+    m.build(None)
+    rng = np.random.default_rng(seed)
+    upd = {}
+    for n, w in m.named_weights().items():
+        if n.endswith("bias") or n.endswith("beta") or n.endswith("moving_mean"):
+            upd[n] = rng.normal(0, 0.1, tuple(w.shape))
+        elif n.endswith("gamma") or n.endswith("moving_variance"):
+            upd[n] = rng.uniform(0.5, 1.5, tuple(w.shape))
+        elif n.endswith("embeddings"):
+            upd[n] = rng.normal(0, 0.3, tuple(w.shape))
+    m.set_weights({n: np.asarray(v, np.float32) for n, v in upd.items()})
+    return m
+
+
+def nfm_params(m):
+    tables = [npy(t) for t in m.emb_layers.emb_layers]
+    bn = (npy(m.bn_mean), npy(m.bn_var), npy(m.bn_gamma), npy(m.bn_beta))
+    hidden = [(npy(k), npy(b)) for k, b in m.dnn_layers.hidden]
+    return tables, bn, hidden, (npy(m.dnn_layers.output[0]), npy(m.dnn_layers.output[1])), (npy(m.out_kernel), npy(m.out_bias))
+
+
+@pytest.mark.parametrize("B,k_embed,hidden,od,rate", [(32, 8, (256, 128, 64), 1, 0.0), (5, 4, (16,), 3, 0.0), (700, 16, (64, 32), 1, 0.3)])
+def test_nfm_one_step_against_the_oracle(lib, B, k_embed, hidden, od, rate):
+    from recommender_system_b200.utils.compile_fit import _NFMTrainer
+    vocab = [50, 7, 1000, 3] + [20] * 22
+    m = make_nfm(vocab, k_embed, hidden, od, rate)
+    dense, ids, y = batch(vocab, B, seed=B + 5)
+    t, bn, hid, out, fin = nfm_params(m)
+    lr, seed = 0.05, 77
+    tr = _NFMTrainer(m)
+    dev = m.device
+    res = tr.train_on_batch(torch.from_numpy(dense).to(dev), torch.from_numpy(ids).to(dev), torch.from_numpy(y).to(dev), lr, seed=seed)
+    torch.cuda.synchronize()
+    masks = kernel_masks(seed, hidden, B, rate) if rate > 0 else None
+    want, bce, correct = O.nfm_train_step(dense.astype(np.float64), ids, t, bn, hid, out, fin, y.astype(np.float64), lr, masks)
+    g = nfm_params(m)
+    assert abs(float(res[0]) - bce) <= 5e-6 * max(1.0, bce) and abs(int(res[1]) - correct) <= 1
+    for f in range(len(vocab)):
+        close(g[0][f], want[0][f], t[f], "table %d" % f, floor=1e-6)
+    for i, name in enumerate(("moving mean", "moving var", "gamma", "beta")):
+        close(g[1][i], want[1][i], bn[i], name, floor=1e-6)
+    for l in range(len(hidden)):
+        close(g[2][l][0], want[2][l][0], hid[l][0], "kernel %d" % l, floor=1e-6)
+        close(g[2][l][1], want[2][l][1], hid[l][1], "bias %d" % l, floor=1e-6)
+    close(g[3][0], want[3][0], out[0], "dnn out kernel", floor=1e-6); close(g[3][1], want[3][1], out[1], "dnn out bias", floor=1e-6)
+    close(g[4][0], want[4][0], fin[0], "final kernel", floor=1e-6); close(g[4][1], want[4][1], fin[1], "final bias", floor=1e-6)
+
+
+def test_nfm_compile_fit_learns_and_serves(lib):
+    """After training, the forward path (inference BatchNormalization on the MOVING statistics the steps maintained) agrees with
+    the float64 oracle on the trained weights."""
+    vocab = [30, 7, 120, 50] + [9] * 22
+    rng = np.random.default_rng(3)
+    N = 1500 + 13
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.concatenate([rng.random((N, 13)), ids], axis=1).astype(np.float32)
+    y = (ids[:, 0] < 15).astype(np.float32)
+    m = make_nfm(vocab, 8, (64, 32), 1, 0.0, seed=5)
+    compile_fit(m, X, y, batch_size=32, epochs=8, sgd=0.1, verbose=False)
+    assert m.history[-1][0] < m.history[0][0], m.history
+    t, bn, hid, out, fin = nfm_params(m)
+    want = O.nfm_model(X[:300].astype(np.float64), t, bn, hid, out, fin)
+    got = npy(m(X[:300]))
+    assert np.max(np.abs(got - want)) <= 5e-5, np.max(np.abs(got - want))

@@ -385,3 +385,52 @@ def test_deepcrossing_train_step_gradients():
     for f, rr, c in [(0, int(ids[0, 0]), 1), (3, int(ids[4, 3]), 2)]:
         gt = fd(tables[f], (rr, c), lambda a: (tables[:f] + [a] + tables[f + 1:], res, final))
         assert abs(gt - ((tables[f] - new[0][f]) / lr)[rr, c]) < 1e-7
+
+
+def test_nfm_train_step_gradients():
+    """Finite differences go through the batch statistics of the training-mode BatchNormalization."""
+    rng = np.random.default_rng(19)
+    B, D, F, K = 9, 3, 4, 4
+    vocab = [6, 4, 7, 5]
+    tables = [rng.normal(0, 0.5, (v, K)) for v in vocab]
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1)
+    ids[1] = ids[0]
+    dense = rng.random((B, D))
+    n = D + K
+    bn = (rng.normal(0, 0.1, n), rng.uniform(0.5, 1.5, n), rng.uniform(0.5, 1.5, n), rng.normal(0, 0.1, n))
+    hidden = [(rng.normal(0, 0.4, (n, 7)), rng.normal(0, 0.1, 7)), (rng.normal(0, 0.4, (7, 5)), rng.normal(0, 0.1, 5))]
+    out = (rng.normal(0, 0.5, (5, 2)), rng.normal(0, 0.1, 2))
+    final = (rng.normal(0, 0.5, (2, 1)), rng.normal(0, 0.1, 1))
+    y = rng.integers(0, 2, B).astype(float)
+    masks = [(rng.random((B, 7)) >= 0.25) / 0.75, (rng.random((B, 5)) >= 0.25) / 0.75]
+    lr = 0.05
+    new, bce, _ = O.nfm_train_step(dense, ids, tables, bn, hidden, out, final, y, lr, masks)
+
+    def loss(tables_, bn_, hidden_, out_, final_):
+        p = np.clip(O.nfm_train_forward(dense, ids, tables_, bn_, hidden_, out_, final_, masks)[0], 1e-7, 1 - 1e-7)
+        return np.mean(-(y * np.log(p) + (1 - y) * np.log(1 - p)))
+    assert abs(loss(tables, bn, hidden, out, final) - bce) < 1e-12
+    eps = 1e-6
+
+    def fd(obj, idx, rebuild):
+        a, b = obj.copy(), obj.copy()
+        a[idx] += eps; b[idx] -= eps
+        return (loss(*rebuild(a)) - loss(*rebuild(b))) / (2 * eps)
+    for f, r, c in [(0, int(ids[0, 0]), 1), (3, int(ids[4, 3]), 2), (2, int(ids[7, 2]), 0)]:
+        gt = fd(tables[f], (r, c), lambda a: (tables[:f] + [a] + tables[f + 1:], bn, hidden, out, final))
+        assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, c]) < 1e-7
+    for j in (0, D, n - 1):
+        gg = fd(bn[2], (j,), lambda a: (tables, (bn[0], bn[1], a, bn[3]), hidden, out, final))
+        assert abs(gg - ((bn[2] - new[1][2]) / lr)[j]) < 1e-7
+        gb = fd(bn[3], (j,), lambda a: (tables, (bn[0], bn[1], bn[2], a), hidden, out, final))
+        assert abs(gb - ((bn[3] - new[1][3]) / lr)[j]) < 1e-7
+    gk = fd(hidden[0][0], (2, 3), lambda a: (tables, bn, [(a, hidden[0][1]), hidden[1]], out, final))
+    assert abs(gk - ((hidden[0][0] - new[2][0][0]) / lr)[2, 3]) < 1e-7
+    go = fd(out[0], (3, 1), lambda a: (tables, bn, hidden, (a, out[1]), final))
+    assert abs(go - ((out[0] - new[3][0]) / lr)[3, 1]) < 1e-7
+    gf = fd(final[0], (1, 0), lambda a: (tables, bn, hidden, out, (a, final[1])))
+    assert abs(gf - ((final[0] - new[4][0]) / lr)[1, 0]) < 1e-7
+    # moving statistics: keras' momentum rule on the batch mean / biased variance of x = [dense | bi-interaction]
+    x = O.nfm_train_forward(dense, ids, tables, bn, hidden, out, final, masks)[1][2]
+    np.testing.assert_allclose(new[1][0], 0.99 * bn[0] + 0.01 * x.mean(0), rtol=0, atol=1e-15)
+    np.testing.assert_allclose(new[1][1], 0.99 * bn[1] + 0.01 * x.var(0), rtol=0, atol=1e-15)
