@@ -462,6 +462,17 @@ int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k
                               float lr, float dropout, uint64_t seed, float* loss_out, void* workspace,
                               int64_t workspace_bytes, int* err_flag, void* stream);
 
+/* ---- 8(f) ranks 1 + 3, AFM under compile_fit (DL/model/afm.py; AFMLayer DL/layer/interaction.py:322-351) --------------------------
+ * x = pool over pairs of e_i * e_j (mode 0 mean, 1 'att' = sum: the softmax over a size-1 axis, :316, makes every weight 1 and leaves
+ * AttentionLayer's Dense layers without gradient; 2 max), q = sigmoid(x w + b), p = sigmoid(q) (n_sigmoid 2: AFM.call) or q
+ * (1: AFMLayer alone); mean clipped BCE.  Updates in place: arena rows (sum / mean: d / d e_fc = S_c - e_fc; max: the arg-max
+ * pair only), out_k [k], out_b [1]. */
+int64_t ctrhot_afm_train_workspace_bytes(int64_t B, int F, int k);
+int ctrhot_afm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                              int64_t ids_ld, const float* y, int64_t B, int mode, int n_sigmoid, float* out_k,
+                              float* out_b, float lr, float* loss_out, void* workspace, int64_t workspace_bytes,
+                              int* err_flag, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

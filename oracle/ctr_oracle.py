@@ -1066,3 +1066,49 @@ def nfm_train_step(dense, ids, tables, bn, hidden, out, final, y, lr, drop_masks
     for f in range(F):
         np.add.at(new_tables[f], ids[:, f], -lr * de[:, f, :])
     return (new_tables, new_bn, new_hidden, new_out, new_final), bce, correct
+
+
+def afm_train_step(ids, tables, mode, out, y, lr, n_sigmoid=2):
+    """One step of keras SGD(lr) on the mean clipped BCE of AFM (DL/model/afm.py: sigmoid of AFMLayer's already-sigmoid output,
+    n_sigmoid = 2; AFMLayer alone: 1).  In 'att' mode the attention weights are identically 1 (softmax over a size-1 axis,
+    interaction.py:316), so AttentionLayer's two Dense layers receive zero gradient and do not move; the pooled vector is the sum
+    over pairs.  PARITY UNPINNED against the reference, pinned by finite differences of `afm_layer`'s loss.
+    -> ((tables, out) updated, mean BCE before the update, number of correct predictions)."""
+    ids = ids_to_int(ids)
+    B, F = ids.shape[0], len(tables)
+    e = np.stack([tables[f][ids[:, f]] for f in range(F)], axis=1)                     # [B, F, k]
+    row, col = pair_index(F)
+    pairs = e[:, row, :] * e[:, col, :]                                                # [B, P, k]
+    P = len(row)
+    if mode == "avg":
+        x = pairs.mean(axis=1)
+    elif mode == "max":
+        x = pairs.max(axis=1)
+    else:
+        x = pairs.sum(axis=1)
+    q = sigmoid(x @ out[0] + out[1])[:, 0]
+    p = sigmoid(q) if n_sigmoid == 2 else q
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    correct = int(np.sum((p > 0.5) == (y > 0.5)))
+    if n_sigmoid == 2:
+        dq = np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B                    # d/d(logit of the outer sigmoid) = d/dq
+        dz = (dq * q * (1 - q))[:, None]
+    else:
+        dz = (np.where((p > 1e-7) & (p < 1 - 1e-7), pc - y, 0.0) / B)[:, None]
+    new_out = (out[0] - lr * (x.T @ dz), out[1] - lr * np.sum(dz))
+    gx = dz @ out[0].T                                                                 # [B, k]
+    if mode == "max":
+        arg = pairs.argmax(axis=1)                                                     # [B, k]
+        gp = np.zeros_like(pairs)
+        bi, ci = np.meshgrid(np.arange(B), np.arange(pairs.shape[2]), indexing="ij")
+        gp[bi, arg, ci] = gx
+    else:
+        gp = np.broadcast_to(gx[:, None, :] / (P if mode == "avg" else 1.0), pairs.shape)
+    de = np.zeros_like(e)
+    np.add.at(de, (slice(None), row), gp * e[:, col, :])
+    np.add.at(de, (slice(None), col), gp * e[:, row, :])
+    new_tables = [t.copy() for t in tables]
+    for f in range(F):
+        np.add.at(new_tables[f], ids[:, f], -lr * de[:, f, :])
+    return (new_tables, new_out), bce, correct

@@ -546,6 +546,89 @@ __global__ void tr_nfm_bi_bwd_kernel(const float* __restrict__ arena, const int6
   }
 }
 
+// ---------------------------------------------------------------- AFM (DL/model/afm.py, AFMLayer DL/layer/interaction.py:322-351)
+// x[b, c] = pool over pairs i < j of e_ic e_jc: sum ('att': the softmax over a size-1 axis makes every weight 1), mean, or max
+// (with the arg-max pair kept).  sum = 0.5 (S^2 - Q); S[b, c] = sum_f e_fc is kept for the backward pass.
+template <int IDKIND>
+__global__ void tr_afm_fwd_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                                  const void* __restrict__ ids, int64_t ids_ld, int64_t B, int mode, float* __restrict__ x,
+                                  float* __restrict__ S, int32_t* __restrict__ amax, int* __restrict__ err_flag) {
+  const int P = F * (F - 1) / 2;
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < B * k; i0 += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i0 / k;
+    const int c = (int)(i0 - b * k);
+    auto row = [&](int f) {
+      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      const bool ok = id >= 0 && id < row_off[f + 1] - row_off[f];
+      if (!ok && err_flag) *err_flag = 1;
+      return ok ? arena[(row_off[f] + id) * k + c] : 0.f;
+    };
+    if (mode == 2) {                                               // max over pairs, first maximum wins (numpy / tf argmax)
+      float best = -INFINITY;
+      int bi = 0, bj = 1;
+      for (int i = 0; i < F - 1; ++i) {
+        const float ei = row(i);
+        for (int j = i + 1; j < F; ++j) {
+          const float v = ei * row(j);
+          if (v > best) { best = v; bi = i; bj = j; }
+        }
+      }
+      x[i0] = best;
+      amax[i0] = (bi << 16) | bj;
+    } else {
+      float s = 0.f, q = 0.f;
+      for (int f = 0; f < F; ++f) { const float e = row(f); s += e; q = fmaf(e, e, q); }
+      S[i0] = s;
+      const float sum = 0.5f * (s * s - q);
+      x[i0] = mode == 0 ? sum / (float)P : sum;
+    }
+  }
+}
+// q = sigmoid(z + b); p = sigmoid(q) (n_sigmoid 2: AFM.call) or q (AFMLayer alone); mean clipped BCE; dz = d loss / d z
+__global__ void tr_afm_loss_kernel(const float* __restrict__ z, const float* __restrict__ b_out, const float* __restrict__ y,
+                                   int64_t B, int n_sigmoid, float* __restrict__ dz, float* __restrict__ loss_out) {
+  __shared__ float s_loss[256], s_ok[256];
+  float l = 0.f, ok = 0.f;
+  for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
+    const float q = 1.0f / (1.0f + __expf(-(z[b] + b_out[0])));
+    const float p = n_sigmoid == 2 ? 1.0f / (1.0f + __expf(-q)) : q;
+    const float eps = 1e-7f;
+    const float pc = fminf(fmaxf(p, eps), 1.f - eps);
+    const float yb = y[b];
+    l -= yb * __logf(pc) + (1.f - yb) * __logf(1.f - pc);
+    ok += ((p > 0.5f) == (yb > 0.5f)) ? 1.f : 0.f;
+    float g = (p > eps && p < 1.f - eps) ? (pc - yb) / (float)B : 0.f;           // d / d(logit of the last sigmoid)
+    if (n_sigmoid == 2) g *= q * (1.f - q);
+    dz[b] = g;
+  }
+  s_loss[threadIdx.x] = l; s_ok[threadIdx.x] = ok;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o >= 1; o >>= 1) {
+    if (threadIdx.x < o) { s_loss[threadIdx.x] += s_loss[threadIdx.x + o]; s_ok[threadIdx.x] += s_ok[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { loss_out[0] = s_loss[0] / (float)B; loss_out[1] = s_ok[0]; }
+}
+// max pooling backward: only the arg-max pair (i, j) of (b, c) receives gx:  dE[b, i, c] = gx e_jc,  dE[b, j, c] = gx e_ic
+template <int IDKIND>
+__global__ void tr_afm_max_bwd_kernel(const float* __restrict__ arena, const int64_t* __restrict__ row_off, int F, int k,
+                                      const void* __restrict__ ids, int64_t ids_ld, int64_t B, const float* __restrict__ gx,
+                                      const int32_t* __restrict__ amax, float* __restrict__ dE) {
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < B * k; i0 += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i0 / k;
+    const int c = (int)(i0 - b * k);
+    for (int f = 0; f < F; ++f) dE[(b * F + f) * k + c] = 0.f;
+    const int i = amax[i0] >> 16, j = amax[i0] & 0xFFFF;
+    auto row = [&](int f) {
+      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      return (id >= 0 && id < row_off[f + 1] - row_off[f]) ? arena[(row_off[f] + id) * k + c] : 0.f;
+    };
+    const float g = gx[i0];
+    dE[(b * F + i) * k + c] = g * row(j);
+    dE[(b * F + j) * k + c] = g * row(i);
+  }
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -1277,5 +1360,51 @@ extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, i
     tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dE, fk, lr, nullptr);
   }
   CTRHOT_LAUNCH_OK("ctrhot_nfm_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- AFM training step (SURVEY 8(f) ranks 1 + 3)
+extern "C" int64_t ctrhot_afm_train_workspace_bytes(int64_t B, int F, int k) {
+  if (B < 0 || F < 2 || k < 1) return CTRHOT_ESHAPE;
+  auto r4 = [](int64_t c) { return (c + 3) / 4 * 4; };
+  return (4 * r4(B * k) + 2 * r4(B) + r4(B * (int64_t)F * k)) * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_afm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
+                                         int64_t ids_ld, const float* y, int64_t B, int mode, int n_sigmoid, float* out_k,
+                                         float* out_b, float lr, float* loss_out, void* workspace, int64_t workspace_bytes,
+                                         int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_afm_train_step_f32");
+  if (!arena || !row_off || !ids || !y || !out_k || !out_b || !loss_out || !workspace || B <= 0 || ids_ld < F || !(lr >= 0.f))
+    return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (F < 2 || F > 0xFFFF || k < 1 || mode < 0 || mode > 2 || (n_sigmoid != 1 && n_sigmoid != 2)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < ctrhot_afm_train_workspace_bytes(B, F, k) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto r4 = [](int64_t c) { return (c + 3) / 4 * 4; };
+  float* ws = static_cast<float*>(workspace);
+  float* x = ws; float* S = x + r4(B * k); float* gx = S + r4(B * k);
+  int32_t* amax = reinterpret_cast<int32_t*>(gx + r4(B * k));
+  float* z = reinterpret_cast<float*>(amax) + r4(B * k); float* dz = z + r4(B); float* dE = dz + r4(B);
+  const int M = (int)B, fk = F * k, P = F * (F - 1) / 2;
+  const bool i32 = ids_kind == CTRHOT_IDS_I32;
+  if (i32) tr_afm_fwd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * k, 128), 128, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, mode, x, S, amax, err_flag);
+  else tr_afm_fwd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * k, 128), 128, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, mode, x, S, amax, err_flag);
+  tr_gemm(st, x, k, 1, out_k, 1, 1, z, 1, M, 1, k, 1.f, 0.f);
+  tr_afm_loss_kernel<<<1, 256, 0, st>>>(z, out_b, y, B, n_sigmoid, dz, loss_out);
+  // gx = dz w^T (old w; the mean's 1 / P folded in), then w, b
+  tr_gemm(st, dz, 1, 1, out_k, 0, 1, gx, k, M, k, 1, mode == 0 ? 1.f / (float)P : 1.f, 0.f);
+  tr_gemm(st, x, 1, k, dz, 1, 1, out_k, 1, k, 1, M, -lr, 1.f);
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, out_b, -lr, 1.f);
+  if (mode == 2) {
+    if (i32) tr_afm_max_bwd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * k, 128), 128, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, gx, amax, dE);
+    else tr_afm_max_bwd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * k, 128), 128, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, gx, amax, dE);
+  } else {                                                       // sum of pairs: d / d e_fc = S_c - e_fc, as NFM's Bi-Interaction
+    if (i32) tr_nfm_bi_bwd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, gx, S, dE);
+    else tr_nfm_bi_bwd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, gx, S, dE);
+  }
+  if (i32) tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dE, fk, lr, nullptr);
+  else tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dE, fk, lr, nullptr);
+  CTRHOT_LAUNCH_OK("ctrhot_afm_train_step_f32");
   return CTRHOT_OK;
 }

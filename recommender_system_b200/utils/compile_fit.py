@@ -11,7 +11,7 @@ rows that were looked up, the FM weights and the tower.  SURVEY 8(f) rank 3; bui
 ``ctrhot_dcn_train_step_f32``) and for PNN (the loop of DL/model/pnn.py:74-85, which compile_fit reproduces for it: BCE on
 the raw output, no regularisers; ``ctrhot_pnn_train_step_f32``) and for WideDeep (DL/model/wideDeep.py:37-49; ``ctrhot_widedeep_train_step_f32``) and DeepCrossing
 (DL/model/deepCrossing.py:35-47; ``ctrhot_deepcrossing_train_step_f32``) and NFM (DL/model/nfm.py:37-50, BatchNormalization in training
-mode; ``ctrhot_nfm_train_step_f32``) -- other models raise NotImplementedError.
+mode; ``ctrhot_nfm_train_step_f32``) and AFM (``ctrhot_afm_train_step_f32``) -- other models raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -28,7 +28,7 @@ class _DeepFMTrainer:
     def __init__(self, model, dropout=None):
         from ..model.criteo import DeepFM
         if not isinstance(model, DeepFM):
-            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, NFM, PNN and FM only (SURVEY 8(f) rank 3)")
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, NFM, AFM, PNN and FM only (SURVEY 8(f) rank 3)")
         self.m = model
         if not model.dnn.built:
             model.build(None)
@@ -415,13 +415,42 @@ class _NFMTrainer:
         return self.loss
 
 
+class _AFMTrainer:
+    """AFM / AFMLayer (DL/model/afm.py, DL/layer/interaction.py:322-351): ctrhot_afm_train_step_f32 per batch.  In 'att' mode
+    AttentionLayer's two Dense layers receive zero gradient (softmax over a size-1 axis) and stay as they are."""
+
+    def __init__(self, model, dropout=None):
+        self.m = model
+        if not hasattr(model, "out_kernel"):
+            model.build(None)
+        self.ws = None
+        self.loss = torch.zeros(2, dtype=torch.float32, device=model.device)
+        self.flag = model.err_flag()
+        self.step = 0
+
+    def train_on_batch(self, dense, ids, y, lr, seed=0):
+        m, E = self.m, self.m.embed_layer
+        ids, kind, ids_ld = ids_arg(ids)
+        B = ids.shape[0]
+        need = _lib.query("ctrhot_afm_train_workspace_bytes", B, E.F, E.k)
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=m.device)
+        _lib.call("ctrhot_afm_train_step_f32", ptr(E.arena), ptr(E.row_off), E.F, E.k, ptr(ids), kind, ids_ld, ptr(y), B,
+                  {"avg": 0, "att": 1, "max": 2}[m.mode], int(m.n_sigmoid), ptr(m.out_kernel), ptr(m.out_bias), float(lr),
+                  ptr(self.loss), ptr(self.ws), self.ws.numel() * 4, ptr(self.flag), stream_ptr())
+        self.step += 1
+        return self.loss
+
+
 def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True, use_graph=True):
     """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
     (loss, accuracy) pairs are left in ``model.history``.  ``use_graph``: the full batches of an epoch replay one captured CUDA
     graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
-    from ..model.criteo import DCN, FM, NFM, PNN, WideDeep
+    from ..model.criteo import AFMLayer, DCN, FM, NFM, PNN, WideDeep
     from ..model.deepCrossing import DeepCrossing
+    if isinstance(model, AFMLayer):                               # AFM is a subclass
+        return _fit_rows(_AFMTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)
     if isinstance(model, NFM):
         model.embed_layer = model.emb_layers                      # (_fit_rows reads the field count from .embed_layer)
         return _fit_rows(_NFMTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)

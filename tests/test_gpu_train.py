@@ -573,3 +573,63 @@ def test_nfm_compile_fit_learns_and_serves(lib):
     want = O.nfm_model(X[:300].astype(np.float64), t, bn, hid, out, fin)
     got = npy(m(X[:300]))
     assert np.max(np.abs(got - want)) <= 5e-5, np.max(np.abs(got - want))
+
+
+# ------------------------------------------------------------------ AFM (DL/model/afm.py under compile_fit)
+def make_afm(vocab, mode, seed=1):
+    from recommender_system_b200.model.criteo import AFM
+    set_seed(seed)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": int(v), "embed_dim": 8} for i, v in enumerate(vocab)]]
+    m = AFM(fc, mode)
+    m.build(None)
+    rng = np.random.default_rng(seed)
+    upd = {}
+    for n, w in m.named_weights().items():
+        if n.endswith("embeddings"):
+            upd[n] = rng.normal(0, 0.4, tuple(w.shape))
+        elif n.startswith("output_layer"):
+            upd[n] = rng.normal(0, 0.5, tuple(w.shape))
+    m.set_weights({n: np.asarray(v, np.float32) for n, v in upd.items()})
+    return m
+
+
+@pytest.mark.parametrize("B,F,mode", [(32, 26, "att"), (1, 3, "avg"), (257, 26, "max"), (600, 13, "avg")])
+def test_afm_one_step_against_the_oracle(lib, B, F, mode):
+    from recommender_system_b200.utils.compile_fit import _AFMTrainer
+    vocab = ([50, 7, 1000, 3] + [20] * 22)[:F]
+    m = make_afm(vocab, mode)
+    _, ids, y = batch(vocab, B, seed=B + 6)
+    tabs = [npy(t) for t in m.embed_layer.emb_layers]
+    out = (npy(m.out_kernel), npy(m.out_bias))
+    att = [npy(w).copy() for n, w in m.named_weights().items() if n.startswith("attention")]
+    lr = 0.5                                                      # the double sigmoid makes gradients small
+    tr = _AFMTrainer(m)
+    dev = m.device
+    res = tr.train_on_batch(None, torch.from_numpy(ids).to(dev), torch.from_numpy(y).to(dev), lr)
+    torch.cuda.synchronize()
+    want, bce, correct = O.afm_train_step(ids, tabs, mode, out, y.astype(np.float64), lr, 2)
+    assert abs(float(res[0]) - bce) <= 2e-6 * max(1.0, bce) and int(res[1]) == correct
+    got = [npy(t) for t in m.embed_layer.emb_layers]
+    for f in range(F):
+        close(got[f], want[0][f], tabs[f], "table %d" % f, floor=1e-6)
+    close(npy(m.out_kernel), want[1][0], out[0], "out kernel"); close(npy(m.out_bias), want[1][1], out[1], "out bias")
+    for a, (n, w) in zip(att, [(n, w) for n, w in m.named_weights().items() if n.startswith("attention")]):
+        np.testing.assert_array_equal(npy(w), a)                  # zero gradient: AttentionLayer's weights do not move
+
+
+def test_afm_compile_fit_lowers_the_loss_and_serves(lib):
+    vocab = [30, 7, 120, 50] + [9] * 22
+    rng = np.random.default_rng(3)
+    N = 1000 + 3
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.concatenate([rng.random((N, 13)), ids], axis=1).astype(np.float32)
+    y = (ids[:, 0] < 15).astype(np.float32)
+    m = make_afm(vocab, "att", seed=5)
+    compile_fit(m, X, y, batch_size=32, epochs=5, sgd=0.5, verbose=False)
+    assert m.history[-1][0] < m.history[0][0], m.history
+    tabs = [npy(t) for t in m.embed_layer.emb_layers]
+    want = O.afm_model(X[:300].astype(np.float64), tabs, "att", att_w=(np.zeros((8, 325)), np.zeros(325)),
+                       att_h=(np.zeros((325, 1)), np.zeros(1)), out=(npy(m.out_kernel), npy(m.out_bias)))
+    got = npy(m(X[:300]))
+    assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))

@@ -434,3 +434,35 @@ def test_nfm_train_step_gradients():
     x = O.nfm_train_forward(dense, ids, tables, bn, hidden, out, final, masks)[1][2]
     np.testing.assert_allclose(new[1][0], 0.99 * bn[0] + 0.01 * x.mean(0), rtol=0, atol=1e-15)
     np.testing.assert_allclose(new[1][1], 0.99 * bn[1] + 0.01 * x.var(0), rtol=0, atol=1e-15)
+
+
+@pytest.mark.parametrize("mode,ns", [("att", 2), ("avg", 2), ("max", 2), ("att", 1)])
+def test_afm_train_step_gradients(mode, ns):
+    rng = np.random.default_rng(23)
+    B, F, K = 9, 5, 4
+    vocab = [6, 4, 7, 5, 3]
+    tables = [rng.normal(0, 0.7, (v, K)) for v in vocab]
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1)
+    ids[1] = ids[0]
+    out = (rng.normal(0, 0.7, (K, 1)), rng.normal(0, 0.1, 1))
+    y = rng.integers(0, 2, B).astype(float)
+    lr = 0.05
+    new, bce, _ = O.afm_train_step(ids, tables, mode, out, y, lr, ns)
+    X = np.concatenate([np.zeros((B, 13)), ids.astype(float)], axis=1)
+
+    def loss(tables_, out_):
+        p = O.afm_layer(X, tables_, mode, att_w=(np.zeros((K, 10)), np.zeros(10)), att_h=(np.zeros((10, 1)), np.zeros(1)), out=out_)[:, 0]
+        p = np.clip(O.sigmoid(p) if ns == 2 else p, 1e-7, 1 - 1e-7)
+        return np.mean(-(y * np.log(p) + (1 - y) * np.log(1 - p)))
+    assert abs(loss(tables, out) - bce) < 1e-12
+    eps = 1e-6
+
+    def fd(obj, idx, rebuild):
+        a, b = obj.copy(), obj.copy()
+        a[idx] += eps; b[idx] -= eps
+        return (loss(*rebuild(a)) - loss(*rebuild(b))) / (2 * eps)
+    for f, r, c in [(0, int(ids[0, 0]), 1), (3, int(ids[4, 3]), 2), (4, int(ids[2, 4]), 0)]:
+        gt = fd(tables[f], (r, c), lambda a: (tables[:f] + [a] + tables[f + 1:], out))
+        assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, c]) < 1e-7
+    go = fd(out[0], (2, 0), lambda a: (tables, (a, out[1])))
+    assert abs(go - ((out[0] - new[1][0]) / lr)[2, 0]) < 1e-7
