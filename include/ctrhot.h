@@ -473,6 +473,17 @@ int ctrhot_afm_train_step_f32(float* arena, const int64_t* row_off, int F, int k
                               float* out_b, float lr, float* loss_out, void* workspace, int64_t workspace_bytes,
                               int* err_flag, void* stream);
 
+/* ---- 8(f) rank 3, FFM under compile_fit (DL/model/ffm.py:14-23; FFMLayer DL/layer/interaction.py:117-163) ------------------------
+ * p = sigmoid(w0 + x.w + sum_{f<g} <ff_f, ff_g>), ff[f, :] = sum_i x_i v[i, f, :] over the one-hot expansion x of [dense | ids]
+ * (never materialised: D counts and one row per sparse field; ids outside their column block give tf.one_hot's zero row).
+ * Mean clipped BCE + l2(reg_w)(w) + l2(reg_v)(v); one step of SGD(lr), in place: w0 [1], w [n_features], v [n_features,
+ * field_num, k] (all of w and v decay by the regularisers; the batch's rows receive x_i (S - ff_f) through atomics). */
+int64_t ctrhot_ffm_train_workspace_bytes(int64_t B, int field_num, int k);
+int ctrhot_ffm_train_step_f32(const float* dense, int64_t dense_ld, int D, const void* ids, int ids_kind, int64_t ids_ld,
+                              int F, const int64_t* col_off, const float* y, int64_t B, float* w0, float* w, float* v,
+                              int64_t n_features, int field_num, int k, float reg_w, float reg_v, float lr,
+                              float* loss_out, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

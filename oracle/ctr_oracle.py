@@ -1112,3 +1112,22 @@ def afm_train_step(ids, tables, mode, out, y, lr, n_sigmoid=2):
     for f in range(F):
         np.add.at(new_tables[f], ids[:, f], -lr * de[:, f, :])
     return (new_tables, new_out), bce, correct
+
+
+def ffm_train_step(inputs, vocab_sizes, w0, w, v, y, lr, reg_w, reg_v, n_dense=13):
+    """One step of keras SGD(lr) on FFM (DL/model/ffm.py:14-23: p = sigmoid(FFMLayer(x))): mean clipped BCE + l2(w_reg)(w) +
+    l2(v_reg)(v) (FFMLayer.build, DL/layer/interaction.py:131-138).  With ff = tensordot(x, v) [B, field, k] and S = sum over
+    fields, inter = 0.5 (|S|^2 - |ff|^2), so d inter / d v[i, f, :] = x_i (S - ff[f]).  PARITY UNPINNED against the reference like
+    deepfm_train_step; gradients pinned by finite differences of `ffm_layer`'s loss.
+    -> ((w0, w, v) updated, mean BCE before the update, number of correct predictions)."""
+    x = onehot_expand(inputs, vocab_sizes, n_dense, dtype=v.dtype)
+    B = x.shape[0]
+    p = sigmoid(ffm_layer(inputs, vocab_sizes, w0, w, v, n_dense)[:, 0])
+    pc = np.clip(p, _BCE_LO, _BCE_HI)                                                  # keras clips in fp32
+    bce = float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+    dz = np.where((p > _BCE_LO) & (p < _BCE_HI), pc - y, 0.0) / B
+    ff = np.tensordot(x, v, axes=1)                                                    # [B, field, k]
+    G = ff.sum(axis=1, keepdims=True) - ff                                             # d inter / d ff
+    g_v = np.tensordot(x * dz[:, None], G, axes=([0], [0])) + 2 * reg_v * v            # [n_feat, field, k]
+    g_w = x.T @ dz[:, None] + 2 * reg_w * w
+    return (w0 - lr * np.sum(dz), w - lr * g_w, v - lr * g_v), bce, int(np.sum((p > 0.5) == (y > 0.5)))

@@ -629,6 +629,80 @@ __global__ void tr_afm_max_bwd_kernel(const float* __restrict__ arena, const int
   }
 }
 
+// ---------------------------------------------------------------- FFM (DL/model/ffm.py:14-23, FFMLayer interaction.py:141-163)
+// One warp per sample.  ff[b, e] (e = field * k + c) = sum over the sample's non-zero features i of x_i v[i, e]; S[c] = sum over
+// fields of ff; z = w0 + sum_i x_i w_i + 0.5 (|S|^2 - |ff|^2).  The one-hot matrix is never built: the D counts and one row of v
+// per sparse field (ids outside their column block: tf.one_hot's zero row).
+#define TR_WARP_IDS()                                                               \
+  const int lane = threadIdx.x & 31;                                                \
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); \
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+template <int IDKIND>
+__global__ void __launch_bounds__(128)
+tr_ffm_fwd_kernel(const float* __restrict__ dense, int64_t dense_ld, int D, const void* __restrict__ ids, int64_t ids_ld, int F,
+                  const int64_t* __restrict__ col_off, int64_t B, const float* __restrict__ w0, const float* __restrict__ w,
+                  const float* __restrict__ v, int len, int k, float* __restrict__ ff, float* __restrict__ S,
+                  float* __restrict__ z) {
+  TR_WARP_IDS();
+  for (int64_t b = warp; b < B; b += nwarps) {
+    float* fb = ff + b * len;
+    float lin = 0.f, sq = 0.f;
+    for (int e = lane; e < len; e += 32) {
+      float a = 0.f;
+      for (int j = 0; j < D; ++j) a = fmaf(dense[b * dense_ld + j], v[(size_t)j * len + e], a);
+      for (int f = 0; f < F; ++f) {
+        const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+        if (id >= 0 && id < col_off[f + 1] - col_off[f]) a += v[(size_t)(col_off[f] + id) * len + e];
+      }
+      fb[e] = a;
+      sq = fmaf(a, a, sq);
+    }
+    for (int j = lane; j < D; j += 32) lin = fmaf(dense[b * dense_ld + j], w[j], lin);
+    for (int f = lane; f < F; f += 32) {
+      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      if (id >= 0 && id < col_off[f + 1] - col_off[f]) lin += w[col_off[f] + id];
+    }
+    __syncwarp();
+    float tsq = 0.f;
+    for (int c = lane; c < k; c += 32) {
+      float t = 0.f;
+      for (int e = c; e < len; e += k) t += fb[e];
+      S[b * k + c] = t;
+      tsq = fmaf(t, t, tsq);
+    }
+    const float r = warp_sum(lin + 0.5f * (tsq - sq));
+    if (lane == 0) z[b] = r + w0[0];
+  }
+}
+// SGD on the rows the batch touched, after the l2 decay of all of w and v:  d z / d v[i, e] = x_i (S[e % k] - ff[e]),
+// d z / d w_i = x_i.  One warp per (sample, non-zero feature); rows shared by several samples add up through atomics.
+template <int IDKIND>
+__global__ void __launch_bounds__(128)
+tr_ffm_sgd_kernel(const float* __restrict__ dense, int64_t dense_ld, int D, const void* __restrict__ ids, int64_t ids_ld, int F,
+                  const int64_t* __restrict__ col_off, int64_t B, const float* __restrict__ dz, float lr, int len, int k,
+                  const float* __restrict__ ff, const float* __restrict__ S, float* __restrict__ w, float* __restrict__ v) {
+  TR_WARP_IDS();
+  const int nf = D + F;
+  for (int64_t i = warp; i < B * nf; i += nwarps) {
+    const int64_t b = i / nf;
+    const int j = (int)(i - b * nf);
+    int64_t col;
+    float xs;
+    if (j < D) { col = j; xs = dense[b * dense_ld + j]; }
+    else {
+      const int f = j - D;
+      const int64_t id = IdLoad<IDKIND>::at(ids, b * ids_ld + f);
+      if (id < 0 || id >= col_off[f + 1] - col_off[f]) continue;
+      col = col_off[f] + id; xs = 1.f;
+    }
+    const float g = -lr * dz[b] * xs;
+    if (g == 0.f) continue;
+    if (lane == 0) atomicAdd(w + col, g);
+    float* vr = v + (size_t)col * len;
+    for (int e = lane; e < len; e += 32) atomicAdd(vr + e, g * (S[b * k + e % k] - ff[b * len + e]));
+  }
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -1406,5 +1480,43 @@ extern "C" int ctrhot_afm_train_step_f32(float* arena, const int64_t* row_off, i
   if (i32) tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dE, fk, lr, nullptr);
   else tr_embed_sgd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * fk, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dE, fk, lr, nullptr);
   CTRHOT_LAUNCH_OK("ctrhot_afm_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- FFM training step (DL/model/ffm.py under compile_fit)
+extern "C" int64_t ctrhot_ffm_train_workspace_bytes(int64_t B, int field_num, int k) {
+  if (B < 0 || field_num < 1 || k < 1) return CTRHOT_ESHAPE;
+  auto r4 = [](int64_t c) { return (c + 3) / 4 * 4; };
+  return (r4(B * (int64_t)field_num * k) + r4(B * k) + 2 * r4(B)) * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_ffm_train_step_f32(const float* dense, int64_t dense_ld, int D, const void* ids, int ids_kind,
+                                         int64_t ids_ld, int F, const int64_t* col_off, const float* y, int64_t B, float* w0,
+                                         float* w, float* v, int64_t n_features, int field_num, int k, float reg_w, float reg_v,
+                                         float lr, float* loss_out, void* workspace, int64_t workspace_bytes, void* stream) {
+  CTRHOT_RANGE("ctrhot_ffm_train_step_f32");
+  if (!y || !w0 || !w || !v || !loss_out || !workspace || B <= 0 || D < 0 || F < 0 || n_features < D || !(lr >= 0.f))
+    return CTRHOT_EARG;
+  if ((D > 0 && (!dense || dense_ld < D)) || (F > 0 && (!ids || !col_off || ids_ld < F))) return CTRHOT_EARG;
+  if (ids_kind != CTRHOT_IDS_I32 && ids_kind != CTRHOT_IDS_F32) return CTRHOT_EARG;
+  if (field_num < 1 || k < 1 || (int64_t)field_num * k > (1 << 20)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < ctrhot_ffm_train_workspace_bytes(B, field_num, k) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto r4 = [](int64_t c) { return (c + 3) / 4 * 4; };
+  const int len = field_num * k;
+  float* ff = static_cast<float*>(workspace); float* S = ff + r4(B * len); float* z = S + r4(B * k); float* dz = z + r4(B);
+  const bool i32 = ids_kind == CTRHOT_IDS_I32;
+  const int g1 = tr_grid(B * 32, 128);
+  if (i32) tr_ffm_fwd_kernel<CTRHOT_IDS_I32><<<g1, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, w0, w, v, len, k, ff, S, z);
+  else tr_ffm_fwd_kernel<CTRHOT_IDS_F32><<<g1, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, w0, w, v, len, k, ff, S, z);
+  tr_loss_kernel<<<1, 256, 0, st>>>(z, nullptr, nullptr, y, B, dz, loss_out, nullptr, 1.0f);
+  // l2(reg)(w) adds 2 reg w to EVERY entry's gradient (FFMLayer.build, interaction.py:131-138): decay first, then the batch's rows
+  if (reg_w != 0.f) tr_scale_kernel<<<tr_grid(n_features, 256), 256, 0, st>>>(w, n_features, 1.f - 2.f * lr * reg_w);
+  if (reg_v != 0.f) tr_scale_kernel<<<tr_grid(n_features * len, 256), 256, 0, st>>>(v, n_features * len, 1.f - 2.f * lr * reg_v);
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, w0, -lr, 1.f);
+  const int g2 = tr_grid(B * (D + F) * 32, 128);
+  if (i32) tr_ffm_sgd_kernel<CTRHOT_IDS_I32><<<g2, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, dz, lr, len, k, ff, S, w, v);
+  else tr_ffm_sgd_kernel<CTRHOT_IDS_F32><<<g2, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, dz, lr, len, k, ff, S, w, v);
+  CTRHOT_LAUNCH_OK("ctrhot_ffm_train_step_f32");
   return CTRHOT_OK;
 }

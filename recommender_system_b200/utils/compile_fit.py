@@ -28,7 +28,7 @@ class _DeepFMTrainer:
     def __init__(self, model, dropout=None):
         from ..model.criteo import DeepFM
         if not isinstance(model, DeepFM):
-            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, NFM, AFM, PNN and FM only (SURVEY 8(f) rank 3)")
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, NFM, AFM, PNN, FM and FFM only (SURVEY 8(f) rank 3)")
         self.m = model
         if not model.dnn.built:
             model.build(None)
@@ -125,8 +125,33 @@ class _FMTrainer:
         return self.loss
 
 
-def _fit_fm(model, X, y, batch_size, epochs, sgd, verbose):
-    tr = _FMTrainer(model)
+class _FFMTrainer:
+    """FFM (DL/model/ffm.py:14-23) on the reference's [B, 13 + 26] matrix (ids stored as floats): ctrhot_ffm_train_step_f32 per
+    batch.  The one-hot expansion FFMLayer.call builds (interaction.py:145-151) is implied by the ids."""
+
+    def __init__(self, model):
+        self.m, self.ws, self.step = model, None, 0
+        self.loss = torch.zeros(2, dtype=torch.float32, device=model.device)
+
+    def train_on_batch(self, x, y, lr):
+        L = self.m.ffm
+        if not L.built:
+            self.m.build((None, x.shape[1]))
+        D, F = len(L.dense_feature_columns), len(L.sparse_feature_columns)
+        B = x.shape[0]
+        need = _lib.query("ctrhot_ffm_train_workspace_bytes", B, L.field_num, L.k)
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=self.m.device)
+        ids = x[:, D:]
+        _lib.call("ctrhot_ffm_train_step_f32", ptr(x), x.stride(0), D, ptr(ids), _lib.IDS_F32, x.stride(0), F, ptr(L.col_off),
+                  ptr(y), B, ptr(L.w0), ptr(L.w), ptr(L.v), L.feature_num, L.field_num, L.k, float(L.w_reg), float(L.v_reg),
+                  float(lr), ptr(self.loss), ptr(self.ws), self.ws.numel() * 4, stream_ptr())
+        self.step += 1
+        return self.loss
+
+
+def _fit_fm(model, X, y, batch_size, epochs, sgd, verbose, trainer=None):
+    tr = trainer or _FMTrainer(model)
     dev = model.device
     Xd = as_device_f32(X, dev).contiguous()
     yd = as_device_f32(np.asarray(y, dtype=np.float32).reshape(-1) if not isinstance(y, torch.Tensor) else y.reshape(-1), dev)
@@ -447,8 +472,10 @@ def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, s
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
     (loss, accuracy) pairs are left in ``model.history``.  ``use_graph``: the full batches of an epoch replay one captured CUDA
     graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
-    from ..model.criteo import AFMLayer, DCN, FM, NFM, PNN, WideDeep
+    from ..model.criteo import AFMLayer, DCN, FFM, FM, NFM, PNN, WideDeep
     from ..model.deepCrossing import DeepCrossing
+    if isinstance(model, FFM):
+        return _fit_fm(model, X, y, batch_size, epochs, sgd, verbose, trainer=_FFMTrainer(model))
     if isinstance(model, AFMLayer):                               # AFM is a subclass
         return _fit_rows(_AFMTrainer(model, dropout), model, X, y, batch_size, epochs, sgd, seed, verbose)
     if isinstance(model, NFM):

@@ -633,3 +633,59 @@ def test_afm_compile_fit_lowers_the_loss_and_serves(lib):
                        att_h=(np.zeros((325, 1)), np.zeros(1)), out=(npy(m.out_kernel), npy(m.out_bias)))
     got = npy(m(X[:300]))
     assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))
+
+
+# ------------------------------------------------------------------ FFM (DL/model/ffm.py under compile_fit)
+@pytest.mark.parametrize("B,vocab,k", [(32, [50, 7, 1000, 3] + [20] * 22, 8), (1, [11] * 26, 4), (257, [30, 7, 120, 50], 8),
+                                       (600, [5000] * 26, 8)])
+def test_ffm_one_step_against_the_oracle(lib, B, vocab, k):
+    """One SGD step of FFM against oracle.ffm_train_step: every entry of w0, w and v (rows the batch did not touch move by the
+    l2 decay alone), the loss and the accuracy.  Ids arrive as floats inside the [B, 13 + F] matrix, like the reference's."""
+    from recommender_system_b200.model.criteo import FFM
+    from recommender_system_b200.utils.compile_fit import _FFMTrainer
+    set_seed(4)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": int(v)} for i, v in enumerate(vocab)]]
+    m = FFM(fc, k, 1e-2, 2e-2)
+    m.build((None, 13 + len(vocab)))
+    L = m.ffm
+    rng = np.random.default_rng(B)
+    with torch.no_grad():
+        L.w0.copy_(torch.tensor([0.05]))
+        L.v.copy_(torch.from_numpy(rng.normal(0, 0.02, tuple(L.v.shape)).astype(np.float32)))
+    dense, ids, y = batch(vocab, B, seed=B + 7)
+    X = np.concatenate([dense, ids.astype(np.float32)], axis=1)
+    before = (npy(L.w0), npy(L.w), npy(L.v))
+    tr = _FFMTrainer(m)
+    dev = m.device
+    lr = 0.1
+    out = tr.train_on_batch(torch.from_numpy(X).to(dev), torch.from_numpy(y).to(dev), lr)
+    torch.cuda.synchronize()
+    want, bce, correct = O.ffm_train_step(X.astype(np.float64), vocab, *before, y.astype(np.float64), lr, 1e-2, 2e-2)
+    # (1e-5: z = 0.5 (|S|^2 - |ff|^2) over 39 x 8 terms cancels in fp32, as it does in the reference's own fp32 graph)
+    assert abs(float(out[0]) - bce) <= 1e-5 * max(1.0, bce) and int(out[1]) == correct
+    close(npy(L.w0), want[0], before[0], "w0"); close(npy(L.w), want[1], before[1], "w")
+    close(npy(L.v), want[2], before[2], "v", floor=1e-6)
+    # the serving kernel reads the same updated weights
+    got = npy(m(X))
+    ref = O.sigmoid(O.ffm_layer(X.astype(np.float64), vocab, npy(L.w0), npy(L.w), npy(L.v)))
+    assert np.max(np.abs(got - ref)) <= 2e-5
+
+
+def test_ffm_compile_fit_lowers_the_loss(lib):
+    from recommender_system_b200.model.criteo import FFM
+    vocab = [30, 7, 120, 50] + [9] * 22
+    rng = np.random.default_rng(3)
+    N = 1000 + 3
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.concatenate([rng.random((N, 13)), ids], axis=1).astype(np.float32)
+    y = (ids[:, 0] < 15).astype(np.float32)
+    set_seed(6)
+    fc = [[{"feat": "I%d" % i} for i in range(13)],
+          [{"feat": "C%d" % i, "feat_onehot_dim": int(v)} for i, v in enumerate(vocab)]]
+    m = FFM(fc, 8, 1e-4, 1e-4)
+    m.build((None, X.shape[1]))
+    with torch.no_grad():                    # keras' random_normal(0.05) start saturates the sigmoid (39 fields x 8): the clipped BCE
+        m.ffm.v.mul_(0.2)                    # then has zero gradient on the wrong-side samples, in the reference as well
+    compile_fit(m, X, y, batch_size=32, epochs=6, sgd=0.01, verbose=False)      # (sgd = 0.05 diverges, in the oracle as well)
+    assert m.history[-1][0] < 0.5 * m.history[0][0] and m.history[-1][1] > 0.95, m.history

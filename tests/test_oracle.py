@@ -466,3 +466,38 @@ def test_afm_train_step_gradients(mode, ns):
         assert abs(gt - ((tables[f] - new[0][f]) / lr)[r, c]) < 1e-7
     go = fd(out[0], (2, 0), lambda a: (tables, (a, out[1])))
     assert abs(go - ((out[0] - new[1][0]) / lr)[2, 0]) < 1e-7
+
+
+def test_ffm_train_step_gradients():
+    rng = np.random.default_rng(29)
+    B, D, K = 7, 3, 4
+    vocab = [5, 3, 6, 4]
+    field = D + len(vocab)
+    n_feat = D + sum(vocab)
+    ids = np.stack([rng.integers(0, v, B) for v in vocab], axis=1)
+    ids[1] = ids[0]
+    X = np.concatenate([rng.random((B, D)), ids.astype(float)], axis=1)
+    w0, w, v = rng.normal(0, 0.1, 1), rng.normal(0, 0.3, (n_feat, 1)), rng.normal(0, 0.3, (n_feat, field, K))
+    y = rng.integers(0, 2, B).astype(float)
+    lr, rw, rv = 0.05, 1e-2, 3e-2
+    new, bce, _ = O.ffm_train_step(X, vocab, w0, w, v, y, lr, rw, rv, n_dense=D)
+
+    def loss(w0_, w_, v_):
+        p = np.clip(O.sigmoid(O.ffm_layer(X, vocab, w0_, w_, v_, D)[:, 0]), O._BCE_LO, O._BCE_HI)
+        return np.mean(-(y * np.log(p) + (1 - y) * np.log(1 - p))) + rw * np.sum(w_ ** 2) + rv * np.sum(v_ ** 2)
+    assert abs(loss(w0, w, v) - rw * np.sum(w ** 2) - rv * np.sum(v ** 2) - bce) < 1e-12
+    eps = 1e-6
+
+    def fd(obj, idx, rebuild):
+        a, b = obj.copy(), obj.copy()
+        a[idx] += eps; b[idx] -= eps
+        return (loss(*rebuild(a)) - loss(*rebuild(b))) / (2 * eps)
+    hit = D + int(ids[0, 0])                                                           # a row two samples share
+    for idx in [(0, 2, 1), (hit, 0, 3), (hit, 5, 0), (D + vocab[0] + int(ids[3, 1]), 6, 2), (n_feat - 1, 1, 1)]:
+        g = fd(v, idx, lambda a: (w0, w, a))
+        assert abs(g - ((v - new[2]) / lr)[idx]) < 1e-7
+    for idx in [(1, 0), (hit, 0), (n_feat - 1, 0)]:
+        g = fd(w, idx, lambda a: (w0, a, v))
+        assert abs(g - ((w - new[1]) / lr)[idx]) < 1e-7
+    g = fd(w0, (0,), lambda a: (a, w, v))
+    assert abs(g - ((w0 - new[0]) / lr)[0]) < 1e-7
