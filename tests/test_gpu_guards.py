@@ -27,7 +27,7 @@ def guarded(t, poison):
     """-> (view equal to t, whole buffer, check()) with `poison` on both sides of the view (first dimension)."""
     t = t.contiguous()
     row = t[0].numel() if t.dim() > 1 else 1
-    g = (G + row - 1) // row
+    g = ((G + row - 1) // row + 15) // 16 * 16   # (a multiple of 16 rows: the view keeps the base alignment the C-ABI asks for)
     big = torch.empty((t.shape[0] + 2 * g,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
     big.fill_(poison)
     big[g:g + t.shape[0]].copy_(t)
