@@ -484,6 +484,27 @@ int ctrhot_ffm_train_step_f32(const float* dense, int64_t dense_ld, int D, const
                               int64_t n_features, int field_num, int k, float reg_w, float reg_v, float lr,
                               float* loss_out, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ---- 8(f) rank 3, DIN under compile_fit (DL/model/din.py:56-95; Attention DL/layer/interaction.py:369-406) ----------------------
+ * One behaviour feature: seq_table [seq_rows, K] serves the history hist [B, T] (int32, 0 = padding) and the candidate cand [B].
+ * Forward in TRAINING mode: A = [q, k, q - k, q * k] -> att_layers (Dense + PReLU, act_param = alpha [T, h], alpha_rows = T) ->
+ * att_out -> scores, -2^32 + 1 where hist == 0, softmax over T, att = sum_t pw_t k_t; emb = [att | q | other tables' rows |
+ * dense] (n columns) -> BatchNormalization on the batch's own mean / biased variance (moving statistics move by `momentum`) ->
+ * tower_layers (Dense + PReLU, alpha [h], alpha_rows = 1) -> Dense(1) -> sigmoid; mean clipped BCE; dnn_dropout = 0 (din.py:17).
+ * One step of SGD(lr) on EVERY variable, in place: seq_table (history rows and candidate row, atomics), other_tables[i]
+ * [other_rows[i], other_dims[i]] (HOST arrays of n_other entries; other_ids [B, n_other] int32 on the device), the layers'
+ * weight / bias / act_param (written through the const pointers of the descriptors), att_out_k [h, 1], att_out_b [1], bn_*,
+ * out_k [h, 1], out_b [1].  loss_out [2] = mean BCE before the update, number of correct predictions. */
+int64_t ctrhot_din_train_workspace_bytes(int64_t B, int T, int K, int n, const ctrhot_dense_desc* att_layers, int n_att,
+                                         const ctrhot_dense_desc* tower_layers, int n_tower);
+int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int K, const int32_t* hist, int64_t hist_ld, int T,
+                              const int32_t* cand, float* const* other_tables, const int64_t* other_rows,
+                              const int32_t* other_dims, int n_other, const int32_t* other_ids, int64_t other_ids_ld,
+                              const float* dense, int64_t dense_ld, int D, const float* y, int64_t B,
+                              const ctrhot_dense_desc* att_layers, int n_att, float* att_out_k, float* att_out_b,
+                              float* bn_gamma, float* bn_beta, float* bn_mean, float* bn_var, float momentum, float eps,
+                              const ctrhot_dense_desc* tower_layers, int n_tower, float* out_k, float* out_b, float lr,
+                              float* loss_out, void* workspace, int64_t workspace_bytes, int* err_flag, void* stream);
+
 /* ---- R15 PNN front: EmbedLayer -> [ flat | InnerProductLayer | OuterProductLayer ] in ONE launch ---------------------------
  * PNN.call DL/model/pnn.py:28-49 up to the concat the tower reads; InnerProductLayer / OuterProductLayer.call
  * DL/layer/interaction.py:170-183 / 201-215 (SURVEY 8(b) `ctrhot_pnn_fwd`: the gathered rows stay in shared memory).

@@ -1131,3 +1131,108 @@ def ffm_train_step(inputs, vocab_sizes, w0, w, v, y, lr, reg_w, reg_v, n_dense=1
     g_v = np.tensordot(x * dz[:, None], G, axes=([0], [0])) + 2 * reg_v * v            # [n_feat, field, k]
     g_w = x.T @ dz[:, None] + 2 * reg_w * w
     return (w0 - lr * np.sum(dz), w - lr * g_w, v - lr * g_v), bce, int(np.sum((p > 0.5) == (y > 0.5)))
+
+
+# --------------------------------------------------------------------------- 8(f) rank 3: DIN under compile_fit
+def din_train_forward(dense_inputs, other_ids, hist_ids, cand_ids, other_tables, seq_table, att_dense, att_out, bn, tower, out):
+    """DIN.call (DL/model/din.py:56-95) in TRAINING mode for one behaviour feature: Attention (DL/layer/interaction.py:369-406,
+    Dense + PReLU with alpha [T, h]), BatchNormalization on the batch's own statistics (biased variance, eps 1e-3), the PReLU
+    tower (alpha [h]); dnn_dropout = 0 (the reference's default).  -> (p [B], cache)."""
+    hist = ids_to_int(hist_ids)
+    cand = ids_to_int(cand_ids).reshape(-1)
+    other_ids = ids_to_int(other_ids) if len(other_tables) else None
+    k = seq_table[hist]                                                                # [B, T, K]
+    q = seq_table[cand]                                                                # [B, K]
+    qt = np.broadcast_to(q[:, None, :], k.shape)
+    xs = [np.concatenate([qt, k, qt - k, qt * k], axis=-1)]                            # [B, T, 4K]
+    pre = []
+    for kernel, bias, alpha in att_dense:
+        pre.append(xs[-1] @ kernel + bias)
+        xs.append(prelu(pre[-1], alpha))
+    s = (xs[-1] @ att_out[0] + att_out[1])[..., 0]                                     # [B, T]
+    mask = hist != 0
+    pw = softmax_last(np.where(mask, s, s.dtype.type(MASK_FILL)))
+    att = np.einsum("bt,btk->bk", pw, k)
+    parts = [att, q] + [other_tables[i][other_ids[:, i]] for i in range(len(other_tables))]
+    if dense_inputs is not None and np.asarray(dense_inputs).shape[1] > 0:
+        parts.append(np.asarray(dense_inputs, dtype=k.dtype))
+    emb = np.concatenate(parts, axis=-1)
+    gamma, beta = bn[0], bn[1]
+    mu, var = emb.mean(axis=0), emb.var(axis=0)
+    rstd = 1.0 / np.sqrt(var + 1e-3)
+    xhat = (emb - mu) * rstd
+    es = [gamma * xhat + beta]
+    tpre = []
+    for kernel, bias, alpha in tower:
+        tpre.append(es[-1] @ kernel + bias)
+        es.append(prelu(tpre[-1], alpha))
+    p = sigmoid(es[-1] @ out[0] + out[1])[:, 0]
+    return p, dict(hist=hist, cand=cand, other_ids=other_ids, k=k, q=q, xs=xs, pre=pre, mask=mask, pw=pw, emb=emb, mu=mu, var=var,
+                   rstd=rstd, xhat=xhat, es=es, tpre=tpre)
+
+
+def din_loss(p, y):
+    pc = np.clip(p, _BCE_LO, _BCE_HI)
+    return float(np.mean(-(y * np.log(pc) + (1 - y) * np.log(1 - pc))))
+
+
+def din_train_step(dense_inputs, other_ids, hist_ids, cand_ids, other_tables, seq_table, att_dense, att_out, bn, tower, out, y,
+                   lr, momentum=0.99):
+    """One step of keras SGD(lr) on DIN's mean clipped BCE (compile_fit, DL/utils/compile_fit.py:9-15, on DL/model/din.py).
+    Every variable moves: the behaviour table (history rows AND the candidate's row: one table, din.py:76-79), the other tables,
+    the attention unit's Dense / PReLU alpha [T, h] / out layer, BatchNormalization's gamma / beta (and its moving statistics by
+    momentum 0.99), the tower's Dense / PReLU alpha [h], the out layer.  Masked positions (history id 0) get no score gradient
+    (tf.where) but still feed the value sum when the whole history is masked (uniform softmax).  PARITY UNPINNED against the
+    reference; gradients pinned by finite differences of `din_train_forward`'s loss.
+    -> (dict of updated parameters, mean BCE before the update, number of correct predictions)."""
+    p, c = din_train_forward(dense_inputs, other_ids, hist_ids, cand_ids, other_tables, seq_table, att_dense, att_out, bn, tower, out)
+    B = p.shape[0]
+    K = seq_table.shape[1]
+    bce = din_loss(p, y)
+    pc = np.clip(p, _BCE_LO, _BCE_HI)
+    dz = (np.where((p > _BCE_LO) & (p < _BCE_HI), pc - y, 0.0) / B)[:, None]
+    new_out = (out[0] - lr * (c["es"][-1].T @ dz), out[1] - lr * np.sum(dz))
+    g = dz @ out[0].T
+    new_tower = [None] * len(tower)
+    for l in range(len(tower) - 1, -1, -1):
+        kernel, bias, alpha = tower[l]
+        P = c["tpre"][l]
+        g_alpha = np.sum(g * np.where(P < 0, P, 0.0), axis=0)
+        gp = g * np.where(P > 0, 1.0, alpha)
+        new_tower[l] = (kernel - lr * (c["es"][l].T @ gp), bias - lr * gp.sum(axis=0), alpha - lr * g_alpha)
+        g = gp @ kernel.T
+    gamma, beta, mean, var = bn
+    xhat = c["xhat"]
+    g_gamma, g_beta = np.sum(g * xhat, axis=0), np.sum(g, axis=0)
+    gx = gamma * c["rstd"] * (g - g_beta / B - xhat * g_gamma / B)
+    new_bn = (gamma - lr * g_gamma, beta - lr * g_beta, momentum * mean + (1 - momentum) * c["mu"],
+              momentum * var + (1 - momentum) * c["var"])
+    g_att, g_q = gx[:, :K], gx[:, K:2 * K].copy()
+    k, q, pw = c["k"], c["q"], c["pw"]
+    g_k = pw[:, :, None] * g_att[:, None, :]
+    g_p = np.einsum("bk,btk->bt", g_att, k)
+    g_s = np.where(c["mask"], pw * (g_p - np.sum(pw * g_p, axis=1, keepdims=True)), 0.0)
+    new_att_out = (att_out[0] - lr * np.einsum("bth,bt->h", c["xs"][-1], g_s)[:, None], att_out[1] - lr * np.sum(g_s))
+    g = g_s[:, :, None] * att_out[0][:, 0]
+    new_att = [None] * len(att_dense)
+    for l in range(len(att_dense) - 1, -1, -1):
+        kernel, bias, alpha = att_dense[l]
+        P = c["pre"][l]
+        g_alpha = np.sum(g * np.where(P < 0, P, 0.0), axis=0)                          # [T, h]
+        gp = g * np.where(P > 0, 1.0, alpha)
+        new_att[l] = (kernel - lr * np.einsum("bti,bth->ih", c["xs"][l], gp), bias - lr * gp.sum(axis=(0, 1)), alpha - lr * g_alpha)
+        g = gp @ kernel.T
+    gA = g                                                                             # [B, T, 4K]
+    g_q += np.sum(gA[..., :K] + gA[..., 2 * K:3 * K] + gA[..., 3 * K:] * k, axis=1)
+    g_k = g_k + gA[..., K:2 * K] - gA[..., 2 * K:3 * K] + gA[..., 3 * K:] * q[:, None, :]
+    new_seq = seq_table.copy()
+    np.add.at(new_seq, c["hist"], -lr * g_k)
+    np.add.at(new_seq, c["cand"], -lr * g_q)
+    new_other = [t.copy() for t in other_tables]
+    col = 2 * K
+    for i, t in enumerate(other_tables):
+        np.add.at(new_other[i], c["other_ids"][:, i], -lr * gx[:, col:col + t.shape[1]])
+        col += t.shape[1]
+    new = dict(seq_table=new_seq, other_tables=new_other, att_dense=new_att, att_out=new_att_out, bn=new_bn, tower=new_tower,
+               out=new_out)
+    return new, bce, int(np.sum((p > 0.5) == (y > 0.5)))

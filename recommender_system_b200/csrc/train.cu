@@ -703,6 +703,169 @@ tr_ffm_sgd_kernel(const float* __restrict__ dense, int64_t dense_ld, int D, cons
   }
 }
 
+// ---------------------------------------------------------------- DIN (DL/model/din.py:56-95 under compile_fit; Attention interaction.py:369-406)
+// history rows k [B, T, K], the candidate's row q [B, K] (same table), the attention unit's input A = [q, k, q - k, q * k] and
+// the mask (history id != 0).  q also goes to its place in the concatenated emb = [att | q | other].  Ids outside the table
+// raise the flag and read as a zero row.
+__global__ void tr_din_gather_kernel(const float* __restrict__ tab, int64_t rows, int K, const int32_t* __restrict__ hist,
+                                     int64_t hist_ld, int T, const int32_t* __restrict__ cand, int64_t B, float* __restrict__ kbuf,
+                                     float* __restrict__ qbuf, float* __restrict__ A, float* __restrict__ mask,
+                                     float* __restrict__ emb, int n, int* __restrict__ err_flag) {
+  const int64_t total = B * T * K;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % K);
+    const int64_t bt = i / K;
+    const int t = (int)(bt % T);
+    const int64_t b = bt / T;
+    const int64_t id = hist[b * hist_ld + t], ic = cand[b];
+    const bool ok = id >= 0 && id < rows, okc = ic >= 0 && ic < rows;
+    if ((!ok || !okc) && err_flag) atomicOr(err_flag, 1);
+    const float kv = ok ? tab[id * K + c] : 0.f, qv = okc ? tab[ic * K + c] : 0.f;
+    kbuf[i] = kv;
+    float* a = A + bt * 4 * K;
+    a[c] = qv; a[K + c] = kv; a[2 * K + c] = qv - kv; a[3 * K + c] = qv * kv;
+    if (c == 0) mask[bt] = id != 0 ? 1.f : 0.f;
+    if (t == 0) { qbuf[b * K + c] = qv; emb[b * n + K + c] = qv; }
+  }
+}
+// pre += bias (kept for the backward pass), out = PReLU(pre) with alpha [alpha_rows, N] (row = r % alpha_rows: the position t for
+// the attention unit's [T, h] alphas, 0 for the tower's [h])
+__global__ void tr_bias_prelu_kernel(float* __restrict__ pre, const float* __restrict__ bias, const float* __restrict__ alpha,
+                                     int64_t R, int N, int arows, float* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < R * N; i += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(i % N);
+    const int64_t r = i / N;
+    const float p = pre[i] + bias[n];
+    pre[i] = p;
+    out[i] = p > 0.f ? p : alpha[(r % arows) * N + n] * p;
+  }
+}
+// PReLU backward, one thread per alpha entry (t, n): g <- g * (pre > 0 ? 1 : alpha_old) over its rows r = b * arows + t, and
+// alpha -= lr * sum_b g * min(pre, 0).  Rows in order: deterministic.
+__global__ void tr_prelu_bwd_kernel(float* __restrict__ g, const float* __restrict__ pre, float* __restrict__ alpha, int64_t R, int N,
+                                    int arows, float lr) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)arows * N) return;
+  const int n = (int)(i % N);
+  const int t = (int)(i / N);
+  const float a = alpha[i];
+  float ga = 0.f;
+  for (int64_t r = t; r < R; r += arows) {
+    const float p = pre[r * N + n], gg = g[r * N + n];
+    if (p < 0.f) ga = fmaf(gg, p, ga);
+    g[r * N + n] = p > 0.f ? gg : a * gg;
+  }
+  alpha[i] = a - lr * ga;
+}
+// scores -> masked softmax over the T positions -> att = sum_t pw_t k_t, written to emb[:, 0:K].  One warp per sample.
+__global__ void __launch_bounds__(128)
+tr_din_softmax_att_kernel(const float* __restrict__ s, const float* __restrict__ b3, const float* __restrict__ mask,
+                          const float* __restrict__ kbuf, int T, int K, int64_t B, float* __restrict__ pw,
+                          float* __restrict__ emb, int n) {
+  TR_WARP_IDS();
+  for (int64_t b = warp; b < B; b += nwarps) {
+    float mx = -INFINITY;
+    for (int t = lane; t < T; t += 32) {
+      const float v = mask[b * T + t] != 0.f ? s[b * T + t] + b3[0] : -4294967295.0f;      // -2^32 + 1 (interaction.py:399)
+      pw[b * T + t] = v;
+      mx = fmaxf(mx, v);
+    }
+    for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+    for (int t = lane; t < T; t += 32) { const float e = expf(pw[b * T + t] - mx); pw[b * T + t] = e; sum += e; }
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    for (int t = lane; t < T; t += 32) pw[b * T + t] *= inv;
+    __syncwarp();
+    for (int c = lane; c < K; c += 32) {
+      float a = 0.f;
+      for (int t = 0; t < T; ++t) a = fmaf(pw[b * T + t], kbuf[(b * T + t) * K + c], a);
+      emb[b * n + c] = a;
+    }
+  }
+}
+// one other-feature table into its columns of emb
+__global__ void tr_din_other_gather_kernel(const float* __restrict__ tab, int64_t rows, int dim, const int32_t* __restrict__ ids,
+                                           int64_t ids_ld, int64_t B, float* __restrict__ emb, int n, int* __restrict__ err_flag) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * dim; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / dim;
+    const int c = (int)(i - b * dim);
+    const int64_t id = ids[b * ids_ld];
+    const bool ok = id >= 0 && id < rows;
+    if (!ok && err_flag) atomicOr(err_flag, 1);
+    emb[b * n + c] = ok ? tab[id * dim + c] : 0.f;
+  }
+}
+__global__ void tr_din_other_sgd_kernel(float* __restrict__ tab, int64_t rows, int dim, const int32_t* __restrict__ ids,
+                                        int64_t ids_ld, int64_t B, const float* __restrict__ gx, int n, float lr) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * dim; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / dim;
+    const int c = (int)(i - b * dim);
+    const int64_t id = ids[b * ids_ld];
+    if (id >= 0 && id < rows) atomicAdd(tab + id * dim + c, -lr * gx[b * n + c]);
+  }
+}
+__global__ void tr_copy_cols_kernel(const float* __restrict__ src, int64_t src_ld, int w, int64_t B, float* __restrict__ dst, int n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * w; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / w;
+    dst[b * n + (i - b * w)] = src[b * src_ld + (i - b * w)];
+  }
+}
+// attention pooling backward, one warp per sample: g_att = gx[b, 0:K];  g_p[t] = <g_att, k_t>;  gs[t] = mask ? pw (g_p - sum pw g_p)
+// : 0  (tf.where passes no gradient to a masked score);  gk[b, t, :] = pw_t g_att  (non-zero on masked positions only when the
+// whole history is masked and the softmax is uniform)
+__global__ void __launch_bounds__(128)
+tr_din_att_bwd_kernel(const float* __restrict__ gx, int n, const float* __restrict__ kbuf, const float* __restrict__ pw,
+                      const float* __restrict__ mask, int T, int K, int64_t B, float* __restrict__ gs, float* __restrict__ gk) {
+  TR_WARP_IDS();
+  for (int64_t b = warp; b < B; b += nwarps) {
+    float dot = 0.f;
+    for (int t = lane; t < T; t += 32) {
+      float gp = 0.f;
+      for (int c = 0; c < K; ++c) gp = fmaf(gx[b * n + c], kbuf[(b * T + t) * K + c], gp);
+      gs[b * T + t] = gp;
+      dot = fmaf(pw[b * T + t], gp, dot);
+    }
+    dot = warp_sum(dot);
+    for (int t = lane; t < T; t += 32)
+      gs[b * T + t] = mask[b * T + t] != 0.f ? pw[b * T + t] * (gs[b * T + t] - dot) : 0.f;
+    for (int i = lane; i < T * K; i += 32) gk[b * T * K + i] = pw[b * T + i / K] * gx[b * n + i % K];
+  }
+}
+// A = [q, k, q - k, q * k] backward and the behaviour table's update, one thread per (sample, column):
+// g_q = gx[b, K + c] + sum_t (gA0 + gA2 + gA3 k);  g_k = gk + gA1 - gA2 + gA3 q;  rows shared by samples / positions add up
+__global__ void tr_din_concat_bwd_sgd_kernel(const float* __restrict__ gA, const float* __restrict__ gk, const float* __restrict__ gx,
+                                             int n, const float* __restrict__ kbuf, const float* __restrict__ qbuf,
+                                             const int32_t* __restrict__ hist, int64_t hist_ld, const int32_t* __restrict__ cand,
+                                             int T, int K, int64_t B, int64_t rows, float lr, float* __restrict__ tab) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B * K; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / K;
+    const int c = (int)(i - b * K);
+    const float q = qbuf[i];
+    float gq = gx[b * n + K + c];
+    // a run of equal ids (the padding tail above all) is summed here and added once: T tiny adds into the padding row would each
+    // round away against the row's own magnitude
+    int64_t run_id = -1;
+    float run = 0.f;
+    for (int t = 0; t < T; ++t) {
+      const int64_t bt = b * T + t;
+      const float* a = gA + bt * 4 * K;
+      const float kv = kbuf[bt * K + c];
+      gq += a[c] + a[2 * K + c] + a[3 * K + c] * kv;
+      const float g = gk[bt * K + c] + a[K + c] - a[2 * K + c] + a[3 * K + c] * q;
+      const int64_t id = hist[b * hist_ld + t];
+      if (id != run_id) {
+        if (run != 0.f && run_id >= 0 && run_id < rows) atomicAdd(tab + run_id * K + c, -lr * run);
+        run_id = id; run = 0.f;
+      }
+      run += g;
+    }
+    if (run != 0.f && run_id >= 0 && run_id < rows) atomicAdd(tab + run_id * K + c, -lr * run);
+    const int64_t ic = cand[b];
+    if (ic >= 0 && ic < rows) atomicAdd(tab + ic * K + c, -lr * gq);
+  }
+}
+
 }  // namespace ctrhot
 
 using namespace ctrhot;
@@ -1518,5 +1681,160 @@ extern "C" int ctrhot_ffm_train_step_f32(const float* dense, int64_t dense_ld, i
   if (i32) tr_ffm_sgd_kernel<CTRHOT_IDS_I32><<<g2, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, dz, lr, len, k, ff, S, w, v);
   else tr_ffm_sgd_kernel<CTRHOT_IDS_F32><<<g2, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, dz, lr, len, k, ff, S, w, v);
   CTRHOT_LAUNCH_OK("ctrhot_ffm_train_step_f32");
+  return CTRHOT_OK;
+}
+
+// ---------------------------------------------------------------- DIN training step (DL/model/din.py under compile_fit)
+namespace {
+struct TrDinLayout {
+  int64_t kbuf, qbuf, A, mask, s, pw, emb, xhat, yb, rstd, z, dz, g0, g1, gx, gs, gk, total;
+  int64_t apre[8], ax[8], tpre[8], tx[8];
+};
+bool tr_din_layout(int64_t B, int T, int K, int n, const ctrhot_dense_desc* att, int n_att, const ctrhot_dense_desc* tw, int n_tw,
+                   TrDinLayout& w) {
+  if (n_att < 1 || n_att > 8 || n_tw < 1 || n_tw > 8 || !att || !tw) return false;
+  int64_t o = 0;
+  auto take = [&](int64_t cnt) { const int64_t at = o; o += (cnt + 3) / 4 * 4; return at; };
+  const int64_t BT = B * T;
+  int64_t wide_a = 4 * K, wide_t = n;
+  for (int l = 0; l < n_att; ++l) {
+    if (att[l].in_dim != (l ? att[l - 1].out_dim : 4 * K) || !att[l].weight || !att[l].bias || !att[l].act_param ||
+        att[l].alpha_rows != T) return false;
+    if (att[l].out_dim > wide_a) wide_a = att[l].out_dim;
+  }
+  for (int l = 0; l < n_tw; ++l) {
+    if (tw[l].in_dim != (l ? tw[l - 1].out_dim : n) || !tw[l].weight || !tw[l].bias || !tw[l].act_param || tw[l].alpha_rows != 1)
+      return false;
+    if (tw[l].out_dim > wide_t) wide_t = tw[l].out_dim;
+  }
+  w.kbuf = take(BT * K); w.qbuf = take(B * K); w.A = take(BT * 4 * K); w.mask = take(BT); w.s = take(BT); w.pw = take(BT);
+  w.emb = take(B * n); w.xhat = take(B * n); w.yb = take(B * n); w.rstd = take(n); w.z = take(B); w.dz = take(B);
+  const int64_t gw = BT * wide_a > B * wide_t ? BT * wide_a : B * wide_t;
+  w.g0 = take(gw); w.g1 = take(gw); w.gx = take(B * n); w.gs = take(BT); w.gk = take(BT * K);
+  for (int l = 0; l < n_att; ++l) { w.apre[l] = take(BT * att[l].out_dim); w.ax[l] = take(BT * att[l].out_dim); }
+  for (int l = 0; l < n_tw; ++l) { w.tpre[l] = take(B * tw[l].out_dim); w.tx[l] = take(B * tw[l].out_dim); }
+  w.total = o;
+  return true;
+}
+}  // namespace
+
+extern "C" int64_t ctrhot_din_train_workspace_bytes(int64_t B, int T, int K, int n, const ctrhot_dense_desc* att_layers, int n_att,
+                                                    const ctrhot_dense_desc* tower_layers, int n_tower) {
+  TrDinLayout w;
+  if (B < 0 || T < 1 || K < 1 || n < 2 * K) return CTRHOT_ESHAPE;
+  if (!tr_din_layout(B, T, K, n, att_layers, n_att, tower_layers, n_tower, w)) return CTRHOT_ESHAPE;
+  return w.total * (int64_t)sizeof(float);
+}
+
+extern "C" int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int K, const int32_t* hist, int64_t hist_ld, int T,
+                                         const int32_t* cand, float* const* other_tables, const int64_t* other_rows,
+                                         const int32_t* other_dims, int n_other, const int32_t* other_ids, int64_t other_ids_ld,
+                                         const float* dense, int64_t dense_ld, int D, const float* y, int64_t B,
+                                         const ctrhot_dense_desc* att_layers, int n_att, float* att_out_k, float* att_out_b,
+                                         float* bn_gamma, float* bn_beta, float* bn_mean, float* bn_var, float momentum, float eps,
+                                         const ctrhot_dense_desc* tower_layers, int n_tower, float* out_k, float* out_b, float lr,
+                                         float* loss_out, void* workspace, int64_t workspace_bytes, int* err_flag, void* stream) {
+  CTRHOT_RANGE("ctrhot_din_train_step_f32");
+  if (!seq_table || !hist || !cand || !y || !att_out_k || !att_out_b || !bn_gamma || !bn_beta || !bn_mean || !bn_var || !out_k ||
+      !out_b || !loss_out || !workspace || B <= 0 || T < 1 || K < 1 || hist_ld < T || seq_rows < 1 || n_other < 0 || D < 0 ||
+      !(lr >= 0.f))
+    return CTRHOT_EARG;
+  if ((n_other > 0 && (!other_tables || !other_rows || !other_dims || !other_ids || other_ids_ld < n_other)) ||
+      (D > 0 && (!dense || dense_ld < D)))
+    return CTRHOT_EARG;
+  int n = 2 * K + D;
+  for (int i = 0; i < n_other; ++i) {
+    if (!other_tables[i] || other_rows[i] < 1 || other_dims[i] < 1) return CTRHOT_EARG;
+    n += other_dims[i];
+  }
+  TrDinLayout w;
+  if (B * (int64_t)T > INT32_MAX || !tr_din_layout(B, T, K, n, att_layers, n_att, tower_layers, n_tower, w)) return CTRHOT_ESHAPE;
+  if (workspace_bytes < w.total * (int64_t)sizeof(float) || !aligned16(workspace)) return CTRHOT_EARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* ws = static_cast<float*>(workspace);
+  float *kbuf = ws + w.kbuf, *qbuf = ws + w.qbuf, *A = ws + w.A, *mask = ws + w.mask, *s = ws + w.s, *pw = ws + w.pw,
+        *emb = ws + w.emb, *xhat = ws + w.xhat, *yb = ws + w.yb, *rstd = ws + w.rstd, *z = ws + w.z, *dz = ws + w.dz,
+        *gx = ws + w.gx, *gs = ws + w.gs, *gk = ws + w.gk;
+  const int M = (int)B, BT = (int)(B * T);
+  // ---- forward: rows, the attention unit over every (sample, position), masked softmax pooling
+  tr_din_gather_kernel<<<tr_grid(B * T * K, 256), 256, 0, st>>>(seq_table, seq_rows, K, hist, hist_ld, T, cand, B, kbuf, qbuf, A, mask,
+                                                               emb, n, err_flag);
+  const float* in = A;
+  int in_dim = 4 * K;
+  for (int l = 0; l < n_att; ++l) {
+    const int N = att_layers[l].out_dim;
+    float* pre = ws + w.apre[l];
+    float* x = ws + w.ax[l];
+    tr_gemm(st, in, in_dim, 1, att_layers[l].weight, N, 1, pre, N, BT, N, in_dim, 1.f, 0.f);
+    tr_bias_prelu_kernel<<<tr_grid((int64_t)BT * N, 256), 256, 0, st>>>(pre, att_layers[l].bias, att_layers[l].act_param, BT, N, T, x);
+    in = x; in_dim = N;
+  }
+  const int ha = in_dim;
+  tr_gemm(st, in, ha, 1, att_out_k, 1, 1, s, 1, BT, 1, ha, 1.f, 0.f);
+  tr_din_softmax_att_kernel<<<tr_grid(B * 32, 128), 128, 0, st>>>(s, att_out_b, mask, kbuf, T, K, B, pw, emb, n);
+  int col = 2 * K;
+  for (int i = 0; i < n_other; ++i) {
+    tr_din_other_gather_kernel<<<tr_grid(B * other_dims[i], 256), 256, 0, st>>>(other_tables[i], other_rows[i], other_dims[i],
+                                                                               other_ids + i, other_ids_ld, B, emb + col, n, err_flag);
+    col += other_dims[i];
+  }
+  if (D > 0) tr_copy_cols_kernel<<<tr_grid(B * D, 256), 256, 0, st>>>(dense, dense_ld, D, B, emb + col, n);
+  // ---- BatchNormalization on the batch's statistics, PReLU tower, Dense(1), loss
+  tr_bn_fwd_kernel<<<n, 256, 0, st>>>(emb, n, B, bn_gamma, bn_beta, bn_mean, bn_var, momentum, eps, xhat, yb, rstd);
+  in = yb; in_dim = n;
+  for (int l = 0; l < n_tower; ++l) {
+    const int N = tower_layers[l].out_dim;
+    float* pre = ws + w.tpre[l];
+    float* x = ws + w.tx[l];
+    tr_gemm(st, in, in_dim, 1, tower_layers[l].weight, N, 1, pre, N, M, N, in_dim, 1.f, 0.f);
+    tr_bias_prelu_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(pre, tower_layers[l].bias, tower_layers[l].act_param, B, N, 1, x);
+    in = x; in_dim = N;
+  }
+  const int ht = in_dim;
+  tr_gemm(st, in, ht, 1, out_k, 1, 1, z, 1, M, 1, ht, 1.f, 0.f);
+  tr_loss_kernel<<<1, 256, 0, st>>>(z, nullptr, out_b, y, B, dz, loss_out, nullptr, 1.0f);
+  // ---- backward: Dense(1), tower
+  float* g = ws + w.g0;
+  float* gn = ws + w.g1;
+  tr_gemm(st, dz, 1, 1, out_k, 0, 1, g, ht, M, ht, 1, 1.f, 0.f);                            // g = dz out_k^T (old out_k)
+  tr_gemm(st, in, 1, ht, dz, 1, 1, out_k, 1, ht, 1, M, -lr, 1.f);
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, out_b, -lr, 1.f);
+  for (int l = n_tower - 1; l >= 0; --l) {
+    const int N = tower_layers[l].out_dim, Kd = tower_layers[l].in_dim;
+    const float* hin = l > 0 ? ws + w.tx[l - 1] : yb;
+    float* W = const_cast<float*>(tower_layers[l].weight);
+    tr_prelu_bwd_kernel<<<(N + 127) / 128, 128, 0, st>>>(g, ws + w.tpre[l], const_cast<float*>(tower_layers[l].act_param), B, N, 1, lr);
+    tr_gemm(st, g, N, 1, W, 1, N, gn, Kd, M, Kd, N, 1.f, 0.f);                              // through the old W
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
+    tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(tower_layers[l].bias), -lr, 1.f);
+    float* tmp = g; g = gn; gn = tmp;
+  }
+  tr_bn_bwd_kernel<<<n, 256, 0, st>>>(g, xhat, n, B, bn_gamma, bn_beta, rstd, lr, gx);
+  // ---- attention pooling, the unit's out layer and its Dense + PReLU layers
+  tr_din_att_bwd_kernel<<<tr_grid(B * 32, 128), 128, 0, st>>>(gx, n, kbuf, pw, mask, T, K, B, gs, gk);
+  const float* xl = ws + w.ax[n_att - 1];
+  tr_gemm(st, gs, 1, 1, att_out_k, 0, 1, g, ha, BT, ha, 1, 1.f, 0.f);                       // g = gs w3^T (old w3)
+  tr_gemm(st, xl, 1, ha, gs, 1, 1, att_out_k, 1, ha, 1, BT, -lr, 1.f);
+  tr_colsum_kernel<<<1, 1024, 0, st>>>(gs, 1, nullptr, BT, 1, 0, att_out_b, -lr, 1.f);
+  for (int l = n_att - 1; l >= 0; --l) {
+    const int N = att_layers[l].out_dim, Kd = att_layers[l].in_dim;
+    const float* hin = l > 0 ? ws + w.ax[l - 1] : A;
+    float* W = const_cast<float*>(att_layers[l].weight);
+    tr_prelu_bwd_kernel<<<(T * N + 127) / 128, 128, 0, st>>>(g, ws + w.apre[l], const_cast<float*>(att_layers[l].act_param), BT, N, T, lr);
+    tr_gemm(st, g, N, 1, W, 1, N, gn, Kd, BT, Kd, N, 1.f, 0.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, BT, -lr, 1.f);
+    tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, BT, N, 0, const_cast<float*>(att_layers[l].bias), -lr, 1.f);
+    float* tmp = g; g = gn; gn = tmp;
+  }
+  // ---- the concat [q, k, q - k, q * k], then every table (all reads of the tables happened in the forward pass)
+  tr_din_concat_bwd_sgd_kernel<<<tr_grid(B * K, 128), 128, 0, st>>>(g, gk, gx, n, kbuf, qbuf, hist, hist_ld, cand, T, K, B, seq_rows, lr,
+                                                                   seq_table);
+  col = 2 * K;
+  for (int i = 0; i < n_other; ++i) {
+    tr_din_other_sgd_kernel<<<tr_grid(B * other_dims[i], 256), 256, 0, st>>>(other_tables[i], other_rows[i], other_dims[i], other_ids + i,
+                                                                            other_ids_ld, B, gx + col, n, lr);
+    col += other_dims[i];
+  }
+  CTRHOT_LAUNCH_OK("ctrhot_din_train_step_f32");
   return CTRHOT_OK;
 }

@@ -11,7 +11,8 @@ rows that were looked up, the FM weights and the tower.  SURVEY 8(f) rank 3; bui
 ``ctrhot_dcn_train_step_f32``) and for PNN (the loop of DL/model/pnn.py:74-85, which compile_fit reproduces for it: BCE on
 the raw output, no regularisers; ``ctrhot_pnn_train_step_f32``) and for WideDeep (DL/model/wideDeep.py:37-49; ``ctrhot_widedeep_train_step_f32``) and DeepCrossing
 (DL/model/deepCrossing.py:35-47; ``ctrhot_deepcrossing_train_step_f32``) and NFM (DL/model/nfm.py:37-50, BatchNormalization in training
-mode; ``ctrhot_nfm_train_step_f32``) and AFM (``ctrhot_afm_train_step_f32``) -- other models raise NotImplementedError.
+mode; ``ctrhot_nfm_train_step_f32``) and AFM (``ctrhot_afm_train_step_f32``), FFM (``ctrhot_ffm_train_step_f32``) and DIN on its dict
+input (DL/model/din.py:98-108; ``ctrhot_din_train_step_f32``) -- other models raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -28,7 +29,7 @@ class _DeepFMTrainer:
     def __init__(self, model, dropout=None):
         from ..model.criteo import DeepFM
         if not isinstance(model, DeepFM):
-            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, NFM, AFM, PNN, FM and FFM only (SURVEY 8(f) rank 3)")
+            raise NotImplementedError("compile_fit: the training step exists for DeepFM, DCN, WideDeep, DeepCrossing, NFM, AFM, PNN, FM, FFM and DIN only (SURVEY 8(f) rank 3)")
         self.m = model
         if not model.dnn.built:
             model.build(None)
@@ -467,6 +468,111 @@ class _AFMTrainer:
         return self.loss
 
 
+class _DINTrainer:
+    """DIN (DL/model/din.py:56-95 and its ``__main__``, :98-108): ctrhot_din_train_step_f32 per batch.  One behaviour feature,
+    PReLU attention unit and tower, dnn_dropout 0 -- the reference's defaults; BatchNormalization runs on the batch's statistics
+    and its moving statistics are the ones the forward path serves afterwards."""
+
+    def __init__(self, model):
+        import ctypes
+        m = self.m = model
+        if m.behavior_num != 1 or m.att_layer.activation != "prelu" or m.dnn_activation != "prelu" or m.dnn_dropout:
+            raise NotImplementedError("compile_fit(DIN): one behaviour feature, 'prelu' attention and tower, dnn_dropout = 0 only")
+        self.ws, self.step, self.ct = None, 0, ctypes
+        self.loss = torch.zeros(2, dtype=torch.float32, device=m.device)
+        self.flag = m.err_flag()
+        self.desc = None
+
+    def _descs(self):
+        m, ct = self.m, self.ct
+        att, tw = m.att_layer.layers, m.dense_layer
+        self.att_desc = (_lib.DenseDesc * len(att))()
+        self.tw_desc = (_lib.DenseDesc * len(tw))()
+        for arr, layers, rows in ((self.att_desc, att, m.att_layer.T), (self.tw_desc, tw, 1)):
+            for d, (k, b, a) in zip(arr, layers):
+                d.weight, d.bias, d.act_param = ptr(k), ptr(b), ptr(a)
+                d.in_dim, d.out_dim, d.act, d.alpha_rows = int(k.shape[0]), int(k.shape[1]), _lib.ACT_PRELU, rows
+        tabs = m.embed_sparse_layers
+        self.n_other = len(tabs)
+        self.o_ptr = (ct.c_void_p * max(1, len(tabs)))(*[ptr(t) for t in tabs])
+        self.o_rows = (ct.c_int64 * max(1, len(tabs)))(*[int(t.shape[0]) for t in tabs])
+        self.o_dims = (ct.c_int32 * max(1, len(tabs)))(*[int(t.shape[1]) for t in tabs])
+        self.desc = m._version
+
+    def train_on_batch(self, inputs, y, lr):
+        from ..layer.core import _ids_to_device
+        m, dev = self.m, self.m.device
+        hist = _ids_to_device(m._col(inputs, m.behavior[0]["feat"]), dev).to(torch.int32).contiguous()
+        B, T = hist.shape
+        if not m.att_layer.built:
+            if not hasattr(m, "bn_gamma"):
+                m.build(None)
+            m.att_layer.build_for(T, m.K)
+        elif not hasattr(m, "bn_gamma"):
+            m.build(None)
+        if T != m.att_layer.T:
+            raise ValueError("DIN: history length %d, the attention unit was built for %d" % (T, m.att_layer.T))
+        if self.desc is None:
+            self._descs()
+        cand = _ids_to_device(m._col(inputs, m.candidate_key), dev).reshape(B, -1)[:, 0].to(torch.int32).contiguous()
+        if self.n_other:
+            oid = torch.stack([_ids_to_device(m._col(inputs, f["feat"]), dev).reshape(B, -1)[:, 0].to(torch.int32)
+                               for f in m.other_sparse], dim=1).contiguous()
+        else:
+            oid = None
+        dense = None
+        if m.dense_num:
+            cols = [as_device_f32(m._col(inputs, f["feat"]), dev).reshape(B, -1) for f in m.dense_feature_columns]
+            dense = (cols[0] if len(cols) == 1 else torch.cat(cols, dim=-1)).contiguous()
+        yd = as_device_f32(y, dev).reshape(-1)
+        need = _lib.query("ctrhot_din_train_workspace_bytes", B, T, m.K, m.dcat, self.att_desc, len(self.att_desc), self.tw_desc,
+                          len(self.tw_desc))
+        if self.ws is None or self.ws.numel() * 4 < need:
+            self.ws = torch.empty(need // 4 + 4, dtype=torch.float32, device=dev)
+        seq = m.embed_seq_layers[0]
+        A = m.att_layer
+        _lib.call("ctrhot_din_train_step_f32", ptr(seq), int(seq.shape[0]), m.K, ptr(hist), hist.stride(0), T, ptr(cand),
+                  self.o_ptr if self.n_other else None, self.o_rows if self.n_other else None,
+                  self.o_dims if self.n_other else None, self.n_other, ptr(oid) if oid is not None else None,
+                  self.n_other, ptr(dense) if dense is not None else None, dense.stride(0) if dense is not None else 0,
+                  m.dense_num, ptr(yd), B, self.att_desc, len(self.att_desc), ptr(A.out_kernel), ptr(A.out_bias),
+                  ptr(m.bn_gamma), ptr(m.bn_beta), ptr(m.bn_mean), ptr(m.bn_var), 0.99, 1e-3, self.tw_desc, len(self.tw_desc),
+                  ptr(m.out_kernel), ptr(m.out_bias), float(lr), ptr(self.loss), ptr(self.ws), self.ws.numel() * 4,
+                  ptr(self.flag), stream_ptr())
+        self.step += 1
+        return self.loss
+
+
+def _fit_din(model, X, y, batch_size, epochs, sgd, verbose):
+    """X: the reference's dict of per-feature lists / arrays (DL/model/din.py:101-105); batches in order."""
+    from ..layer.core import _ids_to_device
+    tr = _DINTrainer(model)
+    dev = model.device
+    names = [f["feat"] for f in model.dense_feature_columns] + [f["feat"] for f in model.sparse_feature_columns]
+    if model.candidate_key not in names:
+        names.append(model.candidate_key)
+    dense_names = set(f["feat"] for f in model.dense_feature_columns)
+    Xd = {n: (as_device_f32(np.asarray(X[n], dtype=np.float32) if not isinstance(X[n], torch.Tensor) else X[n], dev)
+              if n in dense_names else _ids_to_device(X[n], dev)) for n in names}
+    yd = as_device_f32(np.asarray(y, dtype=np.float32).reshape(-1) if not isinstance(y, torch.Tensor) else y.reshape(-1), dev)
+    N = yd.shape[0]
+    model.history = []
+    for ep in range(epochs):
+        tot = torch.zeros(2, dtype=torch.float64, device=dev)
+        for s in range(0, N, batch_size):
+            e = min(N, s + batch_size)
+            out = tr.train_on_batch({n: v[s:e] for n, v in Xd.items()}, yd[s:e], sgd)
+            tot[0] += out[0].double() * (e - s)
+            tot[1] += out[1].double()
+        loss, acc = (tot / N).tolist()
+        _lib.check(_lib.load().ctrhot_check_flag(ptr(tr.flag), stream_ptr()), "compile_fit")
+        model.history.append((loss, acc))
+        if verbose:
+            print("Epoch %d/%d - loss: %.4f - accuracy: %.4f" % (ep + 1, epochs, loss, acc))
+    model._bump()
+    return model
+
+
 def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, seed=0, verbose=True, use_graph=True):
     """``X`` the reference's [N, 39] matrix (13 dense floats, 26 label-encoded ids stored as floats), numpy or torch; ``y`` [N].
     ``dropout=None`` uses the model's DNNLayer rate (0.2 in the reference).  Returns the model, trained in place; the per-epoch
@@ -474,6 +580,9 @@ def compile_fit(model, X, y, batch_size=32, epochs=10, sgd=0.01, dropout=None, s
     graph (the step is launch-bound at the reference's batch size); the ragged last batch is an ordinary call."""
     from ..model.criteo import AFMLayer, DCN, FFM, FM, NFM, PNN, WideDeep
     from ..model.deepCrossing import DeepCrossing
+    from ..model.din import DIN
+    if isinstance(model, DIN):
+        return _fit_din(model, X, y, batch_size, epochs, sgd, verbose)
     if isinstance(model, FFM):
         return _fit_fm(model, X, y, batch_size, epochs, sgd, verbose, trainer=_FFMTrainer(model))
     if isinstance(model, AFMLayer):                               # AFM is a subclass

@@ -689,3 +689,102 @@ def test_ffm_compile_fit_lowers_the_loss(lib):
         m.ffm.v.mul_(0.2)                    # then has zero gradient on the wrong-side samples, in the reference as well
     compile_fit(m, X, y, batch_size=32, epochs=6, sgd=0.01, verbose=False)      # (sgd = 0.05 diverges, in the oracle as well)
     assert m.history[-1][0] < 0.5 * m.history[0][0] and m.history[-1][1] > 0.95, m.history
+
+
+# ------------------------------------------------------------------ DIN (DL/model/din.py under compile_fit)
+def make_din(v_item, v_user, K, T, att_hidden, dnn_hidden, seed=1):
+    from recommender_system_b200.model.din import DIN
+    from recommender_system_b200.utils import synth
+    set_seed(seed)
+    m = DIN(synth.din_feature_columns(v_item=v_item, v_user=v_user, embed_dim=K), ["movies_seq"], tuple(att_hidden), tuple(dnn_hidden),
+            "prelu", "prelu", 0.0, precision="fp32")
+    m.build(None)
+    m.att_layer.build_for(T, K)
+    rng = np.random.default_rng(seed)
+    upd = {}
+    for n, w in m.named_weights().items():                       # keras' zero biases / alphas would hide mistakes in their gradients
+        if n.endswith("bias") or n.endswith("beta"):
+            upd[n] = rng.normal(0, 0.1, tuple(w.shape))
+        elif n.endswith("prelu_alpha"):
+            upd[n] = rng.normal(0.2, 0.2, tuple(w.shape))
+        elif n.endswith("gamma"):
+            upd[n] = rng.normal(1.0, 0.2, tuple(w.shape))
+        elif n.endswith("embeddings"):
+            upd[n] = rng.normal(0, 0.5, tuple(w.shape))
+    m.set_weights({n: np.asarray(v, np.float32) for n, v in upd.items()})
+    return m
+
+
+def din_params(m):
+    A = m.att_layer
+    return dict(other_tables=[npy(t) for t in m.embed_sparse_layers], seq_table=npy(m.embed_seq_layers[0]),
+                att_dense=[(npy(k), npy(b), npy(a)) for k, b, a in A.layers], att_out=(npy(A.out_kernel), npy(A.out_bias)),
+                bn=(npy(m.bn_gamma), npy(m.bn_beta), npy(m.bn_mean), npy(m.bn_var)),
+                tower=[(npy(k), npy(b), npy(a)) for k, b, a in m.dense_layer], out=(npy(m.out_kernel), npy(m.out_bias)))
+
+
+@pytest.mark.parametrize("B,T,K,att_hidden,dnn_hidden,v_item", [
+    (32, 10, 8, (80, 40), (256, 128, 64), 50), (1, 3, 4, (6,), (8,), 50), (257, 7, 16, (20, 10), (64, 32), 50),
+    (600, 40, 8, (80, 40), (64, 32), 3000)])      # (3000 items: at 50 every row would take ~480 atomic adds, 3e-6 of fp32 round-off)
+def test_din_one_step_against_the_oracle(lib, B, T, K, att_hidden, dnn_hidden, v_item):
+    """One SGD step of DIN against oracle.din_train_step: the behaviour table (history + candidate rows, duplicates, padding id
+    0, one all-padding history), the other table, every Dense / PReLU alpha of the attention unit and the tower, both out
+    layers, BatchNormalization's gamma / beta and moving statistics, the loss and the accuracy."""
+    from recommender_system_b200.utils import synth
+    from recommender_system_b200.utils.compile_fit import _DINTrainer
+    v_user = 9
+    m = make_din(v_item, v_user, K, T, att_hidden, dnn_hidden, seed=B)
+    d = synth.din_batch(B, T, v_item=v_item, v_user=v_user, seed=B + 3)
+    if B > 2:
+        d["movies_seq"][2] = 0                                   # whole history masked: uniform softmax over the padding row
+        d["movie_id"][1, 0] = max(1, int(d["movies_seq"][1, 0]))  # the candidate's row also sits in its history
+    rng = np.random.default_rng(B)
+    y = rng.integers(0, 2, B).astype(np.float32)
+    P = din_params(m)
+    before = din_params(m)
+    lr = 0.1
+    tr = _DINTrainer(m)
+    dev = m.device
+    res = tr.train_on_batch({k: torch.from_numpy(v).to(dev) for k, v in d.items()}, torch.from_numpy(y).to(dev), lr)
+    torch.cuda.synchronize()
+    m.check_ids()
+    want, bce, correct = O.din_train_step(d["age"].astype(np.float64), d["user_id"], d["movies_seq"], d["movie_id"][:, 0], y=y.astype(np.float64),
+                                          lr=lr, **P)
+    assert abs(float(res[0]) - bce) <= 2e-6 * max(1.0, bce) and int(res[1]) == correct
+    got = din_params(m)
+    close(got["seq_table"], want["seq_table"], before["seq_table"], "seq table", floor=1e-6)
+    close(got["other_tables"][0], want["other_tables"][0], before["other_tables"][0], "other table", floor=1e-6)
+    for name in ("att_dense", "tower"):
+        for l, (g3, w3, b3) in enumerate(zip(got[name], want[name], before[name])):
+            for part, what in enumerate(("kernel", "bias", "alpha")):
+                close(g3[part], w3[part], b3[part], "%s %d %s" % (name, l, what))
+    for name in ("att_out", "out"):
+        for part in (0, 1):
+            close(got[name][part], want[name][part], before[name][part], "%s %d" % (name, part))
+    for part, what in enumerate(("gamma", "beta", "moving mean", "moving variance")):
+        close(got["bn"][part], want["bn"][part], before["bn"][part], "bn " + what)
+
+
+def test_din_compile_fit_learns_and_serves(lib):
+    """compile_fit on the reference's dict input (DL/model/din.py:98-108): the loss falls on a planted rule (the label says
+    whether the candidate occurs in the history), and the forward path then serves the trained weights with the moving
+    statistics the steps maintained."""
+    from recommender_system_b200.utils import synth
+    v_item, v_user, T, K = 40, 9, 8, 8
+    N = 1500 + 7
+    d = synth.din_batch(N, T, v_item=v_item, v_user=v_user, seed=5)
+    rng = np.random.default_rng(8)
+    pos = rng.random(N) < 0.5
+    for i in np.nonzero(pos)[0]:
+        d["movies_seq"][i, 0] = d["movie_id"][i, 0]
+    y = np.array([float(d["movie_id"][i, 0] in d["movies_seq"][i]) for i in range(N)], np.float32)
+    m = make_din(v_item, v_user, K, T, (16, 8), (32, 16), seed=2)
+    X = {k: list(v) if k == "movies_seq" else v for k, v in d.items()}
+    compile_fit(m, X, y, batch_size=32, epochs=8, sgd=0.05, verbose=False)
+    assert m.history[-1][0] < 0.9 * m.history[0][0] and m.history[-1][1] > m.history[0][1] + 0.1, m.history
+    P = din_params(m)
+    sub = {k: v[:300] for k, v in d.items()}
+    want = O.din_model(sub["age"].astype(np.float64), sub["user_id"], sub["movies_seq"][:, :, None], sub["movie_id"], P["other_tables"],
+                       [P["seq_table"]], P["att_dense"], P["att_out"], P["bn"], P["tower"], P["out"])
+    got = npy(m(sub))
+    assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))

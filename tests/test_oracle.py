@@ -501,3 +501,83 @@ def test_ffm_train_step_gradients():
         assert abs(g - ((w - new[1]) / lr)[idx]) < 1e-7
     g = fd(w0, (0,), lambda a: (a, w, v))
     assert abs(g - ((w0 - new[0]) / lr)[0]) < 1e-7
+
+
+def _din_case(seed=31, B=6, T=5, K=4, all_masked_row=True):
+    rng = np.random.default_rng(seed)
+    v_seq, other_v, other_k, nd = 9, [5, 4], [3, 2], 2
+    seq = rng.normal(0, 0.6, (v_seq, K))
+    other_tables = [rng.normal(0, 0.6, (v, k)) for v, k in zip(other_v, other_k)]
+    hist = rng.integers(0, v_seq, (B, T))
+    hist[0, 3:] = 0
+    if all_masked_row:
+        hist[2] = 0
+    cand = rng.integers(1, v_seq, B)
+    cand[1] = hist[1, 0] if hist[1, 0] else 1                     # candidate row also in the history
+    other_ids = np.stack([rng.integers(0, v, B) for v in other_v], axis=1)
+    dense = rng.random((B, nd))
+    dims = [4 * K, 6, 5]
+    att = [(rng.normal(0, 0.5, (dims[i], dims[i + 1])), rng.normal(0, 0.1, dims[i + 1]), rng.normal(0.2, 0.2, (T, dims[i + 1])))
+           for i in range(2)]
+    att_out = (rng.normal(0, 0.5, (dims[-1], 1)), rng.normal(0, 0.1, 1))
+    n = 2 * K + sum(other_k) + nd
+    bn = (rng.normal(1, 0.2, n), rng.normal(0, 0.2, n), rng.normal(0, 0.1, n), rng.random(n) + 0.5)
+    td = [n, 7, 5]
+    tower = [(rng.normal(0, 0.5, (td[i], td[i + 1])), rng.normal(0, 0.1, td[i + 1]), rng.normal(0.2, 0.2, td[i + 1])) for i in range(2)]
+    out = (rng.normal(0, 0.5, (td[-1], 1)), rng.normal(0, 0.1, 1))
+    y = rng.integers(0, 2, B).astype(float)
+    return dict(dense_inputs=dense, other_ids=other_ids, hist_ids=hist, cand_ids=cand, other_tables=other_tables, seq_table=seq,
+                att_dense=att, att_out=att_out, bn=bn, tower=tower, out=out), y
+
+
+def test_din_train_step_gradients():
+    P, y = _din_case()
+    lr = 0.05
+    new, bce, _ = O.din_train_step(**P, y=y, lr=lr)
+    assert abs(O.din_loss(O.din_train_forward(**P)[0], y) - bce) < 1e-12
+    # the training-mode forward with the batch statistics put in as moving statistics equals the inference model
+    _, c = O.din_train_forward(**P)
+    inf = O.din_model(P["dense_inputs"], P["other_ids"], P["hist_ids"][:, :, None], P["cand_ids"][:, None], P["other_tables"],
+                      [P["seq_table"]], P["att_dense"], P["att_out"], (P["bn"][0], P["bn"][1], c["mu"], c["var"]), P["tower"], P["out"])
+    np.testing.assert_allclose(inf[:, 0], O.din_train_forward(**P)[0], rtol=0, atol=1e-12)
+    eps = 1e-6
+
+    def fd(get, put, idx):
+        vals = []
+        for sgn in (1, -1):
+            Q = dict(P)
+            a = get(P).copy()
+            a[idx] += sgn * eps
+            put(Q, a)
+            vals.append(O.din_loss(O.din_train_forward(**Q)[0], y))
+        return (vals[0] - vals[1]) / (2 * eps)
+
+    def check(get, put, got_new, idxs, what):
+        for idx in idxs:
+            g = fd(get, put, idx)
+            assert abs(g - ((get(P) - got_new) / lr)[idx]) < 2e-7, (what, idx, g, ((get(P) - got_new) / lr)[idx])
+    hist, cand = P["hist_ids"], P["cand_ids"]
+    check(lambda D: D["seq_table"], lambda D, a: D.__setitem__("seq_table", a), new["seq_table"],
+          [(int(hist[1, 0]), 1), (int(cand[3]), 2), (0, 0), (int(hist[4, 2]), 3)], "seq")
+    for i in range(2):
+        check(lambda D: D["other_tables"][i], lambda D, a: D.__setitem__("other_tables", [a if j == i else t for j, t in enumerate(P["other_tables"])]),
+              new["other_tables"][i], [(int(P["other_ids"][0, i]), 1)], "other")
+    for l in range(2):
+        for part, idxs in ((0, [(1, 2), (3, 0)]), (1, [(2,)]), (2, [(1, 3), (4, 0)])):
+            check(lambda D: D["att_dense"][l][part],
+                  lambda D, a: D.__setitem__("att_dense", [tuple(a if (j == l and q_ == part) else t[q_] for q_ in range(3)) for j, t in enumerate(P["att_dense"])]),
+                  new["att_dense"][l][part], idxs, "att %d %d" % (l, part))
+        for part, idxs in ((0, [(1, 2), (3, 0)]), (1, [(2,)]), (2, [(1,), (4,)])):
+            check(lambda D: D["tower"][l][part],
+                  lambda D, a: D.__setitem__("tower", [tuple(a if (j == l and q_ == part) else t[q_] for q_ in range(3)) for j, t in enumerate(P["tower"])]),
+                  new["tower"][l][part], idxs, "tower %d %d" % (l, part))
+    for part, idxs in ((0, [(2, 0)]), (1, [(0,)])):
+        check(lambda D: D["att_out"][part], lambda D, a: D.__setitem__("att_out", tuple(a if q_ == part else P["att_out"][q_] for q_ in range(2))),
+              new["att_out"][part], idxs, "att_out")
+        check(lambda D: D["out"][part], lambda D, a: D.__setitem__("out", tuple(a if q_ == part else P["out"][q_] for q_ in range(2))),
+              new["out"][part], idxs, "out")
+    for part in (0, 1):
+        check(lambda D: D["bn"][part], lambda D, a: D.__setitem__("bn", tuple(a if q_ == part else P["bn"][q_] for q_ in range(4))),
+              new["bn"][part], [(0,), (5,), (9,)], "bn")
+    np.testing.assert_allclose(new["bn"][2], 0.99 * P["bn"][2] + 0.01 * c["mu"], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(new["bn"][3], 0.99 * P["bn"][3] + 0.01 * c["var"], rtol=0, atol=1e-15)
