@@ -374,6 +374,45 @@ def train_leg(dev, timeit):
     ms_p = timeit(lambda: tp.train_on_batch(i, yy, 0.01), 50, 5)
     res["other_models_B32"] = {"dcn_L6_steps_per_s": 1e3 / ms_d, "pnn_both_steps_per_s": 1e3 / ms_p,
                                "note": "call by call (no graph replay), fp32 CUDA cores"}
+    # the rest of compile_fit's models at the same batch: Wide&Deep, DeepCrossing (3 residual units), NFM, AFM ('att'), FFM on the
+    # [B, 39] matrix, DIN (T = 10 as in DL/model/din.py:99, attention 80-40, tower 256-128-64)
+    from recommender_system_b200.model.criteo import AFM, FFM, NFM, WideDeep
+    from recommender_system_b200.model.deepCrossing import DeepCrossing
+    from recommender_system_b200.model.din import DIN
+    from recommender_system_b200.utils.compile_fit import (_AFMTrainer, _DeepCrossingTrainer, _DINTrainer, _FFMTrainer, _NFMTrainer,
+                                                           _WideDeepTrainer)
+    more = {}
+    set_seed(5)
+    mw = WideDeep(fc, [256, 128, 64], 1, "relu", embed_dim=8, precision="fp32", check_ids=False, device=dev)
+    mw.build(None)
+    tw = _WideDeepTrainer(mw, dropout=0.0)
+    more["widedeep"] = timeit(lambda: tw.train_on_batch(d, i, yy, 0.01), 50, 5)
+    mc = DeepCrossing(fc, 32, [256, 128], 3, embed_dim=8, precision="fp32", device=dev)
+    mc.build(None)
+    tc = _DeepCrossingTrainer(mc)
+    more["deepcrossing_3res"] = timeit(lambda: tc.train_on_batch(d, i, yy, 0.01), 50, 5)
+    mn = NFM(fc, [256, 128, 64], 1, "relu", 0.0, embed_dim=8, precision="fp32", device=dev)
+    mn.build(None)
+    mn.embed_layer = mn.emb_layers
+    tn = _NFMTrainer(mn, dropout=0.0)
+    more["nfm"] = timeit(lambda: tn.train_on_batch(d, i, yy, 0.01), 50, 5)
+    ma = AFM(fc, "att", device=dev)
+    ma.build(None)
+    ta = _AFMTrainer(ma)
+    more["afm_att"] = timeit(lambda: ta.train_on_batch(d, i, yy, 0.01), 50, 5)
+    mf = FFM(fc, 8, 1e-4, 1e-4, device=dev)
+    mf.build((None, 39))
+    tf_ = _FFMTrainer(mf)
+    xm = torch.cat([d, i.to(torch.float32)], dim=1).contiguous()
+    more["ffm_k8"] = timeit(lambda: tf_.train_on_batch(xm, yy, 0.01), 50, 5)
+    mi = DIN(synth.din_feature_columns(v_item=63002, v_user=192404, embed_dim=8), ["movies_seq"], (80, 40), (256, 128, 64),
+             "prelu", "prelu", 0.0, precision="fp32", check_ids=False, device=dev)
+    mi.build(None)
+    mi.att_layer.build_for(10, 8)
+    db = {k_: torch.from_numpy(v_).to(dev) for k_, v_ in synth.din_batch(32, 10, seed=6).items()}
+    ti = _DINTrainer(mi)
+    more["din_T10"] = timeit(lambda: ti.train_on_batch(db, yy, 0.01), 50, 5)
+    res["other_models_B32"].update({k_ + "_steps_per_s": 1e3 / v_ for k_, v_ in more.items()})
     return res
 
 
