@@ -41,13 +41,21 @@ tr_gemm_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float*
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;          // 16 x 16 threads, 2 x 2 outputs each
   const int m0 = blockIdx.y * TR_T, n0 = blockIdx.x * TR_T;
   float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-  for (int k0 = 0; k0 < K; k0 += TR_T) {
+  const bool a_kfast = ak == 1 && am != 1, b_kfast = bk == 1 && bn != 1;
+  // split-K (gridDim.z > 1, only launched with beta == 1): slice z of the k range, added to C with atomics
+  const int kchunk = gridDim.z > 1 ? ((K + (int)gridDim.z - 1) / (int)gridDim.z + TR_T - 1) / TR_T * TR_T : K;
+  const int kbeg = blockIdx.z * kchunk;
+  K = min(K, kbeg + kchunk);
+  for (int k0 = kbeg; k0 < K; k0 += TR_T) {
     for (int e = threadIdx.x; e < TR_T * TR_T; e += 256) {
-      const int r = e / TR_T, c = e % TR_T;                        // As[k][m], Bs[k][n]
-      const int m = m0 + c, k = k0 + r;
-      As[r][c] = (m < M && k < K) ? A[(int64_t)m * am + (int64_t)k * ak] : 0.f;
-      const int n = n0 + c;
-      Bs[r][c] = (n < N && k < K) ? Bm[(int64_t)k * bk + (int64_t)n * bn] : 0.f;
+      // As[k][m], Bs[k][n]; consecutive threads walk whichever index is contiguous in memory (whole 128-byte lines either way;
+      // the 33-float rows keep the transposed store free of bank conflicts)
+      const int ra = a_kfast ? e % TR_T : e / TR_T, ca = a_kfast ? e / TR_T : e % TR_T;
+      const int m = m0 + ca, ka = k0 + ra;
+      As[ra][ca] = (m < M && ka < K) ? A[(int64_t)m * am + (int64_t)ka * ak] : 0.f;
+      const int rb = b_kfast ? e % TR_T : e / TR_T, cb = b_kfast ? e / TR_T : e % TR_T;
+      const int n = n0 + cb, kb = k0 + rb;
+      Bs[rb][cb] = (n < N && kb < K) ? Bm[(int64_t)kb * bk + (int64_t)n * bn] : 0.f;
     }
     __syncthreads();
 #pragma unroll 8
@@ -65,7 +73,8 @@ tr_gemm_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float*
       const int m = m0 + ty + 16 * i, n = n0 + tx + 16 * j;
       if (m < M && n < N) {
         float* c = C + (int64_t)m * ldc + n;
-        *c = (beta == 0.f ? 0.f : beta * *c) + alpha * acc[i][j];
+        if (gridDim.z > 1) atomicAdd(c, alpha * acc[i][j]);
+        else *c = (beta == 0.f ? 0.f : beta * *c) + alpha * acc[i][j];
       }
     }
 }
@@ -195,7 +204,7 @@ __global__ void tr_relu_drop_bwd_kernel(float* __restrict__ g, const float* __re
 }
 
 // out[n] = beta * out[n] + alpha * sum_b w_b A[b, n] (w = NULL: ones).  Block = 32 columns x 32 row groups; every thread sums
-// its rows in order, the 32 partial sums of a column are added in a fixed order: deterministic for a given B
+// its rows in order, the 32 partial sums of a column are added in a fixed order: deterministic for a given B below 2048 rows
 __global__ void __launch_bounds__(1024)
 tr_colsum_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ w, int64_t B, int N,
                  int square, float* __restrict__ out, float alpha, float beta) {
@@ -203,8 +212,10 @@ tr_colsum_kernel(const float* __restrict__ A, int64_t lda, const float* __restri
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int n = blockIdx.x * 32 + cx;
   float s = 0.f;
+  // gridDim.y > 1 (launched only with beta == 1 and thousands of rows): row slices, added with atomics
+  const int64_t rows = (B + gridDim.y - 1) / gridDim.y, b0 = blockIdx.y * rows, b1 = b0 + rows < B ? b0 + rows : B;
   if (n < N)
-    for (int64_t b = ry; b < B; b += 32) {
+    for (int64_t b = b0 + ry; b < b1; b += 32) {
       const float a = A[b * lda + n];
       s = fmaf(w ? w[b] : 1.f, square ? a * a : a, s);
     }
@@ -214,7 +225,8 @@ tr_colsum_kernel(const float* __restrict__ A, int64_t lda, const float* __restri
     float t = 0.f;
 #pragma unroll
     for (int r = 0; r < 32; ++r) t += part[r][cx];
-    out[n] = (beta == 0.f ? 0.f : beta * out[n]) + alpha * t;
+    if (gridDim.y > 1) atomicAdd(out + n, alpha * t);
+    else out[n] = (beta == 0.f ? 0.f : beta * out[n]) + alpha * t;
   }
 }
 
@@ -895,9 +907,25 @@ inline int tr_grid(int64_t total, int block) {
   if (g > (int64_t)kNumSMs * 32) g = (int64_t)kNumSMs * 32;
   return g < 1 ? 1 : (int)g;
 }
+// column sums: beta == 1 over thousands of rows -> row slices added with atomics (one or a few CTAs would walk the whole batch)
+inline void tr_colsum(cudaStream_t st, int gx, const float* A, int64_t lda, const float* w, int64_t B, int N, int square, float* out,
+                      float alpha, float beta) {
+  dim3 grid(gx, 1);
+  if (beta == 1.f && B >= 2048) { const int64_t y = B / 512; grid.y = (unsigned)(y < 32 ? y : 32); }
+  tr_colsum_kernel<<<grid, 1024, 0, st>>>(A, lda, w, B, N, square, out, alpha, beta);
+}
 inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, const float* Bm, int64_t bk, int64_t bn, float* C,
                     int64_t ldc, int M, int N, int K, float alpha, float beta) {
   dim3 grid((N + TR_T - 1) / TR_T, (M + TR_T - 1) / TR_T);
+  // the weight-gradient products (W += -lr X^T G: a few tiles of output, the batch as the k range) would walk thousands of rows
+  // in a handful of CTAs: split the k range over enough CTAs for two per SM
+  const int tiles = (int)(grid.x * grid.y);
+  if (beta == 1.f && K >= 16 * TR_T && tiles < 2 * kNumSMs) {
+    int z = (2 * kNumSMs + tiles - 1) / tiles;
+    int zmax = K / (4 * TR_T);                                     // at least 4 k-tiles per slice,
+    if (zmax > 32) zmax = 32;                                      // at most 32 roundings at the weight's own magnitude
+    grid.z = z < zmax ? z : zmax;
+  }
   tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
 }
 // FM backward and update with d loss / d fm = gscale * dz:  w0, w1 = (1 - 2 lr reg_w) w1 - lr x^T dfm, and v with its -x^2 v part
@@ -908,9 +936,9 @@ static void tr_fm_update(cudaStream_t st, const float* x, int n, int64_t B, cons
   const int M = (int)B;
   const int nb = dx ? n : k_fm;                            // without dx only t = dfm * xv is formed: B x k_fm elements
   tr_fm_bwd_kernel<<<tr_grid(B * nb, 256), 256, 0, st>>>(x, nb, B, dz, fm_w1, fm_v, k_fm, xv, dx, t, gscale);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, fm_w0, -gscale * lr, 1.f);
-  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 0, fm_w1, -gscale * lr, 1.f - 2.f * lr * reg_w);
-  tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(x, n, dz, B, n, 1, s2, gscale, 0.f);   // s2[j] = sum_b dfm_b x_bj^2
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, fm_w0, -gscale * lr, 1.f);
+  tr_colsum(st, (n + 31) / 32, x, n, dz, B, n, 0, fm_w1, -gscale * lr, 1.f - 2.f * lr * reg_w);
+  tr_colsum(st, (n + 31) / 32, x, n, dz, B, n, 1, s2, gscale, 0.f);   // s2[j] = sum_b dfm_b x_bj^2
   tr_scale_rows_kernel<<<tr_grid((int64_t)n * k_fm, 256), 256, 0, st>>>(fm_v, n, k_fm, s2, 1.f - 2.f * lr * reg_v, lr);
   tr_gemm(st, x, 1, n, t, k_fm, 1, fm_v, k_fm, n, k_fm, M, -lr, 1.f);                      // v -= lr * x^T (dfm xv)
 }
@@ -969,7 +997,7 @@ static int tr_step(float* arena, const int64_t* row_off, int F, int k, const voi
     tr_gemm(st, dz, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 0.5f, 0.f);                 // [B,1] x [1,h]: B(k=0, n) = wo[n]
     tr_gemm(st, in, 1, in_dim, dz, 1, 1, wo, 1, in_dim, 1, M, -0.5f * lr, 1.f);           // w_out -= lr * h^T (dz / 2)
     if (h_layers[NH].bias)
-      tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
+      tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
     float* tmp = g; g = gn; gn = tmp;
   }
   for (int l = NH - 1; l >= 0; --l) {
@@ -983,7 +1011,7 @@ static int tr_step(float* arena, const int64_t* row_off, int F, int k, const voi
     tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);                           // W -= lr * in^T g
     if (h_layers[l].bias)
-      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- FM backward (old w1, v), then its updates
@@ -1136,7 +1164,7 @@ extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, i
     tr_gemm(st, gd, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 1.f, 0.f);
     tr_gemm(st, in, 1, in_dim, gd, 1, 1, wo, 1, in_dim, 1, M, -lr, 1.f);
     if (h_layers[NH].bias)
-      tr_colsum_kernel<<<1, 1024, 0, st>>>(gd, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
+      tr_colsum(st, 1, gd, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
     float* tmp = g; g = gn; gn = tmp;
   }
   for (int l = NH - 1; l >= 0; --l) {
@@ -1149,7 +1177,7 @@ extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, i
     tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
     if (h_layers[l].bias)
-      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- cross layers backward (old w_l, old fk), dx += its share; then the updates of w_l, b_l and of the final Dense
@@ -1157,12 +1185,12 @@ extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, i
   for (int l = 0; l < L; ++l) {
     const float* xin = l > 0 ? XL + (int64_t)(l - 1) * B * n : x;
     tr_gemm(st, xin, 1, n, C + (int64_t)l * B, 1, 1, const_cast<float*>(cw.w[l]), 1, n, 1, M, -lr, 1.f - 2.f * lr * reg_w);
-    tr_colsum_kernel<<<(n + 31) / 32, 1024, 0, st>>>(G + (int64_t)l * B * n, n, nullptr, B, n, 0, const_cast<float*>(cw.b[l]), -lr,
+    tr_colsum(st, (n + 31) / 32, G + (int64_t)l * B * n, n, nullptr, B, n, 0, const_cast<float*>(cw.b[l]), -lr,
                                                      1.f - 2.f * lr * reg_b);
   }
   tr_gemm(st, XL + (int64_t)(L - 1) * B * n, 1, n, dz, 1, 1, final_k, 1, n, 1, M, -lr, 1.f);   // fk[0:n] -= lr x_L^T dz
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(d, 1, dz, B, 1, 0, final_k + n, -lr, 1.f);              // fk[n]   -= lr sum_b d dz
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
+  tr_colsum(st, 1, d, 1, dz, B, 1, 0, final_k + n, -lr, 1.f);              // fk[n]   -= lr sum_b d dz
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
   // ---- embedding rows
   if (ids_kind == CTRHOT_IDS_I32)
     tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F * k, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, D, B, dx, n, lr, nullptr);
@@ -1250,7 +1278,7 @@ extern "C" int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, i
     tr_gemm(st, dz, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 1.f, 0.f);
     tr_gemm(st, in, 1, in_dim, dz, 1, 1, wo, 1, in_dim, 1, M, -lr, 1.f);
     if (h_layers[NH].bias)
-      tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
+      tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
     float* tmp = g; g = gn; gn = tmp;
   }
   for (int l = NH - 1; l >= 0; --l) {
@@ -1263,7 +1291,7 @@ extern "C" int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, i
     tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
     if (h_layers[l].bias)
-      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- product layers backward into dx's flat columns (old W), then W, then the embedding rows
@@ -1352,7 +1380,7 @@ extern "C" int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_o
     tr_gemm(st, dz, 1, 1, wo, 0, 1, gn, in_dim, M, in_dim, 1, 0.5f, 0.f);
     tr_gemm(st, in, 1, in_dim, dz, 1, 1, wo, 1, in_dim, 1, M, -0.5f * lr, 1.f);
     if (h_layers[NH].bias)
-      tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
+      tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, const_cast<float*>(h_layers[NH].bias), -0.5f * lr, 1.f);
     float* tmp = g; g = gn; gn = tmp;
   }
   for (int l = NH - 1; l >= 0; --l) {
@@ -1365,16 +1393,16 @@ extern "C" int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_o
     tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
     if (h_layers[l].bias)
-      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- wide side: w <- (1 - 2 lr reg) w - lr x_w^T (dz / 2) over [dense | dense | one-hot], w0
   tr_scale_kernel<<<tr_grid(n_wide, 256), 256, 0, st>>>(wide_w, n_wide, 1.f - 2.f * lr * reg_w);
   if (D > 0) {
-    tr_colsum_kernel<<<(D + 31) / 32, 1024, 0, st>>>(dense, dense_ld, dz, B, D, 0, wide_w, -0.5f * lr, 1.f);
-    tr_colsum_kernel<<<(D + 31) / 32, 1024, 0, st>>>(dense, dense_ld, dz, B, D, 0, wide_w + D, -0.5f * lr, 1.f);
+    tr_colsum(st, (D + 31) / 32, dense, dense_ld, dz, B, D, 0, wide_w, -0.5f * lr, 1.f);
+    tr_colsum(st, (D + 31) / 32, dense, dense_ld, dz, B, D, 0, wide_w + D, -0.5f * lr, 1.f);
   }
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, wide_w0, -0.5f * lr, 1.f);
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, wide_w0, -0.5f * lr, 1.f);
   if (ids_kind == CTRHOT_IDS_I32) {
     tr_wide_onehot_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * F, 256), 256, 0, st>>>(ids, ids_ld, F, col_off, dz, 0.5f * lr, B, wide_w);
     tr_embed_sgd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * n, 256), 256, 0, st>>>(arena, row_off, F, k, ids, ids_ld, 0, B, dx, n, lr, nullptr);
@@ -1461,7 +1489,7 @@ extern "C" int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* r
   // ---- backward: g = dL/dx_R = dz fk^T (old fk), then the final Dense
   tr_gemm(st, dz, 1, 1, final_k, 0, 1, g, n, M, n, 1, 1.f, 0.f);
   tr_gemm(st, xR, 1, n, dz, 1, 1, final_k, 1, n, 1, M, -lr, 1.f);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
   for (int r = n_res - 1; r >= 0; --r) {
     tr_mask_copy_kernel<<<tr_grid(Bn, 256), 256, 0, st>>>(g, xs + (int64_t)(r + 1) * Bn, Bn, gm);   // through the unit's relu
     const float* gcur = gm;                                  // gradient at the current layer's pre-activation
@@ -1478,7 +1506,7 @@ extern "C" int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* r
       float* dst = l > 0 ? (gcur == ga ? gb : ga) : g;       // the unit's input gradient lands in g, then the skip path is added
       tr_gemm(st, gcur, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
       tr_gemm(st, hin, 1, Kd, gcur, N, 1, W, N, Kd, N, M, -lr, 1.f);
-      tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(gcur, N, nullptr, B, N, 0, const_cast<float*>(d.bias), -lr, 1.f);
+      tr_colsum(st, (N + 31) / 32, gcur, N, nullptr, B, N, 0, const_cast<float*>(d.bias), -lr, 1.f);
       gcur = dst;
     }
     tr_add_kernel<<<tr_grid(Bn, 256), 256, 0, st>>>(g, gm, Bn);
@@ -1566,14 +1594,14 @@ extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, i
   // ---- backward: final Dense(1), the DNNLayer's output layer, its hidden layers
   tr_gemm(st, dz, 1, 1, final_k, 0, 1, gd, od, M, od, 1, 1.f, 0.f);                         // gd = dz fk^T (old fk)
   tr_gemm(st, d, 1, od, dz, 1, 1, final_k, 1, od, 1, M, -lr, 1.f);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, final_b, -lr, 1.f);
   float* g = ws + w.g0;
   float* gn = ws + w.g1;
   {
     float* wo = const_cast<float*>(h_layers[NH].weight);
     tr_gemm(st, gd, od, 1, wo, 1, od, g, in_dim, M, in_dim, od, 1.f, 0.f);                  // [B, od] x [od, h]: B(k, n) = wo[n * od + k]
     tr_gemm(st, in, 1, in_dim, gd, od, 1, wo, od, in_dim, od, M, -lr, 1.f);
-    tr_colsum_kernel<<<(od + 31) / 32, 1024, 0, st>>>(gd, od, nullptr, B, od, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
+    tr_colsum(st, (od + 31) / 32, gd, od, nullptr, B, od, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
   }
   for (int l = NH - 1; l >= 0; --l) {
     const int N = h_layers[l].out_dim, Kd = h_layers[l].in_dim;
@@ -1584,7 +1612,7 @@ extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, i
     float* dst = l > 0 ? gn : gy;
     tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
-    tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- BatchNormalization (gamma, beta move), Bi-Interaction, embedding rows
@@ -1632,7 +1660,7 @@ extern "C" int ctrhot_afm_train_step_f32(float* arena, const int64_t* row_off, i
   // gx = dz w^T (old w; the mean's 1 / P folded in), then w, b
   tr_gemm(st, dz, 1, 1, out_k, 0, 1, gx, k, M, k, 1, mode == 0 ? 1.f / (float)P : 1.f, 0.f);
   tr_gemm(st, x, 1, k, dz, 1, 1, out_k, 1, k, 1, M, -lr, 1.f);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, out_b, -lr, 1.f);
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, out_b, -lr, 1.f);
   if (mode == 2) {
     if (i32) tr_afm_max_bwd_kernel<CTRHOT_IDS_I32><<<tr_grid(B * k, 128), 128, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, gx, amax, dE);
     else tr_afm_max_bwd_kernel<CTRHOT_IDS_F32><<<tr_grid(B * k, 128), 128, 0, st>>>(arena, row_off, F, k, ids, ids_ld, B, gx, amax, dE);
@@ -1676,7 +1704,7 @@ extern "C" int ctrhot_ffm_train_step_f32(const float* dense, int64_t dense_ld, i
   // l2(reg)(w) adds 2 reg w to EVERY entry's gradient (FFMLayer.build, interaction.py:131-138): decay first, then the batch's rows
   if (reg_w != 0.f) tr_scale_kernel<<<tr_grid(n_features, 256), 256, 0, st>>>(w, n_features, 1.f - 2.f * lr * reg_w);
   if (reg_v != 0.f) tr_scale_kernel<<<tr_grid(n_features * len, 256), 256, 0, st>>>(v, n_features * len, 1.f - 2.f * lr * reg_v);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, w0, -lr, 1.f);
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, w0, -lr, 1.f);
   const int g2 = tr_grid(B * (D + F) * 32, 128);
   if (i32) tr_ffm_sgd_kernel<CTRHOT_IDS_I32><<<g2, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, dz, lr, len, k, ff, S, w, v);
   else tr_ffm_sgd_kernel<CTRHOT_IDS_F32><<<g2, 128, 0, st>>>(dense, dense_ld, D, ids, ids_ld, F, col_off, B, dz, lr, len, k, ff, S, w, v);
@@ -1798,7 +1826,7 @@ extern "C" int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int
   float* gn = ws + w.g1;
   tr_gemm(st, dz, 1, 1, out_k, 0, 1, g, ht, M, ht, 1, 1.f, 0.f);                            // g = dz out_k^T (old out_k)
   tr_gemm(st, in, 1, ht, dz, 1, 1, out_k, 1, ht, 1, M, -lr, 1.f);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(dz, 1, nullptr, B, 1, 0, out_b, -lr, 1.f);
+  tr_colsum(st, 1, dz, 1, nullptr, B, 1, 0, out_b, -lr, 1.f);
   for (int l = n_tower - 1; l >= 0; --l) {
     const int N = tower_layers[l].out_dim, Kd = tower_layers[l].in_dim;
     const float* hin = l > 0 ? ws + w.tx[l - 1] : yb;
@@ -1806,7 +1834,7 @@ extern "C" int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int
     tr_prelu_bwd_kernel<<<(N + 127) / 128, 128, 0, st>>>(g, ws + w.tpre[l], const_cast<float*>(tower_layers[l].act_param), B, N, 1, lr);
     tr_gemm(st, g, N, 1, W, 1, N, gn, Kd, M, Kd, N, 1.f, 0.f);                              // through the old W
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
-    tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, B, N, 0, const_cast<float*>(tower_layers[l].bias), -lr, 1.f);
+    tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(tower_layers[l].bias), -lr, 1.f);
     float* tmp = g; g = gn; gn = tmp;
   }
   tr_bn_bwd_kernel<<<n, 256, 0, st>>>(g, xhat, n, B, bn_gamma, bn_beta, rstd, lr, gx);
@@ -1815,7 +1843,7 @@ extern "C" int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int
   const float* xl = ws + w.ax[n_att - 1];
   tr_gemm(st, gs, 1, 1, att_out_k, 0, 1, g, ha, BT, ha, 1, 1.f, 0.f);                       // g = gs w3^T (old w3)
   tr_gemm(st, xl, 1, ha, gs, 1, 1, att_out_k, 1, ha, 1, BT, -lr, 1.f);
-  tr_colsum_kernel<<<1, 1024, 0, st>>>(gs, 1, nullptr, BT, 1, 0, att_out_b, -lr, 1.f);
+  tr_colsum(st, 1, gs, 1, nullptr, BT, 1, 0, att_out_b, -lr, 1.f);
   for (int l = n_att - 1; l >= 0; --l) {
     const int N = att_layers[l].out_dim, Kd = att_layers[l].in_dim;
     const float* hin = l > 0 ? ws + w.ax[l - 1] : A;
@@ -1823,7 +1851,7 @@ extern "C" int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int
     tr_prelu_bwd_kernel<<<(T * N + 127) / 128, 128, 0, st>>>(g, ws + w.apre[l], const_cast<float*>(att_layers[l].act_param), BT, N, T, lr);
     tr_gemm(st, g, N, 1, W, 1, N, gn, Kd, BT, Kd, N, 1.f, 0.f);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, BT, -lr, 1.f);
-    tr_colsum_kernel<<<(N + 31) / 32, 1024, 0, st>>>(g, N, nullptr, BT, N, 0, const_cast<float*>(att_layers[l].bias), -lr, 1.f);
+    tr_colsum(st, (N + 31) / 32, g, N, nullptr, BT, N, 0, const_cast<float*>(att_layers[l].bias), -lr, 1.f);
     float* tmp = g; g = gn; gn = tmp;
   }
   // ---- the concat [q, k, q - k, q * k], then every table (all reads of the tables happened in the forward pass)
