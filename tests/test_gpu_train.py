@@ -788,3 +788,37 @@ def test_din_compile_fit_learns_and_serves(lib):
                        [P["seq_table"]], P["att_dense"], P["att_out"], P["bn"], P["tower"], P["out"])
     got = npy(m(sub))
     assert np.max(np.abs(got - want)) <= 2e-5, np.max(np.abs(got - want))
+
+
+# ------------------------------------------------------------------ the staged graph step (trainers without dropout)
+def test_staged_graph_equals_call_by_call(lib):
+    """compile_fit(use_graph=True) replays one captured step over staging buffers for the trainers whose step has no dropout;
+    it must leave the same weights and history as the call-by-call loop (the atomics' order aside: 1e-6)."""
+    from recommender_system_b200.utils import synth
+    vocab = [30, 7, 120, 50] + [9] * 22
+    rng = np.random.default_rng(3)
+    N = 32 * 9 + 5
+    ids = np.stack([rng.integers(0, v, N) for v in vocab], axis=1)
+    X = np.concatenate([rng.random((N, 13)), ids], axis=1).astype(np.float32)
+    y = (ids[:, 0] < 15).astype(np.float32)
+    pairs = []
+    for g in (True, False):
+        m = make_afm(vocab, "att", seed=3)
+        compile_fit(m, X, y, batch_size=32, epochs=3, sgd=0.5, verbose=False, use_graph=g)
+        pairs.append((m.history, {n: npy(w) for n, w in m.named_weights().items()}))
+    for (ha, hb) in zip(pairs[0][0], pairs[1][0]):
+        assert abs(ha[0] - hb[0]) <= 1e-6 and ha[1] == hb[1]
+    for n in pairs[0][1]:
+        assert np.max(np.abs(pairs[0][1][n] - pairs[1][1][n])) <= 1e-6, n
+    # DIN on its dict input
+    v_item, v_user, T, K = 40, 9, 8, 8
+    d = synth.din_batch(N, T, v_item=v_item, v_user=v_user, seed=5)
+    pairs = []
+    for g in (True, False):
+        m = make_din(v_item, v_user, K, T, (16, 8), (32, 16), seed=2)
+        compile_fit(m, dict(d), y, batch_size=32, epochs=3, sgd=0.05, verbose=False, use_graph=g)
+        pairs.append((m.history, {n: npy(w) for n, w in m.named_weights().items()}))
+    for (ha, hb) in zip(pairs[0][0], pairs[1][0]):
+        assert abs(ha[0] - hb[0]) <= 1e-6 and ha[1] == hb[1]
+    for n in pairs[0][1]:
+        assert np.max(np.abs(pairs[0][1][n] - pairs[1][1][n])) <= 1e-6, n
