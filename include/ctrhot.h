@@ -625,7 +625,10 @@ int ctrhot_augru_f32(const float* x, int64_t x_ld_b, const float* att, int64_t a
  * step): same distribution as keras' Dropout, not TensorFlow's random stream.  loss_out (DEVICE, 2 floats) = mean BCE of the
  * batch BEFORE the update (without the regularisers, which is what keras prints minus its regularisation term) and the
  * number of samples on the right side of 0.5.  ids [B, F] local row numbers; dense [B, D]; y [B] in {0, 1}.
- * fp32 CUDA cores throughout (the reference trains at batch 32).  Bad ids: the row contributes zeros, *err_flag = 1. */
+ * fp32 CUDA cores throughout (the reference trains at batch 32).  Bad ids: the row contributes zeros, *err_flag = 1.
+ * Summation order (all ctrhot_*_train_step_f32): embedding rows take their samples' gradients through atomic adds; from 512
+ * rows per batch the weight gradients, and from 2 048 the bias gradients, are summed over up to 32 row slices the same way --
+ * results repeat to fp32 round-off (~1e-7 of a weight), not bit for bit. */
 int64_t ctrhot_deepfm_train_workspace_bytes(int64_t B, int n, int k_fm, const ctrhot_dense_desc* h_layers,
                                             int n_layers);
 int ctrhot_deepfm_train_step_f32(float* arena, const int64_t* row_off, int F, int k, const void* ids, int ids_kind,
