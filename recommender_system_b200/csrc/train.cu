@@ -79,13 +79,30 @@ tr_gemm_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float*
     }
 }
 
+__device__ __forceinline__ float tr_uniform(uint64_t seed, uint32_t layer, uint64_t idx) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (idx + 1) + ((uint64_t)layer << 56);     // splitmix64
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+// optional epilogue of the small-M product: h = dropout(relu(acc + bias)), the Dense layer of a tower in one launch
+struct TrEpi {
+  const float* bias;
+  const TrCtl* ctl;
+  uint64_t seed;
+  float rate;
+  uint32_t layer;
+  int relu, on;
+};
 // The reference's batch of 32: M <= 32 rows.  The 32 x 32 kernel above walks K in 32-wide steps, each a global load, two barriers
 // and 32 FMA deep -- ~1.2 us per step, 7 steps for the 221-wide first layer.  Here the 8 warps of a CTA take one eighth of the k
 // range each (A slice staged in shared memory by the warp itself, B read straight from global: every load independent), then the
 // eight partial tiles are added through shared memory in a fixed order.  One pass instead of K / 32 dependent ones.
 __global__ void __launch_bounds__(256)
 tr_gemm_m32_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float* __restrict__ Bm, int64_t bk, int64_t bn,
-                   float* __restrict__ C, int64_t ldc, int M, int N, int K, float alpha, float beta) {
+                   float* __restrict__ C, int64_t ldc, int M, int N, int K, float alpha, float beta, TrEpi epi) {
   __shared__ float sm[8][32][33];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int n = blockIdx.x * 32 + lane;
@@ -126,7 +143,16 @@ tr_gemm_m32_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const fl
     for (int q = 0; q < 8; ++q) t += sm[q][m][nn];
     if (m < M && nc < N) {
       float* c = C + (int64_t)m * ldc + nc;
-      *c = (beta == 0.f ? 0.f : beta * *c) + alpha * t;
+      t = (beta == 0.f ? 0.f : beta * *c) + alpha * t;
+      if (epi.on) {                                               // same arithmetic and mask index as tr_bias_relu_drop_kernel
+        t += epi.bias ? epi.bias[nc] : 0.f;
+        if (epi.relu) t = fmaxf(t, 0.f);
+        if (epi.rate > 0.f) {
+          const uint64_t seed = epi.seed + (epi.ctl ? epi.ctl->step : 0ull);
+          t = (tr_uniform(seed, epi.layer, (uint64_t)m * N + nc) >= epi.rate) ? t * (1.f / (1.f - epi.rate)) : 0.f;
+        }
+      }
+      *c = t;
     }
   }
 }
@@ -199,14 +225,6 @@ tr_gemm64_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const floa
         else *c = (beta == 0.f ? 0.f : beta * *c) + alpha * acc[i][j];
       }
     }
-}
-
-__device__ __forceinline__ float tr_uniform(uint64_t seed, uint32_t layer, uint64_t idx) {
-  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (idx + 1) + ((uint64_t)layer << 56);     // splitmix64
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  z ^= z >> 31;
-  return (float)(z >> 40) * (1.0f / 16777216.0f);
 }
 
 // x[b] = [dense_b (D) | rows of the F fields (F * k)]   (reference column order)
@@ -1051,11 +1069,23 @@ inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, con
     grid.z = z < zmax ? z : zmax;
   }
   if (M <= 32 && K >= 64 && grid.z == 1) {
-    tr_gemm_m32_kernel<<<(N + 31) / 32, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
+    tr_gemm_m32_kernel<<<(N + 31) / 32, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, TrEpi{});
     return;
   }
   if (big) tr_gemm64_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
   else tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
+}
+// One Dense layer of a tower, forward: h = dropout(relu(in W + bias)).  At the reference's batch (M <= 32) the bias / ReLU / dropout
+// ride in the product's epilogue -- one launch instead of two on a chain where every link costs 3-5 us.
+inline void tr_dense_fwd(cudaStream_t st, const float* in, int in_dim, const float* W, const float* bias, int N, float* h, int M,
+                         int relu, float rate, uint64_t seed, uint32_t layer, const TrCtl* ctl) {
+  if (M <= 32 && in_dim >= 64) {
+    TrEpi e{bias, ctl, seed, rate, layer, relu, 1};
+    tr_gemm_m32_kernel<<<(N + 31) / 32, 256, 0, st>>>(in, in_dim, 1, W, N, 1, h, N, M, N, in_dim, 1.f, 0.f, e);
+    return;
+  }
+  tr_gemm(st, in, in_dim, 1, W, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
+  tr_bias_relu_drop_kernel<<<tr_grid((int64_t)M * N, 256), 256, 0, st>>>(h, bias, N, M, relu, rate, seed, layer, ctl);
 }
 // FM backward and update with d loss / d fm = gscale * dz:  w0, w1 = (1 - 2 lr reg_w) w1 - lr x^T dfm, and v with its -x^2 v part
 // folded into a per-row scale (old w1 / v are used for dx, which is formed first; dx may be NULL)
@@ -1111,8 +1141,7 @@ static int tr_step(float* arena, const int64_t* row_off, int F, int k, const voi
   for (int l = 0; l < NH; ++l) {
     float* h = ws + w.h[l];
     const int N = h_layers[l].out_dim;
-    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
-    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, ctl);
+    tr_dense_fwd(st, in, in_dim, h_layers[l].weight, h_layers[l].bias, N, h, M, 1, dropout, seed, (uint32_t)l, ctl);
     in = h; in_dim = N;
   }
   tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, dnn, 1, M, 1, in_dim, 1.f, 0.f);
@@ -1273,8 +1302,7 @@ extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, i
   for (int l = 0; l < NH; ++l) {
     float* h = ws + w.h[l];
     const int N = h_layers[l].out_dim;
-    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
-    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    tr_dense_fwd(st, in, in_dim, h_layers[l].weight, h_layers[l].bias, N, h, M, 1, dropout, seed, (uint32_t)l, nullptr);
     in = h; in_dim = N;
   }
   tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, d, 1, M, 1, in_dim, 1.f, 0.f);
@@ -1393,8 +1421,7 @@ extern "C" int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, i
   for (int l = 0; l < NH; ++l) {
     float* h = ws + w.h[l];
     const int N = h_layers[l].out_dim;
-    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
-    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    tr_dense_fwd(st, in, in_dim, h_layers[l].weight, h_layers[l].bias, N, h, M, 1, dropout, seed, (uint32_t)l, nullptr);
     in = h; in_dim = N;
   }
   tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, z, 1, M, 1, in_dim, 1.f, 0.f);
@@ -1495,8 +1522,7 @@ extern "C" int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_o
   for (int l = 0; l < NH; ++l) {
     float* h = ws + w.h[l];
     const int N = h_layers[l].out_dim;
-    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
-    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    tr_dense_fwd(st, in, in_dim, h_layers[l].weight, h_layers[l].bias, N, h, M, 1, dropout, seed, (uint32_t)l, nullptr);
     in = h; in_dim = N;
   }
   tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, 1, 1, dnn, 1, M, 1, in_dim, 1.f, 0.f);
@@ -1606,8 +1632,7 @@ extern "C" int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* r
     for (int l = 0; l < per_res; ++l) {
       const ctrhot_dense_desc& d = h_layers[r * per_res + l];
       float* h = ws + w.act[r][l];
-      tr_gemm(st, in, in_dim, 1, d.weight, d.out_dim, 1, h, d.out_dim, M, d.out_dim, in_dim, 1.f, 0.f);
-      tr_bias_relu_drop_kernel<<<tr_grid(B * d.out_dim, 256), 256, 0, st>>>(h, d.bias, d.out_dim, B, l < per_res - 1, 0.f, 0, 0, nullptr);
+      tr_dense_fwd(st, in, in_dim, d.weight, d.bias, d.out_dim, h, M, l < per_res - 1, 0.f, 0, 0, nullptr);
       in = h; in_dim = d.out_dim;
     }
     tr_residual_relu_kernel<<<tr_grid(Bn, 256), 256, 0, st>>>(xs + (int64_t)r * Bn, in, Bn, xs + (int64_t)(r + 1) * Bn);
@@ -1712,12 +1737,10 @@ extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, i
   for (int l = 0; l < NH; ++l) {
     float* h = ws + w.h[l];
     const int N = h_layers[l].out_dim;
-    tr_gemm(st, in, in_dim, 1, h_layers[l].weight, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
-    tr_bias_relu_drop_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(h, h_layers[l].bias, N, B, 1, dropout, seed, (uint32_t)l, nullptr);
+    tr_dense_fwd(st, in, in_dim, h_layers[l].weight, h_layers[l].bias, N, h, M, 1, dropout, seed, (uint32_t)l, nullptr);
     in = h; in_dim = N;
   }
-  tr_gemm(st, in, in_dim, 1, h_layers[NH].weight, od, 1, d, od, M, od, in_dim, 1.f, 0.f);
-  tr_bias_relu_drop_kernel<<<tr_grid(B * od, 256), 256, 0, st>>>(d, h_layers[NH].bias, od, B, 0, 0.f, 0, 0, nullptr);
+  tr_dense_fwd(st, in, in_dim, h_layers[NH].weight, h_layers[NH].bias, od, d, M, 0, 0.f, 0, 0, nullptr);
   tr_gemm(st, d, od, 1, final_k, 1, 1, z, 1, M, 1, od, 1.f, 0.f);
   tr_loss_kernel<<<1, 256, 0, st>>>(z, nullptr, final_b, y, B, dz, loss_out, nullptr, 1.0f);
   // ---- backward: final Dense(1), the DNNLayer's output layer, its hidden layers
