@@ -144,7 +144,15 @@ tr_gemm_m32_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const fl
     if (m < M && nc < N) {
       float* c = C + (int64_t)m * ldc + nc;
       t = (beta == 0.f ? 0.f : beta * *c) + alpha * t;
-      if (epi.on) {                                               // same arithmetic and mask index as tr_bias_relu_drop_kernel
+      if (epi.on == 2) {                                          // backward: t *= d dropout(relu(.)) at h = epi.bias[m, nc]
+        float mk = 1.f;
+        if (epi.rate > 0.f) {
+          const uint64_t seed = epi.seed + (epi.ctl ? epi.ctl->step : 0ull);
+          mk = (tr_uniform(seed, epi.layer, (uint64_t)m * N + nc) >= epi.rate) ? 1.f / (1.f - epi.rate) : 0.f;
+        }
+        if (epi.relu && !(epi.bias[(int64_t)m * N + nc] > 0.f)) mk = 0.f;
+        t *= mk;
+      } else if (epi.on) {                                        // same arithmetic and mask index as tr_bias_relu_drop_kernel
         t += epi.bias ? epi.bias[nc] : 0.f;
         if (epi.relu) t = fmaxf(t, 0.f);
         if (epi.rate > 0.f) {
@@ -1087,6 +1095,19 @@ inline void tr_dense_fwd(cudaStream_t st, const float* in, int in_dim, const flo
   tr_gemm(st, in, in_dim, 1, W, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
   tr_bias_relu_drop_kernel<<<tr_grid((int64_t)M * N, 256), 256, 0, st>>>(h, bias, N, M, relu, rate, seed, layer, ctl);
 }
+inline bool tr_m32_ok(int M, int K) { return M <= 32 && K >= 64; }
+// Gradient w.r.t. a Dense layer's input through the OLD weights, dst [M, Kd] = g [M, N] W^T; when hprev (the activations of the
+// layer below, [M, Kd]) is given and the small-M product runs, that layer's ReLU / dropout derivative is applied in the epilogue
+// (what tr_relu_drop_bwd_kernel would do as the next launch) -- the loops test the same condition before launching that kernel.
+inline void tr_dense_bwd_input(cudaStream_t st, const float* g, int N, const float* W, float* dst, int Kd, int M, const float* hprev,
+                               float rate, uint64_t seed, uint32_t layer, const TrCtl* ctl) {
+  if (hprev && tr_m32_ok(M, N)) {
+    TrEpi e{hprev, ctl, seed, rate, layer, 1, 2};
+    tr_gemm_m32_kernel<<<(Kd + 31) / 32, 256, 0, st>>>(g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f, e);
+    return;
+  }
+  tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+}
 // FM backward and update with d loss / d fm = gscale * dz:  w0, w1 = (1 - 2 lr reg_w) w1 - lr x^T dfm, and v with its -x^2 v part
 // folded into a per-row scale (old w1 / v are used for dx, which is formed first; dx may be NULL)
 static void tr_fm_update(cudaStream_t st, const float* x, int n, int64_t B, const float* dz, float gscale, float* fm_w0,
@@ -1163,10 +1184,11 @@ static int tr_step(float* arena, const int64_t* row_off, int F, int k, const voi
     const float* h = ws + w.h[l];
     const float* hin = l > 0 ? ws + w.h[l - 1] : x;
     float* W = const_cast<float*>(h_layers[l].weight);
-    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, ctl);
+    if (!(l < NH - 1 && tr_m32_ok(M, h_layers[l + 1].out_dim)))   // (else the product above applied this mask in its epilogue)
+      tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, ctl);
     // gradient w.r.t. this layer's input with the OLD weights: [B,N] x [N,Kd]  (B(k, n) = W[n * N + k])
     float* dst = l > 0 ? gn : dx;
-    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), ctl);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);                           // W -= lr * in^T g
     if (h_layers[l].bias)
       tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
@@ -1329,9 +1351,10 @@ extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, i
     const float* h = ws + w.h[l];
     const float* hin = l > 0 ? ws + w.h[l - 1] : x;
     float* W = const_cast<float*>(h_layers[l].weight);
-    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    if (!(l < NH - 1 && tr_m32_ok(M, h_layers[l + 1].out_dim)))   // (else the product above applied this mask in its epilogue)
+      tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : dx;
-    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
     if (h_layers[l].bias)
       tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
@@ -1442,9 +1465,10 @@ extern "C" int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, i
     const float* h = ws + w.h[l];
     const float* hin = l > 0 ? ws + w.h[l - 1] : x;
     float* W = const_cast<float*>(h_layers[l].weight);
-    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    if (!(l < NH - 1 && tr_m32_ok(M, h_layers[l + 1].out_dim)))   // (else the product above applied this mask in its epilogue)
+      tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : dx;
-    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
     if (h_layers[l].bias)
       tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
@@ -1543,9 +1567,10 @@ extern "C" int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_o
     const float* h = ws + w.h[l];
     const float* hin = l > 0 ? ws + w.h[l - 1] : x;
     float* W = const_cast<float*>(h_layers[l].weight);
-    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    if (!(l < NH - 1 && tr_m32_ok(M, h_layers[l + 1].out_dim)))   // (else the product above applied this mask in its epilogue)
+      tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : dx;
-    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
     if (h_layers[l].bias)
       tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
@@ -1760,9 +1785,10 @@ extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, i
     const float* h = ws + w.h[l];
     const float* hin = l > 0 ? ws + w.h[l - 1] : yb;
     float* W = const_cast<float*>(h_layers[l].weight);
-    tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
+    if (!(l < NH - 1 && tr_m32_ok(M, h_layers[l + 1].out_dim)))   // (else the product above applied this mask in its epilogue)
+      tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : gy;
-    tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
+    tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
     tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
     tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
