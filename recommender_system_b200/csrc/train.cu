@@ -36,11 +36,13 @@ __global__ void tr_advance_kernel(TrCtl* ctl, long long B) { ctl->step += 1; ctl
 // C[m, n] = beta * C[m, n] + alpha * sum_k A(m, k) B(k, n);  A(m, k) = A[m * am + k * ak], B(k, n) = B[k * bk + n * bn]
 __global__ void __launch_bounds__(256)
 tr_gemm_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float* __restrict__ Bm, int64_t bk, int64_t bn,
-               float* __restrict__ C, int64_t ldc, int M, int N, int K, float alpha, float beta) {
+               float* __restrict__ C, int64_t ldc, int M, int N, int K, float alpha, float beta,
+               float* __restrict__ csum = nullptr, float csum_alpha = 0.f) {
   __shared__ float As[TR_T][TR_T + 1], Bs[TR_T][TR_T + 1];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;          // 16 x 16 threads, 2 x 2 outputs each
   const int m0 = blockIdx.y * TR_T, n0 = blockIdx.x * TR_T;
   float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+  float cs0 = 0.f, cs1 = 0.f;
   const bool a_kfast = ak == 1 && am != 1, b_kfast = bk == 1 && bn != 1;
   // split-K (gridDim.z > 1, only launched with beta == 1): slice z of the k range, added to C with atomics
   const int kchunk = gridDim.z > 1 ? ((K + (int)gridDim.z - 1) / (int)gridDim.z + TR_T - 1) / TR_T * TR_T : K;
@@ -63,8 +65,19 @@ tr_gemm_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float*
       const float a0 = As[k][ty], a1 = As[k][ty + 16], b0 = Bs[k][tx], b1 = Bs[k][tx + 16];
       acc[0][0] = fmaf(a0, b0, acc[0][0]); acc[0][1] = fmaf(a0, b1, acc[0][1]);
       acc[1][0] = fmaf(a1, b0, acc[1][0]); acc[1][1] = fmaf(a1, b1, acc[1][1]);
+      cs0 += b0; cs1 += b1;
     }
     __syncthreads();
+  }
+  // csum[n] += csum_alpha * sum_k B(k, n): the bias gradient of a Dense layer rides in its weight-gradient product (B = g, k = the
+  // batch) -- the first row of CTAs has the tiles of g in shared memory anyway
+  if (csum && blockIdx.y == 0 && ty == 0) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int n = n0 + tx + 16 * j;
+      const float v = csum_alpha * (j ? cs1 : cs0);
+      if (n < N) { if (gridDim.z > 1) atomicAdd(csum + n, v); else csum[n] += v; }
+    }
   }
 #pragma unroll
   for (int i = 0; i < 2; ++i)
@@ -1063,7 +1076,7 @@ inline void tr_colsum(cudaStream_t st, int gx, const float* A, int64_t lda, cons
   tr_colsum_kernel<<<grid, 1024, 0, st>>>(A, lda, w, B, N, square, out, alpha, beta);
 }
 inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, const float* Bm, int64_t bk, int64_t bn, float* C,
-                    int64_t ldc, int M, int N, int K, float alpha, float beta) {
+                    int64_t ldc, int M, int N, int K, float alpha, float beta, float* csum = nullptr, float csum_alpha = 0.f) {
   const bool big = M >= 128 && N >= 64 && K >= 64;
   const int T = big ? TR_T64 : TR_T;
   dim3 grid((N + T - 1) / T, (M + T - 1) / T);
@@ -1076,12 +1089,18 @@ inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, con
     if (zmax > 32) zmax = 32;                                      // at most 32 roundings at the weight's own magnitude
     grid.z = z < zmax ? z : zmax;
   }
+  // csum (B must be [K, N] row-major: bn == 1): fused in the 32 x 32 kernel, a separate column sum beside the other two
   if (M <= 32 && K >= 64 && grid.z == 1) {
     tr_gemm_m32_kernel<<<(N + 31) / 32, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, TrEpi{});
+    if (csum) tr_colsum(st, (N + 31) / 32, Bm, bk, nullptr, K, N, 0, csum, csum_alpha, 1.f);
     return;
   }
-  if (big) tr_gemm64_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
-  else tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
+  if (big) {
+    tr_gemm64_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
+    if (csum) tr_colsum(st, (N + 31) / 32, Bm, bk, nullptr, K, N, 0, csum, csum_alpha, 1.f);
+  } else {
+    tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, csum, csum_alpha);
+  }
 }
 // One Dense layer of a tower, forward: h = dropout(relu(in W + bias)).  At the reference's batch (M <= 32) the bias / ReLU / dropout
 // ride in the product's epilogue -- one launch instead of two on a chain where every link costs 3-5 us.
@@ -1189,9 +1208,7 @@ static int tr_step(float* arena, const int64_t* row_off, int F, int k, const voi
     // gradient w.r.t. this layer's input with the OLD weights: [B,N] x [N,Kd]  (B(k, n) = W[n * N + k])
     float* dst = l > 0 ? gn : dx;
     tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), ctl);
-    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);                           // W -= lr * in^T g
-    if (h_layers[l].bias)
-      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f, const_cast<float*>(h_layers[l].bias), -lr);                           // W -= lr * in^T g
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- FM backward (old w1, v), then its updates
@@ -1355,9 +1372,7 @@ extern "C" int ctrhot_dcn_train_step_f32(float* arena, const int64_t* row_off, i
       tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : dx;
     tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
-    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
-    if (h_layers[l].bias)
-      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f, const_cast<float*>(h_layers[l].bias), -lr);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- cross layers backward (old w_l, old fk), dx += its share; then the updates of w_l, b_l and of the final Dense
@@ -1469,9 +1484,7 @@ extern "C" int ctrhot_pnn_train_step_f32(float* arena, const int64_t* row_off, i
       tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : dx;
     tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
-    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
-    if (h_layers[l].bias)
-      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f, const_cast<float*>(h_layers[l].bias), -lr);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- product layers backward into dx's flat columns (old W), then W, then the embedding rows
@@ -1571,9 +1584,7 @@ extern "C" int ctrhot_widedeep_train_step_f32(float* arena, const int64_t* row_o
       tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : dx;
     tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
-    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
-    if (h_layers[l].bias)
-      tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f, const_cast<float*>(h_layers[l].bias), -lr);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- wide side: w <- (1 - 2 lr reg) w - lr x_w^T (dz / 2) over [dense | dense | one-hot], w0
@@ -1789,8 +1800,7 @@ extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, i
       tr_relu_drop_bwd_kernel<<<tr_grid(B * N, 256), 256, 0, st>>>(g, h, B * N, 1, dropout, seed, (uint32_t)l, nullptr);
     float* dst = l > 0 ? gn : gy;
     tr_dense_bwd_input(st, g, N, W, dst, Kd, M, l > 0 ? ws + w.h[l - 1] : nullptr, dropout, seed, (uint32_t)(l - 1), nullptr);
-    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
-    tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(h_layers[l].bias), -lr, 1.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f, const_cast<float*>(h_layers[l].bias), -lr);
     if (l > 0) { float* tmp = g; g = gn; gn = tmp; }
   }
   // ---- BatchNormalization (gamma, beta move), Bi-Interaction, embedding rows
