@@ -1695,8 +1695,7 @@ extern "C" int ctrhot_deepcrossing_train_step_f32(float* arena, const int64_t* r
       }
       float* dst = l > 0 ? (gcur == ga ? gb : ga) : g;       // the unit's input gradient lands in g, then the skip path is added
       tr_gemm(st, gcur, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);
-      tr_gemm(st, hin, 1, Kd, gcur, N, 1, W, N, Kd, N, M, -lr, 1.f);
-      tr_colsum(st, (N + 31) / 32, gcur, N, nullptr, B, N, 0, const_cast<float*>(d.bias), -lr, 1.f);
+      tr_gemm(st, hin, 1, Kd, gcur, N, 1, W, N, Kd, N, M, -lr, 1.f, const_cast<float*>(d.bias), -lr);
       gcur = dst;
     }
     tr_add_kernel<<<tr_grid(Bn, 256), 256, 0, st>>>(g, gm, Bn);
@@ -1788,8 +1787,7 @@ extern "C" int ctrhot_nfm_train_step_f32(float* arena, const int64_t* row_off, i
   {
     float* wo = const_cast<float*>(h_layers[NH].weight);
     tr_gemm(st, gd, od, 1, wo, 1, od, g, in_dim, M, in_dim, od, 1.f, 0.f);                  // [B, od] x [od, h]: B(k, n) = wo[n * od + k]
-    tr_gemm(st, in, 1, in_dim, gd, od, 1, wo, od, in_dim, od, M, -lr, 1.f);
-    tr_colsum(st, (od + 31) / 32, gd, od, nullptr, B, od, 0, const_cast<float*>(h_layers[NH].bias), -lr, 1.f);
+    tr_gemm(st, in, 1, in_dim, gd, od, 1, wo, od, in_dim, od, M, -lr, 1.f, const_cast<float*>(h_layers[NH].bias), -lr);
   }
   for (int l = NH - 1; l >= 0; --l) {
     const int N = h_layers[l].out_dim, Kd = h_layers[l].in_dim;
@@ -2021,8 +2019,7 @@ extern "C" int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int
     float* W = const_cast<float*>(tower_layers[l].weight);
     tr_prelu_bwd_kernel<<<(N + 127) / 128, 128, 0, st>>>(g, ws + w.tpre[l], const_cast<float*>(tower_layers[l].act_param), B, N, 1, lr);
     tr_gemm(st, g, N, 1, W, 1, N, gn, Kd, M, Kd, N, 1.f, 0.f);                              // through the old W
-    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f);
-    tr_colsum(st, (N + 31) / 32, g, N, nullptr, B, N, 0, const_cast<float*>(tower_layers[l].bias), -lr, 1.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, M, -lr, 1.f, const_cast<float*>(tower_layers[l].bias), -lr);
     float* tmp = g; g = gn; gn = tmp;
   }
   tr_bn_bwd_kernel<<<n, 256, 0, st>>>(g, xhat, n, B, bn_gamma, bn_beta, rstd, lr, gx);
@@ -2038,8 +2035,7 @@ extern "C" int ctrhot_din_train_step_f32(float* seq_table, int64_t seq_rows, int
     float* W = const_cast<float*>(att_layers[l].weight);
     tr_prelu_bwd_kernel<<<(T * N + 127) / 128, 128, 0, st>>>(g, ws + w.apre[l], const_cast<float*>(att_layers[l].act_param), BT, N, T, lr);
     tr_gemm(st, g, N, 1, W, 1, N, gn, Kd, BT, Kd, N, 1.f, 0.f);
-    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, BT, -lr, 1.f);
-    tr_colsum(st, (N + 31) / 32, g, N, nullptr, BT, N, 0, const_cast<float*>(att_layers[l].bias), -lr, 1.f);
+    tr_gemm(st, hin, 1, Kd, g, N, 1, W, N, Kd, N, BT, -lr, 1.f, const_cast<float*>(att_layers[l].bias), -lr);
     float* tmp = g; g = gn; gn = tmp;
   }
   // ---- the concat [q, k, q - k, q * k], then every table (all reads of the tables happened in the forward pass)
