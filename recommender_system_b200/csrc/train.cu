@@ -184,7 +184,8 @@ tr_gemm_m32_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const fl
 constexpr int TR_T64 = 64, TR_K64 = 16;
 __global__ void __launch_bounds__(256)
 tr_gemm64_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const float* __restrict__ Bm, int64_t bk, int64_t bn,
-                 float* __restrict__ C, int64_t ldc, int M, int N, int K, float alpha, float beta) {
+                 float* __restrict__ C, int64_t ldc, int M, int N, int K, float alpha, float beta,
+                 float* __restrict__ csum = nullptr, float csum_alpha = 0.f) {
   __shared__ __align__(16) float As[TR_K64][TR_T64 + 4], Bs[TR_K64][TR_T64 + 4];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   const int m0 = blockIdx.y * TR_T64, n0 = blockIdx.x * TR_T64;
@@ -197,7 +198,7 @@ tr_gemm64_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const floa
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  float ra[4], rb[4];
+  float ra[4], rb[4], cs[4] = {0.f, 0.f, 0.f, 0.f};
   auto fetch = [&](int k0) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -232,8 +233,17 @@ tr_gemm64_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const floa
       for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) cs[j] += bv[j];
     }
     __syncthreads();
+  }
+  if (csum && blockIdx.y == 0 && ty == 0) {                       // the bias gradient, as in tr_gemm_kernel
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n < N) { if (gridDim.z > 1) atomicAdd(csum + n, csum_alpha * cs[j]); else csum[n] += csum_alpha * cs[j]; }
+    }
   }
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -1089,15 +1099,14 @@ inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, con
     if (zmax > 32) zmax = 32;                                      // at most 32 roundings at the weight's own magnitude
     grid.z = z < zmax ? z : zmax;
   }
-  // csum (B must be [K, N] row-major: bn == 1): fused in the 32 x 32 kernel, a separate column sum beside the other two
+  // csum (B must be [K, N] row-major: bn == 1): fused in the tiled kernels, a separate column sum beside the small-M one
   if (M <= 32 && K >= 64 && grid.z == 1) {
     tr_gemm_m32_kernel<<<(N + 31) / 32, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, TrEpi{});
     if (csum) tr_colsum(st, (N + 31) / 32, Bm, bk, nullptr, K, N, 0, csum, csum_alpha, 1.f);
     return;
   }
   if (big) {
-    tr_gemm64_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta);
-    if (csum) tr_colsum(st, (N + 31) / 32, Bm, bk, nullptr, K, N, 0, csum, csum_alpha, 1.f);
+    tr_gemm64_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, csum, csum_alpha);
   } else {
     tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, csum, csum_alpha);
   }
