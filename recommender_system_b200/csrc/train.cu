@@ -109,7 +109,7 @@ struct TrEpi {
   uint32_t layer;
   int relu, on;
 };
-// The reference's batch of 32: M <= 32 rows.  The 32 x 32 kernel above walks K in 32-wide steps, each a global load, two barriers
+// The reference's batch of 32 (and batches up to 128 as gridDim.y blocks of 32 rows).  The 32 x 32 kernel above walks K in 32-wide steps, each a global load, two barriers
 // and 32 FMA deep -- ~1.2 us per step, 7 steps for the 221-wide first layer.  Here the 8 warps of a CTA take one eighth of the k
 // range each (A slice staged in shared memory by the warp itself, B read straight from global: every load independent), then the
 // eight partial tiles are added through shared memory in a fixed order.  One pass instead of K / 32 dependent ones.
@@ -119,6 +119,10 @@ tr_gemm_m32_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const fl
   __shared__ float sm[8][32][33];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int n = blockIdx.x * 32 + lane;
+  const int mb = blockIdx.y * 32;                                 // batches up to 128 rows: one CTA row per 32 of them
+  A += (int64_t)mb * am;
+  C += (int64_t)mb * ldc;
+  M = min(32, M - mb);
   const int kper = (K + 7) / 8, kw0 = w * kper, kw1 = min(K, kw0 + kper);
   float acc[32];
 #pragma unroll
@@ -161,16 +165,16 @@ tr_gemm_m32_kernel(const float* __restrict__ A, int64_t am, int64_t ak, const fl
         float mk = 1.f;
         if (epi.rate > 0.f) {
           const uint64_t seed = epi.seed + (epi.ctl ? epi.ctl->step : 0ull);
-          mk = (tr_uniform(seed, epi.layer, (uint64_t)m * N + nc) >= epi.rate) ? 1.f / (1.f - epi.rate) : 0.f;
+          mk = (tr_uniform(seed, epi.layer, (uint64_t)(mb + m) * N + nc) >= epi.rate) ? 1.f / (1.f - epi.rate) : 0.f;
         }
-        if (epi.relu && !(epi.bias[(int64_t)m * N + nc] > 0.f)) mk = 0.f;
+        if (epi.relu && !(epi.bias[(int64_t)(mb + m) * N + nc] > 0.f)) mk = 0.f;
         t *= mk;
       } else if (epi.on) {                                        // same arithmetic and mask index as tr_bias_relu_drop_kernel
         t += epi.bias ? epi.bias[nc] : 0.f;
         if (epi.relu) t = fmaxf(t, 0.f);
         if (epi.rate > 0.f) {
           const uint64_t seed = epi.seed + (epi.ctl ? epi.ctl->step : 0ull);
-          t = (tr_uniform(seed, epi.layer, (uint64_t)m * N + nc) >= epi.rate) ? t * (1.f / (1.f - epi.rate)) : 0.f;
+          t = (tr_uniform(seed, epi.layer, (uint64_t)(mb + m) * N + nc) >= epi.rate) ? t * (1.f / (1.f - epi.rate)) : 0.f;
         }
       }
       *c = t;
@@ -1100,8 +1104,8 @@ inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, con
     grid.z = z < zmax ? z : zmax;
   }
   // csum (B must be [K, N] row-major: bn == 1): fused in the tiled kernels, a separate column sum beside the small-M one
-  if (M <= 32 && K >= 64 && grid.z == 1) {
-    tr_gemm_m32_kernel<<<(N + 31) / 32, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, TrEpi{});
+  if (M <= 128 && K >= 64 && grid.z == 1) {
+    tr_gemm_m32_kernel<<<dim3((N + 31) / 32, (M + 31) / 32), 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, TrEpi{});
     if (csum) tr_colsum(st, (N + 31) / 32, Bm, bk, nullptr, K, N, 0, csum, csum_alpha, 1.f);
     return;
   }
@@ -1111,19 +1115,19 @@ inline void tr_gemm(cudaStream_t st, const float* A, int64_t am, int64_t ak, con
     tr_gemm_kernel<<<grid, 256, 0, st>>>(A, am, ak, Bm, bk, bn, C, ldc, M, N, K, alpha, beta, csum, csum_alpha);
   }
 }
+inline bool tr_m32_ok(int M, int K) { return M <= 128 && K >= 64; }
 // One Dense layer of a tower, forward: h = dropout(relu(in W + bias)).  At the reference's batch (M <= 32) the bias / ReLU / dropout
 // ride in the product's epilogue -- one launch instead of two on a chain where every link costs 3-5 us.
 inline void tr_dense_fwd(cudaStream_t st, const float* in, int in_dim, const float* W, const float* bias, int N, float* h, int M,
                          int relu, float rate, uint64_t seed, uint32_t layer, const TrCtl* ctl) {
-  if (M <= 32 && in_dim >= 64) {
+  if (tr_m32_ok(M, in_dim)) {
     TrEpi e{bias, ctl, seed, rate, layer, relu, 1};
-    tr_gemm_m32_kernel<<<(N + 31) / 32, 256, 0, st>>>(in, in_dim, 1, W, N, 1, h, N, M, N, in_dim, 1.f, 0.f, e);
+    tr_gemm_m32_kernel<<<dim3((N + 31) / 32, (M + 31) / 32), 256, 0, st>>>(in, in_dim, 1, W, N, 1, h, N, M, N, in_dim, 1.f, 0.f, e);
     return;
   }
   tr_gemm(st, in, in_dim, 1, W, N, 1, h, N, M, N, in_dim, 1.f, 0.f);
   tr_bias_relu_drop_kernel<<<tr_grid((int64_t)M * N, 256), 256, 0, st>>>(h, bias, N, M, relu, rate, seed, layer, ctl);
 }
-inline bool tr_m32_ok(int M, int K) { return M <= 32 && K >= 64; }
 // Gradient w.r.t. a Dense layer's input through the OLD weights, dst [M, Kd] = g [M, N] W^T; when hprev (the activations of the
 // layer below, [M, Kd]) is given and the small-M product runs, that layer's ReLU / dropout derivative is applied in the epilogue
 // (what tr_relu_drop_bwd_kernel would do as the next launch) -- the loops test the same condition before launching that kernel.
@@ -1131,7 +1135,7 @@ inline void tr_dense_bwd_input(cudaStream_t st, const float* g, int N, const flo
                                float rate, uint64_t seed, uint32_t layer, const TrCtl* ctl) {
   if (hprev && tr_m32_ok(M, N)) {
     TrEpi e{hprev, ctl, seed, rate, layer, 1, 2};
-    tr_gemm_m32_kernel<<<(Kd + 31) / 32, 256, 0, st>>>(g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f, e);
+    tr_gemm_m32_kernel<<<dim3((Kd + 31) / 32, (M + 31) / 32), 256, 0, st>>>(g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f, e);
     return;
   }
   tr_gemm(st, g, N, 1, W, 1, N, dst, Kd, M, Kd, N, 1.f, 0.f);

@@ -86,6 +86,8 @@ def close(got, want, before, what, floor=2e-7):
     (1, [11] * 26, 4, 4, (16,), 0.0),
     (257, [50, 7, 1000, 3] + [20] * 22, 16, 8, (64, 32), 0.2),
     (4096, [5000] * 26, 8, 10, (256, 128, 64), 0.2),
+    (96, [50, 7, 1000, 3] + [20] * 22, 8, 10, (256, 128, 64), 0.2),      # three 32-row blocks of the small-batch product
+    (128, [5000] * 26, 8, 10, (256, 128, 64), 0.0),
 ])
 def test_one_step_against_the_oracle(lib, B, vocab, k_embed, k_fm, hidden, rate):
     m = make_model(vocab, k_embed, k_fm, hidden, rate)
